@@ -1,0 +1,310 @@
+"""Oracle: closed-form potential energy U(z) and gradient for the four registered
+model families.  TEST INFRASTRUCTURE (see ``oracle/__init__.py``).
+
+The reference derives U by tracing a model through its effect handlers
+(``numpyro/infer/util.py:302-327`` ``potential_energy`` -> ``:109-124``
+``log_density``), substituting ``value = t(z)`` and adding ``log|det J|`` for
+every constrained site (``:269-299`` ``_unconstrain_reparam``), and gets the
+gradient by reverse-mode AD (``hmc_util.py:242-252``).  Here each family's U is
+written out from the distributions' ``log_prob`` formulas and differentiated by
+hand; ``tests/test_oracle_potentials.py`` checks the log-probs against scipy and
+the gradients against central finite differences in float64.
+
+Flattening follows ``ravel_pytree`` on the site dict = sorted site names
+(SURVEY.md section 8a "Flattening rule").
+"""
+import math
+
+import numpy as np
+
+LOG_SQRT_2PI = 0.5 * math.log(2.0 * math.pi)
+
+
+def _lgamma(x):
+    from scipy.special import gammaln
+
+    return gammaln(x)
+
+
+def _digamma(x):
+    from scipy.special import digamma
+
+    return digamma(x)
+
+
+class Family:
+    """A registered potential family: flat dimension, site table, U and grad."""
+
+    name = ""
+    #: (site, size) in model TRACE order (init draws happen in this order,
+    #: ``numpyro/infer/util.py:425-432``)
+    trace_sites = ()
+
+    def __init__(self, dtype=np.float32):
+        self.dtype = np.dtype(dtype)
+
+    @property
+    def dim(self):
+        return sum(s for _, s in self.trace_sites)
+
+    @property
+    def flat_sites(self):
+        """(site, size, offset) in flat (sorted-name) order."""
+        out, off = [], 0
+        for k, s in sorted(self.trace_sites):
+            out.append((k, s, off))
+            off += s
+        return out
+
+    def offsets(self):
+        return {k: (off, s) for k, s, off in self.flat_sites}
+
+    def unravel(self, z):
+        return {k: z[..., off:off + s] for k, s, off in self.flat_sites}
+
+    def potential_and_grad(self, z):
+        raise NotImplementedError
+
+    def constrain(self, z):
+        """postprocess_fn (``infer/util.py:176-230,583-609``): constrained sites +
+        deterministic sites."""
+        raise NotImplementedError
+
+
+# --------------------------------------------------------------------------
+# Bayesian logistic regression: examples/covtype.py:66-71
+# --------------------------------------------------------------------------
+class Logistic(Family):
+    """coefs ~ Normal(0, 1)[D]; obs ~ Bernoulli(logits = X @ coefs).
+
+    Normal.log_prob: ``continuous.py:2203-2207``; Bernoulli-logits log_prob =
+    ``-binary_cross_entropy_with_logits`` (``discrete.py:137-139``,
+    ``distributions/util.py:295-298``).
+    """
+
+    name = "logistic"
+
+    def __init__(self, X, y, dtype=np.float32):
+        super().__init__(dtype)
+        self.X = np.ascontiguousarray(X, dtype=self.dtype)
+        self.y = np.ascontiguousarray(y).astype(self.dtype)
+        self.trace_sites = (("coefs", self.X.shape[1]),)
+
+    def potential_and_grad(self, z):
+        f = self.dtype.type
+        z = np.asarray(z, self.dtype)
+        logits = self.X @ z
+        # -log N(z; 0, 1) = 0.5 z^2 + log sqrt(2 pi)
+        prior = (f(0.5) * z * z + f(LOG_SQRT_2PI)).sum(dtype=self.dtype)
+        e = np.exp(-np.abs(logits))
+        bce = np.maximum(logits, f(0)) + np.log1p(e) - logits * self.y
+        U = prior + bce.sum(dtype=self.dtype)
+        sig = np.where(logits >= 0, f(1) / (f(1) + e), e / (f(1) + e)).astype(self.dtype)
+        grad = z + self.X.T @ (sig - self.y)
+        return self.dtype.type(U), grad.astype(self.dtype)
+
+    def constrain(self, z):
+        return {"coefs": np.asarray(z)}
+
+
+# --------------------------------------------------------------------------
+# Eight schools, non-centred: README.md:101-110 with TransformReparam
+# (reparam.py:159-185): latent sites mu, tau, theta_base; theta deterministic.
+# --------------------------------------------------------------------------
+class EightSchools(Family):
+    """z = [mu, log tau, theta_base[J]].
+
+    mu ~ Normal(0, 5); tau ~ HalfCauchy(5) (``continuous.py:238-244,721-723``)
+    through ExpTransform (``transforms.py:563-571``: log|J| = z);
+    theta_base ~ Normal(0, 1); obs ~ Normal(mu + tau * theta_base, sigma).
+    """
+
+    name = "eight_schools"
+
+    def __init__(self, sigma, y, dtype=np.float32):
+        super().__init__(dtype)
+        self.sigma = np.asarray(sigma, self.dtype)
+        self.y = np.asarray(y, self.dtype)
+        self.J = self.y.shape[0]
+        self.trace_sites = (("mu", 1), ("tau", 1), ("theta_base", self.J))
+
+    def potential_and_grad(self, z):
+        f = self.dtype.type
+        z = np.asarray(z, self.dtype)
+        mu, tu, b = z[0], z[1], z[2:]
+        tau = np.exp(tu)
+        # log N(mu; 0, 5)
+        lp = -f(0.5) * (mu / f(5)) ** 2 - np.log(f(math.sqrt(2 * math.pi)) * f(5))
+        # log HalfCauchy(tau; 5) + jacobian
+        q = tau / f(5)
+        lp = lp + (f(math.log(2.0)) - f(math.log(math.pi)) - np.log(f(5)) - np.log1p(q * q)) + tu
+        # theta_base
+        lp = lp + (-f(0.5) * b * b - f(LOG_SQRT_2PI)).sum(dtype=self.dtype)
+        # obs
+        theta = mu + tau * b
+        resid = (self.y - theta) / self.sigma
+        lp = lp + (-f(0.5) * resid * resid - np.log(f(math.sqrt(2 * math.pi)) * self.sigma)).sum(
+            dtype=self.dtype
+        )
+        # gradient of U = -lp
+        dtheta = -(resid / self.sigma)  # dU/dtheta_j
+        g = np.empty_like(z)
+        g[0] = mu / f(25) + dtheta.sum(dtype=self.dtype)
+        g[1] = (f(2) * q * q / (f(1) + q * q)) - f(1) + tau * (dtheta * b).sum(dtype=self.dtype)
+        g[2:] = b + tau * dtheta
+        return self.dtype.type(-lp), g
+
+    def constrain(self, z):
+        z = np.asarray(z)
+        mu, tau, b = z[..., 0], np.exp(z[..., 1]), z[..., 2:]
+        return {"mu": mu, "tau": tau, "theta_base": b,
+                "theta": mu[..., None] + tau[..., None] * b}
+
+
+# --------------------------------------------------------------------------
+# Horseshoe regression: examples/horseshoe_regression.py:37-78
+# --------------------------------------------------------------------------
+class Horseshoe(Family):
+    """z = [lambdas_u[D], (prec_obs_u,) tau_u, unscaled_betas[D]] (sorted names).
+
+    lambdas ~ HalfCauchy(1)[D], tau ~ HalfCauchy(1)[1] (exp transform + log|J|),
+    unscaled_betas ~ Normal(0,1)[D]; betas = tau*lambdas*unscaled_betas;
+    likelihood "bernoulli": Y ~ Bernoulli(logits = X betas) (``:78``) or
+    "normal": prec_obs ~ Gamma(3,1) (``continuous.py:515-525``),
+    Y ~ Normal(X betas, prec_obs**-0.5) (``:54-58``).
+    """
+
+    name = "horseshoe"
+
+    def __init__(self, X, Y, likelihood="bernoulli", dtype=np.float32):
+        super().__init__(dtype)
+        assert likelihood in ("bernoulli", "normal")
+        self.likelihood = likelihood
+        self.X = np.ascontiguousarray(X, dtype=self.dtype)
+        self.Y = np.asarray(Y).astype(self.dtype)
+        D = self.X.shape[1]
+        self.D = D
+        if likelihood == "normal":
+            self.trace_sites = (("lambdas", D), ("tau", 1), ("unscaled_betas", D), ("prec_obs", 1))
+        else:
+            self.trace_sites = (("lambdas", D), ("tau", 1), ("unscaled_betas", D))
+
+    def potential_and_grad(self, z):
+        f = self.dtype.type
+        z = np.asarray(z, self.dtype)
+        off = self.offsets()
+        lu = z[off["lambdas"][0]:off["lambdas"][0] + self.D]
+        tu = z[off["tau"][0]]
+        ub = z[off["unscaled_betas"][0]:off["unscaled_betas"][0] + self.D]
+        lam, tau = np.exp(lu), np.exp(tu)
+        c_hc = f(math.log(2.0) - math.log(math.pi))
+        lp = (c_hc - np.log1p(lam * lam) + lu).sum(dtype=self.dtype)
+        lp = lp + (c_hc - np.log1p(tau * tau) + tu)
+        lp = lp + (-f(0.5) * ub * ub - f(LOG_SQRT_2PI)).sum(dtype=self.dtype)
+        beta = tau * lam * ub
+        m = self.X @ beta
+        g = np.zeros_like(z)
+        if self.likelihood == "bernoulli":
+            e = np.exp(-np.abs(m))
+            lp = lp - (np.maximum(m, f(0)) + np.log1p(e) - m * self.Y).sum(dtype=self.dtype)
+            sig = np.where(m >= 0, f(1) / (f(1) + e), e / (f(1) + e)).astype(self.dtype)
+            dm = sig - self.Y  # dU/dm
+        else:
+            pu = z[off["prec_obs"][0]]
+            prec = np.exp(pu)
+            # Gamma(3, 1): (a-1) log x - x - lgamma(a) ; + jacobian pu
+            lp = lp + (f(2) * pu - prec - f(math.lgamma(3.0))) + pu
+            resid = self.Y - m
+            n = f(self.Y.shape[0])
+            # log N(Y; m, prec^-1/2) = -0.5 prec r^2 - log(sqrt(2pi)) + 0.5 log prec
+            ss = (resid * resid).sum(dtype=self.dtype)
+            lp = lp + (-f(0.5) * prec * ss - n * f(LOG_SQRT_2PI) + f(0.5) * n * pu)
+            dm = -prec * resid
+            g[off["prec_obs"][0]] = -(f(3) - prec) + f(0.5) * prec * ss - f(0.5) * n
+        dbeta = self.X.T @ dm  # dU/dbeta
+        g[off["lambdas"][0]:off["lambdas"][0] + self.D] = (
+            f(2) * lam * lam / (f(1) + lam * lam) - f(1) + dbeta * beta
+        )
+        g[off["tau"][0]] = f(2) * tau * tau / (f(1) + tau * tau) - f(1) + (dbeta * beta).sum(
+            dtype=self.dtype
+        )
+        g[off["unscaled_betas"][0]:off["unscaled_betas"][0] + self.D] = ub + dbeta * tau * lam
+        return self.dtype.type(-lp), g
+
+    def constrain(self, z):
+        z = np.asarray(z)
+        off = self.offsets()
+        out = {}
+        for k, (o, s) in off.items():
+            v = z[..., o:o + s]
+            out[k] = v if k == "unscaled_betas" else np.exp(v)
+        if "prec_obs" in out:
+            out["prec_obs"] = out["prec_obs"][..., 0]
+        out["betas"] = out["tau"] * out["lambdas"] * out["unscaled_betas"]
+        return out
+
+
+# --------------------------------------------------------------------------
+# Stochastic volatility: examples/stochastic_volatility.py:57-65
+# --------------------------------------------------------------------------
+class StochasticVolatility(Family):
+    """z = [nu_u, s[T], sigma_u] (sorted names: nu, s, sigma).
+
+    sigma ~ Exponential(50) (``continuous.py:473-475``), s ~
+    GaussianRandomWalk(sigma, T) (``:684-689``; support real_vector -> no
+    transform, ``infer/util.py:287-291``), nu ~ Exponential(0.1),
+    r ~ StudentT(nu, 0, exp(s)) (``:2375-2385``).
+    """
+
+    name = "stochastic_volatility"
+
+    def __init__(self, returns, dtype=np.float32):
+        super().__init__(dtype)
+        self.r = np.asarray(returns, self.dtype)
+        self.T = self.r.shape[0]
+        self.trace_sites = (("sigma", 1), ("s", self.T), ("nu", 1))
+
+    def potential_and_grad(self, z):
+        f = self.dtype.type
+        z = np.asarray(z, self.dtype)
+        T = self.T
+        nu_u, s, sg_u = z[0], z[1:1 + T], z[1 + T]
+        nu, sg = np.exp(nu_u), np.exp(sg_u)
+        lp = (f(math.log(50.0)) - f(50) * sg) + sg_u
+        lp = lp + (f(math.log(0.1)) - f(0.1) * nu) + nu_u
+        # GRW: N(s0; 0, sg) * prod N(s_t; s_{t-1}, sg)
+        d = np.empty_like(s)
+        d[0] = s[0]
+        d[1:] = s[1:] - s[:-1]
+        ds = d / sg
+        lp = lp + (-f(0.5) * ds * ds).sum(dtype=self.dtype) - f(T) * (f(LOG_SQRT_2PI) + sg_u)
+        # StudentT
+        y = self.r * np.exp(-s)
+        y2n = y * y / nu
+        zt = f(0.5) * nu_u + f(0.5 * math.log(math.pi)) + f(_lgamma(0.5 * float(nu))) - f(
+            _lgamma(0.5 * (float(nu) + 1.0))
+        )
+        l1p = np.log1p(y2n)
+        lp = lp + (-f(0.5) * (nu + f(1)) * l1p - s).sum(dtype=self.dtype) - f(T) * zt
+        g = np.empty_like(z)
+        # d/ds_t of -GRW
+        gs = ds / sg  # dU/dd_t
+        gs_full = gs.copy()
+        gs_full[:-1] -= gs[1:]
+        # d/ds_t of -StudentT: 1 - (nu+1) * y2n/(1+y2n)
+        w = y2n / (f(1) + y2n)
+        g[1:1 + T] = gs_full + (f(1) - (nu + f(1)) * w)
+        # d/dsigma_u
+        g[1 + T] = f(50) * sg - f(1) - (ds * ds).sum(dtype=self.dtype) + f(T)
+        # d/dnu_u: nu * d/dnu
+        dig = f(_digamma(0.5 * float(nu))) - f(_digamma(0.5 * (float(nu) + 1.0)))
+        dnu = (f(0.5) * l1p - f(0.5) * (nu + f(1)) * w / nu).sum(dtype=self.dtype) + f(T) * (
+            f(0.5) / nu + f(0.5) * dig
+        )
+        g[0] = f(0.1) * nu - f(1) + nu * dnu
+        return self.dtype.type(-lp), g
+
+    def constrain(self, z):
+        z = np.asarray(z)
+        T = self.T
+        return {"nu": np.exp(z[..., 0]), "s": z[..., 1:1 + T], "sigma": np.exp(z[..., 1 + T])}
