@@ -1,0 +1,177 @@
+/* b200mc -- C ABI of the B200-native HMC/NUTS sampling hot path.
+ *
+ * The reference (NumPyro 0.18.0) has no FFI of its own: its hot path sits behind the
+ * Python MCMCKernel interface (numpyro/infer/mcmc.py:32-158) implemented by HMC/NUTS
+ * (numpyro/infer/hmc.py:541-948).  Each entry point below names the reference
+ * function it replaces; INTEGRATION.md shows the ctypes / jax.ffi binding.
+ *
+ * Conventions: plain pointers and sizes only.  Pointers named *_dev are DEVICE
+ * pointers on the handle's device, owned by the caller; *_host are host pointers.
+ * All work is enqueued on the caller's stream (a cudaStream_t passed as void*;
+ * NULL = default stream).  Functions return 0 on success, non-zero on failure;
+ * b200mc_last_error() describes the last failure of the calling thread.  A handle is
+ * not thread-safe; distinct handles are independent.  float32 / int32 / uint32 only,
+ * flat vectors in sorted-site-name order (jax ravel_pytree order).
+ */
+#ifndef B200MC_H_
+#define B200MC_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200mc_handle b200mc_handle;
+
+enum { B200MC_LOGISTIC = 0, B200MC_EIGHT_SCHOOLS = 1, B200MC_HORSESHOE = 2, B200MC_SV = 3 };
+enum { B200MC_NUTS = 0, B200MC_HMC = 1 };
+
+/* Arguments of NUTS.__init__/HMC.__init__ (hmc.py:625-642, 913-930) + MCMC's
+ * num_warmup/num_chains (mcmc.py:323-335) + the registered model family and its data
+ * (the `model_args` of MCMC.run). */
+typedef struct {
+  int family;
+  int num_chains;
+  /* data, device pointers:
+   *   LOGISTIC      data0 = X[N][ncols] float32 row-major, data1 = labels[N] uint8
+   *   EIGHT_SCHOOLS data0 = y[N] float32, data1 = sigma[N] float32
+   *   SV            data0 = returns[N] float32, data1 = NULL                         */
+  int N;
+  int ncols;
+  const void* data0_dev;
+  const void* data1_dev;
+  int algo;
+  float step_size;
+  int adapt_step_size;
+  int adapt_mass_matrix;
+  int dense_mass;               /* must be 0 in this round: raises otherwise */
+  int regularize_mass_matrix;
+  float target_accept_prob;
+  int max_tree_depth_warmup;    /* max_tree_depth=(d1, d2): hmc.py:299-303 */
+  int max_tree_depth_sample;
+  int num_warmup;
+  int has_trajectory_length;    /* HMC */
+  float trajectory_length;
+  int num_steps;                /* HMC: <= 0 means None */
+  int threefry_partitionable;   /* jax_threefry_partitionable: 1 = JAX >= 0.5 default */
+  float init_radius;            /* init_to_uniform(radius=2) (initialization.py:95) */
+  const float* inverse_mass_matrix_dev; /* [D] diagonal or NULL (identity) */
+} b200mc_config;
+
+/* Scalar leaves of HMCState (hmc.py:31-48) and HMCAdaptState (hmc_util.py:18-30). */
+typedef struct {
+  int32_t i;
+  float potential_energy;
+  float energy;
+  int32_t num_steps;
+  float accept_prob;
+  float mean_accept_prob;
+  int32_t diverging;
+  uint32_t rng_key[2];
+  float step_size;
+  float ss_x_t, ss_x_avg, ss_g_avg;
+  int32_t ss_t;
+  float ss_prox_center;
+  int32_t mm_n;
+  int32_t window_idx;
+  uint32_t adapt_key[2];
+  int32_t status;       /* 1: "Cannot find valid initial parameters" (infer/util.py:795) */
+  int32_t init_tries;
+  int64_t grad_evals;   /* cumulative potential+gradient evaluations of this chain */
+} b200mc_chain_scalars;
+
+/* Vector leaves, each [num_chains][D] float32. */
+enum {
+  B200MC_VEC_Z = 0,
+  B200MC_VEC_Z_GRAD = 1,
+  B200MC_VEC_INVERSE_MASS_MATRIX = 2,
+  B200MC_VEC_MASS_MATRIX_SQRT = 3,
+  B200MC_VEC_WELFORD_MEAN = 4,
+  B200MC_VEC_WELFORD_M2 = 5
+};
+
+/* Collection buffers of fori_collect (numpyro/util.py:277-407): [n_keep][num_chains][...]
+ * device arrays, any of which may be NULL. */
+typedef struct {
+  int n_keep;
+  float* z_dev;                 /* [n_keep][C][D] unconstrained draws */
+  float* potential_energy_dev;  /* [n_keep][C] */
+  float* energy_dev;
+  int32_t* num_steps_dev;
+  float* accept_prob_dev;
+  float* mean_accept_prob_dev;
+  int32_t* diverging_dev;
+  float* step_size_dev;         /* adapt_state.step_size */
+} b200mc_collect;
+
+const char* b200mc_last_error(void);
+int b200mc_version(void);
+
+/* HMC.__init__ + the data binding of MCMC.run.  Raises (returns non-zero) for an
+ * unregistered family or unsupported option: there is no fallback path. */
+int b200mc_create(const b200mc_config* cfg, b200mc_handle** out);
+void b200mc_destroy(b200mc_handle* h);
+int b200mc_dim(const b200mc_handle* h);           /* flat unconstrained dimension D */
+
+/* HMC.init (hmc.py:740-799): per-chain keys uint32[C][2] (already split by the caller
+ * as MCMC.run does, mcmc.py:661-662); init_z_dev = init_params [C][D] or NULL for
+ * init_to_uniform via find_valid_initial_params (infer/util.py:335-477). */
+int b200mc_init(b200mc_handle* h, const uint32_t* keys_dev, const float* init_z_dev, void* stream);
+
+/* HMC.sample applied num_iters times inside one launch = the fori_collect loop
+ * (util.py:359-369).  Local iteration k is collected into slot
+ * (k - collect_start) / thinning when k >= collect_start (last write wins). */
+int b200mc_sample(b200mc_handle* h, int num_iters, int collect_start, int thinning,
+                  const b200mc_collect* out, void* stream);
+
+/* mcmc.last_state / post_warmup_state round trip (mcmc.py:549-578). */
+int b200mc_get_scalars(b200mc_handle* h, b200mc_chain_scalars* out_host);
+int b200mc_set_scalars(b200mc_handle* h, const b200mc_chain_scalars* in_host);
+int b200mc_get_vector(b200mc_handle* h, int which, float* out_dev, void* stream);
+int b200mc_set_vector(b200mc_handle* h, int which, const float* in_dev, void* stream);
+
+/* potential_energy + value_and_grad (infer/util.py:302-327, hmc_util.py:242-252) at
+ * n points z[n][D]: tier-2 parity hook. */
+int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, int n, float* U_dev,
+                              float* grad_dev, void* stream);
+
+/* jax.random on Threefry-2x32 (tier-1 parity hooks). */
+int b200mc_threefry2x32(const uint32_t* key_dev /*[n][2]*/, const uint32_t* ctr_dev /*[n][2]*/,
+                        uint32_t* out_dev /*[n][2]*/, int n, void* stream);
+int b200mc_random_split(const uint32_t* key_dev /*[n][2]*/, int n, int num,
+                        uint32_t* out_dev /*[n][num][2]*/, int partitionable, void* stream);
+int b200mc_random_bits(const uint32_t* key_dev /*[2]*/, int n, uint32_t* out_dev,
+                       int partitionable, void* stream);
+int b200mc_random_uniform(const uint32_t* key_dev, int n, float minval, float maxval,
+                          float* out_dev, int partitionable, void* stream);
+int b200mc_random_normal(const uint32_t* key_dev, int n, float* out_dev, int partitionable,
+                         void* stream);
+
+/* build_adaptation_schedule (hmc_util.py:387-436), host only: writes up to cap windows,
+ * returns the number of windows. */
+int b200mc_adaptation_schedule(int num_steps, int* starts_host, int* ends_host, int cap);
+
+/* Device-memory plumbing so a host binding needs nothing but this library. */
+int b200mc_device_count(void);
+int b200mc_set_device(int device);
+void* b200mc_malloc(uint64_t bytes);
+int b200mc_free(void* p_dev);
+int b200mc_memcpy_h2d(void* dst_dev, const void* src_host, uint64_t bytes, void* stream);
+int b200mc_memcpy_d2h(void* dst_host, const void* src_dev, uint64_t bytes, void* stream);
+int b200mc_memset(void* dst_dev, int value, uint64_t bytes, void* stream);
+int b200mc_stream_synchronize(void* stream);
+void* b200mc_host_alloc(uint64_t bytes);          /* pinned host memory */
+int b200mc_host_free(void* p_host);
+/* CUDA-event timing on the launching stream. */
+void* b200mc_event_create(void);
+int b200mc_event_record(void* event, void* stream);
+int b200mc_event_elapsed_ms(void* start, void* stop, float* ms_host);
+int b200mc_event_destroy(void* event);
+/* number of this library's kernels launched so far by the calling process */
+int64_t b200mc_kernel_launches(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200MC_H_ */

@@ -1,0 +1,592 @@
+// C ABI of libb200mc (declared in include/b200mc.h): handle management, launch logic.
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/b200mc.h"
+#include "chain_kernel.cuh"
+#include "glm_kernel.cuh"
+
+using namespace b200mc;
+
+static_assert(sizeof(b200mc_chain_scalars) == sizeof(ChainScalars), "ABI mirror out of sync");
+
+static thread_local std::string g_err;
+static std::atomic<int64_t> g_launches{0};
+
+static int fail(const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return 1;
+}
+#define CK(call)                                                                         \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess) return fail("%s failed: %s", #call, cudaGetErrorString(e_)); \
+  } while (0)
+
+struct b200mc_handle {
+  b200mc_config cfg;
+  int device = 0, num_sms = 0, max_smem = 0;
+  int C = 0, D = 0;
+  SamplerParams P;
+  ModelData M;
+  ChainScalars* cs = nullptr;
+  ChainVectors cv{};
+  float* work = nullptr;
+  int mode = 0, c_pad = 0;
+  // glm
+  int glm_ctas = 0, glm_rows_per_cta = 0, glm_stages = 0, glm_smem = 0;
+  float* partials = nullptr;
+  float* theta_pub = nullptr;
+  unsigned* counters = nullptr;  // [0] arrive, [1] pub_gen, [2] ctrl, [3] error
+  bool initialized = false;
+};
+
+extern "C" const char* b200mc_last_error(void) { return g_err.c_str(); }
+extern "C" int b200mc_version(void) { return 1; }
+extern "C" int64_t b200mc_kernel_launches(void) { return g_launches.load(); }
+
+// build_adaptation_schedule: hmc_util.py:387-436
+static std::vector<std::pair<int, int>> adaptation_schedule(int num_steps) {
+  std::vector<std::pair<int, int>> sch;
+  if (num_steps < 20) {
+    sch.push_back({0, num_steps - 1});
+    return sch;
+  }
+  int start_buffer = 75, end_buffer = 50, init_window = 25;
+  if (start_buffer + end_buffer + init_window > num_steps) {
+    start_buffer = (int)(0.15 * num_steps);
+    end_buffer = (int)(0.1 * num_steps);
+    init_window = num_steps - start_buffer - end_buffer;
+  }
+  sch.push_back({0, start_buffer - 1});
+  const int end_window_start = num_steps - end_buffer;
+  int next_size = init_window, next_start = start_buffer;
+  while (next_start < end_window_start) {
+    const int cur_start = next_start;
+    int cur_size = next_size;
+    if (3 * cur_size <= end_window_start - cur_start) next_size = 2 * cur_size;
+    else cur_size = end_window_start - cur_start;
+    next_start = cur_start + cur_size;
+    sch.push_back({cur_start, next_start - 1});
+  }
+  sch.push_back({end_window_start, num_steps - 1});
+  return sch;
+}
+
+extern "C" int b200mc_adaptation_schedule(int num_steps, int* starts, int* ends, int cap) {
+  auto sch = adaptation_schedule(num_steps);
+  for (size_t i = 0; i < sch.size() && (int)i < cap; ++i) {
+    starts[i] = sch[i].first;
+    ends[i] = sch[i].second;
+  }
+  return (int)sch.size();
+}
+
+static int family_sites(const b200mc_config& c, SamplerParams& P, int& D) {
+  // sites in TRACE order with their offsets in the flat (sorted-name) vector
+  switch (c.family) {
+    case B200MC_LOGISTIC:  // coefs
+      D = c.ncols;
+      P.nsites = 1; P.site_off[0] = 0; P.site_size[0] = D;
+      return 0;
+    case B200MC_EIGHT_SCHOOLS:  // trace: mu, tau, theta_base == sorted
+      D = 2 + c.N;
+      P.nsites = 3;
+      P.site_off[0] = 0; P.site_size[0] = 1;
+      P.site_off[1] = 1; P.site_size[1] = 1;
+      P.site_off[2] = 2; P.site_size[2] = c.N;
+      return 0;
+    case B200MC_SV:  // trace: sigma, s, nu; sorted: nu, s, sigma
+      D = 2 + c.N;
+      P.nsites = 3;
+      P.site_off[0] = 1 + c.N; P.site_size[0] = 1;
+      P.site_off[1] = 1;       P.site_size[1] = c.N;
+      P.site_off[2] = 0;       P.site_size[2] = 1;
+      return 0;
+    default:
+      return fail("model family %d is not a registered potential family "
+                  "(logistic=0, eight_schools=1, stochastic_volatility=3); no fallback", c.family);
+  }
+}
+
+extern "C" void b200mc_destroy(b200mc_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaFree(h->cs);
+  cudaFree(h->cv.z); cudaFree(h->cv.z_grad); cudaFree(h->cv.inverse_mass_matrix);
+  cudaFree(h->cv.mass_matrix_sqrt); cudaFree(h->cv.welford_mean); cudaFree(h->cv.welford_m2);
+  cudaFree(h->work); cudaFree(h->partials); cudaFree(h->theta_pub); cudaFree(h->counters);
+  delete h;
+}
+
+extern "C" int b200mc_dim(const b200mc_handle* h) { return h ? h->D : -1; }
+
+extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
+  if (!cfg || !out) return fail("null argument");
+  *out = nullptr;
+  const b200mc_config& c = *cfg;
+  if (c.num_chains < 1) return fail("num_chains must be >= 1");
+  if (c.dense_mass) return fail("dense_mass=True is not implemented yet (diagonal mass only)");
+  if (c.algo != B200MC_NUTS && c.algo != B200MC_HMC)
+    return fail("`algo` must be one of `HMC` or `NUTS`.");
+  if (c.algo == B200MC_HMC && c.num_steps <= 0 && !c.has_trajectory_length)
+    return fail("At least one of `num_steps` or `trajectory_length` must be specified.");
+  if (c.max_tree_depth_warmup < 1 || c.max_tree_depth_sample < 1 ||
+      c.max_tree_depth_warmup > kMaxTreeDepth || c.max_tree_depth_sample > kMaxTreeDepth)
+    return fail("max_tree_depth must be in [1, %d]", kMaxTreeDepth);
+  if (c.N < 1 || !c.data0_dev) return fail("model data missing");
+
+  auto* h = new b200mc_handle();
+  h->cfg = c;
+  SamplerParams& P = h->P;
+  memset(&P, 0, sizeof(P));
+  if (family_sites(c, P, h->D)) { delete h; return 1; }
+  cudaGetDevice(&h->device);
+  cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, h->device);
+  cudaDeviceGetAttribute(&h->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device);
+  const int C = h->C = c.num_chains, D = h->D;
+  P.D = D;
+  P.algo = c.algo;
+  P.max_depth_warmup = c.max_tree_depth_warmup;
+  P.max_depth_sample = c.max_tree_depth_sample;
+  P.max_depth = c.max_tree_depth_warmup > c.max_tree_depth_sample ? c.max_tree_depth_warmup
+                                                                  : c.max_tree_depth_sample;
+  P.num_warmup = c.num_warmup;
+  P.adapt_step_size = c.adapt_step_size;
+  P.adapt_mass_matrix = c.adapt_mass_matrix;
+  P.regularize_mass_matrix = c.regularize_mass_matrix;
+  P.partitionable = c.threefry_partitionable;
+  P.target_accept_prob = c.target_accept_prob;
+  P.init_step_size = c.step_size;
+  P.has_trajectory_length = c.has_trajectory_length;
+  P.trajectory_length = c.trajectory_length;
+  P.fixed_num_steps = c.num_steps;
+  P.max_delta_energy = 1000.0f;  // hmc.py:188
+  P.init_radius = c.init_radius > 0.f ? c.init_radius : 2.0f;
+  auto sch = adaptation_schedule(c.num_warmup);
+  if ((int)sch.size() > kMaxWindows) { delete h; return fail("too many adaptation windows"); }
+  P.num_windows = (int)sch.size();
+  for (size_t i = 0; i < sch.size(); ++i) P.window_end[i] = sch[i].second;
+
+  h->M.family = c.family;
+  h->M.N = c.N;
+  h->M.D = D;
+  h->M.a = (const float*)c.data0_dev;
+  h->M.b = (const float*)c.data1_dev;
+
+  const size_t vec_bytes = (size_t)C * D * sizeof(float);
+  auto alloc = [&](void** p, size_t bytes) {
+    cudaError_t e = cudaMalloc(p, bytes);
+    if (e == cudaSuccess) e = cudaMemset(*p, 0, bytes);
+    return e;
+  };
+#define ACK(call)                                             \
+  do {                                                        \
+    cudaError_t e_ = (call);                                  \
+    if (e_ != cudaSuccess) {                                  \
+      fail("%s failed: %s", #call, cudaGetErrorString(e_));   \
+      b200mc_destroy(h);                                      \
+      return 1;                                               \
+    }                                                         \
+  } while (0)
+  ACK(alloc((void**)&h->cs, sizeof(ChainScalars) * C));
+  ACK(alloc((void**)&h->cv.z, vec_bytes));
+  ACK(alloc((void**)&h->cv.z_grad, vec_bytes));
+  ACK(alloc((void**)&h->cv.inverse_mass_matrix, vec_bytes));
+  ACK(alloc((void**)&h->cv.mass_matrix_sqrt, vec_bytes));
+  ACK(alloc((void**)&h->cv.welford_mean, vec_bytes));
+  ACK(alloc((void**)&h->cv.welford_m2, vec_bytes));
+
+  const int nslots = num_slots(P.max_depth);
+  if (c.family == B200MC_LOGISTIC) {
+    if (D > kGlmMaxD) { b200mc_destroy(h); return fail("logistic: D=%d > %d not supported", D, kGlmMaxD); }
+    if (!c.data1_dev) { b200mc_destroy(h); return fail("logistic: labels missing"); }
+    if (((uintptr_t)c.data0_dev & 15) || ((uintptr_t)c.data1_dev & 15)) {
+      b200mc_destroy(h);
+      return fail("logistic: X and labels must be 16-byte aligned device pointers");
+    }
+    int ctas = (c.N + 1023) / 1024;
+    if (ctas > h->num_sms) ctas = h->num_sms;
+    if (ctas < 1) ctas = 1;
+    int rpc = (c.N + ctas - 1) / ctas;
+    rpc = (rpc + kGlmTileRows - 1) / kGlmTileRows * kGlmTileRows;
+    ctas = (c.N + rpc - 1) / rpc;
+    h->glm_ctas = ctas;
+    h->glm_rows_per_cta = rpc;
+    // as many ring stages as shared memory allows (<= 64)
+    int ns = 64;
+    while (ns > 2 && glm_smem_layout(D, ns, P.max_depth).total > h->max_smem) --ns;
+    if (glm_smem_layout(D, ns, P.max_depth).total > h->max_smem) {
+      b200mc_destroy(h);
+      return fail("logistic: shared memory layout does not fit");
+    }
+    h->glm_stages = ns;
+    h->glm_smem = glm_smem_layout(D, ns, P.max_depth).total;
+    ACK(cudaFuncSetAttribute(glm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->glm_smem));
+    int occ = 0;
+    ACK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, glm_kernel, kGlmThreads, h->glm_smem));
+    if (occ < 1) { b200mc_destroy(h); return fail("logistic kernel does not fit on an SM"); }
+    ACK(alloc((void**)&h->partials, sizeof(float) * (size_t)ctas * (D + 1)));
+    ACK(alloc((void**)&h->theta_pub, sizeof(float) * D));
+    ACK(alloc((void**)&h->counters, sizeof(unsigned) * 8));
+  } else {
+    h->mode = (D <= 32) ? 0 : (D <= 512 ? 1 : 2);
+    h->c_pad = (C + 31) / 32 * 32;
+    const size_t chains = (h->mode == 0) ? (size_t)h->c_pad : (size_t)C;
+    ACK(alloc((void**)&h->work, sizeof(float) * chains * nslots * D));
+  }
+#undef ACK
+  *out = h;
+  return 0;
+}
+
+// ---------------------------------------------------------------- small utility kernels
+__global__ void init_vectors_kernel(ChainVectors cv, const float* imm_in, const float* z_in, int C,
+                                    int D) {
+  const long n = (long)C * D;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+    const int d = (int)(i % D);
+    // _initialize_mass_matrix (hmc_util.py:488-515), diagonal branch
+    const float im = imm_in ? imm_in[d] : 1.0f;
+    const float sq_inv = sqrtf(im);
+    cv.inverse_mass_matrix[i] = im;
+    cv.mass_matrix_sqrt[i] = imm_in ? 1.0f / sq_inv : 1.0f;
+    cv.welford_mean[i] = 0.f;
+    cv.welford_m2[i] = 0.f;
+    cv.z[i] = z_in ? z_in[i] : 0.f;
+    cv.z_grad[i] = 0.f;
+  }
+}
+
+static CollectSpec make_collect(int num_iters, int collect_start, int thinning,
+                                const b200mc_collect* o) {
+  CollectSpec c;
+  memset(&c, 0, sizeof(c));
+  c.num_iters = num_iters;
+  c.collect_start = collect_start;
+  c.thinning = thinning < 1 ? 1 : thinning;
+  if (o) {
+    c.n_keep = o->n_keep;
+    c.z = o->z_dev;
+    c.potential_energy = o->potential_energy_dev;
+    c.energy = o->energy_dev;
+    c.num_steps = o->num_steps_dev;
+    c.accept_prob = o->accept_prob_dev;
+    c.mean_accept_prob = o->mean_accept_prob_dev;
+    c.diverging = o->diverging_dev;
+    c.step_size = o->step_size_dev;
+  }
+  return c;
+}
+
+static int launch_chain(b200mc_handle* h, const CollectSpec& col, const uint32_t* keys,
+                        int user_init, cudaStream_t st) {
+  ChainLaunch L;
+  L.P = h->P; L.M = h->M; L.col = col; L.cs = h->cs; L.cv = h->cv; L.work = h->work;
+  L.init_keys = keys; L.user_init = user_init; L.C = h->C; L.c_pad = h->c_pad;
+  if (h->mode == 0) {
+    const int threads = 64;  // small blocks spread the chains over all SMs
+    chain_kernel<0><<<(h->C + threads - 1) / threads, threads, 0, st>>>(L);
+  } else if (h->mode == 1) {
+    const int wpb = 4;
+    chain_kernel<1><<<(h->C + wpb - 1) / wpb, wpb * 32, 0, st>>>(L);
+  } else {
+    chain_kernel<2><<<h->C, 256, 0, st>>>(L);
+  }
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+static int launch_glm(b200mc_handle* h, const CollectSpec& col, const uint32_t* keys, int user_init,
+                      int chain, const float* eval_z, float* eval_U, float* eval_grad,
+                      cudaStream_t st) {
+  GlmLaunch L;
+  memset(&L, 0, sizeof(L));
+  L.P = h->P; L.col = col; L.cs = h->cs; L.cv = h->cv;
+  L.X = (const float*)h->cfg.data0_dev;
+  L.y = (const uint8_t*)h->cfg.data1_dev;
+  L.N = h->cfg.N; L.D = h->D;
+  L.rows_per_cta = h->glm_rows_per_cta;
+  L.n_stages = h->glm_stages;
+  L.partials = h->partials;
+  L.arrive = h->counters + 0;
+  L.pub_gen = h->counters + 1;
+  L.ctrl = (int*)(h->counters + 2);
+  L.error = (int*)(h->counters + 3);
+  L.theta_pub = h->theta_pub;
+  L.init_keys = keys; L.user_init = user_init; L.chain = chain; L.C = h->C;
+  L.eval_z = eval_z; L.eval_U = eval_U; L.eval_grad = eval_grad;
+  CK(cudaMemsetAsync(h->counters, 0, sizeof(unsigned) * 3, st));  // arrive, pub_gen, ctrl
+  void* args[] = {&L};
+  CK(cudaLaunchCooperativeKernel((const void*)glm_kernel, dim3(h->glm_ctas), dim3(kGlmThreads), args,
+                                 (size_t)h->glm_smem, st));
+  g_launches++;
+  return 0;
+}
+
+extern "C" int b200mc_init(b200mc_handle* h, const uint32_t* keys_dev, const float* init_z_dev,
+                           void* stream) {
+  if (!h || !keys_dev) return fail("null argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  init_vectors_kernel<<<148, 256, 0, st>>>(h->cv, h->cfg.inverse_mass_matrix_dev, init_z_dev, h->C,
+                                           h->D);
+  g_launches++;
+  CK(cudaGetLastError());
+  CK(cudaMemsetAsync(h->cs, 0, sizeof(ChainScalars) * h->C, st));
+  const CollectSpec col = make_collect(0, 0, 1, nullptr);
+  const int user_init = init_z_dev ? 1 : 0;
+  if (h->cfg.family == B200MC_LOGISTIC) {
+    for (int c = 0; c < h->C; ++c)
+      if (launch_glm(h, col, keys_dev, user_init, c, nullptr, nullptr, nullptr, st)) return 1;
+  } else {
+    if (launch_chain(h, col, keys_dev, user_init, st)) return 1;
+  }
+  h->initialized = true;
+  return 0;
+}
+
+extern "C" int b200mc_sample(b200mc_handle* h, int num_iters, int collect_start, int thinning,
+                             const b200mc_collect* out, void* stream) {
+  if (!h) return fail("null handle");
+  if (!h->initialized) return fail("b200mc_sample called before b200mc_init / b200mc_set_*");
+  if (num_iters <= 0) return 0;
+  if (thinning < 1) return fail("thinning must be a positive integer");
+  cudaStream_t st = (cudaStream_t)stream;
+  const CollectSpec col = make_collect(num_iters, collect_start, thinning, out);
+  if (h->cfg.family == B200MC_LOGISTIC) {
+    for (int c = 0; c < h->C; ++c)
+      if (launch_glm(h, col, nullptr, 0, c, nullptr, nullptr, nullptr, st)) return 1;
+    return 0;
+  }
+  return launch_chain(h, col, nullptr, 0, st);
+}
+
+extern "C" int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, int n, float* U_dev,
+                                         float* grad_dev, void* stream) {
+  if (!h || !z_dev || !U_dev || !grad_dev) return fail("null argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (h->cfg.family == B200MC_LOGISTIC) {
+    const CollectSpec col = make_collect(0, 0, 1, nullptr);
+    for (int i = 0; i < n; ++i)
+      if (launch_glm(h, col, nullptr, 0, 0, z_dev + (long)i * h->D, U_dev + i,
+                     grad_dev + (long)i * h->D, st))
+        return 1;
+    return 0;
+  }
+  if (h->mode == 0) chain_potential_kernel<0><<<(n + 63) / 64, 64, 0, st>>>(h->M, z_dev, U_dev, grad_dev, n);
+  else if (h->mode == 1) chain_potential_kernel<1><<<(n + 3) / 4, 128, 0, st>>>(h->M, z_dev, U_dev, grad_dev, n);
+  else chain_potential_kernel<2><<<n, 256, 0, st>>>(h->M, z_dev, U_dev, grad_dev, n);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------- state round trip
+extern "C" int b200mc_get_scalars(b200mc_handle* h, b200mc_chain_scalars* out_host) {
+  if (!h || !out_host) return fail("null argument");
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpy(out_host, h->cs, sizeof(ChainScalars) * h->C, cudaMemcpyDeviceToHost));
+  if (h->counters) {
+    int err = 0;
+    CK(cudaMemcpy(&err, h->counters + 3, sizeof(int), cudaMemcpyDeviceToHost));
+    if (err) return fail("grid barrier timed out inside the streaming kernel");
+  }
+  return 0;
+}
+
+extern "C" int b200mc_set_scalars(b200mc_handle* h, const b200mc_chain_scalars* in_host) {
+  if (!h || !in_host) return fail("null argument");
+  CK(cudaMemcpy(h->cs, in_host, sizeof(ChainScalars) * h->C, cudaMemcpyHostToDevice));
+  h->initialized = true;
+  return 0;
+}
+
+static float* vec_ptr(b200mc_handle* h, int which) {
+  switch (which) {
+    case B200MC_VEC_Z: return h->cv.z;
+    case B200MC_VEC_Z_GRAD: return h->cv.z_grad;
+    case B200MC_VEC_INVERSE_MASS_MATRIX: return h->cv.inverse_mass_matrix;
+    case B200MC_VEC_MASS_MATRIX_SQRT: return h->cv.mass_matrix_sqrt;
+    case B200MC_VEC_WELFORD_MEAN: return h->cv.welford_mean;
+    case B200MC_VEC_WELFORD_M2: return h->cv.welford_m2;
+    default: return nullptr;
+  }
+}
+
+extern "C" int b200mc_get_vector(b200mc_handle* h, int which, float* out_dev, void* stream) {
+  float* p = h ? vec_ptr(h, which) : nullptr;
+  if (!p || !out_dev) return fail("bad argument");
+  CK(cudaMemcpyAsync(out_dev, p, sizeof(float) * (size_t)h->C * h->D, cudaMemcpyDeviceToDevice,
+                     (cudaStream_t)stream));
+  return 0;
+}
+
+extern "C" int b200mc_set_vector(b200mc_handle* h, int which, const float* in_dev, void* stream) {
+  float* p = h ? vec_ptr(h, which) : nullptr;
+  if (!p || !in_dev) return fail("bad argument");
+  CK(cudaMemcpyAsync(p, in_dev, sizeof(float) * (size_t)h->C * h->D, cudaMemcpyDeviceToDevice,
+                     (cudaStream_t)stream));
+  return 0;
+}
+
+// ---------------------------------------------------------------- jax.random test hooks
+__global__ void threefry_kernel(const uint32_t* key, const uint32_t* ctr, uint32_t* out, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t a = ctr[2 * i], b = ctr[2 * i + 1];
+  threefry2x32(key[2 * i], key[2 * i + 1], a, b);
+  out[2 * i] = a;
+  out[2 * i + 1] = b;
+}
+__global__ void split_kernel(const uint32_t* key, int n, int num, uint32_t* out, int part) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n * num) return;
+  const int k = i / num, j = i % num;
+  Key o;
+  if (num == 2) {  // exercise the specialised paths the sampler uses
+    Key a, b;
+    split2(Key{key[2 * k], key[2 * k + 1]}, part != 0, a, b);
+    o = j ? b : a;
+  } else if (num == 3) {
+    Key a, b, c;
+    split3(Key{key[2 * k], key[2 * k + 1]}, part != 0, a, b, c);
+    o = j == 0 ? a : (j == 1 ? b : c);
+  } else {
+    o = split_at(Key{key[2 * k], key[2 * k + 1]}, (uint32_t)num, (uint32_t)j, part != 0);
+  }
+  out[2 * i] = o.k0;
+  out[2 * i + 1] = o.k1;
+}
+// what: 0 bits, 1 uniform, 2 normal
+__global__ void draw_kernel(const uint32_t* key, int n, int what, float lo, float hi, void* out,
+                            int part) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const Key k{key[0], key[1]};
+  if (what == 0) ((uint32_t*)out)[i] = random_bits_at(k, (uint32_t)n, (uint32_t)i, part != 0);
+  else if (what == 1) ((float*)out)[i] = uniform_at(k, (uint32_t)n, (uint32_t)i, lo, hi, part != 0);
+  else ((float*)out)[i] = normal_at(k, (uint32_t)n, (uint32_t)i, part != 0);
+}
+
+extern "C" int b200mc_threefry2x32(const uint32_t* key_dev, const uint32_t* ctr_dev,
+                                   uint32_t* out_dev, int n, void* stream) {
+  if (n <= 0) return 0;
+  threefry_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(key_dev, ctr_dev, out_dev, n);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+extern "C" int b200mc_random_split(const uint32_t* key_dev, int n, int num, uint32_t* out_dev,
+                                   int partitionable, void* stream) {
+  if (n <= 0 || num <= 0) return 0;
+  split_kernel<<<(n * num + 255) / 256, 256, 0, (cudaStream_t)stream>>>(key_dev, n, num, out_dev,
+                                                                       partitionable);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+static int draw(const uint32_t* key_dev, int n, int what, float lo, float hi, void* out, int part,
+                void* stream) {
+  if (n <= 0) return 0;
+  draw_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(key_dev, n, what, lo, hi, out, part);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+extern "C" int b200mc_random_bits(const uint32_t* key_dev, int n, uint32_t* out_dev,
+                                  int partitionable, void* stream) {
+  return draw(key_dev, n, 0, 0.f, 0.f, out_dev, partitionable, stream);
+}
+extern "C" int b200mc_random_uniform(const uint32_t* key_dev, int n, float minval, float maxval,
+                                     float* out_dev, int partitionable, void* stream) {
+  return draw(key_dev, n, 1, minval, maxval, out_dev, partitionable, stream);
+}
+extern "C" int b200mc_random_normal(const uint32_t* key_dev, int n, float* out_dev,
+                                    int partitionable, void* stream) {
+  return draw(key_dev, n, 2, 0.f, 0.f, out_dev, partitionable, stream);
+}
+
+// ---------------------------------------------------------------- device plumbing
+extern "C" int b200mc_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+extern "C" int b200mc_set_device(int device) {
+  CK(cudaSetDevice(device));
+  return 0;
+}
+extern "C" void* b200mc_malloc(uint64_t bytes) {
+  void* p = nullptr;
+  if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) {
+    fail("cudaMalloc(%llu) failed: %s", (unsigned long long)bytes,
+         cudaGetErrorString(cudaGetLastError()));
+    return nullptr;
+  }
+  return p;
+}
+extern "C" int b200mc_free(void* p) {
+  CK(cudaFree(p));
+  return 0;
+}
+extern "C" int b200mc_memcpy_h2d(void* dst, const void* src, uint64_t bytes, void* stream) {
+  CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  return 0;
+}
+extern "C" int b200mc_memcpy_d2h(void* dst, const void* src, uint64_t bytes, void* stream) {
+  CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  return 0;
+}
+extern "C" int b200mc_memset(void* dst, int value, uint64_t bytes, void* stream) {
+  CK(cudaMemsetAsync(dst, value, bytes, (cudaStream_t)stream));
+  return 0;
+}
+extern "C" int b200mc_stream_synchronize(void* stream) {
+  CK(cudaStreamSynchronize((cudaStream_t)stream));
+  return 0;
+}
+extern "C" void* b200mc_host_alloc(uint64_t bytes) {
+  void* p = nullptr;
+  if (cudaMallocHost(&p, bytes ? bytes : 16) != cudaSuccess) {
+    fail("cudaMallocHost failed: %s", cudaGetErrorString(cudaGetLastError()));
+    return nullptr;
+  }
+  return p;
+}
+extern "C" int b200mc_host_free(void* p) {
+  CK(cudaFreeHost(p));
+  return 0;
+}
+extern "C" void* b200mc_event_create(void) {
+  cudaEvent_t e = nullptr;
+  if (cudaEventCreate(&e) != cudaSuccess) return nullptr;
+  return (void*)e;
+}
+extern "C" int b200mc_event_record(void* event, void* stream) {
+  CK(cudaEventRecord((cudaEvent_t)event, (cudaStream_t)stream));
+  return 0;
+}
+extern "C" int b200mc_event_elapsed_ms(void* start, void* stop, float* ms) {
+  CK(cudaEventSynchronize((cudaEvent_t)stop));
+  CK(cudaEventElapsedTime(ms, (cudaEvent_t)start, (cudaEvent_t)stop));
+  return 0;
+}
+extern "C" int b200mc_event_destroy(void* event) {
+  CK(cudaEventDestroy((cudaEvent_t)event));
+  return 0;
+}

@@ -1,0 +1,87 @@
+// Chain-batched persistent kernels for the per-chain families (eight schools,
+// stochastic volatility): every chain is owned by one thread, one warp or one CTA and
+// runs ALL of its transitions inside a single launch; chains advance independently
+// (no lock-step across chains, unlike the reference's vmap, hmc.py:797).
+#pragma once
+#include "models.cuh"
+#include "sampler.cuh"
+
+namespace b200mc {
+
+struct ChainLaunch {
+  SamplerParams P;
+  ModelData M;
+  CollectSpec col;
+  ChainScalars* cs;
+  ChainVectors cv;
+  float* work;              // tree / adaptation slots, layout depends on the mode
+  const uint32_t* init_keys;  // [C][2] -> run the init search first; null -> continue
+  int user_init;            // init: cv.z already holds caller-supplied positions
+  int C;
+  int c_pad;                // thread-per-chain: chains padded to a multiple of 32
+};
+
+// MODE 0: thread per chain (work is [slot][D][c_pad]); 1: warp per chain; 2: CTA per
+// chain (work is [chain][slot][D]).
+template <int MODE>
+__global__ void chain_kernel(const __grid_constant__ ChainLaunch L) {
+  __shared__ float red_scratch[64];
+  const int D = L.P.D;
+  const int nslots = num_slots(L.P.max_depth);
+  int chain;
+  float* base;
+  long sstride;
+  int es;
+  if (MODE == 0) {
+    chain = blockIdx.x * blockDim.x + threadIdx.x;
+    base = L.work + chain;
+    sstride = (long)D * L.c_pad;
+    es = L.c_pad;
+  } else {
+    chain = (MODE == 1) ? (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) : blockIdx.x;
+    base = L.work + (long)chain * nslots * D;
+    sstride = D;
+    es = 1;
+  }
+  if (chain >= L.C) return;
+
+  auto run = [&](auto g) {
+    Sampler<decltype(g)> S;
+    S.setup(&L.P, g, base, sstride, es, chain, L.C, &L.col);
+    S.load(L.cs, L.cv);
+    StepResult r;
+    if (L.init_keys)
+      r = S.begin_init(Key{L.init_keys[2 * chain], L.init_keys[2 * chain + 1]}, L.user_init != 0);
+    else
+      r = S.begin_sampling();
+    while (r == NEED_GRAD) {
+      const float U = model_potential(L.M, g, S.v(LZ), es, S.v(LG), es);
+      r = S.advance(U);
+    }
+    S.store(L.cs, L.cv);
+  };
+  if (MODE == 0) run(ThreadGroup{});
+  else if (MODE == 1) run(WarpGroup{});
+  else run(BlockGroup{red_scratch});
+}
+
+// Tier-2 test hook: U and gradient at caller-supplied points z[C][D].
+template <int MODE>
+__global__ void chain_potential_kernel(ModelData M, const float* z, float* U, float* grad,
+                                       int C) {
+  __shared__ float red_scratch[64];
+  const int D = M.D;
+  int chain;
+  if (MODE == 0) chain = blockIdx.x * blockDim.x + threadIdx.x;
+  else chain = (MODE == 1) ? (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) : blockIdx.x;
+  if (chain >= C) return;
+  auto run = [&](auto g) {
+    const float u = model_potential(M, g, z + (long)chain * D, 1, grad + (long)chain * D, 1);
+    if (g.lane() == 0) U[chain] = u;
+  };
+  if (MODE == 0) run(ThreadGroup{});
+  else if (MODE == 1) run(WarpGroup{});
+  else run(BlockGroup{red_scratch});
+}
+
+}  // namespace b200mc

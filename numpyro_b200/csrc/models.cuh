@@ -1,0 +1,134 @@
+// Closed-form potential energy U(z) and gradient for the per-chain model families
+// (those whose data is small enough that one thread / warp / CTA evaluates a whole
+// chain).  The tall-data logistic family has its own streaming kernel (glm_kernel.cu).
+//
+// Each function restates what the reference obtains by tracing the model and running
+// reverse-mode AD (numpyro/infer/util.py:302-327, hmc_util.py:242-252); the log-prob
+// formulas come from numpyro/distributions/continuous.py (cited per family).
+// Evaluates at z (element stride zs), writes the gradient to grad, returns U in every lane.
+#pragma once
+#include <cmath>
+
+#include "group.cuh"
+#include "types.h"
+
+namespace b200mc {
+
+enum Family { FAM_LOGISTIC = 0, FAM_EIGHT_SCHOOLS = 1, FAM_HORSESHOE = 2, FAM_SV = 3 };
+
+struct ModelData {
+  int family;
+  int N;           // rows / schools / time steps
+  int D;           // flat unconstrained dimension
+  const float* a;  // eight schools: y[J];    SV: returns[T]
+  const float* b;  // eight schools: sigma[J]
+};
+
+#define B200MC_LOG_SQRT_2PI 0.9189385332046727f
+#define B200MC_SQRT_2PI 2.5066282746310002f
+
+// Eight schools, non-centred (README.md:101-110 + reparam.py:159-185).
+// z = [mu, log tau, theta_base[J]].  Normal: continuous.py:2203-2207; HalfCauchy:
+// :238-244,721-723; ExpTransform log|J| = z: transforms.py:563-571.
+template <class G>
+__device__ float eight_schools_potential(const ModelData& M, const G& g, const float* z, int zs,
+                                         float* grad, int gs) {
+  const int J = M.N;
+  g.sync();  // z[0], z[1] were written by their owner lanes
+  const float mu = z[0], tu = z[zs];
+  const float tau = expf(tu);
+  const float q = tau / 5.0f;
+  const float qq = q * q;
+  float lp0 = -0.5f * (mu / 5.0f) * (mu / 5.0f) - logf(B200MC_SQRT_2PI * 5.0f);
+  lp0 += (0.6931471805599453f - 1.1447298858494002f - 1.6094379124341003f - log1pf(qq)) + tu;
+  float lp = 0.f, s1 = 0.f, s2 = 0.f;
+  for (int j = g.lane(); j < J; j += g.size()) {
+    const float b = z[(2 + j) * zs];
+    const float sig = M.b[j];
+    const float theta = mu + tau * b;
+    const float resid = (M.a[j] - theta) / sig;
+    lp += (-0.5f * b * b - B200MC_LOG_SQRT_2PI) +
+          (-0.5f * resid * resid - logf(B200MC_SQRT_2PI * sig));
+    const float dth = -(resid / sig);
+    s1 += dth;
+    s2 += dth * b;
+    grad[(2 + j) * gs] = b + tau * dth;
+  }
+  g.sum2(s1, s2);
+  lp = g.sum(lp);
+  if (g.lane() == 0) {
+    grad[0] = mu / 25.0f + s1;
+    grad[gs] = (2.0f * qq / (1.0f + qq)) - 1.0f + tau * s2;
+  }
+  g.sync();  // gradient elements are read back by their owner lanes
+  return -(lp0 + lp);
+}
+
+// digamma(x), x > 0, in double (recurrence up to x >= 6, then the asymptotic series).
+__device__ inline double digamma_f64(double x) {
+  double r = 0.0;
+  while (x < 6.0) {
+    r -= 1.0 / x;
+    x += 1.0;
+  }
+  const double f = 1.0 / (x * x);
+  return r + log(x) - 0.5 / x -
+         f * (1.0 / 12.0 - f * (1.0 / 120.0 - f * (1.0 / 252.0 - f * (1.0 / 240.0 - f / 132.0))));
+}
+
+// Stochastic volatility (examples/stochastic_volatility.py:57-65).
+// z = [log nu, s[T], log sigma].  Exponential: continuous.py:473-475;
+// GaussianRandomWalk: :684-689; StudentT: :2375-2385.
+template <class G>
+__device__ float sv_potential(const ModelData& M, const G& g, const float* z, int zs, float* grad,
+                              int gs) {
+  const int T = M.N;
+  g.sync();  // neighbours' s[t-1], s[t+1] were written by other lanes
+  const float nu_u = z[0], sg_u = z[(1 + T) * zs];
+  const float nu = expf(nu_u), sg = expf(sg_u);
+  const float nup1 = nu + 1.0f;
+  float sum_ds2 = 0.f, sum_t = 0.f, sum_nu = 0.f, sum_l = 0.f;
+  for (int e = 1 + g.lane(); e <= T; e += g.size()) {
+    const int t = e - 1;
+    const float st = z[e * zs];
+    const float prev = (t > 0) ? z[(e - 1) * zs] : 0.0f;
+    const float ds = (st - prev) / sg;
+    float gsv = ds / sg;
+    if (t + 1 < T) gsv -= ((z[(e + 1) * zs] - st) / sg) / sg;
+    const float y = M.a[t] * expf(-st);
+    const float y2n = y * y / nu;
+    const float l1p = log1pf(y2n);
+    const float wq = y2n / (1.0f + y2n);
+    sum_ds2 += ds * ds;
+    sum_t += -0.5f * nup1 * l1p - st;
+    sum_l += 0.5f * l1p;
+    sum_nu += 0.5f * nup1 * wq / nu;
+    grad[e * gs] = gsv + (1.0f - nup1 * wq);
+  }
+  g.sum2(sum_ds2, sum_t);
+  g.sum2(sum_l, sum_nu);
+  const float fT = (float)T;
+  const double hn = 0.5 * (double)nu, hn1 = 0.5 * ((double)nu + 1.0);
+  const float zt = 0.5f * nu_u + 0.5723649429247001f + (float)(lgamma(hn) - lgamma(hn1));
+  float lp = (3.912023005428146f - 50.0f * sg) + sg_u;    // log 50
+  lp += (-2.302585092994046f - 0.1f * nu) + nu_u;         // log 0.1
+  lp += -0.5f * sum_ds2 - fT * (B200MC_LOG_SQRT_2PI + sg_u);
+  lp += sum_t - fT * zt;
+  if (g.lane() == 0) {
+    grad[(1 + T) * gs] = 50.0f * sg - 1.0f - sum_ds2 + fT;
+    const float dig = (float)(digamma_f64(hn) - digamma_f64(hn1));
+    const float dnu = (sum_l - sum_nu) + fT * (0.5f / nu + 0.5f * dig);
+    grad[0] = 0.1f * nu - 1.0f + nu * dnu;
+  }
+  g.sync();
+  return -lp;
+}
+
+template <class G>
+__device__ __forceinline__ float model_potential(const ModelData& M, const G& g, const float* z,
+                                                 int zs, float* grad, int gs) {
+  if (M.family == FAM_EIGHT_SCHOOLS) return eight_schools_potential(M, g, z, zs, grad, gs);
+  return sv_potential(M, g, z, zs, grad, gs);
+}
+
+}  // namespace b200mc

@@ -1,0 +1,644 @@
+// The HMC/NUTS transition as a device-side step machine.
+//
+// One call of advance(U) consumes exactly one potential+gradient evaluation (made
+// at the point the previous call asked for) and carries the chain to the next point
+// that needs one.  Everything between two gradient evaluations of the reference's
+// nested loops -- leapfrog halves, energy test, multinomial / biased-progressive
+// selection, checkpointed U-turn test, subtree and tree combination, warm-up
+// adaptation, momentum refresh, init search -- happens inside advance().
+//
+// Reference functions restated here (numpyro/infer/):
+//   hmc_util.py:289-309   velocity_verlet.update_fn      -> half_step / finish_leapfrog
+//   hmc_util.py:1183-1200 euclidean_kinetic_energy       -> kinetic()
+//   hmc_util.py:851-894   _build_basetree                -> advance_tree step 1
+//   hmc_util.py:749-848   transition kernels/_combine_tree -> step 2 / step 5
+//   hmc_util.py:941-981   ckpt indices / iterative turning -> step 3
+//   hmc_util.py:984-1085  _iterative_build_subtree       -> steps 2-4
+//   hmc_util.py:907-938   _double_tree                   -> next_doubling / step 5
+//   hmc_util.py:1088-1180 build_tree                     -> start_transition / step 6
+//   hmc_util.py:60-130    dual_averaging                 -> da_update
+//   hmc_util.py:133-239   welford_covariance (diagonal)  -> adapt()
+//   hmc_util.py:518-707   warmup_adapter                 -> adapt()
+//   hmc.py:92-110         momentum_generator             -> draw_momentum
+//   hmc.py:193-362        init_kernel                    -> init_kernel
+//   hmc.py:364-530        _hmc_next/_nuts_next/sample_kernel -> advance_hmc / finish_transition
+//   infer/util.py:386-450 find_valid_initial_params      -> init_candidate / advance_init
+//   util.py:334-351       fori_collect body              -> collect
+//
+// Elementwise float arithmetic keeps the reference's operation order and is compiled
+// with -fmad=false, so it is bit-identical to the NumPy oracle; only reductions and
+// libm calls can differ in the last ulp.
+#pragma once
+#include <cfloat>
+#include <cmath>
+
+#include "group.cuh"
+#include "rng.cuh"
+#include "types.h"
+
+namespace b200mc {
+
+enum Slot {
+  Z_LEFT = 0, R_LEFT, G_LEFT, Z_RIGHT, R_RIGHT, G_RIGHT,  // tree end points
+  Z_PROP, G_PROP,                                          // tree proposal == HMCState.z, z_grad
+  R_SUM,
+  LZ, LR, LG,                                              // leaf under construction; LZ = point to evaluate
+  SZ_PROP, SG_PROP, S_RSUM,                                // subtree proposal / momentum sum
+  IMM, MSQRT, WMEAN, WM2,                                  // adaptation vectors
+  CKPT0                                                    // r_ckpts[i] = CKPT0+2i, r_sum_ckpts[i] = CKPT0+2i+1
+};
+__host__ __device__ inline int num_slots(int max_depth) { return CKPT0 + 2 * max_depth; }
+
+enum Phase { PH_INIT = 0, PH_TREE, PH_HMC, PH_IDLE, PH_FAIL };
+enum StepResult { NEED_GRAD = 0, FINISHED = 1 };
+
+__device__ __forceinline__ float logaddexp_f32(float a, float b) {
+  // jnp.logaddexp: amax + log1p(exp(-|a-b|)), with the (inf - inf) case = a + b
+  const float delta = a - b;
+  if (isnan(delta)) return a + b;
+  return fmaxf(a, b) + log1pf(expf(-fabsf(delta)));
+}
+
+template <class G>
+struct Sampler {
+  const SamplerParams* P;
+  G g;
+  float* w;            // this chain's slot 0, element 0
+  long slot_stride;    // floats between slots
+  int es;              // floats between elements of one vector
+  int D;
+  bool part;
+
+  ChainScalars s;      // persistent scalars (registers)
+
+  // run control
+  int iters_left, local_iter, chain, C;
+  const CollectSpec* col;
+  int phase;
+
+  // transition state
+  float e0, eps_s;
+  int depth, nprop, turning, diverging, going_right, max_depth_cur;
+  float weight, sum_acc, prop_pe, prop_energy;
+  Key tree_key, sub_key, top_key;
+  int s_n, s_div;
+  float s_w, s_sum_acc, s_prop_pe, s_prop_energy;
+  // precomputed leaf-level randomness (does not depend on the gradient)
+  int pre_valid;
+  Key pre_sub_key;
+  float pre_u;
+  // HMC
+  int hmc_steps, hmc_done;
+  float energy_old;
+  Key mh_key;
+  // init search
+  Key init_key;
+  int user_init;
+
+  __device__ __forceinline__ float* v(int slot) const { return w + (long)slot * slot_stride; }
+  __device__ __forceinline__ float* ckpt_r(int i) const { return v(CKPT0 + 2 * i); }
+  __device__ __forceinline__ float* ckpt_rs(int i) const { return v(CKPT0 + 2 * i + 1); }
+
+#define B200MC_FOR_D for (int d = g.lane(); d < D; d += g.size())
+
+  __device__ __forceinline__ void copy(int dst, int src) {
+    float* a = v(dst);
+    const float* b = v(src);
+    B200MC_FOR_D a[d * es] = b[d * es];
+  }
+
+  // ------------------------------------------------------------------ setup / persistence
+  __device__ void setup(const SamplerParams* p, G grp, float* work, long sstride, int estride,
+                        int chain_, int C_, const CollectSpec* c) {
+    P = p; g = grp; w = work; slot_stride = sstride; es = estride; D = p->D;
+    part = p->partitionable != 0;
+    chain = chain_; C = C_; col = c;
+    iters_left = c ? c->num_iters : 0;
+    local_iter = 0;
+    phase = PH_IDLE;
+    pre_valid = 0;
+  }
+
+  __device__ void load(const ChainScalars* cs, const ChainVectors& cv) {
+    s = cs[chain];
+    const long o = (long)chain * D;
+    float *zp = v(Z_PROP), *gp = v(G_PROP), *im = v(IMM), *ms = v(MSQRT), *wm = v(WMEAN),
+          *w2 = v(WM2);
+    B200MC_FOR_D {
+      zp[d * es] = cv.z[o + d];
+      gp[d * es] = cv.z_grad[o + d];
+      im[d * es] = cv.inverse_mass_matrix[o + d];
+      ms[d * es] = cv.mass_matrix_sqrt[o + d];
+      wm[d * es] = cv.welford_mean[o + d];
+      w2[d * es] = cv.welford_m2[o + d];
+    }
+  }
+
+  __device__ void store(ChainScalars* cs, const ChainVectors& cv) {
+    const long o = (long)chain * D;
+    const float *zp = v(Z_PROP), *gp = v(G_PROP), *im = v(IMM), *ms = v(MSQRT), *wm = v(WMEAN),
+                *w2 = v(WM2);
+    B200MC_FOR_D {
+      cv.z[o + d] = zp[d * es];
+      cv.z_grad[o + d] = gp[d * es];
+      cv.inverse_mass_matrix[o + d] = im[d * es];
+      cv.mass_matrix_sqrt[o + d] = ms[d * es];
+      cv.welford_mean[o + d] = wm[d * es];
+      cv.welford_m2[o + d] = w2[d * es];
+    }
+    if (g.lane() == 0) cs[chain] = s;
+  }
+
+  // ------------------------------------------------------------------ small pieces
+  __device__ __forceinline__ float kinetic(int rslot) {  // 0.5 * dot(M^-1 r, r)
+    const float *r = v(rslot), *im = v(IMM);
+    float acc = 0.f;
+    B200MC_FOR_D {
+      const float rv = r[d * es];
+      const float vv = im[d * es] * rv;
+      acc += vv * rv;
+    }
+    return 0.5f * g.sum(acc);
+  }
+
+  // hmc_util.py:710-746 with r_sum already the (sub)tree sum
+  __device__ __forceinline__ bool is_turning(const float* rl, const float* rr, const float* rsum,
+                                             const float* sub_a, const float* add_b) {
+    // s = rsum (- sub_a + add_b); s' = s - (rl + rr)/2; (M^-1 rl).s' <= 0 | (M^-1 rr).s' <= 0
+    const float* im = v(IMM);
+    float la = 0.f, ra = 0.f;
+    B200MC_FOR_D {
+      float sv = rsum[d * es];
+      if (sub_a) {
+        sv = sv - sub_a[d * es];
+        sv = sv + add_b[d * es];
+      }
+      const float l = rl[d * es], r = rr[d * es];
+      const float h = (l + r) / 2.0f;
+      const float sp = sv - h;
+      const float vl = im[d * es] * l, vr = im[d * es] * r;
+      la += vl * sp;
+      ra += vr * sp;
+    }
+    g.sum2(la, ra);
+    return (la <= 0.f) | (ra <= 0.f);
+  }
+
+  // r = M^{1/2} eps, eps ~ N(0, I): hmc.py:92-110 (one dict block => split(key, 1))
+  __device__ __forceinline__ void draw_momentum(Key k_mom, int dst) {
+    const Key kb = split_at(k_mom, 1u, 0u, part);
+    float* r = v(dst);
+    const float* ms = v(MSQRT);
+    B200MC_FOR_D {
+      const float eps = normal_at(kb, (uint32_t)D, (uint32_t)d, part);
+      r[d * es] = ms[d * es] * eps;
+    }
+  }
+
+  // first half of velocity Verlet from the leaf in (LZ, LR, LG): hmc_util.py:297-302
+  __device__ __forceinline__ void half_step() {
+    float *z = v(LZ), *r = v(LR);
+    const float *gr = v(LG), *im = v(IMM);
+    const float hs = 0.5f * eps_s;
+    B200MC_FOR_D {
+      const float t = hs * gr[d * es];
+      const float rn = r[d * es] - t;
+      r[d * es] = rn;
+      const float vv = im[d * es] * rn;
+      const float dz = eps_s * vv;
+      z[d * es] = z[d * es] + dz;
+    }
+  }
+
+  // second half: hmc_util.py:306-308
+  __device__ __forceinline__ void finish_leapfrog() {
+    float* r = v(LR);
+    const float* gr = v(LG);
+    const float hs = 0.5f * eps_s;
+    B200MC_FOR_D {
+      const float t = hs * gr[d * es];
+      r[d * es] = r[d * es] - t;
+    }
+  }
+
+  // ------------------------------------------------------------------ warm-up adaptation
+  __device__ __forceinline__ void da_init(float prox_center) {  // hmc_util.py:97-107
+    s.ss_x_t = 0.f; s.ss_x_avg = 0.f; s.ss_g_avg = 0.f; s.ss_t = 0;
+    s.ss_prox_center = prox_center;
+  }
+
+  __device__ __forceinline__ void da_update(float gstat) {  // hmc_util.py:109-128
+    const float t0 = 10.f, kappa = 0.75f, gamma = 0.05f;
+    s.ss_t += 1;
+    const float t = (float)s.ss_t;
+    const float inv = 1.0f / (t + t0);
+    const float a = (1.0f - inv) * s.ss_g_avg;
+    const float b = gstat / (t + t0);
+    s.ss_g_avg = a + b;
+    const float c = sqrtf(t) / gamma;
+    s.ss_x_t = s.ss_prox_center - c * s.ss_g_avg;
+    const float wt = powf(t, -kappa);
+    const float e = (1.0f - wt) * s.ss_x_avg;
+    const float f = wt * s.ss_x_t;
+    s.ss_x_avg = e + f;
+  }
+
+  // warmup_adapter.update_fn: hmc_util.py:637-705 (diagonal mass matrix)
+  __device__ void adapt(int t, float accept_prob) {
+    Key nk, kss;
+    split2(Key{s.adapt_key[0], s.adapt_key[1]}, part, nk, kss);  // :656 (k_ss unused here)
+    s.adapt_key[0] = nk.k0; s.adapt_key[1] = nk.k1;
+    if (P->adapt_step_size) {
+      da_update(P->target_accept_prob - accept_prob);
+      float ss = (t == P->num_warmup - 1) ? expf(s.ss_x_avg) : expf(s.ss_x_t);
+      ss = fminf(fmaxf(ss, FLT_MIN), FLT_MAX);  // :671-672
+      s.step_size = ss;
+    }
+    const bool is_middle = (0 < s.window_idx) && (s.window_idx < P->num_windows - 1);
+    if (P->adapt_mass_matrix && is_middle) {  // welford update, :172-196
+      s.mm_n += 1;
+      const float n = (float)s.mm_n;
+      const float* z = v(Z_PROP);
+      float *mean = v(WMEAN), *m2 = v(WM2);
+      B200MC_FOR_D {
+        const float x = z[d * es];
+        const float dpre = x - mean[d * es];
+        const float q = dpre / n;
+        const float mnew = mean[d * es] + q;
+        mean[d * es] = mnew;
+        const float dpost = x - mnew;
+        const float pr = dpre * dpost;
+        m2[d * es] = m2[d * es] + pr;
+      }
+    }
+    const int wend = P->window_end[min(s.window_idx, P->num_windows - 1)];
+    const bool at_end = (t == wend);
+    if (at_end) s.window_idx += 1;
+    if (at_end && is_middle) {  // _update_at_window_end, :596-635
+      if (P->adapt_mass_matrix) {  // welford final, :198-237
+        const float n = (float)s.mm_n;
+        float *mean = v(WMEAN), *m2 = v(WM2), *im = v(IMM), *ms = v(MSQRT);
+        const float scale = n / (n + 5.0f);
+        const float shrink = 1e-3f * (5.0f / (n + 5.0f));
+        B200MC_FOR_D {
+          float cov = m2[d * es] / (n - 1.0f);
+          if (P->regularize_mass_matrix) {
+            const float sc = scale * cov;
+            cov = sc + shrink;
+          }
+          im[d * es] = cov;
+          ms[d * es] = 1.0f / sqrtf(cov);
+          mean[d * es] = 0.f;
+          m2[d * es] = 0.f;
+        }
+        s.mm_n = 0;
+      }
+      if (P->adapt_step_size) da_init(logf(10.0f) + logf(s.step_size));  // :624
+    }
+  }
+
+  // ------------------------------------------------------------------ collection (util.py:334-351)
+  __device__ void collect() {
+    const int k = local_iter;  // index of the transition just finished, within this call
+    if (!col || col->n_keep <= 0 || k < col->collect_start) return;
+    const int rel = k - col->collect_start;
+    if (rel % col->thinning != col->thinning - 1) return;  // the last write to a slot wins
+    const int idx = rel / col->thinning;
+    if (idx >= col->n_keep) return;
+    const long row = (long)idx * C + chain;
+    if (col->z) {
+      const float* z = v(Z_PROP);
+      float* out = col->z + row * D;
+      B200MC_FOR_D out[d] = z[d * es];
+    }
+    if (g.lane() == 0) {
+      if (col->potential_energy) col->potential_energy[row] = s.potential_energy;
+      if (col->energy) col->energy[row] = s.energy;
+      if (col->num_steps) col->num_steps[row] = s.num_steps;
+      if (col->accept_prob) col->accept_prob[row] = s.accept_prob;
+      if (col->mean_accept_prob) col->mean_accept_prob[row] = s.mean_accept_prob;
+      if (col->diverging) col->diverging[row] = s.diverging;
+      if (col->step_size) col->step_size[row] = s.step_size;
+    }
+  }
+
+  // tail of sample_kernel: hmc.py:500-530
+  __device__ StepResult finish_transition(float accept_prob, int num_steps, int div) {
+    s.accept_prob = accept_prob;
+    s.num_steps = num_steps;
+    s.diverging = div;
+    const int t = s.i;
+    if (t < P->num_warmup) adapt(t, accept_prob);
+    const int itr = t + 1;
+    const int n = (t < P->num_warmup) ? itr : itr - P->num_warmup;
+    const float dm = accept_prob - s.mean_accept_prob;
+    s.mean_accept_prob = s.mean_accept_prob + dm / (float)n;
+    s.i = itr;
+    collect();
+    local_iter += 1;
+    iters_left -= 1;
+    if (iters_left <= 0) {
+      phase = PH_IDLE;
+      return FINISHED;
+    }
+    return start_transition();
+  }
+
+  // ------------------------------------------------------------------ transition start
+  // sample_kernel head (hmc.py:472-490) + build_tree head (hmc_util.py:1129-1153)
+  __device__ StepResult start_transition() {
+    Key nk, k_mom, k_tr;
+    split3(Key{s.rng_key[0], s.rng_key[1]}, part, nk, k_mom, k_tr);
+    s.rng_key[0] = nk.k0; s.rng_key[1] = nk.k1;
+    if (P->algo == ALGO_HMC) return start_hmc(k_mom, k_tr);
+    draw_momentum(k_mom, R_LEFT);
+    {
+      float *rl = v(R_LEFT), *rr = v(R_RIGHT), *rs = v(R_SUM);
+      float *zl = v(Z_LEFT), *zr = v(Z_RIGHT), *gl = v(G_LEFT), *gr = v(G_RIGHT);
+      const float *zp = v(Z_PROP), *gp = v(G_PROP);
+      B200MC_FOR_D {
+        const float r = rl[d * es];
+        rr[d * es] = r;
+        rs[d * es] = r;
+        const float z = zp[d * es], gg = gp[d * es];
+        zl[d * es] = z; zr[d * es] = z;
+        gl[d * es] = gg; gr[d * es] = gg;
+      }
+    }
+    e0 = s.potential_energy + kinetic(R_LEFT);
+    depth = 0; weight = 0.f; turning = 0; diverging = 0; sum_acc = 0.f; nprop = 0;
+    prop_pe = s.potential_energy;
+    prop_energy = e0;
+    tree_key = k_tr;
+    max_depth_cur = (s.i < P->num_warmup) ? P->max_depth_warmup : P->max_depth_sample;
+    phase = PH_TREE;
+    if (!(depth < max_depth_cur)) return finish_transition(nanf(""), 0, 0);
+    next_doubling();
+    return NEED_GRAD;
+  }
+
+  // build_tree._body_fn (hmc_util.py:1159-1176) + _double_tree head (:920)
+  __device__ void next_doubling() {
+    Key nk, dir_key, dbl_key;
+    split3(tree_key, part, nk, dir_key, dbl_key);
+    tree_key = nk;
+    going_right = uniform01(dir_key, part) < 0.5f;
+    split2(dbl_key, part, sub_key, top_key);
+    s_n = 0;
+    pre_valid = 0;
+    eps_s = going_right ? s.step_size : -s.step_size;
+    if (going_right) {
+      copy(LZ, Z_RIGHT); copy(LR, R_RIGHT); copy(LG, G_RIGHT);
+    } else {
+      copy(LZ, Z_LEFT); copy(LR, R_LEFT); copy(LG, G_LEFT);
+    }
+    half_step();
+  }
+
+  // Leaf-level randomness of _iterative_build_subtree (hmc_util.py:1005, :804): does
+  // not depend on the gradient, so a kernel may call this while the gradient is still
+  // being computed.
+  __device__ __forceinline__ void prefetch_rng() {
+    if (phase != PH_TREE || pre_valid) return;
+    Key tkey;
+    split2(sub_key, part, pre_sub_key, tkey);
+    pre_u = uniform01(tkey, part);
+    pre_valid = 1;
+  }
+
+  // ------------------------------------------------------------------ NUTS: one leaf
+  __device__ StepResult advance_tree(float U) {
+    // 1. finish the leapfrog, energy test (_build_basetree, hmc_util.py:863-875)
+    finish_leapfrog();
+    const float e_new = U + kinetic(LR);
+    float dE = e_new - e0;
+    if (isnan(dE)) dE = INFINITY;
+    const float wleaf = -dE;
+    const int leaf_div = dE > P->max_delta_energy;
+    const float acc = fminf(expf(-dE), 1.0f);
+
+    // 2. fold the leaf into the subtree (uniform / multinomial kernel, :749-753, :1020-1032)
+    prefetch_rng();
+    sub_key = pre_sub_key;
+    pre_valid = 0;
+    const int leaf_idx = s_n;
+    if (s_n == 0) {
+      s_w = wleaf; s_div = leaf_div; s_sum_acc = acc;
+      s_prop_pe = U; s_prop_energy = e_new;
+      copy(SZ_PROP, LZ); copy(SG_PROP, LG); copy(S_RSUM, LR);
+      s_n = 1;
+    } else {
+      const float p = 1.0f / (1.0f + expf(-(wleaf - s_w)));  // expit
+      const bool take = pre_u < p;
+      if (take) {
+        s_prop_pe = U; s_prop_energy = e_new;
+        copy(SZ_PROP, LZ); copy(SG_PROP, LG);
+      }
+      s_w = logaddexp_f32(s_w, wleaf);
+      s_div = leaf_div;
+      s_sum_acc = s_sum_acc + acc;
+      s_n += 1;
+      float* rs = v(S_RSUM);
+      const float* r = v(LR);
+      B200MC_FOR_D rs[d * es] = rs[d * es] + r[d * es];
+    }
+
+    // 3. checkpoints and iterative U-turn test (:941-981, :1034-1058)
+    const int idx_max = __popc(leaf_idx >> 1);
+    const int num_sub = __popc(((~leaf_idx) & (leaf_idx + 1)) - 1);
+    const int idx_min = idx_max - num_sub + 1;
+    if ((leaf_idx & 1) == 0) {
+      float *cr = ckpt_r(idx_max), *crs = ckpt_rs(idx_max);
+      const float *r = v(LR), *rs = v(S_RSUM);
+      B200MC_FOR_D {
+        cr[d * es] = r[d * es];
+        crs[d * es] = rs[d * es];
+      }
+    }
+    bool sub_turning = false;
+    for (int i = idx_max; i >= idx_min && !sub_turning; --i)
+      sub_turning = is_turning(ckpt_r(i), v(LR), v(S_RSUM), ckpt_rs(i), ckpt_r(i));
+
+    // 4. keep extending the subtree? (_cond_fn, :999-1001)
+    if (s_n < (1 << depth) && !sub_turning && !s_div) {
+      half_step();
+      return NEED_GRAD;
+    }
+
+    // 5. subtree finished: biased-progressive combine with the tree (:767-848, biased=True)
+    if (going_right) {
+      copy(Z_RIGHT, LZ); copy(R_RIGHT, LR); copy(G_RIGHT, LG);
+    } else {
+      copy(Z_LEFT, LZ); copy(R_LEFT, LR); copy(G_LEFT, LG);
+    }
+    {
+      float* rs = v(R_SUM);
+      const float* srs = v(S_RSUM);
+      B200MC_FOR_D rs[d * es] = rs[d * es] + srs[d * es];
+    }
+    float p = expf(s_w - weight);
+    p = (sub_turning || s_div) ? 0.0f : fminf(p, 1.0f);
+    const bool tree_turning =
+        sub_turning | is_turning(v(R_LEFT), v(R_RIGHT), v(R_SUM), nullptr, nullptr);
+    if (uniform01(top_key, part) < p) {
+      copy(Z_PROP, SZ_PROP); copy(G_PROP, SG_PROP);
+      prop_pe = s_prop_pe; prop_energy = s_prop_energy;
+    }
+    depth += 1;
+    weight = logaddexp_f32(weight, s_w);
+    diverging = s_div;
+    turning = tree_turning;
+    sum_acc = sum_acc + s_sum_acc;
+    nprop += s_n;
+
+    // 6. double again? (build_tree._cond_fn, :1155-1157)
+    if (depth < max_depth_cur && !turning && !diverging) {
+      next_doubling();
+      return NEED_GRAD;
+    }
+
+    // 7. _nuts_next tail (hmc.py:441-455)
+    s.potential_energy = prop_pe;
+    s.energy = prop_energy;
+    return finish_transition(sum_acc / (float)nprop, nprop, diverging);
+  }
+
+  // ------------------------------------------------------------------ HMC (hmc.py:364-414)
+  __device__ StepResult start_hmc(Key k_mom, Key k_tr) {
+    draw_momentum(k_mom, LR);
+    copy(LZ, Z_PROP); copy(LG, G_PROP);
+    mh_key = k_tr;
+    float eps = s.step_size;
+    int n;
+    if (P->fixed_num_steps > 0) n = P->fixed_num_steps;
+    else n = (int)ceilf(P->trajectory_length / eps);  // hmc.py:85-89
+    if (P->has_trajectory_length) eps = P->trajectory_length / (float)n;
+    hmc_steps = n; hmc_done = 0;
+    eps_s = eps;
+    energy_old = s.potential_energy + kinetic(LR);
+    phase = PH_HMC;
+    half_step();
+    return NEED_GRAD;
+  }
+
+  __device__ StepResult advance_hmc(float U) {
+    finish_leapfrog();
+    hmc_done += 1;
+    if (hmc_done < hmc_steps) {
+      half_step();
+      return NEED_GRAD;
+    }
+    const float e_new = U + kinetic(LR);
+    float dE = e_new - energy_old;
+    if (isnan(dE)) dE = INFINITY;
+    const float acc = fminf(expf(-dE), 1.0f);
+    const int div = dE > P->max_delta_energy;
+    if (uniform01(mh_key, part) < acc) {
+      copy(Z_PROP, LZ); copy(G_PROP, LG);
+      s.potential_energy = U;
+      s.energy = e_new;
+    } else {
+      s.energy = energy_old;
+    }
+    return finish_transition(acc, hmc_steps, div);
+  }
+
+  // ------------------------------------------------------------------ initialisation
+  // HMC.init (hmc.py:744-750): rng_key, rng_key_init_model = split(rng_key)
+  __device__ StepResult begin_init(Key chain_key, bool has_user_z) {
+    Key k_run, k_init;
+    split2(chain_key, part, k_run, k_init);
+    s.rng_key[0] = k_run.k0; s.rng_key[1] = k_run.k1;
+    s.status = 0; s.init_tries = 0; s.grad_evals = 0;
+    init_key = k_init;
+    user_init = has_user_z ? 1 : 0;
+    phase = PH_INIT;
+    if (user_init) copy(LZ, Z_PROP);
+    else init_candidate();
+    return NEED_GRAD;
+  }
+
+  // find_valid_initial_params body_fn, fast branch (infer/util.py:390-432)
+  __device__ void init_candidate() {
+    Key key, subkey;
+    split2(init_key, part, key, subkey);
+    float* z = v(LZ);
+    for (int k = 0; k < P->nsites; ++k) {
+      const int off = P->site_off[k], n = P->site_size[k];
+      for (int j = g.lane(); j < n; j += g.size())
+        z[(off + j) * es] =
+            uniform_at(subkey, (uint32_t)n, (uint32_t)j, -P->init_radius, P->init_radius, part);
+      Key nk, ns;
+      split2(key, part, nk, ns);
+      key = nk; subkey = ns;
+    }
+    init_key = key;
+    s.init_tries += 1;
+  }
+
+  __device__ StepResult advance_init(float U) {
+    if (!user_init) {
+      const float* gr = v(LG);
+      float bad = 0.f;
+      B200MC_FOR_D bad += isfinite(gr[d * es]) ? 0.f : 1.f;
+      bad = g.sum(bad);
+      const bool valid = isfinite(U) && bad == 0.f;
+      if (!valid) {
+        if (s.init_tries >= 100) {  // RuntimeError("Cannot find valid initial parameters")
+          s.status = 1;
+          phase = PH_FAIL;
+          return FINISHED;
+        }
+        init_candidate();
+        return NEED_GRAD;
+      }
+    }
+    copy(Z_PROP, LZ); copy(G_PROP, LG);
+    s.potential_energy = U;
+    init_kernel();
+    if (iters_left <= 0) {
+      phase = PH_IDLE;
+      return FINISHED;
+    }
+    return start_transition();
+  }
+
+  // init_kernel (hmc.py:335-362) + warmup_adapter.init_fn (hmc_util.py:552-594); the
+  // caller has put the initial mass matrix into IMM / MSQRT.
+  __device__ void init_kernel() {
+    Key k_hmc, k_wa, k_mom, k_adapt, k_ss;
+    split3(Key{s.rng_key[0], s.rng_key[1]}, part, k_hmc, k_wa, k_mom);
+    split2(k_wa, part, k_adapt, k_ss);
+    s.adapt_key[0] = k_adapt.k0; s.adapt_key[1] = k_adapt.k1;
+    s.step_size = P->init_step_size;
+    da_init(logf(10.0f * s.step_size));
+    {
+      float *mean = v(WMEAN), *m2 = v(WM2);
+      B200MC_FOR_D { mean[d * es] = 0.f; m2[d * es] = 0.f; }
+    }
+    s.mm_n = 0;
+    s.window_idx = 0;
+    draw_momentum(k_mom, LR);  // value discarded by the reference except for `energy`
+    s.energy = s.potential_energy + kinetic(LR);
+    s.rng_key[0] = k_hmc.k0; s.rng_key[1] = k_hmc.k1;
+    s.i = 0; s.num_steps = 0; s.accept_prob = 0.f; s.mean_accept_prob = 0.f; s.diverging = 0;
+  }
+
+  // ------------------------------------------------------------------ driver interface
+  __device__ StepResult begin_sampling() {
+    if (iters_left <= 0 || s.status != 0) return FINISHED;
+    return start_transition();
+  }
+
+  // The gradient of the potential at v(LZ) has been written to v(LG); U is its value.
+  __device__ StepResult advance(float U) {
+    s.grad_evals += 1;
+    if (phase == PH_TREE) return advance_tree(U);
+    if (phase == PH_HMC) return advance_hmc(U);
+    if (phase == PH_INIT) return advance_init(U);
+    return FINISHED;
+  }
+#undef B200MC_FOR_D
+};
+
+}  // namespace b200mc

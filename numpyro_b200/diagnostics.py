@@ -1,0 +1,134 @@
+"""Host-side convergence diagnostics with the surface of ``numpyro/diagnostics.py``
+(NumPy; not on the accelerated path).  ``MCMC.print_summary`` uses these."""
+from collections import OrderedDict
+from itertools import product
+
+import numpy as np
+
+
+def _chain_variance_stats(x):  # diagnostics.py:29-42
+    n = x.shape[1]
+    var_within = x.var(axis=1, ddof=1).mean(axis=0)
+    var_estimator = var_within * (n - 1) / n
+    if x.shape[0] > 1:
+        var_estimator = var_estimator + x.mean(axis=1).var(axis=0, ddof=1)
+    else:
+        var_within = var_estimator
+    return var_within, var_estimator
+
+
+def gelman_rubin(x):  # diagnostics.py:45-61
+    assert x.ndim >= 2 and x.shape[0] >= 2 and x.shape[1] >= 2
+    var_within, var_estimator = _chain_variance_stats(x)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        return np.sqrt(var_estimator / var_within)
+
+
+def split_gelman_rubin(x):  # diagnostics.py:64-80
+    assert x.ndim >= 2 and x.shape[1] >= 4
+    h = x.shape[1] // 2
+    return gelman_rubin(np.concatenate([x[:, :h], x[:, -h:]], axis=0))
+
+
+def _fft_next_fast_len(target):  # diagnostics.py:83-98
+    if target <= 2:
+        return target
+    while True:
+        m = target
+        for p in (2, 3, 5):
+            while m % p == 0:
+                m //= p
+        if m == 1:
+            return target
+        target += 1
+
+
+def autocorrelation(x, axis=0, bias=True):  # diagnostics.py:101-142
+    n = x.shape[axis]
+    m2 = 2 * _fft_next_fast_len(n)
+    x = np.swapaxes(x, axis, -1)
+    centered = x - x.mean(axis=-1, keepdims=True)
+    freq = np.fft.rfft(centered, n=m2, axis=-1)
+    ac = np.fft.irfft(freq * np.conjugate(freq), n=m2, axis=-1)[..., :n]
+    if not bias:
+        ac = ac / np.arange(n, 0.0, -1)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        ac = (ac / ac[..., :1]).astype(np.float64)
+    return np.swapaxes(ac, axis, -1)
+
+
+def autocovariance(x, axis=0, bias=True):  # diagnostics.py:145-155
+    return autocorrelation(x, axis, bias) * x.var(axis=axis, keepdims=True)
+
+
+def effective_sample_size(x, bias=True):  # diagnostics.py:158-203
+    x = np.asarray(x)
+    assert x.ndim >= 2 and x.shape[1] >= 2
+    gamma_k_c = autocovariance(x, axis=1, bias=bias)
+    var_within, var_estimator = _chain_variance_stats(x)
+    rho_k = 1.0 - (var_within - gamma_k_c.mean(axis=0)) / var_estimator
+    rho_k[0] = 1.0
+    big_rho = rho_k[:-1:2, ...] + rho_k[1::2, ...]
+    big_rho = np.concatenate(
+        [big_rho[:1], np.minimum.accumulate(np.clip(big_rho[1:, ...], 0, None), axis=0)], axis=0)
+    tau = -1.0 + 2.0 * big_rho.sum(axis=0)
+    return np.prod(x.shape[:2]) / tau
+
+
+def hpdi(x, prob=0.90, axis=0):  # diagnostics.py:206-231
+    x = np.swapaxes(x, axis, 0)
+    sorted_x = np.sort(x, axis=0)
+    mass = x.shape[0]
+    index_length = int(prob * mass)
+    lengths = sorted_x[index_length:] - sorted_x[: (mass - index_length)]
+    start = lengths.argmin(axis=0)
+    left = np.swapaxes(np.take_along_axis(sorted_x, start[None, ...], axis=0), axis, 0)
+    right = np.swapaxes(np.take_along_axis(sorted_x, (start + index_length)[None, ...], axis=0),
+                        axis, 0)
+    return np.concatenate([left, right], axis=axis)
+
+
+def summary(samples, prob=0.90, group_by_chain=True):  # diagnostics.py:234-285
+    if not isinstance(samples, dict):
+        samples = {"Param:0": samples}
+    if not group_by_chain:
+        samples = {k: np.asarray(v)[None, ...] for k, v in samples.items()}
+    out = {}
+    for name, value in samples.items():
+        value = np.asarray(value)
+        if len(value) == 0:
+            continue
+        flat = np.reshape(value, (-1,) + value.shape[2:])
+        hpd = hpdi(flat, prob=prob)
+        out[name] = OrderedDict([
+            ("mean", flat.mean(axis=0)), ("std", flat.std(axis=0, ddof=1)),
+            ("median", np.median(flat, axis=0)),
+            ("{:.1f}%".format(50 * (1 - prob)), hpd[0]), ("{:.1f}%".format(50 * (1 + prob)), hpd[1]),
+            ("n_eff", effective_sample_size(value)), ("r_hat", split_gelman_rubin(value))])
+    return out
+
+
+def print_summary(samples, prob=0.90, group_by_chain=True):  # diagnostics.py:288-342
+    if not isinstance(samples, dict):
+        samples = {"Param:0": samples}
+    if not group_by_chain:
+        samples = {k: np.asarray(v)[None, ...] for k, v in samples.items()}
+    summary_dict = summary(samples, prob, group_by_chain=True)
+    if not summary_dict:
+        return
+    max_len = max(max(len(k) + 2 + 3 * (np.ndim(v) - 2) for k, v in samples.items()), 10)
+    name_format = "{:>" + str(max_len) + "}"
+    header_format = name_format + " {:>9}" * 7
+    columns = [""] + list(list(summary_dict.values())[0].keys())
+    print()
+    print(header_format.format(*columns))
+    row_format = name_format + " {:>9.2f}" * 7
+    for name, stats in summary_dict.items():
+        shape = stats["mean"].shape
+        if len(shape) == 0:
+            print(row_format.format(name, *stats.values()))
+        else:
+            for idx in product(*map(range, shape)):
+                idx_str = "[{}]".format(",".join(map(str, idx)))
+                print(row_format.format(name + idx_str, *[v[idx] for v in stats.values()]))
+    print()

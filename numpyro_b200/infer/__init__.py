@@ -1,0 +1,5 @@
+from .hmc import HMC, NUTS, HMCAdaptState, HMCState, MCMCKernel, init_to_uniform, init_to_value
+from .mcmc import MCMC
+
+__all__ = ["HMC", "NUTS", "MCMC", "MCMCKernel", "HMCState", "HMCAdaptState", "init_to_uniform",
+           "init_to_value"]

@@ -1,0 +1,408 @@
+"""``HMC`` / ``NUTS`` kernels with the constructor and ``MCMCKernel`` surface of
+``numpyro/infer/hmc.py:541-948``, running on the CUDA library.
+
+The transition itself (``hmc.py:459-530`` and everything below it in
+``hmc_util.py``) executes inside persistent CUDA kernels; this module only mirrors the
+reference's plugin interface: argument checking, ``HMCState`` pytrees, key handling.
+"""
+from collections import namedtuple
+import ctypes as C
+import math
+import warnings
+
+import numpy as np
+
+from .. import _lib, models
+from .. import random as b2random
+
+HMCState = namedtuple(  # hmc.py:31-48
+    "HMCState",
+    ["i", "z", "z_grad", "potential_energy", "energy", "r", "trajectory_length", "num_steps",
+     "accept_prob", "mean_accept_prob", "diverging", "adapt_state", "rng_key"],
+)
+HMCAdaptState = namedtuple(  # hmc_util.py:18-30
+    "HMCAdaptState",
+    ["step_size", "inverse_mass_matrix", "mass_matrix_sqrt", "mass_matrix_sqrt_inv", "ss_state",
+     "mm_state", "window_idx", "rng_key"],
+)
+
+_VEC = {"z": 0, "z_grad": 1, "inverse_mass_matrix": 2, "mass_matrix_sqrt": 3, "welford_mean": 4,
+        "welford_m2": 5}
+EXTRA_FIELDS = ("potential_energy", "energy", "num_steps", "accept_prob", "mean_accept_prob",
+                "diverging", "adapt_state.step_size")
+
+
+def init_to_uniform(site=None, radius=2):
+    """``numpyro/infer/initialization.py:95-129`` (marker: the draws happen on device)."""
+    return ("uniform", float(radius))
+
+
+def init_to_value(site=None, values={}):
+    """``numpyro/infer/initialization.py`` ``init_to_value``: constrained values per site."""
+    return ("value", dict(values))
+
+
+class MCMCKernel:
+    """The abstract plugin surface ``MCMC`` drives (``numpyro/infer/mcmc.py:32-158``)."""
+
+    def postprocess_fn(self, model_args, model_kwargs):
+        return lambda x: x
+
+    def init(self, rng_key, num_warmup, init_params, model_args, model_kwargs):
+        raise NotImplementedError
+
+    def sample(self, state, model_args, model_kwargs):
+        raise NotImplementedError
+
+    @property
+    def sample_field(self):
+        raise NotImplementedError
+
+    @property
+    def default_fields(self):
+        return (self.sample_field,)
+
+    @property
+    def is_ensemble_kernel(self):
+        return False
+
+    def get_diagnostics_str(self, state):
+        return ""
+
+
+class HMC(MCMCKernel):
+    """Hamiltonian Monte Carlo with fixed trajectory length (``hmc.py:541-822``)."""
+
+    def __init__(self, model=None, potential_fn=None, kinetic_fn=None, step_size=1.0,
+                 inverse_mass_matrix=None, adapt_step_size=True, adapt_mass_matrix=True,
+                 dense_mass=False, target_accept_prob=0.8, num_steps=None,
+                 trajectory_length=2 * math.pi, init_strategy=init_to_uniform,
+                 find_heuristic_step_size=False, forward_mode_differentiation=False,
+                 regularize_mass_matrix=True):
+        if not (model is None) ^ (potential_fn is None):
+            raise ValueError("Only one of `model` or `potential_fn` must be specified.")
+        if type(self) is HMC:
+            if (num_steps is None) & (trajectory_length is None):
+                raise ValueError(
+                    "At least one of `num_steps` or `trajectory_length` must be specified.")
+            if adapt_step_size & (num_steps is not None) & (trajectory_length is not None):
+                warnings.warn("If both `num_steps` and `trajectory_length` are specified step size "
+                              "can't be adapted", stacklevel=2)
+        if potential_fn is not None:
+            raise NotImplementedError(
+                "an arbitrary `potential_fn` is outside the registered potential families; "
+                "numpyro_b200 has no generic autodiff fallback")
+        if kinetic_fn is not None:
+            raise NotImplementedError("only the euclidean kinetic energy is implemented")
+        if find_heuristic_step_size:
+            raise NotImplementedError("find_heuristic_step_size=True is not implemented yet")
+        if dense_mass is not False and dense_mass != []:
+            raise NotImplementedError("dense_mass / structured mass matrices are not implemented yet")
+        self._model = models.resolve(model)
+        self._potential_fn = None
+        self._kinetic_fn = None
+        self._num_steps = num_steps
+        self._step_size = float(step_size) if isinstance(step_size, int) else step_size
+        self._inverse_mass_matrix = inverse_mass_matrix
+        self._adapt_step_size = adapt_step_size
+        self._adapt_mass_matrix = adapt_mass_matrix
+        self._dense_mass = dense_mass
+        self._target_accept_prob = target_accept_prob
+        self._trajectory_length = (float(trajectory_length) if isinstance(trajectory_length, int)
+                                   else trajectory_length)
+        self._algo = "HMC"
+        self._max_tree_depth = 10
+        self._init_strategy = init_strategy
+        self._find_heuristic_step_size = find_heuristic_step_size
+        self._forward_mode_differentiation = forward_mode_differentiation
+        self._regularize_mass_matrix = regularize_mass_matrix
+        self.partitionable = None  # None -> numpyro_b200.random.DEFAULT_PARTITIONABLE
+        # set on first call to init
+        self._init_fn = None
+        self._potential_fn_gen = None
+        self._postprocess_fn = None
+        self._sample_fn = None
+        self._handle = None
+        self._bound = None
+        self._data = None
+        self._vectorized = False
+        self._last_state = None
+
+    # ------------------------------------------------------------------ properties
+    @property
+    def model(self):
+        return self._model
+
+    @property
+    def sample_field(self):
+        return "z"
+
+    @property
+    def default_fields(self):
+        return ("z", "diverging")
+
+    def get_diagnostics_str(self, state):
+        return "{} steps of size {:.2e}. acc. prob={:.2f}".format(
+            state.num_steps, state.adapt_state.step_size, state.mean_accept_prob)
+
+    def postprocess_fn(self, args, kwargs):
+        if self._postprocess_fn is None:
+            return lambda x: x
+        return self._postprocess_fn
+
+    # ------------------------------------------------------------------ handle management
+    def _destroy(self):
+        if self._handle is not None:
+            _lib.lib().b200mc_destroy(self._handle)
+            self._handle = None
+
+    def __del__(self):
+        try:
+            self._destroy()
+        except Exception:
+            pass
+
+    def __getstate__(self):  # hmc.py:818-822
+        state = self.__dict__.copy()
+        for k in ("_sample_fn", "_init_fn", "_handle", "_data", "_last_state", "_postprocess_fn"):
+            state[k] = None
+        return state
+
+    def _part(self):
+        return int(b2random.DEFAULT_PARTITIONABLE if self.partitionable is None
+                   else self.partitionable)
+
+    def _create(self, bound, num_chains, num_warmup):
+        _lib.require_device()
+        self._destroy()
+        lib = _lib.lib()
+        d0 = _lib.DeviceArray.from_numpy(bound.data0)
+        d1 = _lib.DeviceArray.from_numpy(bound.data1) if bound.data1 is not None else None
+        imm = None
+        if self._inverse_mass_matrix is not None:
+            m = self._inverse_mass_matrix
+            if isinstance(m, dict):
+                if len(m) != 1:
+                    raise NotImplementedError("block mass matrices are not implemented yet")
+                m = next(iter(m.values()))
+            m = np.asarray(m, np.float32)
+            if m.ndim != 1 or m.shape[0] != bound.dim:
+                raise NotImplementedError("only a diagonal inverse_mass_matrix [D] is implemented")
+            imm = _lib.DeviceArray.from_numpy(m)
+        depth = self._max_tree_depth
+        depth = depth if isinstance(depth, tuple) else (depth, depth)
+        kind, arg = self._strategy()
+        cfg = _lib.Config(
+            family=bound.family, num_chains=num_chains, N=bound.N, ncols=bound.ncols,
+            data0_dev=d0.ptr, data1_dev=d1.ptr if d1 is not None else None,
+            algo=0 if self._algo == "NUTS" else 1, step_size=float(self._step_size),
+            adapt_step_size=int(bool(self._adapt_step_size)),
+            adapt_mass_matrix=int(bool(self._adapt_mass_matrix)), dense_mass=0,
+            regularize_mass_matrix=int(bool(self._regularize_mass_matrix)),
+            target_accept_prob=float(self._target_accept_prob),
+            max_tree_depth_warmup=int(depth[0]), max_tree_depth_sample=int(depth[1]),
+            num_warmup=int(num_warmup),
+            has_trajectory_length=int(self._trajectory_length is not None),
+            trajectory_length=float(self._trajectory_length or 0.0),
+            num_steps=int(self._num_steps or 0), threefry_partitionable=self._part(),
+            init_radius=float(arg) if kind == "uniform" else 2.0,
+            inverse_mass_matrix_dev=imm.ptr if imm is not None else None)
+        h = C.c_void_p()
+        _lib.check(lib.b200mc_create(C.byref(cfg), C.byref(h)))
+        self._handle = h
+        self._data = (d0, d1, imm)
+        self._bound = bound
+        self._num_chains = num_chains
+        self._num_warmup = num_warmup
+        self._postprocess_fn = bound.postprocess
+        self._potential_fn_gen = bound
+
+    def _strategy(self):
+        s = self._init_strategy
+        if callable(s):
+            s = s()
+        if not (isinstance(s, tuple) and s[0] in ("uniform", "value")):
+            raise NotImplementedError("init_strategy must be init_to_uniform or init_to_value")
+        return s
+
+    # ------------------------------------------------------------------ state <-> device
+    def _snapshot(self):
+        lib, h = _lib.lib(), self._handle
+        Cn, D = self._num_chains, self._bound.dim
+        sc = np.zeros(Cn, _lib.SCALARS_DTYPE)
+        _lib.check(lib.b200mc_get_scalars(h, sc.ctypes.data))
+        tmp = _lib.DeviceArray((Cn, D), np.float32)
+        vec = {}
+        for name, which in _VEC.items():
+            _lib.check(lib.b200mc_get_vector(h, which, tmp.ptr, None))
+            vec[name] = tmp.numpy()
+        return sc, vec
+
+    def _to_state(self, sc, vec):
+        b = self._bound
+        sq = (lambda a: a) if self._vectorized else (lambda a: a[0])
+        block = tuple(sorted(k for k, _ in b.trace_sites))
+        imm = vec["inverse_mass_matrix"]
+        adapt = HMCAdaptState(
+            step_size=sq(sc["step_size"].copy()),
+            inverse_mass_matrix={block: sq(imm)},
+            mass_matrix_sqrt={block: sq(vec["mass_matrix_sqrt"])},
+            mass_matrix_sqrt_inv={block: sq(np.sqrt(imm))},
+            ss_state=(sq(sc["ss_x_t"].copy()), sq(sc["ss_x_avg"].copy()), sq(sc["ss_g_avg"].copy()),
+                      sq(sc["ss_t"].copy()), sq(sc["ss_prox_center"].copy())),
+            mm_state={block: (sq(vec["welford_mean"]), sq(vec["welford_m2"]), sq(sc["mm_n"].copy()))},
+            window_idx=sq(sc["window_idx"].copy()),
+            rng_key=sq(sc["adapt_key"].copy()))
+        tl = None
+        if self._algo == "HMC" and self._trajectory_length is not None:
+            tl = np.float32(self._trajectory_length)
+        state = HMCState(
+            i=sq(sc["i"].copy()), z=b.unravel(sq(vec["z"])), z_grad=b.unravel(sq(vec["z_grad"])),
+            potential_energy=sq(sc["potential_energy"].copy()), energy=sq(sc["energy"].copy()),
+            r=None, trajectory_length=tl, num_steps=sq(sc["num_steps"].copy()),
+            accept_prob=sq(sc["accept_prob"].copy()),
+            mean_accept_prob=sq(sc["mean_accept_prob"].copy()),
+            diverging=sq(sc["diverging"].astype(bool)), adapt_state=adapt,
+            rng_key=sq(sc["rng_key"].copy()))
+        self._last_state = state
+        self._last_grad_evals = sc["grad_evals"].copy()
+        return state
+
+    def _push_state(self, state):
+        """Make the device hold ``state`` (no-op when it is the state we last returned)."""
+        if state is self._last_state:
+            return
+        lib, h, b = _lib.lib(), self._handle, self._bound
+        Cn = self._num_chains
+        up = (lambda a: np.asarray(a)) if self._vectorized else (lambda a: np.asarray(a)[None])
+        sc = np.zeros(Cn, _lib.SCALARS_DTYPE)
+        a = state.adapt_state
+        block = next(iter(a.inverse_mass_matrix))
+        for name, val in (("i", state.i), ("potential_energy", state.potential_energy),
+                          ("energy", state.energy), ("num_steps", state.num_steps),
+                          ("accept_prob", state.accept_prob),
+                          ("mean_accept_prob", state.mean_accept_prob),
+                          ("diverging", np.asarray(state.diverging).astype(np.int32)),
+                          ("rng_key", state.rng_key), ("step_size", a.step_size),
+                          ("ss_x_t", a.ss_state[0]), ("ss_x_avg", a.ss_state[1]),
+                          ("ss_g_avg", a.ss_state[2]), ("ss_t", a.ss_state[3]),
+                          ("ss_prox_center", a.ss_state[4]), ("mm_n", a.mm_state[block][2]),
+                          ("window_idx", a.window_idx), ("adapt_key", a.rng_key)):
+            sc[name] = up(val)
+        if getattr(self, "_last_grad_evals", None) is not None:
+            sc["grad_evals"] = self._last_grad_evals
+        _lib.check(lib.b200mc_set_scalars(h, sc.ctypes.data))
+        vecs = {"z": b.ravel(state.z), "z_grad": b.ravel(state.z_grad),
+                "inverse_mass_matrix": a.inverse_mass_matrix[block],
+                "mass_matrix_sqrt": a.mass_matrix_sqrt[block],
+                "welford_mean": a.mm_state[block][0], "welford_m2": a.mm_state[block][1]}
+        for name, val in vecs.items():
+            d = _lib.DeviceArray.from_numpy(up(val).reshape(Cn, b.dim), np.float32)
+            _lib.check(lib.b200mc_set_vector(h, _VEC[name], d.ptr, None))
+            _lib.check(lib.b200mc_stream_synchronize(None))
+        self._last_state = state
+
+    # ------------------------------------------------------------------ MCMCKernel interface
+    def init(self, rng_key, num_warmup, init_params=None, model_args=(), model_kwargs={}):
+        """``hmc.py:740-799``: ``rng_key`` is ``uint32[2]`` (one chain) or ``uint32[C, 2]``
+        (vectorized chains)."""
+        rng_key = np.asarray(rng_key, np.uint32)
+        self._vectorized = not b2random.is_prng_key(rng_key)
+        keys = rng_key.reshape(-1, 2)
+        bound = self._model.bind(*model_args, **model_kwargs)
+        self._create(bound, keys.shape[0], num_warmup)
+        kind, arg = self._strategy()
+        if init_params is None and kind == "value":
+            missing = [k for k, _ in bound.trace_sites if k not in arg]
+            if missing:
+                raise NotImplementedError(f"init_to_value must cover every latent site; missing {missing}")
+            raise NotImplementedError(
+                "init_to_value is not implemented yet: pass unconstrained `init_params` instead")
+        z0 = None
+        if init_params is not None:
+            z = bound.ravel(init_params)
+            z = z.reshape(keys.shape[0], bound.dim) if self._vectorized else z.reshape(1, bound.dim)
+            z0 = _lib.DeviceArray.from_numpy(z, np.float32)
+        kd = _lib.DeviceArray.from_numpy(keys)
+        _lib.check(_lib.lib().b200mc_init(self._handle, kd.ptr, z0.ptr if z0 is not None else None,
+                                          None))
+        sc, vec = self._snapshot()
+        if (sc["status"] != 0).any():
+            raise RuntimeError("Cannot find valid initial parameters. Please check your model again.")
+        self._sample_fn = self._sample_one
+        self._init_fn = True
+        return self._to_state(sc, vec)
+
+    def _sample_one(self, state, model_args, model_kwargs):
+        self._push_state(state)
+        _lib.check(_lib.lib().b200mc_sample(self._handle, 1, 1, 1, None, None))
+        return self._to_state(*self._snapshot())
+
+    def sample(self, state, model_args, model_kwargs):
+        """``hmc.py:806-816``: one transition."""
+        if self._handle is None:
+            raise RuntimeError("call `init` before `sample`")
+        return self._sample_one(state, model_args, model_kwargs)
+
+    # ------------------------------------------------------------------ fused loop (fori_collect)
+    def run_loop(self, state, num_iters, collect_start, thinning, n_keep, fields):
+        """Run ``num_iters`` transitions in ONE launch, collecting ``fields`` (a subset of
+        ``("z",) + EXTRA_FIELDS``) exactly as ``fori_collect`` would
+        (``numpyro/util.py:277-407``).  Returns ``(dict of [n_keep, C, ...] arrays, last state)``."""
+        self._push_state(state)
+        Cn, D = self._num_chains, self._bound.dim
+        bufs, col = {}, _lib.Collect(n_keep=n_keep)
+        spec = {"z": ("z_dev", (n_keep, Cn, D), np.float32),
+                "potential_energy": ("potential_energy_dev", (n_keep, Cn), np.float32),
+                "energy": ("energy_dev", (n_keep, Cn), np.float32),
+                "num_steps": ("num_steps_dev", (n_keep, Cn), np.int32),
+                "accept_prob": ("accept_prob_dev", (n_keep, Cn), np.float32),
+                "mean_accept_prob": ("mean_accept_prob_dev", (n_keep, Cn), np.float32),
+                "diverging": ("diverging_dev", (n_keep, Cn), np.int32),
+                "adapt_state.step_size": ("step_size_dev", (n_keep, Cn), np.float32)}
+        if n_keep > 0:
+            for f in fields:
+                attr, shape, dt = spec[f]
+                bufs[f] = _lib.DeviceArray(shape, dt).zero_()
+                setattr(col, attr, bufs[f].ptr)
+        _lib.check(_lib.lib().b200mc_sample(self._handle, int(num_iters), int(collect_start),
+                                            int(thinning), C.byref(col), None))
+        new_state = self._to_state(*self._snapshot())
+        out = {f: b.numpy() for f, b in bufs.items()}
+        if "diverging" in out:
+            out["diverging"] = out["diverging"].astype(bool)
+        return out, new_state
+
+    def grad_evals(self):
+        """Cumulative potential+gradient evaluations per chain (init search included)."""
+        return None if getattr(self, "_last_grad_evals", None) is None else self._last_grad_evals.copy()
+
+    def potential_and_grad(self, z):
+        """Tier-2 hook: ``(U, grad)`` at flat unconstrained points ``z[n, D]``."""
+        z = np.ascontiguousarray(z, np.float32).reshape(-1, self._bound.dim)
+        zd = _lib.DeviceArray.from_numpy(z)
+        U = _lib.DeviceArray((z.shape[0],), np.float32)
+        g = _lib.DeviceArray(z.shape, np.float32)
+        _lib.check(_lib.lib().b200mc_potential_and_grad(self._handle, zd.ptr, z.shape[0], U.ptr,
+                                                        g.ptr, None))
+        return U.numpy(), g.numpy()
+
+
+class NUTS(HMC):
+    """No-U-Turn Sampler (``hmc.py:825-948``)."""
+
+    def __init__(self, model=None, potential_fn=None, kinetic_fn=None, step_size=1.0,
+                 inverse_mass_matrix=None, adapt_step_size=True, adapt_mass_matrix=True,
+                 dense_mass=False, target_accept_prob=0.8, trajectory_length=None,
+                 max_tree_depth=10, init_strategy=init_to_uniform, find_heuristic_step_size=False,
+                 forward_mode_differentiation=False, regularize_mass_matrix=True):
+        super().__init__(potential_fn=potential_fn, model=model, kinetic_fn=kinetic_fn,
+                         step_size=step_size, inverse_mass_matrix=inverse_mass_matrix,
+                         adapt_step_size=adapt_step_size, adapt_mass_matrix=adapt_mass_matrix,
+                         dense_mass=dense_mass, target_accept_prob=target_accept_prob,
+                         trajectory_length=trajectory_length, init_strategy=init_strategy,
+                         find_heuristic_step_size=find_heuristic_step_size,
+                         forward_mode_differentiation=forward_mode_differentiation,
+                         regularize_mass_matrix=regularize_mass_matrix)
+        self._max_tree_depth = max_tree_depth
+        self._algo = "NUTS"

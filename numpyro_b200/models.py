@@ -1,0 +1,131 @@
+"""Registry of potential families.
+
+The reference turns an arbitrary Python model into a potential by tracing it through
+its effect handlers (``numpyro/infer/util.py:632-800``).  Here generic tracing is replaced
+by closed-form potentials for the registered families; a model outside the registry
+raises ``NotImplementedError`` -- there is no fallback.
+
+Each registered model is a callable marker with the same *signature* as the reference's
+example model, so user code reads ``NUTS(models.logistic_regression)`` /
+``mcmc.run(key, X, y)``.
+"""
+from collections import OrderedDict
+
+import numpy as np
+
+LOGISTIC, EIGHT_SCHOOLS, HORSESHOE, SV = 0, 1, 2, 3
+
+
+class BoundModel:
+    """A family bound to its data: what ``initialize_model`` returns in the reference
+    (``ModelInfo``: site layout, postprocess_fn), minus the potential, which lives in CUDA."""
+
+    def __init__(self, family, name, N, ncols, data0, data1, trace_sites, constrain):
+        self.family, self.name, self.N, self.ncols = family, name, N, ncols
+        self.data0, self.data1 = data0, data1
+        self.trace_sites = tuple(trace_sites)  # (site, shape) in model trace order
+        self._constrain = constrain
+        off, self.flat_sites = 0, OrderedDict()
+        for k, shape in sorted(self.trace_sites):  # ravel_pytree: sorted site names
+            size = int(np.prod(shape)) if len(shape) else 1
+            self.flat_sites[k] = (off, size, tuple(shape))
+            off += size
+        self.dim = off
+
+    def unravel(self, zflat):
+        """flat ``[..., D]`` -> dict of sites (batch dims kept)."""
+        zflat = np.asarray(zflat)
+        batch = zflat.shape[:-1]
+        return {k: zflat[..., o:o + s].reshape(batch + shp) for k, (o, s, shp) in
+                self.flat_sites.items()}
+
+    def ravel(self, zdict):
+        parts = []
+        batch = None
+        for k, (o, s, shp) in self.flat_sites.items():
+            v = np.asarray(zdict[k], np.float32)
+            b = v.shape[:v.ndim - len(shp)]
+            batch = b if batch is None else batch
+            parts.append(v.reshape(b + (s,)))
+        return np.concatenate(parts, axis=-1)
+
+    def postprocess(self, zdict):
+        """``postprocess_fn``: unconstrained dict -> constrained + deterministic sites
+        (``infer/util.py:176-230,583-609``)."""
+        return self._constrain(zdict)
+
+
+class RegisteredModel:
+    def __init__(self, name, binder, doc):
+        self.__name__ = name
+        self.__doc__ = doc
+        self._binder = binder
+
+    def bind(self, *args, **kwargs):
+        return self._binder(*args, **kwargs)
+
+    def __call__(self, *args, **kwargs):
+        raise NotImplementedError(
+            f"{self.__name__} is a registered potential family, not a traced program: "
+            "pass it to numpyro_b200.infer.NUTS/HMC")
+
+
+def _bind_logistic(data, labels, subsample_size=None):
+    if subsample_size is not None:
+        raise NotImplementedError("subsample_size (HMCECS) is not part of the registered hot path")
+    X = np.ascontiguousarray(data, np.float32)
+    y = np.ascontiguousarray(labels).astype(np.uint8)
+    if X.ndim != 2 or y.shape != (X.shape[0],):
+        raise ValueError("logistic_regression expects data [N, D] and labels [N]")
+    return BoundModel(LOGISTIC, "logistic", X.shape[0], X.shape[1], X, y,
+                      [("coefs", (X.shape[1],))], lambda z: dict(z))
+
+
+def _bind_eight_schools(J, sigma, y=None):
+    if y is None:
+        raise NotImplementedError("eight_schools without observations (prior sampling) is not registered")
+    sigma = np.ascontiguousarray(sigma, np.float32)
+    y = np.ascontiguousarray(y, np.float32)
+    assert sigma.shape == (J,) and y.shape == (J,)
+
+    def constrain(z):
+        mu, tau = z["mu"], np.exp(z["tau"])
+        out = {"mu": mu, "tau": tau, "theta_base": z["theta_base"]}
+        out["theta"] = mu[..., None] + tau[..., None] * z["theta_base"]
+        return out
+
+    return BoundModel(EIGHT_SCHOOLS, "eight_schools", J, 0, y, sigma,
+                      [("mu", ()), ("tau", ()), ("theta_base", (J,))], constrain)
+
+
+def _bind_sv(returns):
+    r = np.ascontiguousarray(returns, np.float32)
+    T = r.shape[0]
+
+    def constrain(z):
+        return {"nu": np.exp(z["nu"]), "s": z["s"], "sigma": np.exp(z["sigma"])}
+
+    return BoundModel(SV, "stochastic_volatility", T, 0, r, None,
+                      [("sigma", ()), ("s", (T,)), ("nu", ())], constrain)
+
+
+logistic_regression = RegisteredModel(
+    "logistic_regression", _bind_logistic,
+    "coefs ~ Normal(0, 1)[D]; obs ~ Bernoulli(logits=data @ coefs)  (examples/covtype.py:66-71)")
+eight_schools_noncentered = RegisteredModel(
+    "eight_schools_noncentered", _bind_eight_schools,
+    "Non-centred eight schools with TransformReparam (README.md:101-110)")
+stochastic_volatility = RegisteredModel(
+    "stochastic_volatility", _bind_sv,
+    "Random-walk stochastic volatility (examples/stochastic_volatility.py:57-65)")
+
+REGISTRY = {m.__name__: m for m in (logistic_regression, eight_schools_noncentered,
+                                    stochastic_volatility)}
+
+
+def resolve(model):
+    if isinstance(model, RegisteredModel):
+        return model
+    raise NotImplementedError(
+        f"model {getattr(model, '__name__', model)!r} is outside the registered potential families "
+        f"{sorted(REGISTRY)}; numpyro_b200 has no generic tracing fallback")

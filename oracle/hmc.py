@@ -205,7 +205,9 @@ def run_chain(kernel, rng_key, num_warmup, num_samples, thinning=1, init_params=
     for i in range(upper):
         state = kernel.sample(state)
         idx = (i - start_idx) // thinning
-        if i >= start_idx and (i - start_idx) % thinning == 0 and 0 <= idx < size:
+        # util.py:334-351: every i >= start_idx writes slot idx, so the LAST draw of each
+        # thinning block is the one kept.
+        if i >= start_idx and 0 <= idx < size:
             out["z"][idx] = state.z.copy()
             for k in FIELDS[1:-1]:
                 out[k][idx] = getattr(state, k)

@@ -1,0 +1,129 @@
+"""CPU-only checks of the host side: the C-ABI library loads and exports every symbol the
+header declares, host-only entry points work, and the kernel classes keep the reference's
+argument checking (hmc.py:643-658, mcmc.py:342-354).  No compute calls."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def nb():
+    import __graft_entry__ as g
+
+    return g.build()
+
+
+def test_library_exports_every_declared_symbol(nb):
+    from numpyro_b200 import _lib
+
+    header = open(os.path.join(ROOT, "include", "b200mc.h")).read()
+    declared = set(re.findall(r"\b(b200mc_[a-z0-9_]+)\s*\(", header))
+    assert declared, "no declarations parsed"
+    lib = _lib.lib()
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in b200mc.h but not exported"
+    assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
+    assert lib.b200mc_version() == 1
+    assert C.sizeof(_lib.ChainScalars) == _lib.SCALARS_DTYPE.itemsize
+
+
+@pytest.mark.parametrize(
+    "num_steps, expected",  # reference golden vectors: test/infer/test_hmc_util.py:278-292
+    [(18, [(0, 17)]), (50, [(0, 6), (7, 44), (45, 49)]), (100, [(0, 14), (15, 89), (90, 99)]),
+     (150, [(0, 74), (75, 99), (100, 149)]), (200, [(0, 74), (75, 99), (100, 149), (150, 199)]),
+     (280, [(0, 74), (75, 99), (100, 229), (230, 279)])],
+)
+def test_adaptation_schedule_through_c_abi(nb, num_steps, expected):
+    from numpyro_b200 import _lib
+
+    s, e = (C.c_int * 40)(), (C.c_int * 40)()
+    n = _lib.lib().b200mc_adaptation_schedule(num_steps, s, e, 40)
+    assert [(s[i], e[i]) for i in range(n)] == expected
+
+
+def test_schedule_matches_oracle_everywhere(nb):
+    from numpyro_b200 import _lib
+    from oracle.hmc_util import build_adaptation_schedule
+
+    s, e = (C.c_int * 40)(), (C.c_int * 40)()
+    for num_steps in list(range(1, 400)) + [1000, 5000, 100000]:
+        n = _lib.lib().b200mc_adaptation_schedule(num_steps, s, e, 40)
+        assert [(s[i], e[i]) for i in range(n)] == [tuple(w) for w in
+                                                    build_adaptation_schedule(num_steps)]
+
+
+def test_constructor_contract(nb):
+    from numpyro_b200 import models
+    from numpyro_b200.infer import HMC, MCMC, NUTS
+
+    with pytest.raises(ValueError, match="Only one of `model` or `potential_fn`"):
+        NUTS()
+    with pytest.raises(ValueError, match="Only one of `model` or `potential_fn`"):
+        NUTS(models.logistic_regression, potential_fn=lambda z: 0.0)
+    with pytest.raises(ValueError, match="num_steps` or `trajectory_length"):
+        HMC(models.logistic_regression, trajectory_length=None)
+    with pytest.warns(UserWarning, match="step size can't be adapted"):
+        HMC(models.logistic_regression, num_steps=3)
+    # outside the registered families: raises, never falls back
+    with pytest.raises(NotImplementedError):
+        NUTS(lambda x: x)
+    with pytest.raises(NotImplementedError):
+        NUTS(potential_fn=lambda z: 0.0)
+    with pytest.raises(NotImplementedError):
+        NUTS(models.logistic_regression, dense_mass=True)
+    k = NUTS(models.eight_schools_noncentered, step_size=1, max_tree_depth=(5, 10))
+    assert k._step_size == 1.0 and isinstance(k._step_size, float)
+    assert k.sample_field == "z" and k.default_fields == ("z", "diverging")
+    assert k._algo == "NUTS" and k._max_tree_depth == (5, 10) and k.model is models.eight_schools_noncentered
+    assert k.postprocess_fn((), {})("x") == "x"  # identity before init (hmc.py:801-804)
+    assert not k.is_ensemble_kernel
+    with pytest.raises(ValueError, match="thinning"):
+        MCMC(k, num_warmup=1, num_samples=1, thinning=0)
+    with pytest.raises(ValueError, match="Only supporting"):
+        MCMC(k, num_warmup=1, num_samples=1, chain_method="foo")
+    with pytest.raises(NotImplementedError):
+        models.logistic_regression(np.zeros((2, 2)), np.zeros(2))
+
+
+def test_no_device_raises_loudly(nb):
+    from numpyro_b200 import _lib, models, random
+    from numpyro_b200.infer import NUTS
+
+    if _lib.lib().b200mc_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(_lib.B200Error, match="no CPU fallback"):
+        random.split(random.PRNGKey(0))
+    with pytest.raises(_lib.B200Error, match="no CPU fallback"):
+        NUTS(models.eight_schools_noncentered).init(random.PRNGKey(0), 10, None,
+                                                    (8, np.ones(8)), {"y": np.ones(8)})
+
+
+def test_site_layout_follows_sorted_names(nb):
+    from numpyro_b200 import models
+
+    b = models.stochastic_volatility.bind(np.ones(5, np.float32))
+    assert list(b.flat_sites) == ["nu", "s", "sigma"] and b.dim == 7
+    assert [k for k, _ in b.trace_sites] == ["sigma", "s", "nu"]
+    z = np.arange(14, dtype=np.float32).reshape(2, 7)
+    u = b.unravel(z)
+    assert u["nu"].shape == (2,) and u["s"].shape == (2, 5)
+    assert np.array_equal(b.ravel(u), z)
+    b8 = models.eight_schools_noncentered.bind(8, np.ones(8), y=np.ones(8))
+    assert list(b8.flat_sites) == ["mu", "tau", "theta_base"] and b8.dim == 10
+    out = b8.postprocess(b8.unravel(np.zeros((3, 10), np.float32)))
+    assert out["theta"].shape == (3, 8) and np.allclose(out["tau"], 1.0)
+
+
+def test_diagnostics_known_answers(nb):
+    from numpyro_b200 import diagnostics as D
+
+    x = np.arange(1000.0).reshape(100, 10)  # test/test_diagnostics.py:105-107
+    np.testing.assert_allclose(D.effective_sample_size(x, bias=False), 52.64, atol=0.01)
+    s = D.summary({"a": np.random.default_rng(0).normal(size=(2, 100, 3))})
+    assert s["a"]["r_hat"].shape == (3,)
+    D.print_summary({"a": np.random.default_rng(0).normal(size=(2, 100, 3))})
