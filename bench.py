@@ -1,0 +1,372 @@
+#!/usr/bin/env python
+"""Benchmark of the HMC/NUTS hot path on the headline workload.
+
+Workload (BASELINE.json configs[2]): Bayesian logistic regression NUTS on synthetic
+covtype-shape data (N=581,012 rows, D=55 columns, float32 X, uint8 labels), one chain per
+GPU.  A "step" is one pass of the hot path over one batch: ``--transitions`` NUTS
+transitions (after an untimed adaptation warm-up) executed by ONE persistent kernel
+launch; the metric is gradient evaluations (= leapfrogs, ``num_steps``) per second, the
+quantity the reference's own notebook divides by
+(notebooks/source/logistic_regression.ipynb:309-310).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl own|reference]
+
+N > 1 (torchrun, one rank per GPU): chains are sharded over ranks, X replicated, no
+data-path collective ("weak" scaling); time is the max over ranks.
+
+``--impl reference`` times the CPU restatement of the reference's algorithm (oracle/,
+C potential with OpenMP over all host cores): jax/numpyro cannot be imported in this image
+(no wheel, no network), so the oracle port stands in for NumPyro's JAX-CPU path.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+N_ROWS, N_COLS = 581012, 55
+ALGO_BYTES_PER_GRAD = N_ROWS * N_COLS * 4 + N_ROWS  # X once as fp32 + 1-byte labels
+METRIC = "grad_evals_per_sec"
+UNIT = "grad-evals/s"
+
+
+def make_covtype_shape(seed=0, n=N_ROWS, d=N_COLS):
+    """standardised N(0,1) features + intercept column (covtype.py:47-49)."""
+    rng = np.random.default_rng(seed)
+    X0 = rng.standard_normal((n, d - 1), dtype=np.float32)
+    X0 = (X0 - X0.mean(0)) / X0.std(0)
+    X = np.hstack([X0, np.ones((n, 1), np.float32)]).astype(np.float32)
+    theta = (rng.standard_normal(d) * 0.5).astype(np.float32)
+    y = (rng.random(n) < 1.0 / (1.0 + np.exp(-(X @ theta)))).astype(np.uint8)
+    return np.ascontiguousarray(X), y
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            pass
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 7:
+                continue
+            try:
+                sm.append(float(c[0])); mx.append(float(c[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, c[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        self.f.close()
+        os.unlink(self.f.name)
+        if sm:
+            out["sm_mhz"] = float(np.median(sm))
+            out["sm_max_mhz"] = float(max(mx))
+            out["samples"] = len(sm)
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+# ---------------------------------------------------------------------------- CPU legs
+def cpu_nuts_sample(X, y, budget_s, max_transitions, cores_note=True):
+    """NUTS transitions of the oracle (reference restatement, C potential on all host cores)
+    from the init state with adaptation on, until ``budget_s`` seconds or
+    ``max_transitions``.  Returns (grad_evals, seconds, transitions, cores)."""
+    from oracle import cpotentials, hmc as ohmc, threefry as T
+    from oracle.hmc_util import Config
+
+    cpotentials.build()
+    fam = cpotentials.CLogistic(X, y)
+    kern = ohmc.HMCKernel(fam, cfg=Config(np.float32, True))
+    state = kern.init(T.PRNGKey(1), 1000)
+    fam.potential_and_grad(np.zeros(X.shape[1], np.float32))  # touch pages / spin up threads
+    g0, t0, n = kern.num_grad_evals, time.perf_counter(), 0
+    while n < max_transitions and time.perf_counter() - t0 < budget_s:
+        state = kern.sample(state)
+        n += 1
+    dt = time.perf_counter() - t0
+    return kern.num_grad_evals - g0, dt, n, fam.cores
+
+
+def run_reference(args):
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return 0
+    X, y = make_covtype_shape()
+    from oracle import cpotentials, hmc as ohmc, threefry as T
+    from oracle.hmc_util import Config
+
+    cpotentials.build()
+    fam = cpotentials.CLogistic(X, y)
+    kern = ohmc.HMCKernel(fam, cfg=Config(np.float32, True))
+    state = kern.init(T.PRNGKey(1), 1000)
+    per_step = args.ref_transitions
+    budget = args.ref_budget  # seconds for the whole run: stop adding transitions to a step past it
+    t_begin = time.perf_counter()
+
+    def step(state):
+        g0, t0 = kern.num_grad_evals, time.perf_counter()
+        for _ in range(per_step):
+            state = kern.sample(state)
+            if time.perf_counter() - t_begin > budget:
+                break
+        return state, kern.num_grad_evals - g0, time.perf_counter() - t0
+
+    for _ in range(args.warmup):
+        state, _, _ = step(state)
+    grads, secs = 0, 0.0
+    for _ in range(args.steps):
+        state, g, dt = step(state)
+        grads += g
+        secs += dt
+    value = grads / secs
+    sample = (f"{args.steps} steps x <= {per_step} NUTS transitions from the init state with "
+              f"adaptation on ({grads} grad evals), full N={N_ROWS} D={N_COLS} data")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": "covtype-shape logistic NUTS N=581012 D=55 (configs[2])",
+                   "chains_per_gpu": 1, "max_tree_depth": 10,
+                   "reference_kind": "CPU restatement of numpyro HMC/NUTS (oracle/), "
+                                     "jax not importable in this image"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": fam.cores, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------- GPU arm
+def run_own(args):
+    import ctypes as C
+
+    rank, world, local = dist_env()
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    import __graft_entry__ as g
+
+    nb = g.build()
+    from numpyro_b200 import _lib, models
+    from numpyro_b200.infer import MCMC, NUTS
+    from numpyro_b200.random import PRNGKey, split
+
+    lib = _lib.lib()
+    _lib.require_device()
+    _lib.check(lib.b200mc_set_device(local))
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        _lib.check(lib.b200mc_stream_synchronize(None))
+        if dist is not None:
+            dist.barrier()
+        _lib.check(lib.b200mc_stream_synchronize(None))
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        import torch
+
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if dist is None:
+            return x
+        import torch
+
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    X, y = make_covtype_shape()
+    # one chain per GPU: chain keys as MCMC.run would split them for `world` chains
+    key = PRNGKey(1) if world == 1 else split(PRNGKey(1), world)[rank]
+
+    # ---- untimed: bind data, adaptation warm-up (dual averaging + Welford windows)
+    kern = NUTS(models.logistic_regression)
+    mc = MCMC(kern, num_warmup=args.adapt, num_samples=args.transitions)
+    t0 = time.perf_counter()
+    mc.warmup(key, X, y, extra_fields=("num_steps",))
+    adapt_s = time.perf_counter() - t0
+    state = mc.post_warmup_state
+    adapted_step = float(np.asarray(state.adapt_state.step_size))
+    imm = np.asarray(next(iter(state.adapt_state.inverse_mass_matrix.values())), np.float32)
+
+    # ---- device-timed leg: inputs resident in HBM, one persistent launch per step,
+    #      CUDA events on the launching (null) stream
+    T_ = args.transitions
+    ns_buf = _lib.DeviceArray((T_, 1), np.int32)
+    z_buf = _lib.DeviceArray((T_, 1, N_COLS), np.float32)
+    col = _lib.Collect(n_keep=T_, z_dev=z_buf.ptr, num_steps_dev=ns_buf.ptr)
+    ev0, ev1 = lib.b200mc_event_create(), lib.b200mc_event_create()
+
+    def device_step():
+        _lib.check(lib.b200mc_event_record(ev0, None))
+        _lib.check(lib.b200mc_sample(kern._handle, T_, 0, 1, C.byref(col), None))
+        _lib.check(lib.b200mc_event_record(ev1, None))
+        ms = C.c_float()
+        _lib.check(lib.b200mc_event_elapsed_ms(ev0, ev1, C.byref(ms)))
+        return float(ms.value), int(ns_buf.numpy().sum())
+
+    for _ in range(args.warmup):
+        device_step()
+    launches0 = lib.b200mc_kernel_launches()
+    clocks = ClockSampler(local) if rank == 0 else None
+    barrier()
+    step_ms, step_grads = [], []
+    for _ in range(args.steps):
+        ms, gsum = device_step()
+        step_ms.append(ms)
+        step_grads.append(gsum)
+    barrier()
+    launches = lib.b200mc_kernel_launches() - launches0
+    total_ms = max_over_ranks(sum(step_ms))
+    total_grads = sum_over_ranks(float(sum(step_grads)))
+    value = total_grads / (total_ms * 1e-3)
+
+    # roofline of the dominant (only) kernel, this rank: algorithmic bytes per launch / duration
+    peak, peak_src = peaks()
+    my_gbs = ALGO_BYTES_PER_GRAD * sum(step_grads) / (sum(step_ms) * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "achieved": my_gbs, "peak": peak, "unit": "GB/s",
+                "frac": my_gbs / peak, "traffic": None, "peak_source": peak_src,
+                "kernel": "glm_kernel",
+                "bytes_per_grad_eval": ALGO_BYTES_PER_GRAD,
+                "grad_evals_per_launch": sum(step_grads) / max(1, len(step_grads)),
+                "us_per_grad_eval": 1e3 * sum(step_ms) / max(1, sum(step_grads))}
+    tr = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr):
+        with open(tr) as f:
+            roofline["traffic"] = json.load(f).get("glm_kernel_bytes_per_grad_eval")
+
+    # ---- end-to-end leg: public API (MCMC.run) with HOST buffers every step: X, y are
+    #      copied host->device inside the timed region, draws are read back
+    e2e_grads, e2e_s = 0, 0.0
+    z_last = {k: np.asarray(v) for k, v in kern._last_state.z.items()}
+    barrier()
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        k2 = NUTS(models.logistic_regression, step_size=adapted_step, inverse_mass_matrix=imm,
+                  adapt_step_size=False, adapt_mass_matrix=False)
+        m2 = MCMC(k2, num_warmup=0, num_samples=T_)
+        m2.run(key, X, y, init_params=z_last, extra_fields=("num_steps",))
+        ns = m2.get_extra_fields()["num_steps"]
+        _ = m2.get_samples()["coefs"].mean()
+        dt = time.perf_counter() - t0
+        k2._destroy()
+        if i >= args.warmup:
+            e2e_grads += int(ns.sum())
+            e2e_s += dt
+    barrier()
+    e2e_s = max_over_ranks(e2e_s)
+    e2e_grads = sum_over_ranks(float(e2e_grads))
+    e2e = {"value": e2e_grads / e2e_s, "unit": UNIT,
+           "h2d_bytes_per_step": int(X.nbytes + y.nbytes + 4 * N_COLS * 2 + 8),
+           "d2h_bytes_per_step": int(T_ * (N_COLS * 4 + 4 + 4))}
+    clk = clocks.stop() if clocks is not None else None
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        gr, dt, ntr, cores = cpu_nuts_sample(X, y, args.cpu_budget, 10**6)
+        cpu = {"value": gr / dt, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"{ntr} NUTS transitions ({gr} grad evals, {dt:.1f} s) of the oracle "
+                         f"from the init state on the full N={N_ROWS} D={N_COLS} data"}
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "covtype-shape logistic NUTS N=581012 D=55 (configs[2])",
+                       "chains_per_gpu": 1, "transitions_per_step": T_,
+                       "adapt_transitions_untimed": args.adapt, "adapted_step_size": adapted_step,
+                       "max_tree_depth": 10, "parallelism": f"chains x{world}",
+                       "l2": "inputs 128.4 MB per pass > 126 MB L2, streamed once per grad eval"},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+            "clocks": clk, "adapt_seconds": adapt_s,
+            "mean_tree_size": float(np.mean(step_grads)) / T_,
+        }
+        print(json.dumps(line))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--transitions", type=int, default=20, help="NUTS transitions per step")
+    ap.add_argument("--adapt", type=int, default=300, help="untimed adaptation transitions")
+    ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU baseline work")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--ref-transitions", type=int, default=2)
+    ap.add_argument("--ref-budget", type=float, default=150.0)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_own(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
