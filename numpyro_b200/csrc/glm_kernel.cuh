@@ -82,8 +82,9 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {
-  }
+  // bounded: a copy that never lands is a bug; fail loudly (launch error) instead of hanging
+  for (long it = 0; !mbar_try_wait(bar, parity); ++it)
+    if (it > (1L << 28)) __trap();
 }
 // TMA bulk copy global -> shared, completion counted in bytes on an mbarrier
 __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes,

@@ -164,7 +164,7 @@ def _tier3(nb, model, args, kwargs, fam32, n=50, part=True, algo="NUTS", chains=
 def test_tier3_logistic(nb, part):
     X, y = make_logistic(3000, 3, seed=5)
     ex, _ = _tier3(nb, nb.models.logistic_regression, (X, y), {}, opot.Logistic(X, y), part=part,
-                   step_size=0.05)
+                   step_size=0.01)
     assert ex["num_steps"].max() > 3
 
 
@@ -244,7 +244,8 @@ def test_warmup_adaptation_trace(nb):
                              collect_warmup=True)
     m = 25  # trajectories are chaotic: compare the part before round-off has grown
     assert np.array_equal(mc.get_extra_fields()["num_steps"][:m], res["num_steps"][:m])
-    assert_allclose(ss[:m], res["step_size"][:m], rtol=2e-3)
+    assert_allclose(ss[:12], res["step_size"][:12], rtol=1e-4)
+    assert_allclose(ss[:m], res["step_size"][:m], rtol=1e-2)
     last = mc.last_state
     assert int(last.adapt_state.window_idx) == st.adapt_state.window_idx == 3
     assert int(last.i) == 60
