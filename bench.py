@@ -269,6 +269,8 @@ def run_own(args):
 
     for _ in range(args.warmup):
         device_step()
+    prof = (C.c_uint64 * 8)()
+    _lib.check(lib.b200mc_get_profile(kern._handle, prof, 1))  # reset the cycle counters
     launches0 = lib.b200mc_kernel_launches()
     clocks = ClockSampler(local) if rank == 0 else None
     barrier()
@@ -279,6 +281,10 @@ def run_own(args):
         step_grads.append(gsum)
     barrier()
     launches = lib.b200mc_kernel_launches() - launches0
+    _lib.check(lib.b200mc_get_profile(kern._handle, prof, 0))
+    passes = max(1, int(prof[4]))
+    breakdown = {k: float(prof[i]) / passes for i, k in
+                 enumerate(("stream", "arrival_wait", "grid_reduce", "sampler_step"))}
     total_ms = max_over_ranks(sum(step_ms))
     total_grads = sum_over_ranks(float(sum(step_grads)))
     value = total_grads / (total_ms * 1e-3)
@@ -344,6 +350,7 @@ def run_own(args):
                        "l2": "inputs 128.4 MB per pass > 126 MB L2, streamed once per grad eval"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clk, "adapt_seconds": adapt_s,
+            "cta0_cycles_per_grad_eval": breakdown,
             "mean_tree_size": float(np.mean(step_grads)) / T_,
         }
         print(json.dumps(line))

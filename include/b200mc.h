@@ -131,6 +131,12 @@ int b200mc_set_scalars(b200mc_handle* h, const b200mc_chain_scalars* in_host);
 int b200mc_get_vector(b200mc_handle* h, int which, float* out_dev, void* stream);
 int b200mc_set_vector(b200mc_handle* h, int which, const float* in_dev, void* stream);
 
+/* Cycle counters of the streaming (logistic) kernel, accumulated over launches by CTA 0:
+ * out[0] stream+partial, [1] grid-arrival wait, [2] grid reduction, [3] sampler step,
+ * [4] passes (= gradient evaluations); SM clock cycles.  No reference counterpart
+ * (diagnostic). */
+int b200mc_get_profile(b200mc_handle* h, uint64_t* out_host /*[8]*/, int reset);
+
 /* potential_energy + value_and_grad (infer/util.py:302-327, hmc_util.py:242-252) at
  * n points z[n][D]: tier-2 parity hook. */
 int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, int n, float* U_dev,

@@ -77,6 +77,7 @@ SYMBOLS = {
     "b200mc_set_scalars": (_i, [_vp, _vp]),
     "b200mc_get_vector": (_i, [_vp, _i, _vp, _vp]),
     "b200mc_set_vector": (_i, [_vp, _i, _vp, _vp]),
+    "b200mc_get_profile": (_i, [_vp, _vp, _i]),
     "b200mc_potential_and_grad": (_i, [_vp, _vp, _i, _vp, _vp, _vp]),
     "b200mc_threefry2x32": (_i, [_vp, _vp, _vp, _i, _vp]),
     "b200mc_random_split": (_i, [_vp, _i, _i, _vp, _i, _vp]),

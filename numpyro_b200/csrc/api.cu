@@ -4,6 +4,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -46,9 +47,10 @@ struct b200mc_handle {
   int mode = 0, c_pad = 0;
   // glm
   int glm_ctas = 0, glm_rows_per_cta = 0, glm_stages = 0, glm_smem = 0;
-  float* partials = nullptr;
-  float* theta_pub = nullptr;
-  unsigned* counters = nullptr;  // [0] arrive, [1] pub_gen, [2] ctrl, [3] error
+  float* partials = nullptr;     // [2][ctas][D+1]
+  unsigned* counters = nullptr;  // [0] arrive, [3] error
+  unsigned long long* prof = nullptr;  // [kGlmProfSlots]
+  int glm_reverse = 1;
   bool initialized = false;
 };
 
@@ -126,7 +128,7 @@ extern "C" void b200mc_destroy(b200mc_handle* h) {
   cudaFree(h->cs);
   cudaFree(h->cv.z); cudaFree(h->cv.z_grad); cudaFree(h->cv.inverse_mass_matrix);
   cudaFree(h->cv.mass_matrix_sqrt); cudaFree(h->cv.welford_mean); cudaFree(h->cv.welford_m2);
-  cudaFree(h->work); cudaFree(h->partials); cudaFree(h->theta_pub); cudaFree(h->counters);
+  cudaFree(h->work); cudaFree(h->partials); cudaFree(h->counters); cudaFree(h->prof);
   delete h;
 }
 
@@ -224,22 +226,25 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
     ctas = (c.N + rpc - 1) / rpc;
     h->glm_ctas = ctas;
     h->glm_rows_per_cta = rpc;
-    // as many ring stages as shared memory allows (<= 64)
-    int ns = 64;
-    while (ns > 2 && glm_smem_layout(D, ns, P.max_depth).total > h->max_smem) --ns;
+    // ring stages: a multiple of the consumer-warp count (every stage is owned by one
+    // warp), as many as shared memory allows
+    int ns = kGlmConsumerWarps * kGlmMaxStagesPerWarp;
+    while (ns > kGlmConsumerWarps && glm_smem_layout(D, ns, P.max_depth).total > h->max_smem)
+      ns -= kGlmConsumerWarps;
     if (glm_smem_layout(D, ns, P.max_depth).total > h->max_smem) {
       b200mc_destroy(h);
       return fail("logistic: shared memory layout does not fit");
     }
     h->glm_stages = ns;
     h->glm_smem = glm_smem_layout(D, ns, P.max_depth).total;
-    ACK(cudaFuncSetAttribute(glm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->glm_smem));
+    ACK(cudaFuncSetAttribute(glm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     int occ = 0;
     ACK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, glm_kernel, kGlmThreads, h->glm_smem));
     if (occ < 1) { b200mc_destroy(h); return fail("logistic kernel does not fit on an SM"); }
-    ACK(alloc((void**)&h->partials, sizeof(float) * (size_t)ctas * (D + 1)));
-    ACK(alloc((void**)&h->theta_pub, sizeof(float) * D));
+    ACK(alloc((void**)&h->partials, sizeof(float) * 2 * (size_t)ctas * (D + 1)));
     ACK(alloc((void**)&h->counters, sizeof(unsigned) * 8));
+    ACK(alloc((void**)&h->prof, sizeof(unsigned long long) * kGlmProfSlots));
+    if (const char* e = getenv("B200MC_GLM_REVERSE")) h->glm_reverse = atoi(e);
   } else {
     h->mode = (D <= 32) ? 0 : (D <= 512 ? 1 : 2);
     h->c_pad = (C + 31) / 32 * 32;
@@ -320,15 +325,14 @@ static int launch_glm(b200mc_handle* h, const CollectSpec& col, const uint32_t* 
   L.N = h->cfg.N; L.D = h->D;
   L.rows_per_cta = h->glm_rows_per_cta;
   L.n_stages = h->glm_stages;
+  L.reverse_odd = h->glm_reverse;
   L.partials = h->partials;
   L.arrive = h->counters + 0;
-  L.pub_gen = h->counters + 1;
-  L.ctrl = (int*)(h->counters + 2);
   L.error = (int*)(h->counters + 3);
-  L.theta_pub = h->theta_pub;
+  L.prof = h->prof;
   L.init_keys = keys; L.user_init = user_init; L.chain = chain; L.C = h->C;
   L.eval_z = eval_z; L.eval_U = eval_U; L.eval_grad = eval_grad;
-  CK(cudaMemsetAsync(h->counters, 0, sizeof(unsigned) * 3, st));  // arrive, pub_gen, ctrl
+  CK(cudaMemsetAsync(h->counters, 0, sizeof(unsigned) * 3, st));  // arrive
   void* args[] = {&L};
   CK(cudaLaunchCooperativeKernel((const void*)glm_kernel, dim3(h->glm_ctas), dim3(kGlmThreads), args,
                                  (size_t)h->glm_smem, st));
@@ -410,6 +414,17 @@ extern "C" int b200mc_set_scalars(b200mc_handle* h, const b200mc_chain_scalars* 
   if (!h || !in_host) return fail("null argument");
   CK(cudaMemcpy(h->cs, in_host, sizeof(ChainScalars) * h->C, cudaMemcpyHostToDevice));
   h->initialized = true;
+  return 0;
+}
+
+extern "C" int b200mc_get_profile(b200mc_handle* h, uint64_t* out_host, int reset) {
+  if (!h || !out_host) return fail("null argument");
+  for (int i = 0; i < 8; ++i) out_host[i] = 0;
+  if (!h->prof) return 0;
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpy(out_host, h->prof, sizeof(unsigned long long) * kGlmProfSlots,
+                cudaMemcpyDeviceToHost));
+  if (reset) CK(cudaMemset(h->prof, 0, sizeof(unsigned long long) * kGlmProfSlots));
   return 0;
 }
 

@@ -1,18 +1,23 @@
 // Persistent streaming kernel for tall-data Bayesian logistic regression
-// (examples/covtype.py:66-71): one launch runs whole NUTS/HMC trajectories.
+// (examples/covtype.py:66-71): one cooperative launch runs whole NUTS/HMC trajectories.
 //
-// Every CTA owns a contiguous slice of the rows of X.  Per leapfrog:
+// Every CTA (one per SM) owns a contiguous slice of the rows of X.  Per leapfrog ("pass"):
 //   * a producer warp keeps a ring of shared-memory stages full with TMA bulk copies
-//     (cp.async.bulk + mbarrier complete_tx) of 32-row tiles of X (+ their labels);
-//     it runs AHEAD across leapfrog boundaries (tile addresses do not depend on
-//     theta), so HBM keeps streaming while the sampler decides the next point;
-//   * consumer warps compute, in ONE pass over the tile (the reference's XLA program
-//     reads X twice: forward dot + transposed dot), logits = X theta, the Bernoulli
-//     log-likelihood and the partial gradient X^T (sigmoid(l) - y);
-//   * CTA partials go to global memory; a grid-wide arrive counter hands them to the
-//     leader CTA, which reduces them in a fixed order, runs the sampler step machine
-//     (sampler.cuh) on one warp with its state in shared memory, and publishes the
-//     next theta behind a generation flag.
+//     (cp.async.bulk + mbarrier complete_tx) of 32-row tiles of X (+ their labels).  It
+//     runs AHEAD across pass boundaries (tile addresses do not depend on theta), so HBM
+//     keeps streaming while the sampler decides the next point.  Odd passes sweep the
+//     slice backwards, so the tail of one pass is still in the 126 MB L2 when the next
+//     pass starts.
+//   * consumer warps own one row per lane: the row goes shared memory -> registers once,
+//     and logit = x . theta, the Bernoulli log-likelihood and the gradient contribution
+//     (sigmoid(l) - y) x are all computed from those registers (the reference's XLA
+//     program reads X twice: forward dot + transposed dot).  Per-lane gradient
+//     accumulators are folded across lanes once per pass with a shuffle transpose-reduce.
+//   * CTA partials (D + 1 floats) go to global memory behind a grid-wide arrival counter.
+//     EVERY CTA then reduces all partials in the same fixed order and advances its own
+//     replica of the sampler step machine (sampler.cuh) in warp 0 -- bit-identical in all
+//     CTAs -- so the next theta is available locally without a publish/poll round trip.
+//     Only CTA 0 writes chain state and collected draws.
 //
 // Replaces: potential_energy/log_density for this family (infer/util.py:302-327),
 // value_and_grad (hmc_util.py:242-252) and the whole sample_kernel loop (hmc.py:459-530).
@@ -23,10 +28,14 @@
 
 namespace b200mc {
 
-constexpr int kGlmConsumerWarps = 14;
-constexpr int kGlmThreads = (kGlmConsumerWarps + 1) * 32;
+constexpr int kGlmConsumerWarps = 7;  // + 1 producer warp = 2 warps per SM sub-partition (255 regs)
+constexpr int kGlmConsumerThreads = kGlmConsumerWarps * 32;
+constexpr int kGlmThreads = kGlmConsumerThreads + 32;  // + producer warp
 constexpr int kGlmTileRows = 32;
 constexpr int kGlmMaxD = 128;
+constexpr int kGlmGroups = 4;        // grid reduction: CTAs are summed in kGlmGroups strided groups
+constexpr int kGlmMaxStagesPerWarp = 8;
+constexpr int kGlmProfSlots = 8;
 
 struct GlmLaunch {
   SamplerParams P;
@@ -37,14 +46,13 @@ struct GlmLaunch {
   const uint8_t* y;    // [N] 0/1, 16-byte aligned
   int N, D;
   int rows_per_cta;    // multiple of 32
-  int n_stages;
+  int n_stages;        // multiple of kGlmConsumerWarps
+  int reverse_odd;     // sweep odd passes backwards (L2 reuse)
   // grid-level exchange (global memory)
-  float* partials;       // [nCTA][DP1]
-  unsigned* arrive;      // monotonic arrival counter
-  unsigned* pub_gen;     // generation of theta_pub / ctrl
-  float* theta_pub;      // [D]
-  int* ctrl;             // 1 continue, 0 stop
+  float* partials;       // [2][nCTA][DP1], double-buffered by pass parity
+  unsigned* arrive;      // monotonic arrival counter, zeroed by the host before the launch
   int* error;            // set to 1 on a spin time-out
+  unsigned long long* prof;  // [kGlmProfSlots] cycle counters of CTA 0 (or null)
   const uint32_t* init_keys;  // [C][2] or null
   int user_init;
   int chain;             // which chain of cs/cv this launch advances
@@ -84,7 +92,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   // bounded: a copy that never lands is a bug; fail loudly (launch error) instead of hanging
   for (long it = 0; !mbar_try_wait(bar, parity); ++it)
-    if (it > (1L << 28)) __trap();
+    if (it > (1L << 24)) __trap();
 }
 // TMA bulk copy global -> shared, completion counted in bytes on an mbarrier
 __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes,
@@ -100,65 +108,99 @@ __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ void st_release_u32(unsigned* p, unsigned v) {
-  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
 __device__ __forceinline__ void red_release_add(unsigned* p, unsigned v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ void consumer_bar() {  // named barrier 1: consumer warps only
-  asm volatile("bar.sync 1, %0;" ::"n"(kGlmConsumerWarps * 32) : "memory");
+  asm volatile("bar.sync 1, %0;" ::"n"(kGlmConsumerThreads) : "memory");
 }
 
-// Spin until *p >= target (monotonic counters); false on time-out (~ seconds).
+// Spin until *p >= target (monotonic counter); false on time-out (seconds).
 __device__ __forceinline__ bool spin_until_ge(const unsigned* p, unsigned target) {
-  for (long it = 0; it < (1L << 27); ++it) {
+  for (long it = 0; it < (1L << 24); ++it) {
     if ((int)(ld_acquire_u32(p) - target) >= 0) return true;
-    if (it > 64) __nanosleep(20);
+    if (it > 4096) __nanosleep(100);
   }
   return false;
 }
 
-// One 32-row tile: logits, log-likelihood terms, gradient contribution.
-// xs: [rows][D] floats (shared), ys: labels, th: theta (shared, 16-byte aligned).
-// Lane r owns row r for the logits; lane c owns columns c, c+32, ... for the gradient.
-template <int K>
+// 1/d for d in [1, 2]: MUFU.RCP + one Newton step (<= 1 ulp), no slow-path call -- a call in
+// the tile loop would force the register-resident row and accumulators through the stack.
+__device__ __forceinline__ float rcp_1to2(float d) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
+  return fmaf(r, fmaf(-d, r, 1.0f), r);
+}
+
+// ---------------------------------------------------------------- per-tile arithmetic
+// One 32-row tile, lane r <-> row r.  NCH = ceil(D / 32) column chunks.  For D <= 64 the
+// row is read from shared memory once and kept in registers for both the logit and the
+// gradient accumulation; for wider rows it is re-read chunk by chunk.
+// xs: [32][D] floats (shared), ys: labels, th: theta zero-padded to 32*NCH (shared).
+// acc[k] accumulates, per lane, (sigmoid(l) - y) * x[k] over this lane's rows.
+template <int NCH>
 __device__ __forceinline__ void glm_tile(const float* __restrict__ xs,
                                          const uint8_t* __restrict__ ys, int rows,
-                                         const float* __restrict__ th, int D, float (&acc)[K],
-                                         float& ll) {
+                                         const float* __restrict__ th, int D,
+                                         float (&acc)[NCH * 32], float& ll) {
+  constexpr int DM = NCH * 32;
+  constexpr int LB = DM - 32;  // columns below LB exist for every D of this NCH
+  constexpr bool KEEP = (NCH <= 2);
   const int lane = threadIdx.x & 31;
   const float* xr = xs + lane * D;
+  const int dl = D - 1;
+  // Branch-free: a column index >= D is clamped to D-1 (a valid, finite element) and meets
+  // a zero of the padded theta; its accumulator is never read.
+  float x[KEEP ? DM : 4];
   float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
-  int d = 0;
-  for (; d + 3 < D; d += 4) {
-    const float4 t4 = *reinterpret_cast<const float4*>(th + d);
-    l0 = fmaf(xr[d], t4.x, l0);
-    l1 = fmaf(xr[d + 1], t4.y, l1);
-    l2 = fmaf(xr[d + 2], t4.z, l2);
-    l3 = fmaf(xr[d + 3], t4.w, l3);
+#pragma unroll
+  for (int k = 0; k < DM; k += 4) {
+    const float4 t4 = *reinterpret_cast<const float4*>(th + k);
+    const float x0 = xr[(k + 0 < LB) ? k + 0 : min(k + 0, dl)];
+    const float x1 = xr[(k + 1 < LB) ? k + 1 : min(k + 1, dl)];
+    const float x2 = xr[(k + 2 < LB) ? k + 2 : min(k + 2, dl)];
+    const float x3 = xr[(k + 3 < LB) ? k + 3 : min(k + 3, dl)];
+    if (KEEP) {
+      x[k] = x0; x[k + 1] = x1; x[k + 2] = x2; x[k + 3] = x3;
+    }
+    l0 = fmaf(x0, t4.x, l0);
+    l1 = fmaf(x1, t4.y, l1);
+    l2 = fmaf(x2, t4.z, l2);
+    l3 = fmaf(x3, t4.w, l3);
   }
-  for (; d < D; ++d) l0 = fmaf(xr[d], th[d], l0);
   const float l = (l0 + l1) + (l2 + l3);
   float gres = 0.f;
   if (lane < rows) {
     const float yv = (float)ys[lane];
     const float e = expf(-fabsf(l));
-    const float inv = 1.0f / (1.0f + e);
+    const float inv = rcp_1to2(1.0f + e);
     const float sig = (l >= 0.f) ? inv : e * inv;
     // binary_cross_entropy_with_logits (distributions/util.py:295-298)
     ll += (fmaxf(l, 0.f) + log1pf(e)) - l * yv;
     gres = sig - yv;
   }
-  for (int r = 0; r < rows; ++r) {
-    const float gr = __shfl_sync(0xffffffffu, gres, r);
-    const float* row = xs + r * D;
 #pragma unroll
-    for (int k = 0; k < K; ++k) {
-      const int c = lane + 32 * k;
-      if (c < D) acc[k] = fmaf(gr, row[c], acc[k]);
+  for (int k = 0; k < DM; ++k) {
+    if (KEEP) acc[k] = fmaf(gres, x[k], acc[k]);
+    else acc[k] = fmaf(gres, xr[(k < LB) ? k : min(k, dl)], acc[k]);
+  }
+}
+
+// Recursive-halving transpose-reduce: on return a[0] of lane L holds the sum over all
+// lanes of the original a[L] (31 shuffles for 32 columns; fixed order => deterministic).
+__device__ __forceinline__ float warp_transpose_reduce32(float* a) {
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+    const bool upper = (lane & s) != 0;
+#pragma unroll
+    for (int i = 0; i < s; ++i) {
+      const float send = upper ? a[i] : a[i + s];
+      const float keep = upper ? a[i + s] : a[i];
+      a[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
     }
   }
+  return a[0];
 }
 
 // ---------------------------------------------------------------- shared-memory layout
@@ -166,7 +208,6 @@ struct GlmSmem {
   int stage_bytes, off_tail, off_full, off_empty, off_theta, off_red, off_red2, off_work,
       off_flags, total;
 };
-constexpr int kGlmParts = kGlmConsumerWarps * 32 / 64;  // leader reduction: rows split in parts
 
 __host__ __device__ inline GlmSmem glm_smem_layout(int D, int n_stages, int max_depth) {
   GlmSmem s;
@@ -177,9 +218,9 @@ __host__ __device__ inline GlmSmem glm_smem_layout(int D, int n_stages, int max_
   s.off_full = o;  o += n_stages * 8;
   s.off_empty = o; o += n_stages * 8;
   o = (o + 15) & ~15;
-  s.off_theta = o; o += ((D + 3) & ~3) * 4;
+  s.off_theta = o; o += kGlmMaxD * 4;  // zero-padded to a multiple of 32 columns
   s.off_red = o;   o += kGlmConsumerWarps * dp1 * 4;
-  s.off_red2 = o;  o += kGlmParts * dp1 * 4;
+  s.off_red2 = o;  o += kGlmGroups * dp1 * 4;
   o = (o + 15) & ~15;
   s.off_work = o;  o += num_slots(max_depth) * D * 4;
   s.off_flags = o; o += 16;
@@ -187,9 +228,16 @@ __host__ __device__ inline GlmSmem glm_smem_layout(int D, int n_stages, int max_
   return s;
 }
 
-// One leapfrog's worth of tiles for one consumer warp; leaves its partial gradient and
-// log-likelihood in red[warp][0..D].
-template <int K>
+// Row offset (within the CTA's slice, in tiles) of the j-th tile of pass `pass`.
+__device__ __forceinline__ int glm_tile_of(int j, int pass, int ntiles, int reverse_odd) {
+  return (reverse_odd && (pass & 1)) ? (ntiles - 1 - j) : j;
+}
+
+// One pass worth of tiles for one consumer warp; leaves its partial gradient and
+// log-likelihood in red[warp][0..D].  Tile q (global sequence number over all passes) is
+// consumed by warp q % W from stage q % NS; NS is a multiple of W, so every stage is only
+// ever consumed by one warp, strictly in phase order.
+template <int NCH>
 __device__ __forceinline__ void glm_consume_pass(const GlmLaunch& L, unsigned char* smem,
                                                  const GlmSmem& lay, int warp, long& q_next,
                                                  long q_end, int row0, int ntiles, int tail_rows) {
@@ -198,39 +246,40 @@ __device__ __forceinline__ void glm_consume_pass(const GlmLaunch& L, unsigned ch
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + lay.off_full);
   uint64_t* empty = reinterpret_cast<uint64_t*>(smem + lay.off_empty);
   const float* th = reinterpret_cast<const float*>(smem + lay.off_theta);
-  float acc[K];
+  float acc[NCH * 32];
 #pragma unroll
-  for (int k = 0; k < K; ++k) acc[k] = 0.f;
+  for (int k = 0; k < NCH * 32; ++k) acc[k] = 0.f;
   float ll = 0.f;
   for (; q_next < q_end; q_next += kGlmConsumerWarps) {
     const int stage = (int)(q_next % NS);
     const uint32_t parity = (uint32_t)((q_next / NS) & 1);
     mbar_wait(&full[stage], parity);
     const unsigned char* sp = smem + (long)stage * lay.stage_bytes;
-    glm_tile<K>(reinterpret_cast<const float*>(sp), sp + kGlmTileRows * D * 4, kGlmTileRows, th, D,
-                acc, ll);
+    glm_tile<NCH>(reinterpret_cast<const float*>(sp), sp + kGlmTileRows * D * 4, kGlmTileRows, th,
+                  D, acc, ll);
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[stage]);
   }
   if (tail_rows > 0 && warp == kGlmConsumerWarps - 1) {
-    // the last (< 32)-row tile of the data set: plain loads into the tail buffer
+    // the last (< 32)-row tile of the data set: plain loads into the (zero-filled) tail buffer
     unsigned char* tp = smem + lay.off_tail;
     float* tx = reinterpret_cast<float*>(tp);
     unsigned char* ty = tp + kGlmTileRows * D * 4;
     const long r0 = (long)row0 + (long)ntiles * kGlmTileRows;
-    for (int i = lane; i < tail_rows * D; i += 32) tx[i] = L.X[r0 * D + i];
-    if (lane < tail_rows) ty[lane] = L.y[r0 + lane];
+    for (int i = lane; i < kGlmTileRows * D; i += 32)
+      tx[i] = (i < tail_rows * D) ? L.X[r0 * D + i] : 0.f;
+    ty[lane] = (lane < tail_rows) ? L.y[r0 + lane] : (uint8_t)0;
     __syncwarp();
-    glm_tile<K>(tx, ty, tail_rows, th, D, acc, ll);
+    glm_tile<NCH>(tx, ty, tail_rows, th, D, acc, ll);
     __syncwarp();
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) ll += __shfl_xor_sync(0xffffffffu, ll, o);
   float* red = reinterpret_cast<float*>(smem + lay.off_red) + warp * (D + 1);
 #pragma unroll
-  for (int k = 0; k < K; ++k) {
-    const int c = lane + 32 * k;
-    if (c < D) red[c] = acc[k];
+  for (int c = 0; c < NCH; ++c) {
+    const float v = warp_transpose_reduce32(acc + 32 * c);
+    if (32 * c + lane < D) red[32 * c + lane] = v;
   }
   if (lane == 0) red[D] = ll;
 }
@@ -244,14 +293,15 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
   float* th = reinterpret_cast<float*>(smem + lay.off_theta);
   float* red = reinterpret_cast<float*>(smem + lay.off_red);
   float* red2 = reinterpret_cast<float*>(smem + lay.off_red2);
-  volatile int* flags = reinterpret_cast<volatile int*>(smem + lay.off_flags);  // [0] done, [1] passes
+  // [0] consumers done, [1] passes consumed, [2] go (1) / stop (0), [3] spin ok
+  volatile int* flags = reinterpret_cast<volatile int*>(smem + lay.off_flags);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int cta = blockIdx.x, nCTA = gridDim.x;
   const long row0l = (long)cta * L.rows_per_cta;
   const int row0 = (int)(row0l < L.N ? row0l : L.N);
   const int row1 = (int)((row0l + L.rows_per_cta) < L.N ? (row0l + L.rows_per_cta) : L.N);
-  const int ntiles = (row1 - row0) / kGlmTileRows;           // full tiles: TMA
+  const int ntiles = (row1 - row0) / kGlmTileRows;              // full tiles: TMA
   const int tail_rows = (row1 - row0) - ntiles * kGlmTileRows;  // < 32, last CTA only
 
   if (threadIdx.x == 0) {
@@ -259,32 +309,32 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
       mbar_init(&full[i], 1);
       mbar_init(&empty[i], 1);
     }
-    flags[0] = 0;
-    flags[1] = 0;
+    flags[0] = 0; flags[1] = 0; flags[2] = 0; flags[3] = 1;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  const unsigned gen0 = 0u, arr0 = 0u;  // the host zeroes pub_gen / arrive before every launch
 
   if (warp == kGlmConsumerWarps) {
-    // ================= producer warp: TMA ring, runs ahead across leapfrogs =================
+    // ================= producer warp: TMA ring, runs ahead across passes =================
     if (lane == 0 && ntiles > 0) {
       const uint32_t xbytes = kGlmTileRows * D * 4, ybytes = kGlmTileRows;
       long q = 0;
-      bool stop = false;
-      while (!stop) {
-        for (int j = 0; j < ntiles && !stop; ++j, ++q) {
-          const int stage = (int)(q % NS);
-          const uint32_t parity = (uint32_t)(((q / NS) & 1) ^ 1);
-          while (!mbar_try_wait(&empty[stage], parity)) {
-            if (flags[0]) { stop = true; break; }
-          }
-          if (stop || flags[0]) { stop = true; break; }
-          unsigned char* sp = smem + (long)stage * lay.stage_bytes;
-          mbar_arrive_expect_tx(&full[stage], xbytes + ybytes);
-          tma_load_1d(sp, L.X + ((long)row0 + (long)j * kGlmTileRows) * D, xbytes, &full[stage]);
-          tma_load_1d(sp + xbytes, L.y + row0 + (long)j * kGlmTileRows, ybytes, &full[stage]);
+      int pass = 0, j = 0;
+      while (true) {
+        const int stage = (int)(q % NS);
+        const uint32_t parity = (uint32_t)(((q / NS) & 1) ^ 1);
+        bool stop = false;
+        while (!mbar_try_wait(&empty[stage], parity)) {
+          if (flags[0]) { stop = true; break; }
         }
+        if (stop || flags[0]) break;
+        const long r = (long)row0 + (long)glm_tile_of(j, pass, ntiles, L.reverse_odd) * kGlmTileRows;
+        unsigned char* sp = smem + (long)stage * lay.stage_bytes;
+        mbar_arrive_expect_tx(&full[stage], xbytes + ybytes);
+        tma_load_1d(sp, L.X + r * D, xbytes, &full[stage]);
+        tma_load_1d(sp + xbytes, L.y + r, ybytes, &full[stage]);
+        ++q;
+        if (++j == ntiles) { j = 0; ++pass; }
       }
       // drain: wait for every copy that was issued but never consumed
       const long consumed = (long)flags[1] * ntiles;
@@ -295,14 +345,14 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
   }
 
   // ================= consumer warps =================
-  const int tid = threadIdx.x;  // 0 .. kGlmConsumerWarps*32-1
-  const bool leader = (cta == 0);
-  Sampler<WarpGroup> S;
-  StepResult sres = FINISHED;
+  const int tid = threadIdx.x;  // 0 .. kGlmConsumerThreads-1
   const bool eval_mode = (L.eval_z != nullptr);
-  if (leader && warp == 0) {
+  Sampler<WarpGroup> S;  // a replica in every CTA; only CTA 0 writes
+  StepResult sres = FINISHED;
+  if (warp == 0) {
     float* work = reinterpret_cast<float*>(smem + lay.off_work);
     S.setup(&L.P, WarpGroup{}, work, D, 1, L.chain, L.C, &L.col);
+    S.writer = (cta == 0);
     if (eval_mode) {
       for (int d = lane; d < D; d += 32) S.v(LZ)[d] = L.eval_z[d];
       sres = NEED_GRAD;
@@ -314,33 +364,22 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
       else
         sres = S.begin_sampling();
     }
-    for (int d = lane; d < D; d += 32) __stcg(&L.theta_pub[d], S.v(LZ)[d]);
-    if (lane == 0) *L.ctrl = (sres == NEED_GRAD) ? 1 : 0;
     __syncwarp();
-    __threadfence();
-    if (lane == 0) st_release_u32(L.pub_gen, gen0 + 1u);
+    for (int d = lane; d < kGlmMaxD; d += 32) th[d] = (d < D) ? S.v(LZ)[d] : 0.f;
+    if (lane == 0) flags[2] = (sres == NEED_GRAD) ? 1 : 0;
+    if (sres == NEED_GRAD) S.prefetch_rng();
   }
+  consumer_bar();
 
-  const int K = (D + 31) / 32;
+  const int NCH = (D + 31) / 32;
   long q_next = warp;
   int pass = 0;
-  bool ok = true;
-  while (true) {
-    // ---- wait for theta of this pass
-    if (tid == 0) {
-      ok = spin_until_ge(L.pub_gen, gen0 + 1u + (unsigned)pass);
-      if (!ok) atomicExch(L.error, 1);
-      flags[2] = ok ? __ldcg(L.ctrl) : 0;
-    }
-    consumer_bar();
-    const int go = flags[2];
-    if (!go) break;
-    if (tid < D) th[tid] = __ldcg(&L.theta_pub[tid]);
-    consumer_bar();
-
+  long long t_mark = clock64();
+  unsigned long long c_stream = 0, c_wait = 0, c_reduce = 0, c_sampler = 0;
+  while (flags[2]) {
     // ---- stream this CTA's rows
     const long q_end = (long)(pass + 1) * ntiles;
-    switch (K) {
+    switch (NCH) {
       case 1: glm_consume_pass<1>(L, smem, lay, warp, q_next, q_end, row0, ntiles, tail_rows); break;
       case 2: glm_consume_pass<2>(L, smem, lay, warp, q_next, q_end, row0, ntiles, tail_rows); break;
       case 3: glm_consume_pass<3>(L, smem, lay, warp, q_next, q_end, row0, ntiles, tail_rows); break;
@@ -348,65 +387,88 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
     }
     consumer_bar();
     // ---- CTA partial: fixed-order sum over warps
+    float* my_partials = L.partials + ((long)(pass & 1) * nCTA + cta) * DP1;
     if (tid < DP1) {
       float a = 0.f;
 #pragma unroll
       for (int w2 = 0; w2 < kGlmConsumerWarps; ++w2) a += red[w2 * DP1 + tid];
-      __stcg(&L.partials[(long)cta * DP1 + tid], a);
+      __stcg(&my_partials[tid], a);
     }
     consumer_bar();
     if (tid == 0) {
       flags[1] = pass + 1;
       __threadfence();
       red_release_add(L.arrive, 1u);
+      const long long t1 = clock64();
+      c_stream += (unsigned long long)(t1 - t_mark);
+      const bool ok = spin_until_ge(L.arrive, (unsigned)(pass + 1) * (unsigned)nCTA);
+      if (!ok) {
+        atomicExch(L.error, 1);
+        flags[3] = 0;
+      }
+      t_mark = clock64();
+      c_wait += (unsigned long long)(t_mark - t1);
     }
-
-    // ---- leader: grid reduction in a fixed order + one sampler step
-    if (leader) {
-      if (tid == 0) {
-        ok = spin_until_ge(L.arrive, arr0 + (unsigned)(pass + 1) * (unsigned)nCTA);
-        if (!ok) atomicExch(L.error, 1);
+    consumer_bar();
+    // ---- every CTA: grid reduction in a fixed order
+    const float* all_partials = L.partials + (long)(pass & 1) * nCTA * DP1;
+    for (int item = tid; item < kGlmGroups * DP1; item += kGlmConsumerThreads) {
+      const int c = item % DP1, grp = item / DP1;
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+      int b = grp;
+      for (; b + 3 * kGlmGroups < nCTA; b += 4 * kGlmGroups) {
+        const float v0 = __ldcg(&all_partials[(long)b * DP1 + c]);
+        const float v1 = __ldcg(&all_partials[(long)(b + kGlmGroups) * DP1 + c]);
+        const float v2 = __ldcg(&all_partials[(long)(b + 2 * kGlmGroups) * DP1 + c]);
+        const float v3 = __ldcg(&all_partials[(long)(b + 3 * kGlmGroups) * DP1 + c]);
+        a0 += v0; a1 += v1; a2 += v2; a3 += v3;
       }
-      consumer_bar();
-      for (int item = tid; item < kGlmParts * DP1; item += kGlmConsumerWarps * 32) {
-        const int c = item % DP1, part = item / DP1;
+      for (; b < nCTA; b += kGlmGroups) a0 += __ldcg(&all_partials[(long)b * DP1 + c]);
+      red2[grp * DP1 + c] = (a0 + a1) + (a2 + a3);
+    }
+    consumer_bar();
+    // ---- warp 0: finish the potential, advance the sampler replica, next theta
+    if (warp == 0) {
+      long long t2 = 0;
+      if (lane == 0) {
+        t2 = clock64();
+        c_reduce += (unsigned long long)(t2 - t_mark);
+      }
+      float* lz = S.v(LZ);
+      float* lg = S.v(LG);
+      float prior = 0.f;
+      for (int d = lane; d < D; d += 32) {
         float a = 0.f;
-        for (int b = part; b < nCTA; b += kGlmParts) a += __ldcg(&L.partials[(long)b * DP1 + c]);
-        red2[part * DP1 + c] = a;
+#pragma unroll
+        for (int p2 = 0; p2 < kGlmGroups; ++p2) a += red2[p2 * DP1 + d];
+        const float t = lz[d];
+        lg[d] = t + a;                                // grad U = theta + X^T (sigmoid - y)
+        prior += 0.5f * t * t + 0.9189385332046727f;  // -log N(theta; 0, 1)
       }
-      consumer_bar();
-      if (warp == 0) {
-        float* lz = S.v(LZ);
-        float* lg = S.v(LG);
-        float prior = 0.f;
-        for (int d = lane; d < D; d += 32) {
-          float a = 0.f;
+      prior = WarpGroup{}.sum(prior);
+      float llik = 0.f;
 #pragma unroll
-          for (int p2 = 0; p2 < kGlmParts; ++p2) a += red2[p2 * DP1 + d];
-          const float t = lz[d];
-          lg[d] = t + a;                           // grad U = theta + X^T (sigmoid - y)
-          prior += 0.5f * t * t + 0.9189385332046727f;  // -log N(theta; 0, 1)
-        }
-        prior = WarpGroup{}.sum(prior);
-        float llik = 0.f;
-#pragma unroll
-        for (int p2 = 0; p2 < kGlmParts; ++p2) llik += red2[p2 * DP1 + D];
-        const float U = prior + llik;
-        if (eval_mode) {
+      for (int p2 = 0; p2 < kGlmGroups; ++p2) llik += red2[p2 * DP1 + D];
+      const float U = prior + llik;
+      if (eval_mode) {
+        if (cta == 0) {
           for (int d = lane; d < D; d += 32) L.eval_grad[d] = lg[d];
           if (lane == 0) *L.eval_U = U;
-          sres = FINISHED;
-        } else {
-          sres = ok ? S.advance(U) : FINISHED;
         }
-        for (int d = lane; d < D; d += 32) __stcg(&L.theta_pub[d], S.v(LZ)[d]);
-        if (lane == 0) *L.ctrl = (sres == NEED_GRAD) ? 1 : 0;
-        __syncwarp();
-        __threadfence();
-        if (lane == 0) st_release_u32(L.pub_gen, gen0 + 2u + (unsigned)pass);
-        if (sres == NEED_GRAD) S.prefetch_rng();
+        sres = FINISHED;
+      } else {
+        sres = flags[3] ? S.advance(U) : FINISHED;
+      }
+      __syncwarp();
+      for (int d = lane; d < D; d += 32) th[d] = S.v(LZ)[d];
+      if (lane == 0) {
+        flags[2] = (sres == NEED_GRAD) ? 1 : 0;
+        t_mark = clock64();
+        c_sampler += (unsigned long long)(t_mark - t2);
       }
     }
+    consumer_bar();
+    if (warp == 0 && sres == NEED_GRAD) S.prefetch_rng();
     ++pass;
   }
   // ---- shutdown: tell the producer, persist the chain
@@ -414,8 +476,15 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
     flags[1] = pass;
     __threadfence_block();
     flags[0] = 1;
+    if (cta == 0 && L.prof) {
+      atomicAdd(&L.prof[0], c_stream);
+      atomicAdd(&L.prof[1], c_wait);
+      atomicAdd(&L.prof[2], c_reduce);
+      atomicAdd(&L.prof[3], c_sampler);
+      atomicAdd(&L.prof[4], (unsigned long long)pass);
+    }
   }
-  if (leader && warp == 0 && !eval_mode) S.store(L.cs, L.cv);
+  if (warp == 0 && !eval_mode) S.store(L.cs, L.cv);
 }
 
 }  // namespace b200mc

@@ -69,6 +69,7 @@ struct Sampler {
   int D;
   bool part;
 
+  bool writer;         // false: a replica that advances the same chain but writes nothing
   ChainScalars s;      // persistent scalars (registers)
 
   // run control
@@ -113,6 +114,7 @@ struct Sampler {
     P = p; g = grp; w = work; slot_stride = sstride; es = estride; D = p->D;
     part = p->partitionable != 0;
     chain = chain_; C = C_; col = c;
+    writer = true;
     iters_left = c ? c->num_iters : 0;
     local_iter = 0;
     phase = PH_IDLE;
@@ -135,6 +137,7 @@ struct Sampler {
   }
 
   __device__ void store(ChainScalars* cs, const ChainVectors& cv) {
+    if (!writer) return;
     const long o = (long)chain * D;
     const float *zp = v(Z_PROP), *gp = v(G_PROP), *im = v(IMM), *ms = v(MSQRT), *wm = v(WMEAN),
                 *w2 = v(WM2);
@@ -300,7 +303,7 @@ struct Sampler {
   // ------------------------------------------------------------------ collection (util.py:334-351)
   __device__ void collect() {
     const int k = local_iter;  // index of the transition just finished, within this call
-    if (!col || col->n_keep <= 0 || k < col->collect_start) return;
+    if (!writer || !col || col->n_keep <= 0 || k < col->collect_start) return;
     const int rel = k - col->collect_start;
     if (rel % col->thinning != col->thinning - 1) return;  // the last write to a slot wins
     const int idx = rel / col->thinning;
