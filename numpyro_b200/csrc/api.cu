@@ -46,7 +46,8 @@ struct b200mc_handle {
   float* work = nullptr;
   int mode = 0, c_pad = 0;
   // glm
-  int glm_ctas = 0, glm_rows_per_cta = 0, glm_stages = 0, glm_smem = 0;
+  int glm_ctas = 0, glm_nt_total = 0, glm_stages = 0, glm_smem = 0;
+  unsigned char* glm_xt = nullptr;  // re-tiled X + labels
   float* partials = nullptr;     // [2][ctas][D+1]
   unsigned* counters = nullptr;  // [0] arrive, [3] error
   unsigned long long* prof = nullptr;  // [kGlmProfSlots]
@@ -128,7 +129,7 @@ extern "C" void b200mc_destroy(b200mc_handle* h) {
   cudaFree(h->cs);
   cudaFree(h->cv.z); cudaFree(h->cv.z_grad); cudaFree(h->cv.inverse_mass_matrix);
   cudaFree(h->cv.mass_matrix_sqrt); cudaFree(h->cv.welford_mean); cudaFree(h->cv.welford_m2);
-  cudaFree(h->work); cudaFree(h->partials); cudaFree(h->counters); cudaFree(h->prof);
+  cudaFree(h->work); cudaFree(h->partials); cudaFree(h->counters); cudaFree(h->prof); cudaFree(h->glm_xt);
   delete h;
 }
 
@@ -214,21 +215,22 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   if (c.family == B200MC_LOGISTIC) {
     if (D > kGlmMaxD) { b200mc_destroy(h); return fail("logistic: D=%d > %d not supported", D, kGlmMaxD); }
     if (!c.data1_dev) { b200mc_destroy(h); return fail("logistic: labels missing"); }
-    if (((uintptr_t)c.data0_dev & 15) || ((uintptr_t)c.data1_dev & 15)) {
-      b200mc_destroy(h);
-      return fail("logistic: X and labels must be 16-byte aligned device pointers");
-    }
-    int ctas = (c.N + 1023) / 1024;
-    if (ctas > h->num_sms) ctas = h->num_sms;
-    if (ctas < 1) ctas = 1;
-    int rpc = (c.N + ctas - 1) / ctas;
-    rpc = (rpc + kGlmTileRows - 1) / kGlmTileRows * kGlmTileRows;
-    ctas = (c.N + rpc - 1) / rpc;
+    // Re-tile X and the labels once (layout: glm_kernel.cuh); the caller's buffers are not
+    // referenced after b200mc_create returns.
+    const int nt_total = (c.N + kGlmTileRows - 1) / kGlmTileRows;
+    h->glm_nt_total = nt_total;
+    ACK(cudaMalloc((void**)&h->glm_xt, (size_t)nt_total * glm_tile_bytes(D)));
+    glm_retile_kernel<<<h->num_sms * 8, 256>>>((const float*)c.data0_dev,
+                                                (const uint8_t*)c.data1_dev, c.N, D, nt_total,
+                                                h->glm_xt);
+    g_launches++;
+    ACK(cudaGetLastError());
+    ACK(cudaDeviceSynchronize());
+    int ctas = nt_total < h->num_sms ? nt_total : h->num_sms;
     h->glm_ctas = ctas;
-    h->glm_rows_per_cta = rpc;
     // ring stages: a multiple of the consumer-warp count (every stage is owned by one
-    // warp), as many as shared memory allows
-    int ns = kGlmConsumerWarps * kGlmMaxStagesPerWarp;
+    // warp) and at most one per producer lane, as many as shared memory allows
+    int ns = kGlmMaxStages / kGlmConsumerWarps * kGlmConsumerWarps;
     while (ns > kGlmConsumerWarps && glm_smem_layout(D, ns, P.max_depth).total > h->max_smem)
       ns -= kGlmConsumerWarps;
     if (glm_smem_layout(D, ns, P.max_depth).total > h->max_smem) {
@@ -241,7 +243,7 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
     int occ = 0;
     ACK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, glm_kernel, kGlmThreads, h->glm_smem));
     if (occ < 1) { b200mc_destroy(h); return fail("logistic kernel does not fit on an SM"); }
-    ACK(alloc((void**)&h->partials, sizeof(float) * 2 * (size_t)ctas * (D + 1)));
+    ACK(alloc((void**)&h->partials, sizeof(float) * 2 * (size_t)ctas * glm_partial_stride(D)));
     ACK(alloc((void**)&h->counters, sizeof(unsigned) * 8));
     ACK(alloc((void**)&h->prof, sizeof(unsigned long long) * kGlmProfSlots));
     if (const char* e = getenv("B200MC_GLM_REVERSE")) h->glm_reverse = atoi(e);
@@ -320,10 +322,9 @@ static int launch_glm(b200mc_handle* h, const CollectSpec& col, const uint32_t* 
   GlmLaunch L;
   memset(&L, 0, sizeof(L));
   L.P = h->P; L.col = col; L.cs = h->cs; L.cv = h->cv;
-  L.X = (const float*)h->cfg.data0_dev;
-  L.y = (const uint8_t*)h->cfg.data1_dev;
+  L.Xt = h->glm_xt;
   L.N = h->cfg.N; L.D = h->D;
-  L.rows_per_cta = h->glm_rows_per_cta;
+  L.nt_total = h->glm_nt_total;
   L.n_stages = h->glm_stages;
   L.reverse_odd = h->glm_reverse;
   L.partials = h->partials;

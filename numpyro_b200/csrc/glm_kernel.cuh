@@ -1,23 +1,29 @@
 // Persistent streaming kernel for tall-data Bayesian logistic regression
 // (examples/covtype.py:66-71): one cooperative launch runs whole NUTS/HMC trajectories.
 //
-// Every CTA (one per SM) owns a contiguous slice of the rows of X.  Per leapfrog ("pass"):
-//   * a producer warp keeps a ring of shared-memory stages full with TMA bulk copies
-//     (cp.async.bulk + mbarrier complete_tx) of 32-row tiles of X (+ their labels).  It
-//     runs AHEAD across pass boundaries (tile addresses do not depend on theta), so HBM
-//     keeps streaming while the sampler decides the next point.  Odd passes sweep the
-//     slice backwards, so the tail of one pass is still in the 126 MB L2 when the next
-//     pass starts.
+// Data layout in HBM (built once by glm_retile_kernel when the handle is created): X and
+// the labels are re-tiled into 32-row tiles, each one contiguous block of
+//     [G column groups][32 rows][4 floats]  +  32 label bytes        (G = ceil(D / 4))
+// so that ONE TMA bulk copy brings a whole tile and lane r reads its row as conflict-free
+// 128-bit shared-memory loads.  Rows past N and columns past D are zero.
+//
+// Every CTA (one per SM) owns a contiguous range of tiles.  Per leapfrog ("pass"):
+//   * the producer warp keeps a ring of shared-memory stages full: lane s owns stage s,
+//     polls its "empty" mbarrier and issues cp.async.bulk (mbarrier complete_tx) for the
+//     next tile of that stage.  It runs AHEAD across pass boundaries (tile addresses do
+//     not depend on theta), so memory keeps streaming while the sampler decides the next
+//     point.  Odd passes sweep the range backwards, so most of X (128 MB) is still in the
+//     126 MB L2 when the next pass reads it.
 //   * consumer warps own one row per lane: the row goes shared memory -> registers once,
-//     and logit = x . theta, the Bernoulli log-likelihood and the gradient contribution
-//     (sigmoid(l) - y) x are all computed from those registers (the reference's XLA
-//     program reads X twice: forward dot + transposed dot).  Per-lane gradient
-//     accumulators are folded across lanes once per pass with a shuffle transpose-reduce.
-//   * CTA partials (D + 1 floats) go to global memory behind a grid-wide arrival counter.
-//     EVERY CTA then reduces all partials in the same fixed order and advances its own
-//     replica of the sampler step machine (sampler.cuh) in warp 0 -- bit-identical in all
-//     CTAs -- so the next theta is available locally without a publish/poll round trip.
-//     Only CTA 0 writes chain state and collected draws.
+//     and logit = x . theta (packed FFMA2), the Bernoulli log-likelihood and the gradient
+//     contribution (sigmoid(l) - y) x are all computed from those registers (the
+//     reference's XLA program reads X twice: forward dot + transposed dot).  Per-lane
+//     gradient accumulators are folded across lanes once per pass (shuffle transpose-reduce).
+//   * CTA partials go to global memory behind a grid-wide arrival counter.  EVERY CTA then
+//     reduces all partials in the same fixed order and advances its own replica of the
+//     sampler step machine (sampler.cuh) in warp 0 -- bit-identical in all CTAs -- so the
+//     next theta is available locally without a publish/poll round trip.  Only CTA 0
+//     writes chain state and collected draws.
 //
 // Replaces: potential_energy/log_density for this family (infer/util.py:302-327),
 // value_and_grad (hmc_util.py:242-252) and the whole sample_kernel loop (hmc.py:459-530).
@@ -28,28 +34,30 @@
 
 namespace b200mc {
 
-constexpr int kGlmConsumerWarps = 7;  // + 1 producer warp = 2 warps per SM sub-partition (255 regs)
+constexpr int kGlmConsumerWarps = 11;  // + 1 producer warp = 3 warps per SM sub-partition
 constexpr int kGlmConsumerThreads = kGlmConsumerWarps * 32;
-constexpr int kGlmThreads = kGlmConsumerThreads + 32;  // + producer warp
+constexpr int kGlmThreads = kGlmConsumerThreads + 32;
 constexpr int kGlmTileRows = 32;
 constexpr int kGlmMaxD = 128;
-constexpr int kGlmGroups = 4;        // grid reduction: CTAs are summed in kGlmGroups strided groups
-constexpr int kGlmMaxStagesPerWarp = 8;
+constexpr int kGlmMaxStages = 32;      // one producer lane per stage
 constexpr int kGlmProfSlots = 8;
+
+__host__ __device__ inline int glm_groups(int D) { return (D + 3) / 4; }
+__host__ __device__ inline int glm_tile_bytes(int D) { return glm_groups(D) * 512 + 32; }
+__host__ __device__ inline int glm_partial_stride(int D) { return (D + 1 + 3) & ~3; }
 
 struct GlmLaunch {
   SamplerParams P;
   CollectSpec col;
   ChainScalars* cs;
   ChainVectors cv;
-  const float* X;      // [N][D] row-major, 16-byte aligned
-  const uint8_t* y;    // [N] 0/1, 16-byte aligned
+  const unsigned char* Xt;  // re-tiled data, glm_tile_bytes(D) per tile, 16-byte aligned
   int N, D;
-  int rows_per_cta;    // multiple of 32
-  int n_stages;        // multiple of kGlmConsumerWarps
+  int nt_total;        // ceil(N / 32)
+  int n_stages;        // multiple of kGlmConsumerWarps, <= kGlmMaxStages
   int reverse_odd;     // sweep odd passes backwards (L2 reuse)
   // grid-level exchange (global memory)
-  float* partials;       // [2][nCTA][DP1], double-buffered by pass parity
+  float* partials;       // [2][nCTA][glm_partial_stride(D)], double-buffered by pass parity
   unsigned* arrive;      // monotonic arrival counter, zeroed by the host before the launch
   int* error;            // set to 1 on a spin time-out
   unsigned long long* prof;  // [kGlmProfSlots] cycle counters of CTA 0 (or null)
@@ -132,43 +140,67 @@ __device__ __forceinline__ float rcp_1to2(float d) {
   return fmaf(r, fmaf(-d, r, 1.0f), r);
 }
 
-// ---------------------------------------------------------------- per-tile arithmetic
-// One 32-row tile, lane r <-> row r.  NCH = ceil(D / 32) column chunks.  For D <= 64 the
-// row is read from shared memory once and kept in registers for both the logit and the
-// gradient accumulation; for wider rows it is re-read chunk by chunk.
-// xs: [32][D] floats (shared), ys: labels, th: theta zero-padded to 32*NCH (shared).
-// acc[k] accumulates, per lane, (sigmoid(l) - y) * x[k] over this lane's rows.
-template <int NCH>
-__device__ __forceinline__ void glm_tile(const float* __restrict__ xs,
-                                         const uint8_t* __restrict__ ys, int rows,
-                                         const float* __restrict__ th, int D,
-                                         float (&acc)[NCH * 32], float& ll) {
-  constexpr int DM = NCH * 32;
-  constexpr int LB = DM - 32;  // columns below LB exist for every D of this NCH
-  constexpr bool KEEP = (NCH <= 2);
-  const int lane = threadIdx.x & 31;
-  const float* xr = xs + lane * D;
-  const int dl = D - 1;
-  // Branch-free: a column index >= D is clamped to D-1 (a valid, finite element) and meets
-  // a zero of the padded theta; its accumulator is never read.
-  float x[KEEP ? DM : 4];
-  float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
-#pragma unroll
-  for (int k = 0; k < DM; k += 4) {
-    const float4 t4 = *reinterpret_cast<const float4*>(th + k);
-    const float x0 = xr[(k + 0 < LB) ? k + 0 : min(k + 0, dl)];
-    const float x1 = xr[(k + 1 < LB) ? k + 1 : min(k + 1, dl)];
-    const float x2 = xr[(k + 2 < LB) ? k + 2 : min(k + 2, dl)];
-    const float x3 = xr[(k + 3 < LB) ? k + 3 : min(k + 3, dl)];
-    if (KEEP) {
-      x[k] = x0; x[k + 1] = x1; x[k + 2] = x2; x[k + 3] = x3;
+// Re-tile X [N][D] row-major + labels [N] into the layout described at the top of the file.
+__global__ void glm_retile_kernel(const float* __restrict__ X, const uint8_t* __restrict__ y,
+                                  int N, int D, int nt_total, unsigned char* __restrict__ Xt) {
+  const int G = glm_groups(D);
+  const long tb = glm_tile_bytes(D);
+  const long per_tile = (long)G * 32 + 2;  // float4 slots + two 16-byte label slots
+  const long total = per_tile * nt_total;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total;
+       i += (long)gridDim.x * blockDim.x) {
+    const long t = i / per_tile;
+    const int s = (int)(i - t * per_tile);
+    unsigned char* tile = Xt + t * tb;
+    if (s < G * 32) {
+      const int g = s >> 5, r = s & 31;
+      const long row = t * 32 + r;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (row < N) {
+        const float* xr = X + row * D + 4 * g;
+        v.x = xr[0];
+        if (4 * g + 1 < D) v.y = xr[1];
+        if (4 * g + 2 < D) v.z = xr[2];
+        if (4 * g + 3 < D) v.w = xr[3];
+      }
+      reinterpret_cast<float4*>(tile)[s] = v;
+    } else {
+      const int h = s - G * 32;  // 0 or 1: rows 16h .. 16h+15
+      unsigned char* dst = tile + (long)G * 512 + 16 * h;
+      for (int k = 0; k < 16; ++k) {
+        const long row = t * 32 + 16 * h + k;
+        dst[k] = (row < N) ? y[row] : (unsigned char)0;
+      }
     }
-    l0 = fmaf(x0, t4.x, l0);
-    l1 = fmaf(x1, t4.y, l1);
-    l2 = fmaf(x2, t4.z, l2);
-    l3 = fmaf(x3, t4.w, l3);
   }
-  const float l = (l0 + l1) + (l2 + l3);
+}
+
+// ---------------------------------------------------------------- per-tile arithmetic
+// One 32-row tile, lane r <-> row r.  xt: [G][32] float4 (shared), ys: 32 labels, th4: theta
+// zero-padded to 4G floats (shared).  acc[k] accumulates, per lane, (sigmoid(l) - y) * x[k]
+// over this lane's rows.  GT = G for the register-resident variant (G <= 16); GT = 0 selects
+// the wide variant (G <= 32), which re-reads the row for the gradient.
+template <int GT>
+__device__ __forceinline__ void glm_tile(const float4* __restrict__ xt,
+                                         const uint8_t* __restrict__ ys, int rows,
+                                         const float4* __restrict__ th4, int G,
+                                         float (&acc)[GT ? 4 * GT : 128], float& ll) {
+  constexpr int GM = GT ? GT : 32;
+  const int lane = threadIdx.x & 31;
+  const float4* xr = xt + lane;
+  float4 x[GT ? GT : 1];
+  float2 l01 = make_float2(0.f, 0.f), l23 = make_float2(0.f, 0.f);
+#pragma unroll
+  for (int g = 0; g < GM; ++g) {
+    if (GT || g < G) {
+      const float4 v = xr[g * 32];
+      const float4 t = th4[g];
+      if (GT) x[g] = v;
+      l01 = __ffma2_rn(make_float2(v.x, v.y), make_float2(t.x, t.y), l01);
+      l23 = __ffma2_rn(make_float2(v.z, v.w), make_float2(t.z, t.w), l23);
+    }
+  }
+  const float l = (l01.x + l01.y) + (l23.x + l23.y);
   float gres = 0.f;
   if (lane < rows) {
     const float yv = (float)ys[lane];
@@ -179,16 +211,23 @@ __device__ __forceinline__ void glm_tile(const float* __restrict__ xs,
     ll += (fmaxf(l, 0.f) + log1pf(e)) - l * yv;
     gres = sig - yv;
   }
+  const float2 g2 = make_float2(gres, gres);
 #pragma unroll
-  for (int k = 0; k < DM; ++k) {
-    if (KEEP) acc[k] = fmaf(gres, x[k], acc[k]);
-    else acc[k] = fmaf(gres, xr[(k < LB) ? k : min(k, dl)], acc[k]);
+  for (int g = 0; g < GM; ++g) {
+    if (GT || g < G) {
+      const float4 v = GT ? x[GT ? g : 0] : xr[g * 32];
+      const float2 a01 = __ffma2_rn(g2, make_float2(v.x, v.y), make_float2(acc[4 * g], acc[4 * g + 1]));
+      const float2 a23 =
+          __ffma2_rn(g2, make_float2(v.z, v.w), make_float2(acc[4 * g + 2], acc[4 * g + 3]));
+      acc[4 * g] = a01.x; acc[4 * g + 1] = a01.y;
+      acc[4 * g + 2] = a23.x; acc[4 * g + 3] = a23.y;
+    }
   }
 }
 
 // Recursive-halving transpose-reduce: on return a[0] of lane L holds the sum over all
 // lanes of the original a[L] (31 shuffles for 32 columns; fixed order => deterministic).
-__device__ __forceinline__ float warp_transpose_reduce32(float* a) {
+__device__ __forceinline__ float warp_transpose_reduce32(float (&a)[32]) {
   const int lane = threadIdx.x & 31;
 #pragma unroll
   for (int s = 16; s >= 1; s >>= 1) {
@@ -205,88 +244,92 @@ __device__ __forceinline__ float warp_transpose_reduce32(float* a) {
 
 // ---------------------------------------------------------------- shared-memory layout
 struct GlmSmem {
-  int stage_bytes, off_tail, off_full, off_empty, off_theta, off_red, off_red2, off_work,
-      off_flags, total;
+  int stage_bytes, off_full, off_empty, off_theta, off_red, off_red2, off_work, off_flags, total;
 };
+constexpr int kGlmRedGroups = 16;  // grid reduction: CTAs are summed in strided groups
 
 __host__ __device__ inline GlmSmem glm_smem_layout(int D, int n_stages, int max_depth) {
   GlmSmem s;
-  const int dp1 = D + 1;
-  s.stage_bytes = kGlmTileRows * D * 4 + kGlmTileRows;  // X tile then labels; multiple of 16
+  const int ps = glm_partial_stride(D);
+  s.stage_bytes = glm_tile_bytes(D);  // multiple of 16
   int o = n_stages * s.stage_bytes;
-  s.off_tail = o;  o += s.stage_bytes;
-  s.off_full = o;  o += n_stages * 8;
-  s.off_empty = o; o += n_stages * 8;
-  o = (o + 15) & ~15;
-  s.off_theta = o; o += kGlmMaxD * 4;  // zero-padded to a multiple of 32 columns
-  s.off_red = o;   o += kGlmConsumerWarps * dp1 * 4;
-  s.off_red2 = o;  o += kGlmGroups * dp1 * 4;
-  o = (o + 15) & ~15;
+  s.off_full = o;  o += kGlmMaxStages * 8;
+  s.off_empty = o; o += kGlmMaxStages * 8;
+  s.off_theta = o; o += kGlmMaxD * 4;  // zero-padded
+  s.off_red = o;   o += kGlmConsumerWarps * ps * 4;
+  s.off_red2 = o;  o += kGlmRedGroups * ps * 4;
   s.off_work = o;  o += num_slots(max_depth) * D * 4;
+  o = (o + 15) & ~15;
   s.off_flags = o; o += 16;
   s.total = o;
   return s;
 }
 
-// Row offset (within the CTA's slice, in tiles) of the j-th tile of pass `pass`.
-__device__ __forceinline__ int glm_tile_of(int j, int pass, int ntiles, int reverse_odd) {
-  return (reverse_odd && (pass & 1)) ? (ntiles - 1 - j) : j;
+__device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
 }
 
 // One pass worth of tiles for one consumer warp; leaves its partial gradient and
-// log-likelihood in red[warp][0..D].  Tile q (global sequence number over all passes) is
-// consumed by warp q % W from stage q % NS; NS is a multiple of W, so every stage is only
-// ever consumed by one warp, strictly in phase order.
-template <int NCH>
+// log-likelihood in red[warp][0..D].  The CTA's tile stream is numbered p = 0, 1, ... over
+// all passes; position p is consumed by warp p % W from stage p % NS.  NS = m * W, so warp w
+// only ever touches stages w, w + W, ..., w + (m-1) W, strictly in phase order (si, ph).
+template <int GT>
 __device__ __forceinline__ void glm_consume_pass(const GlmLaunch& L, unsigned char* smem,
-                                                 const GlmSmem& lay, int warp, long& q_next,
-                                                 long q_end, int row0, int ntiles, int tail_rows) {
+                                                 const GlmSmem& lay, int warp, long& p_next,
+                                                 long p_begin, long p_end, int& si, uint32_t& ph,
+                                                 int m, int tile0, int nt, bool rev) {
+  constexpr int NA = GT ? 4 * GT : 128;
   const int lane = threadIdx.x & 31;
-  const int D = L.D, NS = L.n_stages;
+  const int G = glm_groups(L.D), PS = glm_partial_stride(L.D);
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + lay.off_full);
   uint64_t* empty = reinterpret_cast<uint64_t*>(smem + lay.off_empty);
-  const float* th = reinterpret_cast<const float*>(smem + lay.off_theta);
-  float acc[NCH * 32];
+  const float4* th4 = reinterpret_cast<const float4*>(smem + lay.off_theta);
+  float acc[NA];
 #pragma unroll
-  for (int k = 0; k < NCH * 32; ++k) acc[k] = 0.f;
+  for (int k = 0; k < NA; ++k) acc[k] = 0.f;
   float ll = 0.f;
-  for (; q_next < q_end; q_next += kGlmConsumerWarps) {
-    const int stage = (int)(q_next % NS);
-    const uint32_t parity = (uint32_t)((q_next / NS) & 1);
-    mbar_wait(&full[stage], parity);
+  for (; p_next < p_end; p_next += kGlmConsumerWarps) {
+    const int stage = warp + si * kGlmConsumerWarps;
+    mbar_wait(&full[stage], ph);
     const unsigned char* sp = smem + (long)stage * lay.stage_bytes;
-    glm_tile<NCH>(reinterpret_cast<const float*>(sp), sp + kGlmTileRows * D * 4, kGlmTileRows, th,
-                  D, acc, ll);
+    const int j = (int)(p_next - p_begin);
+    const int tile = tile0 + (rev ? (nt - 1 - j) : j);
+    const int rows = (tile == L.nt_total - 1) ? (L.N - 32 * tile) : 32;
+    glm_tile<GT>(reinterpret_cast<const float4*>(sp), sp + G * 512, rows, th4, G, acc, ll);
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[stage]);
-  }
-  if (tail_rows > 0 && warp == kGlmConsumerWarps - 1) {
-    // the last (< 32)-row tile of the data set: plain loads into the (zero-filled) tail buffer
-    unsigned char* tp = smem + lay.off_tail;
-    float* tx = reinterpret_cast<float*>(tp);
-    unsigned char* ty = tp + kGlmTileRows * D * 4;
-    const long r0 = (long)row0 + (long)ntiles * kGlmTileRows;
-    for (int i = lane; i < kGlmTileRows * D; i += 32)
-      tx[i] = (i < tail_rows * D) ? L.X[r0 * D + i] : 0.f;
-    ty[lane] = (lane < tail_rows) ? L.y[r0 + lane] : (uint8_t)0;
-    __syncwarp();
-    glm_tile<NCH>(tx, ty, tail_rows, th, D, acc, ll);
-    __syncwarp();
+    if (++si == m) {
+      si = 0;
+      ph ^= 1u;
+    }
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) ll += __shfl_xor_sync(0xffffffffu, ll, o);
-  float* red = reinterpret_cast<float*>(smem + lay.off_red) + warp * (D + 1);
+  float* red = reinterpret_cast<float*>(smem + lay.off_red) + warp * PS;
 #pragma unroll
-  for (int c = 0; c < NCH; ++c) {
-    const float v = warp_transpose_reduce32(acc + 32 * c);
-    if (32 * c + lane < D) red[32 * c + lane] = v;
+  for (int c = 0; c < (NA + 31) / 32; ++c) {
+    if (GT || 32 * c < L.D) {
+      float a[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) a[i] = (32 * c + i < NA) ? acc[(32 * c + i < NA) ? 32 * c + i : 0] : 0.f;
+      const float v = warp_transpose_reduce32(a);
+      if (32 * c + lane < L.D) red[32 * c + lane] = v;
+    }
   }
-  if (lane == 0) red[D] = ll;
+  if (lane == 0) red[L.D] = ll;
 }
 
 __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_constant__ GlmLaunch L) {
   extern __shared__ __align__(128) unsigned char smem[];
-  const int D = L.D, NS = L.n_stages, DP1 = D + 1;
+  const int D = L.D, NS = L.n_stages, PS = glm_partial_stride(D);
   const GlmSmem lay = glm_smem_layout(D, NS, L.P.max_depth);
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + lay.off_full);
   uint64_t* empty = reinterpret_cast<uint64_t*>(smem + lay.off_empty);
@@ -298,11 +341,9 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int cta = blockIdx.x, nCTA = gridDim.x;
-  const long row0l = (long)cta * L.rows_per_cta;
-  const int row0 = (int)(row0l < L.N ? row0l : L.N);
-  const int row1 = (int)((row0l + L.rows_per_cta) < L.N ? (row0l + L.rows_per_cta) : L.N);
-  const int ntiles = (row1 - row0) / kGlmTileRows;              // full tiles: TMA
-  const int tail_rows = (row1 - row0) - ntiles * kGlmTileRows;  // < 32, last CTA only
+  const int tile0 = (int)((long)cta * L.nt_total / nCTA);
+  const int nt = (int)((long)(cta + 1) * L.nt_total / nCTA) - tile0;
+  const long tb = lay.stage_bytes;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < NS; ++i) {
@@ -312,34 +353,33 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
     flags[0] = 0; flags[1] = 0; flags[2] = 0; flags[3] = 1;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  for (int i = threadIdx.x; i < (kGlmConsumerWarps + kGlmRedGroups) * PS; i += blockDim.x)
+    red[i] = 0.f;  // red and red2 are adjacent; their pad columns stay zero
   __syncthreads();
 
   if (warp == kGlmConsumerWarps) {
-    // ================= producer warp: TMA ring, runs ahead across passes =================
-    if (lane == 0 && ntiles > 0) {
-      const uint32_t xbytes = kGlmTileRows * D * 4, ybytes = kGlmTileRows;
-      long q = 0;
-      int pass = 0, j = 0;
-      while (true) {
-        const int stage = (int)(q % NS);
-        const uint32_t parity = (uint32_t)(((q / NS) & 1) ^ 1);
-        bool stop = false;
-        while (!mbar_try_wait(&empty[stage], parity)) {
-          if (flags[0]) { stop = true; break; }
+    // ================= producer warp: lane s feeds stage s, runs ahead across passes ========
+    const int s = lane;
+    if (s < NS && nt > 0) {
+      int pass_l = 0, j = s;
+      while (j >= nt) { j -= nt; ++pass_l; }
+      uint32_t n_issued = 0;
+      unsigned char* sp = smem + (long)s * tb;
+      while (!flags[0]) {
+        if (mbar_test_wait(&empty[s], (n_issued & 1u) ^ 1u)) {
+          const int jj = (L.reverse_odd && (pass_l & 1)) ? (nt - 1 - j) : j;
+          mbar_arrive_expect_tx(&full[s], (uint32_t)tb);
+          tma_load_1d(sp, L.Xt + (long)(tile0 + jj) * tb, (uint32_t)tb, &full[s]);
+          ++n_issued;
+          j += NS;
+          while (j >= nt) { j -= nt; ++pass_l; }
         }
-        if (stop || flags[0]) break;
-        const long r = (long)row0 + (long)glm_tile_of(j, pass, ntiles, L.reverse_odd) * kGlmTileRows;
-        unsigned char* sp = smem + (long)stage * lay.stage_bytes;
-        mbar_arrive_expect_tx(&full[stage], xbytes + ybytes);
-        tma_load_1d(sp, L.X + r * D, xbytes, &full[stage]);
-        tma_load_1d(sp + xbytes, L.y + r, ybytes, &full[stage]);
-        ++q;
-        if (++j == ntiles) { j = 0; ++pass; }
       }
-      // drain: wait for every copy that was issued but never consumed
-      const long consumed = (long)flags[1] * ntiles;
-      for (long t = consumed; t < q; ++t)
-        mbar_wait(&full[(int)(t % NS)], (uint32_t)((t / NS) & 1));
+      // drain: only the last copy of this stage can still be unconsumed
+      if (n_issued > 0) {
+        const long p_last = (long)s + (long)(n_issued - 1) * NS;
+        if (p_last >= (long)flags[1] * nt) mbar_wait(&full[s], (n_issued - 1) & 1u);
+      }
     }
     return;
   }
@@ -371,27 +411,37 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
   }
   consumer_bar();
 
-  const int NCH = (D + 31) / 32;
-  long q_next = warp;
+  const int G = glm_groups(D);
+  const int m = NS / kGlmConsumerWarps;
+  long p_next = warp;
+  int si = 0;
+  uint32_t ph = 0;
   int pass = 0;
   long long t_mark = clock64();
   unsigned long long c_stream = 0, c_wait = 0, c_reduce = 0, c_sampler = 0;
   while (flags[2]) {
-    // ---- stream this CTA's rows
-    const long q_end = (long)(pass + 1) * ntiles;
-    switch (NCH) {
-      case 1: glm_consume_pass<1>(L, smem, lay, warp, q_next, q_end, row0, ntiles, tail_rows); break;
-      case 2: glm_consume_pass<2>(L, smem, lay, warp, q_next, q_end, row0, ntiles, tail_rows); break;
-      case 3: glm_consume_pass<3>(L, smem, lay, warp, q_next, q_end, row0, ntiles, tail_rows); break;
-      default: glm_consume_pass<4>(L, smem, lay, warp, q_next, q_end, row0, ntiles, tail_rows); break;
+    // ---- stream this CTA's tiles
+    const long p_begin = (long)pass * nt, p_end = p_begin + nt;
+    const bool rev = L.reverse_odd && (pass & 1);
+#define B200MC_GLM_CASE(GT) \
+  case GT: glm_consume_pass<GT>(L, smem, lay, warp, p_next, p_begin, p_end, si, ph, m, tile0, nt, rev); break;
+    switch (G <= 16 ? G : 0) {
+      B200MC_GLM_CASE(1) B200MC_GLM_CASE(2) B200MC_GLM_CASE(3) B200MC_GLM_CASE(4)
+      B200MC_GLM_CASE(5) B200MC_GLM_CASE(6) B200MC_GLM_CASE(7) B200MC_GLM_CASE(8)
+      B200MC_GLM_CASE(9) B200MC_GLM_CASE(10) B200MC_GLM_CASE(11) B200MC_GLM_CASE(12)
+      B200MC_GLM_CASE(13) B200MC_GLM_CASE(14) B200MC_GLM_CASE(15) B200MC_GLM_CASE(16)
+      default:
+        glm_consume_pass<0>(L, smem, lay, warp, p_next, p_begin, p_end, si, ph, m, tile0, nt, rev);
+        break;
     }
+#undef B200MC_GLM_CASE
     consumer_bar();
     // ---- CTA partial: fixed-order sum over warps
-    float* my_partials = L.partials + ((long)(pass & 1) * nCTA + cta) * DP1;
-    if (tid < DP1) {
+    float* my_partials = L.partials + ((long)(pass & 1) * nCTA + cta) * PS;
+    if (tid < PS) {
       float a = 0.f;
 #pragma unroll
-      for (int w2 = 0; w2 < kGlmConsumerWarps; ++w2) a += red[w2 * DP1 + tid];
+      for (int w2 = 0; w2 < kGlmConsumerWarps; ++w2) a += red[w2 * PS + tid];
       __stcg(&my_partials[tid], a);
     }
     consumer_bar();
@@ -410,21 +460,25 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
       c_wait += (unsigned long long)(t_mark - t1);
     }
     consumer_bar();
-    // ---- every CTA: grid reduction in a fixed order
-    const float* all_partials = L.partials + (long)(pass & 1) * nCTA * DP1;
-    for (int item = tid; item < kGlmGroups * DP1; item += kGlmConsumerThreads) {
-      const int c = item % DP1, grp = item / DP1;
-      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-      int b = grp;
-      for (; b + 3 * kGlmGroups < nCTA; b += 4 * kGlmGroups) {
-        const float v0 = __ldcg(&all_partials[(long)b * DP1 + c]);
-        const float v1 = __ldcg(&all_partials[(long)(b + kGlmGroups) * DP1 + c]);
-        const float v2 = __ldcg(&all_partials[(long)(b + 2 * kGlmGroups) * DP1 + c]);
-        const float v3 = __ldcg(&all_partials[(long)(b + 3 * kGlmGroups) * DP1 + c]);
-        a0 += v0; a1 += v1; a2 += v2; a3 += v3;
+    // ---- every CTA: grid reduction in a fixed order (128-bit L2 loads, all independent)
+    const float4* all4 = reinterpret_cast<const float4*>(L.partials + (long)(pass & 1) * nCTA * PS);
+    const int PS4 = PS >> 2;
+    for (int item = tid; item < kGlmRedGroups * PS4; item += kGlmConsumerThreads) {
+      const int c4 = item % PS4, grp = item / PS4;
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int b0 = grp; b0 < nCTA; b0 += kGlmRedGroups * 10) {
+        float4 v[10];
+#pragma unroll
+        for (int i = 0; i < 10; ++i) {
+          const int b = b0 + kGlmRedGroups * i;
+          v[i] = (b < nCTA) ? __ldcg(&all4[(long)b * PS4 + c4]) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int i = 0; i < 10; ++i) {
+          a.x += v[i].x; a.y += v[i].y; a.z += v[i].z; a.w += v[i].w;
+        }
       }
-      for (; b < nCTA; b += kGlmGroups) a0 += __ldcg(&all_partials[(long)b * DP1 + c]);
-      red2[grp * DP1 + c] = (a0 + a1) + (a2 + a3);
+      reinterpret_cast<float4*>(red2 + grp * PS)[c4] = a;
     }
     consumer_bar();
     // ---- warp 0: finish the potential, advance the sampler replica, next theta
@@ -440,7 +494,7 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
       for (int d = lane; d < D; d += 32) {
         float a = 0.f;
 #pragma unroll
-        for (int p2 = 0; p2 < kGlmGroups; ++p2) a += red2[p2 * DP1 + d];
+        for (int p2 = 0; p2 < kGlmRedGroups; ++p2) a += red2[p2 * PS + d];
         const float t = lz[d];
         lg[d] = t + a;                                // grad U = theta + X^T (sigmoid - y)
         prior += 0.5f * t * t + 0.9189385332046727f;  // -log N(theta; 0, 1)
@@ -448,7 +502,7 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
       prior = WarpGroup{}.sum(prior);
       float llik = 0.f;
 #pragma unroll
-      for (int p2 = 0; p2 < kGlmGroups; ++p2) llik += red2[p2 * DP1 + D];
+      for (int p2 = 0; p2 < kGlmRedGroups; ++p2) llik += red2[p2 * PS + D];
       const float U = prior + llik;
       if (eval_mode) {
         if (cta == 0) {
