@@ -238,6 +238,17 @@ def run_own(args):
         return float(t.item())
 
     X, y = make_covtype_shape()
+    # the e2e leg copies from PINNED host memory: move X, y into pinned allocations
+    def pinned_copy(a):
+        ptr = lib.b200mc_host_alloc(a.nbytes)
+        if not ptr:
+            raise _lib.B200Error(lib.b200mc_last_error().decode())
+        buf = (C.c_char * a.nbytes).from_address(ptr)
+        out = np.frombuffer(buf, dtype=a.dtype).reshape(a.shape)
+        out[...] = a
+        return out
+
+    X, y = pinned_copy(X), pinned_copy(y)
     # one chain per GPU: chain keys as MCMC.run would split them for `world` chains
     key = PRNGKey(1) if world == 1 else split(PRNGKey(1), world)[rank]
 
@@ -269,7 +280,7 @@ def run_own(args):
 
     for _ in range(args.warmup):
         device_step()
-    prof = (C.c_uint64 * 8)()
+    prof = (C.c_uint64 * 16)()
     _lib.check(lib.b200mc_get_profile(kern._handle, prof, 1))  # reset the cycle counters
     launches0 = lib.b200mc_kernel_launches()
     clocks = ClockSampler(local) if rank == 0 else None
@@ -285,6 +296,8 @@ def run_own(args):
     passes = max(1, int(prof[4]))
     breakdown = {k: float(prof[i]) / passes for i, k in
                  enumerate(("stream", "arrival_wait", "grid_reduce", "sampler_step"))}
+    if any(prof[8 + i] for i in range(8)):
+        breakdown["sampler_sub"] = [float(prof[8 + i]) / passes for i in range(8)]
     total_ms = max_over_ranks(sum(step_ms))
     total_grads = sum_over_ranks(float(sum(step_grads)))
     value = total_grads / (total_ms * 1e-3)
@@ -363,7 +376,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
-    ap.add_argument("--transitions", type=int, default=20, help="NUTS transitions per step")
+    ap.add_argument("--transitions", type=int, default=100, help="NUTS transitions per step")
     ap.add_argument("--adapt", type=int, default=300, help="untimed adaptation transitions")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU baseline work")
     ap.add_argument("--no-cpu", action="store_true")

@@ -133,9 +133,10 @@ int b200mc_set_vector(b200mc_handle* h, int which, const float* in_dev, void* st
 
 /* Cycle counters of the streaming (logistic) kernel, accumulated over launches by CTA 0:
  * out[0] stream+partial, [1] grid-arrival wait, [2] grid reduction, [3] sampler step,
- * [4] passes (= gradient evaluations); SM clock cycles.  No reference counterpart
+ * [4] passes (= gradient evaluations); SM clock cycles.  [8..15]: sampler sub-phases when
+ * the library is built with -DB200MC_SAMPLER_PROF, else 0.  No reference counterpart
  * (diagnostic). */
-int b200mc_get_profile(b200mc_handle* h, uint64_t* out_host /*[8]*/, int reset);
+int b200mc_get_profile(b200mc_handle* h, uint64_t* out_host /*[16]*/, int reset);
 
 /* potential_energy + value_and_grad (infer/util.py:302-327, hmc_util.py:242-252) at
  * n points z[n][D]: tier-2 parity hook. */

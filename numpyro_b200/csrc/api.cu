@@ -420,7 +420,7 @@ extern "C" int b200mc_set_scalars(b200mc_handle* h, const b200mc_chain_scalars* 
 
 extern "C" int b200mc_get_profile(b200mc_handle* h, uint64_t* out_host, int reset) {
   if (!h || !out_host) return fail("null argument");
-  for (int i = 0; i < 8; ++i) out_host[i] = 0;
+  for (int i = 0; i < kGlmProfSlots; ++i) out_host[i] = 0;
   if (!h->prof) return 0;
   CK(cudaDeviceSynchronize());
   CK(cudaMemcpy(out_host, h->prof, sizeof(unsigned long long) * kGlmProfSlots,

@@ -40,7 +40,7 @@ constexpr int kGlmThreads = kGlmConsumerThreads + 32;
 constexpr int kGlmTileRows = 32;
 constexpr int kGlmMaxD = 128;
 constexpr int kGlmMaxStages = 32;      // one producer lane per stage
-constexpr int kGlmProfSlots = 8;
+constexpr int kGlmProfSlots = 16;
 
 __host__ __device__ inline int glm_groups(int D) { return (D + 3) / 4; }
 __host__ __device__ inline int glm_tile_bytes(int D) { return glm_groups(D) * 512 + 32; }
@@ -393,6 +393,9 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
     float* work = reinterpret_cast<float*>(smem + lay.off_work);
     S.setup(&L.P, WarpGroup{}, work, D, 1, L.chain, L.C, &L.col);
     S.writer = (cta == 0);
+#ifdef B200MC_SAMPLER_PROF
+    for (int i = 0; i < 8; ++i) S.pc[i] = 0;
+#endif
     if (eval_mode) {
       for (int d = lane; d < D; d += 32) S.v(LZ)[d] = L.eval_z[d];
       sres = NEED_GRAD;
@@ -536,6 +539,9 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
       atomicAdd(&L.prof[2], c_reduce);
       atomicAdd(&L.prof[3], c_sampler);
       atomicAdd(&L.prof[4], (unsigned long long)pass);
+#ifdef B200MC_SAMPLER_PROF
+      for (int i = 0; i < 8; ++i) atomicAdd(&L.prof[8 + i], S.pc[i]);
+#endif
     }
   }
   if (warp == 0 && !eval_mode) S.store(L.cs, L.cv);

@@ -70,6 +70,14 @@ struct Sampler {
   bool part;
 
   bool writer;         // false: a replica that advances the same chain but writes nothing
+#ifdef B200MC_SAMPLER_PROF
+  unsigned long long pc[8];
+#define B200MC_STAMP(var) const long long var = clock64()
+#define B200MC_ACC(i, a, b) pc[i] += (unsigned long long)((b) - (a))
+#else
+#define B200MC_STAMP(var)
+#define B200MC_ACC(i, a, b)
+#endif
   ChainScalars s;      // persistent scalars (registers)
 
   // run control
@@ -412,6 +420,7 @@ struct Sampler {
   // ------------------------------------------------------------------ NUTS: one leaf
   __device__ StepResult advance_tree(float U) {
     // 1. finish the leapfrog, energy test (_build_basetree, hmc_util.py:863-875)
+    B200MC_STAMP(t0_);
     finish_leapfrog();
     const float e_new = U + kinetic(LR);
     float dE = e_new - e0;
@@ -421,6 +430,8 @@ struct Sampler {
     const float acc = fminf(expf(-dE), 1.0f);
 
     // 2. fold the leaf into the subtree (uniform / multinomial kernel, :749-753, :1020-1032)
+    B200MC_STAMP(t1_);
+    B200MC_ACC(0, t0_, t1_);
     prefetch_rng();
     sub_key = pre_sub_key;
     pre_valid = 0;
@@ -447,6 +458,8 @@ struct Sampler {
     }
 
     // 3. checkpoints and iterative U-turn test (:941-981, :1034-1058)
+    B200MC_STAMP(t2_);
+    B200MC_ACC(1, t1_, t2_);
     const int idx_max = __popc(leaf_idx >> 1);
     const int num_sub = __popc(((~leaf_idx) & (leaf_idx + 1)) - 1);
     const int idx_min = idx_max - num_sub + 1;
@@ -463,8 +476,13 @@ struct Sampler {
       sub_turning = is_turning(ckpt_r(i), v(LR), v(S_RSUM), ckpt_rs(i), ckpt_r(i));
 
     // 4. keep extending the subtree? (_cond_fn, :999-1001)
+    B200MC_STAMP(t3_);
+    B200MC_ACC(2, t2_, t3_);
     if (s_n < (1 << depth) && !sub_turning && !s_div) {
       half_step();
+      B200MC_STAMP(t4_);
+      B200MC_ACC(3, t3_, t4_);
+      B200MC_ACC(4, 0, 1);
       return NEED_GRAD;
     }
 
@@ -495,8 +513,13 @@ struct Sampler {
     nprop += s_n;
 
     // 6. double again? (build_tree._cond_fn, :1155-1157)
+    B200MC_STAMP(t5_);
+    B200MC_ACC(5, t3_, t5_);
     if (depth < max_depth_cur && !turning && !diverging) {
       next_doubling();
+      B200MC_STAMP(t6_);
+      B200MC_ACC(6, t5_, t6_);
+      B200MC_ACC(7, 0, 1);
       return NEED_GRAD;
     }
 

@@ -74,7 +74,7 @@ def _bind_logistic(data, labels, subsample_size=None):
     if subsample_size is not None:
         raise NotImplementedError("subsample_size (HMCECS) is not part of the registered hot path")
     X = np.ascontiguousarray(data, np.float32)
-    y = np.ascontiguousarray(labels).astype(np.uint8)
+    y = np.ascontiguousarray(labels).astype(np.uint8, copy=False)
     if X.ndim != 2 or y.shape != (X.shape[0],):
         raise ValueError("logistic_regression expects data [N, D] and labels [N]")
     return BoundModel(LOGISTIC, "logistic", X.shape[0], X.shape[1], X, y,
