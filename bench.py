@@ -370,8 +370,94 @@ def run_own(args):
     return 0
 
 
+# ---------------------------------------------------------------------------- other configs
+def make_workload(name, chains):
+    """BASELINE.json configs[1], [3], [4] on synthetic data."""
+    from numpyro_b200 import models
+
+    if name == "eight_schools":
+        y = np.array([28.0, 8.0, -3.0, 7.0, -1.0, 1.0, 18.0, 12.0])
+        sg = np.array([15.0, 10.0, 16.0, 11.0, 9.0, 11.0, 10.0, 18.0])
+        return (models.eight_schools_noncentered, (8, sg), {"y": y}, {}, chains or 16384,
+                "eight schools non-centred NUTS, vectorized chains (configs[1])")
+    if name == "sv":
+        rng = np.random.default_rng(21)
+        T_ = 3000
+        s = np.cumsum(rng.normal(size=T_) * 0.02) - 4.5
+        r = (np.exp(s) * rng.standard_t(10, size=T_)).astype(np.float32)
+        return (models.stochastic_volatility, (r,), {}, {}, chains or 1024,
+                "stochastic volatility random walk T=3000 NUTS (configs[4])")
+    if name == "horseshoe":
+        rng = np.random.RandomState(0)
+        N, D = 10000, 1000
+        X = rng.randn(N, D).astype(np.float32)
+        Y = X[:, :3] @ np.array([2.0, -1.0, 0.5])
+        Y = (Y - Y.mean() + 0.05 * rng.randn(N)).astype(np.float32)
+        return (models.horseshoe_normal, (X, Y), {}, {"dense_mass": True}, chains or 256,
+                "horseshoe regression D=1000 N=10000 dense mass NUTS (configs[3])")
+    raise SystemExit(f"unknown workload {name}")
+
+
+def run_chain_workload(args):
+    """Chain-batched configs: a step = `--transitions` NUTS transitions of ALL chains in one
+    persistent launch; metric = grad evals/s summed over chains (device timed)."""
+    import ctypes as C
+
+    rank, world, local = dist_env()
+    import __graft_entry__ as g
+
+    g.build()
+    from numpyro_b200 import _lib
+    from numpyro_b200.infer import MCMC, NUTS
+    from numpyro_b200.random import PRNGKey
+
+    lib = _lib.lib()
+    _lib.require_device()
+    _lib.check(lib.b200mc_set_device(local))
+    model, margs, mkw, kkw, chains, desc = make_workload(args.workload, args.chains)
+    kern = NUTS(model, **kkw)
+    mc = MCMC(kern, num_warmup=args.adapt, num_samples=args.transitions, num_chains=chains,
+              chain_method="vectorized")
+    t0 = time.perf_counter()
+    mc.warmup(PRNGKey(0), *margs, **mkw)
+    adapt_s = time.perf_counter() - t0
+    T_ = args.transitions
+    ns_buf = _lib.DeviceArray((T_, chains), np.int32)
+    col = _lib.Collect(n_keep=T_, num_steps_dev=ns_buf.ptr)
+    ev0, ev1 = lib.b200mc_event_create(), lib.b200mc_event_create()
+    tot_ms, tot_g = 0.0, 0
+    launches0 = None
+    clocks = None
+    for i in range(args.warmup + args.steps):
+        if i == args.warmup:
+            launches0 = lib.b200mc_kernel_launches()
+            clocks = ClockSampler(local)
+        _lib.check(lib.b200mc_event_record(ev0, None))
+        _lib.check(lib.b200mc_sample(kern._handle, T_, 0, 1, C.byref(col), None))
+        _lib.check(lib.b200mc_event_record(ev1, None))
+        ms = C.c_float()
+        _lib.check(lib.b200mc_event_elapsed_ms(ev0, ev1, C.byref(ms)))
+        if i >= args.warmup:
+            tot_ms += float(ms.value)
+            tot_g += int(ns_buf.numpy().sum())
+    clk = clocks.stop()
+    line = {"metric": METRIC, "value": tot_g / (tot_ms * 1e-3), "unit": UNIT, "n_gpus": 1,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": desc, "chains": chains, "transitions_per_step": T_,
+                       "adapt_transitions_untimed": args.adapt, **{k: str(v) for k, v in kkw.items()}},
+            "gpu_launches": int(lib.b200mc_kernel_launches() - launches0), "clocks": clk,
+            "adapt_seconds": adapt_s, "mean_tree_size": tot_g / (args.steps * T_ * chains)}
+    print(json.dumps(line))
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--workload", default="logistic",
+                    choices=["logistic", "eight_schools", "sv", "horseshoe"])
+    ap.add_argument("--chains", type=int, default=0)
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
@@ -385,6 +471,8 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload != "logistic":
+        return run_chain_workload(args)
     return run_own(args)
 
 

@@ -36,6 +36,7 @@ typedef struct {
   /* data, device pointers:
    *   LOGISTIC      data0 = X[N][ncols] float32 row-major, data1 = labels[N] uint8
    *   EIGHT_SCHOOLS data0 = y[N] float32, data1 = sigma[N] float32
+   *   HORSESHOE     data0 = X[N][ncols] float32 row-major, data1 = Y[N] float32
    *   SV            data0 = returns[N] float32, data1 = NULL                         */
   int N;
   int ncols;
@@ -45,7 +46,7 @@ typedef struct {
   float step_size;
   int adapt_step_size;
   int adapt_mass_matrix;
-  int dense_mass;               /* must be 0 in this round: raises otherwise */
+  int dense_mass;               /* 1: full mass matrix; inverse_mass_matrix_dev is then [D][D] */
   int regularize_mass_matrix;
   float target_accept_prob;
   int max_tree_depth_warmup;    /* max_tree_depth=(d1, d2): hmc.py:299-303 */
@@ -56,7 +57,9 @@ typedef struct {
   int num_steps;                /* HMC: <= 0 means None */
   int threefry_partitionable;   /* jax_threefry_partitionable: 1 = JAX >= 0.5 default */
   float init_radius;            /* init_to_uniform(radius=2) (initialization.py:95) */
-  const float* inverse_mass_matrix_dev; /* [D] diagonal or NULL (identity) */
+  const float* inverse_mass_matrix_dev; /* [D] diagonal ([D][D] if dense_mass) or NULL (identity) */
+  int find_heuristic_step_size; /* hmc_util.py:314-384 at init and at every window end */
+  int likelihood;               /* HORSESHOE: 0 Bernoulli(logits), 1 Normal(mean, prec_obs^-1/2) */
 } b200mc_config;
 
 /* Scalar leaves of HMCState (hmc.py:31-48) and HMCAdaptState (hmc_util.py:18-30). */
@@ -88,7 +91,12 @@ enum {
   B200MC_VEC_INVERSE_MASS_MATRIX = 2,
   B200MC_VEC_MASS_MATRIX_SQRT = 3,
   B200MC_VEC_WELFORD_MEAN = 4,
-  B200MC_VEC_WELFORD_M2 = 5
+  B200MC_VEC_WELFORD_M2 = 5,
+  /* dense_mass only, each [num_chains][D][D] */
+  B200MC_MAT_INVERSE_MASS_MATRIX = 6,
+  B200MC_MAT_MASS_MATRIX_SQRT = 7,
+  B200MC_MAT_MASS_MATRIX_SQRT_INV = 8,
+  B200MC_MAT_WELFORD_M2 = 9
 };
 
 /* Collection buffers of fori_collect (numpyro/util.py:277-407): [n_keep][num_chains][...]

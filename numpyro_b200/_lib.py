@@ -27,7 +27,8 @@ class Config(C.Structure):
         ("num_warmup", C.c_int), ("has_trajectory_length", C.c_int),
         ("trajectory_length", C.c_float), ("num_steps", C.c_int),
         ("threefry_partitionable", C.c_int), ("init_radius", C.c_float),
-        ("inverse_mass_matrix_dev", C.c_void_p),
+        ("inverse_mass_matrix_dev", C.c_void_p), ("find_heuristic_step_size", C.c_int),
+        ("likelihood", C.c_int),
     ]
 
 

@@ -52,6 +52,7 @@ struct b200mc_handle {
   unsigned* counters = nullptr;  // [0] arrive, [3] error
   unsigned long long* prof = nullptr;  // [kGlmProfSlots]
   int glm_reverse = 1;
+  float* dense_replicas = nullptr;
   bool initialized = false;
 };
 
@@ -117,9 +118,22 @@ static int family_sites(const b200mc_config& c, SamplerParams& P, int& D) {
       P.site_off[1] = 1;       P.site_size[1] = c.N;
       P.site_off[2] = 0;       P.site_size[2] = 1;
       return 0;
+    case B200MC_HORSESHOE: {
+      // trace: lambdas, tau, unscaled_betas(, prec_obs); sorted: lambdas(, prec_obs), tau,
+      // unscaled_betas
+      const int Dh = c.ncols, nrm = c.likelihood == 1 ? 1 : 0;
+      if (Dh < 1) return fail("horseshoe: ncols must be >= 1");
+      D = 2 * Dh + 1 + nrm;
+      P.nsites = 3 + nrm;
+      P.site_off[0] = 0;            P.site_size[0] = Dh;
+      P.site_off[1] = Dh + nrm;     P.site_size[1] = 1;
+      P.site_off[2] = Dh + nrm + 1; P.site_size[2] = Dh;
+      if (nrm) { P.site_off[3] = Dh; P.site_size[3] = 1; }
+      return 0;
+    }
     default:
-      return fail("model family %d is not a registered potential family "
-                  "(logistic=0, eight_schools=1, stochastic_volatility=3); no fallback", c.family);
+      return fail("model family %d is not a registered potential family (logistic=0, "
+                  "eight_schools=1, horseshoe=2, stochastic_volatility=3); no fallback", c.family);
   }
 }
 
@@ -130,6 +144,7 @@ extern "C" void b200mc_destroy(b200mc_handle* h) {
   cudaFree(h->cv.z); cudaFree(h->cv.z_grad); cudaFree(h->cv.inverse_mass_matrix);
   cudaFree(h->cv.mass_matrix_sqrt); cudaFree(h->cv.welford_mean); cudaFree(h->cv.welford_m2);
   cudaFree(h->work); cudaFree(h->partials); cudaFree(h->counters); cudaFree(h->prof); cudaFree(h->glm_xt);
+  cudaFree(h->cv.dense); cudaFree(h->dense_replicas); cudaFree(h->M.scratch);
   delete h;
 }
 
@@ -140,7 +155,6 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   *out = nullptr;
   const b200mc_config& c = *cfg;
   if (c.num_chains < 1) return fail("num_chains must be >= 1");
-  if (c.dense_mass) return fail("dense_mass=True is not implemented yet (diagonal mass only)");
   if (c.algo != B200MC_NUTS && c.algo != B200MC_HMC)
     return fail("`algo` must be one of `HMC` or `NUTS`.");
   if (c.algo == B200MC_HMC && c.num_steps <= 0 && !c.has_trajectory_length)
@@ -176,6 +190,9 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   P.trajectory_length = c.trajectory_length;
   P.fixed_num_steps = c.num_steps;
   P.max_delta_energy = 1000.0f;  // hmc.py:188
+  P.dense_mass = c.dense_mass ? 1 : 0;
+  P.find_heuristic = c.find_heuristic_step_size ? 1 : 0;
+  P.factor_at_init = (c.dense_mass && c.inverse_mass_matrix_dev) ? 1 : 0;
   P.init_radius = c.init_radius > 0.f ? c.init_radius : 2.0f;
   auto sch = adaptation_schedule(c.num_warmup);
   if ((int)sch.size() > kMaxWindows) { delete h; return fail("too many adaptation windows"); }
@@ -187,6 +204,9 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   h->M.D = D;
   h->M.a = (const float*)c.data0_dev;
   h->M.b = (const float*)c.data1_dev;
+  h->M.ncols = c.ncols;
+  h->M.likelihood = c.likelihood;
+  h->M.scratch = nullptr;
 
   const size_t vec_bytes = (size_t)C * D * sizeof(float);
   auto alloc = [&](void** p, size_t bytes) {
@@ -210,6 +230,7 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   ACK(alloc((void**)&h->cv.mass_matrix_sqrt, vec_bytes));
   ACK(alloc((void**)&h->cv.welford_mean, vec_bytes));
   ACK(alloc((void**)&h->cv.welford_m2, vec_bytes));
+  if (c.dense_mass) ACK(alloc((void**)&h->cv.dense, sizeof(float) * 4 * (size_t)C * D * D));
 
   const int nslots = num_slots(P.max_depth);
   if (c.family == B200MC_LOGISTIC) {
@@ -246,9 +267,16 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
     ACK(alloc((void**)&h->partials, sizeof(float) * 2 * (size_t)ctas * glm_partial_stride(D)));
     ACK(alloc((void**)&h->counters, sizeof(unsigned) * 8));
     ACK(alloc((void**)&h->prof, sizeof(unsigned long long) * kGlmProfSlots));
+    if (c.dense_mass && ctas > 1)
+      ACK(alloc((void**)&h->dense_replicas, sizeof(float) * 4 * (size_t)(ctas - 1) * D * D));
     if (const char* e = getenv("B200MC_GLM_REVERSE")) h->glm_reverse = atoi(e);
   } else {
-    h->mode = (D <= 32) ? 0 : (D <= 512 ? 1 : 2);
+    if (c.family == B200MC_HORSESHOE) {
+      if (!c.data1_dev) { b200mc_destroy(h); return fail("horseshoe: Y missing"); }
+      ACK(alloc((void**)&h->M.scratch, sizeof(float) * (size_t)C * c.N));
+    }
+    // thread per chain (tiny D, diagonal mass), warp per chain, CTA per chain
+    h->mode = (D <= 32 && !c.dense_mass) ? 0 : (D <= 512 ? 1 : 2);
     h->c_pad = (C + 31) / 32 * 32;
     const size_t chains = (h->mode == 0) ? (size_t)h->c_pad : (size_t)C;
     ACK(alloc((void**)&h->work, sizeof(float) * chains * nslots * D));
@@ -273,6 +301,20 @@ __global__ void init_vectors_kernel(ChainVectors cv, const float* imm_in, const 
     cv.welford_m2[i] = 0.f;
     cv.z[i] = z_in ? z_in[i] : 0.f;
     cv.z_grad[i] = 0.f;
+  }
+}
+
+// _initialize_mass_matrix, dense branch (hmc_util.py:488-507): identity, or the user's M^-1
+// in slot 0 (its factors are computed on device by Sampler::factor_dense in init_kernel)
+__global__ void init_dense_kernel(float* dense, const float* imm_in, int C, int D) {
+  const long dd = (long)D * D, n = (long)C * 4 * dd;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+    const long e = i % dd;
+    const int which = (int)((i / dd) % 4), r = (int)(e / D), col = (int)(e % D);
+    float v = 0.f;
+    if (which == 0) v = imm_in ? imm_in[e] : (r == col ? 1.f : 0.f);
+    else if (which < 3) v = (r == col) ? 1.f : 0.f;
+    dense[i] = v;
   }
 }
 
@@ -331,6 +373,7 @@ static int launch_glm(b200mc_handle* h, const CollectSpec& col, const uint32_t* 
   L.arrive = h->counters + 0;
   L.error = (int*)(h->counters + 3);
   L.prof = h->prof;
+  L.dense_replicas = h->dense_replicas;
   L.init_keys = keys; L.user_init = user_init; L.chain = chain; L.C = h->C;
   L.eval_z = eval_z; L.eval_U = eval_U; L.eval_grad = eval_grad;
   CK(cudaMemsetAsync(h->counters, 0, sizeof(unsigned) * 3, st));  // arrive
@@ -345,9 +388,13 @@ extern "C" int b200mc_init(b200mc_handle* h, const uint32_t* keys_dev, const flo
                            void* stream) {
   if (!h || !keys_dev) return fail("null argument");
   cudaStream_t st = (cudaStream_t)stream;
-  init_vectors_kernel<<<148, 256, 0, st>>>(h->cv, h->cfg.inverse_mass_matrix_dev, init_z_dev, h->C,
-                                           h->D);
+  init_vectors_kernel<<<148, 256, 0, st>>>(
+      h->cv, h->cfg.dense_mass ? nullptr : h->cfg.inverse_mass_matrix_dev, init_z_dev, h->C, h->D);
   g_launches++;
+  if (h->cfg.dense_mass) {
+    init_dense_kernel<<<148, 256, 0, st>>>(h->cv.dense, h->cfg.inverse_mass_matrix_dev, h->C, h->D);
+    g_launches++;
+  }
   CK(cudaGetLastError());
   CK(cudaMemsetAsync(h->cs, 0, sizeof(ChainScalars) * h->C, st));
   const CollectSpec col = make_collect(0, 0, 1, nullptr);
@@ -390,11 +437,17 @@ extern "C" int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, i
         return 1;
     return 0;
   }
-  if (h->mode == 0) chain_potential_kernel<0><<<(n + 63) / 64, 64, 0, st>>>(h->M, z_dev, U_dev, grad_dev, n);
-  else if (h->mode == 1) chain_potential_kernel<1><<<(n + 3) / 4, 128, 0, st>>>(h->M, z_dev, U_dev, grad_dev, n);
-  else chain_potential_kernel<2><<<n, 256, 0, st>>>(h->M, z_dev, U_dev, grad_dev, n);
-  g_launches++;
-  CK(cudaGetLastError());
+  // per-chain scratch (horseshoe residuals) is sized for num_chains: evaluate in batches
+  for (int i0 = 0; i0 < n; i0 += h->C) {
+    const int m = (n - i0 < h->C) ? n - i0 : h->C;
+    const float* zp = z_dev + (long)i0 * h->D;
+    float* gp = grad_dev + (long)i0 * h->D;
+    if (h->mode == 0) chain_potential_kernel<0><<<(m + 63) / 64, 64, 0, st>>>(h->M, zp, U_dev + i0, gp, m);
+    else if (h->mode == 1) chain_potential_kernel<1><<<(m + 3) / 4, 128, 0, st>>>(h->M, zp, U_dev + i0, gp, m);
+    else chain_potential_kernel<2><<<m, 256, 0, st>>>(h->M, zp, U_dev + i0, gp, m);
+    g_launches++;
+    CK(cudaGetLastError());
+  }
   return 0;
 }
 
@@ -441,7 +494,21 @@ static float* vec_ptr(b200mc_handle* h, int which) {
   }
 }
 
+// dense matrices are stored [C][4][D][D]; the ABI exposes each kind as [C][D][D]
+static int copy_matrix(b200mc_handle* h, int which, float* user, bool to_user, cudaStream_t st) {
+  if (!h->cv.dense) return fail("matrix state exists only with dense_mass");
+  const size_t dd = (size_t)h->D * h->D;
+  float* base = h->cv.dense + (size_t)(which - B200MC_MAT_INVERSE_MASS_MATRIX) * dd;
+  if (to_user)
+    CK(cudaMemcpy2DAsync(user, dd * 4, base, 4 * dd * 4, dd * 4, h->C, cudaMemcpyDeviceToDevice, st));
+  else
+    CK(cudaMemcpy2DAsync(base, 4 * dd * 4, user, dd * 4, dd * 4, h->C, cudaMemcpyDeviceToDevice, st));
+  return 0;
+}
+
 extern "C" int b200mc_get_vector(b200mc_handle* h, int which, float* out_dev, void* stream) {
+  if (h && out_dev && which >= B200MC_MAT_INVERSE_MASS_MATRIX && which <= B200MC_MAT_WELFORD_M2)
+    return copy_matrix(h, which, out_dev, true, (cudaStream_t)stream);
   float* p = h ? vec_ptr(h, which) : nullptr;
   if (!p || !out_dev) return fail("bad argument");
   CK(cudaMemcpyAsync(out_dev, p, sizeof(float) * (size_t)h->C * h->D, cudaMemcpyDeviceToDevice,
@@ -450,6 +517,8 @@ extern "C" int b200mc_get_vector(b200mc_handle* h, int which, float* out_dev, vo
 }
 
 extern "C" int b200mc_set_vector(b200mc_handle* h, int which, const float* in_dev, void* stream) {
+  if (h && in_dev && which >= B200MC_MAT_INVERSE_MASS_MATRIX && which <= B200MC_MAT_WELFORD_M2)
+    return copy_matrix(h, which, const_cast<float*>(in_dev), false, (cudaStream_t)stream);
   float* p = h ? vec_ptr(h, which) : nullptr;
   if (!p || !in_dev) return fail("bad argument");
   CK(cudaMemcpyAsync(p, in_dev, sizeof(float) * (size_t)h->C * h->D, cudaMemcpyDeviceToDevice,

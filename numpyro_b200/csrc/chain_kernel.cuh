@@ -55,7 +55,7 @@ __global__ void chain_kernel(const __grid_constant__ ChainLaunch L) {
     else
       r = S.begin_sampling();
     while (r == NEED_GRAD) {
-      const float U = model_potential(L.M, g, S.v(LZ), es, S.v(LG), es);
+      const float U = model_potential(L.M, g, S.v(LZ), es, S.v(LG), es, chain);
       r = S.advance(U);
     }
     S.store(L.cs, L.cv);
@@ -76,7 +76,7 @@ __global__ void chain_potential_kernel(ModelData M, const float* z, float* U, fl
   else chain = (MODE == 1) ? (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) : blockIdx.x;
   if (chain >= C) return;
   auto run = [&](auto g) {
-    const float u = model_potential(M, g, z + (long)chain * D, 1, grad + (long)chain * D, 1);
+    const float u = model_potential(M, g, z + (long)chain * D, 1, grad + (long)chain * D, 1, chain);
     if (g.lane() == 0) U[chain] = u;
   };
   if (MODE == 0) run(ThreadGroup{});

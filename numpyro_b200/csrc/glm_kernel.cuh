@@ -61,6 +61,7 @@ struct GlmLaunch {
   unsigned* arrive;      // monotonic arrival counter, zeroed by the host before the launch
   int* error;            // set to 1 on a spin time-out
   unsigned long long* prof;  // [kGlmProfSlots] cycle counters of CTA 0 (or null)
+  float* dense_replicas;     // dense mass: private [nCTA-1][4][D][D] copies for CTAs > 0
   const uint32_t* init_keys;  // [C][2] or null
   int user_init;
   int chain;             // which chain of cs/cv this launch advances
@@ -400,6 +401,18 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
       for (int d = lane; d < D; d += 32) S.v(LZ)[d] = L.eval_z[d];
       sres = NEED_GRAD;
     } else {
+      if (L.P.dense_mass) {
+        // replicas must not share read-modify-write state: CTA 0 owns the chain's matrices,
+        // every other CTA works on a private copy taken at launch
+        float* canon = L.cv.dense + (long)L.chain * 4 * D * D;
+        if (cta == 0) {
+          S.dn = canon;
+        } else {
+          S.dn = L.dense_replicas + (long)(cta - 1) * 4 * D * D;
+          for (int i = lane; i < 4 * D * D; i += 32) S.dn[i] = canon[i];
+          __syncwarp();
+        }
+      }
       S.load(L.cs, L.cv);
       if (L.init_keys)
         sres = S.begin_init(Key{L.init_keys[2 * L.chain], L.init_keys[2 * L.chain + 1]},

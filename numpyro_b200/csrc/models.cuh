@@ -20,8 +20,11 @@ struct ModelData {
   int family;
   int N;           // rows / schools / time steps
   int D;           // flat unconstrained dimension
-  const float* a;  // eight schools: y[J];    SV: returns[T]
-  const float* b;  // eight schools: sigma[J]
+  const float* a;  // eight schools: y[J];    SV: returns[T];  horseshoe: X[N][ncols] row-major
+  const float* b;  // eight schools: sigma[J];                 horseshoe: Y[N] (float)
+  int ncols;       // horseshoe: number of covariates
+  int likelihood;  // horseshoe: 0 Bernoulli(logits), 1 Normal(mean, prec_obs^-1/2)
+  float* scratch;  // horseshoe: [C][N] residuals dU/dmean
 };
 
 #define B200MC_LOG_SQRT_2PI 0.9189385332046727f
@@ -124,10 +127,102 @@ __device__ float sv_potential(const ModelData& M, const G& g, const float* z, in
   return -lp;
 }
 
+// Horseshoe regression (examples/horseshoe_regression.py:37-78).
+// z = [log lambdas[Dh], (log prec_obs,) log tau, unscaled_betas[Dh]] (sorted site names).
+// HalfCauchy(1): continuous.py:703-723; Gamma(3, 1): :515-525; Normal: :2203-2207; Bernoulli
+// logits: discrete.py:137-139 + distributions/util.py:295-298; exp transform log|J| = z.
+// CUDA-core version: X is read twice per evaluation (X beta, then X^T residual) from L2.
+template <class G>
+__device__ float horseshoe_potential(const ModelData& M, const G& g, const float* z, int zs,
+                                     float* grad, int gs, int chain) {
+  const int Dh = M.ncols, N = M.N;
+  const bool normal = M.likelihood == 1;
+  const int o_l = 0, o_p = Dh, o_t = Dh + (normal ? 1 : 0), o_u = o_t + 1;
+  const float c_hc = 0.6931471805599453f - 1.1447298858494002f;  // log 2 - log pi
+  g.sync();
+  const float tu = z[o_t * zs];
+  const float tau = expf(tu);
+  float pu = 0.f, prec = 1.f;
+  if (normal) {
+    pu = z[o_p * zs];
+    prec = expf(pu);
+  }
+  float lp = 0.f;
+  for (int d = g.lane(); d < Dh; d += g.size()) {  // priors; beta parked in grad[o_u + d]
+    const float lu = z[(o_l + d) * zs], ub = z[(o_u + d) * zs];
+    const float lam = expf(lu);
+    lp += (c_hc - log1pf(lam * lam)) + lu;
+    lp += -0.5f * ub * ub - B200MC_LOG_SQRT_2PI;
+    grad[(o_u + d) * gs] = (tau * lam) * ub;
+  }
+  g.sync();
+  float* res = M.scratch + (long)chain * N;
+  float ll = 0.f, ss = 0.f;
+  for (int i = g.lane(); i < N; i += g.size()) {  // mean_i = x_i . beta, dU/dmean_i
+    const float* x = M.a + (long)i * Dh;
+    float m0 = 0.f, m1 = 0.f;
+    int d = 0;
+    for (; d + 1 < Dh; d += 2) {
+      m0 = fmaf(x[d], grad[(o_u + d) * gs], m0);
+      m1 = fmaf(x[d + 1], grad[(o_u + d + 1) * gs], m1);
+    }
+    if (d < Dh) m0 = fmaf(x[d], grad[(o_u + d) * gs], m0);
+    const float m = m0 + m1;
+    const float yv = M.b[i];
+    if (normal) {
+      const float r = yv - m;
+      ss += r * r;
+      res[i] = -(prec * r);
+    } else {
+      const float e = expf(-fabsf(m));
+      const float inv = 1.0f / (1.0f + e);
+      ll += (fmaxf(m, 0.f) + log1pf(e)) - m * yv;
+      res[i] = ((m >= 0.f) ? inv : e * inv) - yv;
+    }
+  }
+  g.sync();
+  float sbb = 0.f;
+  for (int d = g.lane(); d < Dh; d += g.size()) {  // dU/dbeta_d = sum_i X[i][d] res_i
+    float a0 = 0.f, a1 = 0.f;
+    int i = 0;
+    for (; i + 1 < N; i += 2) {
+      a0 = fmaf(M.a[(long)i * Dh + d], res[i], a0);
+      a1 = fmaf(M.a[(long)(i + 1) * Dh + d], res[i + 1], a1);
+    }
+    if (i < N) a0 = fmaf(M.a[(long)i * Dh + d], res[i], a0);
+    const float db = a0 + a1;
+    const float beta = grad[(o_u + d) * gs];
+    const float lu = z[(o_l + d) * zs], ub = z[(o_u + d) * zs];
+    const float lam = expf(lu);
+    const float l2 = lam * lam;
+    grad[(o_l + d) * gs] = (2.0f * l2 / (1.0f + l2) - 1.0f) + db * beta;
+    grad[(o_u + d) * gs] = ub + db * (tau * lam);
+    sbb += db * beta;
+  }
+  g.sum2(lp, sbb);
+  g.sum2(ll, ss);
+  lp += (c_hc - log1pf(tau * tau)) + tu;
+  const float fN = (float)N;
+  if (normal) {
+    lp += (2.0f * pu - prec - 0.6931471805599453f) + pu;  // Gamma(3,1): lgamma(3) = log 2
+    lp += -0.5f * prec * ss - fN * B200MC_LOG_SQRT_2PI + 0.5f * fN * pu;
+  } else {
+    lp -= ll;
+  }
+  if (g.lane() == 0) {
+    const float t2 = tau * tau;
+    grad[o_t * gs] = (2.0f * t2 / (1.0f + t2) - 1.0f) + sbb;
+    if (normal) grad[o_p * gs] = -(3.0f - prec) + 0.5f * prec * ss - 0.5f * fN;
+  }
+  g.sync();
+  return -lp;
+}
+
 template <class G>
 __device__ __forceinline__ float model_potential(const ModelData& M, const G& g, const float* z,
-                                                 int zs, float* grad, int gs) {
+                                                 int zs, float* grad, int gs, int chain) {
   if (M.family == FAM_EIGHT_SCHOOLS) return eight_schools_potential(M, g, z, zs, grad, gs);
+  if (M.family == FAM_HORSESHOE) return horseshoe_potential(M, g, z, zs, grad, gs, chain);
   return sv_potential(M, g, z, zs, grad, gs);
 }
 

@@ -45,11 +45,12 @@ enum Slot {
   LZ, LR, LG,                                              // leaf under construction; LZ = point to evaluate
   SZ_PROP, SG_PROP, S_RSUM,                                // subtree proposal / momentum sum
   IMM, MSQRT, WMEAN, WM2,                                  // adaptation vectors
-  CKPT0                                                    // r_ckpts[i] = CKPT0+2i, r_sum_ckpts[i] = CKPT0+2i+1
+  LV, V_LEFT, V_RIGHT,                                     // dense mass: cached M^-1 r of LR, R_LEFT, R_RIGHT
+  CKPT0                                                    // r_ckpts[i], r_sum_ckpts[i], M^-1 r_ckpts[i] = CKPT0+3i+{0,1,2}
 };
-__host__ __device__ inline int num_slots(int max_depth) { return CKPT0 + 2 * max_depth; }
+__host__ __device__ inline int num_slots(int max_depth) { return CKPT0 + 3 * max_depth; }
 
-enum Phase { PH_INIT = 0, PH_TREE, PH_HMC, PH_IDLE, PH_FAIL };
+enum Phase { PH_INIT = 0, PH_TREE, PH_HMC, PH_IDLE, PH_FAIL, PH_FRSS };
 enum StepResult { NEED_GRAD = 0, FINISHED = 1 };
 
 __device__ __forceinline__ float logaddexp_f32(float a, float b) {
@@ -68,6 +69,8 @@ struct Sampler {
   int es;              // floats between elements of one vector
   int D;
   bool part;
+  bool dense;
+  float* dn;           // dense mass matrices [4][D][D] (null unless dense)
 
   bool writer;         // false: a replica that advances the same chain but writes nothing
 #ifdef B200MC_SAMPLER_PROF
@@ -103,10 +106,18 @@ struct Sampler {
   // init search
   Key init_key;
   int user_init;
+  // find_reasonable_step_size (hmc_util.py:314-384)
+  float fr_step, fr_e_cur;
+  int fr_last_dir, fr_dir, fr_cont;
+  Key fr_key;
+  Key init_mom_key;
 
   __device__ __forceinline__ float* v(int slot) const { return w + (long)slot * slot_stride; }
-  __device__ __forceinline__ float* ckpt_r(int i) const { return v(CKPT0 + 2 * i); }
-  __device__ __forceinline__ float* ckpt_rs(int i) const { return v(CKPT0 + 2 * i + 1); }
+  __device__ __forceinline__ float* ckpt_r(int i) const { return v(CKPT0 + 3 * i); }
+  __device__ __forceinline__ float* ckpt_rs(int i) const { return v(CKPT0 + 3 * i + 1); }
+  __device__ __forceinline__ float* ckpt_v(int i) const { return v(CKPT0 + 3 * i + 2); }
+  // dense mass: this chain's (or this replica's) four D x D matrices in global memory
+  __device__ __forceinline__ float* mat(int which) const { return dn + (long)which * D * D; }
 
 #define B200MC_FOR_D for (int d = g.lane(); d < D; d += g.size())
 
@@ -121,6 +132,8 @@ struct Sampler {
                         int chain_, int C_, const CollectSpec* c) {
     P = p; g = grp; w = work; slot_stride = sstride; es = estride; D = p->D;
     part = p->partitionable != 0;
+    dense = p->dense_mass != 0;
+    dn = nullptr;
     chain = chain_; C = C_; col = c;
     writer = true;
     iters_left = c ? c->num_iters : 0;
@@ -131,6 +144,7 @@ struct Sampler {
 
   __device__ void load(const ChainScalars* cs, const ChainVectors& cv) {
     s = cs[chain];
+    if (dense && !dn) dn = cv.dense + (long)chain * 4 * D * D;
     const long o = (long)chain * D;
     float *zp = v(Z_PROP), *gp = v(G_PROP), *im = v(IMM), *ms = v(MSQRT), *wm = v(WMEAN),
           *w2 = v(WM2);
@@ -161,20 +175,43 @@ struct Sampler {
   }
 
   // ------------------------------------------------------------------ small pieces
-  __device__ __forceinline__ float kinetic(int rslot) {  // 0.5 * dot(M^-1 r, r)
+  // dst = M src for a dense row-major D x D matrix (rows over lanes); `lower` restricts
+  // the sum to j <= i (triangular factor: the skipped terms are exact zeros).
+  __device__ void matvec(const float* M, const float* src, float* dst, bool lower = false) {
+    g.sync();  // src was written by its owner lanes
+    B200MC_FOR_D {
+      const float* row = M + (long)d * D;
+      const int n = lower ? d + 1 : D;
+      float a0 = 0.f, a1 = 0.f;
+      int j = 0;
+      for (; j + 1 < n; j += 2) {
+        a0 = fmaf(row[j], src[j * es], a0);
+        a1 = fmaf(row[j + 1], src[(j + 1) * es], a1);
+      }
+      if (j < n) a0 = fmaf(row[j], src[j * es], a0);
+      dst[d * es] = a0 + a1;
+    }
+    g.sync();
+  }
+
+  // 0.5 * dot(M^-1 r, r): hmc_util.py:1183-1200.  Dense: vslot holds the cached M^-1 r.
+  __device__ __forceinline__ float kinetic(int rslot, int vslot = -1) {
     const float *r = v(rslot), *im = v(IMM);
+    const float* vv_ = dense ? v(vslot) : nullptr;
     float acc = 0.f;
     B200MC_FOR_D {
       const float rv = r[d * es];
-      const float vv = im[d * es] * rv;
+      const float vv = dense ? vv_[d * es] : im[d * es] * rv;
       acc += vv * rv;
     }
     return 0.5f * g.sum(acc);
   }
 
-  // hmc_util.py:710-746 with r_sum already the (sub)tree sum
+  // hmc_util.py:710-746 with r_sum already the (sub)tree sum; vl_/vr_: cached M^-1 r (dense)
   __device__ __forceinline__ bool is_turning(const float* rl, const float* rr, const float* rsum,
-                                             const float* sub_a, const float* add_b) {
+                                             const float* sub_a, const float* add_b,
+                                             const float* vl_ = nullptr,
+                                             const float* vr_ = nullptr) {
     // s = rsum (- sub_a + add_b); s' = s - (rl + rr)/2; (M^-1 rl).s' <= 0 | (M^-1 rr).s' <= 0
     const float* im = v(IMM);
     float la = 0.f, ra = 0.f;
@@ -187,7 +224,8 @@ struct Sampler {
       const float l = rl[d * es], r = rr[d * es];
       const float h = (l + r) / 2.0f;
       const float sp = sv - h;
-      const float vl = im[d * es] * l, vr = im[d * es] * r;
+      const float vl = dense ? vl_[d * es] : im[d * es] * l;
+      const float vr = dense ? vr_[d * es] : im[d * es] * r;
       la += vl * sp;
       ra += vr * sp;
     }
@@ -195,11 +233,19 @@ struct Sampler {
     return (la <= 0.f) | (ra <= 0.f);
   }
 
-  // r = M^{1/2} eps, eps ~ N(0, I): hmc.py:92-110 (one dict block => split(key, 1))
-  __device__ __forceinline__ void draw_momentum(Key k_mom, int dst) {
+  // r = M^{1/2} eps, eps ~ N(0, I): hmc.py:92-110 (one dict block => split(key, 1)).
+  // use_imm: the reference's find_reasonable_step_size hands the INVERSE mass matrix to
+  // momentum_generator (hmc_util.py:362), so r = M^-1 eps there; restated as is.
+  __device__ __forceinline__ void draw_momentum(Key k_mom, int dst, bool use_imm = false) {
     const Key kb = split_at(k_mom, 1u, 0u, part);
     float* r = v(dst);
-    const float* ms = v(MSQRT);
+    if (dense) {
+      float* eps = v(LV);
+      B200MC_FOR_D eps[d * es] = normal_at(kb, (uint32_t)D, (uint32_t)d, part);
+      matvec(use_imm ? mat(0) : mat(1), eps, r, !use_imm);
+      return;
+    }
+    const float* ms = use_imm ? v(IMM) : v(MSQRT);
     B200MC_FOR_D {
       const float eps = normal_at(kb, (uint32_t)D, (uint32_t)d, part);
       r[d * es] = ms[d * es] * eps;
@@ -211,6 +257,19 @@ struct Sampler {
     float *z = v(LZ), *r = v(LR);
     const float *gr = v(LG), *im = v(IMM);
     const float hs = 0.5f * eps_s;
+    if (dense) {
+      B200MC_FOR_D {
+        const float t = hs * gr[d * es];
+        r[d * es] = r[d * es] - t;
+      }
+      matvec(mat(0), r, v(LV));
+      const float* lv = v(LV);
+      B200MC_FOR_D {
+        const float dz = eps_s * lv[d * es];
+        z[d * es] = z[d * es] + dz;
+      }
+      return;
+    }
     B200MC_FOR_D {
       const float t = hs * gr[d * es];
       const float rn = r[d * es] - t;
@@ -230,6 +289,7 @@ struct Sampler {
       const float t = hs * gr[d * es];
       r[d * es] = r[d * es] - t;
     }
+    if (dense) matvec(mat(0), r, v(LV));  // cached for the energy and the U-turn tests
   }
 
   // ------------------------------------------------------------------ warm-up adaptation
@@ -254,10 +314,63 @@ struct Sampler {
     s.ss_x_avg = e + f;
   }
 
-  // warmup_adapter.update_fn: hmc_util.py:637-705 (diagonal mass matrix)
-  __device__ void adapt(int t, float accept_prob) {
+  // (inverse_mass_matrix, mass_matrix_sqrt, mass_matrix_sqrt_inv) from a dense covariance in
+  // mat(0): hmc_util.py:224-233 (welford final) == :497-507 (_initialize_mass_matrix):
+  //   tril_inv     = swapaxes(cholesky(cov[::-1, ::-1])[::-1, ::-1])
+  //   cov_inv_sqrt = solve_triangular(tril_inv, identity, lower=True)
+  // mat(3) (the Welford m2 buffer) is the workspace and is left zeroed.
+  __device__ void factor_dense() {
+    float *cov = mat(0), *msq = mat(1), *tinv = mat(2), *W = mat(3);
+    const int n = D;
+    g.sync();
+    B200MC_FOR_D  // W = cov reversed in both axes
+      for (int j = 0; j < n; ++j) W[(long)d * n + j] = cov[(long)(n - 1 - d) * n + (n - 1 - j)];
+    g.sync();
+    for (int k = 0; k < n; ++k) {  // left-looking Cholesky, lower triangle, in place
+      float dk = W[(long)k * n + k];
+      for (int p = 0; p < k; ++p) {
+        const float l = W[(long)k * n + p];
+        dk -= l * l;
+      }
+      dk = sqrtf(dk);
+      g.sync();  // every lane has read row k before its diagonal changes
+      for (int i = k + g.lane(); i < n; i += g.size()) {
+        if (i == k) {
+          W[(long)k * n + k] = dk;
+        } else {
+          float a = W[(long)i * n + k];
+          for (int p = 0; p < k; ++p) a -= W[(long)i * n + p] * W[(long)k * n + p];
+          W[(long)i * n + k] = a / dk;
+        }
+      }
+      g.sync();
+    }
+    B200MC_FOR_D  // tril_inv[i][j] = Lc[n-1-j][n-1-i] for j <= i, else 0
+      for (int j = 0; j < n; ++j)
+        tinv[(long)d * n + j] = (j <= d) ? W[(long)(n - 1 - j) * n + (n - 1 - d)] : 0.f;
+    g.sync();
+    B200MC_FOR_D {  // column d of the inverse of the lower-triangular tril_inv
+      for (int i = 0; i < n; ++i) {
+        float a = (i == d) ? 1.f : 0.f;
+        if (i < d) {
+          msq[(long)i * n + d] = 0.f;
+          continue;
+        }
+        for (int p = d; p < i; ++p) a -= tinv[(long)i * n + p] * msq[(long)p * n + d];
+        msq[(long)i * n + d] = a / tinv[(long)i * n + i];
+      }
+    }
+    g.sync();
+    B200MC_FOR_D
+      for (int j = 0; j < n; ++j) W[(long)d * n + j] = 0.f;
+    g.sync();
+  }
+
+  // warmup_adapter.update_fn: hmc_util.py:637-705.  Returns true when a step-size search
+  // (find_heuristic_step_size) was started and the transition tail must wait for it.
+  __device__ bool adapt(int t, float accept_prob) {
     Key nk, kss;
-    split2(Key{s.adapt_key[0], s.adapt_key[1]}, part, nk, kss);  // :656 (k_ss unused here)
+    split2(Key{s.adapt_key[0], s.adapt_key[1]}, part, nk, kss);  // :656
     s.adapt_key[0] = nk.k0; s.adapt_key[1] = nk.k1;
     if (P->adapt_step_size) {
       da_update(P->target_accept_prob - accept_prob);
@@ -271,6 +384,7 @@ struct Sampler {
       const float n = (float)s.mm_n;
       const float* z = v(Z_PROP);
       float *mean = v(WMEAN), *m2 = v(WM2);
+      float *dpre_v = v(LV), *dpost_v = v(LR);  // free between transitions
       B200MC_FOR_D {
         const float x = z[d * es];
         const float dpre = x - mean[d * es];
@@ -278,8 +392,26 @@ struct Sampler {
         const float mnew = mean[d * es] + q;
         mean[d * es] = mnew;
         const float dpost = x - mnew;
-        const float pr = dpre * dpost;
-        m2[d * es] = m2[d * es] + pr;
+        if (dense) {
+          dpre_v[d * es] = dpre;
+          dpost_v[d * es] = dpost;
+        } else {
+          const float pr = dpre * dpost;
+          m2[d * es] = m2[d * es] + pr;
+        }
+      }
+      if (dense) {  // m2 += outer(delta_post, delta_pre), :195
+        g.sync();
+        float* M2 = mat(3);
+        B200MC_FOR_D {
+          const float dp = dpost_v[d * es];
+          float* row = M2 + (long)d * D;
+          for (int j = 0; j < D; ++j) {
+            const float pr = dp * dpre_v[j * es];
+            row[j] = row[j] + pr;
+          }
+        }
+        g.sync();
       }
     }
     const int wend = P->window_end[min(s.window_idx, P->num_windows - 1)];
@@ -291,21 +423,97 @@ struct Sampler {
         float *mean = v(WMEAN), *m2 = v(WM2), *im = v(IMM), *ms = v(MSQRT);
         const float scale = n / (n + 5.0f);
         const float shrink = 1e-3f * (5.0f / (n + 5.0f));
-        B200MC_FOR_D {
-          float cov = m2[d * es] / (n - 1.0f);
-          if (P->regularize_mass_matrix) {
-            const float sc = scale * cov;
-            cov = sc + shrink;
+        if (dense) {
+          float *cov = mat(0), *M2 = mat(3);
+          B200MC_FOR_D {
+            for (int j = 0; j < D; ++j) {
+              float c = M2[(long)d * D + j] / (n - 1.0f);
+              if (P->regularize_mass_matrix) {
+                c = scale * c;
+                if (j == d) c = c + shrink;
+              }
+              cov[(long)d * D + j] = c;
+            }
+            mean[d * es] = 0.f;
           }
-          im[d * es] = cov;
-          ms[d * es] = 1.0f / sqrtf(cov);
-          mean[d * es] = 0.f;
-          m2[d * es] = 0.f;
+          factor_dense();
+        } else {
+          B200MC_FOR_D {
+            float cov = m2[d * es] / (n - 1.0f);
+            if (P->regularize_mass_matrix) {
+              const float sc = scale * cov;
+              cov = sc + shrink;
+            }
+            im[d * es] = cov;
+            ms[d * es] = 1.0f / sqrtf(cov);
+            mean[d * es] = 0.f;
+            m2[d * es] = 0.f;
+          }
         }
         s.mm_n = 0;
       }
-      if (P->adapt_step_size) da_init(logf(10.0f) + logf(s.step_size));  // :624
+      if (P->adapt_step_size) {
+        if (P->find_heuristic) {
+          start_frss(kss, 1);
+          return true;
+        }
+        da_init(logf(10.0f) + logf(s.step_size));  // :624
+      }
     }
+    return false;
+  }
+
+  // ------------------------------------------------------------------ find_reasonable_step_size
+  // hmc_util.py:314-384 as a phase of the step machine: each try draws a fresh momentum,
+  // takes ONE leapfrog from the current position (Z_PROP, G_PROP) and doubles or halves the
+  // step size until the direction of change flips.  cont: 0 = called from init_kernel,
+  // 1 = called at a window end (the transition tail resumes afterwards).
+  __device__ void start_frss(Key key, int cont) {
+    fr_step = s.step_size;
+    fr_last_dir = 0;
+    fr_dir = 0;
+    fr_key = key;
+    fr_cont = cont;
+  }
+
+  // true: a leapfrog was started (NEED_GRAD); false: the search is over (s.step_size set)
+  __device__ bool frss_try() {
+    const bool not_small = (fr_step > FLT_MIN) || (fr_dir >= 0);   // :373
+    const bool not_large = (fr_step < FLT_MAX) || (fr_dir <= 0);   // :375
+    const bool go = not_small && not_large && ((fr_last_dir == 0) || (fr_dir == fr_last_dir));
+    if (!go) {
+      s.step_size = fr_step;
+      return false;
+    }
+    Key nk, k_mom;
+    split2(fr_key, part, nk, k_mom);  // :355
+    fr_key = nk;
+    const float scale = (fr_dir > 0) ? 2.0f : ((fr_dir < 0) ? 0.5f : 1.0f);
+    fr_step = scale * fr_step;
+    draw_momentum(k_mom, LR, true);
+    if (dense) matvec(mat(0), v(LR), v(LV));
+    fr_e_cur = kinetic(LR, LV) + s.potential_energy;
+    copy(LZ, Z_PROP); copy(LG, G_PROP);
+    eps_s = fr_step;
+    phase = PH_FRSS;
+    half_step();
+    return true;
+  }
+
+  __device__ StepResult advance_frss(float U) {
+    finish_leapfrog();
+    const float e_new = kinetic(LR, LV) + U;
+    const float dE = e_new - fr_e_cur;
+    const int dir_new = (-0.2231435513142097558f < -dE) ? 1 : -1;  // log(0.8); NaN -> -1
+    fr_last_dir = fr_dir;
+    fr_dir = dir_new;
+    if (frss_try()) return NEED_GRAD;
+    if (fr_cont == 0) {
+      da_init(logf(10.0f * s.step_size));  // :577
+      return after_init();
+    }
+    da_init(logf(10.0f) + logf(s.step_size));  // :624
+    return finish_transition_tail();
   }
 
   // ------------------------------------------------------------------ collection (util.py:334-351)
@@ -339,7 +547,16 @@ struct Sampler {
     s.num_steps = num_steps;
     s.diverging = div;
     const int t = s.i;
-    if (t < P->num_warmup) adapt(t, accept_prob);
+    if (t < P->num_warmup && adapt(t, accept_prob)) {
+      if (frss_try()) return NEED_GRAD;               // step-size search needs gradients
+      da_init(logf(10.0f) + logf(s.step_size));       // search ended at once
+    }
+    return finish_transition_tail();
+  }
+
+  __device__ StepResult finish_transition_tail() {
+    const int t = s.i;
+    const float accept_prob = s.accept_prob;
     const int itr = t + 1;
     const int n = (t < P->num_warmup) ? itr : itr - P->num_warmup;
     const float dm = accept_prob - s.mean_accept_prob;
@@ -376,7 +593,11 @@ struct Sampler {
         gl[d * es] = gg; gr[d * es] = gg;
       }
     }
-    e0 = s.potential_energy + kinetic(R_LEFT);
+    if (dense) {
+      matvec(mat(0), v(R_LEFT), v(V_LEFT));
+      copy(V_RIGHT, V_LEFT);
+    }
+    e0 = s.potential_energy + kinetic(R_LEFT, V_LEFT);
     depth = 0; weight = 0.f; turning = 0; diverging = 0; sum_acc = 0.f; nprop = 0;
     prop_pe = s.potential_energy;
     prop_energy = e0;
@@ -422,7 +643,7 @@ struct Sampler {
     // 1. finish the leapfrog, energy test (_build_basetree, hmc_util.py:863-875)
     B200MC_STAMP(t0_);
     finish_leapfrog();
-    const float e_new = U + kinetic(LR);
+    const float e_new = U + kinetic(LR, LV);
     float dE = e_new - e0;
     if (isnan(dE)) dE = INFINITY;
     const float wleaf = -dE;
@@ -470,10 +691,15 @@ struct Sampler {
         cr[d * es] = r[d * es];
         crs[d * es] = rs[d * es];
       }
+      if (dense) {
+        float* cv_ = ckpt_v(idx_max);
+        const float* lv = v(LV);
+        B200MC_FOR_D cv_[d * es] = lv[d * es];
+      }
     }
     bool sub_turning = false;
     for (int i = idx_max; i >= idx_min && !sub_turning; --i)
-      sub_turning = is_turning(ckpt_r(i), v(LR), v(S_RSUM), ckpt_rs(i), ckpt_r(i));
+      sub_turning = is_turning(ckpt_r(i), v(LR), v(S_RSUM), ckpt_rs(i), ckpt_r(i), ckpt_v(i), v(LV));
 
     // 4. keep extending the subtree? (_cond_fn, :999-1001)
     B200MC_STAMP(t3_);
@@ -489,8 +715,10 @@ struct Sampler {
     // 5. subtree finished: biased-progressive combine with the tree (:767-848, biased=True)
     if (going_right) {
       copy(Z_RIGHT, LZ); copy(R_RIGHT, LR); copy(G_RIGHT, LG);
+      if (dense) copy(V_RIGHT, LV);
     } else {
       copy(Z_LEFT, LZ); copy(R_LEFT, LR); copy(G_LEFT, LG);
+      if (dense) copy(V_LEFT, LV);
     }
     {
       float* rs = v(R_SUM);
@@ -500,7 +728,8 @@ struct Sampler {
     float p = expf(s_w - weight);
     p = (sub_turning || s_div) ? 0.0f : fminf(p, 1.0f);
     const bool tree_turning =
-        sub_turning | is_turning(v(R_LEFT), v(R_RIGHT), v(R_SUM), nullptr, nullptr);
+        sub_turning | is_turning(v(R_LEFT), v(R_RIGHT), v(R_SUM), nullptr, nullptr, v(V_LEFT),
+                                 v(V_RIGHT));
     if (uniform01(top_key, part) < p) {
       copy(Z_PROP, SZ_PROP); copy(G_PROP, SG_PROP);
       prop_pe = s_prop_pe; prop_energy = s_prop_energy;
@@ -541,7 +770,8 @@ struct Sampler {
     if (P->has_trajectory_length) eps = P->trajectory_length / (float)n;
     hmc_steps = n; hmc_done = 0;
     eps_s = eps;
-    energy_old = s.potential_energy + kinetic(LR);
+    if (dense) matvec(mat(0), v(LR), v(LV));
+    energy_old = s.potential_energy + kinetic(LR, LV);
     phase = PH_HMC;
     half_step();
     return NEED_GRAD;
@@ -554,7 +784,7 @@ struct Sampler {
       half_step();
       return NEED_GRAD;
     }
-    const float e_new = U + kinetic(LR);
+    const float e_new = U + kinetic(LR, LV);
     float dE = e_new - energy_old;
     if (isnan(dE)) dE = INFINITY;
     const float acc = fminf(expf(-dE), 1.0f);
@@ -621,33 +851,43 @@ struct Sampler {
     }
     copy(Z_PROP, LZ); copy(G_PROP, LG);
     s.potential_energy = U;
-    init_kernel();
-    if (iters_left <= 0) {
-      phase = PH_IDLE;
-      return FINISHED;
-    }
-    return start_transition();
+    return init_kernel();
   }
 
   // init_kernel (hmc.py:335-362) + warmup_adapter.init_fn (hmc_util.py:552-594); the
-  // caller has put the initial mass matrix into IMM / MSQRT.
-  __device__ void init_kernel() {
-    Key k_hmc, k_wa, k_mom, k_adapt, k_ss;
-    split3(Key{s.rng_key[0], s.rng_key[1]}, part, k_hmc, k_wa, k_mom);
+  // host has put the initial mass matrix into IMM / MSQRT (diagonal) or mat(0..2) (dense).
+  __device__ StepResult init_kernel() {
+    Key k_hmc, k_wa, k_adapt, k_ss;
+    split3(Key{s.rng_key[0], s.rng_key[1]}, part, k_hmc, k_wa, init_mom_key);
     split2(k_wa, part, k_adapt, k_ss);
     s.adapt_key[0] = k_adapt.k0; s.adapt_key[1] = k_adapt.k1;
+    s.rng_key[0] = k_hmc.k0; s.rng_key[1] = k_hmc.k1;
     s.step_size = P->init_step_size;
-    da_init(logf(10.0f * s.step_size));
     {
       float *mean = v(WMEAN), *m2 = v(WM2);
       B200MC_FOR_D { mean[d * es] = 0.f; m2[d * es] = 0.f; }
     }
     s.mm_n = 0;
     s.window_idx = 0;
-    draw_momentum(k_mom, LR);  // value discarded by the reference except for `energy`
-    s.energy = s.potential_energy + kinetic(LR);
-    s.rng_key[0] = k_hmc.k0; s.rng_key[1] = k_hmc.k1;
+    if (dense && P->factor_at_init) factor_dense();  // user-supplied dense M^-1, :497-507
+    if (P->adapt_step_size && P->find_heuristic) {   // :573-576
+      start_frss(k_ss, 0);
+      if (frss_try()) return NEED_GRAD;
+    }
+    da_init(logf(10.0f * s.step_size));
+    return after_init();
+  }
+
+  __device__ StepResult after_init() {
+    draw_momentum(init_mom_key, LR);  // value discarded by the reference except for `energy`
+    if (dense) matvec(mat(0), v(LR), v(LV));
+    s.energy = s.potential_energy + kinetic(LR, LV);
     s.i = 0; s.num_steps = 0; s.accept_prob = 0.f; s.mean_accept_prob = 0.f; s.diverging = 0;
+    if (iters_left <= 0) {
+      phase = PH_IDLE;
+      return FINISHED;
+    }
+    return start_transition();
   }
 
   // ------------------------------------------------------------------ driver interface
@@ -662,6 +902,7 @@ struct Sampler {
     if (phase == PH_TREE) return advance_tree(U);
     if (phase == PH_HMC) return advance_hmc(U);
     if (phase == PH_INIT) return advance_init(U);
+    if (phase == PH_FRSS) return advance_frss(U);
     return FINISHED;
   }
 #undef B200MC_FOR_D

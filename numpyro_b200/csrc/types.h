@@ -25,6 +25,9 @@ struct SamplerParams {
   float trajectory_length;
   int fixed_num_steps;  // HMC, <=0: none
   float max_delta_energy;  // hmc.py:188
+  int dense_mass;          // 1: full D x D mass matrix (hmc_util.py:439-515, 133-239)
+  int find_heuristic;      // find_heuristic_step_size (hmc_util.py:314-384)
+  int factor_at_init;      // dense M^-1 supplied by the user: factorise it in init_kernel
   int num_windows;
   int window_end[kMaxWindows];
   // init_to_uniform draws, sites in TRACE order (infer/util.py:423-432)
@@ -64,6 +67,9 @@ struct ChainVectors {
   float* mass_matrix_sqrt;
   float* welford_mean;
   float* welford_m2;
+  // dense_mass only: [C][4][D][D] = inverse_mass_matrix, mass_matrix_sqrt,
+  // mass_matrix_sqrt_inv, welford m2 (row-major); null otherwise
+  float* dense;
 };
 
 // Where collected draws go: [n_keep][C][...] (draw-major, like the reference's

@@ -28,6 +28,7 @@ HMCAdaptState = namedtuple(  # hmc_util.py:18-30
 
 _VEC = {"z": 0, "z_grad": 1, "inverse_mass_matrix": 2, "mass_matrix_sqrt": 3, "welford_mean": 4,
         "welford_m2": 5}
+_MAT = {"inverse_mass_matrix": 6, "mass_matrix_sqrt": 7, "mass_matrix_sqrt_inv": 8, "welford_m2": 9}
 EXTRA_FIELDS = ("potential_energy", "energy", "num_steps", "accept_prob", "mean_accept_prob",
                 "diverging", "adapt_state.step_size")
 
@@ -94,10 +95,12 @@ class HMC(MCMCKernel):
                 "numpyro_b200 has no generic autodiff fallback")
         if kinetic_fn is not None:
             raise NotImplementedError("only the euclidean kinetic energy is implemented")
-        if find_heuristic_step_size:
-            raise NotImplementedError("find_heuristic_step_size=True is not implemented yet")
-        if dense_mass is not False and dense_mass != []:
-            raise NotImplementedError("dense_mass / structured mass matrices are not implemented yet")
+        if not isinstance(dense_mass, bool):
+            if isinstance(dense_mass, (list, tuple)) and len(dense_mass) == 0:
+                dense_mass = False
+            else:
+                raise NotImplementedError(
+                    "structured (block) mass matrices are not implemented: dense_mass must be a bool")
         self._model = models.resolve(model)
         self._potential_fn = None
         self._kinetic_fn = None
@@ -186,8 +189,14 @@ class HMC(MCMCKernel):
                     raise NotImplementedError("block mass matrices are not implemented yet")
                 m = next(iter(m.values()))
             m = np.asarray(m, np.float32)
-            if m.ndim != 1 or m.shape[0] != bound.dim:
-                raise NotImplementedError("only a diagonal inverse_mass_matrix [D] is implemented")
+            want = (bound.dim, bound.dim) if self._dense_mass else (bound.dim,)
+            if m.shape != want:
+                if m.shape == (bound.dim,) and self._dense_mass:
+                    m = np.diag(m).astype(np.float32)  # hmc_util.py:492-493
+                elif m.shape == (bound.dim, bound.dim) and not self._dense_mass:
+                    raise ValueError("a 2-D inverse_mass_matrix needs dense_mass=True")
+                else:
+                    raise ValueError(f"inverse_mass_matrix must have shape {want}")
             imm = _lib.DeviceArray.from_numpy(m)
         depth = self._max_tree_depth
         depth = depth if isinstance(depth, tuple) else (depth, depth)
@@ -197,7 +206,10 @@ class HMC(MCMCKernel):
             data0_dev=d0.ptr, data1_dev=d1.ptr if d1 is not None else None,
             algo=0 if self._algo == "NUTS" else 1, step_size=float(self._step_size),
             adapt_step_size=int(bool(self._adapt_step_size)),
-            adapt_mass_matrix=int(bool(self._adapt_mass_matrix)), dense_mass=0,
+            adapt_mass_matrix=int(bool(self._adapt_mass_matrix)),
+            dense_mass=int(bool(self._dense_mass)),
+            find_heuristic_step_size=int(bool(self._find_heuristic_step_size)),
+            likelihood=int(getattr(bound, "likelihood", 0)),
             regularize_mass_matrix=int(bool(self._regularize_mass_matrix)),
             target_accept_prob=float(self._target_accept_prob),
             max_tree_depth_warmup=int(depth[0]), max_tree_depth_sample=int(depth[1]),
@@ -236,6 +248,11 @@ class HMC(MCMCKernel):
         for name, which in _VEC.items():
             _lib.check(lib.b200mc_get_vector(h, which, tmp.ptr, None))
             vec[name] = tmp.numpy()
+        if self._dense_mass:
+            mt = _lib.DeviceArray((Cn, D, D), np.float32)
+            for name, which in _MAT.items():
+                _lib.check(lib.b200mc_get_vector(h, which, mt.ptr, None))
+                vec[name] = mt.numpy()
         return sc, vec
 
     def _to_state(self, sc, vec):
@@ -243,11 +260,12 @@ class HMC(MCMCKernel):
         sq = (lambda a: a) if self._vectorized else (lambda a: a[0])
         block = tuple(sorted(k for k, _ in b.trace_sites))
         imm = vec["inverse_mass_matrix"]
+        sqrt_inv = vec["mass_matrix_sqrt_inv"] if self._dense_mass else np.sqrt(imm)
         adapt = HMCAdaptState(
             step_size=sq(sc["step_size"].copy()),
             inverse_mass_matrix={block: sq(imm)},
             mass_matrix_sqrt={block: sq(vec["mass_matrix_sqrt"])},
-            mass_matrix_sqrt_inv={block: sq(np.sqrt(imm))},
+            mass_matrix_sqrt_inv={block: sq(sqrt_inv)},
             ss_state=(sq(sc["ss_x_t"].copy()), sq(sc["ss_x_avg"].copy()), sq(sc["ss_g_avg"].copy()),
                       sq(sc["ss_t"].copy()), sq(sc["ss_prox_center"].copy())),
             mm_state={block: (sq(vec["welford_mean"]), sq(vec["welford_m2"]), sq(sc["mm_n"].copy()))},
@@ -296,9 +314,18 @@ class HMC(MCMCKernel):
                 "inverse_mass_matrix": a.inverse_mass_matrix[block],
                 "mass_matrix_sqrt": a.mass_matrix_sqrt[block],
                 "welford_mean": a.mm_state[block][0], "welford_m2": a.mm_state[block][1]}
+        mats = {}
+        if self._dense_mass:
+            for name in ("inverse_mass_matrix", "mass_matrix_sqrt", "welford_m2"):
+                mats[name] = vecs.pop(name)
+            mats["mass_matrix_sqrt_inv"] = a.mass_matrix_sqrt_inv[block]
         for name, val in vecs.items():
             d = _lib.DeviceArray.from_numpy(up(val).reshape(Cn, b.dim), np.float32)
             _lib.check(lib.b200mc_set_vector(h, _VEC[name], d.ptr, None))
+            _lib.check(lib.b200mc_stream_synchronize(None))
+        for name, val in mats.items():
+            d = _lib.DeviceArray.from_numpy(up(val).reshape(Cn, b.dim, b.dim), np.float32)
+            _lib.check(lib.b200mc_set_vector(h, _MAT[name], d.ptr, None))
             _lib.check(lib.b200mc_stream_synchronize(None))
         self._last_state = state
 

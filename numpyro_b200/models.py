@@ -20,8 +20,10 @@ class BoundModel:
     """A family bound to its data: what ``initialize_model`` returns in the reference
     (``ModelInfo``: site layout, postprocess_fn), minus the potential, which lives in CUDA."""
 
-    def __init__(self, family, name, N, ncols, data0, data1, trace_sites, constrain):
+    def __init__(self, family, name, N, ncols, data0, data1, trace_sites, constrain,
+                 likelihood=0):
         self.family, self.name, self.N, self.ncols = family, name, N, ncols
+        self.likelihood = likelihood
         self.data0, self.data1 = data0, data1
         self.trace_sites = tuple(trace_sites)  # (site, shape) in model trace order
         self._constrain = constrain
@@ -109,6 +111,31 @@ def _bind_sv(returns):
                       [("sigma", ()), ("s", (T,)), ("nu", ())], constrain)
 
 
+def _bind_horseshoe(likelihood):
+    def bind(X, Y):
+        X = np.ascontiguousarray(X, np.float32)
+        Y = np.ascontiguousarray(Y).astype(np.float32)
+        if X.ndim != 2 or Y.shape != (X.shape[0],):
+            raise ValueError("horseshoe regression expects X [N, D] and Y [N]")
+        Dh = X.shape[1]
+        sites = [("lambdas", (Dh,)), ("tau", (1,)), ("unscaled_betas", (Dh,))]
+        if likelihood == 1:
+            sites.append(("prec_obs", ()))
+
+        def constrain(z):
+            out = {"lambdas": np.exp(z["lambdas"]), "tau": np.exp(z["tau"]),
+                   "unscaled_betas": z["unscaled_betas"]}
+            if likelihood == 1:
+                out["prec_obs"] = np.exp(z["prec_obs"])
+            out["betas"] = out["tau"] * out["lambdas"] * out["unscaled_betas"]
+            return out
+
+        return BoundModel(HORSESHOE, "horseshoe", X.shape[0], Dh, X, Y, sites, constrain,
+                          likelihood=likelihood)
+
+    return bind
+
+
 logistic_regression = RegisteredModel(
     "logistic_regression", _bind_logistic,
     "coefs ~ Normal(0, 1)[D]; obs ~ Bernoulli(logits=data @ coefs)  (examples/covtype.py:66-71)")
@@ -119,8 +146,16 @@ stochastic_volatility = RegisteredModel(
     "stochastic_volatility", _bind_sv,
     "Random-walk stochastic volatility (examples/stochastic_volatility.py:57-65)")
 
+horseshoe_bernoulli = RegisteredModel(
+    "horseshoe_bernoulli", _bind_horseshoe(0),
+    "Horseshoe regression, Bernoulli likelihood (examples/horseshoe_regression.py:62-78)")
+horseshoe_normal = RegisteredModel(
+    "horseshoe_normal", _bind_horseshoe(1),
+    "Horseshoe regression, Normal likelihood (examples/horseshoe_regression.py:37-58)")
+
 REGISTRY = {m.__name__: m for m in (logistic_regression, eight_schools_noncentered,
-                                    stochastic_volatility)}
+                                    stochastic_volatility, horseshoe_bernoulli,
+                                    horseshoe_normal)}
 
 
 def resolve(model):

@@ -63,7 +63,8 @@ class HMCKernel:
     def __init__(self, family, algo="NUTS", step_size=1.0, inverse_mass_matrix=None,
                  adapt_step_size=True, adapt_mass_matrix=True, dense_mass=False,
                  target_accept_prob=0.8, num_steps=None, trajectory_length=2 * math.pi,
-                 max_tree_depth=10, regularize_mass_matrix=True, cfg=None):
+                 max_tree_depth=10, regularize_mass_matrix=True, find_heuristic_step_size=False,
+                 cfg=None):
         self.cfg = cfg if cfg is not None else Config()
         self.family = family
         self.algo = algo
@@ -78,6 +79,7 @@ class HMCKernel:
         self.max_treedepth = (max_tree_depth if isinstance(max_tree_depth, tuple)
                               else (max_tree_depth, max_tree_depth))
         self.regularize_mass_matrix = regularize_mass_matrix
+        self.find_heuristic_step_size = find_heuristic_step_size
         self.max_delta_energy = 1000.0
         self.num_grad_evals = 0
         self.trace = None  # optional list collecting every decision (tier-3 parity)
@@ -101,8 +103,14 @@ class HMCKernel:
             z = np.asarray(init_params, cfg.dtype)
             pe, z_grad = self.potential_fn(z)
         self.wa_steps = num_warmup
+        frss = None
+        if self.find_heuristic_step_size:  # hmc.py:319-323
+            def frss(step_size, imm, z_info, key):
+                return hu.find_reasonable_step_size(
+                    cfg, self.vv_update, lambda m, k: momentum_generator(cfg, m, k), step_size, imm,
+                    z_info, key)
         self.wa_init, self.wa_update = hu.warmup_adapter(
-            cfg, num_warmup, adapt_step_size=self.adapt_step_size,
+            cfg, num_warmup, find_reasonable_step_size=frss, adapt_step_size=self.adapt_step_size,
             adapt_mass_matrix=self.adapt_mass_matrix, dense_mass=self.dense_mass,
             target_accept_prob=self.target_accept_prob,
             regularize_mass_matrix=self.regularize_mass_matrix)

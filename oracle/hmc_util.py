@@ -161,6 +161,39 @@ def velocity_verlet(cfg, potential_fn):
     return init_fn, update_fn
 
 
+# ---------------------------------------------------------------- step-size heuristic
+def find_reasonable_step_size(cfg, vv_update, momentum_generator, init_step_size,
+                              inverse_mass_matrix, z_info, rng_key):
+    """hmc_util.py:314-384.  ``momentum_generator(inverse_mass_matrix, key)``: the reference
+    hands the INVERSE mass matrix to its momentum generator here (``:362``), restated as is.
+    ``z_info`` = IntegratorState with potential_energy and z_grad set."""
+    f = cfg.f
+    target = f(np.log(f(0.8)))
+    finfo = np.finfo(cfg.dtype)
+    z, _, potential_energy, z_grad = z_info
+    step_size, last_direction, direction = f(init_step_size), 0, 0
+
+    def cond(step_size, last_direction, direction):
+        not_small = (step_size > finfo.tiny) or (direction >= 0)
+        not_large = (step_size < finfo.max) or (direction <= 0)
+        return not_small and not_large and (last_direction == 0 or direction == last_direction)
+
+    while cond(step_size, last_direction, direction):
+        rng_key, rng_key_momentum = cfg.split(rng_key)
+        with np.errstate(all="ignore"):
+            step_size = f(f(2.0) ** direction) * step_size
+            r = momentum_generator(inverse_mass_matrix, rng_key_momentum)
+            new = vv_update(step_size, inverse_mass_matrix,
+                            IntegratorState(z, r, potential_energy, z_grad))
+            energy_current = f(kinetic_energy(cfg, inverse_mass_matrix, r) + f(potential_energy))
+            energy_new = f(kinetic_energy(cfg, inverse_mass_matrix, new.r)
+                           + f(new.potential_energy))
+            delta_energy = f(energy_new - energy_current)
+        direction_new = 1 if target < -delta_energy else -1
+        last_direction, direction = direction, direction_new
+    return step_size
+
+
 # ---------------------------------------------------------------- schedule
 def build_adaptation_schedule(num_steps):
     """hmc_util.py:387-436 (integer, host)."""

@@ -75,7 +75,8 @@ def test_constructor_contract(nb):
     with pytest.raises(NotImplementedError):
         NUTS(potential_fn=lambda z: 0.0)
     with pytest.raises(NotImplementedError):
-        NUTS(models.logistic_regression, dense_mass=True)
+        NUTS(models.logistic_regression, dense_mass=[("coefs",)])  # structured blocks
+    assert NUTS(models.logistic_regression, dense_mass=True, find_heuristic_step_size=True)._dense_mass
     k = NUTS(models.eight_schools_noncentered, step_size=1, max_tree_depth=(5, 10))
     assert k._step_size == 1.0 and isinstance(k._step_size, float)
     assert k.sample_field == "z" and k.default_fields == ("z", "diverging")
