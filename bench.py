@@ -250,10 +250,20 @@ def run_own(args):
 
     X, y = pinned_copy(X), pinned_copy(y)
     # one chain per GPU: chain keys as MCMC.run would split them for `world` chains
-    key = PRNGKey(1) if world == 1 else split(PRNGKey(1), world)[rank]
+    rows = args.sharding == "rows" and world > 1
+    key = PRNGKey(1) if (world == 1 or rows) else split(PRNGKey(1), world)[rank]
+    allgather = None
+    if rows:
+        # ONE chain over all GPUs: every rank keeps its row slice, sampler state replicated,
+        # D+1 partial sums exchanged per leapfrog over NVLink peer memory ("strong" scaling)
+        from numpyro_b200 import distributed as nbd
+
+        lo, hi = nbd.shard_bounds(N_ROWS, rank, world)
+        X, y = X[lo:hi], y[lo:hi]
+        allgather = nbd.allgather_bytes()
 
     # ---- untimed: bind data, adaptation warm-up (dual averaging + Welford windows)
-    kern = NUTS(models.logistic_regression)
+    kern = NUTS(models.logistic_regression).shard_rows(rank, world if rows else 1, allgather)
     mc = MCMC(kern, num_warmup=args.adapt, num_samples=args.transitions)
     t0 = time.perf_counter()
     mc.warmup(key, X, y, extra_fields=("num_steps",))
@@ -299,12 +309,13 @@ def run_own(args):
     if any(prof[8 + i] for i in range(8)):
         breakdown["sampler_sub"] = [float(prof[8 + i]) / passes for i in range(8)]
     total_ms = max_over_ranks(sum(step_ms))
-    total_grads = sum_over_ranks(float(sum(step_grads)))
+    total_grads = float(sum(step_grads)) if rows else sum_over_ranks(float(sum(step_grads)))
     value = total_grads / (total_ms * 1e-3)
 
     # roofline of the dominant (only) kernel, this rank: algorithmic bytes per launch / duration
     peak, peak_src = peaks()
-    my_gbs = ALGO_BYTES_PER_GRAD * sum(step_grads) / (sum(step_ms) * 1e-3) / 1e9
+    my_bytes = ALGO_BYTES_PER_GRAD / world if rows else ALGO_BYTES_PER_GRAD
+    my_gbs = my_bytes * sum(step_grads) / (sum(step_ms) * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": my_gbs, "peak": peak, "unit": "GB/s",
                 "frac": my_gbs / peak, "traffic": None, "peak_source": peak_src,
                 "kernel": "glm_kernel",
@@ -324,7 +335,8 @@ def run_own(args):
     for i in range(args.warmup + args.steps):
         t0 = time.perf_counter()
         k2 = NUTS(models.logistic_regression, step_size=adapted_step, inverse_mass_matrix=imm,
-                  adapt_step_size=False, adapt_mass_matrix=False)
+                  adapt_step_size=False, adapt_mass_matrix=False).shard_rows(
+                      rank, world if rows else 1, allgather)
         m2 = MCMC(k2, num_warmup=0, num_samples=T_)
         m2.run(key, X, y, init_params=z_last, extra_fields=("num_steps",))
         ns = m2.get_extra_fields()["num_steps"]
@@ -336,7 +348,7 @@ def run_own(args):
             e2e_s += dt
     barrier()
     e2e_s = max_over_ranks(e2e_s)
-    e2e_grads = sum_over_ranks(float(e2e_grads))
+    e2e_grads = float(e2e_grads) if rows else sum_over_ranks(float(e2e_grads))
     e2e = {"value": e2e_grads / e2e_s, "unit": UNIT,
            "h2d_bytes_per_step": int(X.nbytes + y.nbytes + 4 * N_COLS * 2 + 8),
            "d2h_bytes_per_step": int(T_ * (N_COLS * 4 + 4 + 4))}
@@ -355,11 +367,13 @@ def run_own(args):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "strong" if rows else "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
             "config": {"workload": "covtype-shape logistic NUTS N=581012 D=55 (configs[2])",
                        "chains_per_gpu": 1, "transitions_per_step": T_,
                        "adapt_transitions_untimed": args.adapt, "adapted_step_size": adapted_step,
-                       "max_tree_depth": 10, "parallelism": f"chains x{world}",
+                       "max_tree_depth": 10, "parallelism": (f"rows x{world} (one chain, per-leapfrog NVLink exchange)" if rows
+                                       else f"chains x{world}"),
                        "l2": "inputs 128.4 MB per pass > 126 MB L2, streamed once per grad eval"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clk, "adapt_seconds": adapt_s,
@@ -458,6 +472,8 @@ def main():
     ap.add_argument("--workload", default="logistic",
                     choices=["logistic", "eight_schools", "sv", "horseshoe"])
     ap.add_argument("--chains", type=int, default=0)
+    ap.add_argument("--sharding", default="chains", choices=["chains", "rows"],
+                    help="N>1: independent chains per GPU (weak) or one row-sharded chain (strong)")
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)

@@ -60,6 +60,12 @@ typedef struct {
   const float* inverse_mass_matrix_dev; /* [D] diagonal ([D][D] if dense_mass) or NULL (identity) */
   int find_heuristic_step_size; /* hmc_util.py:314-384 at init and at every window end */
   int likelihood;               /* HORSESHOE: 0 Bernoulli(logits), 1 Normal(mean, prec_obs^-1/2) */
+  /* LOGISTIC row sharding (the reference's GSPMD row sharding, mcmc.py:239-265): this handle
+   * holds rows [rank*N_total/nranks, ...) of X only (N, data0, data1 describe the LOCAL slice);
+   * the sampler state is replicated on every rank and the D+1 partial sums are exchanged per
+   * leapfrog over NVLink peer memory.  nranks <= 1: single GPU. */
+  int nranks;
+  int rank;
 } b200mc_config;
 
 /* Scalar leaves of HMCState (hmc.py:31-48) and HMCAdaptState (hmc_util.py:18-30). */
@@ -138,6 +144,13 @@ int b200mc_get_scalars(b200mc_handle* h, b200mc_chain_scalars* out_host);
 int b200mc_set_scalars(b200mc_handle* h, const b200mc_chain_scalars* in_host);
 int b200mc_get_vector(b200mc_handle* h, int which, float* out_dev, void* stream);
 int b200mc_set_vector(b200mc_handle* h, int which, const float* in_dev, void* stream);
+
+/* Row sharding: every rank exports the IPC handles of its exchange buffers (128 bytes), the
+ * host all-gathers them (any transport), and every rank imports the table [nranks][128].
+ * Must be called on all ranks between b200mc_create and b200mc_init. */
+#define B200MC_COMM_HANDLE_BYTES 128
+int b200mc_comm_export(b200mc_handle* h, void* out_host /*[128]*/);
+int b200mc_comm_import(b200mc_handle* h, const void* all_host /*[nranks][128]*/);
 
 /* Cycle counters of the streaming (logistic) kernel, accumulated over launches by CTA 0:
  * out[0] stream+partial, [1] grid-arrival wait, [2] grid reduction, [3] sampler step,

@@ -53,6 +53,13 @@ struct b200mc_handle {
   unsigned long long* prof = nullptr;  // [kGlmProfSlots]
   int glm_reverse = 1;
   float* dense_replicas = nullptr;
+  // row sharding
+  int nranks = 1, rank = 0;
+  float* xchg_local = nullptr;
+  unsigned* xarrive_local = nullptr;
+  float* xchg[kGlmMaxRanks] = {};
+  unsigned* xarrive[kGlmMaxRanks] = {};
+  bool comm_ready = false;
   bool initialized = false;
 };
 
@@ -145,6 +152,12 @@ extern "C" void b200mc_destroy(b200mc_handle* h) {
   cudaFree(h->cv.mass_matrix_sqrt); cudaFree(h->cv.welford_mean); cudaFree(h->cv.welford_m2);
   cudaFree(h->work); cudaFree(h->partials); cudaFree(h->counters); cudaFree(h->prof); cudaFree(h->glm_xt);
   cudaFree(h->cv.dense); cudaFree(h->dense_replicas); cudaFree(h->M.scratch);
+  for (int r = 0; r < h->nranks; ++r) {
+    if (r == h->rank) continue;
+    if (h->xchg[r]) cudaIpcCloseMemHandle(h->xchg[r]);
+    if (h->xarrive[r]) cudaIpcCloseMemHandle(h->xarrive[r]);
+  }
+  cudaFree(h->xchg_local); cudaFree(h->xarrive_local);
   delete h;
 }
 
@@ -270,6 +283,18 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
     if (c.dense_mass && ctas > 1)
       ACK(alloc((void**)&h->dense_replicas, sizeof(float) * 4 * (size_t)(ctas - 1) * D * D));
     if (const char* e = getenv("B200MC_GLM_REVERSE")) h->glm_reverse = atoi(e);
+    h->nranks = c.nranks > 1 ? c.nranks : 1;
+    h->rank = c.nranks > 1 ? c.rank : 0;
+    if (h->nranks > kGlmMaxRanks || h->rank < 0 || h->rank >= h->nranks) {
+      b200mc_destroy(h);
+      return fail("row sharding: need 0 <= rank < nranks <= %d", kGlmMaxRanks);
+    }
+    if (h->nranks > 1) {
+      if (C != 1) { b200mc_destroy(h); return fail("row sharding runs one chain per handle"); }
+      ACK(alloc((void**)&h->xchg_local,
+                sizeof(float) * 2 * 2 * (size_t)h->nranks * glm_partial_stride(D)));
+      ACK(alloc((void**)&h->xarrive_local, sizeof(unsigned) * 4));
+    }
   } else {
     if (c.family == B200MC_HORSESHOE) {
       if (!c.data1_dev) { b200mc_destroy(h); return fail("horseshoe: Y missing"); }
@@ -374,6 +399,15 @@ static int launch_glm(b200mc_handle* h, const CollectSpec& col, const uint32_t* 
   L.error = (int*)(h->counters + 3);
   L.prof = h->prof;
   L.dense_replicas = h->dense_replicas;
+  L.nranks = h->nranks;
+  L.rank = h->rank;
+  if (h->nranks > 1) {
+    if (!h->comm_ready) return fail("row sharding: b200mc_comm_import has not been called");
+    for (int r = 0; r < h->nranks; ++r) {
+      L.xchg[r] = h->xchg[r];
+      L.xarrive[r] = h->xarrive[r];
+    }
+  }
   L.init_keys = keys; L.user_init = user_init; L.chain = chain; L.C = h->C;
   L.eval_z = eval_z; L.eval_U = eval_U; L.eval_grad = eval_grad;
   CK(cudaMemsetAsync(h->counters, 0, sizeof(unsigned) * 3, st));  // arrive
@@ -459,6 +493,7 @@ extern "C" int b200mc_get_scalars(b200mc_handle* h, b200mc_chain_scalars* out_ho
   if (h->counters) {
     int err = 0;
     CK(cudaMemcpy(&err, h->counters + 3, sizeof(int), cudaMemcpyDeviceToHost));
+    if (err == 2) return fail("cross-rank exchange timed out inside the streaming kernel");
     if (err) return fail("grid barrier timed out inside the streaming kernel");
   }
   return 0;
@@ -468,6 +503,36 @@ extern "C" int b200mc_set_scalars(b200mc_handle* h, const b200mc_chain_scalars* 
   if (!h || !in_host) return fail("null argument");
   CK(cudaMemcpy(h->cs, in_host, sizeof(ChainScalars) * h->C, cudaMemcpyHostToDevice));
   h->initialized = true;
+  return 0;
+}
+
+extern "C" int b200mc_comm_export(b200mc_handle* h, void* out_host) {
+  if (!h || !out_host) return fail("null argument");
+  if (h->nranks <= 1) return fail("handle is not row sharded");
+  static_assert(2 * sizeof(cudaIpcMemHandle_t) <= B200MC_COMM_HANDLE_BYTES, "handle size");
+  cudaIpcMemHandle_t hs[2];
+  CK(cudaIpcGetMemHandle(&hs[0], h->xchg_local));
+  CK(cudaIpcGetMemHandle(&hs[1], h->xarrive_local));
+  memcpy(out_host, hs, sizeof(hs));
+  return 0;
+}
+
+extern "C" int b200mc_comm_import(b200mc_handle* h, const void* all_host) {
+  if (!h || !all_host) return fail("null argument");
+  if (h->nranks <= 1) return fail("handle is not row sharded");
+  const char* base = (const char*)all_host;
+  for (int r = 0; r < h->nranks; ++r) {
+    if (r == h->rank) {
+      h->xchg[r] = h->xchg_local;
+      h->xarrive[r] = h->xarrive_local;
+      continue;
+    }
+    cudaIpcMemHandle_t hs[2];
+    memcpy(hs, base + (size_t)r * B200MC_COMM_HANDLE_BYTES, sizeof(hs));
+    CK(cudaIpcOpenMemHandle((void**)&h->xchg[r], hs[0], cudaIpcMemLazyEnablePeerAccess));
+    CK(cudaIpcOpenMemHandle((void**)&h->xarrive[r], hs[1], cudaIpcMemLazyEnablePeerAccess));
+  }
+  h->comm_ready = true;
   return 0;
 }
 

@@ -34,13 +34,18 @@
 
 namespace b200mc {
 
-constexpr int kGlmConsumerWarps = 11;  // + 1 producer warp = 3 warps per SM sub-partition
+// warps 0..9 consume tiles, warp 10 is the control (sampler) warp, warp 11 the TMA producer:
+// 12 warps = 3 per SM sub-partition (168 registers per thread)
+constexpr int kGlmConsumerWarps = 10;
 constexpr int kGlmConsumerThreads = kGlmConsumerWarps * 32;
-constexpr int kGlmThreads = kGlmConsumerThreads + 32;
+constexpr int kGlmControlWarp = kGlmConsumerWarps;
+constexpr int kGlmProducerWarp = kGlmConsumerWarps + 1;
+constexpr int kGlmThreads = kGlmConsumerThreads + 64;
 constexpr int kGlmTileRows = 32;
 constexpr int kGlmMaxD = 128;
 constexpr int kGlmMaxStages = 32;      // one producer lane per stage
 constexpr int kGlmProfSlots = 16;
+constexpr int kGlmMaxRanks = 8;
 
 __host__ __device__ inline int glm_groups(int D) { return (D + 3) / 4; }
 __host__ __device__ inline int glm_tile_bytes(int D) { return glm_groups(D) * 512 + 32; }
@@ -62,6 +67,15 @@ struct GlmLaunch {
   int* error;            // set to 1 on a spin time-out
   unsigned long long* prof;  // [kGlmProfSlots] cycle counters of CTA 0 (or null)
   float* dense_replicas;     // dense mass: private [nCTA-1][4][D][D] copies for CTAs > 0
+  // row sharding over GPUs (one rank per GPU, rows split, sampler replicated on every rank):
+  // per pass every rank writes its D+1 partial sums into every rank's exchange buffer over
+  // NVLink (P2P stores of (value, sequence) pairs, no fence or flag); all ranks then add the same
+  // nranks vectors in rank order, so the reduced gradient is bit-identical everywhere.
+  int nranks, rank;
+  float* xchg[kGlmMaxRanks];        // rank r's buffer [2][nranks][PS] of (value, seq) pairs
+                                    // (peer-mapped), own included
+  unsigned* xarrive[kGlmMaxRanks];  // rank r's counters: [1] exchanges completed before this
+                                    // launch (only the local one is used)
   const uint32_t* init_keys;  // [C][2] or null
   int user_init;
   int chain;             // which chain of cs/cv this launch advances
@@ -120,8 +134,35 @@ __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
 __device__ __forceinline__ void red_release_add(unsigned* p, unsigned v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_sys_add(unsigned* p, unsigned v) {
+  asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ float ld_relaxed_sys_f32(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_sys_f32(float* p, float v) {
+  asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_sys_v2(uint2* p, unsigned x, unsigned y) {
+  asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ uint2 ld_relaxed_sys_v2(const uint2* p) {
+  uint2 v;
+  asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ void consumer_bar() {  // named barrier 1: consumer warps only
   asm volatile("bar.sync 1, %0;" ::"n"(kGlmConsumerThreads) : "memory");
+}
+__device__ __forceinline__ void handoff_bar() {  // named barrier 2: consumer warps + control warp
+  asm volatile("bar.sync 2, %0;" ::"n"(kGlmConsumerThreads + 32) : "memory");
 }
 
 // Spin until *p >= target (monotonic counter); false on time-out (seconds).
@@ -358,7 +399,7 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
     red[i] = 0.f;  // red and red2 are adjacent; their pad columns stay zero
   __syncthreads();
 
-  if (warp == kGlmConsumerWarps) {
+  if (warp == kGlmProducerWarp) {
     // ================= producer warp: lane s feeds stage s, runs ahead across passes ========
     const int s = lane;
     if (s < NS && nt > 0) {
@@ -385,12 +426,17 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
     return;
   }
 
-  // ================= consumer warps =================
-  const int tid = threadIdx.x;  // 0 .. kGlmConsumerThreads-1
   const bool eval_mode = (L.eval_z != nullptr);
-  Sampler<WarpGroup> S;  // a replica in every CTA; only CTA 0 writes
-  StepResult sres = FINISHED;
-  if (warp == 0) {
+  const int G = glm_groups(D);
+  const unsigned xbase = (L.nranks > 1) ? __ldcg(&L.xarrive[L.rank][1]) : 0u;
+
+  if (warp == kGlmControlWarp) {
+    // ================= control warp: the sampler replica of this CTA =================
+    // It owns the chain state (registers + shared memory), finishes the reduction, runs the
+    // cross-rank exchange and the sampler step, and precomputes all randomness of the coming
+    // leaves / doublings / transitions while the consumer warps stream the next pass.
+    Sampler<WarpGroup> S;  // a replica in every CTA; only CTA 0 writes
+    StepResult sres = FINISHED;
     float* work = reinterpret_cast<float*>(smem + lay.off_work);
     S.setup(&L.P, WarpGroup{}, work, D, 1, L.chain, L.C, &L.col);
     S.writer = (cta == 0);
@@ -423,16 +469,116 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
     __syncwarp();
     for (int d = lane; d < kGlmMaxD; d += 32) th[d] = (d < D) ? S.v(LZ)[d] : 0.f;
     if (lane == 0) flags[2] = (sres == NEED_GRAD) ? 1 : 0;
+    handoff_bar();  // theta of pass 0 is ready
     if (sres == NEED_GRAD) S.prefetch_rng();
+    int pass = 0;
+    while (sres == NEED_GRAD) {
+      handoff_bar();  // red2 holds this rank's grid-reduced partial sums
+      float* lz = S.v(LZ);
+      float* lg = S.v(LG);
+      // this rank's sums over its CTAs, columns lane, lane+32, ... (< PS <= 132)
+      float sl[5];
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const int d = lane + 32 * k;
+        float a = 0.f;
+        if (d < PS) {
+#pragma unroll
+          for (int p2 = 0; p2 < kGlmRedGroups; ++p2) a += red2[p2 * PS + d];
+        }
+        sl[k] = a;
+      }
+      if (L.nranks > 1) {
+        // Low-latency exchange: every 8-byte slot carries (value, sequence number), so one
+        // one-way NVLink store per element is the whole message -- no fence, no flag.  Slots
+        // are double-buffered by exchange parity; a rank can only be one exchange ahead.
+        const unsigned e = xbase + (unsigned)pass;  // exchange index, monotonic over launches
+        const unsigned seq = e + 1u;
+        const long slot = (long)(e & 1u) * L.nranks * PS;
+        if (cta == 0) {
+          for (int r = 0; r < L.nranks; ++r) {
+            uint2* dst = reinterpret_cast<uint2*>(L.xchg[r]) + slot + (long)L.rank * PS;
+#pragma unroll
+            for (int k = 0; k < 5; ++k)
+              if (lane + 32 * k < PS) st_relaxed_sys_v2(dst + lane + 32 * k, __float_as_uint(sl[k]), seq);
+          }
+        }
+        const uint2* mine = reinterpret_cast<const uint2*>(L.xchg[L.rank]) + slot;
+        bool ok = true;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+          const int d = lane + 32 * k;
+          float a = 0.f;
+          if (d < PS) {
+            for (int r = 0; r < L.nranks; ++r) {  // rank order: identical sums on every rank
+              uint2 v = ld_relaxed_sys_v2(mine + (long)r * PS + d);
+              for (long it = 0; v.y != seq && it < (1L << 22); ++it) {
+                if (it > 65536) __nanosleep(200);
+                v = ld_relaxed_sys_v2(mine + (long)r * PS + d);
+              }
+              ok = ok && (v.y == seq);
+              a += __uint_as_float(v.x);
+            }
+          }
+          sl[k] = a;
+        }
+        if (!__all_sync(0xffffffffu, ok)) {
+          if (lane == 0) {
+            atomicExch(L.error, 2);
+            flags[3] = 0;
+          }
+          __syncwarp();
+        }
+      }
+      float prior = 0.f, llik = 0.f;
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const int d = lane + 32 * k;
+        if (d < D) {
+          const float t = lz[d];
+          lg[d] = t + sl[k];                            // grad U = theta + X^T (sigmoid - y)
+          prior += 0.5f * t * t + 0.9189385332046727f;  // -log N(theta; 0, 1)
+        }
+        llik += (d == D) ? sl[k] : 0.f;
+      }
+      prior = WarpGroup{}.sum(prior);
+      llik = WarpGroup{}.sum(llik);
+      const float U = prior + llik;
+      if (eval_mode) {
+        if (cta == 0) {
+          for (int d = lane; d < D; d += 32) L.eval_grad[d] = lg[d];
+          if (lane == 0) *L.eval_U = U;
+        }
+        sres = FINISHED;
+      } else {
+        sres = flags[3] ? S.advance(U) : FINISHED;
+      }
+      __syncwarp();
+      for (int d = lane; d < D; d += 32) th[d] = S.v(LZ)[d];
+      if (lane == 0) flags[2] = (sres == NEED_GRAD) ? 1 : 0;
+      ++pass;
+      handoff_bar();  // theta of the next pass is ready (or stop)
+      if (sres == NEED_GRAD) S.prefetch_rng();
+    }
+    if (lane == 0 && cta == 0) {
+      if (L.nranks > 1) L.xarrive[L.rank][1] = xbase + (unsigned)pass;
+#ifdef B200MC_SAMPLER_PROF
+      if (L.prof)
+        for (int i = 0; i < 8; ++i) atomicAdd(&L.prof[8 + i], S.pc[i]);
+#endif
+    }
+    if (!eval_mode) S.store(L.cs, L.cv);
+    return;
   }
-  consumer_bar();
 
-  const int G = glm_groups(D);
+  // ================= consumer warps =================
+  const int tid = threadIdx.x;  // 0 .. kGlmConsumerThreads-1
   const int m = NS / kGlmConsumerWarps;
   long p_next = warp;
   int si = 0;
   uint32_t ph = 0;
   int pass = 0;
+  handoff_bar();  // theta of pass 0
   long long t_mark = clock64();
   unsigned long long c_stream = 0, c_wait = 0, c_reduce = 0, c_sampler = 0;
   while (flags[2]) {
@@ -496,52 +642,20 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
       }
       reinterpret_cast<float4*>(red2 + grp * PS)[c4] = a;
     }
-    consumer_bar();
-    // ---- warp 0: finish the potential, advance the sampler replica, next theta
-    if (warp == 0) {
-      long long t2 = 0;
-      if (lane == 0) {
-        t2 = clock64();
-        c_reduce += (unsigned long long)(t2 - t_mark);
-      }
-      float* lz = S.v(LZ);
-      float* lg = S.v(LG);
-      float prior = 0.f;
-      for (int d = lane; d < D; d += 32) {
-        float a = 0.f;
-#pragma unroll
-        for (int p2 = 0; p2 < kGlmRedGroups; ++p2) a += red2[p2 * PS + d];
-        const float t = lz[d];
-        lg[d] = t + a;                                // grad U = theta + X^T (sigmoid - y)
-        prior += 0.5f * t * t + 0.9189385332046727f;  // -log N(theta; 0, 1)
-      }
-      prior = WarpGroup{}.sum(prior);
-      float llik = 0.f;
-#pragma unroll
-      for (int p2 = 0; p2 < kGlmRedGroups; ++p2) llik += red2[p2 * PS + D];
-      const float U = prior + llik;
-      if (eval_mode) {
-        if (cta == 0) {
-          for (int d = lane; d < D; d += 32) L.eval_grad[d] = lg[d];
-          if (lane == 0) *L.eval_U = U;
-        }
-        sres = FINISHED;
-      } else {
-        sres = flags[3] ? S.advance(U) : FINISHED;
-      }
-      __syncwarp();
-      for (int d = lane; d < D; d += 32) th[d] = S.v(LZ)[d];
-      if (lane == 0) {
-        flags[2] = (sres == NEED_GRAD) ? 1 : 0;
-        t_mark = clock64();
-        c_sampler += (unsigned long long)(t_mark - t2);
-      }
+    long long t2 = 0;
+    if (tid == 0) {
+      t2 = clock64();
+      c_reduce += (unsigned long long)(t2 - t_mark);
     }
-    consumer_bar();
-    if (warp == 0 && sres == NEED_GRAD) S.prefetch_rng();
+    handoff_bar();  // red2 -> control warp
+    handoff_bar();  // control warp -> next theta
+    if (tid == 0) {
+      t_mark = clock64();
+      c_sampler += (unsigned long long)(t_mark - t2);
+    }
     ++pass;
   }
-  // ---- shutdown: tell the producer, persist the chain
+  // ---- shutdown: tell the producer
   if (tid == 0) {
     flags[1] = pass;
     __threadfence_block();
@@ -552,12 +666,8 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
       atomicAdd(&L.prof[2], c_reduce);
       atomicAdd(&L.prof[3], c_sampler);
       atomicAdd(&L.prof[4], (unsigned long long)pass);
-#ifdef B200MC_SAMPLER_PROF
-      for (int i = 0; i < 8; ++i) atomicAdd(&L.prof[8 + i], S.pc[i]);
-#endif
     }
   }
-  if (warp == 0 && !eval_mode) S.store(L.cs, L.cv);
 }
 
 }  // namespace b200mc

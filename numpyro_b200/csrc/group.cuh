@@ -9,6 +9,7 @@
 namespace b200mc {
 
 struct ThreadGroup {  // one chain per thread (tiny D: eight schools)
+  static constexpr bool kUnitStride = false;  // vectors are strided [D][chain]
   __device__ __forceinline__ int lane() const { return 0; }
   __device__ __forceinline__ int size() const { return 1; }
   __device__ __forceinline__ float sum(float x) const { return x; }
@@ -17,6 +18,7 @@ struct ThreadGroup {  // one chain per thread (tiny D: eight schools)
 };
 
 struct WarpGroup {  // one chain per warp (D up to a few hundred)
+  static constexpr bool kUnitStride = true;
   __device__ __forceinline__ int lane() const { return threadIdx.x & 31; }
   __device__ __forceinline__ int size() const { return 32; }
   __device__ __forceinline__ float sum(float x) const {
@@ -37,6 +39,7 @@ struct WarpGroup {  // one chain per warp (D up to a few hundred)
 // One chain per CTA (large D: stochastic volatility).  `scratch` is 2*32 floats of
 // shared memory private to the CTA.
 struct BlockGroup {
+  static constexpr bool kUnitStride = true;
   float* scratch;
   __device__ __forceinline__ int lane() const { return threadIdx.x; }
   __device__ __forceinline__ int size() const { return blockDim.x; }

@@ -46,6 +46,7 @@ enum Slot {
   SZ_PROP, SG_PROP, S_RSUM,                                // subtree proposal / momentum sum
   IMM, MSQRT, WMEAN, WM2,                                  // adaptation vectors
   LV, V_LEFT, V_RIGHT,                                     // dense mass: cached M^-1 r of LR, R_LEFT, R_RIGHT
+  EPS_NEXT,                                                // prefetched N(0, I) draw of the next transition
   CKPT0                                                    // r_ckpts[i], r_sum_ckpts[i], M^-1 r_ckpts[i] = CKPT0+3i+{0,1,2}
 };
 __host__ __device__ inline int num_slots(int max_depth) { return CKPT0 + 3 * max_depth; }
@@ -66,7 +67,8 @@ struct Sampler {
   G g;
   float* w;            // this chain's slot 0, element 0
   long slot_stride;    // floats between slots
-  int es;              // floats between elements of one vector
+  int es_rt;           // floats between elements of one vector (1 for warp / CTA groups)
+#define es (G::kUnitStride ? 1 : es_rt)
   int D;
   bool part;
   bool dense;
@@ -99,6 +101,17 @@ struct Sampler {
   int pre_valid;
   Key pre_sub_key;
   float pre_u;
+  // doubling-level (hmc_util.py:1161-1162, :920) and transition-level (hmc.py:472, :94-102)
+  // randomness, likewise computable ahead of the gradients that gate its use
+  struct DoublingRng {
+    Key tree_key, sub_key, top_key;
+    int going_right;
+    float u_top;
+  };
+  int pre_d_valid, pre_t_valid, pre_a_valid;
+  DoublingRng pre_d, pre_t_d;
+  Key pre_t_rng_key, pre_t_k_tr, pre_a_nk, pre_a_kss;
+  float u_top;
   // HMC
   int hmc_steps, hmc_done;
   float energy_old;
@@ -130,7 +143,7 @@ struct Sampler {
   // ------------------------------------------------------------------ setup / persistence
   __device__ void setup(const SamplerParams* p, G grp, float* work, long sstride, int estride,
                         int chain_, int C_, const CollectSpec* c) {
-    P = p; g = grp; w = work; slot_stride = sstride; es = estride; D = p->D;
+    P = p; g = grp; w = work; slot_stride = sstride; es_rt = estride; D = p->D;
     part = p->partitionable != 0;
     dense = p->dense_mass != 0;
     dn = nullptr;
@@ -140,6 +153,7 @@ struct Sampler {
     local_iter = 0;
     phase = PH_IDLE;
     pre_valid = 0;
+    pre_d_valid = 0; pre_t_valid = 0; pre_a_valid = 0;
   }
 
   __device__ void load(const ChainScalars* cs, const ChainVectors& cv) {
@@ -369,8 +383,9 @@ struct Sampler {
   // warmup_adapter.update_fn: hmc_util.py:637-705.  Returns true when a step-size search
   // (find_heuristic_step_size) was started and the transition tail must wait for it.
   __device__ bool adapt(int t, float accept_prob) {
-    Key nk, kss;
-    split2(Key{s.adapt_key[0], s.adapt_key[1]}, part, nk, kss);  // :656
+    if (!pre_a_valid) split2(Key{s.adapt_key[0], s.adapt_key[1]}, part, pre_a_nk, pre_a_kss);  // :656
+    pre_a_valid = 0;
+    const Key nk = pre_a_nk, kss = pre_a_kss;
     s.adapt_key[0] = nk.k0; s.adapt_key[1] = nk.k1;
     if (P->adapt_step_size) {
       da_update(P->target_accept_prob - accept_prob);
@@ -575,11 +590,14 @@ struct Sampler {
   // ------------------------------------------------------------------ transition start
   // sample_kernel head (hmc.py:472-490) + build_tree head (hmc_util.py:1129-1153)
   __device__ StepResult start_transition() {
-    Key nk, k_mom, k_tr;
-    split3(Key{s.rng_key[0], s.rng_key[1]}, part, nk, k_mom, k_tr);
-    s.rng_key[0] = nk.k0; s.rng_key[1] = nk.k1;
-    if (P->algo == ALGO_HMC) return start_hmc(k_mom, k_tr);
-    draw_momentum(k_mom, R_LEFT);
+    if (!pre_t_valid) compute_transition_rng();
+    pre_t_valid = 0;
+    s.rng_key[0] = pre_t_rng_key.k0; s.rng_key[1] = pre_t_rng_key.k1;
+    const Key k_tr = pre_t_k_tr;
+    if (P->algo == ALGO_HMC) return start_hmc(k_tr);
+    momentum_from_eps(R_LEFT);
+    pre_d = pre_t_d;  // the first doubling of this transition
+    pre_d_valid = 1;
     {
       float *rl = v(R_LEFT), *rr = v(R_RIGHT), *rs = v(R_SUM);
       float *zl = v(Z_LEFT), *zr = v(Z_RIGHT), *gl = v(G_LEFT), *gr = v(G_RIGHT);
@@ -611,11 +629,13 @@ struct Sampler {
 
   // build_tree._body_fn (hmc_util.py:1159-1176) + _double_tree head (:920)
   __device__ void next_doubling() {
-    Key nk, dir_key, dbl_key;
-    split3(tree_key, part, nk, dir_key, dbl_key);
-    tree_key = nk;
-    going_right = uniform01(dir_key, part) < 0.5f;
-    split2(dbl_key, part, sub_key, top_key);
+    if (!pre_d_valid) compute_doubling_rng(tree_key, pre_d);
+    pre_d_valid = 0;
+    tree_key = pre_d.tree_key;
+    going_right = pre_d.going_right;
+    sub_key = pre_d.sub_key;
+    top_key = pre_d.top_key;
+    u_top = pre_d.u_top;
     s_n = 0;
     pre_valid = 0;
     eps_s = going_right ? s.step_size : -s.step_size;
@@ -631,11 +651,58 @@ struct Sampler {
   // not depend on the gradient, so a kernel may call this while the gradient is still
   // being computed.
   __device__ __forceinline__ void prefetch_rng() {
-    if (phase != PH_TREE || pre_valid) return;
-    Key tkey;
-    split2(sub_key, part, pre_sub_key, tkey);
-    pre_u = uniform01(tkey, part);
-    pre_valid = 1;
+    if (phase == PH_TREE && !pre_valid) {
+      Key tkey;
+      split2(sub_key, part, pre_sub_key, tkey);
+      pre_u = uniform01(tkey, part);
+      pre_valid = 1;
+    }
+    if (phase != PH_TREE && phase != PH_HMC) return;
+    if (phase == PH_TREE && !pre_d_valid) {
+      compute_doubling_rng(tree_key, pre_d);
+      pre_d_valid = 1;
+    }
+    if (!pre_t_valid) {
+      compute_transition_rng();
+      pre_t_valid = 1;
+    }
+    if (!pre_a_valid && s.i < P->num_warmup) {
+      split2(Key{s.adapt_key[0], s.adapt_key[1]}, part, pre_a_nk, pre_a_kss);
+      pre_a_valid = 1;
+    }
+  }
+
+  // build_tree._body_fn randomness (hmc_util.py:1161-1162) + _double_tree's split (:920) +
+  // the top-level combine's bernoulli draw (:804), all functions of the tree key alone
+  __device__ __forceinline__ void compute_doubling_rng(Key tk, DoublingRng& out) {
+    Key dir_key, dbl_key;
+    split3(tk, part, out.tree_key, dir_key, dbl_key);
+    out.going_right = uniform01(dir_key, part) < 0.5f;
+    split2(dbl_key, part, out.sub_key, out.top_key);
+    out.u_top = uniform01(out.top_key, part);
+  }
+
+  // sample_kernel's split (hmc.py:472) + the N(0, I) draw of momentum_generator (hmc.py:94-102,
+  // one dict block => split(key, 1)) + the first doubling's randomness
+  __device__ __forceinline__ void compute_transition_rng() {
+    Key k_mom;
+    split3(Key{s.rng_key[0], s.rng_key[1]}, part, pre_t_rng_key, k_mom, pre_t_k_tr);
+    const Key kb = split_at(k_mom, 1u, 0u, part);
+    float* eps = v(EPS_NEXT);
+    B200MC_FOR_D eps[d * es] = normal_at(kb, (uint32_t)D, (uint32_t)d, part);
+    if (P->algo == ALGO_NUTS) compute_doubling_rng(pre_t_k_tr, pre_t_d);
+  }
+
+  // r = M^{1/2} eps with the prefetched eps
+  __device__ __forceinline__ void momentum_from_eps(int dst) {
+    float* r = v(dst);
+    const float* eps = v(EPS_NEXT);
+    if (dense) {
+      matvec(mat(1), eps, r, true);
+      return;
+    }
+    const float* ms = v(MSQRT);
+    B200MC_FOR_D r[d * es] = ms[d * es] * eps[d * es];
   }
 
   // ------------------------------------------------------------------ NUTS: one leaf
@@ -730,7 +797,7 @@ struct Sampler {
     const bool tree_turning =
         sub_turning | is_turning(v(R_LEFT), v(R_RIGHT), v(R_SUM), nullptr, nullptr, v(V_LEFT),
                                  v(V_RIGHT));
-    if (uniform01(top_key, part) < p) {
+    if (u_top < p) {
       copy(Z_PROP, SZ_PROP); copy(G_PROP, SG_PROP);
       prop_pe = s_prop_pe; prop_energy = s_prop_energy;
     }
@@ -759,8 +826,8 @@ struct Sampler {
   }
 
   // ------------------------------------------------------------------ HMC (hmc.py:364-414)
-  __device__ StepResult start_hmc(Key k_mom, Key k_tr) {
-    draw_momentum(k_mom, LR);
+  __device__ StepResult start_hmc(Key k_tr) {
+    momentum_from_eps(LR);
     copy(LZ, Z_PROP); copy(LG, G_PROP);
     mh_key = k_tr;
     float eps = s.step_size;
@@ -906,6 +973,7 @@ struct Sampler {
     return FINISHED;
   }
 #undef B200MC_FOR_D
+#undef es
 };
 
 }  // namespace b200mc

@@ -77,3 +77,27 @@ def run_sharded(make_mcmc, chain_keys, *args, rank=None, world_size=None, group=
     if got is None:
         return None, None
     return got["samples"], got["extras"]
+
+
+def allgather_bytes(group=None):
+    """Host transport for ``HMC.shard_rows``: ``torch.distributed.all_gather_object``."""
+    import torch.distributed as dist
+
+    def allgather(payload):
+        out = [None] * dist.get_world_size(group)
+        dist.all_gather_object(out, bytes(payload), group=group)
+        return out
+
+    return allgather
+
+
+def shard_rows(kernel, data, labels, rank=None, world_size=None, group=None):
+    """Configure ``kernel`` for row sharding and return this rank's ``(data, labels)`` slice
+    (contiguous rows, same split as ``shard_bounds``)."""
+    if rank is None or world_size is None:
+        import torch.distributed as dist
+
+        rank, world_size = dist.get_rank(group), dist.get_world_size(group)
+    lo, hi = shard_bounds(len(data), rank, world_size)
+    kernel.shard_rows(rank, world_size, allgather_bytes(group) if world_size > 1 else None)
+    return data[lo:hi], labels[lo:hi]

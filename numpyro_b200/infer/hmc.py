@@ -130,6 +130,7 @@ class HMC(MCMCKernel):
         self._data = None
         self._vectorized = False
         self._last_state = None
+        self._row_shard = None  # (rank, nranks, allgather) -- see shard_rows
 
     # ------------------------------------------------------------------ properties
     @property
@@ -153,6 +154,17 @@ class HMC(MCMCKernel):
             return lambda x: x
         return self._postprocess_fn
 
+    def shard_rows(self, rank, nranks, allgather):
+        """Row-shard a tall-data (logistic) model over ``nranks`` GPUs, one process each: this
+        process passes only ITS rows to ``init``/``MCMC.run``; the sampler state is replicated
+        and the D+1 partial sums are exchanged per leapfrog over NVLink peer memory (the
+        reference's analogue is GSPMD row sharding, ``mcmc.py:239-265``).
+        ``allgather(bytes) -> list[bytes]`` (one entry per rank, rank order) is the host
+        transport used once to exchange CUDA IPC handles, e.g.
+        ``numpyro_b200.distributed.allgather_bytes``."""
+        self._row_shard = None if nranks <= 1 else (int(rank), int(nranks), allgather)
+        return self
+
     # ------------------------------------------------------------------ handle management
     def _destroy(self):
         if self._handle is not None:
@@ -167,7 +179,8 @@ class HMC(MCMCKernel):
 
     def __getstate__(self):  # hmc.py:818-822
         state = self.__dict__.copy()
-        for k in ("_sample_fn", "_init_fn", "_handle", "_data", "_last_state", "_postprocess_fn"):
+        for k in ("_sample_fn", "_init_fn", "_handle", "_data", "_last_state", "_postprocess_fn",
+                  "_row_shard"):
             state[k] = None
         return state
 
@@ -210,6 +223,8 @@ class HMC(MCMCKernel):
             dense_mass=int(bool(self._dense_mass)),
             find_heuristic_step_size=int(bool(self._find_heuristic_step_size)),
             likelihood=int(getattr(bound, "likelihood", 0)),
+            nranks=self._row_shard[1] if self._row_shard else 1,
+            rank=self._row_shard[0] if self._row_shard else 0,
             regularize_mass_matrix=int(bool(self._regularize_mass_matrix)),
             target_accept_prob=float(self._target_accept_prob),
             max_tree_depth_warmup=int(depth[0]), max_tree_depth_sample=int(depth[1]),
@@ -220,8 +235,17 @@ class HMC(MCMCKernel):
             init_radius=float(arg) if kind == "uniform" else 2.0,
             inverse_mass_matrix_dev=imm.ptr if imm is not None else None)
         h = C.c_void_p()
+        if self._row_shard and bound.family != models.LOGISTIC:
+            raise NotImplementedError("row sharding exists for the tall-data logistic family only")
         _lib.check(lib.b200mc_create(C.byref(cfg), C.byref(h)))
         self._handle = h
+        if self._row_shard:
+            mine = C.create_string_buffer(128)
+            _lib.check(lib.b200mc_comm_export(h, mine))
+            table = self._row_shard[2](mine.raw)
+            if len(table) != self._row_shard[1] or any(len(t) != 128 for t in table):
+                raise _lib.B200Error("row sharding: allgather must return one 128-byte entry per rank")
+            _lib.check(lib.b200mc_comm_import(h, C.create_string_buffer(b"".join(table), 128 * len(table))))
         self._data = (d0, d1, imm)
         self._bound = bound
         self._num_chains = num_chains
