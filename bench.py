@@ -308,6 +308,9 @@ def run_own(args):
                  enumerate(("stream", "arrival_wait", "grid_reduce", "sampler_step"))}
     if any(prof[8 + i] for i in range(8)):
         breakdown["sampler_sub"] = [float(prof[8 + i]) / passes for i in range(8)]
+        breakdown["control"] = {"prologue": float(prof[5]) / passes,
+                                "advance_fast_leaf": float(prof[6]) / passes,
+                                "advance_other": float(prof[7]) / passes}
     total_ms = max_over_ranks(sum(step_ms))
     total_grads = float(sum(step_grads)) if rows else sum_over_ranks(float(sum(step_grads)))
     value = total_grads / (total_ms * 1e-3)

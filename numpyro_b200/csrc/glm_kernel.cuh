@@ -472,8 +472,14 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
     handoff_bar();  // theta of pass 0 is ready
     if (sres == NEED_GRAD) S.prefetch_rng();
     int pass = 0;
+#ifdef B200MC_SAMPLER_PROF
+    unsigned long long c_pro = 0, c_fast = 0, c_other = 0;
+#endif
     while (sres == NEED_GRAD) {
-      handoff_bar();  // red2 holds this rank's grid-reduced partial sums
+      handoff_bar();  // red[0..PS) holds this rank's grid-reduced partial sums
+#ifdef B200MC_SAMPLER_PROF
+      const long long tp0 = (red2[0] == 12345.678f) ? 0 : clock64();  // after the barrier released
+#endif
       float* lz = S.v(LZ);
       float* lg = S.v(LG);
       // this rank's sums over its CTAs, columns lane, lane+32, ... (< PS <= 132)
@@ -481,12 +487,7 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
 #pragma unroll
       for (int k = 0; k < 5; ++k) {
         const int d = lane + 32 * k;
-        float a = 0.f;
-        if (d < PS) {
-#pragma unroll
-          for (int p2 = 0; p2 < kGlmRedGroups; ++p2) a += red2[p2 * PS + d];
-        }
-        sl[k] = a;
+        sl[k] = (d < PS) ? red[d] : 0.f;
       }
       if (L.nranks > 1) {
         // Low-latency exchange: every 8-byte slot carries (value, sequence number), so one
@@ -541,8 +542,7 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
         }
         llik += (d == D) ? sl[k] : 0.f;
       }
-      prior = WarpGroup{}.sum(prior);
-      llik = WarpGroup{}.sum(llik);
+      WarpGroup{}.sum2(prior, llik);
       const float U = prior + llik;
       if (eval_mode) {
         if (cta == 0) {
@@ -551,20 +551,36 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
         }
         sres = FINISHED;
       } else {
-        sres = flags[3] ? S.advance(U) : FINISHED;
+        // the critical part only: bookkeeping of a continuing leaf is deferred below
+#ifdef B200MC_SAMPLER_PROF
+        const long long tp1 = clock64();
+        c_pro += (unsigned long long)(tp1 - tp0);
+#endif
+        sres = flags[3] ? S.advance_early(U) : FINISHED;
+#ifdef B200MC_SAMPLER_PROF
+        const long long tp2 = clock64();
+        if (S.deferred) c_fast += (unsigned long long)(tp2 - tp1);
+        else c_other += (unsigned long long)(tp2 - tp1);
+#endif
       }
       __syncwarp();
       for (int d = lane; d < D; d += 32) th[d] = S.v(LZ)[d];
       if (lane == 0) flags[2] = (sres == NEED_GRAD) ? 1 : 0;
       ++pass;
       handoff_bar();  // theta of the next pass is ready (or stop)
+      // off the critical path, overlapped with the consumers' streaming of the next pass
+      if (S.deferred) S.leaf_deferred();
       if (sres == NEED_GRAD) S.prefetch_rng();
     }
     if (lane == 0 && cta == 0) {
       if (L.nranks > 1) L.xarrive[L.rank][1] = xbase + (unsigned)pass;
 #ifdef B200MC_SAMPLER_PROF
-      if (L.prof)
+      if (L.prof) {
         for (int i = 0; i < 8; ++i) atomicAdd(&L.prof[8 + i], S.pc[i]);
+        atomicAdd(&L.prof[5], c_pro);
+        atomicAdd(&L.prof[6], c_fast);
+        atomicAdd(&L.prof[7], c_other);
+      }
 #endif
     }
     if (!eval_mode) S.store(L.cs, L.cv);
@@ -641,6 +657,13 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
         }
       }
       reinterpret_cast<float4*>(red2 + grp * PS)[c4] = a;
+    }
+    consumer_bar();
+    if (tid < PS) {  // second stage, fixed order; red[0..PS) is free again and feeds the control warp
+      float a = 0.f;
+#pragma unroll
+      for (int p2 = 0; p2 < kGlmRedGroups; ++p2) a += red2[p2 * PS + tid];
+      red[tid] = a;
     }
     long long t2 = 0;
     if (tid == 0) {

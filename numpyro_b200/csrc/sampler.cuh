@@ -111,6 +111,9 @@ struct Sampler {
   int pre_d_valid, pre_t_valid, pre_a_valid;
   DoublingRng pre_d, pre_t_d;
   Key pre_t_rng_key, pre_t_k_tr, pre_a_nk, pre_a_kss;
+  // leaf state parked between part A and part B of the fused leaf step
+  float fz[4], fg[4], f_U, f_e_new, f_dE;
+  int deferred;
   float u_top;
   // HMC
   int hmc_steps, hmc_done;
@@ -154,6 +157,7 @@ struct Sampler {
     phase = PH_IDLE;
     pre_valid = 0;
     pre_d_valid = 0; pre_t_valid = 0; pre_a_valid = 0;
+    deferred = 0;
   }
 
   __device__ void load(const ChainScalars* cs, const ChainVectors& cv) {
@@ -191,7 +195,7 @@ struct Sampler {
   // ------------------------------------------------------------------ small pieces
   // dst = M src for a dense row-major D x D matrix (rows over lanes); `lower` restricts
   // the sum to j <= i (triangular factor: the skipped terms are exact zeros).
-  __device__ void matvec(const float* M, const float* src, float* dst, bool lower = false) {
+  __device__ __noinline__ void matvec(const float* M, const float* src, float* dst, bool lower = false) {
     g.sync();  // src was written by its owner lanes
     B200MC_FOR_D {
       const float* row = M + (long)d * D;
@@ -333,7 +337,7 @@ struct Sampler {
   //   tril_inv     = swapaxes(cholesky(cov[::-1, ::-1])[::-1, ::-1])
   //   cov_inv_sqrt = solve_triangular(tril_inv, identity, lower=True)
   // mat(3) (the Welford m2 buffer) is the workspace and is left zeroed.
-  __device__ void factor_dense() {
+  __device__ __noinline__ void factor_dense() {
     float *cov = mat(0), *msq = mat(1), *tinv = mat(2), *W = mat(3);
     const int n = D;
     g.sync();
@@ -382,7 +386,7 @@ struct Sampler {
 
   // warmup_adapter.update_fn: hmc_util.py:637-705.  Returns true when a step-size search
   // (find_heuristic_step_size) was started and the transition tail must wait for it.
-  __device__ bool adapt(int t, float accept_prob) {
+  __device__ __noinline__ bool adapt(int t, float accept_prob) {
     if (!pre_a_valid) split2(Key{s.adapt_key[0], s.adapt_key[1]}, part, pre_a_nk, pre_a_kss);  // :656
     pre_a_valid = 0;
     const Key nk = pre_a_nk, kss = pre_a_kss;
@@ -492,7 +496,7 @@ struct Sampler {
   }
 
   // true: a leapfrog was started (NEED_GRAD); false: the search is over (s.step_size set)
-  __device__ bool frss_try() {
+  __device__ __noinline__ bool frss_try() {
     const bool not_small = (fr_step > FLT_MIN) || (fr_dir >= 0);   // :373
     const bool not_large = (fr_step < FLT_MAX) || (fr_dir <= 0);   // :375
     const bool go = not_small && not_large && ((fr_last_dir == 0) || (fr_dir == fr_last_dir));
@@ -515,7 +519,7 @@ struct Sampler {
     return true;
   }
 
-  __device__ StepResult advance_frss(float U) {
+  __device__ __noinline__ StepResult advance_frss(float U) {
     finish_leapfrog();
     const float e_new = kinetic(LR, LV) + U;
     const float dE = e_new - fr_e_cur;
@@ -650,13 +654,17 @@ struct Sampler {
   // Leaf-level randomness of _iterative_build_subtree (hmc_util.py:1005, :804): does
   // not depend on the gradient, so a kernel may call this while the gradient is still
   // being computed.
-  __device__ __forceinline__ void prefetch_rng() {
+  __device__ __forceinline__ void prefetch_leaf_rng() {
     if (phase == PH_TREE && !pre_valid) {
       Key tkey;
       split2(sub_key, part, pre_sub_key, tkey);
       pre_u = uniform01(tkey, part);
       pre_valid = 1;
     }
+  }
+
+  __device__ void prefetch_rng() {
+    prefetch_leaf_rng();
     if (phase != PH_TREE && phase != PH_HMC) return;
     if (phase == PH_TREE && !pre_d_valid) {
       compute_doubling_rng(tree_key, pre_d);
@@ -705,81 +713,226 @@ struct Sampler {
     B200MC_FOR_D r[d * es] = ms[d * es] * eps[d * es];
   }
 
-  // ------------------------------------------------------------------ NUTS: one leaf
-  __device__ StepResult advance_tree(float U) {
-    // 1. finish the leapfrog, energy test (_build_basetree, hmc_util.py:863-875)
-    B200MC_STAMP(t0_);
-    finish_leapfrog();
-    const float e_new = U + kinetic(LR, LV);
-    float dE = e_new - e0;
-    if (isnan(dE)) dE = INFINITY;
+  // Part B of the fused leaf step: fold the leaf (position fz, gradient fg, energy f_e_new)
+  // into the subtree -- uniform / multinomial kernel, hmc_util.py:749-753, :1020-1032.
+  __device__ void leaf_deferred() {
+    deferred = 0;
+    const float dE = f_dE;
     const float wleaf = -dE;
     const int leaf_div = dE > P->max_delta_energy;
     const float acc = fminf(expf(-dE), 1.0f);
-
-    // 2. fold the leaf into the subtree (uniform / multinomial kernel, :749-753, :1020-1032)
-    B200MC_STAMP(t1_);
-    B200MC_ACC(0, t0_, t1_);
-    prefetch_rng();
+    prefetch_leaf_rng();
     sub_key = pre_sub_key;
     pre_valid = 0;
-    const int leaf_idx = s_n;
+    bool take = true;
     if (s_n == 0) {
       s_w = wleaf; s_div = leaf_div; s_sum_acc = acc;
-      s_prop_pe = U; s_prop_energy = e_new;
-      copy(SZ_PROP, LZ); copy(SG_PROP, LG); copy(S_RSUM, LR);
+      s_prop_pe = f_U; s_prop_energy = f_e_new;
       s_n = 1;
     } else {
       const float p = 1.0f / (1.0f + expf(-(wleaf - s_w)));  // expit
-      const bool take = pre_u < p;
+      take = pre_u < p;
       if (take) {
-        s_prop_pe = U; s_prop_energy = e_new;
-        copy(SZ_PROP, LZ); copy(SG_PROP, LG);
+        s_prop_pe = f_U; s_prop_energy = f_e_new;
       }
       s_w = logaddexp_f32(s_w, wleaf);
       s_div = leaf_div;
       s_sum_acc = s_sum_acc + acc;
       s_n += 1;
-      float* rs = v(S_RSUM);
-      const float* r = v(LR);
-      B200MC_FOR_D rs[d * es] = rs[d * es] + r[d * es];
     }
+    if (take) {
+      const int lane = g.lane();
+      float *sz = v(SZ_PROP), *sg = v(SG_PROP);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int d = lane + 32 * k;
+        if (d < D) {
+          sz[d] = fz[k];
+          sg[d] = fg[k];
+        }
+      }
+    }
+  }
 
-    // 3. checkpoints and iterative U-turn test (:941-981, :1034-1058)
-    B200MC_STAMP(t2_);
-    B200MC_ACC(1, t1_, t2_);
-    const int idx_max = __popc(leaf_idx >> 1);
-    const int num_sub = __popc(((~leaf_idx) & (leaf_idx + 1)) - 1);
-    const int idx_min = idx_max - num_sub + 1;
-    if ((leaf_idx & 1) == 0) {
-      float *cr = ckpt_r(idx_max), *crs = ckpt_rs(idx_max);
-      const float *r = v(LR), *rs = v(S_RSUM);
-      B200MC_FOR_D {
-        cr[d * es] = r[d * es];
-        crs[d * es] = rs[d * es];
-      }
-      if (dense) {
-        float* cv_ = ckpt_v(idx_max);
-        const float* lv = v(LV);
-        B200MC_FOR_D cv_[d * es] = lv[d * es];
-      }
-    }
+  // ------------------------------------------------------------------ NUTS: one leaf
+  __device__ StepResult advance_tree(float U) {
     bool sub_turning = false;
-    for (int i = idx_max; i >= idx_min && !sub_turning; --i)
-      sub_turning = is_turning(ckpt_r(i), v(LR), v(S_RSUM), ckpt_rs(i), ckpt_r(i), ckpt_v(i), v(LV));
+    if (G::kRegVec && !dense && D <= 128) {
+      // ---- steps 1-4 fused for one-chain-per-warp groups: the leaf's vectors stay in
+      // registers (<= 4 elements per lane).  Part A is the critical path to the next point:
+      // finish the leapfrog, energy and divergence test, checkpoint U-turn tests, next half
+      // step.  Part B (multinomial fold, proposal copy: leaf_deferred) does not influence the
+      // next point when the subtree continues, so a caller may run it AFTER handing the
+      // point to whoever computes the gradient.  Same arithmetic, same order as below.
+      B200MC_STAMP(t0_);
+      const int lane = g.lane();
+      float *pLZ = v(LZ), *pLR = v(LR), *pRS = v(S_RSUM);
+      const float *pLG = v(LG), *pIM = v(IMM);
+      const float hs = 0.5f * eps_s;
+      float r[4], im[4], rs[4];
+      float kacc = 0.f;
+      const int leaf_idx = s_n;
+      const bool first = (s_n == 0);
+      const int idx_max = __popc(leaf_idx >> 1);
+      const int num_sub = __popc(((~leaf_idx) & (leaf_idx + 1)) - 1);
+      const int idx_min = idx_max - num_sub + 1;
+      const bool even = (leaf_idx & 1) == 0;
+      {
+        float *cr = ckpt_r(idx_max), *crs = ckpt_rs(idx_max);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int d = lane + 32 * k;
+          r[k] = 0.f; im[k] = 0.f; rs[k] = 0.f; fz[k] = 0.f; fg[k] = 0.f;
+          if (d < D) {
+            fg[k] = pLG[d];
+            im[k] = pIM[d];
+            fz[k] = pLZ[d];
+            const float t = hs * fg[k];
+            r[k] = pLR[d] - t;                 // finish_leapfrog, hmc_util.py:306-308
+            const float vv = im[k] * r[k];
+            kacc += vv * r[k];
+            rs[k] = first ? r[k] : pRS[d] + r[k];
+            pRS[d] = rs[k];
+            if (even) {
+              cr[d] = r[k];
+              crs[d] = rs[k];
+            }
+          }
+        }
+      }
+      f_U = U;
+      f_e_new = U + 0.5f * g.sum(kacc);
+      float dE = f_e_new - e0;
+      if (isnan(dE)) dE = INFINITY;
+      f_dE = dE;
+      const int leaf_div = dE > P->max_delta_energy;
+      B200MC_STAMP(t1_);
+      B200MC_ACC(0, t0_, t1_);
+      for (int i = idx_max; i >= idx_min && !sub_turning; --i) {
+        const float *cr = ckpt_r(i), *crs = ckpt_rs(i);
+        float la = 0.f, ra = 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int d = lane + 32 * k;
+          if (d < D) {
+            const float l = cr[d];
+            float sv = rs[k] - crs[d];
+            sv = sv + l;
+            const float h = (l + r[k]) / 2.0f;
+            const float sp = sv - h;
+            const float vl = im[k] * l, vr = im[k] * r[k];
+            la += vl * sp;
+            ra += vr * sp;
+          }
+        }
+        g.sum2(la, ra);
+        sub_turning = (la <= 0.f) | (ra <= 0.f);
+      }
+      B200MC_STAMP(t3_);
+      B200MC_ACC(2, t1_, t3_);
+      if (s_n + 1 < (1 << depth) && !sub_turning && !leaf_div) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {  // half_step of the next leaf, hmc_util.py:297-302
+          const int d = lane + 32 * k;
+          if (d < D) {
+            const float t = hs * fg[k];
+            const float rn = r[k] - t;
+            pLR[d] = rn;
+            const float vv = im[k] * rn;
+            const float dz = eps_s * vv;
+            pLZ[d] = fz[k] + dz;
+          }
+        }
+        g.sync();
+        B200MC_STAMP(t4_);
+        B200MC_ACC(3, t3_, t4_);
+        B200MC_ACC(4, 0, 1);
+        deferred = 1;  // leaf_deferred() still has to fold this leaf into the subtree
+        return NEED_GRAD;
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int d = lane + 32 * k;
+        if (d < D) pLR[d] = r[k];
+      }
+      leaf_deferred();
+      g.sync();
+    } else {
+      // 1. finish the leapfrog, energy test (_build_basetree, hmc_util.py:863-875)
+      B200MC_STAMP(t0_);
+      finish_leapfrog();
+      const float e_new = U + kinetic(LR, LV);
+      float dE = e_new - e0;
+      if (isnan(dE)) dE = INFINITY;
+      const float wleaf = -dE;
+      const int leaf_div = dE > P->max_delta_energy;
+      const float acc = fminf(expf(-dE), 1.0f);
 
-    // 4. keep extending the subtree? (_cond_fn, :999-1001)
-    B200MC_STAMP(t3_);
-    B200MC_ACC(2, t2_, t3_);
-    if (s_n < (1 << depth) && !sub_turning && !s_div) {
-      half_step();
-      B200MC_STAMP(t4_);
-      B200MC_ACC(3, t3_, t4_);
-      B200MC_ACC(4, 0, 1);
-      return NEED_GRAD;
+      // 2. fold the leaf into the subtree (uniform / multinomial kernel, :749-753, :1020-1032)
+      B200MC_STAMP(t1_);
+      B200MC_ACC(0, t0_, t1_);
+      prefetch_leaf_rng();
+      sub_key = pre_sub_key;
+      pre_valid = 0;
+      const int leaf_idx = s_n;
+      if (s_n == 0) {
+        s_w = wleaf; s_div = leaf_div; s_sum_acc = acc;
+        s_prop_pe = U; s_prop_energy = e_new;
+        copy(SZ_PROP, LZ); copy(SG_PROP, LG); copy(S_RSUM, LR);
+        s_n = 1;
+      } else {
+        const float p = 1.0f / (1.0f + expf(-(wleaf - s_w)));  // expit
+        const bool take = pre_u < p;
+        if (take) {
+          s_prop_pe = U; s_prop_energy = e_new;
+          copy(SZ_PROP, LZ); copy(SG_PROP, LG);
+        }
+        s_w = logaddexp_f32(s_w, wleaf);
+        s_div = leaf_div;
+        s_sum_acc = s_sum_acc + acc;
+        s_n += 1;
+        float* rs = v(S_RSUM);
+        const float* r = v(LR);
+        B200MC_FOR_D rs[d * es] = rs[d * es] + r[d * es];
+      }
+
+      // 3. checkpoints and iterative U-turn test (:941-981, :1034-1058)
+      B200MC_STAMP(t2_);
+      B200MC_ACC(1, t1_, t2_);
+      const int idx_max = __popc(leaf_idx >> 1);
+      const int num_sub = __popc(((~leaf_idx) & (leaf_idx + 1)) - 1);
+      const int idx_min = idx_max - num_sub + 1;
+      if ((leaf_idx & 1) == 0) {
+        float *cr = ckpt_r(idx_max), *crs = ckpt_rs(idx_max);
+        const float *r = v(LR), *rs = v(S_RSUM);
+        B200MC_FOR_D {
+          cr[d * es] = r[d * es];
+          crs[d * es] = rs[d * es];
+        }
+        if (dense) {
+          float* cv_ = ckpt_v(idx_max);
+          const float* lv = v(LV);
+          B200MC_FOR_D cv_[d * es] = lv[d * es];
+        }
+      }
+      for (int i = idx_max; i >= idx_min && !sub_turning; --i)
+        sub_turning = is_turning(ckpt_r(i), v(LR), v(S_RSUM), ckpt_rs(i), ckpt_r(i), ckpt_v(i), v(LV));
+
+      // 4. keep extending the subtree? (_cond_fn, :999-1001)
+      B200MC_STAMP(t3_);
+      B200MC_ACC(2, t2_, t3_);
+      if (s_n < (1 << depth) && !sub_turning && !s_div) {
+        half_step();
+        B200MC_STAMP(t4_);
+        B200MC_ACC(3, t3_, t4_);
+        B200MC_ACC(4, 0, 1);
+        return NEED_GRAD;
+      }
+
     }
 
     // 5. subtree finished: biased-progressive combine with the tree (:767-848, biased=True)
+    B200MC_STAMP(t3_);
     if (going_right) {
       copy(Z_RIGHT, LZ); copy(R_RIGHT, LR); copy(G_RIGHT, LG);
       if (dense) copy(V_RIGHT, LV);
@@ -826,7 +979,7 @@ struct Sampler {
   }
 
   // ------------------------------------------------------------------ HMC (hmc.py:364-414)
-  __device__ StepResult start_hmc(Key k_tr) {
+  __device__ __noinline__ StepResult start_hmc(Key k_tr) {
     momentum_from_eps(LR);
     copy(LZ, Z_PROP); copy(LG, G_PROP);
     mh_key = k_tr;
@@ -844,7 +997,7 @@ struct Sampler {
     return NEED_GRAD;
   }
 
-  __device__ StepResult advance_hmc(float U) {
+  __device__ __noinline__ StepResult advance_hmc(float U) {
     finish_leapfrog();
     hmc_done += 1;
     if (hmc_done < hmc_steps) {
@@ -868,7 +1021,7 @@ struct Sampler {
 
   // ------------------------------------------------------------------ initialisation
   // HMC.init (hmc.py:744-750): rng_key, rng_key_init_model = split(rng_key)
-  __device__ StepResult begin_init(Key chain_key, bool has_user_z) {
+  __device__ __noinline__ StepResult begin_init(Key chain_key, bool has_user_z) {
     Key k_run, k_init;
     split2(chain_key, part, k_run, k_init);
     s.rng_key[0] = k_run.k0; s.rng_key[1] = k_run.k1;
@@ -882,7 +1035,7 @@ struct Sampler {
   }
 
   // find_valid_initial_params body_fn, fast branch (infer/util.py:390-432)
-  __device__ void init_candidate() {
+  __device__ __noinline__ void init_candidate() {
     Key key, subkey;
     split2(init_key, part, key, subkey);
     float* z = v(LZ);
@@ -899,7 +1052,7 @@ struct Sampler {
     s.init_tries += 1;
   }
 
-  __device__ StepResult advance_init(float U) {
+  __device__ __noinline__ StepResult advance_init(float U) {
     if (!user_init) {
       const float* gr = v(LG);
       float bad = 0.f;
@@ -923,7 +1076,7 @@ struct Sampler {
 
   // init_kernel (hmc.py:335-362) + warmup_adapter.init_fn (hmc_util.py:552-594); the
   // host has put the initial mass matrix into IMM / MSQRT (diagonal) or mat(0..2) (dense).
-  __device__ StepResult init_kernel() {
+  __device__ __noinline__ StepResult init_kernel() {
     Key k_hmc, k_wa, k_adapt, k_ss;
     split3(Key{s.rng_key[0], s.rng_key[1]}, part, k_hmc, k_wa, init_mom_key);
     split2(k_wa, part, k_adapt, k_ss);
@@ -945,7 +1098,7 @@ struct Sampler {
     return after_init();
   }
 
-  __device__ StepResult after_init() {
+  __device__ __noinline__ StepResult after_init() {
     draw_momentum(init_mom_key, LR);  // value discarded by the reference except for `energy`
     if (dense) matvec(mat(0), v(LR), v(LV));
     s.energy = s.potential_energy + kinetic(LR, LV);
@@ -965,6 +1118,15 @@ struct Sampler {
 
   // The gradient of the potential at v(LZ) has been written to v(LG); U is its value.
   __device__ StepResult advance(float U) {
+    const StepResult r = advance_early(U);
+    if (deferred) leaf_deferred();
+    return r;
+  }
+
+  // advance() in two parts: when `deferred` is set on return, the next point is ready in
+  // v(LZ) but leaf_deferred() must still run before the next call (it may overlap with the
+  // gradient evaluation of that point).
+  __device__ StepResult advance_early(float U) {
     s.grad_evals += 1;
     if (phase == PH_TREE) return advance_tree(U);
     if (phase == PH_HMC) return advance_hmc(U);
