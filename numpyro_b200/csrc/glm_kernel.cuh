@@ -569,7 +569,7 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
       ++pass;
       handoff_bar();  // theta of the next pass is ready (or stop)
       // off the critical path, overlapped with the consumers' streaming of the next pass
-      if (S.deferred) S.leaf_deferred();
+      if (S.deferred) S.run_deferred();
       if (sres == NEED_GRAD) S.prefetch_rng();
     }
     if (lane == 0 && cta == 0) {

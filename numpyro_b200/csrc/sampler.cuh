@@ -113,7 +113,8 @@ struct Sampler {
   Key pre_t_rng_key, pre_t_k_tr, pre_a_nk, pre_a_kss;
   // leaf state parked between part A and part B of the fused leaf step
   float fz[4], fg[4], f_U, f_e_new, f_dE;
-  int deferred;
+  int deferred;  // 0 none, 1 leaf fold, 2 subtree end + doubling state, 3 transition end
+  bool d_sub_turning, d_tree_turning;
   float u_top;
   // HMC
   int hmc_steps, hmc_done;
@@ -632,7 +633,8 @@ struct Sampler {
   }
 
   // build_tree._body_fn (hmc_util.py:1159-1176) + _double_tree head (:920)
-  __device__ void next_doubling() {
+  // the state part of next_doubling (no vector work)
+  __device__ void next_doubling_state() {
     if (!pre_d_valid) compute_doubling_rng(tree_key, pre_d);
     pre_d_valid = 0;
     tree_key = pre_d.tree_key;
@@ -643,6 +645,10 @@ struct Sampler {
     s_n = 0;
     pre_valid = 0;
     eps_s = going_right ? s.step_size : -s.step_size;
+  }
+
+  __device__ void next_doubling() {
+    next_doubling_state();
     if (going_right) {
       copy(LZ, Z_RIGHT); copy(LR, R_RIGHT); copy(LG, G_RIGHT);
     } else {
@@ -754,6 +760,38 @@ struct Sampler {
     }
   }
 
+  // _combine_tree(biased=True) minus the end / r_sum merge: transition kernel, proposal
+  // choice and the scalar tree state (hmc_util.py:756-764, :796-848)
+  __device__ void combine_bookkeeping(bool sub_turning, bool tree_turning) {
+    float p = expf(s_w - weight);
+    p = (sub_turning || s_div) ? 0.0f : fminf(p, 1.0f);
+    if (u_top < p) {
+      copy(Z_PROP, SZ_PROP); copy(G_PROP, SG_PROP);
+      prop_pe = s_prop_pe; prop_energy = s_prop_energy;
+    }
+    depth += 1;
+    weight = logaddexp_f32(weight, s_w);
+    diverging = s_div;
+    turning = tree_turning;
+    sum_acc = sum_acc + s_sum_acc;
+    nprop += s_n;
+  }
+
+  // What the critical path of advance_early left undone (see `deferred`).
+  __device__ void run_deferred() {
+    const int what = deferred;
+    deferred = 0;
+    if (what == 1) {
+      leaf_deferred();
+    } else if (what == 2) {  // a subtree ended and the next doubling's first point is out
+      leaf_deferred();
+      combine_bookkeeping(d_sub_turning, d_tree_turning);
+      next_doubling_state();
+    } else if (what == 3) {  // a transition ended and the next one's first point is out
+      finish_transition(sum_acc / (float)nprop, nprop, diverging);
+    }
+  }
+
   // ------------------------------------------------------------------ NUTS: one leaf
   __device__ StepResult advance_tree(float U) {
     bool sub_turning = false;
@@ -850,13 +888,102 @@ struct Sampler {
         deferred = 1;  // leaf_deferred() still has to fold this leaf into the subtree
         return NEED_GRAD;
       }
+      // ---- the subtree is finished.  Critical path first: merge the tree ends, the
+      // tree-level U-turn test (:710-746 on the merged tree) and, if the tree doubles again,
+      // the first half step of the next doubling; the bookkeeping follows in run_deferred().
+      {
+        float *ze = v(going_right ? Z_RIGHT : Z_LEFT), *re = v(going_right ? R_RIGHT : R_LEFT),
+              *ge = v(going_right ? G_RIGHT : G_LEFT), *pSUM = v(R_SUM);
+        const float* ro = v(going_right ? R_LEFT : R_RIGHT);
+        float la = 0.f, ra = 0.f;
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int d = lane + 32 * k;
-        if (d < D) pLR[d] = r[k];
+        for (int k = 0; k < 4; ++k) {
+          const int d = lane + 32 * k;
+          if (d < D) {
+            pLR[d] = r[k];
+            ze[d] = fz[k]; re[d] = r[k]; ge[d] = fg[k];
+            const float rsum = pSUM[d] + rs[k];
+            pSUM[d] = rsum;
+            const float o = ro[d];
+            const float l = going_right ? o : r[k], rr_ = going_right ? r[k] : o;
+            const float h = (l + rr_) / 2.0f;
+            const float sp = rsum - h;
+            const float vl = im[k] * l, vr = im[k] * rr_;
+            la += vl * sp;
+            ra += vr * sp;
+          }
+        }
+        g.sum2(la, ra);
+        const bool tree_turning = sub_turning | ((la <= 0.f) | (ra <= 0.f));
+        d_sub_turning = sub_turning;
+        d_tree_turning = tree_turning;
+        if (depth + 1 < max_depth_cur && !tree_turning && !leaf_div) {
+          if (!pre_d_valid) {
+            compute_doubling_rng(tree_key, pre_d);
+            pre_d_valid = 1;
+          }
+          const bool gr = pre_d.going_right != 0;
+          const float e2 = gr ? s.step_size : -s.step_size;
+          const float hs2 = 0.5f * e2;
+          const float *zs_ = v(gr ? Z_RIGHT : Z_LEFT), *rs_ = v(gr ? R_RIGHT : R_LEFT),
+                      *gs_ = v(gr ? G_RIGHT : G_LEFT);
+          float* wLG = v(LG);
+          g.sync();
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {  // next_doubling's copies + half_step
+            const int d = lane + 32 * k;
+            if (d < D) {
+              const float gg = gs_[d];
+              wLG[d] = gg;
+              const float t = hs2 * gg;
+              const float rn = rs_[d] - t;
+              pLR[d] = rn;
+              const float vv = im[k] * rn;
+              const float dz = e2 * vv;
+              pLZ[d] = zs_[d] + dz;
+            }
+          }
+          g.sync();
+          deferred = 2;
+          return NEED_GRAD;
+        }
+        // the transition ends here
+        leaf_deferred();
+        combine_bookkeeping(sub_turning, tree_turning);
+        s.potential_energy = prop_pe;
+        s.energy = prop_energy;
+        if (s.i >= P->num_warmup && iters_left > 1) {
+          // sampling phase: nothing adapts between transitions, so the first point of the
+          // next transition is known now (prefetched momentum draw and direction);
+          // finish_transition / start_transition run in run_deferred() and recompute it
+          // bit-identically.
+          if (!pre_t_valid) {
+            compute_transition_rng();
+            pre_t_valid = 1;
+          }
+          const bool gr = pre_t_d.going_right != 0;
+          const float e2 = gr ? s.step_size : -s.step_size;
+          const float hs2 = 0.5f * e2;
+          const float *zp = v(Z_PROP), *gp = v(G_PROP), *ms = v(MSQRT), *eps = v(EPS_NEXT);
+          g.sync();
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int d = lane + 32 * k;
+            if (d < D) {
+              const float r0 = ms[d] * eps[d];
+              const float t = hs2 * gp[d];
+              const float rn = r0 - t;
+              const float vv = im[k] * rn;
+              const float dz = e2 * vv;
+              pLZ[d] = zp[d] + dz;
+            }
+          }
+          g.sync();
+          deferred = 3;
+          return NEED_GRAD;
+        }
+        return finish_transition(sum_acc / (float)nprop, nprop, diverging);
       }
-      leaf_deferred();
-      g.sync();
     } else {
       // 1. finish the leapfrog, energy test (_build_basetree, hmc_util.py:863-875)
       B200MC_STAMP(t0_);
@@ -945,21 +1072,10 @@ struct Sampler {
       const float* srs = v(S_RSUM);
       B200MC_FOR_D rs[d * es] = rs[d * es] + srs[d * es];
     }
-    float p = expf(s_w - weight);
-    p = (sub_turning || s_div) ? 0.0f : fminf(p, 1.0f);
     const bool tree_turning =
         sub_turning | is_turning(v(R_LEFT), v(R_RIGHT), v(R_SUM), nullptr, nullptr, v(V_LEFT),
                                  v(V_RIGHT));
-    if (u_top < p) {
-      copy(Z_PROP, SZ_PROP); copy(G_PROP, SG_PROP);
-      prop_pe = s_prop_pe; prop_energy = s_prop_energy;
-    }
-    depth += 1;
-    weight = logaddexp_f32(weight, s_w);
-    diverging = s_div;
-    turning = tree_turning;
-    sum_acc = sum_acc + s_sum_acc;
-    nprop += s_n;
+    combine_bookkeeping(sub_turning, tree_turning);
 
     // 6. double again? (build_tree._cond_fn, :1155-1157)
     B200MC_STAMP(t5_);
@@ -1119,7 +1235,7 @@ struct Sampler {
   // The gradient of the potential at v(LZ) has been written to v(LG); U is its value.
   __device__ StepResult advance(float U) {
     const StepResult r = advance_early(U);
-    if (deferred) leaf_deferred();
+    if (deferred) run_deferred();
     return r;
   }
 
