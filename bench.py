@@ -280,12 +280,15 @@ def run_own(args):
     col = _lib.Collect(n_keep=T_, z_dev=z_buf.ptr, num_steps_dev=ns_buf.ptr)
     ev0, ev1 = lib.b200mc_event_create(), lib.b200mc_event_create()
 
+    draws = []
+
     def device_step():
         _lib.check(lib.b200mc_event_record(ev0, None))
         _lib.check(lib.b200mc_sample(kern._handle, T_, 0, 1, C.byref(col), None))
         _lib.check(lib.b200mc_event_record(ev1, None))
         ms = C.c_float()
         _lib.check(lib.b200mc_event_elapsed_ms(ev0, ev1, C.byref(ms)))
+        draws.append(z_buf.numpy()[:, 0, :].copy())
         return float(ms.value), int(ns_buf.numpy().sum())
 
     for _ in range(args.warmup):
@@ -296,11 +299,20 @@ def run_own(args):
     clocks = ClockSampler(local) if rank == 0 else None
     barrier()
     step_ms, step_grads = [], []
+    draws.clear()
     for _ in range(args.steps):
         ms, gsum = device_step()
         step_ms.append(ms)
         step_grads.append(gsum)
     barrier()
+    # second half of the metric: min bulk ESS of this rank's chain over the timed draws
+    from numpyro_b200.diagnostics import bulk_effective_sample_size, effective_sample_size
+    chain_draws = np.concatenate(draws, axis=0)[None]  # [1 chain, steps*T, D]
+    ess = None
+    if chain_draws.shape[1] >= 8:
+        ess = {"min_bulk_ess": float(np.min(bulk_effective_sample_size(chain_draws))),
+               "min_n_eff": float(np.min(effective_sample_size(chain_draws))),
+               "draws": int(chain_draws.shape[1])}
     launches = lib.b200mc_kernel_launches() - launches0
     _lib.check(lib.b200mc_get_profile(kern._handle, prof, 0))
     passes = max(1, int(prof[4]))
@@ -312,6 +324,12 @@ def run_own(args):
                                 "advance_fast_leaf": float(prof[6]) / passes,
                                 "advance_other": float(prof[7]) / passes}
     total_ms = max_over_ranks(sum(step_ms))
+    if ess is not None:
+        # chains on different ranks are independent: ESS adds; a row-sharded chain is ONE chain
+        tot = ess["min_bulk_ess"] if rows else sum_over_ranks(ess["min_bulk_ess"])
+        ess.update({"metric": "min_bulk_ess_per_sec", "value": tot / (total_ms * 1e-3),
+                    "unit": "ESS/s", "note": "device-timed sampling phase, rank-normalised "
+                    "split-chain bulk ESS (SURVEY 8d); min_n_eff is the reference's estimator"})
     total_grads = float(sum(step_grads)) if rows else sum_over_ranks(float(sum(step_grads)))
     value = total_grads / (total_ms * 1e-3)
 
@@ -379,7 +397,7 @@ def run_own(args):
                                        else f"chains x{world}"),
                        "l2": "inputs 128.4 MB per pass > 126 MB L2, streamed once per grad eval"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-            "clocks": clk, "adapt_seconds": adapt_s,
+            "clocks": clk, "adapt_seconds": adapt_s, "ess": ess,
             "cta0_cycles_per_grad_eval": breakdown,
             "mean_tree_size": float(np.mean(step_grads)) / T_,
         }

@@ -46,7 +46,7 @@ struct b200mc_handle {
   float* work = nullptr;
   int mode = 0, c_pad = 0;
   // glm
-  int glm_ctas = 0, glm_nt_total = 0, glm_stages = 0, glm_smem = 0;
+  int glm_ctas = 0, glm_nt_total = 0, glm_stages = 0, glm_pinned = 0, glm_smem = 0;
   unsigned char* glm_xt = nullptr;  // re-tiled X + labels
   float* partials = nullptr;     // [2][ctas][D+1]
   unsigned* counters = nullptr;  // [0] arrive, [3] error
@@ -245,7 +245,7 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   ACK(alloc((void**)&h->cv.welford_m2, vec_bytes));
   if (c.dense_mass) ACK(alloc((void**)&h->cv.dense, sizeof(float) * 4 * (size_t)C * D * D));
 
-  const int nslots = num_slots(P.max_depth);
+  const int nslots = num_slots(P.max_depth, P.dense_mass);
   if (c.family == B200MC_LOGISTIC) {
     if (D > kGlmMaxD) { b200mc_destroy(h); return fail("logistic: D=%d > %d not supported", D, kGlmMaxD); }
     if (!c.data1_dev) { b200mc_destroy(h); return fail("logistic: labels missing"); }
@@ -262,17 +262,40 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
     ACK(cudaDeviceSynchronize());
     int ctas = nt_total < h->num_sms ? nt_total : h->num_sms;
     h->glm_ctas = ctas;
-    // ring stages: a multiple of the consumer-warp count (every stage is owned by one
-    // warp) and at most one per producer lane, as many as shared memory allows
-    int ns = kGlmMaxStages / kGlmConsumerWarps * kGlmConsumerWarps;
-    while (ns > kGlmConsumerWarps && glm_smem_layout(D, ns, P.max_depth).total > h->max_smem)
-      ns -= kGlmConsumerWarps;
-    if (glm_smem_layout(D, ns, P.max_depth).total > h->max_smem) {
+    // Shared memory holds a TMA ring (stages: a multiple of the consumer-warp count -- every
+    // stage is owned by one warp -- two per warp when they fit) and, in what is left, tiles
+    // PINNED for the whole launch (at most one per producer lane): they never go through
+    // L2 again, which also shrinks the L2 working set of the ping-pong stream.
+    // Budget: the 196 KB carve-out step (1 KB of it is reserved by the system), not the full
+    // 227 KB -- the next step leaves 28 KB of L1, too little for the control warp's stack:
+    // measured +4.4k cycles per sampler step (profiles/r01_glm_smem_sweep.txt).
+    int budget = 196 * 1024 - 1024;
+    if (const char* e = getenv("B200MC_GLM_SMEM_MAX")) budget = atoi(e);
+    if (budget > h->max_smem ||
+        glm_smem_layout(D, kGlmConsumerWarps, 0, P.max_depth, P.dense_mass).total > budget)
+      budget = h->max_smem;
+    auto fits = [&](int ns_, int np_) {
+      return glm_smem_layout(D, ns_, np_, P.max_depth, P.dense_mass).total <= budget;
+    };
+    int ns = 2 * kGlmConsumerWarps;
+    if (const char* e = getenv("B200MC_GLM_STAGES")) {  // tuning knobs
+      const int v = atoi(e) / kGlmConsumerWarps * kGlmConsumerWarps;
+      if (v >= kGlmConsumerWarps && v <= kGlmMaxStages) ns = v;
+    }
+    while (ns > kGlmConsumerWarps && !fits(ns, 0)) ns -= kGlmConsumerWarps;
+    if (!fits(ns, 0)) {
       b200mc_destroy(h);
       return fail("logistic: shared memory layout does not fit");
     }
+    int np = 0;
+    while (np < kGlmMaxStages && fits(ns, np + 1)) ++np;
+    if (const char* e = getenv("B200MC_GLM_PINNED")) {
+      const int v = atoi(e);
+      if (v >= 0 && v < np) np = v;
+    }
     h->glm_stages = ns;
-    h->glm_smem = glm_smem_layout(D, ns, P.max_depth).total;
+    h->glm_pinned = np;
+    h->glm_smem = glm_smem_layout(D, ns, np, P.max_depth, P.dense_mass).total;
     ACK(cudaFuncSetAttribute(glm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     int occ = 0;
     ACK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, glm_kernel, kGlmThreads, h->glm_smem));
@@ -393,6 +416,7 @@ static int launch_glm(b200mc_handle* h, const CollectSpec& col, const uint32_t* 
   L.N = h->cfg.N; L.D = h->D;
   L.nt_total = h->glm_nt_total;
   L.n_stages = h->glm_stages;
+  L.n_pinned = h->glm_pinned;
   L.reverse_odd = h->glm_reverse;
   L.partials = h->partials;
   L.arrive = h->counters + 0;

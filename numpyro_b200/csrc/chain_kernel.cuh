@@ -27,7 +27,7 @@ template <int MODE>
 __global__ void chain_kernel(const __grid_constant__ ChainLaunch L) {
   __shared__ float red_scratch[64];
   const int D = L.P.D;
-  const int nslots = num_slots(L.P.max_depth);
+  const int nslots = num_slots(L.P.max_depth, L.P.dense_mass);
   int chain;
   float* base;
   long sstride;

@@ -60,6 +60,7 @@ struct GlmLaunch {
   int N, D;
   int nt_total;        // ceil(N / 32)
   int n_stages;        // multiple of kGlmConsumerWarps, <= kGlmMaxStages
+  int n_pinned;        // tiles per CTA that live in shared memory for the whole launch
   int reverse_odd;     // sweep odd passes backwards (L2 reuse)
   // grid-level exchange (global memory)
   float* partials;       // [2][nCTA][glm_partial_stride(D)], double-buffered by pass parity
@@ -286,21 +287,22 @@ __device__ __forceinline__ float warp_transpose_reduce32(float (&a)[32]) {
 
 // ---------------------------------------------------------------- shared-memory layout
 struct GlmSmem {
-  int stage_bytes, off_full, off_empty, off_theta, off_red, off_red2, off_work, off_flags, total;
+  int stage_bytes, off_full, off_empty, off_pin, off_theta, off_red, off_red2, off_work, off_flags, total;
 };
 constexpr int kGlmRedGroups = 16;  // grid reduction: CTAs are summed in strided groups
 
-__host__ __device__ inline GlmSmem glm_smem_layout(int D, int n_stages, int max_depth) {
+__host__ __device__ inline GlmSmem glm_smem_layout(int D, int n_stages, int n_pinned, int max_depth, int dense) {
   GlmSmem s;
   const int ps = glm_partial_stride(D);
   s.stage_bytes = glm_tile_bytes(D);  // multiple of 16
-  int o = n_stages * s.stage_bytes;
+  int o = (n_stages + n_pinned) * s.stage_bytes;  // ring stages, then the pinned tiles
   s.off_full = o;  o += kGlmMaxStages * 8;
   s.off_empty = o; o += kGlmMaxStages * 8;
+  s.off_pin = o;   o += kGlmMaxStages * 8;
   s.off_theta = o; o += kGlmMaxD * 4;  // zero-padded
   s.off_red = o;   o += kGlmConsumerWarps * ps * 4;
   s.off_red2 = o;  o += kGlmRedGroups * ps * 4;
-  s.off_work = o;  o += num_slots(max_depth) * D * 4;
+  s.off_work = o;  o += num_slots(max_depth, dense) * D * 4;
   o = (o + 15) & ~15;
   s.off_flags = o; o += 16;
   s.total = o;
@@ -323,35 +325,56 @@ __device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
 // log-likelihood in red[warp][0..D].  The CTA's tile stream is numbered p = 0, 1, ... over
 // all passes; position p is consumed by warp p % W from stage p % NS.  NS = m * W, so warp w
 // only ever touches stages w, w + W, ..., w + (m-1) W, strictly in phase order (si, ph).
+// `nt` counts the CTA's STREAMED tiles; its last `n_pin` tiles (local index nt + k) were
+// loaded once into the slots behind the ring and are consumed from there in every pass
+// (slot k by warp k % W), after the warp has put its ring stages back in flight.
 template <int GT>
 __device__ __forceinline__ void glm_consume_pass(const GlmLaunch& L, unsigned char* smem,
                                                  const GlmSmem& lay, int warp, long& p_next,
                                                  long p_begin, long p_end, int& si, uint32_t& ph,
-                                                 int m, int tile0, int nt, bool rev) {
+                                                 int m, int tile0, int nt, bool rev, int n_pin) {
   constexpr int NA = GT ? 4 * GT : 128;
   const int lane = threadIdx.x & 31;
   const int G = glm_groups(L.D), PS = glm_partial_stride(L.D);
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + lay.off_full);
   uint64_t* empty = reinterpret_cast<uint64_t*>(smem + lay.off_empty);
+  uint64_t* pin = reinterpret_cast<uint64_t*>(smem + lay.off_pin);
   const float4* th4 = reinterpret_cast<const float4*>(smem + lay.off_theta);
   float acc[NA];
 #pragma unroll
   for (int k = 0; k < NA; ++k) acc[k] = 0.f;
   float ll = 0.f;
-  for (; p_next < p_end; p_next += kGlmConsumerWarps) {
-    const int stage = warp + si * kGlmConsumerWarps;
-    mbar_wait(&full[stage], ph);
-    const unsigned char* sp = smem + (long)stage * lay.stage_bytes;
-    const int j = (int)(p_next - p_begin);
-    const int tile = tile0 + (rev ? (nt - 1 - j) : j);
+  int pin_k = warp, done = 0;
+  for (;;) {
+    const bool ring_left = p_next < p_end;
+    const bool pin_now = pin_k < n_pin && (done >= m || !ring_left);
+    if (!pin_now && !ring_left) break;
+    const unsigned char* sp;
+    int tile, stage = -1;
+    if (pin_now) {
+      mbar_wait(&pin[pin_k], 0u);  // completes once per launch
+      sp = smem + (long)(L.n_stages + pin_k) * lay.stage_bytes;
+      tile = tile0 + nt + pin_k;
+      pin_k += kGlmConsumerWarps;
+    } else {
+      stage = warp + si * kGlmConsumerWarps;
+      mbar_wait(&full[stage], ph);
+      sp = smem + (long)stage * lay.stage_bytes;
+      const int j = (int)(p_next - p_begin);
+      tile = tile0 + (rev ? (nt - 1 - j) : j);
+    }
     const int rows = (tile == L.nt_total - 1) ? (L.N - 32 * tile) : 32;
     glm_tile<GT>(reinterpret_cast<const float4*>(sp), sp + G * 512, rows, th4, G, acc, ll);
     __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[stage]);
-    if (++si == m) {
-      si = 0;
-      ph ^= 1u;
+    if (stage >= 0) {
+      if (lane == 0) mbar_arrive(&empty[stage]);
+      p_next += kGlmConsumerWarps;
+      if (++si == m) {
+        si = 0;
+        ph ^= 1u;
+      }
     }
+    ++done;
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) ll += __shfl_xor_sync(0xffffffffu, ll, o);
@@ -372,7 +395,7 @@ __device__ __forceinline__ void glm_consume_pass(const GlmLaunch& L, unsigned ch
 __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_constant__ GlmLaunch L) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int D = L.D, NS = L.n_stages, PS = glm_partial_stride(D);
-  const GlmSmem lay = glm_smem_layout(D, NS, L.P.max_depth);
+  const GlmSmem lay = glm_smem_layout(D, NS, L.n_pinned, L.P.max_depth, L.P.dense_mass);
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + lay.off_full);
   uint64_t* empty = reinterpret_cast<uint64_t*>(smem + lay.off_empty);
   float* th = reinterpret_cast<float*>(smem + lay.off_theta);
@@ -384,7 +407,10 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int cta = blockIdx.x, nCTA = gridDim.x;
   const int tile0 = (int)((long)cta * L.nt_total / nCTA);
-  const int nt = (int)((long)(cta + 1) * L.nt_total / nCTA) - tile0;
+  const int nt_all = (int)((long)(cta + 1) * L.nt_total / nCTA) - tile0;
+  const int n_pin = L.n_pinned < nt_all ? L.n_pinned : nt_all;  // pinned: the last n_pin tiles
+  const int nt = nt_all - n_pin;                                 // streamed through the ring
+  uint64_t* pin = reinterpret_cast<uint64_t*>(smem + lay.off_pin);
   const long tb = lay.stage_bytes;
 
   if (threadIdx.x == 0) {
@@ -392,6 +418,7 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
       mbar_init(&full[i], 1);
       mbar_init(&empty[i], 1);
     }
+    for (int i = 0; i < L.n_pinned; ++i) mbar_init(&pin[i], 1);
     flags[0] = 0; flags[1] = 0; flags[2] = 0; flags[3] = 1;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -402,6 +429,11 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
   if (warp == kGlmProducerWarp) {
     // ================= producer warp: lane s feeds stage s, runs ahead across passes ========
     const int s = lane;
+    if (s < n_pin) {  // the pinned tiles: loaded once, stay for the whole launch
+      mbar_arrive_expect_tx(&pin[s], (uint32_t)tb);
+      tma_load_1d(smem + (long)(NS + s) * tb, L.Xt + (long)(tile0 + nt + s) * tb, (uint32_t)tb,
+                  &pin[s]);
+    }
     if (s < NS && nt > 0) {
       int pass_l = 0, j = s;
       while (j >= nt) { j -= nt; ++pass_l; }
@@ -423,6 +455,7 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
         if (p_last >= (long)flags[1] * nt) mbar_wait(&full[s], (n_issued - 1) & 1u);
       }
     }
+    if (s < n_pin) mbar_wait(&pin[s], 0u);
     return;
   }
 
@@ -559,7 +592,9 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
         sres = flags[3] ? S.advance_early(U) : FINISHED;
 #ifdef B200MC_SAMPLER_PROF
         const long long tp2 = clock64();
-        if (S.deferred) c_fast += (unsigned long long)(tp2 - tp1);
+        if (S.deferred == 1) c_fast += (unsigned long long)(tp2 - tp1);
+        else if (S.deferred == 2) { S.pc[5] += (unsigned long long)(tp2 - tp1); S.pc[1] += 1; }
+        else if (S.deferred == 3) { S.pc[6] += (unsigned long long)(tp2 - tp1); S.pc[7] += 1; }
         else c_other += (unsigned long long)(tp2 - tp1);
 #endif
       }
@@ -602,14 +637,14 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
     const long p_begin = (long)pass * nt, p_end = p_begin + nt;
     const bool rev = L.reverse_odd && (pass & 1);
 #define B200MC_GLM_CASE(GT) \
-  case GT: glm_consume_pass<GT>(L, smem, lay, warp, p_next, p_begin, p_end, si, ph, m, tile0, nt, rev); break;
+  case GT: glm_consume_pass<GT>(L, smem, lay, warp, p_next, p_begin, p_end, si, ph, m, tile0, nt, rev, n_pin); break;
     switch (G <= 16 ? G : 0) {
       B200MC_GLM_CASE(1) B200MC_GLM_CASE(2) B200MC_GLM_CASE(3) B200MC_GLM_CASE(4)
       B200MC_GLM_CASE(5) B200MC_GLM_CASE(6) B200MC_GLM_CASE(7) B200MC_GLM_CASE(8)
       B200MC_GLM_CASE(9) B200MC_GLM_CASE(10) B200MC_GLM_CASE(11) B200MC_GLM_CASE(12)
       B200MC_GLM_CASE(13) B200MC_GLM_CASE(14) B200MC_GLM_CASE(15) B200MC_GLM_CASE(16)
       default:
-        glm_consume_pass<0>(L, smem, lay, warp, p_next, p_begin, p_end, si, ph, m, tile0, nt, rev);
+        glm_consume_pass<0>(L, smem, lay, warp, p_next, p_begin, p_end, si, ph, m, tile0, nt, rev, n_pin);
         break;
     }
 #undef B200MC_GLM_CASE

@@ -45,11 +45,15 @@ enum Slot {
   LZ, LR, LG,                                              // leaf under construction; LZ = point to evaluate
   SZ_PROP, SG_PROP, S_RSUM,                                // subtree proposal / momentum sum
   IMM, MSQRT, WMEAN, WM2,                                  // adaptation vectors
-  LV, V_LEFT, V_RIGHT,                                     // dense mass: cached M^-1 r of LR, R_LEFT, R_RIGHT
   EPS_NEXT,                                                // prefetched N(0, I) draw of the next transition
-  CKPT0                                                    // r_ckpts[i], r_sum_ckpts[i], M^-1 r_ckpts[i] = CKPT0+3i+{0,1,2}
+  CKPT0                                                    // r_ckpts[i], r_sum_ckpts[i] (, M^-1 r_ckpts[i]) = CKPT0 + stride*i + {0,1(,2)}
 };
-__host__ __device__ inline int num_slots(int max_depth) { return CKPT0 + 3 * max_depth; }
+// Diagonal mass: 2 vectors per checkpoint.  Dense mass: 3 (the cached M^-1 r_ckpts[i]) plus
+// three more slots behind the checkpoints (LV, V_LEFT, V_RIGHT: cached M^-1 r of LR, R_LEFT,
+// R_RIGHT); keeping them out of the diagonal layout buys shared memory for the glm ring.
+__host__ __device__ inline int num_slots(int max_depth, int dense) {
+  return CKPT0 + (dense ? 3 * max_depth + 3 : 2 * max_depth);
+}
 
 enum Phase { PH_INIT = 0, PH_TREE, PH_HMC, PH_IDLE, PH_FAIL, PH_FRSS };
 enum StepResult { NEED_GRAD = 0, FINISHED = 1 };
@@ -99,6 +103,7 @@ struct Sampler {
   float s_w, s_sum_acc, s_prop_pe, s_prop_energy;
   // precomputed leaf-level randomness (does not depend on the gradient)
   int pre_valid;
+  int ck_stride, ck_end;  // checkpoint slot stride (2 diag / 3 dense), first slot behind them
   Key pre_sub_key;
   float pre_u;
   // doubling-level (hmc_util.py:1161-1162, :920) and transition-level (hmc.py:472, :94-102)
@@ -130,9 +135,12 @@ struct Sampler {
   Key init_mom_key;
 
   __device__ __forceinline__ float* v(int slot) const { return w + (long)slot * slot_stride; }
-  __device__ __forceinline__ float* ckpt_r(int i) const { return v(CKPT0 + 3 * i); }
-  __device__ __forceinline__ float* ckpt_rs(int i) const { return v(CKPT0 + 3 * i + 1); }
-  __device__ __forceinline__ float* ckpt_v(int i) const { return v(CKPT0 + 3 * i + 2); }
+  __device__ __forceinline__ float* ckpt_r(int i) const { return v(CKPT0 + ck_stride * i); }
+  __device__ __forceinline__ float* ckpt_rs(int i) const { return v(CKPT0 + ck_stride * i + 1); }
+  __device__ __forceinline__ float* ckpt_v(int i) const { return v(CKPT0 + 3 * i + 2); }  // dense only
+#define LV (ck_end)  // dense-only slots, see num_slots()
+#define V_LEFT (ck_end + 1)
+#define V_RIGHT (ck_end + 2)
   // dense mass: this chain's (or this replica's) four D x D matrices in global memory
   __device__ __forceinline__ float* mat(int which) const { return dn + (long)which * D * D; }
 
@@ -150,6 +158,8 @@ struct Sampler {
     P = p; g = grp; w = work; slot_stride = sstride; es_rt = estride; D = p->D;
     part = p->partitionable != 0;
     dense = p->dense_mass != 0;
+    ck_stride = dense ? 3 : 2;
+    ck_end = CKPT0 + ck_stride * p->max_depth;
     dn = nullptr;
     chain = chain_; C = C_; col = c;
     writer = true;
@@ -1252,6 +1262,9 @@ struct Sampler {
   }
 #undef B200MC_FOR_D
 #undef es
+#undef LV
+#undef V_LEFT
+#undef V_RIGHT
 };
 
 }  // namespace b200mc

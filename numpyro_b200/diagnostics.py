@@ -75,6 +75,26 @@ def effective_sample_size(x, bias=True):  # diagnostics.py:158-203
     return np.prod(x.shape[:2]) / tau
 
 
+def bulk_effective_sample_size(x):
+    """Rank-normalised split-chain bulk ESS (Vehtari et al. 2021) of ``x[chain, draw, ...]``.
+
+    Not in the reference (its ``effective_sample_size`` is the Geyer estimator on raw draws,
+    diagnostics.py:158-203); this is the harness metric of SURVEY.md 8(d): the draws are split
+    in halves, replaced by normal scores of their pooled fractional ranks, and fed through
+    the same Geyer estimator.
+    """
+    from scipy.special import ndtri
+    from scipy.stats import rankdata
+
+    x = np.asarray(x, np.float64)
+    n_half = x.shape[1] // 2
+    halves = np.concatenate([x[:, :n_half], x[:, x.shape[1] - n_half:]], axis=0)
+    flat = halves.reshape((-1,) + halves.shape[2:])
+    ranks = rankdata(flat, method="average", axis=0)
+    z = ndtri((ranks - 0.375) / (flat.shape[0] + 0.25)).reshape(halves.shape)
+    return effective_sample_size(z)
+
+
 def hpdi(x, prob=0.90, axis=0):  # diagnostics.py:206-231
     x = np.swapaxes(x, axis, 0)
     sorted_x = np.sort(x, axis=0)
