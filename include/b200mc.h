@@ -176,6 +176,14 @@ int b200mc_random_uniform(const uint32_t* key_dev, int n, float minval, float ma
 int b200mc_random_normal(const uint32_t* key_dev, int n, float* out_dev, int partitionable,
                          void* stream);
 
+/* Split-precision tensor-core contraction of the many-chain potentials (tier-2 hook):
+ * out[c][m] = sum_k A[m][k] * B[c][k] for row-major f32 A[M][K], B[Nc][K], Nc <= 256, computed
+ * as hi*hi + hi*lo + lo*hi in TF32 on tcgen05 with f32 accumulation over `splits` k-ranges.
+ * Stands where the reference has jnp.dot / matmul inside the traced potential
+ * (examples/horseshoe_regression.py:61,78; examples/covtype.py:68). */
+int b200mc_gemm3xtf32(const float* A_dev, const float* B_dev, int M, int Nc, int K, int splits,
+                      float* out_dev /*[Nc][M]*/, void* stream);
+
 /* build_adaptation_schedule (hmc_util.py:387-436), host only: writes up to cap windows,
  * returns the number of windows. */
 int b200mc_adaptation_schedule(int num_steps, int* starts_host, int* ends_host, int cap);

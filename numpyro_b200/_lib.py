@@ -87,6 +87,7 @@ SYMBOLS = {
     "b200mc_random_bits": (_i, [_vp, _i, _vp, _i, _vp]),
     "b200mc_random_uniform": (_i, [_vp, _i, _f, _f, _vp, _i, _vp]),
     "b200mc_random_normal": (_i, [_vp, _i, _vp, _i, _vp]),
+    "b200mc_gemm3xtf32": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
     "b200mc_adaptation_schedule": (_i, [_i, C.POINTER(_i), C.POINTER(_i), _i]),
     "b200mc_device_count": (_i, []),
     "b200mc_set_device": (_i, [_i]),

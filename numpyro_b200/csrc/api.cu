@@ -11,6 +11,7 @@
 
 #include "../../include/b200mc.h"
 #include "chain_kernel.cuh"
+#include "gemm3x_kernel.cuh"
 #include "glm_kernel.cuh"
 
 using namespace b200mc;
@@ -652,6 +653,72 @@ __global__ void draw_kernel(const uint32_t* key, int n, int what, float lo, floa
   if (what == 0) ((uint32_t*)out)[i] = random_bits_at(k, (uint32_t)n, (uint32_t)i, part != 0);
   else if (what == 1) ((float*)out)[i] = uniform_at(k, (uint32_t)n, (uint32_t)i, lo, hi, part != 0);
   else ((float*)out)[i] = normal_at(k, (uint32_t)n, (uint32_t)i, part != 0);
+}
+
+// ---------------------------------------------------------------- 3xTF32 GEMM (test hook)
+namespace {
+__global__ void sum_splits_kernel(const float* part, int splits, int Nc, int RA, int M, float* out) {
+  const long total = (long)Nc * M;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int c = (int)(i / M), m = (int)(i - (long)c * M);
+    float a = 0.f;
+    for (int s = 0; s < splits; ++s) a += part[((long)s * kGemmN + c) * RA + m];
+    out[i] = a;
+  }
+}
+int build_image(const float* src, int R_src, int K_src, int transpose, int R, int K,
+                unsigned char** hi, unsigned char** lo, cudaStream_t st) {
+  const size_t bytes = (size_t)R * K * 4;
+  CK(cudaMalloc((void**)hi, bytes));
+  CK(cudaMalloc((void**)lo, bytes));
+  image_build_kernel<<<1184, 256, 0, st>>>(src, R_src, K_src, transpose, R, K, *hi, *lo);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+int launch_gemm3x(const Gemm3xLaunch& L, int epi, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute(gemm3x_kernel<EPI_STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+    CK(cudaFuncSetAttribute(gemm3x_kernel<EPI_RESID>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+    attr_set = true;
+  }
+  const int grid = (L.RA / kGemmM) * L.splits;
+  if (epi == EPI_STORE) gemm3x_kernel<EPI_STORE><<<grid, kGemmThreads, kGemmSmem, st>>>(L);
+  else gemm3x_kernel<EPI_RESID><<<grid, kGemmThreads, kGemmSmem, st>>>(L);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+}  // namespace
+
+extern "C" int b200mc_gemm3xtf32(const float* A_dev, const float* B_dev, int M, int Nc, int K,
+                                 int splits, float* out_dev, void* stream) {
+  if (M <= 0 || K <= 0 || Nc <= 0 || Nc > kGemmN) return fail("gemm3xtf32: bad shape");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int RA = (M + kGemmM - 1) / kGemmM * kGemmM, Kp = (K + 31) / 32 * 32, KB = Kp / 32;
+  if (splits < 1) splits = 1;
+  if (splits > KB) splits = KB;
+  unsigned char *a_hi = nullptr, *a_lo = nullptr, *b_hi = nullptr, *b_lo = nullptr;
+  float* part = nullptr;
+  int rc = build_image(A_dev, M, K, 0, RA, Kp, &a_hi, &a_lo, st);
+  if (!rc) rc = build_image(B_dev, Nc, K, 0, kGemmN, Kp, &b_hi, &b_lo, st);
+  if (!rc && cudaMalloc((void**)&part, sizeof(float) * (size_t)splits * kGemmN * RA) != cudaSuccess)
+    rc = fail("gemm3xtf32: out of memory");
+  if (!rc) {
+    Gemm3xLaunch L = {};
+    L.a_hi = a_hi; L.a_lo = a_lo; L.b_hi = b_hi; L.b_lo = b_lo;
+    L.RA = RA; L.KB = KB; L.splits = splits; L.out = part;
+    rc = launch_gemm3x(L, EPI_STORE, st);
+  }
+  if (!rc) {
+    sum_splits_kernel<<<592, 256, 0, st>>>(part, splits, Nc, RA, M, out_dev);
+    g_launches++;
+    if (cudaGetLastError() != cudaSuccess) rc = fail("gemm3xtf32: reduce launch failed");
+  }
+  if (cudaStreamSynchronize(st) != cudaSuccess && !rc) rc = fail("gemm3xtf32: %s", cudaGetErrorString(cudaGetLastError()));
+  cudaFree(a_hi); cudaFree(a_lo); cudaFree(b_hi); cudaFree(b_lo); cudaFree(part);
+  return rc;
 }
 
 extern "C" int b200mc_threefry2x32(const uint32_t* key_dev, const uint32_t* ctr_dev,

@@ -1,0 +1,228 @@
+// Split-precision ("3xTF32") GEMM on the 5th-generation tensor cores, for the many-chain
+// potentials: once >= 64 chains share one design matrix, X.Theta and X^T.R are dense
+// contractions, not matrix-vector sweeps.
+//
+//   D[m, c] = sum_k A[m, k] * B[c, k]          (A: [RA][K], B: [256][K], both K-major)
+//
+// with every f32 operand split as x = hi + lo (TF32 each) and three tcgen05.mma per k-step,
+// hi*hi + hi*lo + lo*hi, accumulated in f32 in TMEM: the result holds f32-level accuracy
+// (~2^-22 per product) at 3 tensor-core passes.  Operands arrive as pre-swizzled "operand
+// images" (umma.cuh) through 1-D TMA bulk copies; one CTA = one 128 x 256 output tile over
+// a k-block range (split-K); warp 0 = TMA producer, warp 1 = MMA issuer (one lane) and TMEM
+// owner, warps 2..5 = epilogue (tcgen05.ld, one TMEM lane quadrant each).
+//
+// Epilogues:
+//   EPI_STORE  partial tile -> out[split][c][m] (chain-major; the consumer sums the splits in a
+//              fixed order: deterministic, no float atomics)
+//   EPI_RESID  rows are data points: turns the linear predictor into the likelihood residual
+//              dU/dl (Bernoulli logits, distributions/util.py:295-298, or Normal with the
+//              chain's precision, continuous.py:2203-2207) written straight into the hi/lo
+//              operand images of the next GEMM (X^T.R), plus per-32-row partial sums of the
+//              log-likelihood terms.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "glm_kernel.cuh"  // mbarrier / bulk-copy helpers
+#include "umma.cuh"
+
+namespace b200mc {
+
+constexpr int kGemmM = 128;        // rows of A per CTA = TMEM lanes
+constexpr int kGemmN = 256;        // chains per tile = TMEM columns
+constexpr int kGemmStages = 2;
+constexpr int kGemmThreads = 192;  // 6 warps
+constexpr int kGemmABytes = kGemmM * 128;  // one operand tile of A: 128 rows x 32 f32
+constexpr int kGemmBBytes = kGemmN * 128;
+constexpr int kGemmStageBytes = 2 * kGemmABytes + 2 * kGemmBBytes;  // hi + lo of both = 96 KB
+constexpr int kGemmSmem = kGemmStages * kGemmStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+
+enum GemmEpilogue { EPI_STORE = 0, EPI_RESID = 1 };
+
+struct Gemm3xLaunch {
+  const unsigned char *a_hi, *a_lo;  // images of A [RA][32*KB]
+  const unsigned char *b_hi, *b_lo;  // images of B [256][32*KB]
+  int RA;      // rows of A, multiple of 128
+  int KB;      // k-blocks (K / 32)
+  int splits;  // split-K: grid = (RA / 128) * splits, every split non-empty (splits <= KB)
+  // EPI_STORE
+  float* out;  // [splits][256][RA]
+  // EPI_RESID (splits == 1)
+  const float* y;          // [n_valid] observations
+  int n_valid;             // rows >= n_valid are padding: residual 0, no log-lik
+  int likelihood;          // 0 Bernoulli(logits), 1 Normal
+  const float* col_scale;  // Normal: precision per chain [256]
+  unsigned char *r_hi, *r_lo;  // images of R [256][RA] (K-major in the data index)
+  float* ll_part;          // [RA / 32][256] partial sums: BCE terms, or squared residuals
+};
+
+template <int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 1) gemm3x_kernel(const __grid_constant__ Gemm3xLaunch L) {
+  extern __shared__ unsigned char gsm_raw[];
+  unsigned char* gsm = reinterpret_cast<unsigned char*>(((uintptr_t)gsm_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t* full = reinterpret_cast<uint64_t*>(gsm + kGemmStages * kGemmStageBytes);
+  uint64_t* empty = full + kGemmStages;
+  uint64_t* acc_full = empty + kGemmStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int mt = blockIdx.x / L.splits, sp = blockIdx.x - mt * L.splits;
+  const int kb0 = (int)((long)sp * L.KB / L.splits), kb1 = (int)((long)(sp + 1) * L.KB / L.splits);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kGemmStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(acc_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) umma::tmem_alloc(tmem_slot, kGemmN);
+  umma::fence_before_sync();
+  __syncthreads();
+  umma::fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    // ---------------- producer: one lane streams the k-blocks of this split
+    if (lane == 0) {
+      const long a_rowgroups = L.RA >> 3;
+      for (int kb = kb0, it = 0; kb < kb1; ++kb, ++it) {
+        const int s = it % kGemmStages;
+        const uint32_t n = (uint32_t)(it / kGemmStages);
+        mbar_wait(&empty[s], (n & 1u) ^ 1u);
+        unsigned char* st = gsm + (long)s * kGemmStageBytes;
+        mbar_arrive_expect_tx(&full[s], (uint32_t)kGemmStageBytes);
+        const long ao = ((long)kb * a_rowgroups + (long)mt * (kGemmM >> 3)) * umma::kAtomBytes;
+        const long bo = (long)kb * (kGemmN >> 3) * umma::kAtomBytes;
+        tma_load_1d(st, L.a_hi + ao, kGemmABytes, &full[s]);
+        tma_load_1d(st + kGemmABytes, L.a_lo + ao, kGemmABytes, &full[s]);
+        tma_load_1d(st + 2 * kGemmABytes, L.b_hi + bo, kGemmBBytes, &full[s]);
+        tma_load_1d(st + 2 * kGemmABytes + kGemmBBytes, L.b_lo + bo, kGemmBBytes, &full[s]);
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------- MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma::make_idesc_tf32(kGemmM, kGemmN);
+      for (int kb = kb0, it = 0; kb < kb1; ++kb, ++it) {
+        const int s = it % kGemmStages;
+        const uint32_t n = (uint32_t)(it / kGemmStages);
+        mbar_wait(&full[s], n & 1u);
+        umma::fence_after_sync();
+        const uint32_t sa = umma::smem_addr(gsm + (long)s * kGemmStageBytes);
+        const uint64_t a_hi = umma::make_desc_k_sw128(sa);
+        const uint64_t a_lo = umma::make_desc_k_sw128(sa + kGemmABytes);
+        const uint64_t b_hi = umma::make_desc_k_sw128(sa + 2 * kGemmABytes);
+        const uint64_t b_lo = umma::make_desc_k_sw128(sa + 2 * kGemmABytes + kGemmBBytes);
+#pragma unroll
+        for (int k = 0; k < umma::kBlockK / 8; ++k) {
+          const uint64_t adv = (uint64_t)(k * 2);  // 8 tf32 = 32 bytes = 2 x 16-byte units
+          // small terms first, then the leading one
+          umma::mma_tf32(tmem, a_lo + adv, b_hi + adv, idesc, (it > 0 || k > 0) ? 1u : 0u);
+          umma::mma_tf32(tmem, a_hi + adv, b_lo + adv, idesc, 1u);
+          umma::mma_tf32(tmem, a_hi + adv, b_hi + adv, idesc, 1u);
+        }
+        umma::mma_commit(&empty[s]);  // the stage is free once these MMAs have read it
+      }
+      umma::mma_commit(acc_full);
+    }
+  } else {
+    // ---------------- epilogue: warp w may touch TMEM lanes 32 * (w % 4) ..
+    const int q = warp & 3;
+    mbar_wait(acc_full, 0u);
+    umma::fence_after_sync();
+    const int m = mt * kGemmM + q * 32 + lane;  // this thread's row of A
+    const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+    if (EPI == EPI_STORE) {
+      float* out = L.out + (long)sp * kGemmN * L.RA;
+#pragma unroll 1
+      for (int c0 = 0; c0 < kGemmN; c0 += 32) {
+        uint32_t v[32];
+        umma::tmem_ld32(trow + c0, v);
+        umma::tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) out[(long)(c0 + j) * L.RA + m] = __uint_as_float(v[j]);
+      }
+    } else {
+      const bool valid = m < L.n_valid;
+      const float yv = valid ? L.y[m] : 0.f;
+      const long kbR = m >> 5;  // this warp's 32 rows are one k-block of the R images
+      unsigned char* rh = L.r_hi + kbR * (kGemmN >> 3) * umma::kAtomBytes;
+      unsigned char* rl = L.r_lo + kbR * (kGemmN >> 3) * umma::kAtomBytes;
+      float* llp = L.ll_part + kbR * kGemmN;
+#pragma unroll 1
+      for (int c0 = 0; c0 < kGemmN; c0 += 32) {
+        uint32_t v[32];
+        umma::tmem_ld32(trow + c0, v);
+        umma::tmem_ld_wait();
+        float part[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int c = c0 + j;
+          const float l = __uint_as_float(v[j]);
+          float res = 0.f, term = 0.f;
+          if (valid) {
+            if (L.likelihood == 1) {
+              const float r = yv - l;
+              term = r * r;
+              res = -(L.col_scale[c] * r);
+            } else {
+              const float e = expf(-fabsf(l));
+              const float inv = 1.0f / (1.0f + e);
+              term = (fmaxf(l, 0.f) + log1pf(e)) - l * yv;
+              res = ((l >= 0.f) ? inv : e * inv) - yv;
+            }
+          }
+          float hi, lo;
+          umma::split_tf32(res, hi, lo);
+          // image element (row c, k = m): same 128-byte line for the whole warp
+          const long off = (long)(c >> 3) * umma::kAtomBytes + (c & 7) * 128 +
+                           (((lane >> 2) ^ (c & 7)) << 4) + ((lane & 3) << 2);
+          *reinterpret_cast<float*>(rh + off) = hi;
+          *reinterpret_cast<float*>(rl + off) = lo;
+          part[j] = term;
+        }
+        const float tot = warp_transpose_reduce32(part);  // lane j: sum over the 32 rows of column c0 + j
+        llp[c0 + lane] = tot;
+      }
+    }
+    umma::fence_before_sync();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    umma::fence_after_sync();
+    umma::tmem_dealloc(tmem, kGemmN);
+  }
+}
+
+// ---------------------------------------------------------------- operand image builders
+// Row-major src[R_src][K_src] (optionally read transposed) -> hi/lo images of Mtx[R][K]
+// (R, K padded with zeros).  One thread per element; writes are 4 bytes into swizzled lines.
+__global__ void image_build_kernel(const float* __restrict__ src, int R_src, int K_src, int transpose,
+                                   int R, int K, unsigned char* __restrict__ hi,
+                                   unsigned char* __restrict__ lo) {
+  const long total = (long)R * K;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    // enumerate in image order so writes are contiguous; derive (r, k) from the offset
+    const long atom = i >> 8;  // 256 floats per atom
+    const int within = (int)(i & 255);
+    const int rr = within >> 5, chunk_sw = (within >> 2) & 7, e = within & 3;
+    const int kk = ((chunk_sw ^ rr) << 2) + e;
+    const long rg = atom % (R >> 3), kb = atom / (R >> 3);
+    const int r = (int)(rg * 8 + rr);
+    const int k = (int)(kb * 32 + kk);
+    float x = 0.f;
+    if (!transpose) {
+      if (r < R_src && k < K_src) x = src[(long)r * K_src + k];
+    } else {
+      if (k < R_src && r < K_src) x = src[(long)k * K_src + r];  // Mtx[r][k] = src[k][r]
+    }
+    float h, l;
+    umma::split_tf32(x, h, l);
+    reinterpret_cast<float*>(hi)[i] = h;
+    reinterpret_cast<float*>(lo)[i] = l;
+  }
+}
+
+}  // namespace b200mc

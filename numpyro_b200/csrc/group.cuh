@@ -11,6 +11,7 @@ namespace b200mc {
 struct ThreadGroup {  // one chain per thread (tiny D: eight schools)
   static constexpr bool kUnitStride = false;  // vectors are strided [D][chain]
   static constexpr bool kRegVec = false;
+  static constexpr bool kBlockWide = false;
   __device__ __forceinline__ int lane() const { return 0; }
   __device__ __forceinline__ int size() const { return 1; }
   __device__ __forceinline__ float sum(float x) const { return x; }
@@ -21,6 +22,7 @@ struct ThreadGroup {  // one chain per thread (tiny D: eight schools)
 struct WarpGroup {  // one chain per warp (D up to a few hundred)
   static constexpr bool kUnitStride = true;
   static constexpr bool kRegVec = true;  // <= 4 elements per lane fit registers (D <= 128)
+  static constexpr bool kBlockWide = false;
   __device__ __forceinline__ int lane() const { return threadIdx.x & 31; }
   __device__ __forceinline__ int size() const { return 32; }
   __device__ __forceinline__ float sum(float x) const {
@@ -43,6 +45,7 @@ struct WarpGroup {  // one chain per warp (D up to a few hundred)
 struct BlockGroup {
   static constexpr bool kUnitStride = true;
   static constexpr bool kRegVec = false;
+  static constexpr bool kBlockWide = true;  // whole warps available: warp-per-row sweeps
   float* scratch;
   __device__ __forceinline__ int lane() const { return threadIdx.x; }
   __device__ __forceinline__ int size() const { return blockDim.x; }

@@ -158,46 +158,119 @@ __device__ float horseshoe_potential(const ModelData& M, const G& g, const float
   g.sync();
   float* res = M.scratch + (long)chain * N;
   float ll = 0.f, ss = 0.f;
-  for (int i = g.lane(); i < N; i += g.size()) {  // mean_i = x_i . beta, dU/dmean_i
-    const float* x = M.a + (long)i * Dh;
-    float m0 = 0.f, m1 = 0.f;
-    int d = 0;
-    for (; d + 1 < Dh; d += 2) {
-      m0 = fmaf(x[d], grad[(o_u + d) * gs], m0);
-      m1 = fmaf(x[d + 1], grad[(o_u + d + 1) * gs], m1);
-    }
-    if (d < Dh) m0 = fmaf(x[d], grad[(o_u + d) * gs], m0);
-    const float m = m0 + m1;
-    const float yv = M.b[i];
-    if (normal) {
-      const float r = yv - m;
-      ss += r * r;
-      res[i] = -(prec * r);
-    } else {
-      const float e = expf(-fabsf(m));
-      const float inv = 1.0f / (1.0f + e);
-      ll += (fmaxf(m, 0.f) + log1pf(e)) - m * yv;
-      res[i] = ((m >= 0.f) ? inv : e * inv) - yv;
-    }
-  }
-  g.sync();
   float sbb = 0.f;
-  for (int d = g.lane(); d < Dh; d += g.size()) {  // dU/dbeta_d = sum_i X[i][d] res_i
-    float a0 = 0.f, a1 = 0.f;
-    int i = 0;
-    for (; i + 1 < N; i += 2) {
-      a0 = fmaf(M.a[(long)i * Dh + d], res[i], a0);
-      a1 = fmaf(M.a[(long)(i + 1) * Dh + d], res[i + 1], a1);
+  if constexpr (G::kBlockWide) {
+    // CTA per chain: warp per data row (coalesced 128-byte lines of X) for X beta ...
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const float* beta = grad + (long)o_u * gs;
+    for (int i = wid; i < N; i += nw) {
+      const float* x = M.a + (long)i * Dh;
+      float a[4] = {0.f, 0.f, 0.f, 0.f};
+      int d = lane;
+      for (; d + 96 < Dh; d += 128) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) a[k] = fmaf(__ldg(x + d + 32 * k), beta[(d + 32 * k) * gs], a[k]);
+      }
+      for (; d < Dh; d += 32) a[0] = fmaf(__ldg(x + d), beta[d * gs], a[0]);
+      float m = (a[0] + a[1]) + (a[2] + a[3]);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) m += __shfl_xor_sync(0xffffffffu, m, o);
+      if (lane == 0) {
+        const float yv = M.b[i];
+        if (normal) {
+          const float r = yv - m;
+          ss += r * r;
+          res[i] = -(prec * r);
+        } else {
+          const float e = expf(-fabsf(m));
+          const float inv = 1.0f / (1.0f + e);
+          ll += (fmaxf(m, 0.f) + log1pf(e)) - m * yv;
+          res[i] = ((m >= 0.f) ? inv : e * inv) - yv;
+        }
+      }
     }
-    if (i < N) a0 = fmaf(M.a[(long)i * Dh + d], res[i], a0);
-    const float db = a0 + a1;
-    const float beta = grad[(o_u + d) * gs];
-    const float lu = z[(o_l + d) * zs], ub = z[(o_u + d) * zs];
-    const float lam = expf(lu);
-    const float l2 = lam * lam;
-    grad[(o_l + d) * gs] = (2.0f * l2 / (1.0f + l2) - 1.0f) + db * beta;
-    grad[(o_u + d) * gs] = ub + db * (tau * lam);
-    sbb += db * beta;
+    g.sync();
+    // ... and for dU/dbeta_d = sum_i X[i][d] res_i each thread owns up to 4 columns at a
+    // time, rows in pairs => 8 coalesced loads in flight per thread
+    const int T = g.size();
+    for (int d0 = g.lane(); d0 < Dh; d0 += 4 * T) {
+      float a[4][2];
+      const float* col[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        a[k][0] = 0.f; a[k][1] = 0.f;
+        col[k] = M.a + ((d0 + k * T < Dh) ? d0 + k * T : d0);
+      }
+      int i = 0;
+      for (; i + 1 < N; i += 2) {
+        const float r0 = res[i], r1 = res[i + 1];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          a[k][0] = fmaf(__ldg(col[k] + (long)i * Dh), r0, a[k][0]);
+          a[k][1] = fmaf(__ldg(col[k] + (long)(i + 1) * Dh), r1, a[k][1]);
+        }
+      }
+      if (i < N) {
+        const float r0 = res[i];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) a[k][0] = fmaf(__ldg(col[k] + (long)i * Dh), r0, a[k][0]);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int d = d0 + k * T;
+        if (d < Dh) {
+          const float db = a[k][0] + a[k][1];
+          const float bt = grad[(o_u + d) * gs];
+          const float lu = z[(o_l + d) * zs], ub = z[(o_u + d) * zs];
+          const float lam = expf(lu);
+          const float l2 = lam * lam;
+          grad[(o_l + d) * gs] = (2.0f * l2 / (1.0f + l2) - 1.0f) + db * bt;
+          grad[(o_u + d) * gs] = ub + db * (tau * lam);
+          sbb += db * bt;
+        }
+      }
+    }
+  } else {
+    for (int i = g.lane(); i < N; i += g.size()) {  // mean_i = x_i . beta, dU/dmean_i
+      const float* x = M.a + (long)i * Dh;
+      float m0 = 0.f, m1 = 0.f;
+      int d = 0;
+      for (; d + 1 < Dh; d += 2) {
+        m0 = fmaf(x[d], grad[(o_u + d) * gs], m0);
+        m1 = fmaf(x[d + 1], grad[(o_u + d + 1) * gs], m1);
+      }
+      if (d < Dh) m0 = fmaf(x[d], grad[(o_u + d) * gs], m0);
+      const float m = m0 + m1;
+      const float yv = M.b[i];
+      if (normal) {
+        const float r = yv - m;
+        ss += r * r;
+        res[i] = -(prec * r);
+      } else {
+        const float e = expf(-fabsf(m));
+        const float inv = 1.0f / (1.0f + e);
+        ll += (fmaxf(m, 0.f) + log1pf(e)) - m * yv;
+        res[i] = ((m >= 0.f) ? inv : e * inv) - yv;
+      }
+    }
+    g.sync();
+    for (int d = g.lane(); d < Dh; d += g.size()) {  // dU/dbeta_d = sum_i X[i][d] res_i
+      float a0 = 0.f, a1 = 0.f;
+      int i = 0;
+      for (; i + 1 < N; i += 2) {
+        a0 = fmaf(M.a[(long)i * Dh + d], res[i], a0);
+        a1 = fmaf(M.a[(long)(i + 1) * Dh + d], res[i + 1], a1);
+      }
+      if (i < N) a0 = fmaf(M.a[(long)i * Dh + d], res[i], a0);
+      const float db = a0 + a1;
+      const float beta = grad[(o_u + d) * gs];
+      const float lu = z[(o_l + d) * zs], ub = z[(o_u + d) * zs];
+      const float lam = expf(lu);
+      const float l2 = lam * lam;
+      grad[(o_l + d) * gs] = (2.0f * l2 / (1.0f + l2) - 1.0f) + db * beta;
+      grad[(o_u + d) * gs] = ub + db * (tau * lam);
+      sbb += db * beta;
+    }
   }
   g.sum2(lp, sbb);
   g.sum2(ll, ss);

@@ -208,6 +208,31 @@ struct Sampler {
   // the sum to j <= i (triangular factor: the skipped terms are exact zeros).
   __device__ __noinline__ void matvec(const float* M, const float* src, float* dst, bool lower = false) {
     g.sync();  // src was written by its owner lanes
+    if constexpr (G::kBlockWide) {
+      // CTA per chain (large D): warp per row, lanes stride over the columns => every load is
+      // a coalesced 128-byte line, 8 independent lines in flight per warp; fixed summation
+      // order (per-lane partials, then an xor tree) => deterministic.
+      const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+      for (int i = wid; i < D; i += nw) {
+        const float* row = M + (long)i * D;
+        const int n = lower ? i + 1 : D;
+        float a[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = 0.f;
+        int j = lane;
+        for (; j + 224 < n; j += 256) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) a[k] = fmaf(__ldcg(row + j + 32 * k), src[j + 32 * k], a[k]);
+        }
+        for (; j < n; j += 32) a[0] = fmaf(__ldcg(row + j), src[j], a[0]);
+        float t = ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if (lane == 0) dst[i] = t;
+      }
+      g.sync();
+      return;
+    }
     B200MC_FOR_D {
       const float* row = M + (long)d * D;
       const int n = lower ? d + 1 : D;
