@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "../../include/b200mc.h"
+#include "batch_kernel.cuh"
 #include "chain_kernel.cuh"
 #include "gemm3x_kernel.cuh"
 #include "glm_kernel.cuh"
@@ -62,7 +63,20 @@ struct b200mc_handle {
   unsigned* xarrive[kGlmMaxRanks] = {};
   bool comm_ready = false;
   bool initialized = false;
+  // many-chain lock-step engine (mode 3): operand images and GEMM plumbing
+  struct Batch {
+    unsigned char *x_hi = nullptr, *x_lo = nullptr;    // X   [RA1][K1]
+    unsigned char *xt_hi = nullptr, *xt_lo = nullptr;  // X^T [RA2][RA1]
+    unsigned char *b_hi = nullptr, *b_lo = nullptr;    // B   [256][K1]
+    unsigned char *r_hi = nullptr, *r_lo = nullptr;    // R   [256][RA1]
+    float *ll_part = nullptr, *gpart = nullptr, *col_scale = nullptr;
+    unsigned char* snap = nullptr;
+    int* status = nullptr;
+    unsigned* active = nullptr;
+    int RA1 = 0, K1 = 0, RA2 = 0, splits = 1, snap_stride = 0;
+  } bt;
 };
+constexpr int kBatchStepsPerSync = 16;
 
 extern "C" const char* b200mc_last_error(void) { return g_err.c_str(); }
 extern "C" int b200mc_version(void) { return 1; }
@@ -145,6 +159,43 @@ static int family_sites(const b200mc_config& c, SamplerParams& P, int& D) {
   }
 }
 
+// ---------------------------------------------------------------- 3xTF32 GEMM plumbing
+namespace {
+__global__ void sum_splits_kernel(const float* part, int splits, int Nc, int RA, int M, float* out) {
+  const long total = (long)Nc * M;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int c = (int)(i / M), m = (int)(i - (long)c * M);
+    float a = 0.f;
+    for (int s = 0; s < splits; ++s) a += part[((long)s * kGemmN + c) * RA + m];
+    out[i] = a;
+  }
+}
+int build_image(const float* src, int R_src, int K_src, int transpose, int R, int K,
+                unsigned char** hi, unsigned char** lo, cudaStream_t st) {
+  const size_t bytes = (size_t)R * K * 4;
+  CK(cudaMalloc((void**)hi, bytes));
+  CK(cudaMalloc((void**)lo, bytes));
+  image_build_kernel<<<1184, 256, 0, st>>>(src, R_src, K_src, transpose, R, K, *hi, *lo);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+int launch_gemm3x(const Gemm3xLaunch& L, int epi, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute(gemm3x_kernel<EPI_STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+    CK(cudaFuncSetAttribute(gemm3x_kernel<EPI_RESID>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+    attr_set = true;
+  }
+  const int grid = (L.RA / kGemmM) * L.splits;
+  if (epi == EPI_STORE) gemm3x_kernel<EPI_STORE><<<grid, kGemmThreads, kGemmSmem, st>>>(L);
+  else gemm3x_kernel<EPI_RESID><<<grid, kGemmThreads, kGemmSmem, st>>>(L);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+}  // namespace
+
 extern "C" void b200mc_destroy(b200mc_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
@@ -159,6 +210,10 @@ extern "C" void b200mc_destroy(b200mc_handle* h) {
     if (h->xarrive[r]) cudaIpcCloseMemHandle(h->xarrive[r]);
   }
   cudaFree(h->xchg_local); cudaFree(h->xarrive_local);
+  cudaFree(h->bt.x_hi); cudaFree(h->bt.x_lo); cudaFree(h->bt.xt_hi); cudaFree(h->bt.xt_lo);
+  cudaFree(h->bt.b_hi); cudaFree(h->bt.b_lo); cudaFree(h->bt.r_hi); cudaFree(h->bt.r_lo);
+  cudaFree(h->bt.ll_part); cudaFree(h->bt.gpart); cudaFree(h->bt.col_scale);
+  cudaFree(h->bt.snap); cudaFree(h->bt.status); cudaFree(h->bt.active);
   delete h;
 }
 
@@ -320,15 +375,46 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
       ACK(alloc((void**)&h->xarrive_local, sizeof(unsigned) * 4));
     }
   } else {
+    int batch_min = 64;  // north_star: from 64 chains on, X.Theta is a real dense contraction
+    if (const char* e = getenv("B200MC_BATCH_MIN_CHAINS")) batch_min = atoi(e);
+    const bool batch = c.family == B200MC_HORSESHOE && C >= batch_min && C <= kBatchCols;
     if (c.family == B200MC_HORSESHOE) {
       if (!c.data1_dev) { b200mc_destroy(h); return fail("horseshoe: Y missing"); }
-      ACK(alloc((void**)&h->M.scratch, sizeof(float) * (size_t)C * c.N));
+      if (!batch) ACK(alloc((void**)&h->M.scratch, sizeof(float) * (size_t)C * c.N));
     }
-    // thread per chain (tiny D, diagonal mass), warp per chain, CTA per chain
-    h->mode = (D <= 32 && !c.dense_mass) ? 0 : (D <= 512 ? 1 : 2);
+    // thread per chain (tiny D, diagonal mass), warp per chain, CTA per chain; or the
+    // lock-step tensor-core engine (batch_kernel.cuh)
+    h->mode = batch ? 3 : ((D <= 32 && !c.dense_mass) ? 0 : (D <= 512 ? 1 : 2));
     h->c_pad = (C + 31) / 32 * 32;
     const size_t chains = (h->mode == 0) ? (size_t)h->c_pad : (size_t)C;
     ACK(alloc((void**)&h->work, sizeof(float) * chains * nslots * D));
+    if (batch) {
+      auto& b = h->bt;
+      b.RA1 = (c.N + kGemmM - 1) / kGemmM * kGemmM;
+      b.K1 = (c.ncols + 31) / 32 * 32;
+      b.RA2 = (c.ncols + kGemmM - 1) / kGemmM * kGemmM;
+      const int kb2 = b.RA1 / 32, tiles2 = b.RA2 / kGemmM;
+      b.splits = h->num_sms / tiles2;
+      if (b.splits < 1) b.splits = 1;
+      if (b.splits > kb2) b.splits = kb2;
+      if (build_image((const float*)c.data0_dev, c.N, c.ncols, 0, b.RA1, b.K1, &b.x_hi, &b.x_lo, 0) ||
+          build_image((const float*)c.data0_dev, c.N, c.ncols, 1, b.RA2, b.RA1, &b.xt_hi, &b.xt_lo, 0)) {
+        b200mc_destroy(h);
+        return 1;
+      }
+      ACK(alloc((void**)&b.b_hi, (size_t)kBatchCols * b.K1 * 4));
+      ACK(alloc((void**)&b.b_lo, (size_t)kBatchCols * b.K1 * 4));
+      ACK(alloc((void**)&b.r_hi, (size_t)kBatchCols * b.RA1 * 4));
+      ACK(alloc((void**)&b.r_lo, (size_t)kBatchCols * b.RA1 * 4));
+      ACK(alloc((void**)&b.ll_part, sizeof(float) * (size_t)(b.RA1 / 32) * kBatchCols));
+      ACK(alloc((void**)&b.gpart, sizeof(float) * (size_t)b.splits * kBatchCols * b.RA2));
+      ACK(alloc((void**)&b.col_scale, sizeof(float) * kBatchCols));
+      b.snap_stride = (int)((sizeof(Sampler<BlockGroup>) + 255) / 256 * 256);
+      ACK(alloc((void**)&b.snap, (size_t)C * b.snap_stride));
+      ACK(alloc((void**)&b.status, sizeof(int) * C));
+      ACK(alloc((void**)&b.active, sizeof(unsigned) * (kBatchStepsPerSync + 1)));
+      ACK(cudaDeviceSynchronize());
+    }
   }
 #undef ACK
   *out = h;
@@ -407,6 +493,67 @@ static int launch_chain(b200mc_handle* h, const CollectSpec& col, const uint32_t
   return 0;
 }
 
+// The two contractions of one batched potential evaluation (batch_kernel.cuh).
+static int launch_batch_gemms(b200mc_handle* h, cudaStream_t st) {
+  auto& b = h->bt;
+  Gemm3xLaunch g1 = {};
+  g1.a_hi = b.x_hi; g1.a_lo = b.x_lo; g1.b_hi = b.b_hi; g1.b_lo = b.b_lo;
+  g1.RA = b.RA1; g1.KB = b.K1 / 32; g1.splits = 1;
+  g1.y = h->M.b; g1.n_valid = h->M.N; g1.likelihood = h->M.likelihood; g1.col_scale = b.col_scale;
+  g1.r_hi = b.r_hi; g1.r_lo = b.r_lo; g1.ll_part = b.ll_part;
+  if (launch_gemm3x(g1, EPI_RESID, st)) return 1;
+  Gemm3xLaunch g2 = {};
+  g2.a_hi = b.xt_hi; g2.a_lo = b.xt_lo; g2.b_hi = b.r_hi; g2.b_lo = b.r_lo;
+  g2.RA = b.RA2; g2.KB = b.RA1 / 32; g2.splits = b.splits; g2.out = b.gpart;
+  return launch_gemm3x(g2, EPI_STORE, st);
+}
+
+static void fill_batch_launch(b200mc_handle* h, BatchLaunch& L) {
+  auto& b = h->bt;
+  memset(&L, 0, sizeof(L));
+  L.P = h->P; L.M = h->M; L.cs = h->cs; L.cv = h->cv; L.work = h->work; L.C = h->C;
+  L.snap = b.snap; L.snap_stride = b.snap_stride; L.status = b.status; L.active = b.active;
+  L.b_hi = b.b_hi; L.b_lo = b.b_lo; L.K1 = b.K1;
+  L.gpart = b.gpart; L.splits = b.splits; L.RA2 = b.RA2;
+  L.ll_part = b.ll_part; L.n_rowgroups = b.RA1 / 32; L.col_scale = b.col_scale;
+}
+
+// Lock-step engine: every global step evaluates the potential of ALL chains with two tensor-core
+// contractions and advances every chain by one gradient.  The host only looks at the device
+// every kBatchStepsPerSync steps (how many chains still wait for a gradient), so this call
+// returns after the work is DONE, unlike the single-launch paths.
+static int launch_batch(b200mc_handle* h, const CollectSpec& col, const uint32_t* keys,
+                        int user_init, cudaStream_t st) {
+  BatchLaunch L;
+  fill_batch_launch(h, L);
+  L.col = col; L.init_keys = keys; L.user_init = user_init;
+  auto& b = h->bt;
+  CK(cudaMemsetAsync(b.active, 0, sizeof(unsigned) * (kBatchStepsPerSync + 1), st));
+  L.begin = 1;
+  L.active = b.active + kBatchStepsPerSync;
+  batch_step_kernel<<<h->C, kBatchThreads, 0, st>>>(L);
+  g_launches++;
+  CK(cudaGetLastError());
+  unsigned active = 0;
+  CK(cudaMemcpyAsync(&active, b.active + kBatchStepsPerSync, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  L.begin = 0;
+  L.init_keys = nullptr;
+  while (active > 0) {
+    CK(cudaMemsetAsync(b.active, 0, sizeof(unsigned) * kBatchStepsPerSync, st));
+    for (int i = 0; i < kBatchStepsPerSync; ++i) {
+      if (launch_batch_gemms(h, st)) return 1;
+      L.active = b.active + i;
+      batch_step_kernel<<<h->C, kBatchThreads, 0, st>>>(L);
+      g_launches++;
+    }
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(&active, b.active + kBatchStepsPerSync - 1, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+  }
+  return 0;
+}
+
 static int launch_glm(b200mc_handle* h, const CollectSpec& col, const uint32_t* keys, int user_init,
                       int chain, const float* eval_z, float* eval_U, float* eval_grad,
                       cudaStream_t st) {
@@ -461,6 +608,8 @@ extern "C" int b200mc_init(b200mc_handle* h, const uint32_t* keys_dev, const flo
   if (h->cfg.family == B200MC_LOGISTIC) {
     for (int c = 0; c < h->C; ++c)
       if (launch_glm(h, col, keys_dev, user_init, c, nullptr, nullptr, nullptr, st)) return 1;
+  } else if (h->mode == 3) {
+    if (launch_batch(h, col, keys_dev, user_init, st)) return 1;
   } else {
     if (launch_chain(h, col, keys_dev, user_init, st)) return 1;
   }
@@ -481,6 +630,7 @@ extern "C" int b200mc_sample(b200mc_handle* h, int num_iters, int collect_start,
       if (launch_glm(h, col, nullptr, 0, c, nullptr, nullptr, nullptr, st)) return 1;
     return 0;
   }
+  if (h->mode == 3) return launch_batch(h, col, nullptr, 0, st);
   return launch_chain(h, col, nullptr, 0, st);
 }
 
@@ -494,6 +644,24 @@ extern "C" int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, i
       if (launch_glm(h, col, nullptr, 0, 0, z_dev + (long)i * h->D, U_dev + i,
                      grad_dev + (long)i * h->D, st))
         return 1;
+    return 0;
+  }
+  if (h->mode == 3) {  // tensor-core path: up to 256 points per pair of contractions
+    for (int i0 = 0; i0 < n; i0 += kBatchCols) {
+      const int m = (n - i0 < kBatchCols) ? n - i0 : kBatchCols;
+      BatchLaunch L;
+      fill_batch_launch(h, L);
+      L.C = m;
+      L.eval_z = z_dev + (long)i0 * h->D;
+      L.eval_U = U_dev + i0;
+      L.eval_grad = grad_dev + (long)i0 * h->D;
+      batch_potential_kernel<<<m, kBatchThreads, 0, st>>>(L, 0);
+      g_launches++;
+      if (launch_batch_gemms(h, st)) return 1;
+      batch_potential_kernel<<<m, kBatchThreads, 0, st>>>(L, 1);
+      g_launches++;
+      CK(cudaGetLastError());
+    }
     return 0;
   }
   // per-chain scratch (horseshoe residuals) is sized for num_chains: evaluate in batches
@@ -656,42 +824,6 @@ __global__ void draw_kernel(const uint32_t* key, int n, int what, float lo, floa
 }
 
 // ---------------------------------------------------------------- 3xTF32 GEMM (test hook)
-namespace {
-__global__ void sum_splits_kernel(const float* part, int splits, int Nc, int RA, int M, float* out) {
-  const long total = (long)Nc * M;
-  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const int c = (int)(i / M), m = (int)(i - (long)c * M);
-    float a = 0.f;
-    for (int s = 0; s < splits; ++s) a += part[((long)s * kGemmN + c) * RA + m];
-    out[i] = a;
-  }
-}
-int build_image(const float* src, int R_src, int K_src, int transpose, int R, int K,
-                unsigned char** hi, unsigned char** lo, cudaStream_t st) {
-  const size_t bytes = (size_t)R * K * 4;
-  CK(cudaMalloc((void**)hi, bytes));
-  CK(cudaMalloc((void**)lo, bytes));
-  image_build_kernel<<<1184, 256, 0, st>>>(src, R_src, K_src, transpose, R, K, *hi, *lo);
-  g_launches++;
-  CK(cudaGetLastError());
-  return 0;
-}
-int launch_gemm3x(const Gemm3xLaunch& L, int epi, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    CK(cudaFuncSetAttribute(gemm3x_kernel<EPI_STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
-    CK(cudaFuncSetAttribute(gemm3x_kernel<EPI_RESID>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
-    attr_set = true;
-  }
-  const int grid = (L.RA / kGemmM) * L.splits;
-  if (epi == EPI_STORE) gemm3x_kernel<EPI_STORE><<<grid, kGemmThreads, kGemmSmem, st>>>(L);
-  else gemm3x_kernel<EPI_RESID><<<grid, kGemmThreads, kGemmSmem, st>>>(L);
-  g_launches++;
-  CK(cudaGetLastError());
-  return 0;
-}
-}  // namespace
-
 extern "C" int b200mc_gemm3xtf32(const float* A_dev, const float* B_dev, int M, int Nc, int K,
                                  int splits, float* out_dev, void* stream) {
   if (M <= 0 || K <= 0 || Nc <= 0 || Nc > kGemmN) return fail("gemm3xtf32: bad shape");

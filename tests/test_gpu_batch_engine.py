@@ -1,0 +1,111 @@
+"""GPU parity of the many-chain lock-step engine (csrc/batch_kernel.cuh): from 64 chains on
+the horseshoe potential runs as two split-precision tensor-core contractions over all chains
+(csrc/gemm3x_kernel.cuh) and every chain advances by one gradient per global step.
+
+Checked against (a) the float64 oracle (tier 2, potential and gradient), (b) the oracle's
+sampler chain by chain (tier 3: identical tree sizes with fixed step size and mass matrix),
+(c) the CTA-per-chain CUDA-core path of the same library on the same keys, and (d) the known
+coefficients of the synthetic regression after a dense-mass warm-up (tier 4).
+"""
+import os
+
+import numpy as np
+from numpy.testing import assert_allclose
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from oracle import hmc as ohmc  # noqa: E402
+from oracle import potentials as opot  # noqa: E402
+from oracle import threefry as T  # noqa: E402
+from oracle.hmc_util import Config  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def nb():
+    import __graft_entry__ as g
+
+    return g.build()
+
+
+def make_horseshoe(N, D, likelihood, seed=0):
+    # examples/horseshoe_regression.py:105-125
+    rng = np.random.RandomState(seed)
+    X = rng.randn(N, D).astype(np.float32)
+    Y = X[:, :3] @ np.array([2.0, -1.0, 0.50])
+    Y = Y - Y.mean()
+    if likelihood == "normal":
+        Y = Y + 0.05 * rng.randn(N)
+    else:
+        Y = rng.binomial(1, 1 / (1 + np.exp(-Y))).astype(np.float64)
+    return X, Y.astype(np.float32)
+
+
+def model_of(nb, likelihood):
+    return nb.models.horseshoe_bernoulli if likelihood == "bernoulli" else nb.models.horseshoe_normal
+
+
+@pytest.mark.parametrize("likelihood", ["bernoulli", "normal"])
+@pytest.mark.parametrize("N,D,n_pts", [(300, 40, 64), (1000, 130, 256), (130, 7, 300)])
+def test_batched_potential_and_grad(nb, likelihood, N, D, n_pts):
+    X, Y = make_horseshoe(N, D, likelihood)
+    k = nb.infer.NUTS(model_of(nb, likelihood))
+    k.init(T.split(T.PRNGKey(0), 64, True), 0, None, (X, Y), {})  # 64 chains: tensor-core engine
+    fam = opot.Horseshoe(X, Y, likelihood, np.float64)
+    rng = np.random.default_rng(1)
+    zs = (rng.normal(size=(n_pts, fam.dim)) * 0.5).astype(np.float32)
+    U, g = k.potential_and_grad(zs)
+    for i in range(0, n_pts, 7):
+        U0, g0 = fam.potential_and_grad(zs[i].astype(np.float64))
+        assert_allclose(U[i], U0, rtol=2e-5)
+        assert_allclose(g[i], g0, rtol=1e-4, atol=1e-4 * np.abs(g0).max())
+
+
+@pytest.mark.parametrize("likelihood", ["bernoulli", "normal"])
+def test_tier3_batched_chains_match_oracle(nb, likelihood):
+    X, Y = make_horseshoe(100, 5, likelihood)
+    fam = opot.Horseshoe(X, Y, likelihood)
+    kw = dict(step_size=0.02, adapt_step_size=False, adapt_mass_matrix=False, max_tree_depth=6)
+    chains, n = 64, 12
+    mc = nb.infer.MCMC(nb.infer.NUTS(model_of(nb, likelihood), **kw), num_warmup=0, num_samples=n,
+                       num_chains=chains, chain_method="vectorized")
+    key = T.PRNGKey(11)
+    mc.run(key, X, Y, extra_fields=("num_steps", "potential_energy"))
+    ex = mc.get_extra_fields(group_by_chain=True)
+    keys = T.split(key, chains, True)
+    for c in (0, 1, 17, 63):
+        ok = ohmc.HMCKernel(fam, cfg=Config(np.float32, True), **kw)
+        r, _ = ohmc.run_chain(ok, keys[c], 0, n)
+        assert np.array_equal(ex["num_steps"][c], r["num_steps"]), c
+        assert_allclose(ex["potential_energy"][c], r["potential_energy"], rtol=5e-4, atol=2e-3)
+
+
+def test_batched_engine_matches_cta_per_chain_path(nb):
+    X, Y = make_horseshoe(200, 12, "normal")
+    kw = dict(step_size=0.01, adapt_step_size=False, adapt_mass_matrix=False, max_tree_depth=5)
+    out = {}
+    for name, env in (("batch", None), ("cta", "100000")):
+        if env is None:
+            os.environ.pop("B200MC_BATCH_MIN_CHAINS", None)
+        else:
+            os.environ["B200MC_BATCH_MIN_CHAINS"] = env
+        try:
+            mc = nb.infer.MCMC(nb.infer.NUTS(nb.models.horseshoe_normal, **kw), num_warmup=0,
+                               num_samples=8, num_chains=64, chain_method="vectorized")
+            mc.run(T.PRNGKey(5), X, Y, extra_fields=("num_steps",))
+            out[name] = (mc.get_extra_fields(group_by_chain=True)["num_steps"],
+                         mc.get_samples(group_by_chain=True)["betas"])
+        finally:
+            os.environ.pop("B200MC_BATCH_MIN_CHAINS", None)
+    assert np.array_equal(out["batch"][0], out["cta"][0])
+    assert_allclose(out["batch"][1], out["cta"][1], rtol=2e-3, atol=2e-3)
+
+
+def test_batched_dense_warmup_recovers_coefficients(nb):
+    X, Y = make_horseshoe(150, 6, "normal")
+    mc = nb.infer.MCMC(nb.infer.NUTS(nb.models.horseshoe_normal, dense_mass=True), num_warmup=150,
+                       num_samples=60, num_chains=64, chain_method="vectorized")
+    mc.run(T.PRNGKey(1), X, Y, extra_fields=("num_steps",))
+    b = mc.get_samples()["betas"].mean(0)
+    assert_allclose(b[:3], [2.0, -1.0, 0.5], atol=0.15)
+    assert int(np.asarray(mc.last_state.i).min()) == 210
