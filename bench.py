@@ -450,6 +450,10 @@ def run_chain_workload(args):
     _lib.require_device()
     _lib.check(lib.b200mc_set_device(local))
     model, margs, mkw, kkw, chains, desc = make_workload(args.workload, args.chains)
+    if args.fixed_step > 0:  # profiling aid: no adaptation, trees at a given step size
+        kkw = dict(kkw, step_size=args.fixed_step, adapt_step_size=False, adapt_mass_matrix=False)
+    if args.max_tree_depth:
+        kkw = dict(kkw, max_tree_depth=args.max_tree_depth)
     kern = NUTS(model, **kkw)
     mc = MCMC(kern, num_warmup=args.adapt, num_samples=args.transitions, num_chains=chains,
               chain_method="vectorized")
@@ -503,6 +507,9 @@ def main():
     ap.add_argument("--adapt", type=int, default=300, help="untimed adaptation transitions")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU baseline work")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--fixed-step", type=float, default=0.0,
+                    help="chain workloads: fixed step size, no adaptation (profiling aid)")
+    ap.add_argument("--max-tree-depth", type=int, default=0)
     ap.add_argument("--ref-transitions", type=int, default=2)
     ap.add_argument("--ref-budget", type=float, default=150.0)
     args = ap.parse_args()

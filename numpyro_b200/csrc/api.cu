@@ -73,6 +73,7 @@ struct b200mc_handle {
     unsigned char* snap = nullptr;
     int* status = nullptr;
     unsigned* active = nullptr;
+    MatvecRequest* reqs = nullptr;
     int RA1 = 0, K1 = 0, RA2 = 0, splits = 1, snap_stride = 0;
   } bt;
 };
@@ -213,7 +214,7 @@ extern "C" void b200mc_destroy(b200mc_handle* h) {
   cudaFree(h->bt.x_hi); cudaFree(h->bt.x_lo); cudaFree(h->bt.xt_hi); cudaFree(h->bt.xt_lo);
   cudaFree(h->bt.b_hi); cudaFree(h->bt.b_lo); cudaFree(h->bt.r_hi); cudaFree(h->bt.r_lo);
   cudaFree(h->bt.ll_part); cudaFree(h->bt.gpart); cudaFree(h->bt.col_scale);
-  cudaFree(h->bt.snap); cudaFree(h->bt.status); cudaFree(h->bt.active);
+  cudaFree(h->bt.snap); cudaFree(h->bt.status); cudaFree(h->bt.active); cudaFree(h->bt.reqs);
   delete h;
 }
 
@@ -412,7 +413,8 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
       b.snap_stride = (int)((sizeof(Sampler<BlockGroup>) + 255) / 256 * 256);
       ACK(alloc((void**)&b.snap, (size_t)C * b.snap_stride));
       ACK(alloc((void**)&b.status, sizeof(int) * C));
-      ACK(alloc((void**)&b.active, sizeof(unsigned) * (kBatchStepsPerSync + 1)));
+      ACK(alloc((void**)&b.reqs, sizeof(MatvecRequest) * C));
+      ACK(alloc((void**)&b.active, sizeof(unsigned) * (kBatchStepsPerSync + 2)));
       ACK(cudaDeviceSynchronize());
     }
   }
@@ -513,6 +515,7 @@ static void fill_batch_launch(b200mc_handle* h, BatchLaunch& L) {
   memset(&L, 0, sizeof(L));
   L.P = h->P; L.M = h->M; L.cs = h->cs; L.cv = h->cv; L.work = h->work; L.C = h->C;
   L.snap = b.snap; L.snap_stride = b.snap_stride; L.status = b.status; L.active = b.active;
+  L.reqs = b.reqs;
   L.b_hi = b.b_hi; L.b_lo = b.b_lo; L.K1 = b.K1;
   L.gpart = b.gpart; L.splits = b.splits; L.RA2 = b.RA2;
   L.ll_part = b.ll_part; L.n_rowgroups = b.RA1 / 32; L.col_scale = b.col_scale;
@@ -528,24 +531,42 @@ static int launch_batch(b200mc_handle* h, const CollectSpec& col, const uint32_t
   fill_batch_launch(h, L);
   L.col = col; L.init_keys = keys; L.user_init = user_init;
   auto& b = h->bt;
-  CK(cudaMemsetAsync(b.active, 0, sizeof(unsigned) * (kBatchStepsPerSync + 1), st));
-  L.begin = 1;
-  L.active = b.active + kBatchStepsPerSync;
+  unsigned* const slot_begin = b.active + kBatchStepsPerSync;     // count after the first launch
+  unsigned* const slot_scrap = b.active + kBatchStepsPerSync + 1;  // launches nobody reads
+  const bool dense = h->P.dense_mass != 0;
+  const dim3 mv_grid((h->D + kMatvecRows - 1) / kMatvecRows, h->C);
+  const size_t mv_smem = sizeof(float) * 2 * (size_t)h->D;
+  // a chain needs at most three sweeps between two gradients (leaf, then the two of a
+  // transition start); chains that still wait afterwards simply continue in the next step
+  auto sweeps_and_resumes = [&](unsigned* count_slot) {
+    for (int k = 0; k < 3; ++k) {
+      batch_matvec_kernel<<<mv_grid, kMatvecThreads, mv_smem, st>>>(L);
+      L.kind = BATCH_RESUME;
+      L.active = (k == 2) ? count_slot : slot_scrap;
+      batch_step_kernel<<<h->C, kBatchThreads, 0, st>>>(L);
+      g_launches += 2;
+    }
+  };
+  CK(cudaMemsetAsync(b.active, 0, sizeof(unsigned) * (kBatchStepsPerSync + 2), st));
+  L.kind = BATCH_BEGIN;
+  L.active = dense ? slot_scrap : slot_begin;
   batch_step_kernel<<<h->C, kBatchThreads, 0, st>>>(L);
   g_launches++;
+  L.init_keys = nullptr;
+  if (dense) sweeps_and_resumes(slot_begin);
   CK(cudaGetLastError());
   unsigned active = 0;
-  CK(cudaMemcpyAsync(&active, b.active + kBatchStepsPerSync, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(&active, slot_begin, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
-  L.begin = 0;
-  L.init_keys = nullptr;
   while (active > 0) {
     CK(cudaMemsetAsync(b.active, 0, sizeof(unsigned) * kBatchStepsPerSync, st));
     for (int i = 0; i < kBatchStepsPerSync; ++i) {
       if (launch_batch_gemms(h, st)) return 1;
-      L.active = b.active + i;
+      L.kind = BATCH_GRAD;
+      L.active = dense ? slot_scrap : b.active + i;
       batch_step_kernel<<<h->C, kBatchThreads, 0, st>>>(L);
       g_launches++;
+      if (dense) sweeps_and_resumes(b.active + i);
     }
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(&active, b.active + kBatchStepsPerSync - 1, sizeof(unsigned), cudaMemcpyDeviceToHost, st));

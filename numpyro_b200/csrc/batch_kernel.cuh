@@ -6,6 +6,11 @@
 //   [GEMM 1 + residual epilogue] -> [GEMM 2, split-K] -> [batch_step_kernel: one CTA per chain
 //    finishes its potential (chain rule, priors), advances its sampler by one gradient and
 //    writes the operand row of its next point].
+// With a dense mass matrix the sampler does not sweep its D x D matrices itself (one CTA
+// cannot keep enough loads in flight): it yields a MatvecRequest, batch_matvec_kernel serves
+// the requests of all chains at once with the whole machine (HBM-bound: D*D*4 bytes per
+// chain per leapfrog, both right-hand sides of a leapfrog in one sweep), and a resume launch
+// of batch_step_kernel continues the step machine.
 // Chains are NOT synchronised at transition boundaries: a chain that ends a transition starts
 // the next one in the same step, so no lane of the batch idles until its own last transition.
 // The sampler object lives in global memory between launches (a plain-data snapshot).
@@ -17,6 +22,9 @@ namespace b200mc {
 
 constexpr int kBatchThreads = 512;
 constexpr int kBatchCols = 256;  // chains per operand image = columns of one GEMM tile
+enum BatchKind { BATCH_BEGIN = 0, BATCH_GRAD = 1, BATCH_RESUME = 2 };
+constexpr int kMatvecThreads = 256;
+constexpr int kMatvecRows = 64;  // rows of one chain's matrix per CTA
 
 struct BatchLaunch {
   SamplerParams P;
@@ -28,11 +36,12 @@ struct BatchLaunch {
   int C;
   const uint32_t* init_keys;
   int user_init;
-  int begin;            // 1: first launch of a b200mc_init / b200mc_sample call
+  int kind;             // BATCH_BEGIN / BATCH_GRAD / BATCH_RESUME
+  MatvecRequest* reqs;  // [C] pending dense-mass sweeps (status 2)
   unsigned char* snap;  // [C][snap_stride] sampler snapshots
   int snap_stride;
-  int* status;          // [C] 0 = waiting for a gradient, 1 = done
-  unsigned* active;     // chains still waiting for a gradient after this launch
+  int* status;          // [C] 0 = waiting for a gradient, 1 = done, 2 = waiting for a sweep
+  unsigned* active;     // chains not done after this launch
   // potential plumbing (one column group of kBatchCols chains)
   unsigned char *b_hi, *b_lo;  // images of B [256][K1]: the linear-predictor coefficients
   int K1;
@@ -122,7 +131,7 @@ __device__ float hs_finish(const BatchLaunch& L, const G& g, const float* z, flo
 
 // One CTA per chain.  begin = 1: set the sampler up and publish its first point.  Otherwise:
 // finish the potential at the published point, advance, publish the next point.
-__global__ void __launch_bounds__(kBatchThreads) batch_step_kernel(const __grid_constant__ BatchLaunch L) {
+__global__ void __launch_bounds__(kBatchThreads, 2) batch_step_kernel(const __grid_constant__ BatchLaunch L) {
   __shared__ float red_scratch[64];
   const int c = blockIdx.x;
   if (c >= L.C) return;
@@ -133,33 +142,109 @@ __global__ void __launch_bounds__(kBatchThreads) batch_step_kernel(const __grid_
   float* base = L.work + (long)c * num_slots(L.P.max_depth, L.P.dense_mass) * D;
   S_t S;
   StepResult r;
-  if (L.begin) {
+  if (L.kind == BATCH_BEGIN) {
     S.setup(&L.P, g, base, D, 1, c, L.C, &L.col);
+    S.mv_yield = L.P.dense_mass != 0;
     S.load(L.cs, L.cv);
     if (L.init_keys)
       r = S.begin_init(Key{L.init_keys[2 * c], L.init_keys[2 * c + 1]}, L.user_init != 0);
     else
       r = S.begin_sampling();
   } else {
-    if (L.status[c] != 0) return;
+    const int st = L.status[c];
+    if (st != ((L.kind == BATCH_GRAD) ? 0 : 2)) {  // not this launch's business
+      if (threadIdx.x == 0 && st != 1) atomicAdd(L.active, 1u);
+      return;
+    }
     S = *snap;
     S.P = &L.P; S.g = g; S.w = base; S.col = &L.col;
     if (S.dense) S.dn = L.cv.dense + (long)c * 4 * D * D;
-    const float U = hs_finish(L, g, S.v(LZ), S.v(LG), c);
-    r = S.advance(U);
+    if (L.kind == BATCH_GRAD) {
+      const float U = hs_finish(L, g, S.v(LZ), S.v(LG), c);
+      r = S.advance(U);
+    } else {
+      r = S.resume();
+    }
   }
   if (r == NEED_GRAD) {
     g.sync();
     hs_prepare(L, g, S.v(LZ), c);
+    if (threadIdx.x == 0) L.status[c] = 0;
+  } else if (r == NEED_MATVEC) {
     if (threadIdx.x == 0) {
-      L.status[c] = 0;
-      atomicAdd(L.active, 1u);
+      L.reqs[c] = S.rq;
+      L.status[c] = 2;
     }
   } else {
     S.store(L.cs, L.cv);
     if (threadIdx.x == 0) L.status[c] = 1;
   }
-  if (threadIdx.x == 0) *snap = S;
+  if (threadIdx.x == 0) {
+    if (r != FINISHED) atomicAdd(L.active, 1u);
+    *snap = S;
+  }
+}
+
+// Serves the pending dense-mass sweeps of all chains: CTA (x, y) computes kMatvecRows rows
+// of chain y's product(s).  Warp per row, lanes stride over the columns (coalesced 128-byte
+// lines, 8 in flight per warp), the right-hand side(s) staged in shared memory; both products
+// of a request come from ONE pass over the matrix.  Fixed summation order => deterministic.
+__global__ void __launch_bounds__(kMatvecThreads, 4) batch_matvec_kernel(const __grid_constant__ BatchLaunch L) {
+  extern __shared__ float mv_src[];  // [2][D]
+  const int c = blockIdx.y;
+  if (L.status[c] != 2) return;
+  const MatvecRequest rq = L.reqs[c];
+  const int D = L.P.D;
+  const int i0 = blockIdx.x * kMatvecRows;
+  float* base = L.work + (long)c * num_slots(L.P.max_depth, L.P.dense_mass) * D;
+  const float* M = L.cv.dense + ((long)c * 4 + rq.mat) * D * D;
+  const float* src1 = base + (long)rq.src1 * D;
+  const float* src2 = rq.src2 >= 0 ? base + (long)rq.src2 * D : nullptr;
+  float* dst1 = base + (long)rq.dst1 * D;
+  float* dst2 = rq.dst2 >= 0 ? base + (long)rq.dst2 * D : nullptr;
+  float* s1 = mv_src;
+  float* s2 = mv_src + D;
+  for (int j = threadIdx.x; j < D; j += blockDim.x) {
+    s1[j] = src1[j];
+    s2[j] = src2 ? src2[j] : 0.f;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int i1 = (i0 + kMatvecRows < D) ? i0 + kMatvecRows : D;
+  for (int i = i0 + wid; i < i1; i += nw) {
+    const float* row = M + (long)i * D;
+    const int n = rq.lower ? i + 1 : D;
+    float a[8], b[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { a[k] = 0.f; b[k] = 0.f; }
+    int j = lane;
+    for (; j + 224 < n; j += 256) {
+      float m[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) m[k] = __ldcs(row + j + 32 * k);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        a[k] = fmaf(m[k], s1[j + 32 * k], a[k]);
+        b[k] = fmaf(m[k], s2[j + 32 * k], b[k]);
+      }
+    }
+    for (; j < n; j += 32) {
+      const float m = __ldcs(row + j);
+      a[0] = fmaf(m, s1[j], a[0]);
+      b[0] = fmaf(m, s2[j], b[0]);
+    }
+    float ta = ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
+    float tb = ((b[0] + b[1]) + (b[2] + b[3])) + ((b[4] + b[5]) + (b[6] + b[7]));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      ta += __shfl_xor_sync(0xffffffffu, ta, o);
+      tb += __shfl_xor_sync(0xffffffffu, tb, o);
+    }
+    if (lane == 0) {
+      dst1[i] = ta;
+      if (dst2) dst2[i] = tb;
+    }
+  }
 }
 
 // Evaluation hook: phase 0 publishes the operand rows of the points eval_z[c], phase 1 turns

@@ -49,14 +49,24 @@ enum Slot {
   CKPT0                                                    // r_ckpts[i], r_sum_ckpts[i] (, M^-1 r_ckpts[i]) = CKPT0 + stride*i + {0,1(,2)}
 };
 // Diagonal mass: 2 vectors per checkpoint.  Dense mass: 3 (the cached M^-1 r_ckpts[i]) plus
-// three more slots behind the checkpoints (LV, V_LEFT, V_RIGHT: cached M^-1 r of LR, R_LEFT,
-// R_RIGHT); keeping them out of the diagonal layout buys shared memory for the glm ring.
+// six more slots behind the checkpoints (LV, V_LEFT, V_RIGHT: cached M^-1 r of LR, R_LEFT,
+// R_RIGHT; LQ, Q_LEFT, Q_RIGHT: cached M^-1 grad of LG, G_LEFT, G_RIGHT, CTA-per-chain mode
+// only); keeping them out of the diagonal layout buys shared memory for the glm ring.
 __host__ __device__ inline int num_slots(int max_depth, int dense) {
-  return CKPT0 + (dense ? 3 * max_depth + 3 : 2 * max_depth);
+  return CKPT0 + (dense ? 3 * max_depth + 6 : 2 * max_depth);
 }
 
 enum Phase { PH_INIT = 0, PH_TREE, PH_HMC, PH_IDLE, PH_FAIL, PH_FRSS };
-enum StepResult { NEED_GRAD = 0, FINISHED = 1 };
+// NEED_MATVEC: only with mv_yield (lock-step engine): the dense-mass product described by
+// `rq` must be computed by the caller, then resume() continues where advance() stopped.
+enum StepResult { NEED_GRAD = 0, FINISHED = 1, NEED_MATVEC = 2 };
+
+struct MatvecRequest {
+  int mat;         // which of the chain's four D x D matrices
+  int lower;       // 1: triangular factor, columns j <= i only
+  int src1, dst1;  // slots: dst1 = M src1
+  int src2, dst2;  // second right-hand side of the same sweep, or -1
+};
 
 __device__ __forceinline__ float logaddexp_f32(float a, float b) {
   // jnp.logaddexp: amax + log1p(exp(-|a-b|)), with the (inf - inf) case = a + b
@@ -133,6 +143,11 @@ struct Sampler {
   int fr_last_dir, fr_dir, fr_cont;
   Key fr_key;
   Key init_mom_key;
+  // lock-step engine: dense-mass sweeps are handed to a batched kernel instead of run in place
+  bool mv_yield, leaf_cached;
+  int mv_resume;  // 0 none, 1 leaf finish, 2 / 3 transition start
+  float pending_U;
+  MatvecRequest rq;
 
   __device__ __forceinline__ float* v(int slot) const { return w + (long)slot * slot_stride; }
   __device__ __forceinline__ float* ckpt_r(int i) const { return v(CKPT0 + ck_stride * i); }
@@ -141,6 +156,9 @@ struct Sampler {
 #define LV (ck_end)  // dense-only slots, see num_slots()
 #define V_LEFT (ck_end + 1)
 #define V_RIGHT (ck_end + 2)
+#define LQ (ck_end + 3)
+#define Q_LEFT (ck_end + 4)
+#define Q_RIGHT (ck_end + 5)
   // dense mass: this chain's (or this replica's) four D x D matrices in global memory
   __device__ __forceinline__ float* mat(int which) const { return dn + (long)which * D * D; }
 
@@ -169,6 +187,7 @@ struct Sampler {
     pre_valid = 0;
     pre_d_valid = 0; pre_t_valid = 0; pre_a_valid = 0;
     deferred = 0;
+    mv_yield = false; leaf_cached = false; mv_resume = 0;
   }
 
   __device__ void load(const ChainScalars* cs, const ChainVectors& cv) {
@@ -248,6 +267,59 @@ struct Sampler {
     g.sync();
   }
 
+  // Two right-hand sides in ONE sweep over the matrix (CTA per chain only): dst1 = M src1,
+  // dst2 = M src2.  The matrix (16 MB at D = 2001) is the HBM traffic of a dense-mass
+  // leapfrog; reading it once instead of twice is the point.  Same per-row summation order
+  // as matvec().
+  __device__ __noinline__ void matvec2(const float* M, const float* src1, const float* src2,
+                                       float* dst1, float* dst2) {
+    g.sync();
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int i = wid; i < D; i += nw) {
+      const float* row = M + (long)i * D;
+      float a[8], b[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { a[k] = 0.f; b[k] = 0.f; }
+      int j = lane;
+      for (; j + 224 < D; j += 256) {
+        float m[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) m[k] = __ldcg(row + j + 32 * k);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          a[k] = fmaf(m[k], src1[j + 32 * k], a[k]);
+          b[k] = fmaf(m[k], src2[j + 32 * k], b[k]);
+        }
+      }
+      for (; j < D; j += 32) {
+        const float m = __ldcg(row + j);
+        a[0] = fmaf(m, src1[j], a[0]);
+        b[0] = fmaf(m, src2[j], b[0]);
+      }
+      float ta = ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
+      float tb = ((b[0] + b[1]) + (b[2] + b[3])) + ((b[4] + b[5]) + (b[6] + b[7]));
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        ta += __shfl_xor_sync(0xffffffffu, ta, o);
+        tb += __shfl_xor_sync(0xffffffffu, tb, o);
+      }
+      if (lane == 0) {
+        dst1[i] = ta;
+        dst2[i] = tb;
+      }
+    }
+    g.sync();
+  }
+
+  // Dense mass, leaf (LZ, LR, LG) complete: cache LV = M^-1 LR for the energy and the U-turn
+  // tests and, CTA per chain, LQ = M^-1 LG from the same sweep: the next half step then needs
+  // no sweep of its own, M^-1 (r - h g) = LV - h LQ (one rounding apart from the reference's
+  // matmul of the updated momentum, hmc_util.py:297-302, 1203-1223).
+  __device__ __forceinline__ void dense_leaf_cache() {
+    if constexpr (G::kBlockWide) matvec2(mat(0), v(LR), v(LG), v(LV), v(LQ));
+    else matvec(mat(0), v(LR), v(LV));
+  }
+
   // 0.5 * dot(M^-1 r, r): hmc_util.py:1183-1200.  Dense: vslot holds the cached M^-1 r.
   __device__ __forceinline__ float kinetic(int rslot, int vslot = -1) {
     const float *r = v(rslot), *im = v(IMM);
@@ -312,6 +384,20 @@ struct Sampler {
     const float *gr = v(LG), *im = v(IMM);
     const float hs = 0.5f * eps_s;
     if (dense) {
+      if constexpr (G::kBlockWide) {
+        float* lv = v(LV);
+        const float* lq = v(LQ);
+        B200MC_FOR_D {
+          const float t = hs * gr[d];
+          r[d] = r[d] - t;
+          const float tq = hs * lq[d];
+          const float vh = lv[d] - tq;  // M^-1 of the half-stepped momentum, by linearity
+          lv[d] = vh;
+          const float dz = eps_s * vh;
+          z[d] = z[d] + dz;
+        }
+        return;
+      }
       B200MC_FOR_D {
         const float t = hs * gr[d * es];
         r[d * es] = r[d * es] - t;
@@ -336,6 +422,7 @@ struct Sampler {
 
   // second half: hmc_util.py:306-308
   __device__ __forceinline__ void finish_leapfrog() {
+    if (leaf_cached) return;  // resume(): momentum and its M^-1 products are already in place
     float* r = v(LR);
     const float* gr = v(LG);
     const float hs = 0.5f * eps_s;
@@ -343,7 +430,7 @@ struct Sampler {
       const float t = hs * gr[d * es];
       r[d * es] = r[d * es] - t;
     }
-    if (dense) matvec(mat(0), r, v(LV));  // cached for the energy and the U-turn tests
+    if (dense) dense_leaf_cache();  // cached for the energy and the U-turn tests
   }
 
   // ------------------------------------------------------------------ warm-up adaptation
@@ -546,9 +633,9 @@ struct Sampler {
     const float scale = (fr_dir > 0) ? 2.0f : ((fr_dir < 0) ? 0.5f : 1.0f);
     fr_step = scale * fr_step;
     draw_momentum(k_mom, LR, true);
-    if (dense) matvec(mat(0), v(LR), v(LV));
-    fr_e_cur = kinetic(LR, LV) + s.potential_energy;
     copy(LZ, Z_PROP); copy(LG, G_PROP);
+    if (dense) dense_leaf_cache();
+    fr_e_cur = kinetic(LR, LV) + s.potential_energy;
     eps_s = fr_step;
     phase = PH_FRSS;
     half_step();
@@ -633,9 +720,17 @@ struct Sampler {
     if (!pre_t_valid) compute_transition_rng();
     pre_t_valid = 0;
     s.rng_key[0] = pre_t_rng_key.k0; s.rng_key[1] = pre_t_rng_key.k1;
-    const Key k_tr = pre_t_k_tr;
-    if (P->algo == ALGO_HMC) return start_hmc(k_tr);
+    if (P->algo == ALGO_HMC) return start_hmc(pre_t_k_tr);
+    if (mv_yield && dense) {  // r = M^{1/2} eps as a batched sweep
+      rq = MatvecRequest{1, 1, EPS_NEXT, R_LEFT, -1, -1};
+      mv_resume = 2;
+      return NEED_MATVEC;
+    }
     momentum_from_eps(R_LEFT);
+    return start_transition_b();
+  }
+
+  __device__ StepResult start_transition_b() {
     pre_d = pre_t_d;  // the first doubling of this transition
     pre_d_valid = 1;
     {
@@ -652,14 +747,30 @@ struct Sampler {
       }
     }
     if (dense) {
-      matvec(mat(0), v(R_LEFT), v(V_LEFT));
+      if constexpr (G::kBlockWide) {
+        if (mv_yield) {
+          rq = MatvecRequest{0, 0, R_LEFT, V_LEFT, G_PROP, Q_LEFT};
+          mv_resume = 3;
+          return NEED_MATVEC;
+        }
+        matvec2(mat(0), v(R_LEFT), v(G_PROP), v(V_LEFT), v(Q_LEFT));
+      } else {
+        matvec(mat(0), v(R_LEFT), v(V_LEFT));
+      }
+    }
+    return start_transition_c();
+  }
+
+  __device__ StepResult start_transition_c() {
+    if (dense) {
+      if constexpr (G::kBlockWide) copy(Q_RIGHT, Q_LEFT);
       copy(V_RIGHT, V_LEFT);
     }
     e0 = s.potential_energy + kinetic(R_LEFT, V_LEFT);
     depth = 0; weight = 0.f; turning = 0; diverging = 0; sum_acc = 0.f; nprop = 0;
     prop_pe = s.potential_energy;
     prop_energy = e0;
-    tree_key = k_tr;
+    tree_key = pre_t_k_tr;
     max_depth_cur = (s.i < P->num_warmup) ? P->max_depth_warmup : P->max_depth_sample;
     phase = PH_TREE;
     if (!(depth < max_depth_cur)) return finish_transition(nanf(""), 0, 0);
@@ -688,6 +799,12 @@ struct Sampler {
       copy(LZ, Z_RIGHT); copy(LR, R_RIGHT); copy(LG, G_RIGHT);
     } else {
       copy(LZ, Z_LEFT); copy(LR, R_LEFT); copy(LG, G_LEFT);
+    }
+    if constexpr (G::kBlockWide) {
+      if (dense) {
+        copy(LV, going_right ? V_RIGHT : V_LEFT);
+        copy(LQ, going_right ? Q_RIGHT : Q_LEFT);
+      }
     }
     half_step();
   }
@@ -1098,9 +1215,11 @@ struct Sampler {
     if (going_right) {
       copy(Z_RIGHT, LZ); copy(R_RIGHT, LR); copy(G_RIGHT, LG);
       if (dense) copy(V_RIGHT, LV);
+      if (dense && G::kBlockWide) copy(Q_RIGHT, LQ);
     } else {
       copy(Z_LEFT, LZ); copy(R_LEFT, LR); copy(G_LEFT, LG);
       if (dense) copy(V_LEFT, LV);
+      if (dense && G::kBlockWide) copy(Q_LEFT, LQ);
     }
     {
       float* rs = v(R_SUM);
@@ -1141,7 +1260,7 @@ struct Sampler {
     if (P->has_trajectory_length) eps = P->trajectory_length / (float)n;
     hmc_steps = n; hmc_done = 0;
     eps_s = eps;
-    if (dense) matvec(mat(0), v(LR), v(LV));
+    if (dense) dense_leaf_cache();
     energy_old = s.potential_energy + kinetic(LR, LV);
     phase = PH_HMC;
     half_step();
@@ -1269,9 +1388,41 @@ struct Sampler {
 
   // The gradient of the potential at v(LZ) has been written to v(LG); U is its value.
   __device__ StepResult advance(float U) {
+    if constexpr (G::kBlockWide) {
+      if (mv_yield && dense && (phase == PH_TREE || phase == PH_HMC || phase == PH_FRSS)) {
+        // second half of the leapfrog, then LV = M^-1 LR and LQ = M^-1 LG from the caller
+        float* r = v(LR);
+        const float* gr = v(LG);
+        const float hs = 0.5f * eps_s;
+        B200MC_FOR_D {
+          const float t = hs * gr[d];
+          r[d] = r[d] - t;
+        }
+        rq = MatvecRequest{0, 0, LR, LV, LG, LQ};
+        pending_U = U;
+        mv_resume = 1;
+        return NEED_MATVEC;
+      }
+    }
     const StepResult r = advance_early(U);
     if (deferred) run_deferred();
     return r;
+  }
+
+  // The product requested through `rq` is in place: continue.
+  __device__ StepResult resume() {
+    const int where = mv_resume;
+    mv_resume = 0;
+    if (where == 1) {
+      leaf_cached = true;
+      const StepResult r = advance_early(pending_U);
+      leaf_cached = false;
+      if (deferred) run_deferred();
+      return r;
+    }
+    if (where == 2) return start_transition_b();
+    if (where == 3) return start_transition_c();
+    return FINISHED;
   }
 
   // advance() in two parts: when `deferred` is set on return, the next point is ready in
@@ -1290,6 +1441,9 @@ struct Sampler {
 #undef LV
 #undef V_LEFT
 #undef V_RIGHT
+#undef LQ
+#undef Q_LEFT
+#undef Q_RIGHT
 };
 
 }  // namespace b200mc
