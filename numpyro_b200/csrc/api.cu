@@ -9,6 +9,9 @@
 #include <string>
 #include <vector>
 
+#include <cusolverDn.h>  // types only: the library is loaded on demand (dlopen)
+#include <dlfcn.h>
+
 #include "../../include/b200mc.h"
 #include "batch_kernel.cuh"
 #include "chain_kernel.cuh"
@@ -242,6 +245,15 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   cudaGetDevice(&h->device);
   cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, h->device);
   cudaDeviceGetAttribute(&h->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device);
+  {
+    // the step machine's call chains (transition end -> adaptation -> next transition) are
+    // deeper than ptxas' static estimate accounts for: give the device stack head-room
+    size_t stack = 2048;
+    if (const char* e = getenv("B200MC_STACK_BYTES")) stack = (size_t)atoi(e);
+    size_t cur = 0;
+    cudaDeviceGetLimit(&cur, cudaLimitStackSize);
+    if (cur < stack) cudaDeviceSetLimit(cudaLimitStackSize, stack);
+  }
   const int C = h->C = c.num_chains, D = h->D;
   P.D = D;
   P.algo = c.algo;
@@ -495,6 +507,90 @@ static int launch_chain(b200mc_handle* h, const CollectSpec& col, const uint32_t
   return 0;
 }
 
+// ---------------------------------------------------------------- window-end factorisation
+// Dense mass, lock-step engine: the Cholesky factor and the triangular inverse of a parked
+// chain's covariance (hmc_util.py:229-233: jnp.linalg.cholesky, solve_triangular) come from
+// cuSOLVER, a plain library call five times per warm-up and chain, not a hot path.  The
+// library is dlopen'ed on first use so that libb200mc.so itself keeps no dependency on it.
+namespace {
+struct Solver {
+  void* lib = nullptr;
+  cusolverDnHandle_t handle = nullptr;
+  decltype(&cusolverDnCreate) create = nullptr;
+  decltype(&cusolverDnSetStream) set_stream = nullptr;
+  decltype(&cusolverDnSpotrf_bufferSize) potrf_size = nullptr;
+  decltype(&cusolverDnSpotrf) potrf = nullptr;
+  decltype(&cusolverDnXtrtri_bufferSize) trtri_size = nullptr;
+  decltype(&cusolverDnXtrtri) trtri = nullptr;
+  void* work = nullptr;
+  size_t work_bytes = 0;
+  void* host_work = nullptr;
+  size_t host_bytes = 0;
+  int* info = nullptr;
+};
+Solver* get_solver() {
+  static Solver S;
+  if (S.handle) return &S;
+  const char* names[] = {"libcusolver.so.11", "libcusolver.so", "/usr/local/cuda/lib64/libcusolver.so.11"};
+  for (const char* n : names)
+    if (!S.lib) S.lib = dlopen(n, RTLD_NOW | RTLD_LOCAL);
+  if (!S.lib) { fail("dense mass: cannot load libcusolver (%s)", dlerror()); return nullptr; }
+#define SYM(field, name)                                                   \
+  S.field = (decltype(S.field))dlsym(S.lib, name);                         \
+  if (!S.field) { fail("dense mass: libcusolver lacks %s", name); return nullptr; }
+  SYM(create, "cusolverDnCreate") SYM(set_stream, "cusolverDnSetStream")
+  SYM(potrf_size, "cusolverDnSpotrf_bufferSize") SYM(potrf, "cusolverDnSpotrf")
+  SYM(trtri_size, "cusolverDnXtrtri_bufferSize") SYM(trtri, "cusolverDnXtrtri")
+#undef SYM
+  if (S.create(&S.handle) != CUSOLVER_STATUS_SUCCESS) { fail("cusolverDnCreate failed"); S.handle = nullptr; return nullptr; }
+  if (cudaMalloc((void**)&S.info, sizeof(int) * 2) != cudaSuccess) { fail("out of memory"); return nullptr; }
+  return &S;
+}
+}  // namespace
+
+// mats: one chain's [4][D][D]; n = Welford count.  Everything on stream st.
+static int factor_chain_dense(float* mats, int D, int n, int regularize, cudaStream_t st) {
+  Solver* S = get_solver();
+  if (!S) return 1;
+  if (S->set_stream(S->handle, st) != CUSOLVER_STATUS_SUCCESS) return fail("cusolverDnSetStream failed");
+  const long DD = (long)D * D;
+  float *msq = mats + DD, *W = mats + 2 * DD, *m2 = mats + 3 * DD;
+  int lwork = 0;
+  size_t dev_b = 0, host_b = 0;
+  if (S->potrf_size(S->handle, CUBLAS_FILL_MODE_LOWER, D, W, D, &lwork) != CUSOLVER_STATUS_SUCCESS)
+    return fail("cusolverDnSpotrf_bufferSize failed");
+  if (S->trtri_size(S->handle, CUBLAS_FILL_MODE_UPPER, CUBLAS_DIAG_NON_UNIT, D, CUDA_R_32F, msq, D, &dev_b,
+                    &host_b) != CUSOLVER_STATUS_SUCCESS)
+    return fail("cusolverDnXtrtri_bufferSize failed");
+  size_t need = sizeof(float) * (size_t)lwork;
+  if (dev_b > need) need = dev_b;
+  if (need > S->work_bytes) {
+    cudaFree(S->work);
+    CK(cudaMalloc(&S->work, need));
+    S->work_bytes = need;
+  }
+  if (host_b > S->host_bytes) {
+    free(S->host_work);
+    S->host_work = malloc(host_b);
+    S->host_bytes = host_b;
+  }
+  factor_cov_kernel<<<592, 256, 0, st>>>(mats, D, (float)n, regularize);
+  // row-major symmetric W == column-major W; LOWER (column-major) leaves Lc[a][b] at W[b*D + a]
+  if (S->potrf(S->handle, CUBLAS_FILL_MODE_LOWER, D, W, D, (float*)S->work, lwork, S->info) != CUSOLVER_STATUS_SUCCESS)
+    return fail("cusolverDnSpotrf failed");
+  factor_tinv_kernel<<<592, 256, 0, st>>>(mats, D);
+  CK(cudaMemcpyAsync(W, m2, sizeof(float) * DD, cudaMemcpyDeviceToDevice, st));  // mass_matrix_sqrt_inv
+  CK(cudaMemsetAsync(m2, 0, sizeof(float) * DD, st));                             // Welford restarts
+  // row-major lower tril_inv == column-major UPPER of its transpose: inverting that in place
+  // leaves the row-major lower inverse, mass_matrix_sqrt (:231-233)
+  if (S->trtri(S->handle, CUBLAS_FILL_MODE_UPPER, CUBLAS_DIAG_NON_UNIT, D, CUDA_R_32F, msq, D, S->work, dev_b,
+               S->host_work, host_b, S->info + 1) != CUSOLVER_STATUS_SUCCESS)
+    return fail("cusolverDnXtrtri failed");
+  g_launches += 2;
+  CK(cudaGetLastError());
+  return 0;
+}
+
 // The two contractions of one batched potential evaluation (batch_kernel.cuh).
 static int launch_batch_gemms(b200mc_handle* h, cudaStream_t st) {
   auto& b = h->bt;
@@ -534,6 +630,8 @@ static int launch_batch(b200mc_handle* h, const CollectSpec& col, const uint32_t
   unsigned* const slot_begin = b.active + kBatchStepsPerSync;     // count after the first launch
   unsigned* const slot_scrap = b.active + kBatchStepsPerSync + 1;  // launches nobody reads
   const bool dense = h->P.dense_mass != 0;
+  std::vector<int> status_h(h->C);
+  std::vector<MatvecRequest> reqs_h(h->C);
   const dim3 mv_grid((h->D + kMatvecRows - 1) / kMatvecRows, h->C);
   const size_t mv_smem = sizeof(float) * 2 * (size_t)h->D;
   // a chain needs at most three sweeps between two gradients (leaf, then the two of a
@@ -570,6 +668,22 @@ static int launch_batch(b200mc_handle* h, const CollectSpec& col, const uint32_t
     }
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(&active, b.active + kBatchStepsPerSync - 1, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    if (dense && h->P.adapt_mass_matrix) {
+      // chains parked at a window end: covariance, Cholesky, triangular inverse, then resume
+      CK(cudaMemcpyAsync(status_h.data(), b.status, sizeof(int) * h->C, cudaMemcpyDeviceToHost, st));
+      CK(cudaMemcpyAsync(reqs_h.data(), b.reqs, sizeof(MatvecRequest) * h->C, cudaMemcpyDeviceToHost, st));
+      CK(cudaStreamSynchronize(st));
+      bool any = false;
+      for (int c = 0; c < h->C; ++c) {
+        if (status_h[c] != 3) continue;
+        if (factor_chain_dense(h->cv.dense + (long)c * 4 * h->D * h->D, h->D, reqs_h[c].src1,
+                               h->P.regularize_mass_matrix, st))
+          return 1;
+        status_h[c] = 2;  // its request has mat = -1: the next resume launch just continues
+        any = true;
+      }
+      if (any) CK(cudaMemcpyAsync(b.status, status_h.data(), sizeof(int) * h->C, cudaMemcpyHostToDevice, st));
+    }
     CK(cudaStreamSynchronize(st));
   }
   return 0;

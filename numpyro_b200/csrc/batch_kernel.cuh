@@ -40,7 +40,8 @@ struct BatchLaunch {
   MatvecRequest* reqs;  // [C] pending dense-mass sweeps (status 2)
   unsigned char* snap;  // [C][snap_stride] sampler snapshots
   int snap_stride;
-  int* status;          // [C] 0 = waiting for a gradient, 1 = done, 2 = waiting for a sweep
+  int* status;          // [C] 0 = waiting for a gradient, 1 = done, 2 = waiting for a sweep,
+                        // 3 = waiting for the window-end factorisation (host side)
   unsigned* active;     // chains not done after this launch
   // potential plumbing (one column group of kBatchCols chains)
   unsigned char *b_hi, *b_lo;  // images of B [256][K1]: the linear-predictor coefficients
@@ -170,10 +171,10 @@ __global__ void __launch_bounds__(kBatchThreads, 2) batch_step_kernel(const __gr
     g.sync();
     hs_prepare(L, g, S.v(LZ), c);
     if (threadIdx.x == 0) L.status[c] = 0;
-  } else if (r == NEED_MATVEC) {
+  } else if (r == NEED_MATVEC || r == NEED_FACTOR) {
     if (threadIdx.x == 0) {
       L.reqs[c] = S.rq;
-      L.status[c] = 2;
+      L.status[c] = (r == NEED_MATVEC) ? 2 : 3;  // 3: parked until the host has factorised
     }
   } else {
     S.store(L.cs, L.cv);
@@ -194,13 +195,14 @@ __global__ void __launch_bounds__(kMatvecThreads, 4) batch_matvec_kernel(const _
   const int c = blockIdx.y;
   if (L.status[c] != 2) return;
   const MatvecRequest rq = L.reqs[c];
+  if (rq.mat < 0) return;  // nothing to sweep (a chain resuming after its factorisation)
   const int D = L.P.D;
   const int i0 = blockIdx.x * kMatvecRows;
   float* base = L.work + (long)c * num_slots(L.P.max_depth, L.P.dense_mass) * D;
   const float* M = L.cv.dense + ((long)c * 4 + rq.mat) * D * D;
   const float* src1 = base + (long)rq.src1 * D;
   const float* src2 = rq.src2 >= 0 ? base + (long)rq.src2 * D : nullptr;
-  float* dst1 = base + (long)rq.dst1 * D;
+  float* dst1 = rq.dst1 >= 0 ? base + (long)rq.dst1 * D : nullptr;
   float* dst2 = rq.dst2 >= 0 ? base + (long)rq.dst2 * D : nullptr;
   float* s1 = mv_src;
   float* s2 = mv_src + D;
@@ -211,6 +213,18 @@ __global__ void __launch_bounds__(kMatvecThreads, 4) batch_matvec_kernel(const _
   __syncthreads();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
   const int i1 = (i0 + kMatvecRows < D) ? i0 + kMatvecRows : D;
+  if (rq.lower == 2) {  // Welford: M += outer(src1, src2), coalesced read-modify-write
+    float* Mw = L.cv.dense + ((long)c * 4 + rq.mat) * D * D;
+    for (int i = i0 + wid; i < i1; i += nw) {
+      const float dp = s1[i];
+      float* row = Mw + (long)i * D;
+      for (int j = lane; j < D; j += 32) {
+        const float pr = dp * s2[j];
+        row[j] = row[j] + pr;
+      }
+    }
+    return;
+  }
   for (int i = i0 + wid; i < i1; i += nw) {
     const float* row = M + (long)i * D;
     const int n = rq.lower ? i + 1 : D;
@@ -244,6 +258,41 @@ __global__ void __launch_bounds__(kMatvecThreads, 4) batch_matvec_kernel(const _
       dst1[i] = ta;
       if (dst2) dst2[i] = tb;
     }
+  }
+}
+
+// ---- window-end factorisation of a dense mass matrix (hmc_util.py:198-237), element-wise
+// pieces around the library Cholesky / triangular inverse.  mats = this chain's [4][D][D]:
+// 0 inverse_mass_matrix (covariance), 1 mass_matrix_sqrt, 2 mass_matrix_sqrt_inv, 3 Welford m2.
+__global__ void factor_cov_kernel(float* mats, int D, float n, int regularize) {
+  // cov = m2 / (n - 1), shrunk towards the identity (:209-216); W = cov reversed in both axes
+  const float scale = n / (n + 5.0f), shrink = 1e-3f * (5.0f / (n + 5.0f));
+  float *cov = mats, *W = mats + 2L * D * D, *M2 = mats + 3L * D * D;
+  const long total = (long)D * D;
+  for (long e = blockIdx.x * (long)blockDim.x + threadIdx.x; e < total; e += (long)gridDim.x * blockDim.x) {
+    const int i = (int)(e / D), j = (int)(e - (long)i * D);
+    float cv = M2[e] / (n - 1.0f);
+    if (regularize) {
+      cv = scale * cv;
+      if (i == j) cv = cv + shrink;
+    }
+    cov[e] = cv;
+    W[(long)(D - 1 - i) * D + (D - 1 - j)] = cv;  // scratch: the slot of mass_matrix_sqrt_inv
+  }
+}
+// After the column-major lower Cholesky of W (in place, slot 2): Lc[a][b] sits at
+// chol[b * D + a].  tril_inv[i][j] = Lc[D-1-j][D-1-i] for j <= i (:229-230), written to the
+// mass_matrix_sqrt slot (the triangular inverse then happens there in place) and to the m2
+// slot, from where the host copies it over slot 2 before clearing m2.
+__global__ void factor_tinv_kernel(float* mats, int D) {
+  float *msq = mats + 1L * D * D, *tmp = mats + 3L * D * D;
+  const float* chol = mats + 2L * D * D;
+  const long total = (long)D * D;
+  for (long e = blockIdx.x * (long)blockDim.x + threadIdx.x; e < total; e += (long)gridDim.x * blockDim.x) {
+    const int i = (int)(e / D), j = (int)(e - (long)i * D);
+    const float t = (j <= i) ? chol[(long)(D - 1 - i) * D + (D - 1 - j)] : 0.f;
+    tmp[e] = t;
+    msq[e] = t;
   }
 }
 

@@ -59,11 +59,13 @@ __host__ __device__ inline int num_slots(int max_depth, int dense) {
 enum Phase { PH_INIT = 0, PH_TREE, PH_HMC, PH_IDLE, PH_FAIL, PH_FRSS };
 // NEED_MATVEC: only with mv_yield (lock-step engine): the dense-mass product described by
 // `rq` must be computed by the caller, then resume() continues where advance() stopped.
-enum StepResult { NEED_GRAD = 0, FINISHED = 1, NEED_MATVEC = 2 };
+enum StepResult { NEED_GRAD = 0, FINISHED = 1, NEED_MATVEC = 2, NEED_FACTOR = 3,
+                  STAGE_DONE = 4 /* internal: an adapt stage fell through */ };
 
 struct MatvecRequest {
   int mat;         // which of the chain's four D x D matrices
-  int lower;       // 1: triangular factor, columns j <= i only
+  int lower;       // 1: triangular factor, columns j <= i only; 2: not a product but the
+                   // rank-1 update M += outer(src1, src2) (Welford, hmc_util.py:195)
   int src1, dst1;  // slots: dst1 = M src1
   int src2, dst2;  // second right-hand side of the same sweep, or -1
 };
@@ -148,6 +150,8 @@ struct Sampler {
   int mv_resume;  // 0 none, 1 leaf finish, 2 / 3 transition start
   float pending_U;
   MatvecRequest rq;
+  Key ad_kss;             // adapt stages: key of the window-end step-size search
+  bool ad_middle, ad_reinit;
 
   __device__ __forceinline__ float* v(int slot) const { return w + (long)slot * slot_stride; }
   __device__ __forceinline__ float* ckpt_r(int i) const { return v(CKPT0 + ck_stride * i); }
@@ -509,10 +513,17 @@ struct Sampler {
 
   // warmup_adapter.update_fn: hmc_util.py:637-705.  Returns true when a step-size search
   // (find_heuristic_step_size) was started and the transition tail must wait for it.
-  __device__ __noinline__ bool adapt(int t, float accept_prob) {
+  // warmup_adapter.update_fn (hmc_util.py:637-705) in three resumable stages, so that the
+  // lock-step engine (mv_yield) can hand the two O(D^2) pieces of a dense mass matrix -- the
+  // Welford rank-1 update and the window-end factorisation -- to whole-machine kernels.
+  // Everywhere else the stages simply run back to back.
+  __device__ __noinline__ StepResult adapt_a() {
+    const int t = s.i;
+    const float accept_prob = s.accept_prob;
     if (!pre_a_valid) split2(Key{s.adapt_key[0], s.adapt_key[1]}, part, pre_a_nk, pre_a_kss);  // :656
     pre_a_valid = 0;
-    const Key nk = pre_a_nk, kss = pre_a_kss;
+    const Key nk = pre_a_nk;
+    ad_kss = pre_a_kss;
     s.adapt_key[0] = nk.k0; s.adapt_key[1] = nk.k1;
     if (P->adapt_step_size) {
       da_update(P->target_accept_prob - accept_prob);
@@ -521,6 +532,7 @@ struct Sampler {
       s.step_size = ss;
     }
     const bool is_middle = (0 < s.window_idx) && (s.window_idx < P->num_windows - 1);
+    ad_middle = is_middle;
     if (P->adapt_mass_matrix && is_middle) {  // welford update, :172-196
       s.mm_n += 1;
       const float n = (float)s.mm_n;
@@ -543,66 +555,122 @@ struct Sampler {
         }
       }
       if (dense) {  // m2 += outer(delta_post, delta_pre), :195
+        if constexpr (G::kBlockWide) {
+          if (mv_yield) {
+            rq = MatvecRequest{3, 2 /* rank-1 update */, LR, -1, LV, -1};
+            mv_resume = 5;
+            return NEED_MATVEC;
+          }
+        }
         g.sync();
         float* M2 = mat(3);
-        B200MC_FOR_D {
-          const float dp = dpost_v[d * es];
-          float* row = M2 + (long)d * D;
-          for (int j = 0; j < D; ++j) {
-            const float pr = dp * dpre_v[j * es];
-            row[j] = row[j] + pr;
+        if constexpr (G::kBlockWide) {  // warp per row: coalesced read-modify-write
+          const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+          for (int i = wid; i < D; i += nw) {
+            const float dp = dpost_v[i];
+            float* row = M2 + (long)i * D;
+            for (int j = lane; j < D; j += 32) {
+              const float pr = dp * dpre_v[j];
+              row[j] = row[j] + pr;
+            }
+          }
+        } else {
+          B200MC_FOR_D {
+            const float dp = dpost_v[d * es];
+            float* row = M2 + (long)d * D;
+            for (int j = 0; j < D; ++j) {
+              const float pr = dp * dpre_v[j * es];
+              row[j] = row[j] + pr;
+            }
           }
         }
         g.sync();
       }
     }
+    return STAGE_DONE;
+  }
+
+  __device__ __noinline__ StepResult adapt_b() {
+    const int t = s.i;
+    const bool is_middle = ad_middle;
     const int wend = P->window_end[min(s.window_idx, P->num_windows - 1)];
     const bool at_end = (t == wend);
     if (at_end) s.window_idx += 1;
-    if (at_end && is_middle) {  // _update_at_window_end, :596-635
-      if (P->adapt_mass_matrix) {  // welford final, :198-237
-        const float n = (float)s.mm_n;
-        float *mean = v(WMEAN), *m2 = v(WM2), *im = v(IMM), *ms = v(MSQRT);
-        const float scale = n / (n + 5.0f);
-        const float shrink = 1e-3f * (5.0f / (n + 5.0f));
-        if (dense) {
-          float *cov = mat(0), *M2 = mat(3);
-          B200MC_FOR_D {
-            for (int j = 0; j < D; ++j) {
-              float c = M2[(long)d * D + j] / (n - 1.0f);
-              if (P->regularize_mass_matrix) {
-                c = scale * c;
-                if (j == d) c = c + shrink;
-              }
-              cov[(long)d * D + j] = c;
-            }
-            mean[d * es] = 0.f;
-          }
-          factor_dense();
-        } else {
-          B200MC_FOR_D {
-            float cov = m2[d * es] / (n - 1.0f);
-            if (P->regularize_mass_matrix) {
-              const float sc = scale * cov;
-              cov = sc + shrink;
-            }
-            im[d * es] = cov;
-            ms[d * es] = 1.0f / sqrtf(cov);
-            mean[d * es] = 0.f;
-            m2[d * es] = 0.f;
+    ad_reinit = at_end && is_middle;
+    if (at_end && is_middle && P->adapt_mass_matrix) {  // welford final, :198-237
+      const float n = (float)s.mm_n;
+      float *mean = v(WMEAN), *m2 = v(WM2), *im = v(IMM), *ms = v(MSQRT);
+      const float scale = n / (n + 5.0f);
+      const float shrink = 1e-3f * (5.0f / (n + 5.0f));
+      if (dense) {
+        if constexpr (G::kBlockWide) {
+          if (mv_yield) {  // covariance + factorisation by the caller (rq.src1 carries n)
+            rq = MatvecRequest{-1, 0, s.mm_n, -1, -1, -1};
+            mv_resume = 6;
+            return NEED_FACTOR;
           }
         }
+        float *cov = mat(0), *M2 = mat(3);
+        B200MC_FOR_D {
+          for (int j = 0; j < D; ++j) {
+            float c = M2[(long)d * D + j] / (n - 1.0f);
+            if (P->regularize_mass_matrix) {
+              c = scale * c;
+              if (j == d) c = c + shrink;
+            }
+            cov[(long)d * D + j] = c;
+          }
+        }
+        factor_dense();
+      } else {
+        B200MC_FOR_D {
+          float cov = m2[d * es] / (n - 1.0f);
+          if (P->regularize_mass_matrix) {
+            const float sc = scale * cov;
+            cov = sc + shrink;
+          }
+          im[d * es] = cov;
+          ms[d * es] = 1.0f / sqrtf(cov);
+          m2[d * es] = 0.f;
+        }
+      }
+    }
+    return STAGE_DONE;
+  }
+
+  __device__ __noinline__ StepResult adapt_c() {
+    if (ad_reinit) {  // _update_at_window_end, :596-635
+      if (P->adapt_mass_matrix) {
+        float* mean = v(WMEAN);
+        B200MC_FOR_D mean[d * es] = 0.f;
         s.mm_n = 0;
       }
       if (P->adapt_step_size) {
         if (P->find_heuristic) {
-          start_frss(kss, 1);
-          return true;
+          start_frss(ad_kss, 1);
+          if (frss_try()) return NEED_GRAD;               // step-size search needs gradients
         }
-        da_init(logf(10.0f) + logf(s.step_size));  // :624
+        da_init(logf(10.0f) + logf(s.step_size));  // :624 (or: the search ended at once)
       }
     }
-    return false;
+    return STAGE_DONE;
+  }
+
+  // The adapt stages from `stage` on, then the transition tail.  Stages return to this frame
+  // (no nesting: the device stack is small).
+  __device__ StepResult run_adapt(int stage) {
+    StepResult r;
+    if (stage <= 0) {
+      r = adapt_a();
+      if (r != STAGE_DONE) return r;
+    }
+    if (stage <= 1) {
+      r = adapt_b();
+      if (r != STAGE_DONE) return r;
+    }
+    r = adapt_c();
+    if (r != STAGE_DONE) return r;
+    return finish_transition_tail();
   }
 
   // ------------------------------------------------------------------ find_reasonable_step_size
@@ -688,11 +756,7 @@ struct Sampler {
     s.accept_prob = accept_prob;
     s.num_steps = num_steps;
     s.diverging = div;
-    const int t = s.i;
-    if (t < P->num_warmup && adapt(t, accept_prob)) {
-      if (frss_try()) return NEED_GRAD;               // step-size search needs gradients
-      da_init(logf(10.0f) + logf(s.step_size));       // search ended at once
-    }
+    if (s.i < P->num_warmup) return run_adapt(0);
     return finish_transition_tail();
   }
 
@@ -1422,6 +1486,8 @@ struct Sampler {
     }
     if (where == 2) return start_transition_b();
     if (where == 3) return start_transition_c();
+    if (where == 5) return run_adapt(1);
+    if (where == 6) return run_adapt(2);
     return FINISHED;
   }
 

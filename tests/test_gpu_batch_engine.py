@@ -109,3 +109,17 @@ def test_batched_dense_warmup_recovers_coefficients(nb):
     b = mc.get_samples()["betas"].mean(0)
     assert_allclose(b[:3], [2.0, -1.0, 0.5], atol=0.15)
     assert int(np.asarray(mc.last_state.i).min()) == 210
+    # the factors the window-end factorisation left behind belong to the adapted covariance:
+    # M^{1/2} M^{1/2}^T = (M^-1)^-1, M^{-1/2} = (M^{1/2})^-1, both lower triangular
+    ad = mc.last_state.adapt_state
+    imm = next(iter(ad.inverse_mass_matrix.values()))
+    msq = next(iter(ad.mass_matrix_sqrt.values()))
+    msqi = next(iter(ad.mass_matrix_sqrt_inv.values()))
+    D = imm.shape[-1]
+    assert imm.shape == (64, D, D)
+    for c in (0, 31, 63):
+        assert not np.allclose(imm[c], np.eye(D))
+        assert_allclose(msq[c] @ msq[c].T @ imm[c], np.eye(D), atol=5e-3)
+        assert_allclose(msqi[c] @ msq[c], np.eye(D), atol=2e-3)
+        assert np.allclose(np.triu(msq[c], 1), 0) and np.allclose(np.triu(msqi[c], 1), 0)
+        assert int(np.asarray(ad.window_idx)[c]) > 1
