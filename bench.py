@@ -422,6 +422,11 @@ def make_workload(name, chains):
         r = (np.exp(s) * rng.standard_t(10, size=T_)).astype(np.float32)
         return (models.stochastic_volatility, (r,), {}, {}, chains or 1024,
                 "stochastic volatility random walk T=3000 NUTS (configs[4])")
+    if name == "logistic_many":
+        X, y = make_covtype_shape()
+        return (models.logistic_regression, (X, y), {}, {}, chains or 256,
+                "covtype-shape logistic NUTS N=581012 D=55, vectorized chains through the "
+                "tensor-core lock-step engine (configs[2] data, many chains)")
     if name == "horseshoe":
         rng = np.random.RandomState(0)
         N, D = 10000, 1000
@@ -495,7 +500,7 @@ def run_chain_workload(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workload", default="logistic",
-                    choices=["logistic", "eight_schools", "sv", "horseshoe"])
+                    choices=["logistic", "eight_schools", "sv", "horseshoe", "logistic_many"])
     ap.add_argument("--chains", type=int, default=0)
     ap.add_argument("--sharding", default="chains", choices=["chains", "rows"],
                     help="N>1: independent chains per GPU (weak) or one row-sharded chain (strong)")

@@ -1,5 +1,14 @@
-CMD="python bench.py --workload horseshoe --chains 256 --steps 1 --warmup 1 --adapt 1 --transitions 2 --fixed-step 0.0005 --max-tree-depth 5"
-timeout 600 $CMD > gpurun_out/hs_plain.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:gemm3x -s 40 -c 2 -o gpurun_out/prof_gemm $CMD > gpurun_out/ncu_gemm.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:batch_matvec -s 60 -c 1 -o gpurun_out/prof_matvec $CMD > gpurun_out/ncu_mv.log 2>&1
-tail -c 300 gpurun_out/hs_plain.log
+CMD="python bench.py --workload logistic_many --chains 256 --steps 1 --warmup 1 --adapt 20 --transitions 3"
+timeout 600 $CMD > gpurun_out/lm_plain.log 2>&1 && \
+ncu --metrics gpu__time_duration.sum --clock-control none -s 600 -c 300 --csv --log-file gpurun_out/launches_lm.csv $CMD > gpurun_out/ncu_lm.log 2>&1
+python - <<EOF
+import csv,collections
+rows=list(csv.reader(l for l in open("gpurun_out/launches_lm.csv") if l.startswith("\"")))
+h=rows[0]; ki=h.index("Kernel Name"); vi=h.index("Metric Value")
+agg=collections.OrderedDict()
+for r in rows[1:]:
+    try: v=float(r[vi].replace(",",""))
+    except: continue
+    a=agg.setdefault(r[ki][:60],[0,0.0]); a[0]+=1; a[1]+=v
+for k,a in agg.items(): print(k, a[0], round(a[1]/a[0]/1000,1), "us avg")
+EOF

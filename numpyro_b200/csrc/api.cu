@@ -77,6 +77,7 @@ struct b200mc_handle {
     int* status = nullptr;
     unsigned* active = nullptr;
     MatvecRequest* reqs = nullptr;
+    float* y_f32 = nullptr;  // logistic: labels as floats
     int RA1 = 0, K1 = 0, RA2 = 0, splits = 1, snap_stride = 0;
   } bt;
 };
@@ -164,6 +165,9 @@ static int family_sites(const b200mc_config& c, SamplerParams& P, int& D) {
 }
 
 // ---------------------------------------------------------------- 3xTF32 GEMM plumbing
+__global__ void labels_to_float_kernel(const uint8_t* y, int n, float* out) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[i] = (float)y[i];
+}
 namespace {
 __global__ void sum_splits_kernel(const float* part, int splits, int Nc, int RA, int M, float* out) {
   const long total = (long)Nc * M;
@@ -217,7 +221,7 @@ extern "C" void b200mc_destroy(b200mc_handle* h) {
   cudaFree(h->bt.x_hi); cudaFree(h->bt.x_lo); cudaFree(h->bt.xt_hi); cudaFree(h->bt.xt_lo);
   cudaFree(h->bt.b_hi); cudaFree(h->bt.b_lo); cudaFree(h->bt.r_hi); cudaFree(h->bt.r_lo);
   cudaFree(h->bt.ll_part); cudaFree(h->bt.gpart); cudaFree(h->bt.col_scale);
-  cudaFree(h->bt.snap); cudaFree(h->bt.status); cudaFree(h->bt.active); cudaFree(h->bt.reqs);
+  cudaFree(h->bt.snap); cudaFree(h->bt.status); cudaFree(h->bt.active); cudaFree(h->bt.reqs); cudaFree(h->bt.y_f32);
   delete h;
 }
 
@@ -315,7 +319,11 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   if (c.dense_mass) ACK(alloc((void**)&h->cv.dense, sizeof(float) * 4 * (size_t)C * D * D));
 
   const int nslots = num_slots(P.max_depth, P.dense_mass);
-  if (c.family == B200MC_LOGISTIC) {
+  int batch_min = 64;  // north_star: from 64 chains on, X.Theta is a real dense contraction
+  if (const char* e = getenv("B200MC_BATCH_MIN_CHAINS")) batch_min = atoi(e);
+  const bool batch = (c.family == B200MC_HORSESHOE || c.family == B200MC_LOGISTIC) &&
+                     C >= batch_min && C <= kBatchCols && !(c.nranks > 1);
+  if (c.family == B200MC_LOGISTIC && !batch) {
     if (D > kGlmMaxD) { b200mc_destroy(h); return fail("logistic: D=%d > %d not supported", D, kGlmMaxD); }
     if (!c.data1_dev) { b200mc_destroy(h); return fail("logistic: labels missing"); }
     // Re-tile X and the labels once (layout: glm_kernel.cuh); the caller's buffers are not
@@ -388,9 +396,6 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
       ACK(alloc((void**)&h->xarrive_local, sizeof(unsigned) * 4));
     }
   } else {
-    int batch_min = 64;  // north_star: from 64 chains on, X.Theta is a real dense contraction
-    if (const char* e = getenv("B200MC_BATCH_MIN_CHAINS")) batch_min = atoi(e);
-    const bool batch = c.family == B200MC_HORSESHOE && C >= batch_min && C <= kBatchCols;
     if (c.family == B200MC_HORSESHOE) {
       if (!c.data1_dev) { b200mc_destroy(h); return fail("horseshoe: Y missing"); }
       if (!batch) ACK(alloc((void**)&h->M.scratch, sizeof(float) * (size_t)C * c.N));
@@ -427,6 +432,14 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
       ACK(alloc((void**)&b.status, sizeof(int) * C));
       ACK(alloc((void**)&b.reqs, sizeof(MatvecRequest) * C));
       ACK(alloc((void**)&b.active, sizeof(unsigned) * (kBatchStepsPerSync + 2)));
+      if (c.family == B200MC_LOGISTIC) {  // labels arrive as bytes; the epilogue reads floats
+        if (!c.data1_dev) { b200mc_destroy(h); return fail("logistic: labels missing"); }
+        ACK(alloc((void**)&b.y_f32, sizeof(float) * (size_t)c.N));
+        labels_to_float_kernel<<<592, 256>>>((const uint8_t*)c.data1_dev, c.N, b.y_f32);
+        g_launches++;
+        h->M.b = b.y_f32;
+        h->M.likelihood = 0;
+      }
       ACK(cudaDeviceSynchronize());
     }
   }
@@ -740,11 +753,11 @@ extern "C" int b200mc_init(b200mc_handle* h, const uint32_t* keys_dev, const flo
   CK(cudaMemsetAsync(h->cs, 0, sizeof(ChainScalars) * h->C, st));
   const CollectSpec col = make_collect(0, 0, 1, nullptr);
   const int user_init = init_z_dev ? 1 : 0;
-  if (h->cfg.family == B200MC_LOGISTIC) {
+  if (h->mode == 3) {
+    if (launch_batch(h, col, keys_dev, user_init, st)) return 1;
+  } else if (h->cfg.family == B200MC_LOGISTIC) {
     for (int c = 0; c < h->C; ++c)
       if (launch_glm(h, col, keys_dev, user_init, c, nullptr, nullptr, nullptr, st)) return 1;
-  } else if (h->mode == 3) {
-    if (launch_batch(h, col, keys_dev, user_init, st)) return 1;
   } else {
     if (launch_chain(h, col, keys_dev, user_init, st)) return 1;
   }
@@ -760,12 +773,12 @@ extern "C" int b200mc_sample(b200mc_handle* h, int num_iters, int collect_start,
   if (thinning < 1) return fail("thinning must be a positive integer");
   cudaStream_t st = (cudaStream_t)stream;
   const CollectSpec col = make_collect(num_iters, collect_start, thinning, out);
+  if (h->mode == 3) return launch_batch(h, col, nullptr, 0, st);
   if (h->cfg.family == B200MC_LOGISTIC) {
     for (int c = 0; c < h->C; ++c)
       if (launch_glm(h, col, nullptr, 0, c, nullptr, nullptr, nullptr, st)) return 1;
     return 0;
   }
-  if (h->mode == 3) return launch_batch(h, col, nullptr, 0, st);
   return launch_chain(h, col, nullptr, 0, st);
 }
 
@@ -773,14 +786,6 @@ extern "C" int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, i
                                          float* grad_dev, void* stream) {
   if (!h || !z_dev || !U_dev || !grad_dev) return fail("null argument");
   cudaStream_t st = (cudaStream_t)stream;
-  if (h->cfg.family == B200MC_LOGISTIC) {
-    const CollectSpec col = make_collect(0, 0, 1, nullptr);
-    for (int i = 0; i < n; ++i)
-      if (launch_glm(h, col, nullptr, 0, 0, z_dev + (long)i * h->D, U_dev + i,
-                     grad_dev + (long)i * h->D, st))
-        return 1;
-    return 0;
-  }
   if (h->mode == 3) {  // tensor-core path: up to 256 points per pair of contractions
     for (int i0 = 0; i0 < n; i0 += kBatchCols) {
       const int m = (n - i0 < kBatchCols) ? n - i0 : kBatchCols;
@@ -797,6 +802,14 @@ extern "C" int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, i
       g_launches++;
       CK(cudaGetLastError());
     }
+    return 0;
+  }
+  if (h->cfg.family == B200MC_LOGISTIC) {
+    const CollectSpec col = make_collect(0, 0, 1, nullptr);
+    for (int i = 0; i < n; ++i)
+      if (launch_glm(h, col, nullptr, 0, 0, z_dev + (long)i * h->D, U_dev + i,
+                     grad_dev + (long)i * h->D, st))
+        return 1;
     return 0;
   }
   // per-chain scratch (horseshoe residuals) is sized for num_chains: evaluate in batches

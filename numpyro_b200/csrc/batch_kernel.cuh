@@ -130,6 +130,50 @@ __device__ float hs_finish(const BatchLaunch& L, const G& g, const float* z, flo
   return -lp;
 }
 
+// ---- Bayesian logistic regression (examples/covtype.py:66-71): coefs ~ N(0, 1),
+// y ~ Bernoulli(logits = X coefs).  Same arithmetic as the streaming kernel (glm_kernel.cuh).
+template <class G>
+__device__ void lg_prepare(const BatchLaunch& L, const G& g, const float* z, int c) {
+  float* bh = reinterpret_cast<float*>(L.b_hi);
+  float* bl = reinterpret_cast<float*>(L.b_lo);
+  for (int d = g.lane(); d < L.P.D; d += g.size()) {
+    float hi, lo;
+    umma::split_tf32(z[d], hi, lo);
+    const long off = umma::image_offset(kBatchCols, c, d) >> 2;
+    bh[off] = hi;
+    bl[off] = lo;
+  }
+  if (g.lane() == 0) L.col_scale[c] = 1.0f;
+}
+
+template <class G>
+__device__ float lg_finish(const BatchLaunch& L, const G& g, const float* z, float* grad, int c) {
+  float prior = 0.f, llik = 0.f;
+  for (int d = g.lane(); d < L.P.D; d += g.size()) {
+    const float t = z[d];
+    float db = 0.f;
+    for (int s = 0; s < L.splits; ++s) db += L.gpart[((long)s * kBatchCols + c) * L.RA2 + d];
+    grad[d] = t + db;                              // grad U = theta + X^T (sigmoid - y)
+    prior += 0.5f * t * t + B200MC_LOG_SQRT_2PI;   // -log N(theta; 0, 1)
+  }
+  for (int r = g.lane(); r < L.n_rowgroups; r += g.size()) llik += L.ll_part[(long)r * kBatchCols + c];
+  g.sum2(prior, llik);
+  g.sync();
+  return prior + llik;
+}
+
+template <class G>
+__device__ __forceinline__ void batch_prepare(const BatchLaunch& L, const G& g, const float* z, int c) {
+  if (L.M.family == FAM_HORSESHOE) hs_prepare(L, g, z, c);
+  else lg_prepare(L, g, z, c);
+}
+template <class G>
+__device__ __forceinline__ float batch_finish(const BatchLaunch& L, const G& g, const float* z,
+                                              float* grad, int c) {
+  if (L.M.family == FAM_HORSESHOE) return hs_finish(L, g, z, grad, c);
+  return lg_finish(L, g, z, grad, c);
+}
+
 // One CTA per chain.  begin = 1: set the sampler up and publish its first point.  Otherwise:
 // finish the potential at the published point, advance, publish the next point.
 __global__ void __launch_bounds__(kBatchThreads, 2) batch_step_kernel(const __grid_constant__ BatchLaunch L) {
@@ -161,7 +205,7 @@ __global__ void __launch_bounds__(kBatchThreads, 2) batch_step_kernel(const __gr
     S.P = &L.P; S.g = g; S.w = base; S.col = &L.col;
     if (S.dense) S.dn = L.cv.dense + (long)c * 4 * D * D;
     if (L.kind == BATCH_GRAD) {
-      const float U = hs_finish(L, g, S.v(LZ), S.v(LG), c);
+      const float U = batch_finish(L, g, S.v(LZ), S.v(LG), c);
       r = S.advance(U);
     } else {
       r = S.resume();
@@ -169,7 +213,7 @@ __global__ void __launch_bounds__(kBatchThreads, 2) batch_step_kernel(const __gr
   }
   if (r == NEED_GRAD) {
     g.sync();
-    hs_prepare(L, g, S.v(LZ), c);
+    batch_prepare(L, g, S.v(LZ), c);
     if (threadIdx.x == 0) L.status[c] = 0;
   } else if (r == NEED_MATVEC || r == NEED_FACTOR) {
     if (threadIdx.x == 0) {
@@ -306,9 +350,9 @@ __global__ void __launch_bounds__(kBatchThreads) batch_potential_kernel(const __
   const BlockGroup g{red_scratch};
   const float* z = L.eval_z + (long)c * L.P.D;
   if (phase == 0) {
-    hs_prepare(L, g, z, c);
+    batch_prepare(L, g, z, c);
   } else {
-    const float U = hs_finish(L, g, z, L.eval_grad + (long)c * L.P.D, c);
+    const float U = batch_finish(L, g, z, L.eval_grad + (long)c * L.P.D, c);
     if (threadIdx.x == 0) L.eval_U[c] = U;
   }
 }

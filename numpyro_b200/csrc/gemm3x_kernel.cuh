@@ -9,7 +9,8 @@
 // (~2^-22 per product) at 3 tensor-core passes.  Operands arrive as pre-swizzled "operand
 // images" (umma.cuh) through 1-D TMA bulk copies; one CTA = one 128 x 256 output tile over
 // a k-block range (split-K); warp 0 = TMA producer, warp 1 = MMA issuer (one lane) and TMEM
-// owner, warps 2..5 = epilogue (tcgen05.ld, one TMEM lane quadrant each).
+// owner, warps 2.. = epilogue (tcgen05.ld; TMEM lane quadrant = warp % 4, kGemmEpiGroups warps
+// per quadrant share its 256 columns: the residual epilogue is transcendental-bound).
 //
 // Epilogues:
 //   EPI_STORE  partial tile -> out[split][c][m] (chain-major; the consumer sums the splits in a
@@ -31,7 +32,8 @@ namespace b200mc {
 constexpr int kGemmM = 128;        // rows of A per CTA = TMEM lanes
 constexpr int kGemmN = 256;        // chains per tile = TMEM columns
 constexpr int kGemmStages = 2;
-constexpr int kGemmThreads = 192;  // 6 warps
+constexpr int kGemmEpiGroups = 4;  // epilogue warps per TMEM lane quadrant (columns split among them)
+constexpr int kGemmThreads = 64 + 128 * kGemmEpiGroups;  // producer, MMA issuer, epilogue warps
 constexpr int kGemmABytes = kGemmM * 128;  // one operand tile of A: 128 rows x 32 f32
 constexpr int kGemmBBytes = kGemmN * 128;
 constexpr int kGemmStageBytes = 2 * kGemmABytes + 2 * kGemmBBytes;  // hi + lo of both = 96 KB
@@ -130,6 +132,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm3x_kernel(const __grid_co
   } else {
     // ---------------- epilogue: warp w may touch TMEM lanes 32 * (w % 4) ..
     const int q = warp & 3;
+    const int c_begin = ((warp - 2) >> 2) * (kGemmN / kGemmEpiGroups), c_end = c_begin + kGemmN / kGemmEpiGroups;
     mbar_wait(acc_full, 0u);
     umma::fence_after_sync();
     const int m = mt * kGemmM + q * 32 + lane;  // this thread's row of A
@@ -137,7 +140,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm3x_kernel(const __grid_co
     if (EPI == EPI_STORE) {
       float* out = L.out + (long)sp * kGemmN * L.RA;
 #pragma unroll 1
-      for (int c0 = 0; c0 < kGemmN; c0 += 32) {
+      for (int c0 = c_begin; c0 < c_end; c0 += 32) {
         uint32_t v[32];
         umma::tmem_ld32(trow + c0, v);
         umma::tmem_ld_wait();
@@ -152,7 +155,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm3x_kernel(const __grid_co
       unsigned char* rl = L.r_lo + kbR * (kGemmN >> 3) * umma::kAtomBytes;
       float* llp = L.ll_part + kbR * kGemmN;
 #pragma unroll 1
-      for (int c0 = 0; c0 < kGemmN; c0 += 32) {
+      for (int c0 = c_begin; c0 < c_end; c0 += 32) {
         uint32_t v[32];
         umma::tmem_ld32(trow + c0, v);
         umma::tmem_ld_wait();
@@ -169,7 +172,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm3x_kernel(const __grid_co
               res = -(L.col_scale[c] * r);
             } else {
               const float e = expf(-fabsf(l));
-              const float inv = 1.0f / (1.0f + e);
+              const float inv = rcp_1to2(1.0f + e);
               term = (fmaxf(l, 0.f) + log1pf(e)) - l * yv;
               res = ((l >= 0.f) ? inv : e * inv) - yv;
             }
