@@ -485,6 +485,25 @@ def run_chain_workload(args):
             tot_ms += float(ms.value)
             tot_g += int(ns_buf.numpy().sum())
     clk = clocks.stop()
+    # step-level roofline of the secondary workloads: whole-step time, not one kernel
+    roofline = None
+    D_flat = int(kern._bound.dim)
+    if args.workload == "horseshoe" and kkw.get("dense_mass"):
+        peak, src = peaks()
+        per = D_flat * D_flat * 4  # one pass over M^-1 per chain and leapfrog
+        ach = per * tot_g / (tot_ms * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                    "traffic": None, "peak_source": src, "kernel": "batch_matvec_kernel (whole step timed)",
+                    "bytes_per_grad_eval": per}
+    elif args.workload == "logistic_many":
+        # two contractions of 2*N*D*C flops each, three TF32 passes; dense TF32 peak 1130 TFLOP/s
+        # (blackwell guide; MEASURED_PEAKS.json holds bf16 only)
+        flops = 3 * 2 * 2.0 * N_ROWS * N_COLS * tot_g
+        ach = flops / (tot_ms * 1e-3) / 1e12
+        roofline = {"bound": "tensor", "achieved": ach, "peak": 1130.0, "unit": "TFLOP/s",
+                    "frac": ach / 1130.0, "traffic": None, "peak_source": "nominal TF32 dense",
+                    "kernel": "gemm3x_kernel x2 (whole step timed; the residual images' HBM "
+                              "round trip and the transcendental epilogue dominate, DESIGN 4.3)"}
     line = {"metric": METRIC, "value": tot_g / (tot_ms * 1e-3), "unit": UNIT, "n_gpus": 1,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -492,7 +511,8 @@ def run_chain_workload(args):
             "config": {"workload": desc, "chains": chains, "transitions_per_step": T_,
                        "adapt_transitions_untimed": args.adapt, **{k: str(v) for k, v in kkw.items()}},
             "gpu_launches": int(lib.b200mc_kernel_launches() - launches0), "clocks": clk,
-            "adapt_seconds": adapt_s, "mean_tree_size": tot_g / (args.steps * T_ * chains)}
+            "adapt_seconds": adapt_s, "mean_tree_size": tot_g / (args.steps * T_ * chains),
+            "roofline": roofline}
     print(json.dumps(line))
     return 0
 

@@ -538,21 +538,30 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
           }
         }
         const uint2* mine = reinterpret_cast<const uint2*>(L.xchg[L.rank]) + slot;
+        // poll ALL ranks' slots together (independent loads in flight), not rank after rank:
+        // the wait is one round trip after the slowest rank, whatever the rank count
         bool ok = true;
 #pragma unroll
         for (int k = 0; k < 5; ++k) {
           const int d = lane + 32 * k;
           float a = 0.f;
           if (d < PS) {
-            for (int r = 0; r < L.nranks; ++r) {  // rank order: identical sums on every rank
-              uint2 v = ld_relaxed_sys_v2(mine + (long)r * PS + d);
-              for (long it = 0; v.y != seq && it < (1L << 22); ++it) {
-                if (it > 65536) __nanosleep(200);
-                v = ld_relaxed_sys_v2(mine + (long)r * PS + d);
-              }
-              ok = ok && (v.y == seq);
-              a += __uint_as_float(v.x);
+            uint2 v[kGlmMaxRanks];
+            bool all = false;
+            for (long it = 0; !all && it < (1L << 22); ++it) {
+              if (it > 65536) __nanosleep(200);
+#pragma unroll
+              for (int r = 0; r < kGlmMaxRanks; ++r)
+                if (r < L.nranks) v[r] = ld_relaxed_sys_v2(mine + (long)r * PS + d);
+              all = true;
+#pragma unroll
+              for (int r = 0; r < kGlmMaxRanks; ++r)
+                if (r < L.nranks) all = all && (v[r].y == seq);
             }
+            ok = ok && all;
+#pragma unroll
+            for (int r = 0; r < kGlmMaxRanks; ++r)  // rank order: identical sums on every rank
+              if (r < L.nranks) a += __uint_as_float(v[r].x);
           }
           sl[k] = a;
         }
