@@ -454,7 +454,35 @@ def run_chain_workload(args):
     lib = _lib.lib()
     _lib.require_device()
     _lib.check(lib.b200mc_set_device(local))
+    dist = None
+    if world > 1:  # chains sharded over the ranks, data replicated, no data-path collective
+        import torch
+        import torch.distributed as dist
+
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def reduce_over_ranks(x, op):
+        if dist is None:
+            return x
+        import torch
+
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=getattr(dist.ReduceOp, op))
+        return float(t.item())
+
+    def barrier():
+        _lib.check(lib.b200mc_stream_synchronize(None))
+        if dist is not None:
+            dist.barrier()
+
     model, margs, mkw, kkw, chains, desc = make_workload(args.workload, args.chains)
+    total_chains = chains
+    from numpyro_b200 import distributed as nbd
+    from numpyro_b200.random import split
+
+    keys = nbd.shard_keys(split(PRNGKey(0), total_chains), rank, world)  # mcmc.py:661-662
+    chains = int(keys.shape[0])
     if args.fixed_step > 0:  # profiling aid: no adaptation, trees at a given step size
         kkw = dict(kkw, step_size=args.fixed_step, adapt_step_size=False, adapt_mass_matrix=False)
     if args.max_tree_depth:
@@ -463,7 +491,7 @@ def run_chain_workload(args):
     mc = MCMC(kern, num_warmup=args.adapt, num_samples=args.transitions, num_chains=chains,
               chain_method="vectorized")
     t0 = time.perf_counter()
-    mc.warmup(PRNGKey(0), *margs, **mkw)
+    mc.warmup(keys if total_chains > 1 else PRNGKey(0), *margs, **mkw)
     adapt_s = time.perf_counter() - t0
     T_ = args.transitions
     ns_buf = _lib.DeviceArray((T_, chains), np.int32)
@@ -476,6 +504,7 @@ def run_chain_workload(args):
         if i == args.warmup:
             launches0 = lib.b200mc_kernel_launches()
             clocks = ClockSampler(local)
+            barrier()
         _lib.check(lib.b200mc_event_record(ev0, None))
         _lib.check(lib.b200mc_sample(kern._handle, T_, 0, 1, C.byref(col), None))
         _lib.check(lib.b200mc_event_record(ev1, None))
@@ -484,34 +513,44 @@ def run_chain_workload(args):
         if i >= args.warmup:
             tot_ms += float(ms.value)
             tot_g += int(ns_buf.numpy().sum())
+    barrier()
     clk = clocks.stop()
+    local_g, local_ms = tot_g, tot_ms
+    tot_ms = reduce_over_ranks(tot_ms, "MAX")
+    tot_g = int(reduce_over_ranks(float(tot_g), "SUM"))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return 0
     # step-level roofline of the secondary workloads: whole-step time, not one kernel
     roofline = None
     D_flat = int(kern._bound.dim)
     if args.workload == "horseshoe" and kkw.get("dense_mass"):
         peak, src = peaks()
         per = D_flat * D_flat * 4  # one pass over M^-1 per chain and leapfrog
-        ach = per * tot_g / (tot_ms * 1e-3) / 1e9
+        ach = per * local_g / (local_ms * 1e-3) / 1e9  # this rank's GPU
         roofline = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                     "traffic": None, "peak_source": src, "kernel": "batch_matvec_kernel (whole step timed)",
                     "bytes_per_grad_eval": per}
     elif args.workload == "logistic_many":
         # two contractions of 2*N*D*C flops each, three TF32 passes; dense TF32 peak 1130 TFLOP/s
         # (blackwell guide; MEASURED_PEAKS.json holds bf16 only)
-        flops = 3 * 2 * 2.0 * N_ROWS * N_COLS * tot_g
-        ach = flops / (tot_ms * 1e-3) / 1e12
+        flops = 3 * 2 * 2.0 * N_ROWS * N_COLS * local_g
+        ach = flops / (local_ms * 1e-3) / 1e12  # this rank's GPU
         roofline = {"bound": "tensor", "achieved": ach, "peak": 1130.0, "unit": "TFLOP/s",
                     "frac": ach / 1130.0, "traffic": None, "peak_source": "nominal TF32 dense",
                     "kernel": "gemm3x_kernel x2 (whole step timed; the residual images' HBM "
                               "round trip and the transcendental epilogue dominate, DESIGN 4.3)"}
-    line = {"metric": METRIC, "value": tot_g / (tot_ms * 1e-3), "unit": UNIT, "n_gpus": 1,
+    line = {"metric": METRIC, "value": tot_g / (tot_ms * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": desc, "chains": chains, "transitions_per_step": T_,
+            "config": {"workload": desc, "chains": total_chains, "chains_per_gpu": chains,
+                       "parallelism": f"chains x{world}", "transitions_per_step": T_,
                        "adapt_transitions_untimed": args.adapt, **{k: str(v) for k, v in kkw.items()}},
             "gpu_launches": int(lib.b200mc_kernel_launches() - launches0), "clocks": clk,
-            "adapt_seconds": adapt_s, "mean_tree_size": tot_g / (args.steps * T_ * chains),
+            "adapt_seconds": adapt_s, "mean_tree_size": tot_g / (args.steps * T_ * total_chains),
             "roofline": roofline}
     print(json.dumps(line))
     return 0

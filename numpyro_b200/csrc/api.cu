@@ -320,6 +320,9 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
 
   const int nslots = num_slots(P.max_depth, P.dense_mass);
   int batch_min = 64;  // north_star: from 64 chains on, X.Theta is a real dense contraction
+  // with a dense mass matrix the batched whole-machine sweeps pay off much earlier (a single
+  // CTA cannot stream its chain's 16 MB matrix at speed): e.g. 256 chains sharded over 8 GPUs
+  if (c.family == B200MC_HORSESHOE && c.dense_mass) batch_min = 16;
   if (const char* e = getenv("B200MC_BATCH_MIN_CHAINS")) batch_min = atoi(e);
   const bool batch = (c.family == B200MC_HORSESHOE || c.family == B200MC_LOGISTIC) &&
                      C >= batch_min && C <= kBatchCols && !(c.nranks > 1);
