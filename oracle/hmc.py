@@ -4,6 +4,7 @@
 TEST INFRASTRUCTURE (see ``oracle/__init__.py``).
 """
 from collections import namedtuple
+import copy
 import math
 
 import numpy as np
@@ -21,6 +22,14 @@ HMCState = namedtuple(  # hmc.py:31-48
 def momentum_generator(cfg, mass_matrix_sqrt, rng_key):
     """hmc.py:92-110.  A model-built kernel always carries a dict mass matrix with a
     single block (``hmc.py:760-769``), so the key is first ``split(key, 1)``."""
+    if isinstance(mass_matrix_sqrt, dict):  # structured mass matrix: one key per block
+        rng_keys = cfg.split(rng_key, len(mass_matrix_sqrt))
+        r = np.zeros(sum(cfg.block_index(k).size for k in mass_matrix_sqrt), cfg.dtype)
+        for (names, mm_sqrt), key in zip(mass_matrix_sqrt.items(), rng_keys):
+            eps = cfg.normal(key, (mm_sqrt.shape[0],))
+            r[cfg.block_index(names)] = (mm_sqrt * eps if mm_sqrt.ndim == 1
+                                         else mm_sqrt @ eps).astype(cfg.dtype)
+        return r
     rng_key = cfg.split(rng_key, 1)[0]
     eps = cfg.normal(rng_key, (mass_matrix_sqrt.shape[0],))
     if mass_matrix_sqrt.ndim == 1:
@@ -65,8 +74,15 @@ class HMCKernel:
                  target_accept_prob=0.8, num_steps=None, trajectory_length=2 * math.pi,
                  max_tree_depth=10, regularize_mass_matrix=True, find_heuristic_step_size=False,
                  cfg=None):
-        self.cfg = cfg if cfg is not None else Config()
+        self.cfg = copy.copy(cfg) if cfg is not None else Config()
+        self.cfg.site_index = {k: np.arange(off, off + s) for k, (off, s) in
+                               family.offsets().items()}
         self.family = family
+        if isinstance(dense_mass, (list, tuple)) or isinstance(inverse_mass_matrix, dict):
+            # hmc.py:760-769: structural form; a bool becomes one block over the sorted sites
+            if isinstance(dense_mass, bool):
+                dense_mass = [tuple(sorted(self.cfg.site_index))] if dense_mass else []
+            dense_mass = [tuple(b) for b in dense_mass]
         self.algo = algo
         self.step_size = step_size
         self.inverse_mass_matrix = inverse_mass_matrix

@@ -3,7 +3,9 @@
 TEST INFRASTRUCTURE (see ``oracle/__init__.py``).  Every function cites the
 reference lines it follows.  State is held as flat vectors (``ravel_pytree`` of
 the site dict in sorted-name order); the mass matrix is one block, 1-D
-(diagonal) or 2-D (dense).  Arithmetic is done in ``dtype`` (float32 by default,
+(diagonal) or 2-D (dense), or -- structured ``dense_mass`` lists / dict-valued
+``inverse_mass_matrix`` (``hmc_util.py:439-486``) -- a dict keyed by site-name tuples whose
+blocks address the flat vector through ``cfg.site_index``.  Arithmetic is done in ``dtype`` (float32 by default,
 like the reference with x64 disabled); Python loops play the role of
 ``lax.while_loop``/``cond`` exactly as the reference's own eager mode does
 (``numpyro/util.py:104-151`` ``control_flow_prims_disabled``).
@@ -37,6 +39,12 @@ class Config:
         self.dtype = np.dtype(dtype)
         self.f = self.dtype.type
         self.partitionable = partitionable
+        self.site_index = {}  # site name -> flat indices (set by oracle.hmc.HMCKernel)
+
+    def block_index(self, site_names):
+        """Flat indices of a mass-matrix block, in the block's OWN site order
+        (``tuple(z[k] for k in site_names)`` then ``ravel_pytree``, hmc_util.py:182-186)."""
+        return np.concatenate([self.site_index[k] for k in site_names])
 
     def split(self, key, n=2):
         return rnd.split(key, n, partitionable=self.partitionable)
@@ -75,16 +83,31 @@ def dual_averaging(cfg, t0=10, kappa=0.75, gamma=0.05):
     return init_fn, update_fn
 
 
+def _cholesky(a):
+    """``jnp.linalg.cholesky``: NaN-filled instead of raising when not positive definite."""
+    try:
+        return np.linalg.cholesky(a)
+    except np.linalg.LinAlgError:
+        return np.full_like(a, np.nan)
+
+
 # ---------------------------------------------------------------- welford
 def welford_covariance(cfg, diagonal=True):
     """hmc_util.py:133-239."""
     f, dt = cfg.f, cfg.dtype
 
     def init_fn(size):
-        shape = (size,) if diagonal else (size, size)
-        return np.zeros(size, dt), np.zeros(shape, dt), 0
+        if isinstance(size, dict):  # hmc_util.py:156-160: block -> SHAPE of its mass matrix
+            return {k: init_fn(v) for k, v in size.items()}
+        if isinstance(size, (int, np.integer)):
+            shape = (size,) if diagonal else (size, size)
+        else:
+            shape = tuple(size)
+        return np.zeros(shape[-1], dt), np.zeros(shape, dt), 0
 
     def update_fn(sample, state):
+        if isinstance(state, dict):  # hmc_util.py:176-182
+            return {k: update_fn(sample[cfg.block_index(k)], st) for k, st in state.items()}
         mean, m2, n = state
         n = n + 1
         delta_pre = sample - mean
@@ -97,6 +120,9 @@ def welford_covariance(cfg, diagonal=True):
         return mean.astype(dt), m2.astype(dt), n
 
     def final_fn(state, regularize=False):
+        if isinstance(state, dict):  # hmc_util.py:205-215
+            out = {k: final_fn(st, regularize=regularize) for k, st in state.items()}
+            return tuple({k: v[i] for k, v in out.items()} for i in range(3))
         mean, m2, n = state
         with np.errstate(divide="ignore", invalid="ignore"):
             cov = m2 / f(n - 1)
@@ -109,12 +135,12 @@ def welford_covariance(cfg, diagonal=True):
                 cov = scaled_cov + shrinkage * np.identity(mean.shape[0], dt)
         cov = cov.astype(dt)
         if cov.ndim == 2:
-            tril_inv = np.swapaxes(
-                np.linalg.cholesky(cov[::-1, ::-1].astype(np.float64))[::-1, ::-1], -2, -1
-            )
+            # in ``dt`` like the reference (LAPACK potrf/trtrs in f32 with x64 off)
+            tril_inv = np.ascontiguousarray(np.swapaxes(
+                _cholesky(cov[::-1, ::-1])[::-1, ::-1], -2, -1))
             from scipy.linalg import solve_triangular
 
-            cov_inv_sqrt = solve_triangular(tril_inv, np.identity(cov.shape[-1]), lower=True)
+            cov_inv_sqrt = solve_triangular(tril_inv, np.identity(cov.shape[-1], dt), lower=True)
             tril_inv, cov_inv_sqrt = tril_inv.astype(dt), cov_inv_sqrt.astype(dt)
         else:
             tril_inv = np.sqrt(cov)
@@ -125,8 +151,14 @@ def welford_covariance(cfg, diagonal=True):
 
 
 # ---------------------------------------------------------------- kinetic energy
-def kinetic_grad(inverse_mass_matrix, r):
+def kinetic_grad(inverse_mass_matrix, r, cfg=None):
     """hmc_util.py:1203-1220 (``M^-1 r``)."""
+    if isinstance(inverse_mass_matrix, dict):
+        v = np.empty_like(r)
+        for names, imm in inverse_mass_matrix.items():
+            idx = cfg.block_index(names)
+            v[idx] = kinetic_grad(imm, r[idx])
+        return v
     if inverse_mass_matrix.ndim == 2:
         return inverse_mass_matrix @ r
     return inverse_mass_matrix * r
@@ -134,6 +166,11 @@ def kinetic_grad(inverse_mass_matrix, r):
 
 def kinetic_energy(cfg, inverse_mass_matrix, r):
     """hmc_util.py:1183-1200."""
+    if isinstance(inverse_mass_matrix, dict):
+        ke = cfg.f(0)
+        for names, imm in inverse_mass_matrix.items():
+            ke = cfg.f(ke + kinetic_energy(cfg, imm, r[cfg.block_index(names)]))
+        return ke
     v = kinetic_grad(inverse_mass_matrix, r)
     return cfg.f(0.5) * cfg.f(np.dot(v, r))
 
@@ -152,7 +189,7 @@ def velocity_verlet(cfg, potential_fn):
         z, r, _, z_grad = state
         step_size = f(step_size)
         r = r - f(0.5) * step_size * z_grad
-        r_grad = kinetic_grad(inverse_mass_matrix, r)
+        r_grad = kinetic_grad(inverse_mass_matrix, r, cfg)
         z = z + step_size * r_grad
         potential_energy, z_grad = potential_fn(z)
         r = r - f(0.5) * step_size * z_grad
@@ -224,8 +261,35 @@ def build_adaptation_schedule(num_steps):
 
 # ---------------------------------------------------------------- mass matrix init
 def initialize_mass_matrix(cfg, size, inverse_mass_matrix, dense_mass):
-    """hmc_util.py:488-515 (single block)."""
+    """hmc_util.py:439-515.  ``dense_mass`` a list of site-name tuples -> block dicts, in the
+    reference's insertion order: the dense blocks, then the user's other blocks (diagonal),
+    then ONE diagonal block of the remaining sites in sorted order."""
     dt, f = cfg.dtype, cfg.f
+    if isinstance(dense_mass, list):
+        sites = sorted(cfg.site_index)
+        if inverse_mass_matrix is None:
+            imm = {}
+        elif not isinstance(inverse_mass_matrix, dict):
+            imm = {tuple(sites): inverse_mass_matrix}
+        else:
+            imm = dict(inverse_mass_matrix)
+        sqrt, sqrt_inv = {}, {}
+        for names in dense_mass:
+            imm[names], sqrt[names], sqrt_inv[names] = initialize_mass_matrix(
+                cfg, cfg.block_index(names).size, imm.get(names), True)
+        for names in list(imm):
+            if names in dense_mass:
+                continue
+            imm[names], sqrt[names], sqrt_inv[names] = initialize_mass_matrix(
+                cfg, cfg.block_index(names).size, imm[names], False)
+        remaining = tuple(sorted(set(sites) - set().union(*imm) if imm else set(sites)))
+        if len(remaining) > 0:
+            imm[remaining], sqrt[remaining], sqrt_inv[remaining] = initialize_mass_matrix(
+                cfg, cfg.block_index(remaining).size, None, False)
+        assert sorted(k for names in imm for k in names) == sites, (
+            "There seems to be a conflict of sites names specified in the initial"
+            " `inverse_mass_matrix` and in `dense_mass` argument.")
+        return imm, sqrt, sqrt_inv
     if inverse_mass_matrix is None:
         imm = np.identity(size, dt) if dense_mass else np.ones(size, dt)
         return imm, imm, imm
@@ -233,12 +297,11 @@ def initialize_mass_matrix(cfg, size, inverse_mass_matrix, dense_mass):
     if dense_mass:
         if imm.ndim == 1:
             imm = np.diag(imm)
-        sqrt_inv = np.swapaxes(
-            np.linalg.cholesky(imm[::-1, ::-1].astype(np.float64))[::-1, ::-1], -2, -1
-        )
+        sqrt_inv = np.ascontiguousarray(np.swapaxes(
+            _cholesky(imm[::-1, ::-1])[::-1, ::-1], -2, -1))
         from scipy.linalg import solve_triangular
 
-        sqrt = solve_triangular(sqrt_inv, np.identity(imm.shape[-1]), lower=True)
+        sqrt = solve_triangular(sqrt_inv, np.identity(imm.shape[-1], dt), lower=True)
         return imm, sqrt.astype(dt), sqrt_inv.astype(dt)
     if imm.ndim == 2:
         imm = np.diag(imm).copy()
@@ -269,6 +332,8 @@ def warmup_adapter(cfg, num_adapt_steps, find_reasonable_step_size=None, adapt_s
             step_size = f(find_reasonable_step_size(step_size, imm, z_info, rng_key_ss))
         with np.errstate(over="ignore"):
             ss_state = ss_init(np.log(f(10) * step_size))
+        if isinstance(imm, dict):  # hmc_util.py:577-580
+            size = {k: v.shape for k, v in imm.items()}
         mm_state = mm_init(size)
         return HMCAdaptState(step_size, imm, mm_sqrt, mm_sqrt_inv, ss_state, mm_state, 0, rng_key)
 
@@ -276,7 +341,8 @@ def warmup_adapter(cfg, num_adapt_steps, find_reasonable_step_size=None, adapt_s
         step_size, imm, mm_sqrt, mm_sqrt_inv, ss_state, mm_state, window_idx, rng_key = state
         if adapt_mass_matrix:
             imm, mm_sqrt, mm_sqrt_inv = mm_final(mm_state, regularize=regularize_mass_matrix)
-            mm_state = mm_init(imm.shape[-1])
+            mm_state = mm_init({k: v.shape for k, v in imm.items()} if isinstance(imm, dict)
+                               else imm.shape[-1])
         if adapt_step_size:
             step_size = f(find_reasonable_step_size(step_size, imm, z_info, rng_key_ss))
             ss_state = ss_init(f(np.log(f(10))) + np.log(step_size))
@@ -315,6 +381,13 @@ def warmup_adapter(cfg, num_adapt_steps, find_reasonable_step_size=None, adapt_s
 def momentum_angle(cfg, inverse_mass_matrix, r_left, r_right, r_sum):
     """hmc_util.py:710-737."""
     f = cfg.f
+    if isinstance(inverse_mass_matrix, dict):  # per block, then summed (:711-720)
+        left_angle, right_angle = f(0), f(0)
+        for names, imm in inverse_mass_matrix.items():
+            idx = cfg.block_index(names)
+            la, ra = momentum_angle(cfg, imm, r_left[idx], r_right[idx], r_sum[idx])
+            left_angle, right_angle = f(left_angle + la), f(right_angle + ra)
+        return left_angle, right_angle
     v_left = kinetic_grad(inverse_mass_matrix, r_left)
     v_right = kinetic_grad(inverse_mass_matrix, r_right)
     r_sum = r_sum - (r_left + r_right) / f(2)
