@@ -66,6 +66,18 @@ typedef struct {
    * leapfrog over NVLink peer memory.  nranks <= 1: single GPU. */
   int nranks;
   int rank;
+  /* Structured mass matrix (dense_mass=[("a","b"), ...] / dict-valued inverse_mass_matrix:
+   * hmc_util.py:439-486, hmc.py:92-102, 760-769).  num_blocks <= 1: one block over the whole
+   * flat vector.  Otherwise HOST tables: block_perm[D] = flat indices in concatenated block
+   * order (each block in its own site order, blocks in the reference's dict order = the order
+   * of the per-block momentum keys), block_sizes[num_blocks], block_dense[num_blocks] (1 =
+   * full sub-matrix, 0 = diagonal).  dense_mass must be 1 iff any block is dense;
+   * inverse_mass_matrix_dev is then the full [D][D] matrix in FLAT order with zeros outside
+   * the blocks. */
+  int num_blocks;
+  const int* block_perm_host;
+  const int* block_sizes_host;
+  const int* block_dense_host;
 } b200mc_config;
 
 /* Scalar leaves of HMCState (hmc.py:31-48) and HMCAdaptState (hmc_util.py:18-30). */

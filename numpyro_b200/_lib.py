@@ -29,6 +29,8 @@ class Config(C.Structure):
         ("threefry_partitionable", C.c_int), ("init_radius", C.c_float),
         ("inverse_mass_matrix_dev", C.c_void_p), ("find_heuristic_step_size", C.c_int),
         ("likelihood", C.c_int), ("nranks", C.c_int), ("rank", C.c_int),
+        ("num_blocks", C.c_int), ("block_perm_host", C.c_void_p),
+        ("block_sizes_host", C.c_void_p), ("block_dense_host", C.c_void_p),
     ]
 
 

@@ -58,6 +58,7 @@ struct b200mc_handle {
   unsigned long long* prof = nullptr;  // [kGlmProfSlots]
   int glm_reverse = 1;
   float* dense_replicas = nullptr;
+  int* blk_tables = nullptr;  // structured mass matrix: blk_of, blk_pos, blk_perm [D] + size, dense [nb]
   // row sharding
   int nranks = 1, rank = 0;
   float* xchg_local = nullptr;
@@ -212,6 +213,7 @@ extern "C" void b200mc_destroy(b200mc_handle* h) {
   cudaFree(h->cv.mass_matrix_sqrt); cudaFree(h->cv.welford_mean); cudaFree(h->cv.welford_m2);
   cudaFree(h->work); cudaFree(h->partials); cudaFree(h->counters); cudaFree(h->prof); cudaFree(h->glm_xt);
   cudaFree(h->cv.dense); cudaFree(h->dense_replicas); cudaFree(h->M.scratch);
+  cudaFree(h->blk_tables);
   for (int r = 0; r < h->nranks; ++r) {
     if (r == h->rank) continue;
     if (h->xchg[r]) cudaIpcCloseMemHandle(h->xchg[r]);
@@ -318,6 +320,37 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   ACK(alloc((void**)&h->cv.welford_m2, vec_bytes));
   if (c.dense_mass) ACK(alloc((void**)&h->cv.dense, sizeof(float) * 4 * (size_t)C * D * D));
 
+  P.num_blocks = 1;
+  if (c.num_blocks > 1) {  // structured mass matrix: validate and upload the block tables
+    if (!c.block_perm_host || !c.block_sizes_host || !c.block_dense_host) {
+      b200mc_destroy(h); return fail("num_blocks > 1 needs block_perm/sizes/dense tables");
+    }
+    const int nb = c.num_blocks;
+    std::vector<int> t(3 * (size_t)D + 2 * (size_t)nb, -1);
+    int *of = t.data(), *pos = of + D, *perm = pos + D, *size = perm + D, *dn = size + nb;
+    int a = 0, any_dense = 0;
+    for (int b = 0; b < nb; ++b) {
+      size[b] = c.block_sizes_host[b];
+      dn[b] = c.block_dense_host[b] ? 1 : 0;
+      any_dense |= dn[b];
+      if (size[b] < 1 || a + size[b] > D) { b200mc_destroy(h); return fail("block sizes do not add up to D=%d", D); }
+      for (int j = 0; j < size[b]; ++j, ++a) {
+        const int f = c.block_perm_host[a];
+        if (f < 0 || f >= D || of[f] != -1) { b200mc_destroy(h); return fail("block_perm is not a permutation of 0..D-1"); }
+        perm[a] = f; of[f] = b; pos[f] = j;
+      }
+    }
+    if (a != D) { b200mc_destroy(h); return fail("block sizes do not add up to D=%d", D); }
+    if ((any_dense != 0) != (c.dense_mass != 0)) {
+      b200mc_destroy(h); return fail("dense_mass must be set iff a block is dense");
+    }
+    ACK(cudaMalloc((void**)&h->blk_tables, t.size() * sizeof(int)));
+    ACK(cudaMemcpy(h->blk_tables, t.data(), t.size() * sizeof(int), cudaMemcpyHostToDevice));
+    P.num_blocks = nb;
+    P.blk_of = h->blk_tables; P.blk_pos = P.blk_of + D; P.blk_perm = P.blk_pos + D;
+    P.blk_size = P.blk_perm + D; P.blk_dense = P.blk_size + nb;
+  }
+
   const int nslots = num_slots(P.max_depth, P.dense_mass);
   int batch_min = 64;  // north_star: from 64 chains on, X.Theta is a real dense contraction
   // with a dense mass matrix the batched whole-machine sweeps pay off much earlier (a single
@@ -325,7 +358,7 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   if (c.family == B200MC_HORSESHOE && c.dense_mass) batch_min = 16;
   if (const char* e = getenv("B200MC_BATCH_MIN_CHAINS")) batch_min = atoi(e);
   const bool batch = (c.family == B200MC_HORSESHOE || c.family == B200MC_LOGISTIC) &&
-                     C >= batch_min && C <= kBatchCols && !(c.nranks > 1);
+                     C >= batch_min && C <= kBatchCols && !(c.nranks > 1) && P.num_blocks <= 1;
   if (c.family == B200MC_LOGISTIC && !batch) {
     if (D > kGlmMaxD) { b200mc_destroy(h); return fail("logistic: D=%d > %d not supported", D, kGlmMaxD); }
     if (!c.data1_dev) { b200mc_destroy(h); return fail("logistic: labels missing"); }

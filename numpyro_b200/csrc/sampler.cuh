@@ -366,16 +366,44 @@ struct Sampler {
   // r = M^{1/2} eps, eps ~ N(0, I): hmc.py:92-110 (one dict block => split(key, 1)).
   // use_imm: the reference's find_reasonable_step_size hands the INVERSE mass matrix to
   // momentum_generator (hmc_util.py:362), so r = M^-1 eps there; restated as is.
-  __device__ __forceinline__ void draw_momentum(Key k_mom, int dst, bool use_imm = false) {
+  // Structured mass matrix (hmc.py:92-102): keys = split(k_mom, num_blocks) in the dict order
+  // of the blocks, block b draws normal(keys[b], (size_b,)); coordinate d takes element
+  // blk_pos[d] of its block's draw.
+  __device__ __forceinline__ float block_eps(Key k_mom, int d) const {
+    const int b = P->blk_of[d];
+    const Key kb = split_at(k_mom, (uint32_t)P->num_blocks, (uint32_t)b, part);
+    return normal_at(kb, (uint32_t)P->blk_size[b], (uint32_t)P->blk_pos[d], part);
+  }
+
+  // eps ~ N(0, I) of momentum_generator into slot `dst`
+  __device__ __forceinline__ void draw_eps(Key k_mom, int dst) {
+    float* eps = v(dst);
+    if (P->num_blocks > 1) {
+      B200MC_FOR_D eps[d * es] = block_eps(k_mom, d);
+      return;
+    }
     const Key kb = split_at(k_mom, 1u, 0u, part);
+    B200MC_FOR_D eps[d * es] = normal_at(kb, (uint32_t)D, (uint32_t)d, part);
+  }
+
+  // M^{1/2} is lower triangular only for ONE block in flat order; with several blocks the
+  // factor is block-structured under a permutation and the sweep covers whole rows (the
+  // entries outside the blocks are exact zeros).
+  __device__ __forceinline__ bool sqrt_is_lower() const { return P->num_blocks <= 1; }
+
+  __device__ __forceinline__ void draw_momentum(Key k_mom, int dst, bool use_imm = false) {
     float* r = v(dst);
     if (dense) {
-      float* eps = v(LV);
-      B200MC_FOR_D eps[d * es] = normal_at(kb, (uint32_t)D, (uint32_t)d, part);
-      matvec(use_imm ? mat(0) : mat(1), eps, r, !use_imm);
+      draw_eps(k_mom, LV);
+      matvec(use_imm ? mat(0) : mat(1), v(LV), r, !use_imm && sqrt_is_lower());
       return;
     }
     const float* ms = use_imm ? v(IMM) : v(MSQRT);
+    if (P->num_blocks > 1) {
+      B200MC_FOR_D r[d * es] = ms[d * es] * block_eps(k_mom, d);
+      return;
+    }
+    const Key kb = split_at(k_mom, 1u, 0u, part);
     B200MC_FOR_D {
       const float eps = normal_at(kb, (uint32_t)D, (uint32_t)d, part);
       r[d * es] = ms[d * es] * eps;
@@ -464,12 +492,20 @@ struct Sampler {
   //   tril_inv     = swapaxes(cholesky(cov[::-1, ::-1])[::-1, ::-1])
   //   cov_inv_sqrt = solve_triangular(tril_inv, identity, lower=True)
   // mat(3) (the Welford m2 buffer) is the workspace and is left zeroed.
+  // Structured mass matrix: the same recipe runs in BLOCK ORDER (position a <-> flat index
+  // blk_perm[a]); there the masked covariance is block diagonal, so the reversed Cholesky of
+  // the whole matrix is the reversed Cholesky of every block (a diagonal block gives
+  // sqrt(cov) and 1/sqrt(cov), hmc_util.py:234-236), and the factors are scattered back to
+  // flat order.
   __device__ __noinline__ void factor_dense() {
     float *cov = mat(0), *msq = mat(1), *tinv = mat(2), *W = mat(3);
     const int n = D;
+    const int* perm = (P->num_blocks > 1) ? P->blk_perm : nullptr;
+#define B200MC_PI(a) (perm ? perm[a] : (a))
     g.sync();
-    B200MC_FOR_D  // W = cov reversed in both axes
-      for (int j = 0; j < n; ++j) W[(long)d * n + j] = cov[(long)(n - 1 - d) * n + (n - 1 - j)];
+    B200MC_FOR_D  // W = cov (block order) reversed in both axes
+      for (int j = 0; j < n; ++j)
+        W[(long)d * n + j] = cov[(long)B200MC_PI(n - 1 - d) * n + B200MC_PI(n - 1 - j)];
     g.sync();
     for (int k = 0; k < n; ++k) {  // left-looking Cholesky, lower triangle, in place
       float dk = W[(long)k * n + k];
@@ -490,22 +526,27 @@ struct Sampler {
       }
       g.sync();
     }
-    B200MC_FOR_D  // tril_inv[i][j] = Lc[n-1-j][n-1-i] for j <= i, else 0
+    B200MC_FOR_D {  // tril_inv[i][j] = Lc[n-1-j][n-1-i] for j <= i, else 0
+      const long row = (long)B200MC_PI(d) * n;
       for (int j = 0; j < n; ++j)
-        tinv[(long)d * n + j] = (j <= d) ? W[(long)(n - 1 - j) * n + (n - 1 - d)] : 0.f;
+        tinv[row + B200MC_PI(j)] = (j <= d) ? W[(long)(n - 1 - j) * n + (n - 1 - d)] : 0.f;
+    }
     g.sync();
     B200MC_FOR_D {  // column d of the inverse of the lower-triangular tril_inv
+      const int pd = B200MC_PI(d);
       for (int i = 0; i < n; ++i) {
+        const long ri = (long)B200MC_PI(i) * n;
         float a = (i == d) ? 1.f : 0.f;
         if (i < d) {
-          msq[(long)i * n + d] = 0.f;
+          msq[ri + pd] = 0.f;
           continue;
         }
-        for (int p = d; p < i; ++p) a -= tinv[(long)i * n + p] * msq[(long)p * n + d];
-        msq[(long)i * n + d] = a / tinv[(long)i * n + i];
+        for (int p = d; p < i; ++p) a -= tinv[ri + B200MC_PI(p)] * msq[(long)B200MC_PI(p) * n + pd];
+        msq[ri + pd] = a / tinv[ri + B200MC_PI(i)];
       }
     }
     g.sync();
+#undef B200MC_PI
     B200MC_FOR_D
       for (int j = 0; j < n; ++j) W[(long)d * n + j] = 0.f;
     g.sync();
@@ -611,13 +652,19 @@ struct Sampler {
           }
         }
         float *cov = mat(0), *M2 = mat(3);
+        const bool blocks = P->num_blocks > 1;
         B200MC_FOR_D {
+          const int bd = blocks ? P->blk_of[d] : 0;
+          const bool full = blocks ? (P->blk_dense[bd] != 0) : true;
           for (int j = 0; j < D; ++j) {
             float c = M2[(long)d * D + j] / (n - 1.0f);
             if (P->regularize_mass_matrix) {
               c = scale * c;
               if (j == d) c = c + shrink;
             }
+            // structured mass matrix: covariances across blocks (and the off-diagonal of a
+            // diagonal block) are not part of the model of M (hmc_util.py:176-182)
+            if (blocks && j != d && !(full && P->blk_of[j] == bd)) c = 0.f;
             cov[(long)d * D + j] = c;
           }
         }
@@ -917,9 +964,7 @@ struct Sampler {
   __device__ __forceinline__ void compute_transition_rng() {
     Key k_mom;
     split3(Key{s.rng_key[0], s.rng_key[1]}, part, pre_t_rng_key, k_mom, pre_t_k_tr);
-    const Key kb = split_at(k_mom, 1u, 0u, part);
-    float* eps = v(EPS_NEXT);
-    B200MC_FOR_D eps[d * es] = normal_at(kb, (uint32_t)D, (uint32_t)d, part);
+    draw_eps(k_mom, EPS_NEXT);
     if (P->algo == ALGO_NUTS) compute_doubling_rng(pre_t_k_tr, pre_t_d);
   }
 
@@ -928,7 +973,7 @@ struct Sampler {
     float* r = v(dst);
     const float* eps = v(EPS_NEXT);
     if (dense) {
-      matvec(mat(1), eps, r, true);
+      matvec(mat(1), eps, r, sqrt_is_lower());
       return;
     }
     const float* ms = v(MSQRT);

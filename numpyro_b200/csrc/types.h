@@ -34,6 +34,15 @@ struct SamplerParams {
   int nsites;
   int site_off[kMaxSites], site_size[kMaxSites];
   float init_radius;
+  // structured mass matrix (hmc_util.py:439-486): num_blocks <= 1 => one block in flat order.
+  // Device tables: blk_of[D] block of a flat coordinate, blk_pos[D] its position inside the
+  // block, blk_perm[D] flat index of block-order position a, blk_size/blk_dense[num_blocks].
+  int num_blocks;
+  const int* blk_of;
+  const int* blk_pos;
+  const int* blk_perm;
+  const int* blk_size;
+  const int* blk_dense;
 };
 
 // Persistent per-chain scalars: the scalar leaves of HMCState (hmc.py:31-48) and

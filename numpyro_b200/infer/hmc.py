@@ -95,12 +95,11 @@ class HMC(MCMCKernel):
                 "numpyro_b200 has no generic autodiff fallback")
         if kinetic_fn is not None:
             raise NotImplementedError("only the euclidean kinetic energy is implemented")
-        if not isinstance(dense_mass, bool):
-            if isinstance(dense_mass, (list, tuple)) and len(dense_mass) == 0:
-                dense_mass = False
-            else:
-                raise NotImplementedError(
-                    "structured (block) mass matrices are not implemented: dense_mass must be a bool")
+        if not isinstance(dense_mass, bool):  # structured form, hmc.py:605-616
+            if not isinstance(dense_mass, (list, tuple)) or not all(
+                    isinstance(b, tuple) and all(isinstance(k, str) for k in b) for b in dense_mass):
+                raise ValueError("dense_mass must be a bool or a list of tuples of site names")
+            dense_mass = [tuple(b) for b in dense_mass]
         self._model = models.resolve(model)
         self._potential_fn = None
         self._kinetic_fn = None
@@ -188,29 +187,96 @@ class HMC(MCMCKernel):
         return int(b2random.DEFAULT_PARTITIONABLE if self.partitionable is None
                    else self.partitionable)
 
+    def _mass_layout(self, bound):
+        """Block structure of the mass matrix, ``hmc.py:760-769`` + ``hmc_util.py:439-486``.
+
+        Returns ``(blocks, key_order, user)``: ``blocks`` = ``[(site_names, flat_idx, dense)]``
+        in the insertion order of the reference's ``inverse_mass_matrix`` dict (the user's
+        entries, then the dense blocks, then ONE diagonal block of the remaining sites in
+        sorted order); ``key_order`` = block indices in the order of its ``mass_matrix_sqrt``
+        dict, which is the order of the per-block momentum keys (``hmc.py:94-96``): dense
+        blocks, the user's other blocks, the remaining sites; ``user`` = the user's matrices
+        per block (or None)."""
+        sites = sorted(k for k, _ in bound.trace_sites)
+        dm = self._dense_mass
+        dm = ([tuple(sites)] if dm else []) if isinstance(dm, bool) else list(dm)
+        m = self._inverse_mass_matrix
+        if m is None:
+            user = {}
+        elif not isinstance(m, dict):
+            user = {tuple(sites): m}
+        else:
+            user = {tuple(k): v for k, v in m.items()}
+        order = list(user)
+        order += [b for b in dm if b not in user]
+        used = [k for b in order for k in b]
+        for k in used:
+            if k not in sites:
+                raise KeyError(k)
+        remaining = tuple(sorted(set(sites) - set(used)))
+        if remaining:
+            order.append(remaining)
+        if sorted(k for b in order for k in b) != sites:
+            raise AssertionError(
+                "There seems to be a conflict of sites names specified in the initial"
+                " `inverse_mass_matrix` and in `dense_mass` argument.")
+        blocks = []
+        for names in order:
+            idx = np.concatenate([np.arange(bound.flat_sites[k][0],
+                                            bound.flat_sites[k][0] + bound.flat_sites[k][1])
+                                  for k in names]).astype(np.int32)
+            blocks.append((names, idx, names in dm))
+        keys = [b for b in dm] + [b for b in user if b not in dm] + ([remaining] if remaining else [])
+        key_order = [order.index(b) for b in keys]
+        return blocks, key_order, user
+
     def _create(self, bound, num_chains, num_warmup):
         _lib.require_device()
         self._destroy()
         lib = _lib.lib()
         d0 = _lib.DeviceArray.from_numpy(bound.data0)
         d1 = _lib.DeviceArray.from_numpy(bound.data1) if bound.data1 is not None else None
+        blocks, key_order, user = self._mass_layout(bound)
+        D = bound.dim
+        any_dense = any(dn for _, _, dn in blocks)
+        if len(blocks) > 1 and key_order != list(range(len(blocks))):
+            if self._adapt_mass_matrix:
+                raise NotImplementedError(
+                    "an `inverse_mass_matrix` dict that lists a diagonal block before a dense one "
+                    "changes the reference's momentum-key order at the first window end "
+                    "(hmc_util.py:205-215 vs :449-474); list the dense blocks first")
+            blocks = [blocks[i] for i in key_order]
+        self._blocks = blocks
+        self._dense = any_dense
         imm = None
-        if self._inverse_mass_matrix is not None:
-            m = self._inverse_mass_matrix
-            if isinstance(m, dict):
-                if len(m) != 1:
-                    raise NotImplementedError("block mass matrices are not implemented yet")
-                m = next(iter(m.values()))
-            m = np.asarray(m, np.float32)
-            want = (bound.dim, bound.dim) if self._dense_mass else (bound.dim,)
-            if m.shape != want:
-                if m.shape == (bound.dim,) and self._dense_mass:
-                    m = np.diag(m).astype(np.float32)  # hmc_util.py:492-493
-                elif m.shape == (bound.dim, bound.dim) and not self._dense_mass:
-                    raise ValueError("a 2-D inverse_mass_matrix needs dense_mass=True")
+        if user:
+            full = np.eye(D, dtype=np.float32) if any_dense else np.ones(D, np.float32)
+            for names, idx, dn in blocks:
+                if names not in user:
+                    continue
+                m = np.asarray(user[names], np.float32)
+                d = idx.size
+                if dn:
+                    if m.shape == (d,):
+                        m = np.diag(m).astype(np.float32)  # hmc_util.py:492-493
+                    if m.shape != (d, d):
+                        raise ValueError(f"inverse_mass_matrix of block {names} must have shape {(d, d)}")
+                    full[np.ix_(idx, idx)] = m
                 else:
-                    raise ValueError(f"inverse_mass_matrix must have shape {want}")
-            imm = _lib.DeviceArray.from_numpy(m)
+                    if m.shape == (d, d):
+                        m = np.diag(m).copy()  # hmc_util.py:509-510
+                    if m.shape != (d,):
+                        raise ValueError(f"inverse_mass_matrix of block {names} must have shape {(d,)}")
+                    if any_dense:
+                        full[idx, idx] = m
+                    else:
+                        full[idx] = m
+            imm = _lib.DeviceArray.from_numpy(full)
+        tables = None
+        if len(blocks) > 1:
+            tables = (np.ascontiguousarray(np.concatenate([idx for _, idx, _ in blocks]), np.int32),
+                      np.array([idx.size for _, idx, _ in blocks], np.int32),
+                      np.array([int(dn) for _, _, dn in blocks], np.int32))
         depth = self._max_tree_depth
         depth = depth if isinstance(depth, tuple) else (depth, depth)
         kind, arg = self._strategy()
@@ -220,7 +286,7 @@ class HMC(MCMCKernel):
             algo=0 if self._algo == "NUTS" else 1, step_size=float(self._step_size),
             adapt_step_size=int(bool(self._adapt_step_size)),
             adapt_mass_matrix=int(bool(self._adapt_mass_matrix)),
-            dense_mass=int(bool(self._dense_mass)),
+            dense_mass=int(any_dense),
             find_heuristic_step_size=int(bool(self._find_heuristic_step_size)),
             likelihood=int(getattr(bound, "likelihood", 0)),
             nranks=self._row_shard[1] if self._row_shard else 1,
@@ -233,7 +299,11 @@ class HMC(MCMCKernel):
             trajectory_length=float(self._trajectory_length or 0.0),
             num_steps=int(self._num_steps or 0), threefry_partitionable=self._part(),
             init_radius=float(arg) if kind == "uniform" else 2.0,
-            inverse_mass_matrix_dev=imm.ptr if imm is not None else None)
+            inverse_mass_matrix_dev=imm.ptr if imm is not None else None,
+            num_blocks=len(blocks),
+            block_perm_host=tables[0].ctypes.data if tables else None,
+            block_sizes_host=tables[1].ctypes.data if tables else None,
+            block_dense_host=tables[2].ctypes.data if tables else None)
         h = C.c_void_p()
         if self._row_shard and bound.family != models.LOGISTIC:
             raise NotImplementedError("row sharding exists for the tall-data logistic family only")
@@ -272,7 +342,7 @@ class HMC(MCMCKernel):
         for name, which in _VEC.items():
             _lib.check(lib.b200mc_get_vector(h, which, tmp.ptr, None))
             vec[name] = tmp.numpy()
-        if self._dense_mass:
+        if self._dense:
             mt = _lib.DeviceArray((Cn, D, D), np.float32)
             for name, which in _MAT.items():
                 _lib.check(lib.b200mc_get_vector(h, which, mt.ptr, None))
@@ -282,17 +352,25 @@ class HMC(MCMCKernel):
     def _to_state(self, sc, vec):
         b = self._bound
         sq = (lambda a: a) if self._vectorized else (lambda a: a[0])
-        block = tuple(sorted(k for k, _ in b.trace_sites))
         imm = vec["inverse_mass_matrix"]
-        sqrt_inv = vec["mass_matrix_sqrt_inv"] if self._dense_mass else np.sqrt(imm)
+        sqrt_inv = vec["mass_matrix_sqrt_inv"] if self._dense else np.sqrt(imm)
+
+        def cut(a, idx, dn):
+            """block of a per-chain [C, D] vector / [C, D, D] matrix (device layout: flat order)"""
+            if a.ndim == 3:
+                return a[:, idx[:, None], idx[None, :]] if dn else a[:, idx, idx]
+            return a[:, idx]
+
+        per_block = lambda a: {names: sq(cut(a, idx, dn)) for names, idx, dn in self._blocks}  # noqa: E731
         adapt = HMCAdaptState(
             step_size=sq(sc["step_size"].copy()),
-            inverse_mass_matrix={block: sq(imm)},
-            mass_matrix_sqrt={block: sq(vec["mass_matrix_sqrt"])},
-            mass_matrix_sqrt_inv={block: sq(sqrt_inv)},
+            inverse_mass_matrix=per_block(imm),
+            mass_matrix_sqrt=per_block(vec["mass_matrix_sqrt"]),
+            mass_matrix_sqrt_inv=per_block(sqrt_inv),
             ss_state=(sq(sc["ss_x_t"].copy()), sq(sc["ss_x_avg"].copy()), sq(sc["ss_g_avg"].copy()),
                       sq(sc["ss_t"].copy()), sq(sc["ss_prox_center"].copy())),
-            mm_state={block: (sq(vec["welford_mean"]), sq(vec["welford_m2"]), sq(sc["mm_n"].copy()))},
+            mm_state={names: (sq(vec["welford_mean"][:, idx]), sq(cut(vec["welford_m2"], idx, dn)),
+                              sq(sc["mm_n"].copy())) for names, idx, dn in self._blocks},
             window_idx=sq(sc["window_idx"].copy()),
             rng_key=sq(sc["adapt_key"].copy()))
         tl = None
@@ -320,6 +398,20 @@ class HMC(MCMCKernel):
         sc = np.zeros(Cn, _lib.SCALARS_DTYPE)
         a = state.adapt_state
         block = next(iter(a.inverse_mass_matrix))
+        D = b.dim
+
+        def join(d, mat):
+            """per-block dict -> [C, D] vector or (``mat``) [C, D, D] matrix in flat order"""
+            out = np.zeros((Cn, D, D) if mat else (Cn, D), np.float32)
+            for names, idx, dn in self._blocks:
+                v = up(d[names]).astype(np.float32)
+                if mat and dn:
+                    out[:, idx[:, None], idx[None, :]] = v.reshape(Cn, idx.size, idx.size)
+                elif mat:
+                    out[:, idx, idx] = v.reshape(Cn, idx.size)
+                else:
+                    out[:, idx] = v.reshape(Cn, idx.size)
+            return out
         for name, val in (("i", state.i), ("potential_energy", state.potential_energy),
                           ("energy", state.energy), ("num_steps", state.num_steps),
                           ("accept_prob", state.accept_prob),
@@ -334,15 +426,16 @@ class HMC(MCMCKernel):
         if getattr(self, "_last_grad_evals", None) is not None:
             sc["grad_evals"] = self._last_grad_evals
         _lib.check(lib.b200mc_set_scalars(h, sc.ctypes.data))
+        dn_ = self._dense
         vecs = {"z": b.ravel(state.z), "z_grad": b.ravel(state.z_grad),
-                "inverse_mass_matrix": a.inverse_mass_matrix[block],
-                "mass_matrix_sqrt": a.mass_matrix_sqrt[block],
-                "welford_mean": a.mm_state[block][0], "welford_m2": a.mm_state[block][1]}
+                "welford_mean": join({k: v[0] for k, v in a.mm_state.items()}, False)}
         mats = {}
-        if self._dense_mass:
-            for name in ("inverse_mass_matrix", "mass_matrix_sqrt", "welford_m2"):
-                mats[name] = vecs.pop(name)
-            mats["mass_matrix_sqrt_inv"] = a.mass_matrix_sqrt_inv[block]
+        (mats if dn_ else vecs).update({
+            "inverse_mass_matrix": join(a.inverse_mass_matrix, dn_),
+            "mass_matrix_sqrt": join(a.mass_matrix_sqrt, dn_),
+            "welford_m2": join({k: v[1] for k, v in a.mm_state.items()}, dn_)})
+        if dn_:
+            mats["mass_matrix_sqrt_inv"] = join(a.mass_matrix_sqrt_inv, True)
         for name, val in vecs.items():
             d = _lib.DeviceArray.from_numpy(up(val).reshape(Cn, b.dim), np.float32)
             _lib.check(lib.b200mc_set_vector(h, _VEC[name], d.ptr, None))

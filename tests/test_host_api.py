@@ -74,8 +74,9 @@ def test_constructor_contract(nb):
         NUTS(lambda x: x)
     with pytest.raises(NotImplementedError):
         NUTS(potential_fn=lambda z: 0.0)
-    with pytest.raises(NotImplementedError):
-        NUTS(models.logistic_regression, dense_mass=[("coefs",)])  # structured blocks
+    with pytest.raises(ValueError, match="list of tuples"):
+        NUTS(models.logistic_regression, dense_mass=["coefs"])
+    assert NUTS(models.logistic_regression, dense_mass=[("coefs",)])._dense_mass == [("coefs",)]
     assert NUTS(models.logistic_regression, dense_mass=True, find_heuristic_step_size=True)._dense_mass
     k = NUTS(models.eight_schools_noncentered, step_size=1, max_tree_depth=(5, 10))
     assert k._step_size == 1.0 and isinstance(k._step_size, float)
@@ -89,6 +90,30 @@ def test_constructor_contract(nb):
         MCMC(k, num_warmup=1, num_samples=1, chain_method="foo")
     with pytest.raises(NotImplementedError):
         models.logistic_regression(np.zeros((2, 2)), np.zeros(2))
+
+
+def test_structured_mass_matrix_layout(nb):
+    """Block order of the reference's dicts (hmc_util.py:439-486): ``inverse_mass_matrix`` =
+    user entries, dense blocks, remaining sites; momentum keys (``mass_matrix_sqrt``) = dense
+    blocks, user's other blocks, remaining sites; a block keeps its OWN site order."""
+    from numpyro_b200 import models
+    from numpyro_b200.infer import NUTS
+
+    b = models.eight_schools_noncentered.bind(8, np.ones(8), y=np.ones(8))
+    lay = lambda **kw: NUTS(models.eight_schools_noncentered, **kw)._mass_layout(b)  # noqa: E731
+    blocks, keys, _ = lay()
+    assert [n for n, _, _ in blocks] == [("mu", "tau", "theta_base")] and not blocks[0][2]
+    blocks, keys, _ = lay(dense_mass=True)
+    assert blocks[0][2] and np.array_equal(blocks[0][1], np.arange(10))
+    blocks, keys, _ = lay(dense_mass=[("theta_base", "mu")])
+    assert [n for n, _, _ in blocks] == [("theta_base", "mu"), ("tau",)]
+    assert np.array_equal(blocks[0][1], [2, 3, 4, 5, 6, 7, 8, 9, 0]) and blocks[0][2]
+    assert np.array_equal(blocks[1][1], [1]) and not blocks[1][2] and keys == [0, 1]
+    blocks, keys, user = lay(dense_mass=[("tau", "theta_base")],
+                             inverse_mass_matrix={("mu",): np.ones(1), ("tau", "theta_base"): np.eye(9)})
+    assert [n for n, _, _ in blocks] == [("mu",), ("tau", "theta_base")] and keys == [1, 0]
+    with pytest.raises(AssertionError, match="conflict of sites names"):
+        lay(dense_mass=[("mu", "tau")], inverse_mass_matrix={("mu",): np.ones(1)})
 
 
 def test_no_device_raises_loudly(nb):

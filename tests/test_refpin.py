@@ -90,3 +90,190 @@ def test_fixture_regenerates_from_the_reference_source(name):
     res = make_refpin.run_case(hmc, util, rc.families(DATA)[fk], algo, kw, seed, nw, ns)
     for f in rc.FIELDS:
         assert np.array_equal(res[f], G[f"{name}/{f}"], equal_nan=True), (name, f)
+
+
+# ------------------------------------------------------------------------------- GPU
+@pytest.fixture(scope="module")
+def nb():
+    import __graft_entry__ as g
+
+    return g.build()
+
+
+def _bind_args(fk):
+    from numpyro_b200 import models
+
+    if fk == "es":
+        return models.eight_schools_noncentered, (8, rc.S8), {"y": rc.Y8}
+    if fk == "logit":
+        return models.logistic_regression, (DATA["logistic_X"], DATA["logistic_y"]), {}
+    if fk == "hsb":
+        return models.horseshoe_bernoulli, (DATA["hs_X"], DATA["hs_Yb"]), {}
+    if fk == "hsn":
+        return models.horseshoe_normal, (DATA["hs_X"], DATA["hs_Yn"]), {}
+    return models.stochastic_volatility, (DATA["sv_returns"],), {}
+
+
+def _cuda_trace(nb, name):
+    from numpyro_b200 import infer
+    from numpyro_b200.random import PRNGKey
+
+    fk, algo, kw, seed, nw, ns, part = rc.CASES[name]
+    model, args, kwargs = _bind_args(fk)
+    kernel = getattr(infer, algo)(model, **kw)
+    kernel.partitionable = part
+    z0 = model.bind(*args, **kwargs).unravel(G[name + "/z0"])
+    state = kernel.init(PRNGKey(seed), nw, init_params=z0, model_args=args, model_kwargs=kwargs)
+    fields = ("z", "potential_energy", "energy", "num_steps", "accept_prob", "mean_accept_prob",
+              "diverging", "adapt_state.step_size")
+    raw, last = kernel.run_loop(state, nw + ns, 0, 1, nw + ns, fields)
+    res = {f: raw[f][:, 0] for f in fields}
+    res["step_size"] = res.pop("adapt_state.step_size")
+    return res, last
+
+
+FIXED = [n for n, c in rc.CASES.items() if c[4] == 0]
+ADAPT = [n for n, c in rc.CASES.items() if c[4] > 0]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", FIXED)
+def test_cuda_fixed_parameter_traces_match_reference_source(nb, name):
+    """Tier 3 against the reference's own code: identical tree sizes, divergences and
+    accepted points over every transition."""
+    res, _ = _cuda_trace(nb, name)
+    assert np.array_equal(res["num_steps"], G[name + "/num_steps"]), name
+    assert np.array_equal(res["diverging"], G[name + "/diverging"]), name
+    np.testing.assert_allclose(res["z"], G[name + "/z"], rtol=5e-3, atol=5e-4)
+    np.testing.assert_allclose(res["potential_energy"], G[name + "/potential_energy"], rtol=1e-4)
+    np.testing.assert_allclose(res["accept_prob"], G[name + "/accept_prob"], rtol=5e-3, atol=1e-5)
+
+
+def _mirror_state(nb, kernel, bound, s):
+    """oracle HMCState (flat vectors; mass matrix an array or a block dict) -> the mirror's
+    HMCState pytree (site dicts, mass matrices keyed by site-name tuples)."""
+    from numpyro_b200.infer.hmc import HMCAdaptState, HMCState
+
+    a = s.adapt_state
+    names = [n for n, _, _ in kernel._blocks]
+    as_dict = lambda m: m if isinstance(m, dict) else {names[0]: m}  # noqa: E731
+    mm = a.mm_state if isinstance(a.mm_state, dict) else {names[0]: a.mm_state}
+    f32, i32 = np.float32, np.int32
+    adapt = HMCAdaptState(
+        f32(a.step_size), as_dict(a.inverse_mass_matrix), as_dict(a.mass_matrix_sqrt),
+        as_dict(a.mass_matrix_sqrt_inv),
+        (f32(a.ss_state[0]), f32(a.ss_state[1]), f32(a.ss_state[2]), i32(a.ss_state[3]),
+         f32(a.ss_state[4])),
+        {k: (np.asarray(v[0], f32), np.asarray(v[1], f32), i32(v[2])) for k, v in mm.items()},
+        i32(a.window_idx), np.asarray(a.rng_key, np.uint32))
+    return HMCState(i32(s.i), bound.unravel(s.z), bound.unravel(s.z_grad), f32(s.potential_energy),
+                    f32(s.energy), None, s.trajectory_length, i32(s.num_steps), f32(s.accept_prob),
+                    f32(s.mean_accept_prob), bool(s.diverging), adapt,
+                    np.asarray(s.rng_key, np.uint32))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(rc.CASES))
+def test_cuda_transition_by_transition_from_reference_states(nb, name):
+    """Teacher-forced parity: before EVERY transition the device is handed the reference's
+    state (the oracle's, which reproduces the reference's own code bit for bit, see above),
+    one ``sample`` runs in CUDA, and the result is compared with the reference's next
+    state -- tree size, divergence, position, energies, dual averaging, Welford state and,
+    at window ends, the (block-structured) mass-matrix factorisation.  No chaos: a
+    transition's inputs are identical, so everything must agree to f32 round-off."""
+    from numpyro_b200 import infer
+    from numpyro_b200.random import PRNGKey
+    from oracle import hmc as ohmc
+    from oracle.hmc_util import Config
+
+    fk, algo, kw, seed, nw, ns, part = rc.CASES[name]
+    fam = rc.families(DATA)[fk]
+    ok = ohmc.HMCKernel(fam, algo=algo, cfg=Config(np.float32, part), **kw)
+    s = ok.init(PRNGKey(seed), nw, init_params=G[name + "/z0"])
+    model, args, kwargs = _bind_args(fk)
+    kernel = getattr(infer, algo)(model, **kw)
+    kernel.partitionable = part
+    bound = model.bind(*args, **kwargs)
+    c0 = kernel.init(PRNGKey(seed), nw, init_params=bound.unravel(G[name + "/z0"]),
+                     model_args=args, model_kwargs=kwargs)
+    np.testing.assert_allclose(c0.energy, s.energy, rtol=1e-5)
+    total = nw + ns
+    tree_mismatch, checked = [], 0
+    for t in range(total):
+        nxt = ok.sample(s)
+        c = kernel.sample(_mirror_state(nb, kernel, bound, s), args, kwargs)
+        s = nxt
+        if int(c.num_steps) != int(nxt.num_steps) or bool(c.diverging) != bool(nxt.diverging):
+            tree_mismatch.append(t)  # a U-turn / energy comparison within one ulp of its threshold
+            continue
+        checked += 1
+        ctx = f"{name} transition {t}"
+        np.testing.assert_allclose(bound.ravel(c.z), nxt.z, rtol=2e-3, atol=2e-4, err_msg=ctx)
+        np.testing.assert_allclose(c.potential_energy, nxt.potential_energy, rtol=1e-4, atol=1e-4,
+                                   err_msg=ctx)
+        np.testing.assert_allclose(c.accept_prob, nxt.accept_prob, rtol=2e-3, atol=1e-5, err_msg=ctx)
+        np.testing.assert_allclose(c.mean_accept_prob, nxt.mean_accept_prob, rtol=2e-3, atol=1e-5,
+                                   err_msg=ctx)
+        assert np.array_equal(c.rng_key, np.asarray(nxt.rng_key, np.uint32)), ctx
+        a, b = c.adapt_state, nxt.adapt_state
+        assert int(a.window_idx) == int(b.window_idx), ctx
+        assert np.array_equal(a.rng_key, np.asarray(b.rng_key, np.uint32)), ctx
+        np.testing.assert_allclose(a.step_size, b.step_size, rtol=2e-3, err_msg=ctx)
+        np.testing.assert_allclose(a.ss_state[:3], b.ss_state[:3], rtol=2e-3, atol=1e-4, err_msg=ctx)
+        assert int(a.ss_state[3]) == int(b.ss_state[3]), ctx
+        names = [n for n, _, _ in kernel._blocks]
+        as_dict = lambda m: m if isinstance(m, dict) else {names[0]: m}  # noqa: E731
+        for got, want in ((a.inverse_mass_matrix, b.inverse_mass_matrix),
+                          (a.mass_matrix_sqrt, b.mass_matrix_sqrt),
+                          (a.mass_matrix_sqrt_inv, b.mass_matrix_sqrt_inv)):
+            want = as_dict(want)
+            assert list(got) == list(want), ctx  # same blocks, same (key) order
+            for k in want:
+                scale = np.abs(want[k]).max()
+                np.testing.assert_allclose(got[k], want[k], rtol=2e-3, atol=2e-4 * scale,
+                                           err_msg=f"{ctx} block {k}")
+        mm = b.mm_state if isinstance(b.mm_state, dict) else {names[0]: b.mm_state}
+        for k in mm:
+            assert int(a.mm_state[k][2]) == int(mm[k][2]), ctx
+            np.testing.assert_allclose(a.mm_state[k][0], mm[k][0], rtol=1e-4, atol=1e-5, err_msg=ctx)
+            sc = max(np.abs(mm[k][1]).max(), 1e-6)
+            np.testing.assert_allclose(a.mm_state[k][1], mm[k][1], rtol=1e-3, atol=1e-4 * sc,
+                                       err_msg=ctx)
+    # from identical inputs a tree may still differ when a comparison sits within an ulp of
+    # its threshold; that must stay rare
+    assert len(tree_mismatch) <= max(1, total // 25), (name, tree_mismatch)
+    assert checked >= total - max(1, total // 25)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ADAPT)
+def test_cuda_adaptation_traces_follow_reference_source(nb, name):
+    """Free-running warm-ups are chaotic in f32 (one ulp in a transcendental eventually flips
+    a tree and the runs separate), so this is only a sanity check next to the teacher-forced
+    test above: identical tree sizes over a leading stretch, the reference's block structure,
+    an adapted step size of the same magnitude."""
+    fk, algo, kw, seed, nw, ns, part = rc.CASES[name]
+    res, last = _cuda_trace(nb, name)
+    want = G[name + "/num_steps"]
+    differ = np.nonzero(res["num_steps"] != want)[0]
+    prefix = int(differ[0]) if differ.size else len(want)
+    os.makedirs(os.path.join(os.path.dirname(HERE), "gpurun_out"), exist_ok=True)
+    with open(os.path.join(os.path.dirname(HERE), "gpurun_out", "refpin_gpu.txt"), "a") as fh:
+        fh.write(f"{name} identical_prefix={prefix}/{len(want)} step_size={res['step_size'][-1]:.5f} "
+                 f"ref={float(G[name + '/step_size'][-1]):.5f} mean_tree={res['num_steps'].mean():.2f} "
+                 f"ref={want.mean():.2f}\n")
+    assert prefix >= min(10, len(want)), (name, prefix)
+    p = min(prefix, 4)
+    np.testing.assert_allclose(res["step_size"][:p], G[name + "/step_size"][:p], rtol=1e-2)
+    if kw.get("adapt_step_size", True):
+        ratio = float(res["step_size"][-1]) / float(G[name + "/step_size"][-1])
+        assert 0.25 < ratio < 4.0, (name, ratio)
+    imm = last.adapt_state.inverse_mass_matrix
+    blocks = sorted(str(b) for b in G[name + "/blocks"])
+    assert sorted(rc.block_tag(k) for k in imm) == blocks
+    for k, m in imm.items():
+        ref = G[f"{name}/imm/{rc.block_tag(k)}"]
+        assert np.shape(m) == ref.shape, (name, k)
+    # momentum keys: the order of mass_matrix_sqrt's blocks is the reference's
+    assert [rc.block_tag(k) for k in last.adapt_state.mass_matrix_sqrt] == [str(b) for b in G[name + "/blocks"]] \
+        or len(imm) == 1 or not kw.get("adapt_mass_matrix", True)
