@@ -11,15 +11,23 @@ does: it fails loudly when the CUDA library is missing.
 
 Parity status
 -------------
-* Sampler numerics (adaptation schedule, checkpoint indices, iterative U-turn
-  truth table, Welford regulariser, dual averaging, velocity Verlet,
-  diagnostics known answers): PINNED against the golden vectors held by the
-  reference's own tests (``test/infer/test_hmc_util.py``,
-  ``test/test_diagnostics.py``) -- see ``tests/test_oracle_golden.py``.
-* Threefry-2x32: pinned against the Random123 known-answer vectors and against
-  the values printed in JAX's own documentation.  ``jax``/``jaxlib`` are not
-  vendored under ``/root/reference`` (``setup.py`` pins only ``jax>=0.4.25``)
-  and cannot be imported in the build container, so exact *sample streams*
-  (tier 3) are "parity unpinned" against a live reference run: they are checked
-  CUDA-vs-oracle only.
+* Sampler (everything in ``hmc.py`` and ``hmc_util.py``): PINNED to the reference's OWN
+  source.  ``tests/golden/refshim.py`` executes the unmodified ``numpyro/util.py``,
+  ``numpyro/infer/hmc_util.py``, ``numpyro/infer/hmc.py`` and ``numpyro/diagnostics.py`` from
+  /root/reference over a NumPy stand-in for the slice of JAX they use;
+  ``tests/golden/make_refpin.py`` drives the reference's ``HMC``/``NUTS`` classes through 28
+  cases (fixed parameters, diagonal / dense / block-structured warm-ups, HMC, both Threefry
+  layouts, four model families) and commits the traces as ``tests/golden/refpin.npz``.  The
+  oracle reproduces every field of every transition of every case BIT FOR BIT
+  (``tests/test_refpin.py``).  Not reference code in those runs, and therefore restated:
+  ``jax.random`` (Threefry, below), autodiff (closed-form gradients, checked against finite
+  differences and float64), and the model tracing / init search of ``infer/util.py``.
+* Also pinned against the golden vectors held by the reference's own tests
+  (``test/infer/test_hmc_util.py``, ``test/test_diagnostics.py``): adaptation schedule,
+  checkpoint indices, iterative U-turn truth table, Welford regulariser, dual averaging,
+  velocity Verlet, diagnostics known answers -- ``tests/test_oracle_golden.py``.
+* Threefry-2x32 (third party, ``jax>=0.4.25``, not under /root/reference, not importable
+  here): restated from the published algorithm, pinned against the Random123 known-answer
+  vectors and the values printed in JAX's documentation.  The random STREAMS of a live
+  JAX run are the one thing that stays unpinned.
 """

@@ -51,6 +51,43 @@ def run_case(hmc, util, fam, algo, kwargs, seed, num_warmup, num_samples):
     return res
 
 
+def diagnostics_inputs():
+    """AR(1) chains [4 chains, 300 draws, 3 params] with different autocorrelations, plus a
+    short anti-correlated one."""
+    rng = np.random.default_rng(77)
+    x = np.zeros((4, 300, 3))
+    for j, rho in enumerate((0.0, 0.7, 0.95)):
+        e = rng.normal(size=(4, 300))
+        for t in range(1, 300):
+            x[:, t, j] = rho * x[:, t - 1, j] + e[:, t]
+    x[2] += 0.3  # one shifted chain: r_hat > 1
+    y = np.zeros((2, 64, 2))
+    e = rng.normal(size=(2, 64, 2))
+    for t in range(1, 64):
+        y[:, t] = -0.5 * y[:, t - 1] + e[:, t]
+    return {"ar": x, "anti": y}
+
+
+def diagnostics_fixture():
+    """Known answers from the reference's own numpyro/diagnostics.py (executed unmodified)."""
+    D = refshim.load_diagnostics()
+    out = {}
+    for name, x in diagnostics_inputs().items():
+        out[f"diag/{name}/x"] = x
+        out[f"diag/{name}/gelman_rubin"] = np.asarray(D.gelman_rubin(x))
+        out[f"diag/{name}/split_gelman_rubin"] = np.asarray(D.split_gelman_rubin(x))
+        out[f"diag/{name}/autocorrelation"] = np.asarray(D.autocorrelation(x, axis=1))
+        out[f"diag/{name}/autocorrelation_unbiased"] = np.asarray(D.autocorrelation(x, axis=1, bias=False))
+        out[f"diag/{name}/autocovariance"] = np.asarray(D.autocovariance(x, axis=1))
+        out[f"diag/{name}/ess"] = np.asarray(D.effective_sample_size(x))
+        out[f"diag/{name}/ess_unbiased"] = np.asarray(D.effective_sample_size(x, bias=False))
+        out[f"diag/{name}/hpdi"] = np.asarray(D.hpdi(x.reshape(-1, x.shape[-1]), 0.9))
+        s = D.summary({"p": x}, prob=0.9, group_by_chain=True)["p"]
+        for k, v in s.items():
+            out[f"diag/{name}/summary/{k}"] = np.asarray(v)
+    return out
+
+
 def main():
     data = rc.make_data()
     fams = rc.families(data)
@@ -66,6 +103,7 @@ def main():
             print(f"{name:28s} grad evals {int(res['grad_evals']):6d}  mean tree "
                   f"{res['num_steps'].mean():7.2f}  step {float(res['step_size'][-1]):.4f}  "
                   f"diverging {int(res['diverging'].sum())}")
+    out.update(diagnostics_fixture())
     np.savez_compressed(os.path.join(HERE, "refpin.npz"), **out)
     print("wrote refpin.npz", os.path.getsize(os.path.join(HERE, "refpin.npz")), "bytes")
 

@@ -9,6 +9,7 @@ the ``jax`` API.  ``install()`` puts a NumPy-backed stand-in for that slice into
     /root/reference/numpyro/util.py
     /root/reference/numpyro/infer/hmc_util.py
     /root/reference/numpyro/infer/hmc.py
+    /root/reference/numpyro/diagnostics.py        (``load_diagnostics()``)
 
 as ``numpyro.util`` / ``numpyro.infer.hmc_util`` / ``numpyro.infer.hmc``.  What is NOT the
 reference's code in such a run:
@@ -514,3 +515,12 @@ def install(partitionable=True):
     hmc = _load("numpyro.infer.hmc", os.path.join(root, "infer", "hmc.py"))
     infer.hmc = hmc
     return hmc, hmc_util, util
+
+
+def load_diagnostics():
+    """The reference's ``numpyro/diagnostics.py`` (NumPy arithmetic; it only touches
+    ``jax.device_get`` and ``jax.tree``), executed unmodified."""
+    install(PARTITIONABLE)
+    if "numpyro.diagnostics" not in sys.modules:
+        _load("numpyro.diagnostics", os.path.join(REFERENCE, "numpyro", "diagnostics.py"))
+    return sys.modules["numpyro.diagnostics"]

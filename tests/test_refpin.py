@@ -92,6 +92,34 @@ def test_fixture_regenerates_from_the_reference_source(name):
         assert np.array_equal(res[f], G[f"{name}/{f}"], equal_nan=True), (name, f)
 
 
+@pytest.mark.parametrize("which", ["oracle", "product"])
+@pytest.mark.parametrize("name", ["ar", "anti"])
+def test_diagnostics_match_reference_source(which, name):
+    """Known answers computed by the reference's own ``numpyro/diagnostics.py``: the oracle's
+    restatement and the shipped ``numpyro_b200.diagnostics`` (NumPy host code, used for the
+    ESS/s metric) reproduce them."""
+    if which == "oracle":
+        from oracle import diagnostics as D
+    else:
+        from numpyro_b200 import diagnostics as D
+    x = G[f"diag/{name}/x"]
+    tol = dict(rtol=1e-9, atol=1e-10)
+    np.testing.assert_allclose(D.gelman_rubin(x), G[f"diag/{name}/gelman_rubin"], **tol)
+    np.testing.assert_allclose(D.split_gelman_rubin(x), G[f"diag/{name}/split_gelman_rubin"], **tol)
+    np.testing.assert_allclose(D.autocorrelation(x, axis=1), G[f"diag/{name}/autocorrelation"], **tol)
+    np.testing.assert_allclose(D.autocorrelation(x, axis=1, bias=False),
+                               G[f"diag/{name}/autocorrelation_unbiased"], **tol)
+    np.testing.assert_allclose(D.autocovariance(x, axis=1), G[f"diag/{name}/autocovariance"], **tol)
+    np.testing.assert_allclose(D.effective_sample_size(x), G[f"diag/{name}/ess"], **tol)
+    np.testing.assert_allclose(D.effective_sample_size(x, bias=False),
+                               G[f"diag/{name}/ess_unbiased"], **tol)
+    if which == "product":
+        np.testing.assert_allclose(D.hpdi(x.reshape(-1, x.shape[-1]), 0.9), G[f"diag/{name}/hpdi"], **tol)
+        s = D.summary({"p": x}, prob=0.9, group_by_chain=True)["p"]
+        for k in ("mean", "std", "median", "5.0%", "95.0%", "n_eff", "r_hat"):
+            np.testing.assert_allclose(s[k], G[f"diag/{name}/summary/{k}"], **tol, err_msg=k)
+
+
 # ------------------------------------------------------------------------------- GPU
 @pytest.fixture(scope="module")
 def nb():
