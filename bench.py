@@ -64,12 +64,12 @@ class ClockSampler:
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index):
+    def __init__(self, index, period_ms=100):
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         self.p = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
-                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                       "--format=csv,noheader,nounits", "-lms", str(period_ms)],
                                       stdout=self.f, stderr=subprocess.DEVNULL)
         except OSError:
             pass
@@ -350,7 +350,15 @@ def run_own(args):
 
     # ---- end-to-end leg: public API (MCMC.run) with HOST buffers every step: X, y are
     #      copied host->device inside the timed region, draws are read back
-    e2e_grads, e2e_s = 0, 0.0
+    # (the clock sampler of the device leg is stopped first: nvidia-smi's start-up and its NVML
+    #  queries take driver locks that the many small driver calls of THIS leg wait on -- host
+    #  stalls of 50-200 ms per step were measured with it running; the device leg is timed with
+    #  CUDA events and does not see them)
+    clk = clocks.stop() if clocks is not None else None
+    clocks = None
+    if os.environ.get("B200MC_BENCH_E2E_SAMPLER"):
+        clocks = ClockSampler(local, 1000) if rank == 0 else None
+    e2e_grads, e2e_s, e2e_ms = 0, 0.0, []
     z_last = {k: np.asarray(v) for k, v in kern._last_state.z.items()}
     barrier()
     for i in range(args.warmup + args.steps):
@@ -367,13 +375,23 @@ def run_own(args):
         if i >= args.warmup:
             e2e_grads += int(ns.sum())
             e2e_s += dt
+            e2e_ms.append(round(dt * 1e3, 3))
     barrier()
     e2e_s = max_over_ranks(e2e_s)
     e2e_grads = float(e2e_grads) if rows else sum_over_ranks(float(e2e_grads))
     e2e = {"value": e2e_grads / e2e_s, "unit": UNIT,
            "h2d_bytes_per_step": int(X.nbytes + y.nbytes + 4 * N_COLS * 2 + 8),
-           "d2h_bytes_per_step": int(T_ * (N_COLS * 4 + 4 + 4))}
-    clk = clocks.stop() if clocks is not None else None
+           "d2h_bytes_per_step": int(T_ * (N_COLS * 4 + 4 + 4)),
+           "ms_per_step": e2e_ms, "grad_evals_per_step": e2e_grads / max(1, len(e2e_ms))}
+    clk2 = clocks.stop() if clocks is not None else None
+    if clk is not None and clk2 is None and rank == 0:
+        # one reading right after the leg (never concurrently with it, see above)
+        probe = ClockSampler(local, 100)
+        time.sleep(0.35)
+        clk2 = probe.stop()
+    if clk is not None and clk2 is not None:
+        clk["e2e_leg"] = clk2
+        clk["reasons"] = sorted(set(clk["reasons"]) | set(clk2["reasons"]))
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:

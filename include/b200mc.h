@@ -203,8 +203,13 @@ int b200mc_adaptation_schedule(int num_steps, int* starts_host, int* ends_host, 
 /* Device-memory plumbing so a host binding needs nothing but this library. */
 int b200mc_device_count(void);
 int b200mc_set_device(int device);
+/* b200mc_malloc / b200mc_free (and the handle's own buffers) go through a caching allocator:
+ * freed blocks are kept and reused on an exact-size match (B200MC_POOL_BYTES caps the cache,
+ * 0 disables it); free a buffer only after the work that uses it has been waited for.
+ * b200mc_pool_trim returns every cached block to the driver. */
 void* b200mc_malloc(uint64_t bytes);
 int b200mc_free(void* p_dev);
+int b200mc_pool_trim(void);
 int b200mc_memcpy_h2d(void* dst_dev, const void* src_host, uint64_t bytes, void* stream);
 int b200mc_memcpy_d2h(void* dst_host, const void* src_dev, uint64_t bytes, void* stream);
 int b200mc_memset(void* dst_dev, int value, uint64_t bytes, void* stream);

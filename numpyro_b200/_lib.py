@@ -95,6 +95,7 @@ SYMBOLS = {
     "b200mc_set_device": (_i, [_i]),
     "b200mc_malloc": (_vp, [_u64]),
     "b200mc_free": (_i, [_vp]),
+    "b200mc_pool_trim": (_i, []),
     "b200mc_memcpy_h2d": (_i, [_vp, _vp, _u64, _vp]),
     "b200mc_memcpy_d2h": (_i, [_vp, _vp, _u64, _vp]),
     "b200mc_memset": (_i, [_vp, _i, _u64, _vp]),

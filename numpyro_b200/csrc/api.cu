@@ -6,6 +6,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
+#include <mutex>
+#include <unordered_map>
 #include <string>
 #include <vector>
 
@@ -169,6 +172,98 @@ static int family_sites(const b200mc_config& c, SamplerParams& P, int& D) {
 __global__ void labels_to_float_kernel(const uint8_t* y, int n, float* out) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[i] = (float)y[i];
 }
+// Caching device allocator.  cudaMalloc / cudaFree of a 128 MB buffer cost ~5-10 ms each (the
+// free also synchronises the device) -- more than the H2D copy of the design matrix itself --
+// and the end-to-end path creates a handle per MCMC.run.  Freed blocks are therefore kept in
+// per-device free lists keyed by their (512-byte rounded) size and handed out again on an
+// exact-size match; the same shapes come back run after run.  Blocks go back to the lists only
+// from b200mc_destroy (after a device synchronise) and b200mc_free (the Python mirror frees a
+// buffer only after the copy or kernel that used it has been waited for), so a cached block
+// has no work in flight.  B200MC_POOL_BYTES caps the cached bytes (default 16 GiB, 0 = off).
+namespace {
+struct DevicePool {
+  std::mutex mu;
+  std::unordered_map<void*, std::pair<int, size_t>> live;   // ptr -> (device, rounded bytes)
+  std::multimap<std::pair<int, size_t>, void*> cached;
+  size_t cached_bytes = 0;
+  size_t cap = (size_t)16 << 30;
+  DevicePool() {
+    if (const char* e = getenv("B200MC_POOL_BYTES")) cap = (size_t)strtoull(e, nullptr, 10);
+  }
+};
+DevicePool& pool() {
+  static DevicePool* p = new DevicePool();  // never destroyed: no frees after the driver is gone
+  return *p;
+}
+}  // namespace
+static cudaError_t dmalloc(void** p, size_t bytes) {
+  bytes = (bytes + 511) & ~(size_t)511;
+  if (bytes == 0) bytes = 512;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  DevicePool& P = pool();
+  {
+    std::lock_guard<std::mutex> lk(P.mu);
+    auto it = P.cached.find({dev, bytes});
+    if (it != P.cached.end()) {
+      *p = it->second;
+      P.cached.erase(it);
+      P.cached_bytes -= bytes;
+      P.live[*p] = {dev, bytes};
+      return cudaSuccess;
+    }
+  }
+  cudaError_t e = cudaMalloc(p, bytes);
+  if (e != cudaSuccess) {  // out of memory: give the cached blocks back and retry once
+    cudaGetLastError();
+    std::vector<void*> drop;
+    {
+      std::lock_guard<std::mutex> lk(P.mu);
+      for (auto& kv : P.cached) drop.push_back(kv.second);
+      P.cached.clear();
+      P.cached_bytes = 0;
+    }
+    for (void* q : drop) cudaFree(q);
+    e = cudaMalloc(p, bytes);
+  }
+  if (e == cudaSuccess) {
+    std::lock_guard<std::mutex> lk(P.mu);
+    P.live[*p] = {dev, bytes};
+  }
+  return e;
+}
+static void dfree(void* p) {
+  if (!p) return;
+  DevicePool& P = pool();
+  {
+    std::lock_guard<std::mutex> lk(P.mu);
+    auto it = P.live.find(p);
+    if (it != P.live.end()) {
+      const auto key = it->second;
+      P.live.erase(it);
+      if (P.cached_bytes + key.second <= P.cap) {
+        P.cached.insert({key, p});
+        P.cached_bytes += key.second;
+        return;
+      }
+    }
+  }
+  cudaFree(p);
+}
+extern "C" int b200mc_pool_trim(void) {
+  DevicePool& P = pool();
+  std::vector<void*> drop;
+  {
+    std::lock_guard<std::mutex> lk(P.mu);
+    for (auto& kv : P.cached) drop.push_back(kv.second);
+    P.cached.clear();
+    P.cached_bytes = 0;
+  }
+  cudaDeviceSynchronize();
+  for (void* q : drop) cudaFree(q);
+  return 0;
+}
+
 namespace {
 __global__ void sum_splits_kernel(const float* part, int splits, int Nc, int RA, int M, float* out) {
   const long total = (long)Nc * M;
@@ -182,8 +277,8 @@ __global__ void sum_splits_kernel(const float* part, int splits, int Nc, int RA,
 int build_image(const float* src, int R_src, int K_src, int transpose, int R, int K,
                 unsigned char** hi, unsigned char** lo, cudaStream_t st) {
   const size_t bytes = (size_t)R * K * 4;
-  CK(cudaMalloc((void**)hi, bytes));
-  CK(cudaMalloc((void**)lo, bytes));
+  CK(dmalloc((void**)hi, bytes));
+  CK(dmalloc((void**)lo, bytes));
   image_build_kernel<<<1184, 256, 0, st>>>(src, R_src, K_src, transpose, R, K, *hi, *lo);
   g_launches++;
   CK(cudaGetLastError());
@@ -196,7 +291,24 @@ int launch_gemm3x(const Gemm3xLaunch& L, int epi, cudaStream_t st) {
     CK(cudaFuncSetAttribute(gemm3x_kernel<EPI_RESID>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
     attr_set = true;
   }
+  static int persist = -1, sms = 0;
+  if (persist < 0) {
+    const char* e = getenv("B200MC_GEMM_PERSIST");
+    persist = e ? atoi(e) : 1;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    CK(cudaFuncSetAttribute(gemm3x_resid_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPersistSmem));
+  }
   const int grid = (L.RA / kGemmM) * L.splits;
+  if (epi == EPI_RESID && persist && L.KB <= kPersistMaxKB && L.splits == 1) {
+    // short inner dimension (logistic: K = 64): persistent CTAs, B resident, TMEM double-buffered
+    const int pgrid = grid < sms ? grid : sms;
+    gemm3x_resid_persistent_kernel<<<pgrid, kGemmThreads, kPersistSmem, st>>>(L);
+    g_launches++;
+    CK(cudaGetLastError());
+    return 0;
+  }
   if (epi == EPI_STORE) gemm3x_kernel<EPI_STORE><<<grid, kGemmThreads, kGemmSmem, st>>>(L);
   else gemm3x_kernel<EPI_RESID><<<grid, kGemmThreads, kGemmSmem, st>>>(L);
   g_launches++;
@@ -208,22 +320,23 @@ int launch_gemm3x(const Gemm3xLaunch& L, int epi, cudaStream_t st) {
 extern "C" void b200mc_destroy(b200mc_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->cs);
-  cudaFree(h->cv.z); cudaFree(h->cv.z_grad); cudaFree(h->cv.inverse_mass_matrix);
-  cudaFree(h->cv.mass_matrix_sqrt); cudaFree(h->cv.welford_mean); cudaFree(h->cv.welford_m2);
-  cudaFree(h->work); cudaFree(h->partials); cudaFree(h->counters); cudaFree(h->prof); cudaFree(h->glm_xt);
-  cudaFree(h->cv.dense); cudaFree(h->dense_replicas); cudaFree(h->M.scratch);
-  cudaFree(h->blk_tables);
+  cudaDeviceSynchronize();  // nothing of this handle is in flight when its blocks are recycled
+  dfree(h->cs);
+  dfree(h->cv.z); dfree(h->cv.z_grad); dfree(h->cv.inverse_mass_matrix);
+  dfree(h->cv.mass_matrix_sqrt); dfree(h->cv.welford_mean); dfree(h->cv.welford_m2);
+  dfree(h->work); dfree(h->partials); dfree(h->counters); dfree(h->prof); dfree(h->glm_xt);
+  dfree(h->cv.dense); dfree(h->dense_replicas); dfree(h->M.scratch);
+  dfree(h->blk_tables);
   for (int r = 0; r < h->nranks; ++r) {
     if (r == h->rank) continue;
     if (h->xchg[r]) cudaIpcCloseMemHandle(h->xchg[r]);
     if (h->xarrive[r]) cudaIpcCloseMemHandle(h->xarrive[r]);
   }
   cudaFree(h->xchg_local); cudaFree(h->xarrive_local);
-  cudaFree(h->bt.x_hi); cudaFree(h->bt.x_lo); cudaFree(h->bt.xt_hi); cudaFree(h->bt.xt_lo);
-  cudaFree(h->bt.b_hi); cudaFree(h->bt.b_lo); cudaFree(h->bt.r_hi); cudaFree(h->bt.r_lo);
-  cudaFree(h->bt.ll_part); cudaFree(h->bt.gpart); cudaFree(h->bt.col_scale);
-  cudaFree(h->bt.snap); cudaFree(h->bt.status); cudaFree(h->bt.active); cudaFree(h->bt.reqs); cudaFree(h->bt.y_f32);
+  dfree(h->bt.x_hi); dfree(h->bt.x_lo); dfree(h->bt.xt_hi); dfree(h->bt.xt_lo);
+  dfree(h->bt.b_hi); dfree(h->bt.b_lo); dfree(h->bt.r_hi); dfree(h->bt.r_lo);
+  dfree(h->bt.ll_part); dfree(h->bt.gpart); dfree(h->bt.col_scale);
+  dfree(h->bt.snap); dfree(h->bt.status); dfree(h->bt.active); dfree(h->bt.reqs); dfree(h->bt.y_f32);
   delete h;
 }
 
@@ -298,6 +411,11 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
 
   const size_t vec_bytes = (size_t)C * D * sizeof(float);
   auto alloc = [&](void** p, size_t bytes) {
+    cudaError_t e = dmalloc(p, bytes);
+    if (e == cudaSuccess) e = cudaMemset(*p, 0, bytes);
+    return e;
+  };
+  auto alloc_ipc = [&](void** p, size_t bytes) {  // cudaIpcGetMemHandle needs cudaMalloc memory
     cudaError_t e = cudaMalloc(p, bytes);
     if (e == cudaSuccess) e = cudaMemset(*p, 0, bytes);
     return e;
@@ -344,7 +462,7 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
     if ((any_dense != 0) != (c.dense_mass != 0)) {
       b200mc_destroy(h); return fail("dense_mass must be set iff a block is dense");
     }
-    ACK(cudaMalloc((void**)&h->blk_tables, t.size() * sizeof(int)));
+    ACK(dmalloc((void**)&h->blk_tables, t.size() * sizeof(int)));
     ACK(cudaMemcpy(h->blk_tables, t.data(), t.size() * sizeof(int), cudaMemcpyHostToDevice));
     P.num_blocks = nb;
     P.blk_of = h->blk_tables; P.blk_pos = P.blk_of + D; P.blk_perm = P.blk_pos + D;
@@ -366,7 +484,7 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
     // referenced after b200mc_create returns.
     const int nt_total = (c.N + kGlmTileRows - 1) / kGlmTileRows;
     h->glm_nt_total = nt_total;
-    ACK(cudaMalloc((void**)&h->glm_xt, (size_t)nt_total * glm_tile_bytes(D)));
+    ACK(dmalloc((void**)&h->glm_xt, (size_t)nt_total * glm_tile_bytes(D)));
     glm_retile_kernel<<<h->num_sms * 8, 256>>>((const float*)c.data0_dev,
                                                 (const uint8_t*)c.data1_dev, c.N, D, nt_total,
                                                 h->glm_xt);
@@ -427,9 +545,9 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
     }
     if (h->nranks > 1) {
       if (C != 1) { b200mc_destroy(h); return fail("row sharding runs one chain per handle"); }
-      ACK(alloc((void**)&h->xchg_local,
+      ACK(alloc_ipc((void**)&h->xchg_local,
                 sizeof(float) * 2 * 2 * (size_t)h->nranks * glm_partial_stride(D)));
-      ACK(alloc((void**)&h->xarrive_local, sizeof(unsigned) * 4));
+      ACK(alloc_ipc((void**)&h->xarrive_local, sizeof(unsigned) * 4));
     }
   } else {
     if (c.family == B200MC_HORSESHOE) {
@@ -1090,15 +1208,15 @@ extern "C" int b200mc_set_device(int device) {
 }
 extern "C" void* b200mc_malloc(uint64_t bytes) {
   void* p = nullptr;
-  if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) {
-    fail("cudaMalloc(%llu) failed: %s", (unsigned long long)bytes,
+  if (dmalloc(&p, bytes) != cudaSuccess) {
+    fail("device allocation of %llu bytes failed: %s", (unsigned long long)bytes,
          cudaGetErrorString(cudaGetLastError()));
     return nullptr;
   }
   return p;
 }
 extern "C" int b200mc_free(void* p) {
-  CK(cudaFree(p));
+  dfree(p);
   return 0;
 }
 extern "C" int b200mc_memcpy_h2d(void* dst, const void* src, uint64_t bytes, void* stream) {

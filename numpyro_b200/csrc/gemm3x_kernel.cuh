@@ -41,6 +41,25 @@ constexpr int kGemmSmem = kGemmStages * kGemmStageBytes + 1024 /*align*/ + 256 /
 
 enum GemmEpilogue { EPI_STORE = 0, EPI_RESID = 1 };
 
+// binary_cross_entropy_with_logits (distributions/util.py:295-298) and its derivative for ONE
+// (row, chain) element of the residual epilogue, on the special-function unit only: three MUFU
+// ops (ex2, rcp, lg2) and no libdevice slow paths -- the epilogue runs once per element of the
+// N x C linear predictor and is the bound of the whole contraction.  Every intermediate lies
+// in [0, 2], so the approximations' errors are ABSOLUTE errors of ~1e-7 on quantities of
+// order 1 (e = exp(-|l|) <= 1, 1 + e in [1, 2], log1p(e) <= ln 2): the same size as the f32
+// round-off of the exact formula and far inside tier 2 (rtol 1e-5 on U and grad U).
+__device__ __forceinline__ void bce_logits_fast(float l, float y, float& term, float& res) {
+  float e, inv, lg;
+  const float t = fabsf(l) * -1.4426950408889634f;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
+  const float d = 1.0f + e;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(d));
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(d));
+  inv = fmaf(inv, fmaf(-d, inv, 1.0f), inv);  // one Newton step: sigmoid to <= 1 ulp
+  term = fmaf(lg, 0.6931471805599453f, fmaxf(l, 0.f)) - l * y;
+  res = ((l >= 0.f) ? inv : e * inv) - y;
+}
+
 struct Gemm3xLaunch {
   const unsigned char *a_hi, *a_lo;  // images of A [RA][32*KB]
   const unsigned char *b_hi, *b_lo;  // images of B [256][32*KB]
@@ -171,10 +190,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm3x_kernel(const __grid_co
               term = r * r;
               res = -(L.col_scale[c] * r);
             } else {
-              const float e = expf(-fabsf(l));
-              const float inv = rcp_1to2(1.0f + e);
-              term = (fmaxf(l, 0.f) + log1pf(e)) - l * yv;
-              res = ((l >= 0.f) ? inv : e * inv) - yv;
+              bce_logits_fast(l, yv, term, res);
             }
           }
           float hi, lo;
@@ -196,6 +212,180 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm3x_kernel(const __grid_co
   if (warp == 1) {
     umma::fence_after_sync();
     umma::tmem_dealloc(tmem, kGemmN);
+  }
+}
+
+// ---------------------------------------------------------------- persistent residual GEMM
+// Same contraction + residual epilogue as gemm3x_kernel<EPI_RESID>, for a SHORT inner dimension
+// (KB <= kPersistMaxKB k-blocks: the logistic design matrix has K = 64): one CTA per SM walks
+// the row tiles mt = blockIdx.x, blockIdx.x + gridDim.x, ...
+//   * B (the 256 coefficient rows, hi + lo) is loaded ONCE and stays in shared memory (128 KB);
+//   * A streams through a 3-stage ring of k-blocks (32 KB each, hi + lo);
+//   * the accumulator is double-buffered in TMEM (2 x 256 columns = the whole 512): the MMAs of
+//     tile i + 1 run while the 16 epilogue warps drain tile i, so loads, tensor-core work and
+//     the transcendental-bound epilogue overlap instead of running back to back per CTA.
+constexpr int kPersistMaxKB = 2;
+constexpr int kPersistStages = 3;
+constexpr int kPersistABytes = 2 * kGemmABytes;                      // one k-block of A, hi + lo
+constexpr int kPersistBBytes = kPersistMaxKB * 2 * kGemmBBytes;      // all of B, hi + lo
+constexpr int kPersistSmem = kPersistBBytes + kPersistStages * kPersistABytes + 1024 + 256;
+constexpr int kPersistEpiWarps = 4 * kGemmEpiGroups;
+
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm3x_resid_persistent_kernel(const __grid_constant__ Gemm3xLaunch L) {
+  extern __shared__ unsigned char gsm_raw[];
+  unsigned char* gsm = reinterpret_cast<unsigned char*>(((uintptr_t)gsm_raw + 1023) & ~(uintptr_t)1023);
+  unsigned char* smB = gsm;
+  unsigned char* smA = gsm + kPersistBBytes;
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(smA + kPersistStages * kPersistABytes);
+  uint64_t* a_empty = a_full + kPersistStages;
+  uint64_t* acc_full = a_empty + kPersistStages;  // [2]
+  uint64_t* acc_empty = acc_full + 2;             // [2]
+  uint64_t* b_full = acc_empty + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(b_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tiles = L.RA / kGemmM;
+  const int KB = L.KB;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kPersistStages; ++s) {
+      mbar_init(&a_full[s], 1);
+      mbar_init(&a_empty[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&acc_full[b], 1);
+      mbar_init(&acc_empty[b], kPersistEpiWarps);
+    }
+    mbar_init(b_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) umma::tmem_alloc(tmem_slot, 2 * kGemmN);
+  umma::fence_before_sync();
+  __syncthreads();
+  umma::fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    // ---------------- producer
+    if (lane == 0) {
+      mbar_arrive_expect_tx(b_full, (uint32_t)(KB * 2 * kGemmBBytes));
+      for (int kb = 0; kb < KB; ++kb) {
+        const long bo = (long)kb * (kGemmN >> 3) * umma::kAtomBytes;
+        tma_load_1d(smB + (long)kb * 2 * kGemmBBytes, L.b_hi + bo, kGemmBBytes, b_full);
+        tma_load_1d(smB + (long)kb * 2 * kGemmBBytes + kGemmBBytes, L.b_lo + bo, kGemmBBytes, b_full);
+      }
+      const long a_rowgroups = L.RA >> 3;
+      int it = 0;
+      for (int mt = blockIdx.x; mt < n_tiles; mt += gridDim.x) {
+        for (int kb = 0; kb < KB; ++kb, ++it) {
+          const int s = it % kPersistStages;
+          const uint32_t n = (uint32_t)(it / kPersistStages);
+          mbar_wait(&a_empty[s], (n & 1u) ^ 1u);
+          unsigned char* st = smA + (long)s * kPersistABytes;
+          mbar_arrive_expect_tx(&a_full[s], (uint32_t)kPersistABytes);
+          const long ao = ((long)kb * a_rowgroups + (long)mt * (kGemmM >> 3)) * umma::kAtomBytes;
+          tma_load_1d(st, L.a_hi + ao, kGemmABytes, &a_full[s]);
+          tma_load_1d(st + kGemmABytes, L.a_lo + ao, kGemmABytes, &a_full[s]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------- MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma::make_idesc_tf32(kGemmM, kGemmN);
+      mbar_wait(b_full, 0u);
+      umma::fence_after_sync();
+      const uint32_t sb = umma::smem_addr(smB);
+      int it = 0, i = 0;
+      for (int mt = blockIdx.x; mt < n_tiles; mt += gridDim.x, ++i) {
+        const int buf = i & 1;
+        const uint32_t u = (uint32_t)(i >> 1);
+        mbar_wait(&acc_empty[buf], (u & 1u) ^ 1u);  // the epilogue has drained this accumulator
+        umma::fence_after_sync();
+        const uint32_t d_tmem = tmem + (uint32_t)(buf * kGemmN);
+        for (int kb = 0; kb < KB; ++kb, ++it) {
+          const int s = it % kPersistStages;
+          const uint32_t n = (uint32_t)(it / kPersistStages);
+          mbar_wait(&a_full[s], n & 1u);
+          umma::fence_after_sync();
+          const uint32_t sa = umma::smem_addr(smA + (long)s * kPersistABytes);
+          const uint64_t a_hi = umma::make_desc_k_sw128(sa);
+          const uint64_t a_lo = umma::make_desc_k_sw128(sa + kGemmABytes);
+          const uint64_t b_hi = umma::make_desc_k_sw128(sb + (uint32_t)(kb * 2 * kGemmBBytes));
+          const uint64_t b_lo = umma::make_desc_k_sw128(sb + (uint32_t)(kb * 2 * kGemmBBytes + kGemmBBytes));
+#pragma unroll
+          for (int k = 0; k < umma::kBlockK / 8; ++k) {
+            const uint64_t adv = (uint64_t)(k * 2);
+            umma::mma_tf32(d_tmem, a_lo + adv, b_hi + adv, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            umma::mma_tf32(d_tmem, a_hi + adv, b_lo + adv, idesc, 1u);
+            umma::mma_tf32(d_tmem, a_hi + adv, b_hi + adv, idesc, 1u);
+          }
+          umma::mma_commit(&a_empty[s]);
+        }
+        umma::mma_commit(&acc_full[buf]);
+      }
+    }
+  } else {
+    // ---------------- epilogue: warp w may touch TMEM lanes 32 * (w % 4) ..
+    const int q = warp & 3;
+    const int c_begin = ((warp - 2) >> 2) * (kGemmN / kGemmEpiGroups), c_end = c_begin + kGemmN / kGemmEpiGroups;
+    int i = 0;
+    for (int mt = blockIdx.x; mt < n_tiles; mt += gridDim.x, ++i) {
+      const int buf = i & 1;
+      const uint32_t u = (uint32_t)(i >> 1);
+      const int m = mt * kGemmM + q * 32 + lane;  // this thread's row of A
+      const bool valid = m < L.n_valid;
+      const float yv = valid ? L.y[m] : 0.f;
+      const long kbR = m >> 5;
+      unsigned char* rh = L.r_hi + kbR * (kGemmN >> 3) * umma::kAtomBytes;
+      unsigned char* rl = L.r_lo + kbR * (kGemmN >> 3) * umma::kAtomBytes;
+      float* llp = L.ll_part + kbR * kGemmN;
+      mbar_wait(&acc_full[buf], u & 1u);
+      umma::fence_after_sync();
+      const uint32_t trow = tmem + (uint32_t)(buf * kGemmN) + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+      for (int c0 = c_begin; c0 < c_end; c0 += 32) {
+        uint32_t v[32];
+        umma::tmem_ld32(trow + c0, v);
+        umma::tmem_ld_wait();
+        float part[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int c = c0 + j;
+          const float l = __uint_as_float(v[j]);
+          float res = 0.f, term = 0.f;
+          if (valid) {
+            if (L.likelihood == 1) {
+              const float r = yv - l;
+              term = r * r;
+              res = -(L.col_scale[c] * r);
+            } else {
+              bce_logits_fast(l, yv, term, res);
+            }
+          }
+          float hi, lo;
+          umma::split_tf32(res, hi, lo);
+          const long off = (long)(c >> 3) * umma::kAtomBytes + (c & 7) * 128 +
+                           (((lane >> 2) ^ (c & 7)) << 4) + ((lane & 3) << 2);
+          *reinterpret_cast<float*>(rh + off) = hi;
+          *reinterpret_cast<float*>(rl + off) = lo;
+          part[j] = term;
+        }
+        const float tot = warp_transpose_reduce32(part);
+        llp[c0 + lane] = tot;
+      }
+      // this warp is done reading the accumulator: hand it back to the MMA issuer
+      umma::fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
+    }
+  }
+  umma::fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    umma::fence_after_sync();
+    umma::tmem_dealloc(tmem, 2 * kGemmN);
   }
 }
 
