@@ -1,7 +1,7 @@
 # many-chain logistic: correctness of the persistent residual GEMM, then timing A/B, then launch list
 python -m pytest tests/test_gpu_batch_engine.py tests/test_gpu_gemm.py -m gpu -q -x > gpurun_out/lm_tests.log 2>&1; tail -3 gpurun_out/lm_tests.log
-B200MC_GEMM_PERSIST=0 timeout 300 python bench.py --workload logistic_many --chains 256 --steps 3 --warmup 3 --no-cpu > gpurun_out/lm_old.json 2> gpurun_out/lm_old.err; tail -c 400 gpurun_out/lm_old.err
-timeout 300 python bench.py --workload logistic_many --chains 256 --steps 3 --warmup 3 --no-cpu > gpurun_out/lm_new.json 2> gpurun_out/lm_new.err; tail -c 400 gpurun_out/lm_new.err
+B200MC_GEMM_PERSIST=0 timeout 300 python bench.py --workload logistic_many --chains 256 --steps 5 --warmup 3 --no-cpu > gpurun_out/lm_old.json 2> gpurun_out/lm_old.err; tail -c 400 gpurun_out/lm_old.err
+timeout 300 python bench.py --workload logistic_many --chains 256 --steps 5 --warmup 3 --no-cpu > gpurun_out/lm_new.json 2> gpurun_out/lm_new.err; tail -c 400 gpurun_out/lm_new.err
 python - <<PY
 import json
 for f in ("lm_old","lm_new"):

@@ -298,13 +298,15 @@ int launch_gemm3x(const Gemm3xLaunch& L, int epi, cudaStream_t st) {
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    CK(cudaFuncSetAttribute(gemm3x_resid_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPersistSmem));
+    CK(cudaFuncSetAttribute(gemm3x_resid_persistent_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPersistSmem));
+    CK(cudaFuncSetAttribute(gemm3x_resid_persistent_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPersistSmem));
   }
   const int grid = (L.RA / kGemmM) * L.splits;
   if (epi == EPI_RESID && persist && L.KB <= kPersistMaxKB && L.splits == 1) {
     // short inner dimension (logistic: K = 64): persistent CTAs, B resident, TMEM double-buffered
     const int pgrid = grid < sms ? grid : sms;
-    gemm3x_resid_persistent_kernel<<<pgrid, kGemmThreads, kPersistSmem, st>>>(L);
+    if (L.likelihood == 1) gemm3x_resid_persistent_kernel<1><<<pgrid, kGemmThreads, kPersistSmem, st>>>(L);
+    else gemm3x_resid_persistent_kernel<0><<<pgrid, kGemmThreads, kPersistSmem, st>>>(L);
     g_launches++;
     CK(cudaGetLastError());
     return 0;

@@ -55,8 +55,8 @@ __device__ __forceinline__ void bce_logits_fast(float l, float y, float& term, f
   const float d = 1.0f + e;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(d));
   asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(d));
-  inv = fmaf(inv, fmaf(-d, inv, 1.0f), inv);  // one Newton step: sigmoid to <= 1 ulp
-  term = fmaf(lg, 0.6931471805599453f, fmaxf(l, 0.f)) - l * y;
+  // (rcp.approx is good to 1 ulp on [1, 2]: no Newton step)
+  term = fmaf(-l, y, fmaf(lg, 0.6931471805599453f, fmaxf(l, 0.f)));
   res = ((l >= 0.f) ? inv : e * inv) - y;
 }
 
@@ -231,6 +231,43 @@ constexpr int kPersistBBytes = kPersistMaxKB * 2 * kGemmBBytes;      // all of B
 constexpr int kPersistSmem = kPersistBBytes + kPersistStages * kPersistABytes + 1024 + 256;
 constexpr int kPersistEpiWarps = 4 * kGemmEpiGroups;
 
+// One 32-column chunk of the residual epilogue for this thread's row: v = the linear predictor
+// of 32 chains.  LIK: 0 Bernoulli(logits), 1 Normal; CHECK: the tile holds padding rows.  The
+// eight line pointers bh/bl[k] (k = chain & 7) already carry the swizzle term of this lane, so
+// a store is [pointer + (j >> 3) * 1024] with no address arithmetic left in the loop.
+template <int LIK, bool CHECK>
+__device__ __forceinline__ void resid_chunk(const uint32_t (&v)[32], float yv, bool valid,
+                                            const float* __restrict__ col_scale_c0,
+                                            unsigned char* const (&bh)[8], unsigned char* const (&bl)[8],
+                                            float (&part)[32]) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const float l = __uint_as_float(v[j]);
+    float res, term;
+    if (LIK == 1) {
+      const float r = yv - l;
+      term = r * r;
+      res = -(col_scale_c0[j] * r);
+    } else {
+      bce_logits_fast(l, yv, term, res);
+    }
+    if (CHECK) {
+      res = valid ? res : 0.f;
+      term = valid ? term : 0.f;
+    }
+    // x = hi + lo in integer arithmetic (res is finite and small: no inf/NaN path needed):
+    // hi = res rounded to TF32, ties away (== cvt.rna.tf32.f32); lo = res - hi is exact and
+    // its low 13 bits are dropped exactly as the tensor core would drop them
+    const uint32_t hb = (__float_as_uint(res) + 0x1000u) & 0xFFFFE000u;
+    const float hi = __uint_as_float(hb);
+    const uint32_t lb = __float_as_uint(res - hi) & 0xFFFFE000u;
+    *reinterpret_cast<uint32_t*>(bh[j & 7] + (j >> 3) * umma::kAtomBytes) = hb;
+    *reinterpret_cast<uint32_t*>(bl[j & 7] + (j >> 3) * umma::kAtomBytes) = lb;
+    part[j] = term;
+  }
+}
+
+template <int LIK>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm3x_resid_persistent_kernel(const __grid_constant__ Gemm3xLaunch L) {
   extern __shared__ unsigned char gsm_raw[];
@@ -344,34 +381,23 @@ gemm3x_resid_persistent_kernel(const __grid_constant__ Gemm3xLaunch L) {
       mbar_wait(&acc_full[buf], u & 1u);
       umma::fence_after_sync();
       const uint32_t trow = tmem + (uint32_t)(buf * kGemmN) + ((uint32_t)(q * 32) << 16);
+      const bool check = (mt + 1) * kGemmM > L.n_valid;  // CTA-uniform: padding rows in this tile
+      const int swz = (lane >> 2) << 4, sub = (lane & 3) << 2;
 #pragma unroll 1
       for (int c0 = c_begin; c0 < c_end; c0 += 32) {
         uint32_t v[32];
         umma::tmem_ld32(trow + c0, v);
+        unsigned char *bh[8], *bl[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const long o = (long)(c0 >> 3) * umma::kAtomBytes + k * 128 + (swz ^ (k << 4)) + sub;
+          bh[k] = rh + o;
+          bl[k] = rl + o;
+        }
         umma::tmem_ld_wait();
         float part[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int c = c0 + j;
-          const float l = __uint_as_float(v[j]);
-          float res = 0.f, term = 0.f;
-          if (valid) {
-            if (L.likelihood == 1) {
-              const float r = yv - l;
-              term = r * r;
-              res = -(L.col_scale[c] * r);
-            } else {
-              bce_logits_fast(l, yv, term, res);
-            }
-          }
-          float hi, lo;
-          umma::split_tf32(res, hi, lo);
-          const long off = (long)(c >> 3) * umma::kAtomBytes + (c & 7) * 128 +
-                           (((lane >> 2) ^ (c & 7)) << 4) + ((lane & 3) << 2);
-          *reinterpret_cast<float*>(rh + off) = hi;
-          *reinterpret_cast<float*>(rl + off) = lo;
-          part[j] = term;
-        }
+        if (check) resid_chunk<LIK, true>(v, yv, valid, L.col_scale + c0, bh, bl, part);
+        else resid_chunk<LIK, false>(v, yv, valid, L.col_scale + c0, bh, bl, part);
         const float tot = warp_transpose_reduce32(part);
         llp[c0 + lane] = tot;
       }
