@@ -124,6 +124,7 @@ def cpu_nuts_sample(X, y, budget_s, max_transitions, cores_note=True):
     from oracle.hmc_util import Config
 
     cpotentials.build()
+    cpotentials.use_all_cores()
     fam = cpotentials.CLogistic(X, y)
     kern = ohmc.HMCKernel(fam, cfg=Config(np.float32, True))
     state = kern.init(T.PRNGKey(1), 1000)
@@ -145,6 +146,7 @@ def run_reference(args):
     from oracle.hmc_util import Config
 
     cpotentials.build()
+    cpotentials.use_all_cores()  # torchrun exports OMP_NUM_THREADS=1
     fam = cpotentials.CLogistic(X, y)
     kern = ohmc.HMCKernel(fam, cfg=Config(np.float32, True))
     state = kern.init(T.PRNGKey(1), 1000)

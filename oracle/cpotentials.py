@@ -29,7 +29,19 @@ def lib():
         _lib.oracle_logistic_potential_and_grad.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_int,
                                                             C.c_void_p, C.c_void_p, C.c_void_p]
         _lib.oracle_num_threads.restype = C.c_int
+        _lib.oracle_set_num_threads.argtypes = [C.c_int]
     return _lib
+
+
+def use_all_cores():
+    """All host cores this process may run on, whatever OMP_NUM_THREADS says (torchrun sets it
+    to 1).  Returns the thread count now in effect."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    lib().oracle_set_num_threads(n)
+    return lib().oracle_num_threads()
 
 
 class CLogistic:
