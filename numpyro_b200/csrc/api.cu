@@ -559,6 +559,10 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
     // thread per chain (tiny D, diagonal mass), warp per chain, CTA per chain; or the
     // lock-step tensor-core engine (batch_kernel.cuh)
     h->mode = batch ? 3 : ((D <= 32 && !c.dense_mass) ? 0 : (D <= 512 ? 1 : 2));
+    if (const char* e = getenv("B200MC_CHAIN_MODE")) {  // tuning aid: force the chain grouping
+      const int m = atoi(e);
+      if (!batch && ((m == 0 && D <= 32 && !c.dense_mass) || (m == 1 && D <= 512) || m == 2)) h->mode = m;
+    }
     h->c_pad = (C + 31) / 32 * 32;
     const size_t chains = (h->mode == 0) ? (size_t)h->c_pad : (size_t)C;
     ACK(alloc((void**)&h->work, sizeof(float) * chains * nslots * D));
@@ -662,6 +666,16 @@ static int launch_chain(b200mc_handle* h, const CollectSpec& col, const uint32_t
   ChainLaunch L;
   L.P = h->P; L.M = h->M; L.col = col; L.cs = h->cs; L.cv = h->cv; L.work = h->work;
   L.init_keys = keys; L.user_init = user_init; L.C = h->C; L.c_pad = h->c_pad;
+  {
+    static int thresh = -1;
+    if (thresh < 0) {
+      const char* e = getenv("B200MC_END_THRESH");
+      thresh = e ? atoi(e) : 28;  // sweep in profiles/r01_chain_kernel_tuning.txt
+      if (thresh < 1) thresh = 1;
+      if (thresh > 32) thresh = 32;
+    }
+    L.end_thresh = thresh;
+  }
   if (h->mode == 0) {
     const int threads = 64;  // small blocks spread the chains over all SMs
     chain_kernel<0><<<(h->C + threads - 1) / threads, threads, 0, st>>>(L);
@@ -669,7 +683,7 @@ static int launch_chain(b200mc_handle* h, const CollectSpec& col, const uint32_t
     const int wpb = 4;
     chain_kernel<1><<<(h->C + wpb - 1) / wpb, wpb * 32, 0, st>>>(L);
   } else {
-    chain_kernel<2><<<h->C, 256, 0, st>>>(L);
+    chain_kernel<2><<<h->C, kChainCtaThreads, 0, st>>>(L);
   }
   g_launches++;
   CK(cudaGetLastError());

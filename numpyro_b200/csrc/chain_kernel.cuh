@@ -19,12 +19,23 @@ struct ChainLaunch {
   int user_init;            // init: cv.z already holds caller-supplied positions
   int C;
   int c_pad;                // thread-per-chain: chains padded to a multiple of 32
+  int end_thresh;           // thread-per-chain: lanes that must wait at a subtree end before
+                            // the tail runs (1 = never wait), see chain_kernel<0>
 };
 
 // MODE 0: thread per chain (work is [slot][D][c_pad]); 1: warp per chain; 2: CTA per
 // chain (work is [chain][slot][D]).
+#ifndef B200MC_CTA_MINB
+#define B200MC_CTA_MINB 4  // resident CTAs per SM asked of ptxas for the CTA-per-chain kernel (64 registers)
+#endif
+#ifndef B200MC_CTA_THREADS
+#define B200MC_CTA_THREADS 256
+#endif
+constexpr int kChainCtaThreads = B200MC_CTA_THREADS;
+
 template <int MODE>
-__global__ void chain_kernel(const __grid_constant__ ChainLaunch L) {
+__global__ void __launch_bounds__(MODE == 2 ? kChainCtaThreads : 128, MODE == 2 ? B200MC_CTA_MINB : 1)
+chain_kernel(const __grid_constant__ ChainLaunch L) {
   __shared__ float red_scratch[64];
   const int D = L.P.D;
   const int nslots = num_slots(L.P.max_depth, L.P.dense_mass);
@@ -42,6 +53,44 @@ __global__ void chain_kernel(const __grid_constant__ ChainLaunch L) {
     base = L.work + (long)chain * nslots * D;
     sstride = D;
     es = 1;
+  }
+  if (MODE == 0) {
+    // Thread per chain.  The 32 chains of a warp run the same leaf step (potential, leapfrog,
+    // energy and checkpoint U-turn tests) in every iteration, but each reaches the END of a
+    // subtree / of a transition in its own iteration, and that tail is long (the Threefry
+    // draws of the next doubling, or split + D normals of the next momentum, plus the
+    // adaptation step): run in place it executes with ~3 of 32 lanes active and takes ~78 % of
+    // all issue slots (ncu: 9.8 active threads per instruction).  So a lane that reaches a
+    // subtree end WAITS (AT_SUBTREE_END) until `end_thresh` lanes of its warp wait too, or no
+    // lane has leaf work left; then all of them run the tail together.  Only the schedule
+    // changes: every chain computes exactly what it computed before.
+    const bool live = chain < L.C;
+    ThreadGroup g{};
+    Sampler<ThreadGroup> S;
+    StepResult r = FINISHED;
+    if (live) {
+      S.setup(&L.P, g, base, sstride, es, chain, L.C, &L.col);
+      S.load(L.cs, L.cv);
+      S.end_yield = L.end_thresh > 1;
+      if (L.init_keys)
+        r = S.begin_init(Key{L.init_keys[2 * chain], L.init_keys[2 * chain + 1]}, L.user_init != 0);
+      else
+        r = S.begin_sampling();
+    }
+    for (;;) {
+      if (r == NEED_GRAD) {
+        const float U = model_potential(L.M, g, S.v(LZ), es, S.v(LG), es, chain);
+        r = S.advance(U);
+      }
+      const unsigned waiting = __ballot_sync(0xffffffffu, r == AT_SUBTREE_END);
+      const unsigned running = __ballot_sync(0xffffffffu, r == NEED_GRAD);
+      if ((waiting | running) == 0u) break;
+      if (waiting != 0u && (__popc(waiting) >= L.end_thresh || running == 0u)) {
+        if (r == AT_SUBTREE_END) r = S.finish_subtree_yielded();
+      }
+    }
+    if (live) S.store(L.cs, L.cv);
+    return;
   }
   if (chain >= L.C) return;
 

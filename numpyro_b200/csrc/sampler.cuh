@@ -60,7 +60,12 @@ enum Phase { PH_INIT = 0, PH_TREE, PH_HMC, PH_IDLE, PH_FAIL, PH_FRSS };
 // NEED_MATVEC: only with mv_yield (lock-step engine): the dense-mass product described by
 // `rq` must be computed by the caller, then resume() continues where advance() stopped.
 enum StepResult { NEED_GRAD = 0, FINISHED = 1, NEED_MATVEC = 2, NEED_FACTOR = 3,
-                  STAGE_DONE = 4 /* internal: an adapt stage fell through */ };
+                  STAGE_DONE = 4 /* internal: an adapt stage fell through */,
+                  // only with end_yield (thread-per-chain kernel): a subtree is complete; the rare,
+                  // long tail (combine, U-turn of the whole tree, next doubling's or next
+                  // transition's Threefry draws, adaptation) runs in finish_subtree_yielded(),
+                  // which the caller invokes when enough lanes of the warp wait for it
+                  AT_SUBTREE_END = 5 };
 
 struct MatvecRequest {
   int mat;         // which of the chain's four D x D matrices
@@ -131,6 +136,8 @@ struct Sampler {
   // leaf state parked between part A and part B of the fused leaf step
   float fz[4], fg[4], f_U, f_e_new, f_dE;
   int deferred;  // 0 none, 1 leaf fold, 2 subtree end + doubling state, 3 transition end
+  bool end_yield;      // return AT_SUBTREE_END instead of running the subtree tail in place
+  bool y_sub_turning;  // the subtree's turning flag while it waits
   bool d_sub_turning, d_tree_turning;
   float u_top;
   // HMC
@@ -191,6 +198,7 @@ struct Sampler {
     pre_valid = 0;
     pre_d_valid = 0; pre_t_valid = 0; pre_a_valid = 0;
     deferred = 0;
+    end_yield = false; y_sub_turning = false;
     mv_yield = false; leaf_cached = false; mv_resume = 0;
   }
 
@@ -1319,6 +1327,16 @@ struct Sampler {
 
     }
 
+    if (end_yield) {
+      y_sub_turning = sub_turning;
+      return AT_SUBTREE_END;
+    }
+    return finish_subtree(sub_turning);
+  }
+
+  __device__ StepResult finish_subtree_yielded() { return finish_subtree(y_sub_turning); }
+
+  __device__ StepResult finish_subtree(bool sub_turning) {
     // 5. subtree finished: biased-progressive combine with the tree (:767-848, biased=True)
     B200MC_STAMP(t3_);
     if (going_right) {
