@@ -457,11 +457,16 @@ class HMC(MCMCKernel):
         self._create(bound, keys.shape[0], num_warmup)
         kind, arg = self._strategy()
         if init_params is None and kind == "value":
+            # initialization.py `init_to_value`: CONSTRAINED values per site.  The reference
+            # falls back to init_to_uniform for sites that are not listed; the device init
+            # search draws either every site or none, so a partial dict is refused.
             missing = [k for k, _ in bound.trace_sites if k not in arg]
             if missing:
                 raise NotImplementedError(f"init_to_value must cover every latent site; missing {missing}")
-            raise NotImplementedError(
-                "init_to_value is not implemented yet: pass unconstrained `init_params` instead")
+            init_params = bound.unconstrain(arg)
+            if self._vectorized:
+                init_params = {k: np.broadcast_to(v, (keys.shape[0],) + np.shape(v)).copy()
+                               for k, v in init_params.items()}
         z0 = None
         if init_params is not None:
             z = bound.ravel(init_params)

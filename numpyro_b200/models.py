@@ -21,12 +21,13 @@ class BoundModel:
     (``ModelInfo``: site layout, postprocess_fn), minus the potential, which lives in CUDA."""
 
     def __init__(self, family, name, N, ncols, data0, data1, trace_sites, constrain,
-                 likelihood=0):
+                 likelihood=0, positive=()):
         self.family, self.name, self.N, self.ncols = family, name, N, ncols
         self.likelihood = likelihood
         self.data0, self.data1 = data0, data1
         self.trace_sites = tuple(trace_sites)  # (site, shape) in model trace order
         self._constrain = constrain
+        self.positive = tuple(positive)  # sites with `positive` support (ExpTransform)
         off, self.flat_sites = 0, OrderedDict()
         for k, shape in sorted(self.trace_sites):  # ravel_pytree: sorted site names
             size = int(np.prod(shape)) if len(shape) else 1
@@ -50,6 +51,15 @@ class BoundModel:
             batch = b if batch is None else batch
             parts.append(v.reshape(b + (s,)))
         return np.concatenate(parts, axis=-1)
+
+    def unconstrain(self, values):
+        """Constrained site values -> unconstrained (``transforms.py:563-571`` inverse: log for
+        the ``positive`` sites, identity for real ones), as ``init_to_value`` needs."""
+        out = {}
+        for k, (o, size, shp) in self.flat_sites.items():
+            v = np.asarray(values[k], np.float32)
+            out[k] = np.log(v) if k in self.positive else v
+        return out
 
     def postprocess(self, zdict):
         """``postprocess_fn``: unconstrained dict -> constrained + deterministic sites
@@ -97,7 +107,8 @@ def _bind_eight_schools(J, sigma, y=None):
         return out
 
     return BoundModel(EIGHT_SCHOOLS, "eight_schools", J, 0, y, sigma,
-                      [("mu", ()), ("tau", ()), ("theta_base", (J,))], constrain)
+                      [("mu", ()), ("tau", ()), ("theta_base", (J,))], constrain,
+                      positive=("tau",))
 
 
 def _bind_sv(returns):
@@ -108,7 +119,8 @@ def _bind_sv(returns):
         return {"nu": np.exp(z["nu"]), "s": z["s"], "sigma": np.exp(z["sigma"])}
 
     return BoundModel(SV, "stochastic_volatility", T, 0, r, None,
-                      [("sigma", ()), ("s", (T,)), ("nu", ())], constrain)
+                      [("sigma", ()), ("s", (T,)), ("nu", ())], constrain,
+                      positive=("sigma", "nu"))
 
 
 def _bind_horseshoe(likelihood):
@@ -131,7 +143,8 @@ def _bind_horseshoe(likelihood):
             return out
 
         return BoundModel(HORSESHOE, "horseshoe", X.shape[0], Dh, X, Y, sites, constrain,
-                          likelihood=likelihood)
+                          likelihood=likelihood,
+                          positive=("lambdas", "tau") + (("prec_obs",) if likelihood == 1 else ()))
 
     return bind
 

@@ -88,6 +88,22 @@ def diagnostics_fixture():
     return out
 
 
+def collect_fixture():
+    """The reference's own ``fori_collect`` (numpyro/util.py, executed unmodified) over a
+    counter: entry k of the result is 1 + the index of the iteration whose value was kept."""
+    _, _, util = refshim.install(True)
+    out = {}
+    for c in rc.COLLECT_CASES:
+        lower, upper, thin, csize = c
+        with util.control_flow_prims_disabled():
+            col, last = util.fori_collect(lower, upper, lambda v: v + 1, refshim._wrap(np.int32(0)),
+                                          progbar=False, return_last_val=True,
+                                          collection_size=csize, thinning=thin)
+        assert int(last) == upper
+        out[rc.collect_tag(c)] = np.asarray(col)
+    return out
+
+
 def main():
     data = rc.make_data()
     fams = rc.families(data)
@@ -104,6 +120,7 @@ def main():
                   f"{res['num_steps'].mean():7.2f}  step {float(res['step_size'][-1]):.4f}  "
                   f"diverging {int(res['diverging'].sum())}")
     out.update(diagnostics_fixture())
+    out.update(collect_fixture())
     np.savez_compressed(os.path.join(HERE, "refpin.npz"), **out)
     print("wrote refpin.npz", os.path.getsize(os.path.join(HERE, "refpin.npz")), "bytes")
 

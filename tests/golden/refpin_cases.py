@@ -95,3 +95,12 @@ FIELDS = ("z", "potential_energy", "energy", "num_steps", "accept_prob", "mean_a
 
 def block_tag(names):
     return "+".join(names)
+
+
+# fori_collect (numpyro/util.py:277-407): (lower, upper, thinning, collection_size)
+COLLECT_CASES = [(0, 10, 1, None), (5, 20, 3, None), (7, 20, 4, None), (0, 9, 2, None), (3, 3, 1, None),
+                 (10, 37, 5, 8), (0, 1, 1, None), (4, 30, 7, None)]
+
+
+def collect_tag(c):
+    return "collect/" + "_".join("x" if v is None else str(v) for v in c)

@@ -116,6 +116,20 @@ def test_structured_mass_matrix_layout(nb):
         lay(dense_mass=[("mu", "tau")], inverse_mass_matrix={("mu",): np.ones(1)})
 
 
+def test_unconstrain_inverts_postprocess(nb):
+    """``init_to_value`` takes CONSTRAINED values: log for the positive sites."""
+    from numpyro_b200 import models
+
+    b = models.horseshoe_normal.bind(np.ones((4, 3), np.float32), np.ones(4, np.float32))
+    z = {k: np.random.default_rng(1).normal(size=shp).astype(np.float32)
+         for k, (_, _, shp) in b.flat_sites.items()}
+    c = b.postprocess(z)
+    back = b.unconstrain(c)
+    for k in z:
+        np.testing.assert_allclose(back[k], z[k], rtol=1e-5, atol=1e-6)
+    assert set(b.positive) == {"lambdas", "tau", "prec_obs"}
+
+
 def test_no_device_raises_loudly(nb):
     from numpyro_b200 import _lib, models, random
     from numpyro_b200.infer import NUTS

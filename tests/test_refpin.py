@@ -120,6 +120,27 @@ def test_diagnostics_match_reference_source(which, name):
             np.testing.assert_allclose(s[k], G[f"diag/{name}/summary/{k}"], **tol, err_msg=k)
 
 
+@pytest.mark.parametrize("case", [c for c in rc.COLLECT_CASES if c[3] is None])
+def test_oracle_collection_matches_reference_fori_collect(case):
+    """Which iterations ``fori_collect`` keeps (thinning keeps the LAST draw of each block,
+    ``start_idx = lower + (upper - lower) % thinning``): the oracle's ``run_chain`` against the
+    reference's own ``numpyro/util.py`` run over a counter."""
+    from types import SimpleNamespace as NS
+
+    from oracle import hmc as ohmc
+
+    lower, upper, thin, _ = case
+
+    def state(n):
+        return NS(z=np.array([n]), potential_energy=n, energy=n, num_steps=n, accept_prob=n,
+                  mean_accept_prob=n, diverging=n, adapt_state=NS(step_size=n), n=n)
+
+    fake = NS(init=lambda key, nw, ip, iv: state(0), sample=lambda st: state(st.n + 1))
+    res, last = ohmc.run_chain(fake, None, lower, upper - lower, thinning=thin)
+    assert last.n == upper
+    assert np.array_equal(res["potential_energy"], G[rc.collect_tag(case)])
+
+
 # ------------------------------------------------------------------------------- GPU
 @pytest.fixture(scope="module")
 def nb():
@@ -305,3 +326,55 @@ def test_cuda_adaptation_traces_follow_reference_source(nb, name):
     # momentum keys: the order of mass_matrix_sqrt's blocks is the reference's
     assert [rc.block_tag(k) for k in last.adapt_state.mass_matrix_sqrt] == [str(b) for b in G[name + "/blocks"]] \
         or len(imm) == 1 or not kw.get("adapt_mass_matrix", True)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", [c for c in rc.COLLECT_CASES if c[3] is None and c[1] > c[0]])
+def test_cuda_collection_matches_reference_fori_collect(nb, case):
+    """The draws ``MCMC`` keeps with a warm-up offset and thinning are the ones the reference's
+    ``fori_collect`` keeps: with adaptation off the chain does not depend on ``num_warmup``, so
+    the thinned run must return exactly the kept iterations of the full run."""
+    from numpyro_b200 import infer, models
+    from numpyro_b200.random import PRNGKey
+
+    lower, upper, thin, _ = case
+    kw = dict(step_size=0.3, adapt_step_size=False, adapt_mass_matrix=False)
+    args, kwargs = (8, rc.S8), {"y": rc.Y8}
+
+    def run(nw, ns, thinning):
+        m = infer.MCMC(infer.NUTS(models.eight_schools_noncentered, **kw), num_warmup=nw,
+                       num_samples=ns, thinning=thinning)
+        m.run(PRNGKey(5), *args, extra_fields=("potential_energy", "num_steps"), **kwargs)
+        return m.get_extra_fields()["potential_energy"], m.get_samples()["mu"]
+
+    full_pe, full_mu = run(0, upper, 1)
+    pe, mu = run(lower, upper - lower, thin)
+    kept = G[rc.collect_tag(case)] - 1  # iteration indices
+    assert np.array_equal(pe, full_pe[kept])
+    assert np.array_equal(mu, full_mu[kept])
+
+
+@pytest.mark.gpu
+def test_cuda_init_to_value_equals_init_params(nb):
+    """``init_to_value`` (constrained values for every site, initialization.py) starts the chain
+    at the same unconstrained point as passing ``init_params``."""
+    from numpyro_b200 import infer, models
+    from numpyro_b200.random import PRNGKey
+
+    kw = dict(step_size=0.3, adapt_step_size=False, adapt_mass_matrix=False)
+    args, kwargs = (8, rc.S8), {"y": rc.Y8}
+    bound = models.eight_schools_noncentered.bind(*args, **kwargs)
+    z0 = bound.unravel(np.linspace(-0.5, 0.5, 10).astype(np.float32))
+    vals = {k: v for k, v in bound.postprocess(z0).items() if k in z0}
+    out = []
+    for kernel, ip in ((infer.NUTS(models.eight_schools_noncentered, **kw), z0),
+                       (infer.NUTS(models.eight_schools_noncentered,
+                                   init_strategy=infer.hmc.init_to_value(values=vals), **kw), None)):
+        m = infer.MCMC(kernel, num_warmup=0, num_samples=20)
+        m.run(PRNGKey(3), *args, init_params=ip, extra_fields=("num_steps",), **kwargs)
+        out.append((m.get_extra_fields()["num_steps"], m.get_samples()["mu"]))
+    assert np.array_equal(out[0][0], out[1][0])
+    np.testing.assert_allclose(out[0][1], out[1][1], rtol=1e-5, atol=1e-6)
+    with pytest.raises(NotImplementedError):
+        k = infer.NUTS(models.eight_schools_noncentered, init_strategy=infer.hmc.init_to_value(values={"mu": 0.0}))
+        infer.MCMC(k, num_warmup=0, num_samples=2).run(PRNGKey(3), *args, **kwargs)
