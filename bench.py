@@ -516,6 +516,13 @@ def run_chain_workload(args):
     T_ = args.transitions
     ns_buf = _lib.DeviceArray((T_, chains), np.int32)
     col = _lib.Collect(n_keep=T_, num_steps_dev=ns_buf.ptr)
+    # second half of BASELINE's metric (min bulk ESS / s): keep the timed draws when they are
+    # small enough to copy out between steps (outside the timed events)
+    D_all = int(kern._bound.dim)
+    z_buf, draws = None, []
+    if T_ * chains * D_all * 4 <= (512 << 20) and world == 1:
+        z_buf = _lib.DeviceArray((T_, chains, D_all), np.float32)
+        col.z_dev = z_buf.ptr
     ev0, ev1 = lib.b200mc_event_create(), lib.b200mc_event_create()
     tot_ms, tot_g = 0.0, 0
     launches0 = None
@@ -536,6 +543,8 @@ def run_chain_workload(args):
         if i >= args.warmup:
             tot_ms += float(ms.value)
             tot_g += int(ns_buf.numpy().sum())
+            if z_buf is not None:
+                draws.append(z_buf.numpy())
     barrier()
     clk = clocks.stop()
     local_g, local_ms = tot_g, tot_ms
@@ -565,7 +574,25 @@ def run_chain_workload(args):
                     "frac": ach / 1130.0, "traffic": None, "peak_source": "nominal TF32 dense",
                     "kernel": "gemm3x_kernel x2 (whole step timed; the residual images' HBM "
                               "round trip and the transcendental epilogue dominate, DESIGN 4.3)"}
+    ess = None
+    if draws and args.steps * T_ >= 8:
+        from numpyro_b200.diagnostics import bulk_effective_sample_size, split_gelman_rubin
+
+        x = np.concatenate(draws, axis=0).transpose(1, 0, 2)  # [chain, draw, D]
+        if x.shape[2] > 16:  # keep the host-side ranking affordable: 16 evenly spaced parameters
+            x = x[:, :, np.unique(np.linspace(0, x.shape[2] - 1, 16).astype(int))]
+        # one parameter at a time: the pooled ranking of chains x draws values is the big array
+        bulk = np.array([bulk_effective_sample_size(x[:, :, d:d + 1])[0] for d in range(x.shape[2])])
+        rhat = np.array([split_gelman_rubin(x[:, :, d:d + 1].astype(np.float64))[0]
+                         for d in range(x.shape[2])])
+        ess = {"min_bulk_ess": float(np.min(bulk)), "draws_per_chain": int(x.shape[1]),
+               "chains": int(x.shape[0]), "params_checked": int(x.shape[2]),
+               "max_split_r_hat": float(np.max(rhat)),
+               "metric": "min_bulk_ess_per_sec", "value": float(np.min(bulk)) / (tot_ms * 1e-3),
+               "unit": "ESS/s", "note": "device-timed sampling phase, rank-normalised split-chain "
+               "bulk ESS over all chains (SURVEY 8d)"}
     line = {"metric": METRIC, "value": tot_g / (tot_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+            "ess": ess,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
