@@ -362,6 +362,10 @@ def run_own(args):
         clocks = ClockSampler(local, 1000) if rank == 0 else None
     e2e_grads, e2e_s, e2e_ms = 0, 0.0, []
     z_last = {k: np.asarray(v) for k, v in kern._last_state.z.items()}
+    import gc
+
+    gc.collect()
+    gc.disable()  # no collector pauses inside the timed host-side steps
     barrier()
     for i in range(args.warmup + args.steps):
         t0 = time.perf_counter()
@@ -378,6 +382,7 @@ def run_own(args):
             e2e_grads += int(ns.sum())
             e2e_s += dt
             e2e_ms.append(round(dt * 1e3, 3))
+    gc.enable()
     barrier()
     e2e_s = max_over_ranks(e2e_s)
     e2e_grads = float(e2e_grads) if rows else sum_over_ranks(float(e2e_grads))
@@ -421,8 +426,30 @@ def run_own(args):
             "cta0_cycles_per_grad_eval": breakdown,
             "mean_tree_size": float(np.mean(step_grads)) / T_,
         }
+        if world == 1 and not args.no_many_chain:
+            line["many_chain"] = many_chain_leg()
         print(json.dumps(line))
     return 0
+
+
+def many_chain_leg():
+    """The same data with 256 vectorized chains through the tensor-core lock-step engine
+    (north_star: from 64 chains on X.Theta is a dense contraction), run as a separate process
+    (`--workload logistic_many`) after the headline legs and reported next to them: grad-evals/s
+    and, above all, min-bulk-ESS/s, which is what many chains buy.  Never fatal for the line."""
+    try:
+        out = subprocess.run([sys.executable, os.path.abspath(__file__), "--workload", "logistic_many",
+                              "--chains", "256", "--steps", "3", "--warmup", "2", "--no-cpu"],
+                             capture_output=True, text=True, timeout=300)
+        d = json.loads(out.stdout.strip().splitlines()[-1])
+        return {"chains": 256, "grad_evals_per_sec": d["value"], "ms_per_step": d["ms_per_step"],
+                "transitions_per_step": d["config"]["transitions_per_step"],
+                "min_bulk_ess_per_sec": (d.get("ess") or {}).get("value"),
+                "max_split_r_hat": (d.get("ess") or {}).get("max_split_r_hat"),
+                "roofline": d.get("roofline"), "clocks": d.get("clocks"),
+                "gpu_launches": d.get("gpu_launches")}
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
 
 
 # ---------------------------------------------------------------------------- other configs
@@ -621,6 +648,8 @@ def main():
     ap.add_argument("--adapt", type=int, default=300, help="untimed adaptation transitions")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU baseline work")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-many-chain", action="store_true",
+                    help="skip the 256-chain leg appended to the default line")
     ap.add_argument("--fixed-step", type=float, default=0.0,
                     help="chain workloads: fixed step size, no adaptation (profiling aid)")
     ap.add_argument("--max-tree-depth", type=int, default=0)
