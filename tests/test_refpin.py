@@ -378,3 +378,31 @@ def test_cuda_init_to_value_equals_init_params(nb):
     with pytest.raises(NotImplementedError):
         k = infer.NUTS(models.eight_schools_noncentered, init_strategy=infer.hmc.init_to_value(values={"mu": 0.0}))
         infer.MCMC(k, num_warmup=0, num_samples=2).run(PRNGKey(3), *args, **kwargs)
+
+
+@pytest.mark.gpu
+def test_cuda_block_mass_vectorized_chains_are_independent(nb):
+    """Structured mass matrix with vectorized chains: chain c of a 3-chain run is the
+    single-chain run on ``split(key, 3)[c]`` (``mcmc.py:661-662``), draw for draw, and the
+    per-block ``adapt_state`` dicts carry the chain dimension."""
+    from numpyro_b200 import infer, models
+    from numpyro_b200.random import PRNGKey, split
+
+    args, kwargs = (8, rc.S8), {"y": rc.Y8}
+    kw = dict(dense_mass=[("theta_base", "mu")])
+    m = infer.MCMC(infer.NUTS(models.eight_schools_noncentered, **kw), num_warmup=60, num_samples=10,
+                   num_chains=3, chain_method="vectorized")
+    m.run(PRNGKey(9), *args, extra_fields=("num_steps",), **kwargs)
+    mu = m.get_samples(group_by_chain=True)["mu"]
+    ns = m.get_extra_fields(group_by_chain=True)["num_steps"]
+    imm = m.last_state.adapt_state.inverse_mass_matrix
+    assert list(imm) == [("theta_base", "mu"), ("tau",)]
+    assert imm[("theta_base", "mu")].shape == (3, 9, 9) and imm[("tau",)].shape == (3, 1)
+    keys = split(PRNGKey(9), 3)
+    for c in range(3):
+        s = infer.MCMC(infer.NUTS(models.eight_schools_noncentered, **kw), num_warmup=60, num_samples=10)
+        s.run(keys[c], *args, extra_fields=("num_steps",), **kwargs)
+        assert np.array_equal(s.get_extra_fields()["num_steps"], ns[c]), c
+        assert np.array_equal(s.get_samples()["mu"], mu[c]), c
+        one = s.last_state.adapt_state.inverse_mass_matrix
+        assert np.array_equal(one[("theta_base", "mu")], imm[("theta_base", "mu")][c])
