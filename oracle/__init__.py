@@ -22,6 +22,14 @@ Parity status
   (``tests/test_refpin.py``).  Not reference code in those runs, and therefore restated:
   ``jax.random`` (Threefry, below), autodiff (closed-form gradients, checked against finite
   differences and float64), and the model tracing / init search of ``infer/util.py``.
+* Potentials, init search (``find_valid_initial_params``), ``postprocess_fn`` and the whole
+  ``MCMC.run`` stack: PINNED to the reference's own model code -- the entire unmodified
+  ``numpyro`` package is imported over the stand-in (``tests/golden/refshim_full.py``) and the
+  model functions of its example files are evaluated by its ``potential_energy`` /
+  ``initialize_model`` / ``constrain_fn`` / ``MCMC`` (``tests/golden/make_refmodels.py`` ->
+  ``refmodels.npz``; ``tests/test_refmodels.py``): potential values to f32 round-off, initial
+  points and MCMC draws exactly.  Gradients are closed forms checked against central
+  differences of an independent ``scipy.stats`` statement.
 * Also pinned against the golden vectors held by the reference's own tests
   (``test/infer/test_hmc_util.py``, ``test/test_diagnostics.py``): adaptation schedule,
   checkpoint indices, iterative U-turn truth table, Welford regulariser, dual averaging,
