@@ -167,6 +167,12 @@ def main():
         out[f"{key}/sites"] = np.array(sorted(shapes))
         print(key, "U", [float(u) for u in Us], "sites", {k: shapes[k] for k in sorted(shapes)})
     out.update(mcmc_fixture(numpyro, data, fams))
+    if "--check" in sys.argv:  # re-derive from the reference source and compare with the committed file
+        old = np.load(os.path.join(HERE, "refmodels.npz"))
+        bad = [k for k in out if k not in old.files or not np.array_equal(np.asarray(out[k]), old[k])]
+        bad += [k for k in old.files if k not in out]
+        print("check:", "identical" if not bad else f"DIFFERENT {bad[:8]}")
+        sys.exit(1 if bad else 0)
     np.savez_compressed(os.path.join(HERE, "refmodels.npz"), **out)
     print("wrote refmodels.npz", os.path.getsize(os.path.join(HERE, "refmodels.npz")), "bytes")
 

@@ -146,6 +146,19 @@ def test_oracle_mcmc_matches_reference_mcmc_stack(name):
                                        atol=1e-7, err_msg=f"{name} {site}")
 
 
+@pytest.mark.skipif(not os.path.isdir("/root/reference/numpyro"),
+                    reason="the reference checkout only exists in the build container")
+def test_fixture_regenerates_from_the_reference_package():
+    """Imports the whole reference package over the stand-in in a fresh process and re-derives
+    every entry of refmodels.npz (never on the GPU box)."""
+    import subprocess
+
+    out = subprocess.run([sys.executable, os.path.join(HERE, "golden", "make_refmodels.py"), "--check"],
+                         capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-600:] + out.stderr[-600:]
+    assert "check: identical" in out.stdout
+
+
 # ------------------------------------------------------------------------------- GPU
 @pytest.fixture(scope="module")
 def nb():
