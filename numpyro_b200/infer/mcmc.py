@@ -159,17 +159,17 @@ class MCMC(object):
         self._args, self._kwargs = args, kwargs
         rng_key = np.asarray(rng_key, np.uint32)
         init_state = None
+        if init_params is not None and self.num_chains > 1:
+            leaves = list(init_params.values()) if isinstance(init_params, dict) else [init_params]
+            if np.shape(leaves[0])[0] != self.num_chains:
+                raise ValueError("`init_params` must have the same leading dimension"
+                                 " as `num_chains`.")
         if self.num_chains > 1 and b2random.is_prng_key(rng_key):
             rng_key = b2random.split(rng_key, self.num_chains,
                                      getattr(self.sampler, "partitionable", None))
         if self._warmup_state is not None:
             self._set_collection_params(0, self.num_samples, self.num_samples, "sample")
             init_state = self._warmup_state._replace(rng_key=rng_key)
-        if init_params is not None and self.num_chains > 1:
-            leaves = list(init_params.values()) if isinstance(init_params, dict) else [init_params]
-            if np.shape(leaves[0])[0] != self.num_chains:
-                raise ValueError("`init_params` must have the same leading dimension"
-                                 " as `num_chains`.")
         assert isinstance(extra_fields, (tuple, list))
         collect_fields, remove_sites = {}, {}
         for field_name in ((self._sample_field,) + tuple(self._default_fields) + tuple(extra_fields)):

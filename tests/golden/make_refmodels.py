@@ -123,6 +123,45 @@ def mcmc_fixture(numpyro, data, fams):
     return out
 
 
+def errors_fixture(numpyro, data):
+    """Argument checking of the reference's ``HMC`` / ``NUTS`` / ``MCMC`` (``hmc.py:643-658``,
+    ``mcmc.py:342-354,672-678``): exception type and message, or the warning text."""
+    import warnings
+
+    from numpyro.infer import HMC, MCMC, NUTS
+
+    model, args, kwargs = models(numpyro, data)["es"]
+    key = W(np.array([0, 1], np.uint32))
+    bad_init = {"mu": W(np.zeros(3, np.float32)), "tau": W(np.zeros(3, np.float32)),
+                "theta_base": W(np.zeros((3, 8), np.float32))}
+    calls = {
+        "nuts_no_model": lambda: NUTS(),
+        "nuts_model_and_potential": lambda: NUTS(model, potential_fn=lambda z: 0.0),
+        "hmc_no_length": lambda: HMC(model, trajectory_length=None),
+        "hmc_both_lengths_warns": lambda: HMC(model, num_steps=3),
+        "mcmc_thinning": lambda: MCMC(NUTS(model), num_warmup=1, num_samples=1, thinning=0),
+        "mcmc_chain_method": lambda: MCMC(NUTS(model), num_warmup=1, num_samples=1, chain_method="foo"),
+        "mcmc_init_params_leading_dim": lambda: MCMC(
+            NUTS(model), num_warmup=1, num_samples=1, num_chains=2, chain_method="sequential",
+            progress_bar=False).run(key, *args, init_params=bad_init, **kwargs),
+    }
+    out = {}
+    for name, f in calls.items():
+        try:
+            with warnings.catch_warnings(record=True) as w:
+                warnings.simplefilter("always")
+                f()
+            rec = ["warning", str(w[0].message)] if w else ["ok", ""]
+        except Exception as e:  # noqa: BLE001
+            rec = [type(e).__name__, str(e)]
+        out["errors/" + name] = np.array(rec)
+        print("errors", name, rec)
+    k = NUTS(model, step_size=1, max_tree_depth=(5, 10))
+    out["attrs/nuts"] = np.array([repr(k._step_size), k.sample_field, repr(k.default_fields), k._algo,
+                                  repr(k._max_tree_depth)])
+    return out
+
+
 def main():
     numpyro = refshim_full.install_full(True)
     from numpyro.infer.util import initialize_model, potential_energy
@@ -167,6 +206,7 @@ def main():
         out[f"{key}/sites"] = np.array(sorted(shapes))
         print(key, "U", [float(u) for u in Us], "sites", {k: shapes[k] for k in sorted(shapes)})
     out.update(mcmc_fixture(numpyro, data, fams))
+    out.update(errors_fixture(numpyro, data))
     if "--check" in sys.argv:  # re-derive from the reference source and compare with the committed file
         old = np.load(os.path.join(HERE, "refmodels.npz"))
         bad = [k for k in out if k not in old.files or not np.array_equal(np.asarray(out[k]), old[k])]

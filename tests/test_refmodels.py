@@ -159,6 +159,45 @@ def test_fixture_regenerates_from_the_reference_package():
     assert "check: identical" in out.stdout
 
 
+def test_argument_checking_matches_reference_classes():
+    """Same exception types and messages (or warning text) as the reference's ``HMC`` / ``NUTS`` /
+    ``MCMC`` constructors and ``MCMC.run`` (recorded from the reference package itself)."""
+    import warnings
+
+    from numpyro_b200 import models
+    from numpyro_b200.infer import HMC, MCMC, NUTS
+
+    model = models.eight_schools_noncentered
+    args, kwargs = (8, rc.S8), {"y": rc.Y8}
+    bad_init = {"mu": np.zeros(3, np.float32), "tau": np.zeros(3, np.float32),
+                "theta_base": np.zeros((3, 8), np.float32)}
+    key = np.array([0, 1], np.uint32)
+    calls = {
+        "nuts_no_model": lambda: NUTS(),
+        "nuts_model_and_potential": lambda: NUTS(model, potential_fn=lambda z: 0.0),
+        "hmc_no_length": lambda: HMC(model, trajectory_length=None),
+        "hmc_both_lengths_warns": lambda: HMC(model, num_steps=3),
+        "mcmc_thinning": lambda: MCMC(NUTS(model), num_warmup=1, num_samples=1, thinning=0),
+        "mcmc_chain_method": lambda: MCMC(NUTS(model), num_warmup=1, num_samples=1, chain_method="foo"),
+        "mcmc_init_params_leading_dim": lambda: MCMC(
+            NUTS(model), num_warmup=1, num_samples=1, num_chains=2, chain_method="sequential",
+            progress_bar=False).run(key, *args, init_params=bad_init, **kwargs),
+    }
+    for name, f in calls.items():
+        kind, msg = (str(x) for x in G["errors/" + name])
+        try:
+            with warnings.catch_warnings(record=True) as w:
+                warnings.simplefilter("always")
+                f()
+            got = ("warning", str(w[0].message)) if w else ("ok", "")
+        except Exception as e:  # noqa: BLE001
+            got = (type(e).__name__, str(e))
+        assert got == (kind, msg), (name, got, (kind, msg))
+    k = NUTS(model, step_size=1, max_tree_depth=(5, 10))
+    assert [repr(k._step_size), k.sample_field, repr(k.default_fields), k._algo,
+            repr(k._max_tree_depth)] == [str(x) for x in G["attrs/nuts"]]
+
+
 # ------------------------------------------------------------------------------- GPU
 @pytest.fixture(scope="module")
 def nb():
