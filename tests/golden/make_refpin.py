@@ -85,6 +85,14 @@ def diagnostics_fixture():
         s = D.summary({"p": x}, prob=0.9, group_by_chain=True)["p"]
         for k, v in s.items():
             out[f"diag/{name}/summary/{k}"] = np.asarray(v)
+    import contextlib
+    import io
+
+    x = diagnostics_inputs()["ar"]
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):  # the table MCMC.print_summary prints
+        D.print_summary({"a": x, "b": x[..., 0] * 2.0}, prob=0.9, group_by_chain=True)
+    out["diag/print_summary"] = np.array(buf.getvalue())
     return out
 
 

@@ -120,6 +120,15 @@ def test_diagnostics_match_reference_source(which, name):
             np.testing.assert_allclose(s[k], G[f"diag/{name}/summary/{k}"], **tol, err_msg=k)
 
 
+def test_print_summary_text_matches_reference_source(capsys):
+    """``MCMC.print_summary``'s table, character for character."""
+    from numpyro_b200 import diagnostics as D
+
+    x = G["diag/ar/x"]
+    D.print_summary({"a": x, "b": x[..., 0] * 2.0}, prob=0.9, group_by_chain=True)
+    assert capsys.readouterr().out == str(G["diag/print_summary"])
+
+
 @pytest.mark.parametrize("case", [c for c in rc.COLLECT_CASES if c[3] is None])
 def test_oracle_collection_matches_reference_fori_collect(case):
     """Which iterations ``fori_collect`` keeps (thinning keeps the LAST draw of each block,
