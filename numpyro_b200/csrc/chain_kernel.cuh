@@ -77,6 +77,11 @@ chain_kernel(const __grid_constant__ ChainLaunch L) {
       else
         r = S.begin_sampling();
     }
+    // a warp with few live chains (num_chains = 4, the tail warp) scales the threshold down:
+    // 7/8 of its live lanes, so one slow chain does not hold the others at every subtree end
+    const int nlive = __popc(__ballot_sync(0xffffffffu, live));
+    int thresh = (nlive * 7) / 8;
+    thresh = thresh < 1 ? 1 : (thresh > L.end_thresh ? L.end_thresh : thresh);
     for (;;) {
       if (r == NEED_GRAD) {
         const float U = model_potential(L.M, g, S.v(LZ), es, S.v(LG), es, chain);
@@ -85,7 +90,7 @@ chain_kernel(const __grid_constant__ ChainLaunch L) {
       const unsigned waiting = __ballot_sync(0xffffffffu, r == AT_SUBTREE_END);
       const unsigned running = __ballot_sync(0xffffffffu, r == NEED_GRAD);
       if ((waiting | running) == 0u) break;
-      if (waiting != 0u && (__popc(waiting) >= L.end_thresh || running == 0u)) {
+      if (waiting != 0u && (__popc(waiting) >= thresh || running == 0u)) {
         if (r == AT_SUBTREE_END) r = S.finish_subtree_yielded();
       }
     }
