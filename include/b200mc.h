@@ -7,8 +7,19 @@
  *
  * Conventions: plain pointers and sizes only.  Pointers named *_dev are DEVICE
  * pointers on the handle's device, owned by the caller; *_host are host pointers.
- * All work is enqueued on the caller's stream (a cudaStream_t passed as void*;
- * NULL = default stream).  Functions return 0 on success, non-zero on failure;
+ * Work is enqueued on the caller's stream (a cudaStream_t passed as void*; NULL = default
+ * stream).  Asynchronous -- return once the work is enqueued: b200mc_init / b200mc_sample /
+ * b200mc_potential_and_grad on the single-launch engines (tall-data logistic with fewer
+ * chains than the lock-step threshold, eight schools, stochastic volatility, horseshoe
+ * below the threshold), the b200mc_random_* / b200mc_threefry2x32 hooks, b200mc_get_vector /
+ * b200mc_set_vector, b200mc_memcpy_* / b200mc_memset.  SYNCHRONISING -- they wait for the
+ * stream (or the device) before they return: b200mc_create (data re-tiling, operand images)
+ * and b200mc_destroy (device synchronise); b200mc_init / b200mc_sample on the lock-step
+ * many-chain engine (>= 64 chains of the logistic / horseshoe families, >= 16 with a dense
+ * mass matrix: the host reads the count of unfinished chains every 16 global steps);
+ * b200mc_get_scalars / b200mc_set_scalars / b200mc_get_profile (device synchronise + host
+ * copy); b200mc_gemm3xtf32; b200mc_stream_synchronize; b200mc_event_elapsed_ms;
+ * b200mc_pool_trim; b200mc_diag_* (host results).  Functions return 0 on success, non-zero on failure;
  * b200mc_last_error() describes the last failure of the calling thread.  A handle is
  * not thread-safe; distinct handles are independent.  float32 / int32 / uint32 only,
  * flat vectors in sorted-site-name order (jax ravel_pytree order).
@@ -31,6 +42,10 @@ enum { B200MC_NUTS = 0, B200MC_HMC = 1 };
  * num_warmup/num_chains (mcmc.py:323-335) + the registered model family and its data
  * (the `model_args` of MCMC.run). */
 typedef struct {
+  /* sizeof(b200mc_config) of the CALLER's header: b200mc_create refuses a struct of another
+   * size (an older or newer binding) instead of reading fields at the wrong offsets.  Fields
+   * are only ever appended; B200MC_ABI_VERSION / b200mc_version() change with the layout. */
+  uint32_t struct_size;
   int family;
   int num_chains;
   /* data, device pointers:
@@ -132,6 +147,9 @@ typedef struct {
 } b200mc_collect;
 
 const char* b200mc_last_error(void);
+/* ABI version of the loaded library; a binding compares it with the B200MC_ABI_VERSION it was
+ * written against before calling anything else (numpyro_b200/_lib.py does). */
+#define B200MC_ABI_VERSION 2
 int b200mc_version(void);
 
 /* HMC.__init__ + the data binding of MCMC.run.  Raises (returns non-zero) for an

@@ -12,13 +12,16 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("B200MC_LIB") or os.path.join(_HERE, "libb200mc.so")
 
 
+ABI_VERSION = 2  # include/b200mc.h B200MC_ABI_VERSION
+
+
 class B200Error(RuntimeError):
     pass
 
 
 class Config(C.Structure):
     _fields_ = [
-        ("family", C.c_int), ("num_chains", C.c_int), ("N", C.c_int), ("ncols", C.c_int),
+        ("struct_size", C.c_uint32), ("family", C.c_int), ("num_chains", C.c_int), ("N", C.c_int), ("ncols", C.c_int),
         ("data0_dev", C.c_void_p), ("data1_dev", C.c_void_p),
         ("algo", C.c_int), ("step_size", C.c_float),
         ("adapt_step_size", C.c_int), ("adapt_mass_matrix", C.c_int), ("dense_mass", C.c_int),
@@ -127,6 +130,10 @@ def lib():
             fn = getattr(handle, name)
             fn.restype = res
             fn.argtypes = args
+        got = handle.b200mc_version()
+        if got != ABI_VERSION:
+            raise B200Error(f"{LIB_PATH} speaks ABI version {got}, this binding was written for "
+                            f"{ABI_VERSION} (include/b200mc.h B200MC_ABI_VERSION): rebuild the library")
         _lib = handle
     return _lib
 

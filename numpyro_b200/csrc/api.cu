@@ -88,7 +88,7 @@ struct b200mc_handle {
 constexpr int kBatchStepsPerSync = 16;
 
 extern "C" const char* b200mc_last_error(void) { return g_err.c_str(); }
-extern "C" int b200mc_version(void) { return 1; }
+extern "C" int b200mc_version(void) { return B200MC_ABI_VERSION; }
 extern "C" int64_t b200mc_kernel_launches(void) { return g_launches.load(); }
 
 // build_adaptation_schedule: hmc_util.py:387-436
@@ -347,6 +347,10 @@ extern "C" int b200mc_dim(const b200mc_handle* h) { return h ? h->D : -1; }
 extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   if (!cfg || !out) return fail("null argument");
   *out = nullptr;
+  if (cfg->struct_size != (uint32_t)sizeof(b200mc_config))
+    return fail("b200mc_config.struct_size = %u but this library's b200mc_config has %u bytes "
+                "(ABI version %d): the binding and the library are out of sync",
+                cfg->struct_size, (unsigned)sizeof(b200mc_config), B200MC_ABI_VERSION);
   const b200mc_config& c = *cfg;
   if (c.num_chains < 1) return fail("num_chains must be >= 1");
   if (c.algo != B200MC_NUTS && c.algo != B200MC_HMC)
@@ -1004,6 +1008,7 @@ extern "C" int b200mc_get_scalars(b200mc_handle* h, b200mc_chain_scalars* out_ho
   if (h->counters) {
     int err = 0;
     CK(cudaMemcpy(&err, h->counters + 3, sizeof(int), cudaMemcpyDeviceToHost));
+    if (err) CK(cudaMemset(h->counters + 3, 0, sizeof(int)));  // reported once, not sticky
     if (err == 2) return fail("cross-rank exchange timed out inside the streaming kernel");
     if (err) return fail("grid barrier timed out inside the streaming kernel");
   }
@@ -1167,7 +1172,8 @@ extern "C" int b200mc_gemm3xtf32(const float* A_dev, const float* B_dev, int M, 
     if (cudaGetLastError() != cudaSuccess) rc = fail("gemm3xtf32: reduce launch failed");
   }
   if (cudaStreamSynchronize(st) != cudaSuccess && !rc) rc = fail("gemm3xtf32: %s", cudaGetErrorString(cudaGetLastError()));
-  cudaFree(a_hi); cudaFree(a_lo); cudaFree(b_hi); cudaFree(b_lo); cudaFree(part);
+  dfree(a_hi); dfree(a_lo); dfree(b_hi); dfree(b_lo);  // build_image allocates from the pool
+  cudaFree(part);
   return rc;
 }
 

@@ -33,6 +33,21 @@ EXTRA_FIELDS = ("potential_energy", "energy", "num_steps", "accept_prob", "mean_
                 "diverging", "adapt_state.step_size")
 
 
+def _args_signature(args, kwargs):
+    """Cheap identity of model arguments: arrays by (address, shape, dtype, a few bytes)."""
+    def one(a):
+        if isinstance(a, np.ndarray):
+            flat = a.reshape(-1)
+            probe = flat[:: max(1, flat.size // 64)][:64].tobytes() if flat.size else b""
+            return ("nd", a.__array_interface__["data"][0], a.shape, str(a.dtype), probe)
+        try:
+            hash(a)
+            return ("h", a)
+        except TypeError:
+            return ("nd*", np.asarray(a).tobytes())
+    return (tuple(one(a) for a in args), tuple((k, one(v)) for k, v in sorted(kwargs.items())))
+
+
 def init_to_uniform(site=None, radius=2):
     """``numpyro/infer/initialization.py:95-129`` (marker: the draws happen on device)."""
     return ("uniform", float(radius))
@@ -130,6 +145,7 @@ class HMC(MCMCKernel):
         self._vectorized = False
         self._last_state = None
         self._row_shard = None  # (rank, nranks, allgather) -- see shard_rows
+        self._bound_sig = None  # identity of the model args the device handle was built from
 
     # ------------------------------------------------------------------ properties
     @property
@@ -189,10 +205,18 @@ class HMC(MCMCKernel):
 
     def __getstate__(self):  # hmc.py:818-822
         state = self.__dict__.copy()
+        # everything that only exists after init() -- device handle and buffers, the model bound
+        # to its data (holds closures), transports -- is dropped; init() rebuilds it
         for k in ("_sample_fn", "_init_fn", "_handle", "_data", "_last_state", "_postprocess_fn",
-                  "_row_shard"):
+                  "_row_shard", "_bound", "_potential_fn_gen", "_bound_sig"):
             state[k] = None
+        state["_model"] = self._model.__name__  # registry entries hold closures: pickle by name
         return state
+
+    def __setstate__(self, state):
+        self.__dict__.update(state)
+        if isinstance(self._model, str):
+            self._model = models.REGISTRY[self._model]
 
     def _part(self):
         return int(b2random.DEFAULT_PARTITIONABLE if self.partitionable is None
@@ -292,7 +316,7 @@ class HMC(MCMCKernel):
         depth = depth if isinstance(depth, tuple) else (depth, depth)
         kind, arg = self._strategy()
         cfg = _lib.Config(
-            family=bound.family, num_chains=num_chains, N=bound.N, ncols=bound.ncols,
+            struct_size=C.sizeof(_lib.Config), family=bound.family, num_chains=num_chains, N=bound.N, ncols=bound.ncols,
             data0_dev=d0.ptr, data1_dev=d1.ptr if d1 is not None else None,
             algo=0 if self._algo == "NUTS" else 1, step_size=float(self._step_size),
             adapt_step_size=int(bool(self._adapt_step_size)),
@@ -466,6 +490,7 @@ class HMC(MCMCKernel):
         keys = rng_key.reshape(-1, 2)
         bound = self._model.bind(*model_args, **model_kwargs)
         self._create(bound, keys.shape[0], num_warmup)
+        self._bound_sig = _args_signature(model_args, model_kwargs)
         kind, arg = self._strategy()
         if init_params is None and kind == "value":
             # initialization.py `init_to_value`: CONSTRAINED values per site.  The reference
@@ -493,7 +518,28 @@ class HMC(MCMCKernel):
         self._init_fn = True
         return self._to_state(sc, vec)
 
+    def _check_args(self, model_args, model_kwargs):
+        """The reference rebuilds the potential from the args on every call
+        (``hmc.py:806-816`` ``potential_fn_gen(*model_args)``); here the data lives in the
+        device handle, so new args after ``init`` are re-bound (new handle, same chain state)."""
+        if self._bound_sig is None or (not model_args and not model_kwargs):
+            return
+        sig = _args_signature(model_args, model_kwargs)
+        if sig == self._bound_sig:
+            return
+        state = self._last_state
+        bound = self._model.bind(*model_args, **model_kwargs)
+        if bound.dim != self._bound.dim or bound.trace_sites != self._bound.trace_sites:
+            raise ValueError("model arguments changed the latent sites; call `init` again")
+        self._create(bound, self._num_chains, self._num_warmup)
+        self._bound_sig = sig
+        self._sample_fn = self._sample_one
+        self._last_state = None
+        if state is not None:
+            self._push_state(state)
+
     def _sample_one(self, state, model_args, model_kwargs):
+        self._check_args(model_args, model_kwargs)
         self._push_state(state)
         _lib.check(_lib.lib().b200mc_sample(self._handle, 1, 1, 1, None, None))
         return self._to_state(*self._snapshot())
@@ -505,10 +551,12 @@ class HMC(MCMCKernel):
         return self._sample_one(state, model_args, model_kwargs)
 
     # ------------------------------------------------------------------ fused loop (fori_collect)
-    def run_loop(self, state, num_iters, collect_start, thinning, n_keep, fields):
+    def run_loop(self, state, num_iters, collect_start, thinning, n_keep, fields,
+                 model_args=(), model_kwargs=None):
         """Run ``num_iters`` transitions in ONE launch, collecting ``fields`` (a subset of
         ``("z",) + EXTRA_FIELDS``) exactly as ``fori_collect`` would
         (``numpyro/util.py:277-407``).  Returns ``(dict of [n_keep, C, ...] arrays, last state)``."""
+        self._check_args(model_args, model_kwargs or {})
         self._push_state(state)
         Cn, D = self._num_chains, self._bound.dim
         bufs, col = {}, _lib.Collect(n_keep=n_keep)

@@ -108,7 +108,7 @@ class MCMC(object):
 
         if hasattr(sampler, "run_loop"):
             raw, last_state = sampler.run_loop(init_state, upper, start_idx, thinning, n_keep,
-                                               device_fields)
+                                               device_fields, model_args=args, model_kwargs=kwargs)
             if not vectorized:
                 raw = {k: v[:, 0] for k, v in raw.items()}
             if "z" in raw:

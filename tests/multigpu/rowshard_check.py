@@ -40,7 +40,9 @@ def main():
     fields = ("num_steps", "potential_energy")
 
     kern = nb.infer.NUTS(nb.models.logistic_regression, **kw)
-    Xl, yl = D.shard_rows(kern, X, y)
+    from tools import torch_transport as TT
+
+    Xl, yl = D.shard_rows(kern, X, y, rank, world, TT.allgather_bytes())
     mc = nb.infer.MCMC(kern, num_warmup=0, num_samples=40)
     mc.run(key, Xl, yl, extra_fields=fields)
     ex = mc.get_extra_fields()

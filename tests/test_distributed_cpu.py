@@ -54,8 +54,10 @@ def _worker(rank, world, port, n_chains, out_path):
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     from numpyro_b200 import distributed as D
+    from tools import torch_transport as TT
 
-    samples, extras = D.run_sharded(_make_mcmc, _chain_keys(n_chains))
+    samples, extras = D.run_sharded(_make_mcmc, _chain_keys(n_chains), rank=rank, world_size=world,
+                                    gather=TT.gather())
     if rank == 0:
         np.save(out_path, samples)
     else:
@@ -78,6 +80,22 @@ def test_shard_bounds_cover_all_chains():
         D.shard_bounds(4, 2, 2)
     with pytest.raises(ValueError):
         D.shard_keys(np.zeros(2, np.uint32), 0, 1)
+
+
+def test_package_imports_no_communication_library():
+    # north_star: PyTorch is plumbing for bench/tests, never part of the product package
+    import subprocess
+
+    code = ("import sys; import numpyro_b200, numpyro_b200.distributed, numpyro_b200.infer; "
+            "bad = [m for m in sys.modules if m == 'torch' or m.startswith('torch.')]; "
+            "assert not bad, bad")
+    subprocess.check_call([sys.executable, "-c", code], cwd=ROOT)
+    src = open(os.path.join(ROOT, "numpyro_b200", "distributed.py")).read()
+    assert "import torch" not in src
+    from numpyro_b200 import distributed as D
+
+    with pytest.raises(ValueError):
+        D.run_sharded(_make_mcmc, _chain_keys(4), rank=0, world_size=2)
 
 
 @pytest.mark.parametrize("n_chains", [5, 8])

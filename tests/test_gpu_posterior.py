@@ -66,9 +66,13 @@ def test_eight_schools_matches_reference_readme(nb):
     assert abs(np.mean(-pe) - (-46.09)) < 0.5
 
 
-def _compare_with_oracle(nb, model, args, kwargs, fam, sites, chains, nw, ns, **kw):
+def _compare_with_oracle(nb, model, args, kwargs, fam, sites, chains, nw, ns, ns_dev=1000, **kw):
+    """Tier 4 (north_star): means / sds of the CUDA chains within 4 MCSE of the oracle's,
+    split r_hat < 1.01 on the CUDA chains.  The device draws ``ns_dev`` samples per chain (r_hat
+    of 4 x 300 draws is itself noisy at the 1 % level); the oracle's run length is what its
+    Python loops afford -- both enter the tolerance through their own MCSE."""
     key = T.PRNGKey(3)
-    mc = nb.infer.MCMC(nb.infer.NUTS(model, **kw), num_warmup=nw, num_samples=ns,
+    mc = nb.infer.MCMC(nb.infer.NUTS(model, **kw), num_warmup=nw, num_samples=ns_dev,
                        num_chains=chains, chain_method="vectorized")
     mc.run(key, *args, **kwargs)
     z_dev = mc.get_samples(group_by_chain=True)
@@ -77,12 +81,12 @@ def _compare_with_oracle(nb, model, args, kwargs, fam, sites, chains, nw, ns, **
     z_ora = res["z"]  # [chain, draw, D] unconstrained, flat sorted-site order
     off = 0
     for name, size, unconstrain in sites:
-        a = np.asarray(z_dev[name], np.float64).reshape(chains, ns, size)
+        a = np.asarray(z_dev[name], np.float64).reshape(chains, ns_dev, size)
         if unconstrain:
             a = np.log(a)
         for j in range(size):
             x, y = a[..., j], np.asarray(z_ora[..., off + j], np.float64)
-            assert nb.diagnostics.split_gelman_rubin(x) < 1.01 + 0.02, (name, j)
+            assert nb.diagnostics.split_gelman_rubin(x) < 1.01, (name, j)
             mx, _ = _mcse(x, nb)
             my, _ = _mcse(y, nb)
             tol = 4.0 * np.hypot(mx, my)

@@ -28,7 +28,10 @@ def test_library_exports_every_declared_symbol(nb):
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in b200mc.h but not exported"
     assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
-    assert lib.b200mc_version() == 1
+    m = re.search(r"#define\s+B200MC_ABI_VERSION\s+(\d+)", header)
+    assert lib.b200mc_version() == int(m.group(1)) == _lib.ABI_VERSION
+    # the ctypes mirror of b200mc_config starts with struct_size and matches the C layout
+    assert _lib.Config._fields_[0][0] == "struct_size"
     assert C.sizeof(_lib.ChainScalars) == _lib.SCALARS_DTYPE.itemsize
 
 
@@ -167,3 +170,21 @@ def test_diagnostics_known_answers(nb):
     s = D.summary({"a": np.random.default_rng(0).normal(size=(2, 100, 3))})
     assert s["a"]["r_hat"].shape == (3,)
     D.print_summary({"a": np.random.default_rng(0).normal(size=(2, 100, 3))})
+
+
+def test_kernel_pickles_after_binding_a_model(nb):
+    # hmc.py:818-822: the kernel (and so MCMC) pickles; what init() built is dropped
+    import pickle
+
+    from numpyro_b200 import models
+    from numpyro_b200.infer import MCMC, NUTS
+
+    for model in (models.logistic_regression, models.horseshoe_normal):
+        k = NUTS(model, step_size=0.5, dense_mass=False)
+        k._bound = model.bind(np.zeros((4, 3), np.float32), np.zeros(4, np.float32))
+        k._potential_fn_gen = k._bound
+        k2 = pickle.loads(pickle.dumps(k))
+        assert k2._model is model and k2._bound is None and k2._handle is None
+        assert k2._step_size == 0.5
+        m2 = pickle.loads(pickle.dumps(MCMC(k, num_warmup=3, num_samples=4)))
+        assert m2.num_samples == 4 and m2.sampler._model is model
