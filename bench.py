@@ -11,8 +11,11 @@ quantity the reference's own notebook divides by
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl own|reference]
 
-N > 1 (torchrun, one rank per GPU): chains are sharded over ranks, X replicated, no
-data-path collective ("weak" scaling); time is the max over ranks.
+N > 1 (torchrun, one rank per GPU): BASELINE configs[2]'s own partitioning -- ONE chain, the
+rows of X sharded over the ranks, the D+1 partial sums exchanged per leapfrog over NVLink peer
+memory inside the kernel ("strong" scaling); time is the max over ranks.  The line also carries
+a `replicas` sub-object: one independent chain per GPU, X replicated, no collective ("weak").
+`--sharding chains` makes the replicas the headline instead.
 
 ``--impl reference`` times the CPU restatement of the reference's algorithm (oracle/,
 C potential with OpenMP over all host cores): jax/numpyro cannot be imported in this image
@@ -137,7 +140,22 @@ def cpu_nuts_sample(X, y, budget_s, max_transitions, cores_note=True):
     return kern.num_grad_evals - g0, dt, n, fam.cores
 
 
+def base_config(args, world, rows):
+    """The workload description shared VERBATIM by both arms (the driver compares them)."""
+    return {"workload": "covtype-shape logistic NUTS N=581012 D=55 (configs[2])",
+            "chains": 1 if rows or world == 1 else world,
+            "transitions_per_step": args.transitions,
+            "adapt_transitions_untimed": args.adapt, "max_tree_depth": 10,
+            "sampler_key": "PRNGKey(1)", "threefry_partitionable": True,
+            "parallelism": (f"rows x{world} (one chain, per-leapfrog NVLink exchange)" if rows
+                            else f"chains x{world}")}
+
+
 def run_reference(args):
+    """The reference arm: the SAME run as the GPU arm -- `--adapt` untimed adaptation transitions
+    from PRNGKey(1), then steps of `--transitions` post-warm-up NUTS transitions at the adapted
+    step size and mass matrix -- by the oracle port (C potential, OpenMP over all host cores).
+    A step is cut short only if the whole run would pass `--ref-budget` seconds."""
     rank, world, _ = dist_env()
     if rank != 0:
         return 0
@@ -149,38 +167,50 @@ def run_reference(args):
     cpotentials.use_all_cores()  # torchrun exports OMP_NUM_THREADS=1
     fam = cpotentials.CLogistic(X, y)
     kern = ohmc.HMCKernel(fam, cfg=Config(np.float32, True))
-    state = kern.init(T.PRNGKey(1), 1000)
-    per_step = args.ref_transitions
-    budget = args.ref_budget  # seconds for the whole run: stop adding transitions to a step past it
     t_begin = time.perf_counter()
+    state = kern.init(T.PRNGKey(1), args.adapt)
+    for _ in range(args.adapt):
+        state = kern.sample(state)
+    adapt_s, adapt_grads = time.perf_counter() - t_begin, kern.num_grad_evals
+    per_step = args.ref_transitions or args.transitions
+    budget = args.ref_budget
+    cut = [False]
 
     def step(state):
-        g0, t0 = kern.num_grad_evals, time.perf_counter()
+        g0, t0, n = kern.num_grad_evals, time.perf_counter(), 0
         for _ in range(per_step):
             state = kern.sample(state)
+            n += 1
             if time.perf_counter() - t_begin > budget:
+                cut[0] = True
                 break
-        return state, kern.num_grad_evals - g0, time.perf_counter() - t0
+        return state, kern.num_grad_evals - g0, time.perf_counter() - t0, n
 
     for _ in range(args.warmup):
-        state, _, _ = step(state)
-    grads, secs = 0, 0.0
+        state, _, _, _ = step(state)
+    grads, secs, ntr = 0, 0.0, 0
     for _ in range(args.steps):
-        state, g, dt = step(state)
+        state, g, dt, n = step(state)
         grads += g
         secs += dt
+        ntr += n
     value = grads / secs
-    sample = (f"{args.steps} steps x <= {per_step} NUTS transitions from the init state with "
-              f"adaptation on ({grads} grad evals), full N={N_ROWS} D={N_COLS} data")
+    sample = (f"{args.steps} steps x {per_step} post-warm-up NUTS transitions ({ntr} transitions, "
+              f"{grads} grad evals, {secs:.1f} s) at the step size / mass matrix adapted over "
+              f"{args.adapt} untimed transitions ({adapt_grads} grad evals, {adapt_s:.1f} s), full "
+              f"N={N_ROWS} D={N_COLS} data" + ("; steps cut short by --ref-budget" if cut[0] else ""))
+    rows = args.sharding == "rows" and args.gpus > 1
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic",
-        "config": {"workload": "covtype-shape logistic NUTS N=581012 D=55 (configs[2])",
-                   "chains_per_gpu": 1, "max_tree_depth": 10,
-                   "reference_kind": "CPU restatement of numpyro HMC/NUTS (oracle/), "
-                                     "jax not importable in this image"},
+        "higher_is_better": True, "scaling": "strong" if rows else "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": base_config(args, args.gpus, rows),
+        "reference_kind": "CPU restatement of numpyro HMC/NUTS (oracle/, pinned bit for bit to the "
+                          "reference's sampler source), C potential with OpenMP; jax is not "
+                          "importable in this image, so NumPyro itself cannot run",
+        "adapted_step_size": float(state.adapt_state.step_size),
+        "mean_tree_size": grads / max(1, ntr),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": fam.cores, "kind": "port",
                          "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -653,8 +683,10 @@ def main():
     ap.add_argument("--fixed-step", type=float, default=0.0,
                     help="chain workloads: fixed step size, no adaptation (profiling aid)")
     ap.add_argument("--max-tree-depth", type=int, default=0)
-    ap.add_argument("--ref-transitions", type=int, default=2)
-    ap.add_argument("--ref-budget", type=float, default=150.0)
+    ap.add_argument("--ref-transitions", type=int, default=0,
+                    help="reference arm: transitions per step (0 = --transitions, the GPU arm's)")
+    ap.add_argument("--ref-budget", type=float, default=240.0,
+                    help="reference arm: seconds after which steps are cut short")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

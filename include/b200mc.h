@@ -189,10 +189,31 @@ int b200mc_comm_import(b200mc_handle* h, const void* all_host /*[nranks][128]*/)
  * (diagnostic). */
 int b200mc_get_profile(b200mc_handle* h, uint64_t* out_host /*[16]*/, int reset);
 
+/* Launch geometry of the streaming kernel of a handle (diagnostic): out[0] CTAs, [1] TMA ring
+ * stages, [2] tiles pinned in shared memory per CTA, [3] bytes per 32-row tile, [4] tiles,
+ * [5] dynamic shared memory bytes, [6] chains per launch, [7] reserved. */
+int b200mc_glm_layout(b200mc_handle* h, int* out_host /*[8]*/);
+
+/* Memory-roofline microbenchmark with the streaming kernel's access pattern (diagnostic; no
+ * reference counterpart): one persistent CTA per SM streams `bytes` of device memory in tiles
+ * of `tile_bytes` through an `n_stages` shared-memory ring with 1-D TMA bulk copies, `passes`
+ * times (odd passes backwards if reverse_odd).  Writes the achieved GB/s: the L2 roof when the
+ * buffer is L2-resident, the HBM read roof when it is several times the L2 size.  Synchronises. */
+int b200mc_membench(uint64_t bytes, int tile_bytes, int n_stages, int passes, int reverse_odd,
+                    float* gbs_host, void* stream);
+
 /* potential_energy + value_and_grad (infer/util.py:302-327, hmc_util.py:242-252) at
  * n points z[n][D]: tier-2 parity hook. */
 int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, int n, float* U_dev,
                               float* grad_dev, void* stream);
+
+/* Tier-2 hook of the streaming (tall-data logistic) kernel in the regime it is benchmarked in:
+ * the SAME point z[D] is evaluated on `passes` consecutive passes of ONE launch -- forward
+ * sweep, reversed sweep, forward, ... with the TMA ring wrapping and the L2-resident ping-pong
+ * in between -- and every pass's result is written: U_dev[passes], grad_dev[passes][D].  All
+ * passes must agree with the oracle (and with each other up to summation order). */
+int b200mc_potential_and_grad_passes(b200mc_handle* h, const float* z_dev, int passes,
+                                     float* U_dev, float* grad_dev, void* stream);
 
 /* jax.random on Threefry-2x32 (tier-1 parity hooks). */
 int b200mc_threefry2x32(const uint32_t* key_dev /*[n][2]*/, const uint32_t* ctr_dev /*[n][2]*/,

@@ -86,7 +86,10 @@ SYMBOLS = {
     "b200mc_get_profile": (_i, [_vp, _vp, _i]),
     "b200mc_comm_export": (_i, [_vp, _vp]),
     "b200mc_comm_import": (_i, [_vp, _vp]),
+    "b200mc_glm_layout": (_i, [_vp, C.POINTER(_i)]),
+    "b200mc_membench": (_i, [_u64, _i, _i, _i, _i, C.POINTER(_f), _vp]),
     "b200mc_potential_and_grad": (_i, [_vp, _vp, _i, _vp, _vp, _vp]),
+    "b200mc_potential_and_grad_passes": (_i, [_vp, _vp, _i, _vp, _vp, _vp]),
     "b200mc_threefry2x32": (_i, [_vp, _vp, _vp, _i, _vp]),
     "b200mc_random_split": (_i, [_vp, _i, _i, _vp, _i, _vp]),
     "b200mc_random_bits": (_i, [_vp, _i, _vp, _i, _vp]),

@@ -20,6 +20,7 @@
 #include "chain_kernel.cuh"
 #include "gemm3x_kernel.cuh"
 #include "glm_kernel.cuh"
+#include "membench.cuh"
 
 using namespace b200mc;
 
@@ -878,7 +879,7 @@ static int launch_batch(b200mc_handle* h, const CollectSpec& col, const uint32_t
 
 static int launch_glm(b200mc_handle* h, const CollectSpec& col, const uint32_t* keys, int user_init,
                       int chain, const float* eval_z, float* eval_U, float* eval_grad,
-                      cudaStream_t st) {
+                      cudaStream_t st, int eval_passes = 1) {
   GlmLaunch L;
   memset(&L, 0, sizeof(L));
   L.P = h->P; L.col = col; L.cs = h->cs; L.cv = h->cv;
@@ -903,7 +904,7 @@ static int launch_glm(b200mc_handle* h, const CollectSpec& col, const uint32_t* 
     }
   }
   L.init_keys = keys; L.user_init = user_init; L.chain = chain; L.C = h->C;
-  L.eval_z = eval_z; L.eval_U = eval_U; L.eval_grad = eval_grad;
+  L.eval_z = eval_z; L.eval_U = eval_U; L.eval_grad = eval_grad; L.eval_passes = eval_passes;
   CK(cudaMemsetAsync(h->counters, 0, sizeof(unsigned) * 3, st));  // arrive
   void* args[] = {&L};
   CK(cudaLaunchCooperativeKernel((const void*)glm_kernel, dim3(h->glm_ctas), dim3(kGlmThreads), args,
@@ -997,6 +998,74 @@ extern "C" int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, i
     g_launches++;
     CK(cudaGetLastError());
   }
+  return 0;
+}
+
+extern "C" int b200mc_potential_and_grad_passes(b200mc_handle* h, const float* z_dev, int passes,
+                                                float* U_dev, float* grad_dev, void* stream) {
+  if (!h || !z_dev || !U_dev || !grad_dev || passes < 1) return fail("bad argument");
+  if (h->cfg.family != B200MC_LOGISTIC || h->mode == 3)
+    return fail("multi-pass evaluation exists for the streaming (tall-data logistic) kernel only");
+  const CollectSpec col = make_collect(0, 0, 1, nullptr);
+  return launch_glm(h, col, nullptr, 0, 0, z_dev, U_dev, grad_dev, (cudaStream_t)stream, passes);
+}
+
+// ---------------------------------------------------------------- roofline microbenchmark
+extern "C" int b200mc_membench(uint64_t bytes, int tile_bytes, int n_stages, int passes,
+                               int reverse_odd, float* gbs_host, void* stream) {
+  if (!gbs_host || tile_bytes < 512 || (tile_bytes & 15) || passes < 1) return fail("membench: bad argument");
+  if (n_stages < kGlmConsumerWarps || n_stages > kGlmMaxStages || n_stages % kGlmConsumerWarps)
+    return fail("membench: n_stages must be a multiple of %d, at most %d", kGlmConsumerWarps, kGlmMaxStages);
+  cudaStream_t st = (cudaStream_t)stream;
+  int dev = 0, sms = 0, max_smem = 0;
+  CK(cudaGetDevice(&dev));
+  CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  CK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  const int smem = n_stages * tile_bytes + 2 * kGlmMaxStages * 8;
+  if (smem > max_smem) return fail("membench: ring of %d x %d bytes does not fit", n_stages, tile_bytes);
+  MemBenchLaunch L;
+  L.nt_total = (int)(bytes / (uint64_t)tile_bytes);
+  if (L.nt_total < sms) return fail("membench: buffer too small");
+  L.tile_bytes = tile_bytes; L.n_stages = n_stages; L.reverse_odd = reverse_odd;
+  unsigned char* buf = nullptr;
+  unsigned* sink = nullptr;
+  CK(dmalloc((void**)&buf, (size_t)L.nt_total * tile_bytes));
+  CK(dmalloc((void**)&sink, 512));
+  CK(cudaMemsetAsync(buf, 1, (size_t)L.nt_total * tile_bytes, st));
+  CK(cudaMemsetAsync(sink, 0, 512, st));
+  L.buf = buf; L.sink = sink;
+  CK(cudaFuncSetAttribute(membench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+  cudaEvent_t e0, e1;
+  CK(cudaEventCreate(&e0));
+  CK(cudaEventCreate(&e1));
+  L.passes = 2;  // warm-up: page in, fill L2
+  membench_kernel<<<sms, kGlmThreads, smem, st>>>(L);
+  L.passes = passes;
+  CK(cudaEventRecord(e0, st));
+  membench_kernel<<<sms, kGlmThreads, smem, st>>>(L);
+  CK(cudaEventRecord(e1, st));
+  g_launches += 2;
+  cudaError_t e = cudaEventSynchronize(e1);
+  float ms = 0.f;
+  if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  dfree(buf);
+  dfree(sink);
+  if (e != cudaSuccess) return fail("membench: %s", cudaGetErrorString(e));
+  *gbs_host = (float)((double)passes * L.nt_total * tile_bytes / (ms * 1e-3) / 1e9);
+  return 0;
+}
+
+// Launch geometry of the streaming (tall-data logistic) kernel of a handle: out[0] CTAs,
+// [1] ring stages, [2] pinned tiles per CTA, [3] tile bytes, [4] tiles, [5] dynamic smem bytes,
+// [6] chains per launch, [7] reserved.
+extern "C" int b200mc_glm_layout(b200mc_handle* h, int* out_host) {
+  if (!h || !out_host) return fail("null argument");
+  if (!h->glm_xt) return fail("handle does not run the streaming kernel");
+  out_host[0] = h->glm_ctas; out_host[1] = h->glm_stages; out_host[2] = h->glm_pinned;
+  out_host[3] = glm_tile_bytes(h->D); out_host[4] = h->glm_nt_total; out_host[5] = h->glm_smem;
+  out_host[6] = 1; out_host[7] = 0;
   return 0;
 }
 

@@ -81,10 +81,13 @@ struct GlmLaunch {
   int user_init;
   int chain;             // which chain of cs/cv this launch advances
   int C;
-  // eval mode (tier-2 hook): evaluate U, grad at eval_z and stop
+  // eval mode (tier-2 hook): evaluate U, grad at eval_z and stop.  eval_passes > 1 evaluates
+  // the SAME point on that many consecutive passes (forward sweep, reversed sweep, ... with the
+  // TMA ring wrapping in between) and writes every pass's result: eval_U[p], eval_grad[p][D]
   const float* eval_z;
   float* eval_U;
   float* eval_grad;
+  int eval_passes;
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -588,10 +591,10 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
       const float U = prior + llik;
       if (eval_mode) {
         if (cta == 0) {
-          for (int d = lane; d < D; d += 32) L.eval_grad[d] = lg[d];
-          if (lane == 0) *L.eval_U = U;
+          for (int d = lane; d < D; d += 32) L.eval_grad[(long)pass * D + d] = lg[d];
+          if (lane == 0) L.eval_U[pass] = U;
         }
-        sres = FINISHED;
+        sres = (pass + 1 < L.eval_passes) ? NEED_GRAD : FINISHED;
       } else {
         // the critical part only: bookkeeping of a continuing leaf is deferred below
 #ifdef B200MC_SAMPLER_PROF

@@ -596,6 +596,19 @@ class HMC(MCMCKernel):
         return U.numpy(), g.numpy()
 
 
+    def potential_and_grad_passes(self, z, passes):
+        """Tier-2 hook of the streaming kernel: the same point on ``passes`` consecutive passes
+        of one launch (forward / reversed sweeps, ring wrap).  Returns ``(U[passes],
+        grad[passes, D])``."""
+        z = np.ascontiguousarray(z, np.float32).reshape(self._bound.dim)
+        zd = _lib.DeviceArray.from_numpy(z)
+        U = _lib.DeviceArray((passes,), np.float32)
+        g = _lib.DeviceArray((passes, z.shape[0]), np.float32)
+        _lib.check(_lib.lib().b200mc_potential_and_grad_passes(self._handle, zd.ptr, int(passes),
+                                                               U.ptr, g.ptr, None))
+        return U.numpy(), g.numpy()
+
+
 class NUTS(HMC):
     """No-U-Turn Sampler (``hmc.py:825-948``)."""
 

@@ -1,0 +1,311 @@
+"""GPU parity AT THE BASELINE.json SHAPES -- the regime the kernels are benchmarked in.
+
+The shape-sweep tests elsewhere stop at 70,001 x 55 (logistic), 1000 x 130 x 256 (horseshoe) and
+64 chains (eight schools); at those sizes `glm_kernel`'s 20-stage TMA ring never wraps inside a
+pass and the reversed (odd-pass) sweep is never evaluated.  Here:
+
+* covtype shape 581,012 x 55 (configs[2]): tier 2 at three points, the SAME point on six
+  consecutive passes of one launch (forward / reversed sweeps, ~117 streamed + 5 pinned tiles
+  per CTA, the ring wrapping ~6 times per pass), tier 3 teacher-forced against the oracle with
+  the C potential, tier 4 (4 CUDA chains vs an oracle chain: 4 MCSE, r_hat < 1.01);
+* the lock-step tensor-core engine at 581,012 x 55 x 256 (persistent residual GEMM with the
+  MUFU-only `bce_logits_fast` epilogue) and 10,000 x 1000 x 256 (horseshoe, both likelihoods,
+  split-K 18, 79 row tiles): tier 2 against the float64 oracle;
+* eight schools with 16,384 vectorized chains (configs[1]): chains {0, 1, 8191, 16383} are
+  bit-identical to their single-chain runs;
+* tier 4 for stochastic volatility (T = 300: T = 3000 is out of reach of the oracle's Python
+  loops) and horseshoe.
+
+Counts that a tolerance would hide (teacher-forced tree / selection mismatches) are appended to
+gpurun_out/parity_counts.txt and committed under profiles/.
+"""
+import os
+import sys
+import time
+
+import numpy as np
+from numpy.testing import assert_allclose
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle import hmc as ohmc  # noqa: E402
+from oracle import potentials as opot  # noqa: E402
+from oracle import threefry as T  # noqa: E402
+from oracle.hmc_util import Config  # noqa: E402
+
+Y8 = np.array([28.0, 8.0, -3.0, 7.0, -1.0, 1.0, 18.0, 12.0])
+S8 = np.array([15.0, 10.0, 16.0, 11.0, 9.0, 11.0, 10.0, 18.0])
+
+
+@pytest.fixture(scope="module")
+def nb():
+    import __graft_entry__ as g
+
+    return g.build()
+
+
+@pytest.fixture(scope="module")
+def covtype():
+    from bench import make_covtype_shape
+
+    X, y = make_covtype_shape()
+    assert X.shape == (581012, 55)
+    return X, y
+
+
+@pytest.fixture(scope="module")
+def covtype_f64(covtype):
+    return opot.Logistic(covtype[0], covtype[1], np.float64)
+
+
+def _note(line):
+    d = os.path.join(ROOT, "gpurun_out")
+    os.makedirs(d, exist_ok=True)
+    with open(os.path.join(d, "parity_counts.txt"), "a") as fh:
+        fh.write(line.rstrip() + "\n")
+
+
+def _theta_star(d=55):
+    rng = np.random.default_rng(0)
+    rng.standard_normal((581012, d - 1), dtype=np.float32)  # advance like make_covtype_shape
+    return (rng.standard_normal(d) * 0.5).astype(np.float32)
+
+
+# ---------------------------------------------------------------- covtype shape, one chain
+def _covtype_kernel(nb, covtype, **kw):
+    k = nb.infer.NUTS(nb.models.logistic_regression, **kw)
+    k.init(nb.random.PRNGKey(0), 0, {"coefs": np.zeros(55, np.float32)}, covtype, {})
+    return k
+
+
+def test_tier2_covtype_shape(nb, covtype, covtype_f64):
+    k = _covtype_kernel(nb, covtype)
+    rng = np.random.default_rng(1)
+    zs = np.stack([rng.normal(size=55) * 0.05, _theta_star(), rng.normal(size=55) * 1.5]).astype(np.float32)
+    U, g = k.potential_and_grad(zs)
+    for i in range(3):
+        U0, g0 = covtype_f64.potential_and_grad(zs[i].astype(np.float64))
+        assert_allclose(U[i], U0, rtol=1e-5)
+        assert_allclose(g[i], g0, rtol=1e-5, atol=1e-5 * np.abs(g0).max())
+
+
+def test_tier2_covtype_every_pass_of_a_launch(nb, covtype, covtype_f64):
+    """Forward sweep, reversed sweep, ring phases after several wraps: the same point evaluated
+    on six consecutive passes of ONE launch must match the float64 oracle on every pass."""
+    k = _covtype_kernel(nb, covtype)
+    z = (_theta_star() + np.random.default_rng(2).normal(size=55).astype(np.float32) * 0.01)
+    U, g = k.potential_and_grad_passes(z, 6)
+    U0, g0 = covtype_f64.potential_and_grad(z.astype(np.float64))
+    for p in range(6):
+        assert_allclose(U[p], U0, rtol=1e-5, err_msg=f"pass {p}")
+        assert_allclose(g[p], g0, rtol=1e-5, atol=1e-5 * np.abs(g0).max(), err_msg=f"pass {p}")
+    # the passes differ from each other by summation order only
+    assert np.abs(U - U[0]).max() <= 4 * np.spacing(np.float32(U0))
+    assert np.abs(g - g[0]).max() <= 2e-6 * np.abs(g0).max()
+    # and a forward-only run of the same launch agrees too (B200MC_GLM_REVERSE=0)
+    os.environ["B200MC_GLM_REVERSE"] = "0"
+    try:
+        k2 = _covtype_kernel(nb, covtype)
+        U2, g2 = k2.potential_and_grad_passes(z, 3)
+    finally:
+        os.environ.pop("B200MC_GLM_REVERSE", None)
+    assert_allclose(U2, U0, rtol=1e-5)
+    assert_allclose(g2, np.broadcast_to(g0, g2.shape), rtol=1e-5, atol=1e-5 * np.abs(g0).max())
+
+
+def test_tier3_covtype_teacher_forced(nb, covtype):
+    """50 fixed-parameter transitions at covtype shape, teacher-forced: before every transition the
+    device is handed the oracle's state (C potential, all host cores), one transition runs on
+    each side.  Tree sizes and divergences must agree.  U ~ 2.9e5 has an f32 spacing of 0.03,
+    so a multinomial / slice comparison whose uniform draw falls inside that spacing can select a
+    different point of the SAME trajectory: such transitions are counted, must stay a minority,
+    and every other transition must agree to f32 round-off."""
+    from oracle import cpotentials
+    from test_refpin import _mirror_state
+
+    cpotentials.build()
+    cpotentials.use_all_cores()
+    X, y = covtype
+    fam = cpotentials.CLogistic(X, y)
+    kw = dict(step_size=0.12, inverse_mass_matrix=np.full(55, 1.2e-5, np.float32),
+              adapt_step_size=False, adapt_mass_matrix=False)
+    z0 = _theta_star()
+    ok = ohmc.HMCKernel(fam, cfg=Config(np.float32, True), **kw)
+    s = ok.init(T.PRNGKey(4), 0, init_params=z0)
+    kern = nb.infer.NUTS(nb.models.logistic_regression, **kw)
+    bound = nb.models.logistic_regression.bind(X, y)
+    c0 = kern.init(nb.random.PRNGKey(4), 0, {"coefs": z0}, (X, y), {})
+    assert_allclose(c0.potential_energy, s.potential_energy, rtol=1e-6)
+    n, tree_mismatch, pick_mismatch, grads = 50, [], [], 0
+    t0 = time.perf_counter()
+    for t in range(n):
+        nxt = ok.sample(s)
+        c = kern.sample(_mirror_state(nb, kern, bound, s), (X, y), {})
+        s = nxt
+        grads += int(nxt.num_steps)
+        if int(c.num_steps) != int(nxt.num_steps) or bool(c.diverging) != bool(nxt.diverging):
+            tree_mismatch.append(t)
+            continue
+        assert np.array_equal(c.rng_key, np.asarray(nxt.rng_key, np.uint32))
+        # mean over the SAME leaves of min(1, exp(-dE)); dE carries the 0.03 spacing of U
+        assert_allclose(c.accept_prob, nxt.accept_prob, atol=0.05)
+        zc = bound.ravel(c.z)
+        if not np.allclose(zc, nxt.z, rtol=0, atol=2e-5):
+            pick_mismatch.append(t)
+            continue
+        assert_allclose(c.potential_energy, nxt.potential_energy, rtol=1e-6)
+        assert_allclose(bound.ravel(c.z_grad), nxt.z_grad, rtol=1e-4,
+                        atol=1e-4 * np.abs(nxt.z_grad).max())
+    _note(f"tier3_covtype_teacher_forced transitions={n} grad_evals={grads} "
+          f"tree_mismatch={len(tree_mismatch)} selection_mismatch={len(pick_mismatch)} "
+          f"oracle_seconds={time.perf_counter() - t0:.1f}")
+    assert grads >= 3 * n, "trees are trivial: the test does not exercise the tree builder"
+    assert len(tree_mismatch) <= n // 10, tree_mismatch
+    assert len(pick_mismatch) <= n // 3, pick_mismatch
+
+
+def test_tier4_covtype_headline(nb, covtype):
+    """north_star tier 4 on the headline workload: 4 CUDA chains (300 warm-up + 1000 draws)
+    against one oracle chain (C potential; 300 + 700): every coefficient's mean within 4 MCSE,
+    sd within 25 %, split r_hat < 1.01 over the CUDA chains."""
+    from oracle import cpotentials
+
+    cpotentials.build()
+    cpotentials.use_all_cores()
+    X, y = covtype
+    mc = nb.infer.MCMC(nb.infer.NUTS(nb.models.logistic_regression), num_warmup=300,
+                       num_samples=1000, num_chains=4, chain_method="vectorized")
+    mc.run(nb.random.PRNGKey(2), X, y, extra_fields=("num_steps",))
+    a = np.asarray(mc.get_samples(group_by_chain=True)["coefs"], np.float64)  # [4, 1000, 55]
+    assert mc.get_extra_fields()["diverging"].mean() < 0.01
+    t0 = time.perf_counter()
+    ok = ohmc.HMCKernel(cpotentials.CLogistic(X, y), cfg=Config(np.float32, True))
+    res, _ = ohmc.run_chain(ok, T.PRNGKey(7), 300, 700)
+    b = np.asarray(res["z"], np.float64)[None]  # [1, 700, 55]
+    rhat = nb.diagnostics.split_gelman_rubin(a)
+    worst = 0.0
+    for j in range(55):
+        ess_a = float(nb.diagnostics.effective_sample_size(a[..., j]))
+        ess_b = float(nb.diagnostics.effective_sample_size(b[..., j]))
+        ma = a[..., j].std(ddof=1) / np.sqrt(max(ess_a, 1.0))
+        mb = b[..., j].std(ddof=1) / np.sqrt(max(ess_b, 1.0))
+        zscore = abs(a[..., j].mean() - b[..., j].mean()) / np.hypot(ma, mb)
+        worst = max(worst, zscore)
+        assert zscore < 4.0, (j, a[..., j].mean(), b[..., j].mean(), ma, mb)
+        assert abs(a[..., j].std() - b[..., j].std()) < 0.25 * b[..., j].std(), j
+    _note(f"tier4_covtype_headline max_split_rhat={rhat.max():.4f} worst_z={worst:.2f} "
+          f"oracle_grad_evals={ok.num_grad_evals} oracle_seconds={time.perf_counter() - t0:.1f} "
+          f"cuda_mean_tree={mc.get_extra_fields()['num_steps'].mean():.2f}")
+    assert rhat.max() < 1.01, rhat.max()
+
+
+# ---------------------------------------------------------------- lock-step engine, full shapes
+def test_batched_tier2_logistic_covtype_256(nb, covtype, covtype_f64):
+    """581,012 x 55 x 256 points through the persistent residual GEMM (`bce_logits_fast`:
+    ex2 / rcp / lg2.approx) and the split-K transposed contraction."""
+    X, y = covtype
+    k = nb.infer.NUTS(nb.models.logistic_regression)
+    k.init(T.split(T.PRNGKey(0), 256, True), 0, {"coefs": np.zeros((256, 55), np.float32)}, (X, y), {})
+    rng = np.random.default_rng(3)
+    scale = np.geomspace(0.01, 2.0, 256)[:, None]
+    zs = (rng.normal(size=(256, 55)) * scale).astype(np.float32)
+    zs[7] = _theta_star()
+    U, g = k.potential_and_grad(zs)
+    assert np.isfinite(U).all() and np.isfinite(g).all()
+    for i in (0, 7, 100, 127, 128, 200, 255):
+        U0, g0 = covtype_f64.potential_and_grad(zs[i].astype(np.float64))
+        assert_allclose(U[i], U0, rtol=1e-5, err_msg=f"point {i}")
+        assert_allclose(g[i], g0, rtol=1e-5, atol=1e-5 * np.abs(g0).max(), err_msg=f"point {i}")
+
+
+@pytest.mark.parametrize("likelihood", ["bernoulli", "normal"])
+def test_batched_tier2_horseshoe_config_shape(nb, likelihood):
+    """10,000 x 1000 x 256 (configs[3]): 79 row tiles, split-K 18."""
+    from test_gpu_batch_engine import make_horseshoe, model_of
+
+    X, Y = make_horseshoe(10000, 1000, likelihood)
+    k = nb.infer.NUTS(model_of(nb, likelihood))
+    fam = opot.Horseshoe(X, Y, likelihood, np.float64)
+    z0 = {"lambdas": np.zeros((256, 1000), np.float32), "tau": np.zeros((256, 1), np.float32),
+          "unscaled_betas": np.zeros((256, 1000), np.float32)}
+    if likelihood == "normal":
+        z0["prec_obs"] = np.zeros((256,), np.float32)
+    k.init(T.split(T.PRNGKey(0), 256, True), 0, z0, (X, Y), {})
+    rng = np.random.default_rng(4)
+    zs = (rng.normal(size=(256, fam.dim)) * 0.3).astype(np.float32)
+    U, g = k.potential_and_grad(zs)
+    assert np.isfinite(U).all() and np.isfinite(g).all()
+    for i in (0, 1, 127, 128, 255):
+        U0, g0 = fam.potential_and_grad(zs[i].astype(np.float64))
+        assert_allclose(U[i], U0, rtol=2e-5, err_msg=f"point {i}")
+        assert_allclose(g[i], g0, rtol=1e-4, atol=1e-4 * np.abs(g0).max(), err_msg=f"point {i}")
+
+
+# ---------------------------------------------------------------- eight schools, 16,384 chains
+def test_eight_schools_16384_chains_equal_their_single_chain_runs(nb):
+    C, nw, ns = 16384, 150, 50
+    key = T.PRNGKey(0)
+    mc = nb.infer.MCMC(nb.infer.NUTS(nb.models.eight_schools_noncentered), num_warmup=nw,
+                       num_samples=ns, num_chains=C, chain_method="vectorized")
+    mc.run(key, 8, S8, y=Y8, extra_fields=("num_steps",))
+    s = mc.get_samples(group_by_chain=True)
+    ex = mc.get_extra_fields(group_by_chain=True)
+    assert s["mu"].shape == (C, ns) and np.isfinite(s["mu"]).all()
+    keys = nb.random.split(key, C)
+    for c in (0, 1, 8191, 16383):
+        m1 = nb.infer.MCMC(nb.infer.NUTS(nb.models.eight_schools_noncentered), num_warmup=nw,
+                           num_samples=ns)
+        m1.run(keys[c], 8, S8, y=Y8, extra_fields=("num_steps",))
+        assert np.array_equal(m1.get_extra_fields()["num_steps"], ex["num_steps"][c]), c
+        for site in ("mu", "tau", "theta_base"):
+            assert np.array_equal(m1.get_samples()[site], s[site][c]), (c, site)
+    # posterior over all chains: README.md:121-123
+    assert abs(s["mu"].mean() - 4.08) < 0.4 and abs(s["tau"].mean() - 3.96) < 0.5
+
+
+# ---------------------------------------------------------------- tier 4: SV and horseshoe
+def _tier4(nb, model, args, fam, chains, nw, ns_dev, ns_ora, ora_chains, tag, **kw):
+    key = T.PRNGKey(3)
+    mc = nb.infer.MCMC(nb.infer.NUTS(model, **kw), num_warmup=nw, num_samples=ns_dev,
+                       num_chains=chains, chain_method="vectorized")
+    mc.run(key, *args)
+    kern = mc.sampler
+    zs = mc.get_samples(group_by_chain=True)
+    # back to the flat unconstrained vector the oracle works in
+    un = {k: (np.log(v) if k in kern._bound.positive else v) for k, v in zs.items()
+          if k in kern._bound.flat_sites}
+    a = np.asarray(kern._bound.ravel(un), np.float64)  # [chains, ns_dev, D]
+    res, _, _ = ohmc.run_mcmc(fam, T.PRNGKey(9), nw, ns_ora, num_chains=ora_chains,
+                              cfg=Config(np.float32, True), **kw)
+    b = np.asarray(res["z"], np.float64)
+    rhat = nb.diagnostics.split_gelman_rubin(a)
+    worst = 0.0
+    for j in range(a.shape[-1]):
+        ma = a[..., j].std(ddof=1) / np.sqrt(max(float(nb.diagnostics.effective_sample_size(a[..., j])), 1.0))
+        mb = b[..., j].std(ddof=1) / np.sqrt(max(float(nb.diagnostics.effective_sample_size(b[..., j])), 1.0))
+        zscore = abs(a[..., j].mean() - b[..., j].mean()) / np.hypot(ma, mb)
+        worst = max(worst, zscore)
+        assert zscore < 4.0, (tag, j, a[..., j].mean(), b[..., j].mean(), ma, mb)
+    _note(f"tier4_{tag} D={a.shape[-1]} max_split_rhat={rhat.max():.4f} worst_z={worst:.2f}")
+    assert rhat.max() < 1.01, (tag, rhat.max(), int(rhat.argmax()))
+
+
+def test_tier4_stochastic_volatility(nb):
+    from test_gpu_parity import make_sv
+
+    r = make_sv(300)
+    _tier4(nb, nb.models.stochastic_volatility, (r,), opot.StochasticVolatility(r), chains=32,
+           nw=600, ns_dev=4000, ns_ora=300, ora_chains=2, tag="sv_T300")
+
+
+def test_tier4_horseshoe(nb):
+    from test_gpu_batch_engine import make_horseshoe
+
+    X, Y = make_horseshoe(400, 8, "normal")
+    _tier4(nb, nb.models.horseshoe_normal, (X, Y), opot.Horseshoe(X, Y, "normal"), chains=32,
+           nw=500, ns_dev=4000, ns_ora=300, ora_chains=2, tag="horseshoe_400x8",
+           target_accept_prob=0.9)
