@@ -579,6 +579,16 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
       const int kb2 = b.RA1 / 32, tiles2 = b.RA2 / kGemmM;
       b.splits = h->num_sms / tiles2;
       if (b.splits < 1) b.splits = 1;
+      // The tensor core's f32 accumulator truncates instead of rounding to nearest: every MMA
+      // pulls the running sum towards zero by ~half an ulp, so a long accumulation chain drifts
+      // (covtype shape, 148 split-K ranges = 123 k-blocks = 1,476 MMAs per TMEM accumulator:
+      // every gradient component 2.5e-5 low against the float64 oracle, same sign --
+      // tests/test_gpu_baseline_shapes.py; at 5,000 rows the chain is 2 k-blocks and the bias
+      // is invisible).  Chains are therefore capped at kMaxChainKB k-blocks; the split partials
+      // are summed in f32 on the CUDA cores (round to nearest, fixed order).
+      constexpr int kMaxChainKB = 64;
+      const int need = (kb2 + kMaxChainKB - 1) / kMaxChainKB;
+      if (b.splits < need) b.splits = (need + b.splits - 1) / b.splits * b.splits;  // whole waves
       if (b.splits > kb2) b.splits = kb2;
       if (build_image((const float*)c.data0_dev, c.N, c.ncols, 0, b.RA1, b.K1, &b.x_hi, &b.x_lo, 0) ||
           build_image((const float*)c.data0_dev, c.N, c.ncols, 1, b.RA2, b.RA1, &b.xt_hi, &b.xt_lo, 0)) {
