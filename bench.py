@@ -223,14 +223,16 @@ def run_reference(args):
 # ---------------------------------------------------------------------------- GPU arm
 def run_own(args):
     import ctypes as C
+    import gc
 
     rank, world, local = dist_env()
     if world != args.gpus and world > 1:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     import __graft_entry__ as g
 
-    nb = g.build()
+    g.build()
     from numpyro_b200 import _lib, models
+    from numpyro_b200 import distributed as nbd
     from numpyro_b200.infer import MCMC, NUTS
     from numpyro_b200.random import PRNGKey, split
 
@@ -251,26 +253,15 @@ def run_own(args):
             dist.barrier()
         _lib.check(lib.b200mc_stream_synchronize(None))
 
-    def max_over_ranks(x):
+    def over_ranks(x, op):
         if dist is None:
             return x
         import torch
 
         t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=getattr(dist.ReduceOp, op))
         return float(t.item())
 
-    def sum_over_ranks(x):
-        if dist is None:
-            return x
-        import torch
-
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
-
-    X, y = make_covtype_shape()
-    # the e2e leg copies from PINNED host memory: move X, y into pinned allocations
     def pinned_copy(a):
         ptr = lib.b200mc_host_alloc(a.nbytes)
         if not ptr:
@@ -280,120 +271,201 @@ def run_own(args):
         out[...] = a
         return out
 
-    X, y = pinned_copy(X), pinned_copy(y)
-    # one chain per GPU: chain keys as MCMC.run would split them for `world` chains
-    rows = args.sharding == "rows" and world > 1
-    key = PRNGKey(1) if (world == 1 or rows) else split(PRNGKey(1), world)[rank]
+    Xfull, yfull = make_covtype_shape()
+    # the e2e leg copies from PINNED host memory
+    Xfull, yfull = pinned_copy(Xfull), pinned_copy(yfull)
     allgather = None
-    if rows:
-        # ONE chain over all GPUs: every rank keeps its row slice, sampler state replicated,
-        # D+1 partial sums exchanged per leapfrog over NVLink peer memory ("strong" scaling)
-        from numpyro_b200 import distributed as nbd
+    if world > 1:
+        from tools import torch_transport as TT
 
-        lo, hi = nbd.shard_bounds(N_ROWS, rank, world)
-        X, y = X[lo:hi], y[lo:hi]
-        allgather = nbd.allgather_bytes()
-
-    # ---- untimed: bind data, adaptation warm-up (dual averaging + Welford windows)
-    kern = NUTS(models.logistic_regression).shard_rows(rank, world if rows else 1, allgather)
-    mc = MCMC(kern, num_warmup=args.adapt, num_samples=args.transitions)
-    t0 = time.perf_counter()
-    mc.warmup(key, X, y, extra_fields=("num_steps",))
-    adapt_s = time.perf_counter() - t0
-    state = mc.post_warmup_state
-    adapted_step = float(np.asarray(state.adapt_state.step_size))
-    imm = np.asarray(next(iter(state.adapt_state.inverse_mass_matrix.values())), np.float32)
-
-    # ---- device-timed leg: inputs resident in HBM, one persistent launch per step,
-    #      CUDA events on the launching (null) stream
+        allgather = TT.allgather_bytes()
     T_ = args.transitions
-    ns_buf = _lib.DeviceArray((T_, 1), np.int32)
-    z_buf = _lib.DeviceArray((T_, 1, N_COLS), np.float32)
-    col = _lib.Collect(n_keep=T_, z_dev=z_buf.ptr, num_steps_dev=ns_buf.ptr)
-    ev0, ev1 = lib.b200mc_event_create(), lib.b200mc_event_create()
+    peak_hbm, peak_src = peaks()
 
-    draws = []
+    def layout_of(kern):
+        out = (C.c_int * 8)()
+        _lib.check(lib.b200mc_glm_layout(kern._handle, out))
+        return dict(zip(("ctas", "stages", "pinned_per_cta", "tile_bytes", "tiles", "smem_bytes",
+                         "chains_per_launch"), list(out)[:7]))
 
-    def device_step():
-        _lib.check(lib.b200mc_event_record(ev0, None))
-        _lib.check(lib.b200mc_sample(kern._handle, T_, 0, 1, C.byref(col), None))
-        _lib.check(lib.b200mc_event_record(ev1, None))
-        ms = C.c_float()
-        _lib.check(lib.b200mc_event_elapsed_ms(ev0, ev1, C.byref(ms)))
-        draws.append(z_buf.numpy()[:, 0, :].copy())
-        return float(ms.value), int(ns_buf.numpy().sum())
+    def device_leg(kind, X, y, key, chains=1, steps=None, warmup=None, kernel_kw=None, adapt=None,
+                   sample_clocks=False):
+        """`adapt` untimed adaptation transitions, then `steps` timed steps of T_ transitions, each
+        ONE b200mc_sample call on inputs resident in HBM, CUDA events on the launching stream.
+        kind: "single" (this GPU), "rows" (one chain over all ranks), "replicas" (a chain per rank)."""
+        steps = args.steps if steps is None else steps
+        warmup = args.warmup if warmup is None else warmup
+        adapt = args.adapt if adapt is None else adapt
+        rows = kind == "rows"
+        kern = NUTS(models.logistic_regression, **(kernel_kw or {})).shard_rows(
+            rank, world if rows else 1, allgather)
+        mc = MCMC(kern, num_warmup=adapt, num_samples=T_, num_chains=chains, chain_method="vectorized")
+        t0 = time.perf_counter()
+        mc.warmup(key, X, y, extra_fields=("num_steps",))
+        adapt_s = time.perf_counter() - t0
+        D = X.shape[1]
+        ns_buf = _lib.DeviceArray((T_, chains), np.int32)
+        z_buf = _lib.DeviceArray((T_, chains, D), np.float32)
+        col = _lib.Collect(n_keep=T_, z_dev=z_buf.ptr, num_steps_dev=ns_buf.ptr)
+        ev0, ev1 = lib.b200mc_event_create(), lib.b200mc_event_create()
+        draws = []
 
-    for _ in range(args.warmup):
-        device_step()
-    prof = (C.c_uint64 * 16)()
-    _lib.check(lib.b200mc_get_profile(kern._handle, prof, 1))  # reset the cycle counters
-    launches0 = lib.b200mc_kernel_launches()
-    clocks = ClockSampler(local) if rank == 0 else None
-    barrier()
-    step_ms, step_grads = [], []
-    draws.clear()
-    for _ in range(args.steps):
-        ms, gsum = device_step()
-        step_ms.append(ms)
-        step_grads.append(gsum)
-    barrier()
-    # second half of the metric: min bulk ESS of this rank's chain over the timed draws
-    from numpyro_b200.diagnostics import bulk_effective_sample_size, effective_sample_size
-    chain_draws = np.concatenate(draws, axis=0)[None]  # [1 chain, steps*T, D]
-    ess = None
-    if chain_draws.shape[1] >= 8:
-        ess = {"min_bulk_ess": float(np.min(bulk_effective_sample_size(chain_draws))),
-               "min_n_eff": float(np.min(effective_sample_size(chain_draws))),
-               "draws": int(chain_draws.shape[1])}
-    launches = lib.b200mc_kernel_launches() - launches0
-    _lib.check(lib.b200mc_get_profile(kern._handle, prof, 0))
-    passes = max(1, int(prof[4]))
-    breakdown = {k: float(prof[i]) / passes for i, k in
-                 enumerate(("stream", "arrival_wait", "grid_reduce", "sampler_step"))}
-    if any(prof[8 + i] for i in range(8)):
-        breakdown["sampler_sub"] = [float(prof[8 + i]) / passes for i in range(8)]
-        breakdown["control"] = {"prologue": float(prof[5]) / passes,
-                                "advance_fast_leaf": float(prof[6]) / passes,
-                                "advance_other": float(prof[7]) / passes}
-    total_ms = max_over_ranks(sum(step_ms))
-    if ess is not None:
-        # chains on different ranks are independent: ESS adds; a row-sharded chain is ONE chain
-        tot = ess["min_bulk_ess"] if rows else sum_over_ranks(ess["min_bulk_ess"])
-        ess.update({"metric": "min_bulk_ess_per_sec", "value": tot / (total_ms * 1e-3),
-                    "unit": "ESS/s", "note": "device-timed sampling phase, rank-normalised "
-                    "split-chain bulk ESS (SURVEY 8d); min_n_eff is the reference's estimator"})
-    total_grads = float(sum(step_grads)) if rows else sum_over_ranks(float(sum(step_grads)))
-    value = total_grads / (total_ms * 1e-3)
+        def device_step():
+            _lib.check(lib.b200mc_event_record(ev0, None))
+            _lib.check(lib.b200mc_sample(kern._handle, T_, 0, 1, C.byref(col), None))
+            _lib.check(lib.b200mc_event_record(ev1, None))
+            ms = C.c_float()
+            _lib.check(lib.b200mc_event_elapsed_ms(ev0, ev1, C.byref(ms)))
+            draws.append(z_buf.numpy())
+            return float(ms.value), int(ns_buf.numpy().sum())
 
-    # roofline of the dominant (only) kernel, this rank: algorithmic bytes per launch / duration
-    peak, peak_src = peaks()
+        for _ in range(warmup):
+            device_step()
+        prof = (C.c_uint64 * 16)()
+        _lib.check(lib.b200mc_get_profile(kern._handle, prof, 1))  # reset the cycle counters
+        launches0 = lib.b200mc_kernel_launches()
+        clocks = ClockSampler(local) if (sample_clocks and rank == 0) else None
+        barrier()
+        step_ms, step_grads = [], []
+        draws.clear()
+        for _ in range(steps):
+            ms, gsum = device_step()
+            step_ms.append(ms)
+            step_grads.append(gsum)
+        barrier()
+        clk = clocks.stop() if clocks is not None else None
+        launches = lib.b200mc_kernel_launches() - launches0
+        _lib.check(lib.b200mc_get_profile(kern._handle, prof, 0))
+        passes = max(1, int(prof[4]))
+        breakdown = {k: float(prof[i]) / passes for i, k in
+                     enumerate(("stream", "arrival_wait", "grid_reduce", "sampler_step"))}
+        breakdown["passes"] = passes
+        total_ms = over_ranks(sum(step_ms), "MAX")
+        local_grads = float(sum(step_grads))
+        total_grads = local_grads if kind != "replicas" else over_ranks(local_grads, "SUM")
+        # second half of the metric: min bulk ESS over the timed draws of this leg's chains
+        from numpyro_b200.diagnostics import (bulk_effective_sample_size, effective_sample_size,
+                                              split_gelman_rubin)
+
+        x = np.concatenate(draws, axis=0).transpose(1, 0, 2)  # [chain, draw, D]
+        ess = None
+        if x.shape[1] >= 8:
+            bulk = float(np.min(bulk_effective_sample_size(x)))
+            tot = bulk if kind != "replicas" else over_ranks(bulk, "SUM")  # independent chains add
+            ess = {"metric": "min_bulk_ess_per_sec", "value": tot / (total_ms * 1e-3), "unit": "ESS/s",
+                   "min_bulk_ess": tot, "min_n_eff": float(np.min(effective_sample_size(x))),
+                   "chains": chains if kind != "replicas" else chains * world,
+                   "draws_per_chain": int(x.shape[1]),
+                   "max_split_r_hat": (float(np.max(split_gelman_rubin(x.astype(np.float64))))
+                                       if x.shape[1] >= 4 else None),
+                   "note": "device-timed sampling phase, rank-normalised split-chain bulk ESS "
+                           "(SURVEY 8d); min_n_eff is the reference's estimator"}
+        st = mc.last_state if False else kern._last_state
+        return {"kind": kind, "kern": kern, "value": total_grads / (total_ms * 1e-3),
+                "total_ms": total_ms, "local_ms": sum(step_ms), "local_grads": local_grads,
+                "total_grads": total_grads, "step_ms": step_ms, "step_grads": step_grads,
+                "ess": ess, "breakdown": breakdown, "launches": int(launches), "clocks": clk,
+                "adapt_s": adapt_s, "state": st,
+                "adapted_step": np.atleast_1d(np.asarray(st.adapt_state.step_size, np.float64)),
+                "imm": np.asarray(next(iter(st.adapt_state.inverse_mass_matrix.values())), np.float32),
+                "layout": layout_of(kern)}
+
+    rows = args.sharding == "rows" and world > 1
+    if rows:
+        lo, hi = nbd.shard_bounds(N_ROWS, rank, world)
+        Xh, yh = Xfull[lo:hi], yfull[lo:hi]
+        head = device_leg("rows", Xh, yh, PRNGKey(1), sample_clocks=True)
+    elif world > 1:
+        Xh, yh = Xfull, yfull
+        head = device_leg("replicas", Xh, yh, split(PRNGKey(1), world)[rank], sample_clocks=True)
+    else:
+        Xh, yh = Xfull, yfull
+        head = device_leg("single", Xh, yh, PRNGKey(1), sample_clocks=True)
+    kern = head["kern"]
+    adapted_step = float(head["adapted_step"][0])
+    imm = head["imm"].reshape(-1, N_COLS)[0]
+
+    # ---- roofline of the dominant (only) kernel on this rank.  The re-tiled design matrix
+    #      (130.7 MB, minus the tiles pinned in shared memory) fits the 126 MB L2 and the ping-pong
+    #      sweep keeps it there, so the roof that binds is the L2 -> SM feed of this access pattern,
+    #      measured here with the kernel's own tile size and ring depth (b200mc_membench); the HBM
+    #      figures sit beside it: DRAM bytes per gradient from the committed ncu capture, and a run
+    #      on 2x the rows (out of L2) against the measured HBM copy peak.
+    lay = head["layout"]
     my_bytes = ALGO_BYTES_PER_GRAD / world if rows else ALGO_BYTES_PER_GRAD
-    my_gbs = my_bytes * sum(step_grads) / (sum(step_ms) * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "achieved": my_gbs, "peak": peak, "unit": "GB/s",
-                "frac": my_gbs / peak, "traffic": None, "peak_source": peak_src,
-                "kernel": "glm_kernel",
-                "bytes_per_grad_eval": ALGO_BYTES_PER_GRAD,
-                "grad_evals_per_launch": sum(step_grads) / max(1, len(step_grads)),
-                "us_per_grad_eval": 1e3 * sum(step_ms) / max(1, sum(step_grads))}
+    my_gbs = my_bytes * head["local_grads"] / (head["local_ms"] * 1e-3) / 1e9
+    streamed = (lay["tiles"] - lay["pinned_per_cta"] * lay["ctas"]) * lay["tile_bytes"]
+    l2_peak = None
+    if rank == 0:
+        gbs = C.c_float()
+        stages = lay["stages"] - lay["stages"] % 10 or 10
+        _lib.check(lib.b200mc_membench(max(streamed, 8 << 20), lay["tile_bytes"], min(stages, 30), 40, 1,
+                                       C.byref(gbs), None))
+        l2_peak = float(gbs.value)
+    traffic, traffic_src = None, None
     tr = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr):
         with open(tr) as f:
-            roofline["traffic"] = json.load(f).get("glm_kernel_bytes_per_grad_eval")
+            tj = json.load(f)
+        traffic = tj.get("glm_kernel_bytes_per_grad_eval")
+        traffic_src = {k: tj.get(k) for k in ("commit", "recipe", "captured") if k in tj}
+    roofline = {"bound": "l2", "achieved": my_gbs, "peak": l2_peak, "unit": "GB/s",
+                "frac": (my_gbs / l2_peak) if l2_peak else None,
+                "peak_source": "measured in this run: b200mc_membench, the kernel's access pattern "
+                               "(7.2 KB TMA tiles, same ring, ping-pong) on an L2-resident buffer of the "
+                               "streamed size",
+                "kernel": "glm_kernel", "bytes_per_grad_eval": ALGO_BYTES_PER_GRAD,
+                "streamed_bytes_per_pass": int(streamed),
+                "grad_evals_per_launch": head["local_grads"] / max(1, len(head["step_grads"])),
+                "us_per_grad_eval": 1e3 * head["local_ms"] / max(1.0, head["local_grads"]),
+                "traffic": traffic, "traffic_source": traffic_src,
+                "hbm": {"peak": peak_hbm, "peak_source": peak_src,
+                        "algorithmic_frac_of_hbm_peak": my_gbs / peak_hbm,
+                        "dram_frac": (traffic * head["local_grads"] / (head["local_ms"] * 1e-3) / 1e9 / peak_hbm
+                                      if traffic else None),
+                        "note": "algorithmic bytes / HBM peak exceeds 1 because ~90 % of every pass is "
+                                "served by L2; dram_frac is the DRAM traffic actually measured (ncu)"}}
 
-    # ---- end-to-end leg: public API (MCMC.run) with HOST buffers every step: X, y are
-    #      copied host->device inside the timed region, draws are read back
-    # (the clock sampler of the device leg is stopped first: nvidia-smi's start-up and its NVML
-    #  queries take driver locks that the many small driver calls of THIS leg wait on -- host
-    #  stalls of 50-200 ms per step were measured with it running; the device leg is timed with
-    #  CUDA events and does not see them)
-    clk = clocks.stop() if clocks is not None else None
-    clocks = None
-    if os.environ.get("B200MC_BENCH_E2E_SAMPLER"):
-        clocks = ClockSampler(local, 1000) if rank == 0 else None
+    # ---- out-of-L2 companion (1 GPU): the same model on 2x the rows (261 MB re-tiled, nothing
+    #      reusable across passes), one chain, against the measured HBM copy peak
+    out_of_l2 = None
+    if world == 1 and not args.no_out_of_l2:
+        X2 = np.concatenate([Xfull, Xfull], axis=0)
+        y2 = np.concatenate([yfull, yfull], axis=0)
+        big = device_leg("single", X2, y2, PRNGKey(1), steps=max(2, args.steps // 4), warmup=2, adapt=150)
+        b2 = 2 * ALGO_BYTES_PER_GRAD
+        gbs2 = b2 * big["local_grads"] / (big["local_ms"] * 1e-3) / 1e9
+        out_of_l2 = {"rows": int(X2.shape[0]), "bytes_per_grad_eval": b2,
+                     "grad_evals_per_sec": big["value"],
+                     "us_per_grad_eval": 1e3 * big["local_ms"] / max(1.0, big["local_grads"]),
+                     "roofline": {"bound": "hbm", "achieved": gbs2, "peak": peak_hbm, "unit": "GB/s",
+                                  "frac": gbs2 / peak_hbm, "peak_source": peak_src},
+                     "cta0_cycles_per_grad_eval": big["breakdown"], "layout": big["layout"]}
+        big["kern"]._destroy()
+        del X2, y2, big
+
+    # ---- parity check on the full data, after the timed region: U and grad of the CUDA path at
+    #      the chain's last position against one float64 oracle evaluation
+    parity = None
+    z_last = np.asarray(head["state"].z["coefs"], np.float32).reshape(-1, N_COLS)[:1]
+    Ud, gd = kern.potential_and_grad(z_last)  # every rank takes part when the rows are sharded
+    if rank == 0:
+        from oracle import potentials as opot
+
+        U0, g0 = opot.Logistic(Xfull, yfull, np.float64).potential_and_grad(z_last[0].astype(np.float64))
+        parity = {"max_rel_err_U": float(abs(Ud[0] - U0) / abs(U0)),
+                  "max_rel_err_grad": float(np.max(np.abs(gd[0] - g0)) / np.max(np.abs(g0))),
+                  "at": "last position of the timed chain, full N=581012 D=55 data",
+                  "oracle": "oracle.potentials.Logistic float64", "tolerance": 1e-5}
+        parity["ok"] = bool(parity["max_rel_err_U"] < 1e-5 and parity["max_rel_err_grad"] < 1e-5)
+
+    # ---- end-to-end leg: public API (MCMC.run) with HOST buffers every step: X, y are copied
+    #      host->device inside the timed region (pinned memory), re-tiled, the chain initialised,
+    #      T_ transitions run and the draws read back.  (No clock sampler here: nvidia-smi's NVML
+    #      queries take driver locks the many small driver calls of this leg wait on.)
     e2e_grads, e2e_s, e2e_ms = 0, 0.0, []
-    z_last = {k: np.asarray(v) for k, v in kern._last_state.z.items()}
-    import gc
-
+    z_last_d = {k: np.asarray(v) for k, v in head["state"].z.items()}
+    e2e_key = PRNGKey(1) if head["kind"] != "replicas" else split(PRNGKey(1), world)[rank]
     gc.collect()
     gc.disable()  # no collector pauses inside the timed host-side steps
     barrier()
@@ -403,7 +475,7 @@ def run_own(args):
                   adapt_step_size=False, adapt_mass_matrix=False).shard_rows(
                       rank, world if rows else 1, allgather)
         m2 = MCMC(k2, num_warmup=0, num_samples=T_)
-        m2.run(key, X, y, init_params=z_last, extra_fields=("num_steps",))
+        m2.run(e2e_key, Xh, yh, init_params=z_last_d, extra_fields=("num_steps",))
         ns = m2.get_extra_fields()["num_steps"]
         _ = m2.get_samples()["coefs"].mean()
         dt = time.perf_counter() - t0
@@ -414,25 +486,45 @@ def run_own(args):
             e2e_ms.append(round(dt * 1e3, 3))
     gc.enable()
     barrier()
-    e2e_s = max_over_ranks(e2e_s)
-    e2e_grads = float(e2e_grads) if rows else sum_over_ranks(float(e2e_grads))
+    e2e_s = over_ranks(e2e_s, "MAX")
+    e2e_grads = float(e2e_grads) if head["kind"] != "replicas" else over_ranks(float(e2e_grads), "SUM")
     e2e = {"value": e2e_grads / e2e_s, "unit": UNIT,
-           "h2d_bytes_per_step": int(X.nbytes + y.nbytes + 4 * N_COLS * 2 + 8),
+           "h2d_bytes_per_step": int(Xh.nbytes + yh.nbytes + 4 * N_COLS * 2 + 8),
            "d2h_bytes_per_step": int(T_ * (N_COLS * 4 + 4 + 4)),
            "ms_per_step": e2e_ms, "grad_evals_per_step": e2e_grads / max(1, len(e2e_ms))}
-    clk2 = clocks.stop() if clocks is not None else None
-    if clk is not None and clk2 is None and rank == 0:
-        # one reading right after the leg (never concurrently with it, see above)
-        probe = ClockSampler(local, 100)
+    clk = head["clocks"]
+    if clk is not None and rank == 0:
+        probe = ClockSampler(local, 100)  # one reading right after the leg (never during it)
         time.sleep(0.35)
         clk2 = probe.stop()
-    if clk is not None and clk2 is not None:
         clk["e2e_leg"] = clk2
         clk["reasons"] = sorted(set(clk["reasons"]) | set(clk2["reasons"]))
 
+    # ---- N > 1: the other partitioning as a sub-object (replicas when rows are the headline)
+    replicas = None
+    if rows:
+        rep = device_leg("replicas", Xfull, yfull, split(PRNGKey(1), world)[rank],
+                         steps=max(2, args.steps // 2), warmup=2)
+        replicas = {"scaling": "weak", "parallelism": f"chains x{world} (one chain per GPU, X replicated, "
+                    "no data-path collective)", "value": rep["value"], "unit": UNIT,
+                    "ms_per_step": rep["total_ms"] / len(rep["step_ms"]), "ess": rep["ess"]}
+        rep["kern"]._destroy()
+
+    # ---- 4 chains on ONE stream of X (glm_mc_kernel): the ESS half of the metric on one GPU
+    multi = None
+    if world == 1 and not args.no_multi_chain:
+        m4 = device_leg("single", Xfull, yfull, PRNGKey(1), chains=4, steps=max(3, args.steps // 2), warmup=2)
+        multi = {"chains": 4, "kernel": "glm_mc_kernel (4 chains per pass over X)",
+                 "grad_evals_per_sec": m4["value"], "vs_one_chain": m4["value"] / head["value"],
+                 "ms_per_step": m4["total_ms"] / len(m4["step_ms"]), "ess": m4["ess"],
+                 "cta0_cycles_per_pass": m4["breakdown"], "layout": m4["layout"],
+                 "gpu_launches": m4["launches"],
+                 "adapted_step_sizes": [float(v) for v in m4["adapted_step"]]}
+        m4["kern"]._destroy()
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        gr, dt, ntr, cores = cpu_nuts_sample(X, y, args.cpu_budget, 10**6)
+        gr, dt, ntr, cores = cpu_nuts_sample(Xfull, yfull, args.cpu_budget, 10**6)
         cpu = {"value": gr / dt, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"{ntr} NUTS transitions ({gr} grad evals, {dt:.1f} s) of the oracle "
                          f"from the init state on the full N={N_ROWS} D={N_COLS} data"}
@@ -441,21 +533,31 @@ def run_own(args):
         dist.destroy_process_group()
     if rank == 0:
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": head["total_ms"] / args.steps, "higher_is_better": True,
             "scaling": "strong" if rows else "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": "covtype-shape logistic NUTS N=581012 D=55 (configs[2])",
-                       "chains_per_gpu": 1, "transitions_per_step": T_,
-                       "adapt_transitions_untimed": args.adapt, "adapted_step_size": adapted_step,
-                       "max_tree_depth": 10, "parallelism": (f"rows x{world} (one chain, per-leapfrog NVLink exchange)" if rows
-                                       else f"chains x{world}"),
-                       "l2": "inputs 128.4 MB per pass > 126 MB L2, streamed once per grad eval"},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-            "clocks": clk, "adapt_seconds": adapt_s, "ess": ess,
-            "cta0_cycles_per_grad_eval": breakdown,
-            "mean_tree_size": float(np.mean(step_grads)) / T_,
+            "config": base_config(args, world, rows),
+            "config_detail": {"adapted_step_size": adapted_step, "layout": lay,
+                              "l2": "re-tiled inputs 130.7 MB per pass; the tiles not pinned in shared "
+                                    "memory (%.1f MB) stay L2-resident under the ping-pong sweep: DRAM "
+                                    "traffic is ~0.09x the algorithmic bytes (roofline.traffic)"
+                                    % (streamed / 1e6)},
+            "roofline": roofline, "out_of_l2": out_of_l2, "parity_check": parity,
+            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": head["launches"],
+            "clocks": clk, "adapt_seconds": head["adapt_s"], "ess": head["ess"],
+            "cta0_cycles_per_grad_eval": head["breakdown"],
+            "mean_tree_size": float(np.mean(head["step_grads"])) / T_,
         }
+        if rows:
+            bd = head["breakdown"]
+            line["exchange"] = {"note": "per-leapfrog serial chain at this rank count, SM cycles of CTA 0 "
+                                        "per gradient: grid arrival wait, fixed-order grid reduction, and the "
+                                        "sampler step that contains the NVLink (value, seq) exchange",
+                                "cycles": {k: bd[k] for k in ("arrival_wait", "grid_reduce", "sampler_step")}}
+            line["replicas"] = replicas
+        if multi is not None:
+            line["multi_chain"] = multi
         if world == 1 and not args.no_many_chain:
             line["many_chain"] = many_chain_leg()
         print(json.dumps(line))
@@ -668,8 +770,11 @@ def main():
     ap.add_argument("--workload", default="logistic",
                     choices=["logistic", "eight_schools", "sv", "horseshoe", "logistic_many"])
     ap.add_argument("--chains", type=int, default=0)
-    ap.add_argument("--sharding", default="chains", choices=["chains", "rows"],
-                    help="N>1: independent chains per GPU (weak) or one row-sharded chain (strong)")
+    ap.add_argument("--sharding", default="rows", choices=["chains", "rows"],
+                    help="N>1 headline: one row-sharded chain (strong, configs[2]'s partitioning; "
+                         "default) or independent chains per GPU (weak)")
+    ap.add_argument("--no-out-of-l2", action="store_true", help="skip the 2x-rows HBM-bound companion run")
+    ap.add_argument("--no-multi-chain", action="store_true", help="skip the 4-chains-on-one-stream leg")
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)

@@ -20,6 +20,7 @@
 #include "chain_kernel.cuh"
 #include "gemm3x_kernel.cuh"
 #include "glm_kernel.cuh"
+#include "glm_mc_kernel.cuh"
 #include "membench.cuh"
 
 using namespace b200mc;
@@ -61,6 +62,10 @@ struct b200mc_handle {
   unsigned* counters = nullptr;  // [0] arrive, [3] error
   unsigned long long* prof = nullptr;  // [kGlmProfSlots]
   int glm_reverse = 1;
+  // several chains on one stream (glm_mc_kernel.cuh): own ring / pinned split and partial buffer
+  bool glm_mc = false;
+  int mc_stages = 0, mc_pinned = 0, mc_smem = 0;
+  float* mc_partials = nullptr;  // [2][ctas][kMcChains][D+1]
   float* dense_replicas = nullptr;
   int* blk_tables = nullptr;  // structured mass matrix: blk_of, blk_pos, blk_perm [D] + size, dense [nb]
   // row sharding
@@ -327,7 +332,7 @@ extern "C" void b200mc_destroy(b200mc_handle* h) {
   dfree(h->cs);
   dfree(h->cv.z); dfree(h->cv.z_grad); dfree(h->cv.inverse_mass_matrix);
   dfree(h->cv.mass_matrix_sqrt); dfree(h->cv.welford_mean); dfree(h->cv.welford_m2);
-  dfree(h->work); dfree(h->partials); dfree(h->counters); dfree(h->prof); dfree(h->glm_xt);
+  dfree(h->work); dfree(h->partials); dfree(h->mc_partials); dfree(h->counters); dfree(h->prof); dfree(h->glm_xt);
   dfree(h->cv.dense); dfree(h->dense_replicas); dfree(h->M.scratch);
   dfree(h->blk_tables);
   for (int r = 0; r < h->nranks; ++r) {
@@ -544,6 +549,44 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
     if (c.dense_mass && ctas > 1)
       ACK(alloc((void**)&h->dense_replicas, sizeof(float) * 4 * (size_t)(ctas - 1) * D * D));
     if (const char* e = getenv("B200MC_GLM_REVERSE")) h->glm_reverse = atoi(e);
+    {
+      // 2+ chains (below the lock-step threshold): up to kMcChains chains share one stream of X
+      // per launch.  B200MC_GLM_MC=0 turns it off (one launch per chain, X streamed per chain);
+      // =1 forces it for a single chain too (parity aid: a chain alone through the same kernel).
+      int want = (C >= 2) ? 1 : 0;
+      if (const char* e = getenv("B200MC_GLM_MC")) want = atoi(e);
+      const bool can = D <= kMcMaxD && !c.dense_mass && !(c.nranks > 1) && P.num_blocks <= 1;
+      if (want && can) {
+        auto mfits = [&](int ns_, int np_) {
+          return glm_mc_smem_layout(D, ns_, np_, P.max_depth).total <= budget;
+        };
+        int mns = 2 * kMcConsumerWarps;
+        if (const char* e = getenv("B200MC_GLM_MC_STAGES")) {
+          const int v = atoi(e) / kMcConsumerWarps * kMcConsumerWarps;
+          if (v >= kMcConsumerWarps && v <= kGlmMaxStages) mns = v;
+        }
+        while (mns > kMcConsumerWarps && !mfits(mns, 0)) mns -= kMcConsumerWarps;
+        if (mfits(mns, 0)) {
+          int mnp = 0;
+          while (mnp < kGlmMaxStages && mfits(mns, mnp + 1)) ++mnp;
+          if (const char* e = getenv("B200MC_GLM_MC_PINNED")) {
+            const int v = atoi(e);
+            if (v >= 0 && v < mnp) mnp = v;
+          }
+          h->mc_stages = mns;
+          h->mc_pinned = mnp;
+          h->mc_smem = glm_mc_smem_layout(D, mns, mnp, P.max_depth).total;
+          ACK(cudaFuncSetAttribute(glm_mc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
+          int mocc = 0;
+          ACK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&mocc, glm_mc_kernel, kMcThreads, h->mc_smem));
+          if (mocc >= 1) {
+            ACK(alloc((void**)&h->mc_partials,
+                      sizeof(float) * 2 * (size_t)ctas * kMcChains * glm_partial_stride(D)));
+            h->glm_mc = true;
+          }
+        }
+      }
+    }
     h->nranks = c.nranks > 1 ? c.nranks : 1;
     h->rank = c.nranks > 1 ? c.rank : 0;
     if (h->nranks > kGlmMaxRanks || h->rank < 0 || h->rank >= h->nranks) {
@@ -923,6 +966,48 @@ static int launch_glm(b200mc_handle* h, const CollectSpec& col, const uint32_t* 
   return 0;
 }
 
+static int launch_glm_mc(b200mc_handle* h, const CollectSpec& col, const uint32_t* keys, int user_init,
+                         int chain0, int n_live, const float* eval_z, float* eval_U, float* eval_grad,
+                         cudaStream_t st) {
+  GlmMcLaunch L;
+  memset(&L, 0, sizeof(L));
+  L.P = h->P; L.col = col; L.cs = h->cs; L.cv = h->cv;
+  L.Xt = h->glm_xt;
+  L.N = h->cfg.N; L.D = h->D;
+  L.nt_total = h->glm_nt_total;
+  L.n_stages = h->mc_stages;
+  L.n_pinned = h->mc_pinned;
+  L.reverse_odd = h->glm_reverse;
+  L.partials = h->mc_partials;
+  L.arrive = h->counters + 0;
+  L.error = (int*)(h->counters + 3);
+  L.prof = h->prof;
+  L.init_keys = keys; L.user_init = user_init;
+  L.chain0 = chain0; L.n_live = n_live; L.C = h->C;
+  L.eval_z = eval_z; L.eval_U = eval_U; L.eval_grad = eval_grad;
+  CK(cudaMemsetAsync(h->counters, 0, sizeof(unsigned) * 3, st));
+  void* args[] = {&L};
+  CK(cudaLaunchCooperativeKernel((const void*)glm_mc_kernel, dim3(h->glm_ctas), dim3(kMcThreads), args,
+                                 (size_t)h->mc_smem, st));
+  g_launches++;
+  return 0;
+}
+
+// all chains of a tall-data logistic handle: groups of kMcChains on one stream, or one by one
+static int launch_glm_all(b200mc_handle* h, const CollectSpec& col, const uint32_t* keys, int user_init,
+                          cudaStream_t st) {
+  if (h->glm_mc) {
+    for (int c0 = 0; c0 < h->C; c0 += kMcChains) {
+      const int n = h->C - c0 < kMcChains ? h->C - c0 : kMcChains;
+      if (launch_glm_mc(h, col, keys, user_init, c0, n, nullptr, nullptr, nullptr, st)) return 1;
+    }
+    return 0;
+  }
+  for (int c = 0; c < h->C; ++c)
+    if (launch_glm(h, col, keys, user_init, c, nullptr, nullptr, nullptr, st)) return 1;
+  return 0;
+}
+
 extern "C" int b200mc_init(b200mc_handle* h, const uint32_t* keys_dev, const float* init_z_dev,
                            void* stream) {
   if (!h || !keys_dev) return fail("null argument");
@@ -941,8 +1026,7 @@ extern "C" int b200mc_init(b200mc_handle* h, const uint32_t* keys_dev, const flo
   if (h->mode == 3) {
     if (launch_batch(h, col, keys_dev, user_init, st)) return 1;
   } else if (h->cfg.family == B200MC_LOGISTIC) {
-    for (int c = 0; c < h->C; ++c)
-      if (launch_glm(h, col, keys_dev, user_init, c, nullptr, nullptr, nullptr, st)) return 1;
+    if (launch_glm_all(h, col, keys_dev, user_init, st)) return 1;
   } else {
     if (launch_chain(h, col, keys_dev, user_init, st)) return 1;
   }
@@ -959,11 +1043,7 @@ extern "C" int b200mc_sample(b200mc_handle* h, int num_iters, int collect_start,
   cudaStream_t st = (cudaStream_t)stream;
   const CollectSpec col = make_collect(num_iters, collect_start, thinning, out);
   if (h->mode == 3) return launch_batch(h, col, nullptr, 0, st);
-  if (h->cfg.family == B200MC_LOGISTIC) {
-    for (int c = 0; c < h->C; ++c)
-      if (launch_glm(h, col, nullptr, 0, c, nullptr, nullptr, nullptr, st)) return 1;
-    return 0;
-  }
+  if (h->cfg.family == B200MC_LOGISTIC) return launch_glm_all(h, col, nullptr, 0, st);
   return launch_chain(h, col, nullptr, 0, st);
 }
 
@@ -986,6 +1066,16 @@ extern "C" int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, i
       batch_potential_kernel<<<m, kBatchThreads, 0, st>>>(L, 1);
       g_launches++;
       CK(cudaGetLastError());
+    }
+    return 0;
+  }
+  if (h->cfg.family == B200MC_LOGISTIC && h->glm_mc) {  // kMcChains points per stream of X
+    const CollectSpec col = make_collect(0, 0, 1, nullptr);
+    for (int i0 = 0; i0 < n; i0 += kMcChains) {
+      const int m = n - i0 < kMcChains ? n - i0 : kMcChains;
+      if (launch_glm_mc(h, col, nullptr, 0, 0, m, z_dev + (long)i0 * h->D, U_dev + i0,
+                        grad_dev + (long)i0 * h->D, st))
+        return 1;
     }
     return 0;
   }
@@ -1075,7 +1165,8 @@ extern "C" int b200mc_glm_layout(b200mc_handle* h, int* out_host) {
   if (!h->glm_xt) return fail("handle does not run the streaming kernel");
   out_host[0] = h->glm_ctas; out_host[1] = h->glm_stages; out_host[2] = h->glm_pinned;
   out_host[3] = glm_tile_bytes(h->D); out_host[4] = h->glm_nt_total; out_host[5] = h->glm_smem;
-  out_host[6] = 1; out_host[7] = 0;
+  out_host[6] = h->glm_mc ? kMcChains : 1; out_host[7] = 0;
+  if (h->glm_mc) { out_host[1] = h->mc_stages; out_host[2] = h->mc_pinned; out_host[5] = h->mc_smem; }
   return 0;
 }
 

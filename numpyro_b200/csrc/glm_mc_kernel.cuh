@@ -1,0 +1,518 @@
+// Several chains on ONE stream of the design matrix (tall-data logistic family, 2..4 chains per
+// launch): the multi-chain form of glm_kernel (glm_kernel.cuh), the reference's
+// chain_method="vectorized" for this model (numpyro/infer/hmc.py:790-798: one X, all chains per
+// step).  Same data layout (32-row tiles), same ping-pong sweep and pinned tiles, same
+// deterministic grid exchange; what changes:
+//   * a row is split over FOUR lanes (lane = 8 * h + r: row r of an 8-row sub-tile, column
+//     groups h, h + 4, h + 8, h + 12), so a lane keeps, PER CHAIN, its 16-float slice of theta
+//     and 16 gradient accumulators in registers (4 chains: 128 registers); the row itself is
+//     streamed from shared memory twice per sub-tile (logits, then gradient) instead of being
+//     parked in registers.  The four partial logits of a row meet through a three-shuffle
+//     transpose-reduce that leaves lane h with the logit of chain h; lane h evaluates the
+//     Bernoulli term of chain h, and the four residuals of the row come back through four
+//     shuffles -- special-function work per (row, chain) as in the one-chain kernel.
+//   * 8 consumer warps + one control warp PER CHAIN = 12 warps, three per SM sub-partition, so
+//     every thread may use 168 registers (a 13th warp would cap them at 128).  There is
+//     therefore NO producer warp: every ring stage is owned by one consumer warp, which re-arms
+//     the stage's mbarrier and issues the TMA bulk copy of the stage's next tile itself, right
+//     after its last read of the stage.  Tile addresses do not depend on theta, so the ring
+//     still runs ahead across pass boundaries.
+//   * each control warp runs its own replica of the sampler step machine: chains are not
+//     synchronised at transition boundaries, a chain that has drawn its quota idles.  The serial
+//     tail of a leapfrog (grid arrival, reduction, sampler step) is paid once per pass for all
+//     chains.  CTA partials and the fixed-order grid reduction carry [chains][D+1] sums.
+// Per-chain arithmetic does not depend on how many chains share the launch: a chain run alone
+// through this kernel (the other control warps idle) is bit-identical to the same chain among
+// four (tests/test_gpu_multichain.py).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "glm_kernel.cuh"
+
+namespace b200mc {
+
+constexpr int kMcChains = 4;                        // chains per launch
+constexpr int kMcLanesPerRow = 4;
+constexpr int kMcRowsPerSub = 32 / kMcLanesPerRow;  // 8
+constexpr int kMcMaxGroups = 16;                    // D <= 64
+constexpr int kMcMaxD = 4 * kMcMaxGroups;
+constexpr int kMcConsumerWarps = 8;
+constexpr int kMcConsumerThreads = kMcConsumerWarps * 32;
+constexpr int kMcControlWarp0 = kMcConsumerWarps;                // warps 8..11
+constexpr int kMcThreads = (kMcConsumerWarps + kMcChains) * 32;  // 384
+constexpr int kMcRedGroups = 8;                                  // grid reduction: strided groups of CTAs
+
+struct GlmMcLaunch {
+  SamplerParams P;
+  CollectSpec col;
+  ChainScalars* cs;
+  ChainVectors cv;
+  const unsigned char* Xt;
+  int N, D, nt_total, n_stages, n_pinned, reverse_odd;
+  float* partials;   // [2][nCTA][kMcChains][PS]
+  unsigned* arrive;
+  int* error;
+  unsigned long long* prof;
+  const uint32_t* init_keys;
+  int user_init;
+  int chain0;        // first chain of this launch
+  int n_live;        // chains of this launch, 1..kMcChains (the other control warps idle)
+  int C;
+  const float* eval_z;  // eval mode (tier-2 hook): [n_live][D] points
+  float* eval_U;        // [n_live]
+  float* eval_grad;     // [n_live][D]
+};
+
+struct GlmMcSmem {
+  int stage_bytes, off_full, off_pin, off_theta, off_red, off_red2, off_work, off_flags, total;
+};
+
+__host__ __device__ inline GlmMcSmem glm_mc_smem_layout(int D, int n_stages, int n_pinned, int max_depth) {
+  GlmMcSmem s;
+  const int ps = glm_partial_stride(D);
+  s.stage_bytes = glm_tile_bytes(D);
+  int o = (n_stages + n_pinned) * s.stage_bytes;
+  s.off_full = o;  o += kGlmMaxStages * 8;
+  s.off_pin = o;   o += kGlmMaxStages * 8;
+  s.off_theta = o; o += kMcChains * kMcMaxD * 4;  // [chain][64] zero-padded
+  s.off_red = o;   o += kMcConsumerWarps * kMcChains * ps * 4;
+  s.off_red2 = o;  o += kMcRedGroups * kMcChains * ps * 4;
+  s.off_work = o;  o += kMcChains * num_slots(max_depth, 0) * D * 4;
+  o = (o + 15) & ~15;
+  s.off_flags = o; o += 64;
+  s.total = o;
+  return s;
+}
+
+__device__ __forceinline__ void mc_consumer_bar() {  // named barrier 1: consumer warps only
+  asm volatile("bar.sync 1, %0;" ::"n"(kMcConsumerThreads) : "memory");
+}
+__device__ __forceinline__ void mc_handoff_bar() {  // named barrier 2: consumers + all control warps
+  asm volatile("bar.sync 2, %0;" ::"n"(kMcConsumerThreads + 32 * kMcChains) : "memory");
+}
+
+// Bernoulli-logits term and residual on the special-function unit only (ex2 / rcp / lg2.approx;
+// every intermediate lies in [0, 2], so the approximations are absolute errors of ~1e-7, the size
+// of the f32 round-off of the exact formula) -- binary_cross_entropy_with_logits,
+// distributions/util.py:295-298; same arithmetic as the lock-step engine's epilogue.
+__device__ __forceinline__ void mc_bce_fast(float l, float y, float& term, float& res) {
+  float e, inv, lg;
+  const float t = fabsf(l) * -1.4426950408889634f;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
+  const float d = 1.0f + e;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(d));
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(d));
+  term = fmaf(-l, y, fmaf(lg, 0.6931471805599453f, fmaxf(l, 0.f)));
+  res = ((l >= 0.f) ? inv : e * inv) - y;
+}
+
+// The row is re-read from shared memory for the gradient phase: an ordinary load would be kept in
+// registers by the compiler across the two phases, next to the 64 + 64 registers of theta and
+// the accumulators (spills).
+__device__ __forceinline__ float4 mc_lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(addr)
+               : "memory");
+  return v;
+}
+
+// One 32-row tile = four 8-row sub-tiles.  `xaddr`: shared-memory address of the tile plus this
+// lane's (h, r) offset.  th[c][k]: chain c's theta for columns 4 (4k + h) .. + 3 (zero beyond D);
+// acc[c][4k + e]: this lane's share of chain c's gradient for column 4 (4k + h) + e; ll:
+// log-likelihood terms of chain h (this lane's chain).  Rows past N are zero in the tile image
+// (x = 0, label 0): their gradient contribution vanishes by itself, only ll is masked.  A lane
+// whose last column group lies beyond the matrix (4k + h >= G) reads group G - 1 instead: theta
+// is zero there, and the accumulators it feeds are never written out.
+template <int G>
+__device__ __forceinline__ void glm_mc_tile(uint32_t xaddr, const uint8_t* __restrict__ ys, int rows,
+                                            const float4 (&th)[kMcChains][(G + 3) / 4],
+                                            float (&acc)[kMcChains][4 * ((G + 3) / 4)], float& ll) {
+  constexpr int S = kMcLanesPerRow, RPW = kMcRowsPerSub, CB = kMcChains, GL = (G + 3) / 4;
+  constexpr int LASTH = G - 4 * (GL - 1);  // lanes h < LASTH hold a real column group at k = GL - 1
+  const int lane = threadIdx.x & 31, h = lane >> 3, r = lane & 7;
+  // byte offset of column group 4k + h relative to group h: k * 4 * 512; the last one is clamped
+  const uint32_t last_off = (LASTH == 4 || h < LASTH) ? (uint32_t)((GL - 1) * S * 512)
+                                                      : (uint32_t)((G - 1 - h) * 512);
+#pragma unroll
+  for (int t = 0; t < S; ++t) {
+    const uint32_t ra = xaddr + (uint32_t)(t * RPW * 16);
+    float2 a[CB];
+#pragma unroll
+    for (int k = 0; k < GL; ++k) {
+      const float4 x = mc_lds128(ra + ((k == GL - 1) ? last_off : (uint32_t)(k * S * 512)));
+#pragma unroll
+      for (int c = 0; c < CB; ++c) {
+        if (k == 0) a[c] = __fmul2_rn(make_float2(x.x, x.y), make_float2(th[c][k].x, th[c][k].y));
+        else a[c] = __ffma2_rn(make_float2(x.x, x.y), make_float2(th[c][k].x, th[c][k].y), a[c]);
+        a[c] = __ffma2_rn(make_float2(x.z, x.w), make_float2(th[c][k].z, th[c][k].w), a[c]);
+      }
+    }
+    float l[CB];
+#pragma unroll
+    for (int c = 0; c < CB; ++c) l[c] = a[c].x + a[c].y;
+    // transpose-reduce over the row's four lanes: lane h ends with the full logit of chain h,
+    // every chain summed as (p0 + p2) + (p1 + p3)
+    const bool up2 = (h & 2) != 0, up1 = (h & 1) != 0;
+    const float k0 = up2 ? l[2] : l[0], k1 = up2 ? l[3] : l[1];
+    const float s0 = up2 ? l[0] : l[2], s1 = up2 ? l[1] : l[3];
+    const float m0 = k0 + __shfl_xor_sync(0xffffffffu, s0, 16);
+    const float m1 = k1 + __shfl_xor_sync(0xffffffffu, s1, 16);
+    const float lm = (up1 ? m1 : m0) + __shfl_xor_sync(0xffffffffu, up1 ? m0 : m1, 8);
+    const int row = t * RPW + r;
+    const float yv = (float)ys[row];
+    float term, gm;
+    mc_bce_fast(lm, yv, term, gm);
+    ll += (row < rows) ? term : 0.f;
+    float gres[CB];
+#pragma unroll
+    for (int c = 0; c < CB; ++c) gres[c] = __shfl_sync(0xffffffffu, gm, c * RPW + r);
+#pragma unroll
+    for (int k = 0; k < GL; ++k) {
+      const float4 x = mc_lds128(ra + ((k == GL - 1) ? last_off : (uint32_t)(k * S * 512)));
+#pragma unroll
+      for (int c = 0; c < CB; ++c) {
+        const float2 g2 = make_float2(gres[c], gres[c]);
+        const float2 a01 = __ffma2_rn(g2, make_float2(x.x, x.y), make_float2(acc[c][4 * k], acc[c][4 * k + 1]));
+        const float2 a23 = __ffma2_rn(g2, make_float2(x.z, x.w), make_float2(acc[c][4 * k + 2], acc[c][4 * k + 3]));
+        acc[c][4 * k] = a01.x; acc[c][4 * k + 1] = a01.y;
+        acc[c][4 * k + 2] = a23.x; acc[c][4 * k + 3] = a23.y;
+      }
+    }
+  }
+}
+
+struct McRefill {  // where this warp's next TMA copy goes: position in the CTA's tile stream
+  int j, pass;
+};
+// One lane: put the next tile of `stage` in flight (positions of a warp advance by the
+// consumer-warp count; odd passes sweep the CTA's range backwards).
+__device__ __forceinline__ void mc_issue_fill(const GlmMcLaunch& L, unsigned char* smem, const GlmMcSmem& lay,
+                                              uint64_t* full, int stage, McRefill& rf, int tile0, int nt) {
+  const int jj = (L.reverse_odd && (rf.pass & 1)) ? (nt - 1 - rf.j) : rf.j;
+  const uint32_t tb = (uint32_t)lay.stage_bytes;
+  mbar_arrive_expect_tx(&full[stage], tb);
+  tma_load_1d(smem + (long)stage * lay.stage_bytes, L.Xt + (long)(tile0 + jj) * lay.stage_bytes, tb, &full[stage]);
+  rf.j += kMcConsumerWarps;
+  while (rf.j >= nt) { rf.j -= nt; ++rf.pass; }
+}
+
+// One pass worth of tiles for one consumer warp (stream position bookkeeping as in
+// glm_consume_pass); leaves the warp's partial sums in red[warp][chain][0..D].  Stage s is
+// consumed AND refilled by warp s % W; `nt` counts the CTA's streamed tiles, its last `n_pin`
+// tiles sit in the slots behind the ring for the whole launch (slot k consumed by warp k % W).
+template <int G>
+__device__ __forceinline__ void glm_mc_consume_pass(const GlmMcLaunch& L, unsigned char* smem,
+                                                    const GlmMcSmem& lay, int warp, long& p_next,
+                                                    long p_begin, long p_end, int& si, uint32_t& ph,
+                                                    int m, int tile0, int nt, bool rev, int n_pin,
+                                                    McRefill& rf) {
+  constexpr int S = kMcLanesPerRow, CB = kMcChains, GL = (G + 3) / 4;
+  const int lane = threadIdx.x & 31, h = lane >> 3, r = lane & 7;
+  const int PS = glm_partial_stride(L.D);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + lay.off_full);
+  uint64_t* pin = reinterpret_cast<uint64_t*>(smem + lay.off_pin);
+  const float4* th4 = reinterpret_cast<const float4*>(smem + lay.off_theta);
+  float4 th[CB][GL];
+#pragma unroll
+  for (int c = 0; c < CB; ++c)
+#pragma unroll
+    for (int k = 0; k < GL; ++k) th[c][k] = th4[c * kMcMaxGroups + k * S + h];  // zero beyond D
+  float acc[CB][4 * GL];
+#pragma unroll
+  for (int c = 0; c < CB; ++c)
+#pragma unroll
+    for (int k = 0; k < 4 * GL; ++k) acc[c][k] = 0.f;
+  float ll = 0.f;
+  const uint32_t lane_off = (uint32_t)((h * 32 + r) * 16);
+  int pin_k = warp, done = 0;
+  for (;;) {
+    const bool ring_left = p_next < p_end;
+    const bool pin_now = pin_k < n_pin && (done >= m || !ring_left);
+    if (!pin_now && !ring_left) break;
+    const unsigned char* sp;
+    int tile, stage = -1;
+    if (pin_now) {
+      mbar_wait(&pin[pin_k], 0u);  // completes once per launch
+      sp = smem + (long)(L.n_stages + pin_k) * lay.stage_bytes;
+      tile = tile0 + nt + pin_k;
+      pin_k += kMcConsumerWarps;
+    } else {
+      stage = warp + si * kMcConsumerWarps;
+      mbar_wait(&full[stage], ph);
+      sp = smem + (long)stage * lay.stage_bytes;
+      const int j = (int)(p_next - p_begin);
+      tile = tile0 + (rev ? (nt - 1 - j) : j);
+    }
+    const int rows = (tile == L.nt_total - 1) ? (L.N - 32 * tile) : 32;
+    glm_mc_tile<G>(smem_u32(sp) + lane_off, sp + G * 512, rows, th, acc, ll);
+    __syncwarp();
+    if (stage >= 0) {
+      // all lanes have read the stage: put its next tile in flight (owner warp = producer)
+      if (lane == 0) mc_issue_fill(L, smem, lay, full, stage, rf, tile0, nt);
+      p_next += kMcConsumerWarps;
+      if (++si == m) {
+        si = 0;
+        ph ^= 1u;
+      }
+    }
+    ++done;
+  }
+  // fold over the 8 row-lanes that share a column slice (butterfly: identical in all of them)
+#pragma unroll
+  for (int o = 1; o < kMcRowsPerSub; o <<= 1) ll += __shfl_xor_sync(0xffffffffu, ll, o);
+  float* red = reinterpret_cast<float*>(smem + lay.off_red) + warp * CB * PS;
+#pragma unroll
+  for (int c = 0; c < CB; ++c) {
+#pragma unroll
+    for (int k = 0; k < GL; ++k) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float v = acc[c][4 * k + e];
+#pragma unroll
+        for (int o = 1; o < kMcRowsPerSub; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        const int d = 4 * (k * S + h) + e;
+        if (r == 0 && d < L.D) red[c * PS + d] = v;
+      }
+    }
+  }
+  if (r == 0) red[h * PS + L.D] = ll;  // lane (h, 0): chain h's log-likelihood terms
+}
+
+__global__ void __launch_bounds__(kMcThreads, 1) glm_mc_kernel(const __grid_constant__ GlmMcLaunch L) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  constexpr int CB = kMcChains;
+  const int D = L.D, NS = L.n_stages, PS = glm_partial_stride(D);
+  const GlmMcSmem lay = glm_mc_smem_layout(D, NS, L.n_pinned, L.P.max_depth);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + lay.off_full);
+  uint64_t* pin = reinterpret_cast<uint64_t*>(smem + lay.off_pin);
+  float* th = reinterpret_cast<float*>(smem + lay.off_theta);
+  float* red = reinterpret_cast<float*>(smem + lay.off_red);
+  float* red2 = reinterpret_cast<float*>(smem + lay.off_red2);
+  // [3] spin ok, [4 + c] chain c still needs gradients
+  volatile int* flags = reinterpret_cast<volatile int*>(smem + lay.off_flags);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int cta = blockIdx.x, nCTA = gridDim.x;
+  const int tile0 = (int)((long)cta * L.nt_total / nCTA);
+  const int nt_all = (int)((long)(cta + 1) * L.nt_total / nCTA) - tile0;
+  const int n_pin = L.n_pinned < nt_all ? L.n_pinned : nt_all;  // pinned: the last n_pin tiles
+  const int nt = nt_all - n_pin;                                 // streamed through the ring
+  const long tb = lay.stage_bytes;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < NS; ++i) mbar_init(&full[i], 1);
+    for (int i = 0; i < L.n_pinned; ++i) mbar_init(&pin[i], 1);
+    for (int i = 0; i < 16; ++i) flags[i] = 0;
+    flags[3] = 1;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  for (int i = threadIdx.x; i < CB * kMcMaxD; i += blockDim.x) th[i] = 0.f;
+  for (int i = threadIdx.x; i < (kMcConsumerWarps + kMcRedGroups) * CB * PS; i += blockDim.x)
+    red[i] = 0.f;  // red and red2 are adjacent; their pad columns stay zero
+  __syncthreads();
+
+  const bool eval_mode = (L.eval_z != nullptr);
+
+  if (warp >= kMcControlWarp0) {
+    // ================= control warp c: the sampler replica of chain chain0 + c =================
+    const int c = warp - kMcControlWarp0;
+    const bool mine = c < L.n_live;
+    Sampler<WarpGroup> S;
+    StepResult sres = FINISHED;
+    float* work = reinterpret_cast<float*>(smem + lay.off_work) + (long)c * num_slots(L.P.max_depth, 0) * D;
+    float* thc = th + c * kMcMaxD;
+    const float* redc = red + c * PS;
+    S.setup(&L.P, WarpGroup{}, work, D, 1, L.chain0 + c, L.C, &L.col);
+    S.writer = (cta == 0);  // a replica in every CTA; only CTA 0 writes
+    if (mine) {
+      if (eval_mode) {
+        for (int d = lane; d < D; d += 32) S.v(LZ)[d] = L.eval_z[(long)c * D + d];
+        sres = NEED_GRAD;
+      } else {
+        S.load(L.cs, L.cv);
+        if (L.init_keys)
+          sres = S.begin_init(Key{L.init_keys[2 * (L.chain0 + c)], L.init_keys[2 * (L.chain0 + c) + 1]},
+                              L.user_init != 0);
+        else
+          sres = S.begin_sampling();
+      }
+      __syncwarp();
+      for (int d = lane; d < D; d += 32) thc[d] = S.v(LZ)[d];
+    }
+    if (lane == 0) flags[4 + c] = (sres == NEED_GRAD) ? 1 : 0;
+    mc_handoff_bar();  // theta of pass 0 is ready
+    if (sres == NEED_GRAD) S.prefetch_rng();
+    bool go = (flags[4] | flags[5] | flags[6] | flags[7]) != 0;
+    while (go) {
+      mc_handoff_bar();  // red[c][0..PS) holds chain c's grid-reduced sums
+      if (sres == NEED_GRAD) {
+        float* lz = S.v(LZ);
+        float* lg = S.v(LG);
+        float prior = 0.f, llik = 0.f;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const int d = lane + 32 * k;
+          if (d < D) {
+            const float t = lz[d];
+            lg[d] = t + redc[d];                          // grad U = theta + X^T (sigmoid - y)
+            prior += 0.5f * t * t + 0.9189385332046727f;  // -log N(theta; 0, 1)
+          }
+          llik += (d == D) ? redc[d] : 0.f;
+        }
+        WarpGroup{}.sum2(prior, llik);
+        const float U = prior + llik;
+        if (eval_mode) {
+          if (cta == 0) {
+            for (int d = lane; d < D; d += 32) L.eval_grad[(long)c * D + d] = lg[d];
+            if (lane == 0) L.eval_U[c] = U;
+          }
+          sres = FINISHED;
+        } else {
+          // the critical part only: bookkeeping of a continuing leaf is deferred below
+          sres = flags[3] ? S.advance_early(U) : FINISHED;
+        }
+        __syncwarp();
+        for (int d = lane; d < D; d += 32) thc[d] = S.v(LZ)[d];
+        if (lane == 0) flags[4 + c] = (sres == NEED_GRAD) ? 1 : 0;
+      }
+      mc_handoff_bar();  // theta of the next pass is ready (or stop)
+      // off the critical path, overlapped with the consumers' streaming of the next pass
+      if (mine) {
+        if (S.deferred) S.run_deferred();
+        if (sres == NEED_GRAD) S.prefetch_rng();
+      }
+      go = (flags[4] | flags[5] | flags[6] | flags[7]) != 0;
+    }
+    if (mine && !eval_mode) S.store(L.cs, L.cv);
+    return;
+  }
+
+  // ================= consumer warps =================
+  const int tid = threadIdx.x;  // 0 .. kMcConsumerThreads-1
+  const int m = NS / kMcConsumerWarps;
+  const int G = glm_groups(D);
+  const int CPS = CB * PS;
+  long p_next = warp;
+  int si = 0;
+  uint32_t ph = 0;
+  int pass = 0;
+  // this warp's stages (warp, warp + W, ...) and pinned slots: first copies
+  McRefill rf;
+  rf.j = warp;
+  rf.pass = 0;
+  if (lane == 0) {
+    for (int k = warp; k < n_pin; k += kMcConsumerWarps) {
+      mbar_arrive_expect_tx(&pin[k], (uint32_t)tb);
+      tma_load_1d(smem + (long)(NS + k) * tb, L.Xt + (long)(tile0 + nt + k) * tb, (uint32_t)tb, &pin[k]);
+    }
+    if (nt > 0) {
+      while (rf.j >= nt) { rf.j -= nt; ++rf.pass; }
+      for (int i = 0; i < m; ++i) mc_issue_fill(L, smem, lay, full, warp + i * kMcConsumerWarps, rf, tile0, nt);
+    }
+  }
+  mc_handoff_bar();  // theta of pass 0
+  long long t_mark = clock64();
+  unsigned long long c_stream = 0, c_wait = 0, c_reduce = 0, c_sampler = 0;
+  bool go = (flags[4] | flags[5] | flags[6] | flags[7]) != 0;
+  while (go) {
+    // ---- stream this CTA's tiles
+    const long p_begin = (long)pass * nt, p_end = p_begin + nt;
+    const bool rev = L.reverse_odd && (pass & 1);
+#define B200MC_MC_CASE(GG) \
+  case GG: glm_mc_consume_pass<GG>(L, smem, lay, warp, p_next, p_begin, p_end, si, ph, m, tile0, nt, rev, n_pin, rf); break;
+    switch (G) {
+      B200MC_MC_CASE(1) B200MC_MC_CASE(2) B200MC_MC_CASE(3) B200MC_MC_CASE(4)
+      B200MC_MC_CASE(5) B200MC_MC_CASE(6) B200MC_MC_CASE(7) B200MC_MC_CASE(8)
+      B200MC_MC_CASE(9) B200MC_MC_CASE(10) B200MC_MC_CASE(11) B200MC_MC_CASE(12)
+      B200MC_MC_CASE(13) B200MC_MC_CASE(14) B200MC_MC_CASE(15)
+      default: glm_mc_consume_pass<16>(L, smem, lay, warp, p_next, p_begin, p_end, si, ph, m, tile0, nt, rev, n_pin, rf); break;
+    }
+#undef B200MC_MC_CASE
+    mc_consumer_bar();
+    // ---- CTA partial: fixed-order sum over warps
+    float* my_partials = L.partials + ((long)(pass & 1) * nCTA + cta) * CPS;
+    if (tid < CPS) {
+      float a = 0.f;
+#pragma unroll
+      for (int w2 = 0; w2 < kMcConsumerWarps; ++w2) a += red[w2 * CPS + tid];
+      __stcg(&my_partials[tid], a);
+    }
+    mc_consumer_bar();
+    if (tid == 0) {
+      __threadfence();
+      red_release_add(L.arrive, 1u);
+      const long long t1 = clock64();
+      c_stream += (unsigned long long)(t1 - t_mark);
+      const bool ok = spin_until_ge(L.arrive, (unsigned)(pass + 1) * (unsigned)nCTA);
+      if (!ok) {
+        atomicExch(L.error, 1);
+        flags[3] = 0;
+      }
+      t_mark = clock64();
+      c_wait += (unsigned long long)(t_mark - t1);
+    }
+    mc_consumer_bar();
+    // ---- every CTA: grid reduction in a fixed order (128-bit L2 loads, all independent)
+    const float4* all4 = reinterpret_cast<const float4*>(L.partials + (long)(pass & 1) * nCTA * CPS);
+    const int CPS4 = CPS >> 2;
+    for (int item = tid; item < kMcRedGroups * CPS4; item += kMcConsumerThreads) {
+      const int c4 = item % CPS4, grp = item / CPS4;
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int b0 = grp; b0 < nCTA; b0 += kMcRedGroups * 10) {
+        float4 v[10];
+#pragma unroll
+        for (int i = 0; i < 10; ++i) {
+          const int b = b0 + kMcRedGroups * i;
+          v[i] = (b < nCTA) ? __ldcg(&all4[(long)b * CPS4 + c4]) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int i = 0; i < 10; ++i) {
+          a.x += v[i].x; a.y += v[i].y; a.z += v[i].z; a.w += v[i].w;
+        }
+      }
+      reinterpret_cast<float4*>(red2 + grp * CPS)[c4] = a;
+    }
+    mc_consumer_bar();
+    if (tid < CPS) {  // second stage, fixed order; red[0..CPS) is free again and feeds the control warps
+      float a = 0.f;
+#pragma unroll
+      for (int p2 = 0; p2 < kMcRedGroups; ++p2) a += red2[p2 * CPS + tid];
+      red[tid] = a;
+    }
+    long long t2 = 0;
+    if (tid == 0) {
+      t2 = clock64();
+      c_reduce += (unsigned long long)(t2 - t_mark);
+    }
+    mc_handoff_bar();  // sums -> control warps
+    mc_handoff_bar();  // control warps -> next theta
+    if (tid == 0) {
+      t_mark = clock64();
+      c_sampler += (unsigned long long)(t_mark - t2);
+    }
+    go = (flags[4] | flags[5] | flags[6] | flags[7]) != 0;
+    ++pass;
+  }
+  // drain: one copy per stage of this warp is still in flight (and the pinned copies, if no pass
+  // ever ran); shared memory must not be released under them
+  if (nt > 0)
+    for (int i = 0; i < m; ++i) {
+      mbar_wait(&full[warp + si * kMcConsumerWarps], ph);
+      if (++si == m) {
+        si = 0;
+        ph ^= 1u;
+      }
+    }
+  for (int k = warp; k < n_pin; k += kMcConsumerWarps) mbar_wait(&pin[k], 0u);
+  if (tid == 0 && cta == 0 && L.prof) {
+    atomicAdd(&L.prof[0], c_stream);
+    atomicAdd(&L.prof[1], c_wait);
+    atomicAdd(&L.prof[2], c_reduce);
+    atomicAdd(&L.prof[3], c_sampler);
+    atomicAdd(&L.prof[4], (unsigned long long)pass);
+  }
+}
+
+}  // namespace b200mc

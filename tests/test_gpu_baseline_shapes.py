@@ -216,15 +216,23 @@ def test_batched_tier2_logistic_covtype_256(nb, covtype, covtype_f64):
     zs[7] = _theta_star()
     U, g = k.potential_and_grad(zs)
     assert np.isfinite(U).all() and np.isfinite(g).all()
-    # Gradient tolerance 2e-5, not 1e-5: the tensor core's f32 accumulator truncates (no round to
-    # nearest), which pulls every component of X^T r towards zero in proportion to the length of
-    # the accumulation chain (api.cu kMaxChainKB; 2.5e-5 before the chains were capped).  The
-    # signed relative bias is recorded so that a regression is visible.
+    # Gradient tolerance: 2e-5 relative, not 1e-5 -- the tensor core's f32 accumulator truncates
+    # (no round to nearest), which pulls every component of X^T r towards zero in proportion to
+    # the length of the accumulation chain (api.cu kMaxChainKB; 2.5e-5 before the chains were
+    # capped) -- plus 2e-7 of sum_i |x_id| |r_i|, the condition of the sum: near the mode
+    # (point 7 = the generating coefficients) 581,012 terms of size ~0.4 cancel to a few hundred,
+    # and no f32 summation, the reference's included, resolves that to 1e-5 of the result.
+    # The signed relative bias of the large components is recorded so a regression is visible.
     worst = 0.0
+    Xa = np.abs(X).astype(np.float64)
     for i in (0, 7, 100, 127, 128, 200, 255):
-        U0, g0 = covtype_f64.potential_and_grad(zs[i].astype(np.float64))
+        z64 = zs[i].astype(np.float64)
+        U0, g0 = covtype_f64.potential_and_grad(z64)
+        res = 1.0 / (1.0 + np.exp(-(X.astype(np.float64) @ z64))) - y
+        cond = Xa.T @ np.abs(res)
         assert_allclose(U[i], U0, rtol=1e-5, err_msg=f"point {i}")
-        assert_allclose(g[i], g0, rtol=2e-5, atol=2e-5 * np.abs(g0).max(), err_msg=f"point {i}")
+        assert np.all(np.abs(g[i] - g0) <= 2e-5 * np.abs(g0) + 2e-7 * cond), \
+            (i, np.abs(g[i] - g0).max(), np.abs(g0).max(), cond.max())
         big = np.abs(g0) > 0.2 * np.abs(g0).max()
         worst = max(worst, float(np.abs((g[i][big] - g0[big]) / g0[big]).max()))
     _note(f"batched_tier2_logistic_covtype_256 max_rel_grad_err_large_components={worst:.2e}")
