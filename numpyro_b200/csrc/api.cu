@@ -16,12 +16,7 @@
 #include <dlfcn.h>
 
 #include "../../include/b200mc.h"
-#include "batch_kernel.cuh"
-#include "chain_kernel.cuh"
-#include "gemm3x_kernel.cuh"
-#include "glm_kernel.cuh"
-#include "glm_mc_kernel.cuh"
-#include "membench.cuh"
+#include "launchers.h"  // launch structs + the per-family translation units' launch wrappers
 
 using namespace b200mc;
 
@@ -285,42 +280,31 @@ int build_image(const float* src, int R_src, int K_src, int transpose, int R, in
   const size_t bytes = (size_t)R * K * 4;
   CK(dmalloc((void**)hi, bytes));
   CK(dmalloc((void**)lo, bytes));
-  image_build_kernel<<<1184, 256, 0, st>>>(src, R_src, K_src, transpose, R, K, *hi, *lo);
+  CK(kl::image_build_launch(src, R_src, K_src, transpose, R, K, *hi, *lo, st));
   g_launches++;
-  CK(cudaGetLastError());
   return 0;
 }
 int launch_gemm3x(const Gemm3xLaunch& L, int epi, cudaStream_t st) {
   static bool attr_set = false;
-  if (!attr_set) {
-    CK(cudaFuncSetAttribute(gemm3x_kernel<EPI_STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
-    CK(cudaFuncSetAttribute(gemm3x_kernel<EPI_RESID>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
-    attr_set = true;
-  }
   static int persist = -1, sms = 0;
-  if (persist < 0) {
+  if (!attr_set) {
+    CK(kl::gemm_prepare());
     const char* e = getenv("B200MC_GEMM_PERSIST");
     persist = e ? atoi(e) : 1;
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    CK(cudaFuncSetAttribute(gemm3x_resid_persistent_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPersistSmem));
-    CK(cudaFuncSetAttribute(gemm3x_resid_persistent_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPersistSmem));
+    attr_set = true;
   }
   const int grid = (L.RA / kGemmM) * L.splits;
   if (epi == EPI_RESID && persist && L.KB <= kPersistMaxKB && L.splits == 1) {
     // short inner dimension (logistic: K = 64): persistent CTAs, B resident, TMEM double-buffered
-    const int pgrid = grid < sms ? grid : sms;
-    if (L.likelihood == 1) gemm3x_resid_persistent_kernel<1><<<pgrid, kGemmThreads, kPersistSmem, st>>>(L);
-    else gemm3x_resid_persistent_kernel<0><<<pgrid, kGemmThreads, kPersistSmem, st>>>(L);
+    CK(kl::gemm3x_persistent_launch(L, grid < sms ? grid : sms, st));
     g_launches++;
-    CK(cudaGetLastError());
     return 0;
   }
-  if (epi == EPI_STORE) gemm3x_kernel<EPI_STORE><<<grid, kGemmThreads, kGemmSmem, st>>>(L);
-  else gemm3x_kernel<EPI_RESID><<<grid, kGemmThreads, kGemmSmem, st>>>(L);
+  CK(kl::gemm3x_launch(L, epi, grid, st));
   g_launches++;
-  CK(cudaGetLastError());
   return 0;
 }
 }  // namespace
@@ -497,11 +481,9 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
     const int nt_total = (c.N + kGlmTileRows - 1) / kGlmTileRows;
     h->glm_nt_total = nt_total;
     ACK(dmalloc((void**)&h->glm_xt, (size_t)nt_total * glm_tile_bytes(D)));
-    glm_retile_kernel<<<h->num_sms * 8, 256>>>((const float*)c.data0_dev,
-                                                (const uint8_t*)c.data1_dev, c.N, D, nt_total,
-                                                h->glm_xt);
+    ACK(kl::glm_retile(h->num_sms * 8, (const float*)c.data0_dev, (const uint8_t*)c.data1_dev, c.N, D,
+                       nt_total, h->glm_xt, 0));
     g_launches++;
-    ACK(cudaGetLastError());
     ACK(cudaDeviceSynchronize());
     int ctas = nt_total < h->num_sms ? nt_total : h->num_sms;
     h->glm_ctas = ctas;
@@ -539,9 +521,8 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
     h->glm_stages = ns;
     h->glm_pinned = np;
     h->glm_smem = glm_smem_layout(D, ns, np, P.max_depth, P.dense_mass).total;
-    ACK(cudaFuncSetAttribute(glm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     int occ = 0;
-    ACK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, glm_kernel, kGlmThreads, h->glm_smem));
+    ACK(kl::glm_prepare(h->max_smem, h->glm_smem, &occ));
     if (occ < 1) { b200mc_destroy(h); return fail("logistic kernel does not fit on an SM"); }
     ACK(alloc((void**)&h->partials, sizeof(float) * 2 * (size_t)ctas * glm_partial_stride(D)));
     ACK(alloc((void**)&h->counters, sizeof(unsigned) * 8));
@@ -576,9 +557,8 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
           h->mc_stages = mns;
           h->mc_pinned = mnp;
           h->mc_smem = glm_mc_smem_layout(D, mns, mnp, P.max_depth).total;
-          ACK(cudaFuncSetAttribute(glm_mc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
           int mocc = 0;
-          ACK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&mocc, glm_mc_kernel, kMcThreads, h->mc_smem));
+          ACK(kl::glm_mc_prepare(h->max_smem, h->mc_smem, &mocc));
           if (mocc >= 1) {
             ACK(alloc((void**)&h->mc_partials,
                       sizeof(float) * 2 * (size_t)ctas * kMcChains * glm_partial_stride(D)));
@@ -736,15 +716,14 @@ static int launch_chain(b200mc_handle* h, const CollectSpec& col, const uint32_t
   }
   if (h->mode == 0) {
     const int threads = 64;  // small blocks spread the chains over all SMs
-    chain_kernel<0><<<(h->C + threads - 1) / threads, threads, 0, st>>>(L);
+    CK(kl::chain_launch(0, L, (h->C + threads - 1) / threads, threads, st));
   } else if (h->mode == 1) {
     const int wpb = 4;
-    chain_kernel<1><<<(h->C + wpb - 1) / wpb, wpb * 32, 0, st>>>(L);
+    CK(kl::chain_launch(1, L, (h->C + wpb - 1) / wpb, wpb * 32, st));
   } else {
-    chain_kernel<2><<<h->C, kChainCtaThreads, 0, st>>>(L);
+    CK(kl::chain_launch(2, L, h->C, kChainCtaThreads, st));
   }
   g_launches++;
-  CK(cudaGetLastError());
   return 0;
 }
 
@@ -815,11 +794,11 @@ static int factor_chain_dense(float* mats, int D, int n, int regularize, cudaStr
     S->host_work = malloc(host_b);
     S->host_bytes = host_b;
   }
-  factor_cov_kernel<<<592, 256, 0, st>>>(mats, D, (float)n, regularize);
+  CK(kl::factor_cov_launch(mats, D, (float)n, regularize, st));
   // row-major symmetric W == column-major W; LOWER (column-major) leaves Lc[a][b] at W[b*D + a]
   if (S->potrf(S->handle, CUBLAS_FILL_MODE_LOWER, D, W, D, (float*)S->work, lwork, S->info) != CUSOLVER_STATUS_SUCCESS)
     return fail("cusolverDnSpotrf failed");
-  factor_tinv_kernel<<<592, 256, 0, st>>>(mats, D);
+  CK(kl::factor_tinv_launch(mats, D, st));
   CK(cudaMemcpyAsync(W, m2, sizeof(float) * DD, cudaMemcpyDeviceToDevice, st));  // mass_matrix_sqrt_inv
   CK(cudaMemsetAsync(m2, 0, sizeof(float) * DD, st));                             // Welford restarts
   // row-major lower tril_inv == column-major UPPER of its transpose: inverting that in place
@@ -877,22 +856,23 @@ static int launch_batch(b200mc_handle* h, const CollectSpec& col, const uint32_t
   const size_t mv_smem = sizeof(float) * 2 * (size_t)h->D;
   // a chain needs at most three sweeps between two gradients (leaf, then the two of a
   // transition start); chains that still wait afterwards simply continue in the next step
-  auto sweeps_and_resumes = [&](unsigned* count_slot) {
+  auto sweeps_and_resumes = [&](unsigned* count_slot) -> int {
     for (int k = 0; k < 3; ++k) {
-      batch_matvec_kernel<<<mv_grid, kMatvecThreads, mv_smem, st>>>(L);
+      CK(kl::batch_matvec_launch(L, mv_grid, mv_smem, st));
       L.kind = BATCH_RESUME;
       L.active = (k == 2) ? count_slot : slot_scrap;
-      batch_step_kernel<<<h->C, kBatchThreads, 0, st>>>(L);
+      CK(kl::batch_step_launch(L, h->C, st));
       g_launches += 2;
     }
+    return 0;
   };
   CK(cudaMemsetAsync(b.active, 0, sizeof(unsigned) * (kBatchStepsPerSync + 2), st));
   L.kind = BATCH_BEGIN;
   L.active = dense ? slot_scrap : slot_begin;
-  batch_step_kernel<<<h->C, kBatchThreads, 0, st>>>(L);
+  CK(kl::batch_step_launch(L, h->C, st));
   g_launches++;
   L.init_keys = nullptr;
-  if (dense) sweeps_and_resumes(slot_begin);
+  if (dense && sweeps_and_resumes(slot_begin)) return 1;
   CK(cudaGetLastError());
   unsigned active = 0;
   CK(cudaMemcpyAsync(&active, slot_begin, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
@@ -903,9 +883,9 @@ static int launch_batch(b200mc_handle* h, const CollectSpec& col, const uint32_t
       if (launch_batch_gemms(h, st)) return 1;
       L.kind = BATCH_GRAD;
       L.active = dense ? slot_scrap : b.active + i;
-      batch_step_kernel<<<h->C, kBatchThreads, 0, st>>>(L);
+      CK(kl::batch_step_launch(L, h->C, st));
       g_launches++;
-      if (dense) sweeps_and_resumes(b.active + i);
+      if (dense && sweeps_and_resumes(b.active + i)) return 1;
     }
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(&active, b.active + kBatchStepsPerSync - 1, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
@@ -959,9 +939,7 @@ static int launch_glm(b200mc_handle* h, const CollectSpec& col, const uint32_t* 
   L.init_keys = keys; L.user_init = user_init; L.chain = chain; L.C = h->C;
   L.eval_z = eval_z; L.eval_U = eval_U; L.eval_grad = eval_grad; L.eval_passes = eval_passes;
   CK(cudaMemsetAsync(h->counters, 0, sizeof(unsigned) * 3, st));  // arrive
-  void* args[] = {&L};
-  CK(cudaLaunchCooperativeKernel((const void*)glm_kernel, dim3(h->glm_ctas), dim3(kGlmThreads), args,
-                                 (size_t)h->glm_smem, st));
+  CK(kl::glm_launch(L, h->glm_ctas, (size_t)h->glm_smem, st));
   g_launches++;
   return 0;
 }
@@ -986,9 +964,7 @@ static int launch_glm_mc(b200mc_handle* h, const CollectSpec& col, const uint32_
   L.chain0 = chain0; L.n_live = n_live; L.C = h->C;
   L.eval_z = eval_z; L.eval_U = eval_U; L.eval_grad = eval_grad;
   CK(cudaMemsetAsync(h->counters, 0, sizeof(unsigned) * 3, st));
-  void* args[] = {&L};
-  CK(cudaLaunchCooperativeKernel((const void*)glm_mc_kernel, dim3(h->glm_ctas), dim3(kMcThreads), args,
-                                 (size_t)h->mc_smem, st));
+  CK(kl::glm_mc_launch(L, h->glm_ctas, (size_t)h->mc_smem, st));
   g_launches++;
   return 0;
 }
@@ -1060,10 +1036,10 @@ extern "C" int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, i
       L.eval_z = z_dev + (long)i0 * h->D;
       L.eval_U = U_dev + i0;
       L.eval_grad = grad_dev + (long)i0 * h->D;
-      batch_potential_kernel<<<m, kBatchThreads, 0, st>>>(L, 0);
+      CK(kl::batch_potential_launch(L, m, 0, st));
       g_launches++;
       if (launch_batch_gemms(h, st)) return 1;
-      batch_potential_kernel<<<m, kBatchThreads, 0, st>>>(L, 1);
+      CK(kl::batch_potential_launch(L, m, 1, st));
       g_launches++;
       CK(cudaGetLastError());
     }
@@ -1092,11 +1068,8 @@ extern "C" int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, i
     const int m = (n - i0 < h->C) ? n - i0 : h->C;
     const float* zp = z_dev + (long)i0 * h->D;
     float* gp = grad_dev + (long)i0 * h->D;
-    if (h->mode == 0) chain_potential_kernel<0><<<(m + 63) / 64, 64, 0, st>>>(h->M, zp, U_dev + i0, gp, m);
-    else if (h->mode == 1) chain_potential_kernel<1><<<(m + 3) / 4, 128, 0, st>>>(h->M, zp, U_dev + i0, gp, m);
-    else chain_potential_kernel<2><<<m, 256, 0, st>>>(h->M, zp, U_dev + i0, gp, m);
+    CK(kl::chain_potential_launch(h->mode, h->M, zp, U_dev + i0, gp, m, st));
     g_launches++;
-    CK(cudaGetLastError());
   }
   return 0;
 }
@@ -1134,15 +1107,15 @@ extern "C" int b200mc_membench(uint64_t bytes, int tile_bytes, int n_stages, int
   CK(cudaMemsetAsync(buf, 1, (size_t)L.nt_total * tile_bytes, st));
   CK(cudaMemsetAsync(sink, 0, 512, st));
   L.buf = buf; L.sink = sink;
-  CK(cudaFuncSetAttribute(membench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+  CK(kl::membench_prepare(max_smem));
   cudaEvent_t e0, e1;
   CK(cudaEventCreate(&e0));
   CK(cudaEventCreate(&e1));
   L.passes = 2;  // warm-up: page in, fill L2
-  membench_kernel<<<sms, kGlmThreads, smem, st>>>(L);
+  CK(kl::membench_launch(L, sms, smem, st));
   L.passes = passes;
   CK(cudaEventRecord(e0, st));
-  membench_kernel<<<sms, kGlmThreads, smem, st>>>(L);
+  CK(kl::membench_launch(L, sms, smem, st));
   CK(cudaEventRecord(e1, st));
   g_launches += 2;
   cudaError_t e = cudaEventSynchronize(e1);

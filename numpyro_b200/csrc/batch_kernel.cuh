@@ -174,6 +174,7 @@ __device__ __forceinline__ float batch_finish(const BatchLaunch& L, const G& g, 
   return lg_finish(L, g, z, grad, c);
 }
 
+#ifdef B200MC_TU_BATCH  // compiled in this family's translation unit only (launchers.h)
 // One CTA per chain.  begin = 1: set the sampler up and publish its first point.  Otherwise:
 // finish the potential at the published point, advance, publish the next point.
 __global__ void __launch_bounds__(kBatchThreads, 2) batch_step_kernel(const __grid_constant__ BatchLaunch L) {
@@ -356,5 +357,7 @@ __global__ void __launch_bounds__(kBatchThreads) batch_potential_kernel(const __
     if (threadIdx.x == 0) L.eval_U[c] = U;
   }
 }
+
+#endif  // B200MC_TU_BATCH
 
 }  // namespace b200mc

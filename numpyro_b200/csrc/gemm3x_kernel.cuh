@@ -415,6 +415,7 @@ gemm3x_resid_persistent_kernel(const __grid_constant__ Gemm3xLaunch L) {
   }
 }
 
+#ifdef B200MC_TU_GEMM  // compiled in this family's translation unit only (launchers.h)
 // ---------------------------------------------------------------- operand image builders
 // Row-major src[R_src][K_src] (optionally read transposed) -> hi/lo images of Mtx[R][K]
 // (R, K padded with zeros).  One thread per element; writes are 4 bytes into swizzled lines.
@@ -443,5 +444,7 @@ __global__ void image_build_kernel(const float* __restrict__ src, int R_src, int
     reinterpret_cast<float*>(lo)[i] = l;
   }
 }
+
+#endif  // B200MC_TU_GEMM
 
 }  // namespace b200mc

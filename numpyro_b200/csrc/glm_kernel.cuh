@@ -186,6 +186,7 @@ __device__ __forceinline__ float rcp_1to2(float d) {
   return fmaf(r, fmaf(-d, r, 1.0f), r);
 }
 
+#ifdef B200MC_TU_GLM  // compiled in this family's translation unit only (launchers.h)
 // Re-tile X [N][D] row-major + labels [N] into the layout described at the top of the file.
 __global__ void glm_retile_kernel(const float* __restrict__ X, const uint8_t* __restrict__ y,
                                   int N, int D, int nt_total, unsigned char* __restrict__ Xt) {
@@ -220,6 +221,8 @@ __global__ void glm_retile_kernel(const float* __restrict__ X, const uint8_t* __
     }
   }
 }
+
+#endif  // B200MC_TU_GLM
 
 // ---------------------------------------------------------------- per-tile arithmetic
 // One 32-row tile, lane r <-> row r.  xt: [G][32] float4 (shared), ys: 32 labels, th4: theta
@@ -395,6 +398,7 @@ __device__ __forceinline__ void glm_consume_pass(const GlmLaunch& L, unsigned ch
   if (lane == 0) red[L.D] = ll;
 }
 
+#ifdef B200MC_TU_GLM  // compiled in this family's translation unit only (launchers.h)
 __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_constant__ GlmLaunch L) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int D = L.D, NS = L.n_stages, PS = glm_partial_stride(D);
@@ -739,5 +743,7 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
     }
   }
 }
+
+#endif  // B200MC_TU_GLM
 
 }  // namespace b200mc

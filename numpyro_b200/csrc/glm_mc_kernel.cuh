@@ -280,6 +280,7 @@ __device__ __forceinline__ void glm_mc_consume_pass(const GlmMcLaunch& L, unsign
   if (r == 0) red[h * PS + L.D] = ll;  // lane (h, 0): chain h's log-likelihood terms
 }
 
+#ifdef B200MC_TU_GLM_MC  // compiled in this family's translation unit only (launchers.h)
 __global__ void __launch_bounds__(kMcThreads, 1) glm_mc_kernel(const __grid_constant__ GlmMcLaunch L) {
   extern __shared__ __align__(128) unsigned char smem[];
   constexpr int CB = kMcChains;
@@ -514,5 +515,7 @@ __global__ void __launch_bounds__(kMcThreads, 1) glm_mc_kernel(const __grid_cons
     atomicAdd(&L.prof[4], (unsigned long long)pass);
   }
 }
+
+#endif  // B200MC_TU_GLM_MC
 
 }  // namespace b200mc

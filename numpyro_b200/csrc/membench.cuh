@@ -20,6 +20,7 @@ struct MemBenchLaunch {
   unsigned* sink;
 };
 
+#ifdef B200MC_TU_GLM  // compiled in this family's translation unit only (launchers.h)
 __global__ void __launch_bounds__(kGlmThreads, 1) membench_kernel(const __grid_constant__ MemBenchLaunch L) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int NS = L.n_stages;
@@ -72,5 +73,7 @@ __global__ void __launch_bounds__(kGlmThreads, 1) membench_kernel(const __grid_c
     if (acc == 0x9e3779b9u) atomicAdd(L.sink, 1u);  // keeps the loads alive
   }
 }
+
+#endif  // B200MC_TU_GLM
 
 }  // namespace b200mc

@@ -311,17 +311,20 @@ def _tier4(nb, model, args, fam, chains, nw, ns_dev, ns_ora, ora_chains, tag, **
 
 
 def test_tier4_stochastic_volatility(nb):
+    # the oracle costs ~1 ms per gradient (Python loops): one chain, 300 + 150 transitions
     from test_gpu_parity import make_sv
 
     r = make_sv(300)
     _tier4(nb, nb.models.stochastic_volatility, (r,), opot.StochasticVolatility(r), chains=32,
-           nw=600, ns_dev=4000, ns_ora=300, ora_chains=2, tag="sv_T300")
+           nw=300, ns_dev=4000, ns_ora=150, ora_chains=1, tag="sv_T300")
 
 
 def test_tier4_horseshoe(nb):
+    # all three coefficients are active (W = [2, -1, 0.5]), so the local scales are identified and
+    # the chains mix; trees capped at depth 8 on both sides to bound the oracle's run time
     from test_gpu_batch_engine import make_horseshoe
 
-    X, Y = make_horseshoe(400, 8, "normal")
+    X, Y = make_horseshoe(100, 3, "normal")
     _tier4(nb, nb.models.horseshoe_normal, (X, Y), opot.Horseshoe(X, Y, "normal"), chains=32,
-           nw=500, ns_dev=4000, ns_ora=300, ora_chains=2, tag="horseshoe_400x8",
-           target_accept_prob=0.9)
+           nw=300, ns_dev=8000, ns_ora=200, ora_chains=1, tag="horseshoe_100x3",
+           target_accept_prob=0.9, max_tree_depth=8)
