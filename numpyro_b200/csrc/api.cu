@@ -59,8 +59,9 @@ struct b200mc_handle {
   int glm_reverse = 1;
   // several chains on one stream (glm_mc_kernel.cuh): own ring / pinned split and partial buffer
   bool glm_mc = false;
-  int mc_stages = 0, mc_pinned = 0, mc_smem = 0;
-  float* mc_partials = nullptr;  // [2][ctas][kMcChains][D+1]
+  int mc_stages = 0, mc_pinned = 0, mc_smem = 0, mc_nt_total = 0, mc_ctas = 0;
+  unsigned char* mc_xt = nullptr;  // X + labels re-tiled in 16-row tiles (glm_mc_kernel.cuh)
+  float* mc_partials = nullptr;    // [2][ctas][kMcChains][D+1]
   float* dense_replicas = nullptr;
   int* blk_tables = nullptr;  // structured mass matrix: blk_of, blk_pos, blk_perm [D] + size, dense [nb]
   // row sharding
@@ -316,7 +317,7 @@ extern "C" void b200mc_destroy(b200mc_handle* h) {
   dfree(h->cs);
   dfree(h->cv.z); dfree(h->cv.z_grad); dfree(h->cv.inverse_mass_matrix);
   dfree(h->cv.mass_matrix_sqrt); dfree(h->cv.welford_mean); dfree(h->cv.welford_m2);
-  dfree(h->work); dfree(h->partials); dfree(h->mc_partials); dfree(h->counters); dfree(h->prof); dfree(h->glm_xt);
+  dfree(h->work); dfree(h->partials); dfree(h->mc_partials); dfree(h->counters); dfree(h->prof); dfree(h->glm_xt); dfree(h->mc_xt);
   dfree(h->cv.dense); dfree(h->dense_replicas); dfree(h->M.scratch);
   dfree(h->blk_tables);
   for (int r = 0; r < h->nranks; ++r) {
@@ -541,15 +542,16 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
         auto mfits = [&](int ns_, int np_) {
           return glm_mc_smem_layout(D, ns_, np_, P.max_depth).total <= budget;
         };
-        int mns = 2 * kMcConsumerWarps;
+        // ring: every consumer warp owns its stages; three per warp when they fit, else two
+        int mns = 3 * kMcConsumerWarps;
         if (const char* e = getenv("B200MC_GLM_MC_STAGES")) {
           const int v = atoi(e) / kMcConsumerWarps * kMcConsumerWarps;
-          if (v >= kMcConsumerWarps && v <= kGlmMaxStages) mns = v;
+          if (v >= kMcConsumerWarps && v <= kMcMaxStages) mns = v;
         }
         while (mns > kMcConsumerWarps && !mfits(mns, 0)) mns -= kMcConsumerWarps;
         if (mfits(mns, 0)) {
           int mnp = 0;
-          while (mnp < kGlmMaxStages && mfits(mns, mnp + 1)) ++mnp;
+          while (mnp < kMcMaxStages && mfits(mns, mnp + 1)) ++mnp;
           if (const char* e = getenv("B200MC_GLM_MC_PINNED")) {
             const int v = atoi(e);
             if (v >= 0 && v < mnp) mnp = v;
@@ -560,8 +562,19 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
           int mocc = 0;
           ACK(kl::glm_mc_prepare(h->max_smem, h->mc_smem, &mocc));
           if (mocc >= 1) {
+            // this handle runs the multi-chain kernel only: its own 16-row image replaces the
+            // 32-row one
+            h->mc_nt_total = (c.N + kMcTileRows - 1) / kMcTileRows;
+            h->mc_ctas = h->mc_nt_total < h->num_sms ? h->mc_nt_total : h->num_sms;
+            ACK(dmalloc((void**)&h->mc_xt, (size_t)h->mc_nt_total * glm_mc_tile_bytes(D)));
+            ACK(kl::glm_mc_retile(h->num_sms * 8, (const float*)c.data0_dev, (const uint8_t*)c.data1_dev,
+                                  c.N, D, h->mc_nt_total, h->mc_xt, 0));
+            g_launches++;
+            ACK(cudaDeviceSynchronize());
+            dfree(h->glm_xt);
+            h->glm_xt = nullptr;
             ACK(alloc((void**)&h->mc_partials,
-                      sizeof(float) * 2 * (size_t)ctas * kMcChains * glm_partial_stride(D)));
+                      sizeof(float) * 2 * (size_t)h->mc_ctas * kMcChains * glm_partial_stride(D)));
             h->glm_mc = true;
           }
         }
@@ -950,9 +963,9 @@ static int launch_glm_mc(b200mc_handle* h, const CollectSpec& col, const uint32_
   GlmMcLaunch L;
   memset(&L, 0, sizeof(L));
   L.P = h->P; L.col = col; L.cs = h->cs; L.cv = h->cv;
-  L.Xt = h->glm_xt;
+  L.Xt = h->mc_xt;
   L.N = h->cfg.N; L.D = h->D;
-  L.nt_total = h->glm_nt_total;
+  L.nt_total = h->mc_nt_total;
   L.n_stages = h->mc_stages;
   L.n_pinned = h->mc_pinned;
   L.reverse_odd = h->glm_reverse;
@@ -964,7 +977,7 @@ static int launch_glm_mc(b200mc_handle* h, const CollectSpec& col, const uint32_
   L.chain0 = chain0; L.n_live = n_live; L.C = h->C;
   L.eval_z = eval_z; L.eval_U = eval_U; L.eval_grad = eval_grad;
   CK(cudaMemsetAsync(h->counters, 0, sizeof(unsigned) * 3, st));
-  CK(kl::glm_mc_launch(L, h->glm_ctas, (size_t)h->mc_smem, st));
+  CK(kl::glm_mc_launch(L, h->mc_ctas, (size_t)h->mc_smem, st));
   g_launches++;
   return 0;
 }
@@ -1077,8 +1090,8 @@ extern "C" int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, i
 extern "C" int b200mc_potential_and_grad_passes(b200mc_handle* h, const float* z_dev, int passes,
                                                 float* U_dev, float* grad_dev, void* stream) {
   if (!h || !z_dev || !U_dev || !grad_dev || passes < 1) return fail("bad argument");
-  if (h->cfg.family != B200MC_LOGISTIC || h->mode == 3)
-    return fail("multi-pass evaluation exists for the streaming (tall-data logistic) kernel only");
+  if (h->cfg.family != B200MC_LOGISTIC || h->mode == 3 || h->glm_mc)
+    return fail("multi-pass evaluation exists for the one-chain streaming (tall-data logistic) kernel only");
   const CollectSpec col = make_collect(0, 0, 1, nullptr);
   return launch_glm(h, col, nullptr, 0, 0, z_dev, U_dev, grad_dev, (cudaStream_t)stream, passes);
 }
@@ -1135,11 +1148,14 @@ extern "C" int b200mc_membench(uint64_t bytes, int tile_bytes, int n_stages, int
 // [6] chains per launch, [7] reserved.
 extern "C" int b200mc_glm_layout(b200mc_handle* h, int* out_host) {
   if (!h || !out_host) return fail("null argument");
-  if (!h->glm_xt) return fail("handle does not run the streaming kernel");
+  if (!h->glm_xt && !h->mc_xt) return fail("handle does not run the streaming kernel");
   out_host[0] = h->glm_ctas; out_host[1] = h->glm_stages; out_host[2] = h->glm_pinned;
   out_host[3] = glm_tile_bytes(h->D); out_host[4] = h->glm_nt_total; out_host[5] = h->glm_smem;
   out_host[6] = h->glm_mc ? kMcChains : 1; out_host[7] = 0;
-  if (h->glm_mc) { out_host[1] = h->mc_stages; out_host[2] = h->mc_pinned; out_host[5] = h->mc_smem; }
+  if (h->glm_mc) {
+    out_host[0] = h->mc_ctas; out_host[1] = h->mc_stages; out_host[2] = h->mc_pinned;
+    out_host[3] = glm_mc_tile_bytes(h->D); out_host[4] = h->mc_nt_total; out_host[5] = h->mc_smem;
+  }
   return 0;
 }
 

@@ -1,19 +1,21 @@
 // Several chains on ONE stream of the design matrix (tall-data logistic family, 2..4 chains per
 // launch): the multi-chain form of glm_kernel (glm_kernel.cuh), the reference's
 // chain_method="vectorized" for this model (numpyro/infer/hmc.py:790-798: one X, all chains per
-// step).  Same data layout (32-row tiles), same ping-pong sweep and pinned tiles, same
-// deterministic grid exchange; what changes:
-//   * a row is split over FOUR lanes (lane = 8 * h + r: row r of an 8-row sub-tile, column
-//     groups h, h + 4, h + 8, h + 12), so a lane keeps, PER CHAIN, its 16-float slice of theta
-//     and 16 gradient accumulators in registers (4 chains: 128 registers); the row itself is
-//     streamed from shared memory twice per sub-tile (logits, then gradient) instead of being
-//     parked in registers.  The four partial logits of a row meet through a three-shuffle
-//     transpose-reduce that leaves lane h with the logit of chain h; lane h evaluates the
-//     Bernoulli term of chain h, and the four residuals of the row come back through four
-//     shuffles -- special-function work per (row, chain) as in the one-chain kernel.
-//   * 8 consumer warps + one control warp PER CHAIN = 12 warps, three per SM sub-partition, so
-//     every thread may use 168 registers (a 13th warp would cap them at 128).  There is
-//     therefore NO producer warp: every ring stage is owned by one consumer warp, which re-arms
+// step).  Same ping-pong sweep and pinned tiles, same deterministic grid exchange; what changes:
+//   * the data is re-tiled into 16-ROW tiles ([G][16 rows][4 floats] + 16 label bytes, 3.6 KB for
+//     D = 55; glm_mc_retile_kernel), so that 12 consumer warps can each OWN two or three ring
+//     stages within the shared-memory budget (ownership is what makes the mbarrier phase
+//     tracking unambiguous: a warp only ever waits on its own stages, strictly in phase order).
+//   * a row is split over EIGHT lanes (lane = 4 h + r: row r of a 4-row sub-tile, column groups
+//     h and h + 8), so a lane keeps, PER CHAIN, an 8-float slice of theta and 8 gradient
+//     accumulators in registers (4 chains: 64 registers) and a thread fits 128 registers.
+//     Rows are processed two sub-tiles at a time: the 2 x 4 partial logits of a lane
+//     (2 rows x 4 chains) meet through a seven-shuffle transpose-reduce over the row's eight
+//     lanes that leaves every lane with ONE finished logit -- (row u, chain c) with 4 u + c = h
+//     -- so every lane evaluates exactly one Bernoulli term per row pair (no idle lanes on the
+//     special-function unit), and the eight residuals come back through eight shuffles.
+//   * 12 consumer warps + one control warp PER CHAIN = 16 warps, four per SM sub-partition.
+//     There is NO producer warp: every ring stage is owned by one consumer warp, which re-arms
 //     the stage's mbarrier and issues the TMA bulk copy of the stage's next tile itself, right
 //     after its last read of the stage.  Tile addresses do not depend on theta, so the ring
 //     still runs ahead across pass boundaries.
@@ -32,15 +34,19 @@
 namespace b200mc {
 
 constexpr int kMcChains = 4;                        // chains per launch
-constexpr int kMcLanesPerRow = 4;
-constexpr int kMcRowsPerSub = 32 / kMcLanesPerRow;  // 8
-constexpr int kMcMaxGroups = 16;                    // D <= 64
+constexpr int kMcTileRows = 16;                     // rows per tile of the multi-chain image
+constexpr int kMcMaxStages = 48;
+constexpr int kMcLanesPerRow = 8;
+constexpr int kMcRowsPerSub = 32 / kMcLanesPerRow;  // 4
+constexpr int kMcMaxGroups = 16;                    // D <= 64: two column groups per lane
 constexpr int kMcMaxD = 4 * kMcMaxGroups;
-constexpr int kMcConsumerWarps = 8;
+constexpr int kMcConsumerWarps = 12;
 constexpr int kMcConsumerThreads = kMcConsumerWarps * 32;
-constexpr int kMcControlWarp0 = kMcConsumerWarps;                // warps 8..11
-constexpr int kMcThreads = (kMcConsumerWarps + kMcChains) * 32;  // 384
+constexpr int kMcControlWarp0 = kMcConsumerWarps;                // warps 12..15
+constexpr int kMcThreads = (kMcConsumerWarps + kMcChains) * 32;  // 512 -> 128 registers per thread
 constexpr int kMcRedGroups = 8;                                  // grid reduction: strided groups of CTAs
+
+__host__ __device__ inline int glm_mc_tile_bytes(int D) { return glm_groups(D) * kMcTileRows * 16 + 16; }
 
 struct GlmMcLaunch {
   SamplerParams P;
@@ -70,10 +76,10 @@ struct GlmMcSmem {
 __host__ __device__ inline GlmMcSmem glm_mc_smem_layout(int D, int n_stages, int n_pinned, int max_depth) {
   GlmMcSmem s;
   const int ps = glm_partial_stride(D);
-  s.stage_bytes = glm_tile_bytes(D);
+  s.stage_bytes = glm_mc_tile_bytes(D);
   int o = (n_stages + n_pinned) * s.stage_bytes;
-  s.off_full = o;  o += kGlmMaxStages * 8;
-  s.off_pin = o;   o += kGlmMaxStages * 8;
+  s.off_full = o;  o += kMcMaxStages * 8;
+  s.off_pin = o;   o += kMcMaxStages * 8;
   s.off_theta = o; o += kMcChains * kMcMaxD * 4;  // [chain][64] zero-padded
   s.off_red = o;   o += kMcConsumerWarps * kMcChains * ps * 4;
   s.off_red2 = o;  o += kMcRedGroups * kMcChains * ps * 4;
@@ -106,9 +112,6 @@ __device__ __forceinline__ void mc_bce_fast(float l, float y, float& term, float
   res = ((l >= 0.f) ? inv : e * inv) - y;
 }
 
-// The row is re-read from shared memory for the gradient phase: an ordinary load would be kept in
-// registers by the compiler across the two phases, next to the 64 + 64 registers of theta and
-// the accumulators (spills).
 __device__ __forceinline__ float4 mc_lds128(uint32_t addr) {
   float4 v;
   asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
@@ -118,68 +121,83 @@ __device__ __forceinline__ float4 mc_lds128(uint32_t addr) {
   return v;
 }
 
-// One 32-row tile = four 8-row sub-tiles.  `xaddr`: shared-memory address of the tile plus this
-// lane's (h, r) offset.  th[c][k]: chain c's theta for columns 4 (4k + h) .. + 3 (zero beyond D);
-// acc[c][4k + e]: this lane's share of chain c's gradient for column 4 (4k + h) + e; ll:
-// log-likelihood terms of chain h (this lane's chain).  Rows past N are zero in the tile image
-// (x = 0, label 0): their gradient contribution vanishes by itself, only ll is masked.  A lane
-// whose last column group lies beyond the matrix (4k + h >= G) reads group G - 1 instead: theta
-// is zero there, and the accumulators it feeds are never written out.
+// One 16-row tile = two "octets" (pairs of 4-row sub-tiles).  `xaddr`: shared-memory
+// address of the tile plus this lane's (h, r) offset.  th[c][k]: chain c's theta for columns
+// 4 (h + 8k) .. + 3 (zero beyond D); acc[c][4k + e]: this lane's share of chain c's gradient for
+// column 4 (h + 8k) + e; ll: log-likelihood terms of chain h & 3 (this lane's chain).  Rows past N
+// are zero in the tile image (x = 0, label 0): their gradient contribution vanishes by itself,
+// only ll is masked.  A lane whose second column group lies beyond the matrix (h + 8 >= G) reads
+// group G - 1 instead: theta is zero there, and the accumulators it feeds are never written out.
 template <int G>
 __device__ __forceinline__ void glm_mc_tile(uint32_t xaddr, const uint8_t* __restrict__ ys, int rows,
-                                            const float4 (&th)[kMcChains][(G + 3) / 4],
-                                            float (&acc)[kMcChains][4 * ((G + 3) / 4)], float& ll) {
-  constexpr int S = kMcLanesPerRow, RPW = kMcRowsPerSub, CB = kMcChains, GL = (G + 3) / 4;
-  constexpr int LASTH = G - 4 * (GL - 1);  // lanes h < LASTH hold a real column group at k = GL - 1
-  const int lane = threadIdx.x & 31, h = lane >> 3, r = lane & 7;
-  // byte offset of column group 4k + h relative to group h: k * 4 * 512; the last one is clamped
-  const uint32_t last_off = (LASTH == 4 || h < LASTH) ? (uint32_t)((GL - 1) * S * 512)
-                                                      : (uint32_t)((G - 1 - h) * 512);
+                                            const float4 (&th)[kMcChains][(G + 7) / 8],
+                                            float (&acc)[kMcChains][4 * ((G + 7) / 8)], float& ll) {
+  constexpr int S = kMcLanesPerRow, RPW = kMcRowsPerSub, CB = kMcChains, GL = (G + 7) / 8;
+  constexpr int LASTH = G - S * (GL - 1);  // lanes h < LASTH hold a real column group at k = GL - 1
+  const int lane = threadIdx.x & 31, h = lane >> 2, r = lane & 3;
+  constexpr int GB = kMcTileRows * 16;  // bytes of one column group of a tile
+  // byte offset of column group h + 8k relative to group h: k * 8 * GB; the last one is clamped
+  const uint32_t last_off = (LASTH == S || h < LASTH) ? (uint32_t)((GL - 1) * S * GB)
+                                                      : (uint32_t)((G - 1 - h) * GB);
+  const bool b4 = (h & 4) != 0, b2 = (h & 2) != 0, b1 = (h & 1) != 0;
 #pragma unroll
-  for (int t = 0; t < S; ++t) {
-    const uint32_t ra = xaddr + (uint32_t)(t * RPW * 16);
-    float2 a[CB];
+  for (int p = 0; p < kMcTileRows / 8; ++p) {
+    float4 x[2][GL];
 #pragma unroll
-    for (int k = 0; k < GL; ++k) {
-      const float4 x = mc_lds128(ra + ((k == GL - 1) ? last_off : (uint32_t)(k * S * 512)));
+    for (int u = 0; u < 2; ++u)
+#pragma unroll
+      for (int k = 0; k < GL; ++k)
+        x[u][k] = mc_lds128(xaddr + (uint32_t)((p * 2 + u) * RPW * 16) +
+                            ((k == GL - 1) ? last_off : (uint32_t)(k * S * GB)));
+    // partial logits of rows u = 0, 1 for the four chains: v[4u + c]
+    float v[8];
+#pragma unroll
+    for (int u = 0; u < 2; ++u)
 #pragma unroll
       for (int c = 0; c < CB; ++c) {
-        if (k == 0) a[c] = __fmul2_rn(make_float2(x.x, x.y), make_float2(th[c][k].x, th[c][k].y));
-        else a[c] = __ffma2_rn(make_float2(x.x, x.y), make_float2(th[c][k].x, th[c][k].y), a[c]);
-        a[c] = __ffma2_rn(make_float2(x.z, x.w), make_float2(th[c][k].z, th[c][k].w), a[c]);
-      }
-    }
-    float l[CB];
+        float2 a = __fmul2_rn(make_float2(x[u][0].x, x[u][0].y), make_float2(th[c][0].x, th[c][0].y));
+        a = __ffma2_rn(make_float2(x[u][0].z, x[u][0].w), make_float2(th[c][0].z, th[c][0].w), a);
 #pragma unroll
-    for (int c = 0; c < CB; ++c) l[c] = a[c].x + a[c].y;
-    // transpose-reduce over the row's four lanes: lane h ends with the full logit of chain h,
-    // every chain summed as (p0 + p2) + (p1 + p3)
-    const bool up2 = (h & 2) != 0, up1 = (h & 1) != 0;
-    const float k0 = up2 ? l[2] : l[0], k1 = up2 ? l[3] : l[1];
-    const float s0 = up2 ? l[0] : l[2], s1 = up2 ? l[1] : l[3];
-    const float m0 = k0 + __shfl_xor_sync(0xffffffffu, s0, 16);
-    const float m1 = k1 + __shfl_xor_sync(0xffffffffu, s1, 16);
-    const float lm = (up1 ? m1 : m0) + __shfl_xor_sync(0xffffffffu, up1 ? m0 : m1, 8);
-    const int row = t * RPW + r;
+        for (int k = 1; k < GL; ++k) {
+          a = __ffma2_rn(make_float2(x[u][k].x, x[u][k].y), make_float2(th[c][k].x, th[c][k].y), a);
+          a = __ffma2_rn(make_float2(x[u][k].z, x[u][k].w), make_float2(th[c][k].z, th[c][k].w), a);
+        }
+        v[4 * u + c] = a.x + a.y;
+      }
+    // transpose-reduce over the row's eight lanes (lane bits 4, 3, 2 = h): lane h ends with the
+    // finished logit of (row u, chain c), 4 u + c = h; fixed order => deterministic
+    float w4[4], w2[2];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float keep = b4 ? v[4 + i] : v[i], send = b4 ? v[i] : v[4 + i];
+      w4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const float keep = b2 ? w4[2 + i] : w4[i], send = b2 ? w4[i] : w4[2 + i];
+      w2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+    const float lm = (b1 ? w2[1] : w2[0]) + __shfl_xor_sync(0xffffffffu, b1 ? w2[0] : w2[1], 4);
+    const int row = (p * 2 + (h >> 2)) * RPW + r;
     const float yv = (float)ys[row];
     float term, gm;
     mc_bce_fast(lm, yv, term, gm);
     ll += (row < rows) ? term : 0.f;
-    float gres[CB];
+    // residuals of the octet back to all eight lanes of the row pair
 #pragma unroll
-    for (int c = 0; c < CB; ++c) gres[c] = __shfl_sync(0xffffffffu, gm, c * RPW + r);
-#pragma unroll
-    for (int k = 0; k < GL; ++k) {
-      const float4 x = mc_lds128(ra + ((k == GL - 1) ? last_off : (uint32_t)(k * S * 512)));
+    for (int u = 0; u < 2; ++u)
 #pragma unroll
       for (int c = 0; c < CB; ++c) {
-        const float2 g2 = make_float2(gres[c], gres[c]);
-        const float2 a01 = __ffma2_rn(g2, make_float2(x.x, x.y), make_float2(acc[c][4 * k], acc[c][4 * k + 1]));
-        const float2 a23 = __ffma2_rn(g2, make_float2(x.z, x.w), make_float2(acc[c][4 * k + 2], acc[c][4 * k + 3]));
-        acc[c][4 * k] = a01.x; acc[c][4 * k + 1] = a01.y;
-        acc[c][4 * k + 2] = a23.x; acc[c][4 * k + 3] = a23.y;
+        const float gres = __shfl_sync(0xffffffffu, gm, ((4 * u + c) << 2) | r);
+        const float2 g2 = make_float2(gres, gres);
+#pragma unroll
+        for (int k = 0; k < GL; ++k) {
+          const float2 a01 = __ffma2_rn(g2, make_float2(x[u][k].x, x[u][k].y), make_float2(acc[c][4 * k], acc[c][4 * k + 1]));
+          const float2 a23 = __ffma2_rn(g2, make_float2(x[u][k].z, x[u][k].w), make_float2(acc[c][4 * k + 2], acc[c][4 * k + 3]));
+          acc[c][4 * k] = a01.x; acc[c][4 * k + 1] = a01.y;
+          acc[c][4 * k + 2] = a23.x; acc[c][4 * k + 3] = a23.y;
+        }
       }
-    }
   }
 }
 
@@ -198,18 +216,20 @@ __device__ __forceinline__ void mc_issue_fill(const GlmMcLaunch& L, unsigned cha
   while (rf.j >= nt) { rf.j -= nt; ++rf.pass; }
 }
 
-// One pass worth of tiles for one consumer warp (stream position bookkeeping as in
-// glm_consume_pass); leaves the warp's partial sums in red[warp][chain][0..D].  Stage s is
-// consumed AND refilled by warp s % W; `nt` counts the CTA's streamed tiles, its last `n_pin`
-// tiles sit in the slots behind the ring for the whole launch (slot k consumed by warp k % W).
+// One pass worth of tiles for one consumer warp; leaves the warp's partial sums in
+// red[warp][chain][0..D].  The CTA's tile stream is numbered p = 0, 1, ... over all passes;
+// position p is consumed by warp p % W from stage p % NS.  NS = m * W, so warp w only ever
+// touches stages w, w + W, ..., w + (m-1) W, strictly in phase order (si, ph), and refills each
+// of them itself right after reading it.  `nt` counts the CTA's streamed tiles; its last `n_pin`
+// tiles sit in the slots behind the ring for the whole launch (slot k: warp k % W).
 template <int G>
 __device__ __forceinline__ void glm_mc_consume_pass(const GlmMcLaunch& L, unsigned char* smem,
                                                     const GlmMcSmem& lay, int warp, long& p_next,
                                                     long p_begin, long p_end, int& si, uint32_t& ph,
                                                     int m, int tile0, int nt, bool rev, int n_pin,
                                                     McRefill& rf) {
-  constexpr int S = kMcLanesPerRow, CB = kMcChains, GL = (G + 3) / 4;
-  const int lane = threadIdx.x & 31, h = lane >> 3, r = lane & 7;
+  constexpr int S = kMcLanesPerRow, CB = kMcChains, GL = (G + 7) / 8;
+  const int lane = threadIdx.x & 31, h = lane >> 2, r = lane & 3;
   const int PS = glm_partial_stride(L.D);
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + lay.off_full);
   uint64_t* pin = reinterpret_cast<uint64_t*>(smem + lay.off_pin);
@@ -225,7 +245,7 @@ __device__ __forceinline__ void glm_mc_consume_pass(const GlmMcLaunch& L, unsign
 #pragma unroll
     for (int k = 0; k < 4 * GL; ++k) acc[c][k] = 0.f;
   float ll = 0.f;
-  const uint32_t lane_off = (uint32_t)((h * 32 + r) * 16);
+  const uint32_t lane_off = (uint32_t)((h * kMcTileRows + r) * 16);
   int pin_k = warp, done = 0;
   for (;;) {
     const bool ring_left = p_next < p_end;
@@ -245,8 +265,8 @@ __device__ __forceinline__ void glm_mc_consume_pass(const GlmMcLaunch& L, unsign
       const int j = (int)(p_next - p_begin);
       tile = tile0 + (rev ? (nt - 1 - j) : j);
     }
-    const int rows = (tile == L.nt_total - 1) ? (L.N - 32 * tile) : 32;
-    glm_mc_tile<G>(smem_u32(sp) + lane_off, sp + G * 512, rows, th, acc, ll);
+    const int rows = (tile == L.nt_total - 1) ? (L.N - kMcTileRows * tile) : kMcTileRows;
+    glm_mc_tile<G>(smem_u32(sp) + lane_off, sp + G * kMcTileRows * 16, rows, th, acc, ll);
     __syncwarp();
     if (stage >= 0) {
       // all lanes have read the stage: put its next tile in flight (owner warp = producer)
@@ -259,9 +279,11 @@ __device__ __forceinline__ void glm_mc_consume_pass(const GlmMcLaunch& L, unsign
     }
     ++done;
   }
-  // fold over the 8 row-lanes that share a column slice (butterfly: identical in all of them)
-#pragma unroll
-  for (int o = 1; o < kMcRowsPerSub; o <<= 1) ll += __shfl_xor_sync(0xffffffffu, ll, o);
+  // fold over the lanes that share a column slice (r = lane bits 0, 1); ll additionally over the
+  // two rows of an octet (h bit 2).  Butterflies: identical in all lanes of a class.
+  ll += __shfl_xor_sync(0xffffffffu, ll, 1);
+  ll += __shfl_xor_sync(0xffffffffu, ll, 2);
+  ll += __shfl_xor_sync(0xffffffffu, ll, 16);
   float* red = reinterpret_cast<float*>(smem + lay.off_red) + warp * CB * PS;
 #pragma unroll
   for (int c = 0; c < CB; ++c) {
@@ -270,17 +292,52 @@ __device__ __forceinline__ void glm_mc_consume_pass(const GlmMcLaunch& L, unsign
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
         float v = acc[c][4 * k + e];
-#pragma unroll
-        for (int o = 1; o < kMcRowsPerSub; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
         const int d = 4 * (k * S + h) + e;
         if (r == 0 && d < L.D) red[c * PS + d] = v;
       }
     }
   }
-  if (r == 0) red[h * PS + L.D] = ll;  // lane (h, 0): chain h's log-likelihood terms
+  if (r == 0 && h < CB) red[h * PS + L.D] = ll;  // lane (h, 0), h < 4: chain h's log-likelihood terms
 }
 
 #ifdef B200MC_TU_GLM_MC  // compiled in this family's translation unit only (launchers.h)
+// Re-tile X [N][D] row-major + labels [N] into 16-row tiles: [G][16 rows][4 floats] + 16 label
+// bytes per tile.  Rows past N and columns past D are zero.
+__global__ void glm_mc_retile_kernel(const float* __restrict__ X, const uint8_t* __restrict__ y,
+                                     int N, int D, int nt_total, unsigned char* __restrict__ Xt) {
+  const int G = glm_groups(D);
+  const long tb = glm_mc_tile_bytes(D);
+  const long per_tile = (long)G * kMcTileRows + 1;  // float4 slots + one 16-byte label slot
+  const long total = per_tile * nt_total;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total;
+       i += (long)gridDim.x * blockDim.x) {
+    const long t = i / per_tile;
+    const int sl = (int)(i - t * per_tile);
+    unsigned char* tile = Xt + t * tb;
+    if (sl < G * kMcTileRows) {
+      const int g = sl / kMcTileRows, r = sl % kMcTileRows;
+      const long row = t * kMcTileRows + r;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (row < N) {
+        const float* xr = X + row * D + 4 * g;
+        v.x = xr[0];
+        if (4 * g + 1 < D) v.y = xr[1];
+        if (4 * g + 2 < D) v.z = xr[2];
+        if (4 * g + 3 < D) v.w = xr[3];
+      }
+      reinterpret_cast<float4*>(tile)[sl] = v;
+    } else {
+      unsigned char* dst = tile + (long)G * kMcTileRows * 16;
+      for (int k = 0; k < kMcTileRows; ++k) {
+        const long row = t * kMcTileRows + k;
+        dst[k] = (row < N) ? y[row] : (unsigned char)0;
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(kMcThreads, 1) glm_mc_kernel(const __grid_constant__ GlmMcLaunch L) {
   extern __shared__ __align__(128) unsigned char smem[];
   constexpr int CB = kMcChains;
@@ -434,7 +491,7 @@ __global__ void __launch_bounds__(kMcThreads, 1) glm_mc_kernel(const __grid_cons
     mc_consumer_bar();
     // ---- CTA partial: fixed-order sum over warps
     float* my_partials = L.partials + ((long)(pass & 1) * nCTA + cta) * CPS;
-    if (tid < CPS) {
+    if (tid < CPS) {  // CPS <= 4 * 68 < 384 consumer threads
       float a = 0.f;
 #pragma unroll
       for (int w2 = 0; w2 < kMcConsumerWarps; ++w2) a += red[w2 * CPS + tid];

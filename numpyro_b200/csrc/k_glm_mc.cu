@@ -5,6 +5,11 @@
 namespace b200mc {
 namespace kl {
 
+cudaError_t glm_mc_retile(int grid, const float* X, const uint8_t* y, int N, int D, int nt_total,
+                          unsigned char* Xt, cudaStream_t st) {
+  glm_mc_retile_kernel<<<grid, 256, 0, st>>>(X, y, N, D, nt_total, Xt);
+  return cudaGetLastError();
+}
 cudaError_t glm_mc_prepare(int max_smem, int smem, int* occupancy) {
   cudaError_t e = cudaFuncSetAttribute(glm_mc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
   if (e != cudaSuccess) return e;

@@ -22,6 +22,8 @@ cudaError_t glm_launch(const GlmLaunch& L, int ctas, size_t smem, cudaStream_t s
 cudaError_t membench_prepare(int max_smem);
 cudaError_t membench_launch(const MemBenchLaunch& L, int ctas, size_t smem, cudaStream_t st);
 // k_glm_mc.cu
+cudaError_t glm_mc_retile(int grid, const float* X, const uint8_t* y, int N, int D, int nt_total,
+                          unsigned char* Xt, cudaStream_t st);
 cudaError_t glm_mc_prepare(int max_smem, int smem, int* occupancy);
 cudaError_t glm_mc_launch(const GlmMcLaunch& L, int ctas, size_t smem, cudaStream_t st);  // cooperative
 // k_chain.cu
