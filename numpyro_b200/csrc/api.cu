@@ -504,6 +504,16 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
       return glm_smem_layout(D, ns_, np_, P.max_depth, P.dense_mass).total <= budget;
     };
     int ns = 2 * kGlmConsumerWarps;
+    {
+      // A slice that (nearly) fits the shared memory of the grid -- e.g. 581,012 rows sharded
+      // over 8 GPUs: 16 tiles of 7.2 KB per CTA -- is PINNED instead of streamed: one ring stage
+      // per consumer warp, every other tile resident for the whole launch, so a pass reads
+      // shared memory only and the leapfrog is left with its serial exchange chain.
+      const int per_cta = (nt_total + ctas - 1) / ctas;
+      int np1 = 0;
+      while (np1 < kGlmMaxStages && fits(kGlmConsumerWarps, np1 + 1)) ++np1;
+      if (per_cta <= np1 + kGlmConsumerWarps / 2) ns = kGlmConsumerWarps;
+    }
     if (const char* e = getenv("B200MC_GLM_STAGES")) {  // tuning knobs
       const int v = atoi(e) / kGlmConsumerWarps * kGlmConsumerWarps;
       if (v >= kGlmConsumerWarps && v <= kGlmMaxStages) ns = v;

@@ -45,10 +45,25 @@ class MCMC(object):
                              ' "sequential", "parallel", or "vectorized"')
         if callable(chain_method):
             raise NotImplementedError("a callable chain_method (jax transform) has no meaning here")
-        # All three methods run every chain of this process in one batched launch: chains
-        # are independent units spread over the SMs (and over ranks in bench.py), and
-        # per-chain results do not depend on the method (test_mcmc.py:848-894).
+        # "vectorized": every chain in one batched launch on the current GPU (mcmc.py:709-710).
+        # "parallel": the chains are spread over the local GPUs, one handle and one host thread
+        # per device (the reference pmaps over devices, mcmc.py:707-708); with fewer devices
+        # than chains the reference warns and runs sequentially (mcmc.py:355-366) -- here the
+        # same warning is issued and every device takes a contiguous slice of the chains.
+        # "sequential": one chain after the other (mcmc.py:704-705).
+        # Per-chain results do not depend on the method (test_mcmc.py:848-894).
+        if chain_method == "parallel" and num_chains > 1:
+            ndev = self._local_device_count()
+            if ndev < num_chains:
+                warnings.warn(
+                    "There are not enough devices to run parallel chains: expected {} but got {}."
+                    " Chains will be drawn sequentially. If you are running MCMC in CPU,"
+                    " consider using `numpyro.set_host_device_count({})` at the beginning"
+                    " of your program. You can double-check how many devices are available in"
+                    " your system using `jax.local_device_count()`.".format(num_chains, ndev, num_chains),
+                    stacklevel=2)
         self.chain_method = chain_method
+        self._device_samplers = None
         self.progress_bar = False  # the loop runs on device in one launch
         self._jit_model_args = jit_model_args
         self._states = None
@@ -78,10 +93,100 @@ class MCMC(object):
     def last_state(self):
         return self._last_state
 
+    @staticmethod
+    def _local_device_count():
+        try:
+            from .. import _lib
+
+            return max(1, int(_lib.lib().b200mc_device_count()))
+        except Exception:  # library not built / no driver: argument checking still works
+            return 1
+
+    def _run_chains_sequential(self, rng_keys, init_state, init_params, args, kwargs, collect_fields,
+                               remove_sites):
+        """``chain_method="sequential"`` (mcmc.py:704-705): one chain after the other, each a
+        one-chain batch; results stacked in chain order."""
+        cut = lambda tree, c: _tree_map(lambda x: np.asarray(x)[c:c + 1], tree)  # noqa: E731
+        outs = []
+        for c in range(rng_keys.shape[0]):
+            outs.append(self._run_chains(
+                rng_keys[c:c + 1], None if init_state is None else cut(init_state, c),
+                None if init_params is None else cut(init_params, c), args, kwargs, collect_fields,
+                remove_sites))
+        cat = lambda trees, axis: (  # noqa: E731
+            {k: cat([t[k] for t in trees], axis) for k in trees[0]} if isinstance(trees[0], dict)
+            else type(trees[0])(*[cat([t[i] for t in trees], axis) for i in range(len(trees[0]))])
+            if isinstance(trees[0], tuple) and hasattr(trees[0], "_fields")
+            else type(trees[0])(cat([t[i] for t in trees], axis) for i in range(len(trees[0])))
+            if isinstance(trees[0], (tuple, list)) else None if trees[0] is None
+            else np.concatenate([np.asarray(t) for t in trees], axis=axis))
+        return cat([o[0] for o in outs], 1), cat([o[1] for o in outs], 0)
+
+    # ------------------------------------------------------------------ chains over local GPUs
+    def _run_chains_parallel(self, rng_keys, init_state, init_params, args, kwargs, collect_fields,
+                             remove_sites, ndev):
+        """``chain_method="parallel"`` with several local GPUs: device d runs the contiguous
+        slice ``shard_bounds(C, d, ndev)`` of the chains with its own kernel object (handle) on
+        its own host thread; collected fields and the last state are concatenated in chain
+        order, so the result equals the one-GPU run chain for chain."""
+        import pickle
+        import threading
+
+        from .. import _lib
+        from ..distributed import shard_bounds
+
+        C = rng_keys.shape[0]
+        if self._device_samplers is None or len(self._device_samplers) != ndev:
+            blob = pickle.dumps(self.sampler)  # __getstate__ drops everything init() built
+            self._device_samplers = [pickle.loads(blob) for _ in range(ndev)]
+        bounds = [shard_bounds(C, d, ndev) for d in range(ndev)]
+        cut = lambda tree, lo, hi: _tree_map(lambda x: np.asarray(x)[lo:hi], tree)  # noqa: E731
+        out, err = [None] * ndev, [None] * ndev
+
+        def work(d):
+            lo, hi = bounds[d]
+            if hi == lo:
+                return
+            try:
+                _lib.check(_lib.lib().b200mc_set_device(d))  # cudaSetDevice is per host thread
+                out[d] = self._run_chains(
+                    rng_keys[lo:hi], None if init_state is None else cut(init_state, lo, hi),
+                    None if init_params is None else cut(init_params, lo, hi), args, kwargs,
+                    collect_fields, remove_sites, sampler=self._device_samplers[d])
+            except BaseException as e:  # noqa: BLE001 -- re-raised on the calling thread
+                err[d] = e
+
+        threads = [threading.Thread(target=work, args=(d,)) for d in range(ndev)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        _lib.check(_lib.lib().b200mc_set_device(0))
+        for e in err:
+            if e is not None:
+                raise e
+        got = [o for o in out if o is not None]
+
+        def cat(trees, axis):
+            t0 = trees[0]
+            if isinstance(t0, dict):
+                return {k: cat([t[k] for t in trees], axis) for k in t0}
+            if isinstance(t0, tuple) and hasattr(t0, "_fields"):
+                return type(t0)(*[cat([t[i] for t in trees], axis) for i in range(len(t0))])
+            if isinstance(t0, (tuple, list)):
+                return type(t0)(cat([t[i] for t in trees], axis) for i in range(len(t0)))
+            if t0 is None:
+                return None
+            return np.concatenate([np.asarray(t) for t in trees], axis=axis)
+
+        states = cat([g[0] for g in got], 1)      # [draw, chain, ...]
+        last_state = cat([g[1] for g in got], 0)  # [chain, ...]
+        return states, last_state
+
     # ------------------------------------------------------------------ one batch of chains
     def _run_chains(self, rng_key, init_state, init_params, args, kwargs, collect_fields,
-                    remove_sites):
-        sampler = self.sampler
+                    remove_sites, sampler=None):
+        sampler = self.sampler if sampler is None else sampler
         if init_state is None or getattr(sampler, "_sample_fn", None) is None:
             new_init_state = sampler.init(rng_key, self.num_warmup, init_params, model_args=args,
                                           model_kwargs=kwargs)
@@ -179,8 +284,18 @@ class MCMC(object):
                 collect_fields[field_name] = None
         collect_fields, remove_sites = tuple(collect_fields), tuple(remove_sites)
 
-        states, last_state = self._run_chains(rng_key, init_state, init_params, args, kwargs,
-                                              collect_fields, remove_sites)
+        ndev = self._local_device_count() if self.chain_method == "parallel" else 1
+        vector_keys = not b2random.is_prng_key(rng_key)
+        if self.chain_method == "parallel" and vector_keys and ndev > 1 and hasattr(self.sampler, "run_loop"):
+            states, last_state = self._run_chains_parallel(rng_key, init_state, init_params, args,
+                                                           kwargs, collect_fields, remove_sites,
+                                                           min(ndev, rng_key.shape[0]))
+        elif self.chain_method == "sequential" and vector_keys:
+            states, last_state = self._run_chains_sequential(rng_key, init_state, init_params, args,
+                                                             kwargs, collect_fields, remove_sites)
+        else:
+            states, last_state = self._run_chains(rng_key, init_state, init_params, args, kwargs,
+                                                  collect_fields, remove_sites)
         if self.num_chains == 1 and b2random.is_prng_key(rng_key):
             states = _tree_map(lambda x: x[np.newaxis, ...], states)
         else:

@@ -113,3 +113,31 @@ def test_two_rank_gloo_matches_single_process(tmp_path, n_chains):
     got = np.load(out)
     assert got.shape == (n_chains, 7, 3)
     assert np.array_equal(got, ref)
+
+
+def test_sequential_chain_method_equals_vectorized():
+    # mcmc.py:704-705 vs :709-710: per-chain results do not depend on the method
+    from numpyro_b200.infer import MCMC
+
+    keys = _chain_keys(3)
+    out = {}
+    for method in ("vectorized", "sequential"):
+        mc = _make_mcmc(3)
+        mc.chain_method = method
+        mc.run(keys)
+        out[method] = mc.get_samples(group_by_chain=True)
+        assert out[method].shape == (3, 7, 3)
+        assert np.asarray(mc.last_state.z).shape == (3, 3)
+    assert np.array_equal(out["vectorized"], out["sequential"])
+
+
+def test_parallel_warns_like_the_reference_when_devices_are_short():
+    import warnings
+
+    from numpyro_b200.infer import MCMC
+
+    mc = _make_mcmc(1)
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        MCMC(mc.sampler, num_warmup=1, num_samples=1, num_chains=64, chain_method="parallel")
+    assert any("not enough devices to run parallel chains" in str(x.message) for x in w)
