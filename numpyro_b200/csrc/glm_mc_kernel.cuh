@@ -2,8 +2,9 @@
 // launch): the multi-chain form of glm_kernel (glm_kernel.cuh), the reference's
 // chain_method="vectorized" for this model (numpyro/infer/hmc.py:790-798: one X, all chains per
 // step).  Same ping-pong sweep and pinned tiles, same deterministic grid exchange; what changes:
-//   * the data is re-tiled into 16-ROW tiles ([G][16 rows][4 floats] + 16 label bytes, 3.6 KB for
-//     D = 55; glm_mc_retile_kernel), so that 12 consumer warps can each OWN two or three ring
+//   * the data is re-tiled into 16-ROW tiles ([G/2 group pairs][16 rows][2 groups][4 floats] + 16
+//     label bytes, 3.6 KB for D = 55; glm_mc_retile_kernel: the 8 lanes of a quarter-warp read
+//     128 contiguous bytes, no bank conflicts), so that 12 consumer warps can each OWN two or three ring
 //     stages within the shared-memory budget (ownership is what makes the mbarrier phase
 //     tracking unambiguous: a warp only ever waits on its own stages, strictly in phase order).
 //   * a row is split over EIGHT lanes (lane = 4 h + r: row r of a 4-row sub-tile, column groups
@@ -44,9 +45,13 @@ constexpr int kMcConsumerWarps = 12;
 constexpr int kMcConsumerThreads = kMcConsumerWarps * 32;
 constexpr int kMcControlWarp0 = kMcConsumerWarps;                // warps 12..15
 constexpr int kMcThreads = (kMcConsumerWarps + kMcChains) * 32;  // 512 -> 128 registers per thread
-constexpr int kMcRedGroups = 8;                                  // grid reduction: strided groups of CTAs
+constexpr int kMcRedGroups = 6;                                  // grid reduction: strided groups of CTAs
+constexpr int kMcRedChunk = 13;                                  // independent 128-bit loads in flight per thread
 
-__host__ __device__ inline int glm_mc_tile_bytes(int D) { return glm_groups(D) * kMcTileRows * 16 + 16; }
+__host__ __device__ inline int glm_mc_pairs(int D) { return (glm_groups(D) + 1) / 2; }
+__host__ __device__ inline int glm_mc_tile_bytes(int D) { return glm_mc_pairs(D) * kMcTileRows * 32 + 16; }
+// byte offset of (column group g, row 0) inside a tile; a row advances by 32 bytes
+__host__ __device__ inline int glm_mc_group_off(int g) { return (g >> 1) * (kMcTileRows * 32) + (g & 1) * 16; }
 
 struct GlmMcLaunch {
   SamplerParams P;
@@ -112,16 +117,7 @@ __device__ __forceinline__ void mc_bce_fast(float l, float y, float& term, float
   res = ((l >= 0.f) ? inv : e * inv) - y;
 }
 
-__device__ __forceinline__ float4 mc_lds128(uint32_t addr) {
-  float4 v;
-  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
-               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-               : "r"(addr)
-               : "memory");
-  return v;
-}
-
-// One 16-row tile = two "octets" (pairs of 4-row sub-tiles).  `xaddr`: shared-memory
+// One 16-row tile = two "octets" (pairs of 4-row sub-tiles).  `tile`: the tile in shared
 // address of the tile plus this lane's (h, r) offset.  th[c][k]: chain c's theta for columns
 // 4 (h + 8k) .. + 3 (zero beyond D); acc[c][4k + e]: this lane's share of chain c's gradient for
 // column 4 (h + 8k) + e; ll: log-likelihood terms of chain h & 3 (this lane's chain).  Rows past N
@@ -129,16 +125,18 @@ __device__ __forceinline__ float4 mc_lds128(uint32_t addr) {
 // only ll is masked.  A lane whose second column group lies beyond the matrix (h + 8 >= G) reads
 // group G - 1 instead: theta is zero there, and the accumulators it feeds are never written out.
 template <int G>
-__device__ __forceinline__ void glm_mc_tile(uint32_t xaddr, const uint8_t* __restrict__ ys, int rows,
+__device__ __forceinline__ void glm_mc_tile(const unsigned char* __restrict__ tile, int rows,
                                             const float4 (&th)[kMcChains][(G + 7) / 8],
                                             float (&acc)[kMcChains][4 * ((G + 7) / 8)], float& ll) {
   constexpr int S = kMcLanesPerRow, RPW = kMcRowsPerSub, CB = kMcChains, GL = (G + 7) / 8;
   constexpr int LASTH = G - S * (GL - 1);  // lanes h < LASTH hold a real column group at k = GL - 1
   const int lane = threadIdx.x & 31, h = lane >> 2, r = lane & 3;
-  constexpr int GB = kMcTileRows * 16;  // bytes of one column group of a tile
-  // byte offset of column group h + 8k relative to group h: k * 8 * GB; the last one is clamped
-  const uint32_t last_off = (LASTH == S || h < LASTH) ? (uint32_t)((GL - 1) * S * GB)
-                                                      : (uint32_t)((G - 1 - h) * GB);
+  const uint8_t* ys = tile + glm_mc_pairs(4 * G) * (kMcTileRows * 32);
+  // column groups of this lane: h + 8k; the last one is clamped to group G - 1 where it does not exist
+  int goff[GL];
+#pragma unroll
+  for (int k = 0; k < GL; ++k)
+    goff[k] = glm_mc_group_off((k < GL - 1 || LASTH == S || h < LASTH) ? h + S * k : G - 1) + r * 32;
   const bool b4 = (h & 4) != 0, b2 = (h & 2) != 0, b1 = (h & 1) != 0;
 #pragma unroll
   for (int p = 0; p < kMcTileRows / 8; ++p) {
@@ -147,8 +145,7 @@ __device__ __forceinline__ void glm_mc_tile(uint32_t xaddr, const uint8_t* __res
     for (int u = 0; u < 2; ++u)
 #pragma unroll
       for (int k = 0; k < GL; ++k)
-        x[u][k] = mc_lds128(xaddr + (uint32_t)((p * 2 + u) * RPW * 16) +
-                            ((k == GL - 1) ? last_off : (uint32_t)(k * S * GB)));
+        x[u][k] = *reinterpret_cast<const float4*>(tile + goff[k] + (p * 2 + u) * RPW * 32);
     // partial logits of rows u = 0, 1 for the four chains: v[4u + c]
     float v[8];
 #pragma unroll
@@ -245,7 +242,6 @@ __device__ __forceinline__ void glm_mc_consume_pass(const GlmMcLaunch& L, unsign
 #pragma unroll
     for (int k = 0; k < 4 * GL; ++k) acc[c][k] = 0.f;
   float ll = 0.f;
-  const uint32_t lane_off = (uint32_t)((h * kMcTileRows + r) * 16);
   int pin_k = warp, done = 0;
   for (;;) {
     const bool ring_left = p_next < p_end;
@@ -266,7 +262,7 @@ __device__ __forceinline__ void glm_mc_consume_pass(const GlmMcLaunch& L, unsign
       tile = tile0 + (rev ? (nt - 1 - j) : j);
     }
     const int rows = (tile == L.nt_total - 1) ? (L.N - kMcTileRows * tile) : kMcTileRows;
-    glm_mc_tile<G>(smem_u32(sp) + lane_off, sp + G * kMcTileRows * 16, rows, th, acc, ll);
+    glm_mc_tile<G>(sp, rows, th, acc, ll);
     __syncwarp();
     if (stage >= 0) {
       // all lanes have read the stage: put its next tile in flight (owner warp = producer)
@@ -303,24 +299,24 @@ __device__ __forceinline__ void glm_mc_consume_pass(const GlmMcLaunch& L, unsign
 }
 
 #ifdef B200MC_TU_GLM_MC  // compiled in this family's translation unit only (launchers.h)
-// Re-tile X [N][D] row-major + labels [N] into 16-row tiles: [G][16 rows][4 floats] + 16 label
-// bytes per tile.  Rows past N and columns past D are zero.
+// Re-tile X [N][D] row-major + labels [N] into 16-row tiles: [G/2 pairs][16 rows][2 groups]
+// [4 floats] + 16 label bytes per tile.  Rows past N and columns past D are zero.
 __global__ void glm_mc_retile_kernel(const float* __restrict__ X, const uint8_t* __restrict__ y,
                                      int N, int D, int nt_total, unsigned char* __restrict__ Xt) {
-  const int G = glm_groups(D);
+  const int G = glm_groups(D), GP = glm_mc_pairs(D);
   const long tb = glm_mc_tile_bytes(D);
-  const long per_tile = (long)G * kMcTileRows + 1;  // float4 slots + one 16-byte label slot
+  const long per_tile = (long)GP * kMcTileRows * 2 + 1;  // float4 slots + one 16-byte label slot
   const long total = per_tile * nt_total;
   for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total;
        i += (long)gridDim.x * blockDim.x) {
     const long t = i / per_tile;
     const int sl = (int)(i - t * per_tile);
     unsigned char* tile = Xt + t * tb;
-    if (sl < G * kMcTileRows) {
-      const int g = sl / kMcTileRows, r = sl % kMcTileRows;
+    if (sl < GP * kMcTileRows * 2) {
+      const int g = 2 * (sl / (kMcTileRows * 2)) + (sl & 1), r = (sl >> 1) % kMcTileRows;
       const long row = t * kMcTileRows + r;
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (row < N) {
+      if (row < N && g < G) {
         const float* xr = X + row * D + 4 * g;
         v.x = xr[0];
         if (4 * g + 1 < D) v.y = xr[1];
@@ -329,7 +325,7 @@ __global__ void glm_mc_retile_kernel(const float* __restrict__ X, const uint8_t*
       }
       reinterpret_cast<float4*>(tile)[sl] = v;
     } else {
-      unsigned char* dst = tile + (long)G * kMcTileRows * 16;
+      unsigned char* dst = tile + (long)GP * kMcTileRows * 32;
       for (int k = 0; k < kMcTileRows; ++k) {
         const long row = t * kMcTileRows + k;
         dst[k] = (row < N) ? y[row] : (unsigned char)0;
@@ -518,15 +514,15 @@ __global__ void __launch_bounds__(kMcThreads, 1) glm_mc_kernel(const __grid_cons
     for (int item = tid; item < kMcRedGroups * CPS4; item += kMcConsumerThreads) {
       const int c4 = item % CPS4, grp = item / CPS4;
       float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int b0 = grp; b0 < nCTA; b0 += kMcRedGroups * 10) {
-        float4 v[10];
+      for (int b0 = grp; b0 < nCTA; b0 += kMcRedGroups * kMcRedChunk) {
+        float4 v[kMcRedChunk];
 #pragma unroll
-        for (int i = 0; i < 10; ++i) {
+        for (int i = 0; i < kMcRedChunk; ++i) {
           const int b = b0 + kMcRedGroups * i;
           v[i] = (b < nCTA) ? __ldcg(&all4[(long)b * CPS4 + c4]) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
 #pragma unroll
-        for (int i = 0; i < 10; ++i) {
+        for (int i = 0; i < kMcRedChunk; ++i) {
           a.x += v[i].x; a.y += v[i].y; a.z += v[i].z; a.w += v[i].w;
         }
       }
