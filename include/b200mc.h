@@ -207,6 +207,14 @@ int b200mc_membench(uint64_t bytes, int tile_bytes, int n_stages, int passes, in
 int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, int n, float* U_dev,
                               float* grad_dev, void* stream);
 
+/* On-device diagnostics over collected draws x[n_total][C][D] (the collection layout of
+ * b200mc_collect.z_dev), draws first .. first+n-1 of every chain: effective_sample_size (Geyer
+ * initial monotone sequence on biased autocovariances, numpyro/diagnostics.py:158-203),
+ * gelman_rubin (:45-61; written only when C > 1) and split_gelman_rubin (:64-80).  Outputs are
+ * device arrays of D float64, any may be NULL.  Synchronises the stream. */
+int b200mc_diag_ess_rhat(const float* x_dev, int n_total, int first, int n, int chains, int D,
+                         double* n_eff_dev, double* r_hat_dev, double* split_r_hat_dev, void* stream);
+
 /* Tier-2 hook of the streaming (tall-data logistic) kernel in the regime it is benchmarked in:
  * the SAME point z[D] is evaluated on `passes` consecutive passes of ONE launch -- forward
  * sweep, reversed sweep, forward, ... with the TMA ring wrapping and the L2-resident ping-pong

@@ -1456,3 +1456,56 @@ extern "C" int b200mc_event_destroy(void* event) {
   CK(cudaEventDestroy((cudaEvent_t)event));
   return 0;
 }
+
+// ---------------------------------------------------------------- on-device diagnostics
+// effective_sample_size + split_gelman_rubin + gelman_rubin (numpyro/diagnostics.py:45-80,
+// 158-203) of draws x[n_total][C][D] as the samplers collect them, draws first .. first+n-1.
+// Outputs are DEVICE arrays of D doubles (any may be null).  Scratch comes from the caching
+// allocator; synchronises the stream before it returns.
+extern "C" int b200mc_diag_ess_rhat(const float* x_dev, int n_total, int first, int n, int chains, int D,
+                                    double* n_eff_dev, double* r_hat_dev, double* split_r_hat_dev,
+                                    void* stream) {
+  if (!x_dev || n_total < 1 || chains < 1 || D < 1 || first < 0 || n < 2 || first + n > n_total)
+    return fail("diag: bad argument");
+  if (split_r_hat_dev && n < 4) return fail("diag: split R-hat needs at least 4 draws");
+  cudaStream_t st = (cudaStream_t)stream;
+  int dev = 0, max_smem = 0;
+  CK(cudaGetDevice(&dev));
+  CK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  CK(kl::diag_prepare(max_smem));
+  int pb = 32;
+  while (pb > 1 && (size_t)n * pb * sizeof(float) > (size_t)max_smem - 4096) pb >>= 1;
+  if ((size_t)n * pb * sizeof(float) > (size_t)max_smem - 4096)
+    return fail("diag: %d draws per chain do not fit the shared-memory series buffer (max %d)", n,
+                (max_smem - 4096) / 4);
+  double *mean = nullptr, *ssd = nullptr, *gamma = nullptr;
+  const size_t stat_bytes = sizeof(double) * 2 * (size_t)chains * D;
+  CK(dmalloc((void**)&mean, stat_bytes));
+  CK(dmalloc((void**)&ssd, stat_bytes));
+  int rc = 0;
+  auto run = [&](int split, int max_lag, double* rhat_out, double* neff_out) -> int {
+    DiagLaunch L;
+    L.x = x_dev; L.n_total = n_total; L.C = chains; L.D = D; L.first = first; L.n = n;
+    L.split = split; L.max_lag = max_lag; L.pb = pb; L.mean = mean; L.ssd = ssd; L.gamma_sum = gamma;
+    const int nn = split ? n / 2 : n;
+    CK(kl::diag_stats_launch(L, (size_t)nn * pb * sizeof(float), st));
+    DiagFinish F;
+    F.mean = mean; F.ssd = ssd; F.M = chains * (split ? 2 : 1); F.n = nn; F.D = D;
+    F.gamma_sum = max_lag > 0 ? gamma : nullptr; F.max_lag = max_lag;
+    F.r_hat = rhat_out; F.n_eff = neff_out;
+    CK(kl::diag_finish_launch(F, st));
+    g_launches += 2;
+    return 0;
+  };
+  if (n_eff_dev || r_hat_dev) {
+    if (n_eff_dev) {
+      if (cudaSuccess != dmalloc((void**)&gamma, sizeof(double) * (size_t)n * D)) rc = fail("diag: out of memory");
+      if (!rc && cudaMemsetAsync(gamma, 0, sizeof(double) * (size_t)n * D, st) != cudaSuccess) rc = fail("diag: memset failed");
+    }
+    if (!rc) rc = run(0, n_eff_dev ? n : 0, chains > 1 ? r_hat_dev : nullptr, n_eff_dev);
+  }
+  if (!rc && split_r_hat_dev) rc = run(1, 0, split_r_hat_dev, nullptr);
+  if (cudaStreamSynchronize(st) != cudaSuccess && !rc) rc = fail("diag: %s", cudaGetErrorString(cudaGetLastError()));
+  dfree(mean); dfree(ssd); dfree(gamma);
+  return rc;
+}

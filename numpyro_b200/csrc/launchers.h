@@ -6,6 +6,7 @@
 
 #include "batch_kernel.cuh"
 #include "chain_kernel.cuh"
+#include "diag_kernel.cuh"
 #include "gemm3x_kernel.cuh"
 #include "glm_kernel.cuh"
 #include "glm_mc_kernel.cuh"
@@ -36,6 +37,10 @@ cudaError_t batch_matvec_launch(const BatchLaunch& L, dim3 grid, size_t smem, cu
 cudaError_t batch_potential_launch(const BatchLaunch& L, int points, int phase, cudaStream_t st);
 cudaError_t factor_cov_launch(float* mats, int D, float n, int regularize, cudaStream_t st);
 cudaError_t factor_tinv_launch(float* mats, int D, cudaStream_t st);
+// k_diag.cu
+cudaError_t diag_prepare(int max_smem);
+cudaError_t diag_stats_launch(const DiagLaunch& L, size_t smem, cudaStream_t st);
+cudaError_t diag_finish_launch(const DiagFinish& L, cudaStream_t st);
 // k_gemm.cu
 cudaError_t image_build_launch(const float* src, int R_src, int K_src, int transpose, int R, int K,
                                unsigned char* hi, unsigned char* lo, cudaStream_t st);

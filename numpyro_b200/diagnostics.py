@@ -152,3 +152,44 @@ def print_summary(samples, prob=0.90, group_by_chain=True):  # diagnostics.py:28
                 idx_str = "[{}]".format(",".join(map(str, idx)))
                 print(row_format.format(name + idx_str, *[v[idx] for v in stats.values()]))
     print()
+
+
+# ---------------------------------------------------------------------------- on the device
+def device_ess_rhat(x, first=0, n=None, layout="chain_draw"):
+    """``effective_sample_size`` / ``gelman_rubin`` / ``split_gelman_rubin``
+    (``numpyro/diagnostics.py:45-80,158-203``) computed by the CUDA library
+    (``b200mc_diag_ess_rhat``) -- no host NumPy on the path, so that diagnostics over 16,384
+    chains x D are not the bottleneck.
+
+    ``x``: a NumPy array ``[chain, draw, D]`` (``layout="chain_draw"``, what ``get_samples(
+    group_by_chain=True)`` returns; uploaded as float32) or a ``_lib.DeviceArray`` in the
+    samplers' collection layout ``[draw, chain, D]`` (``layout="draw_chain"``; nothing is copied).
+    Returns ``{"n_eff", "r_hat", "split_r_hat"}`` as float64 arrays of length D
+    (``r_hat`` is NaN for a single chain, as the reference's function requires two).
+    """
+    import ctypes as C
+
+    from . import _lib
+
+    lib = _lib.lib()
+    if isinstance(x, _lib.DeviceArray):
+        if layout != "draw_chain":
+            raise ValueError("a DeviceArray must be in the collection layout [draw, chain, D]")
+        xd, (nt, c, d) = x, x.shape
+    else:
+        x = np.asarray(x, np.float32)
+        if x.ndim == 2:
+            x = x[..., None]
+        if layout == "chain_draw":
+            x = np.swapaxes(x, 0, 1)
+        x = np.ascontiguousarray(x.reshape(x.shape[0], x.shape[1], -1))
+        nt, c, d = x.shape
+        xd = _lib.DeviceArray.from_numpy(x)
+    n = nt - first if n is None else n
+    outs = [_lib.DeviceArray((d,), np.float64) for _ in range(3)]
+    _lib.check(lib.b200mc_diag_ess_rhat(xd.ptr, nt, first, n, c, d, outs[0].ptr,
+                                        outs[1].ptr if c > 1 else None,
+                                        outs[2].ptr if n >= 4 else None, None))
+    res = {"n_eff": outs[0].numpy(), "r_hat": outs[1].numpy() if c > 1 else np.full(d, np.nan),
+           "split_r_hat": outs[2].numpy() if n >= 4 else np.full(d, np.nan)}
+    return res
