@@ -207,6 +207,19 @@ int b200mc_membench(uint64_t bytes, int tile_bytes, int n_stages, int passes, in
 int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, int n, float* U_dev,
                               float* grad_dev, void* stream);
 
+/* log_likelihood / Predictive (numpyro/infer/util.py:803-1148) for the registered families'
+ * observation site over S posterior draws: m[s][i] = X[i] . B[s] (X_dev [N][K] row-major and
+ * B [S][K], the GLM families) or m = loc [S][N] when X_dev is NULL.  likelihood 0
+ * Bernoulli(logits = m), 1 Normal(m, scale), 2 StudentT(df[s], m, scale); scale_kind 0 none,
+ * 1 per draw [S], 2 per observation [N], 3 full [S][N].  With y_dev (and keys_dev NULL):
+ * out[s][i] = log_prob(y_i).  With keys_dev [S][2] (the observation site's key of every draw, as
+ * the seed handler hands it out): out[s][i] = one draw of the site -- Bernoulli as int32
+ * (uniform(key_s, (N,))[i] < expit(m)), Normal as float32 (m + scale * normal(key_s, (N,))[i]). */
+int b200mc_obs_forward(const float* X_dev, int N, int K, const float* B_or_loc_dev, int S,
+                       const float* scale_dev, int scale_kind, const float* df_dev,
+                       const float* y_dev, const uint32_t* keys_dev, int likelihood,
+                       int partitionable, float* out_dev, void* stream);
+
 /* On-device diagnostics over collected draws x[n_total][C][D] (the collection layout of
  * b200mc_collect.z_dev), draws first .. first+n-1 of every chain: effective_sample_size (Geyer
  * initial monotone sequence on biased autocovariances, numpyro/diagnostics.py:158-203),

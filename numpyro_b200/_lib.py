@@ -86,6 +86,7 @@ SYMBOLS = {
     "b200mc_get_profile": (_i, [_vp, _vp, _i]),
     "b200mc_comm_export": (_i, [_vp, _vp]),
     "b200mc_comm_import": (_i, [_vp, _vp]),
+    "b200mc_obs_forward": (_i, [_vp, _i, _i, _vp, _i, _vp, _i, _vp, _vp, _vp, _i, _i, _vp, _vp]),
     "b200mc_diag_ess_rhat": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "b200mc_glm_layout": (_i, [_vp, C.POINTER(_i)]),
     "b200mc_membench": (_i, [_u64, _i, _i, _i, _i, C.POINTER(_f), _vp]),

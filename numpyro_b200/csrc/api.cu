@@ -1472,7 +1472,7 @@ extern "C" int b200mc_diag_ess_rhat(const float* x_dev, int n_total, int first, 
   int dev = 0, max_smem = 0;
   CK(cudaGetDevice(&dev));
   CK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-  CK(kl::diag_prepare(max_smem));
+  CK(kl::diag_prepare(max_smem - 4096));  // the kernel also holds 2 KB of static shared memory
   int pb = 32;
   while (pb > 1 && (size_t)n * pb * sizeof(float) > (size_t)max_smem - 4096) pb >>= 1;
   if ((size_t)n * pb * sizeof(float) > (size_t)max_smem - 4096)
@@ -1508,4 +1508,32 @@ extern "C" int b200mc_diag_ess_rhat(const float* x_dev, int n_total, int first, 
   if (cudaStreamSynchronize(st) != cudaSuccess && !rc) rc = fail("diag: %s", cudaGetErrorString(cudaGetLastError()));
   dfree(mean); dfree(ssd); dfree(gamma);
   return rc;
+}
+
+// ---------------------------------------------------------------- log_likelihood / Predictive
+extern "C" int b200mc_obs_forward(const float* X_dev, int N, int K, const float* B_or_loc_dev, int S,
+                                  const float* scale_dev, int scale_kind, const float* df_dev,
+                                  const float* y_dev, const uint32_t* keys_dev, int likelihood,
+                                  int partitionable, float* out_dev, void* stream) {
+  if (!B_or_loc_dev || !out_dev || N < 1 || S < 1) return fail("obs_forward: bad argument");
+  if (X_dev && (K < 1 || K > 4096)) return fail("obs_forward: K must be in [1, 4096]");
+  if (likelihood < 0 || likelihood > 2) return fail("obs_forward: likelihood must be 0 (Bernoulli logits), 1 (Normal) or 2 (StudentT)");
+  if (scale_kind < 0 || scale_kind > 3 || (scale_kind && !scale_dev)) return fail("obs_forward: bad scale");
+  if (likelihood == 2 && !df_dev) return fail("obs_forward: StudentT needs df");
+  if (!keys_dev && !y_dev) return fail("obs_forward: give observations (log-likelihood) or keys (sampling)");
+  if (keys_dev && likelihood == 2)
+    return fail("obs_forward: sampling a StudentT site is not implemented (jax.random.t draws through a "
+                "rejection-sampled gamma); log_likelihood is");
+  ObsLaunch L;
+  L.X = X_dev; L.N = N; L.K = X_dev ? K : 0; L.S = S; L.B = B_or_loc_dev;
+  L.scale = scale_dev; L.scale_kind = scale_kind; L.df = df_dev; L.y = keys_dev ? nullptr : y_dev;
+  L.keys = keys_dev; L.likelihood = likelihood; L.partitionable = partitionable; L.out = out_dev;
+  int dev = 0, max_smem = 0;
+  CK(cudaGetDevice(&dev));
+  CK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  if (X_dev && obs_smem(K) > (size_t)max_smem)
+    return fail("obs_forward: K = %d columns do not fit the shared-memory tile", K);
+  CK(kl::obs_forward_launch(L, (cudaStream_t)stream));
+  g_launches++;
+  return 0;
 }

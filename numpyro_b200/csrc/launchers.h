@@ -11,6 +11,7 @@
 #include "glm_kernel.cuh"
 #include "glm_mc_kernel.cuh"
 #include "membench.cuh"
+#include "obs_kernel.cuh"
 
 namespace b200mc {
 namespace kl {
@@ -41,6 +42,8 @@ cudaError_t factor_tinv_launch(float* mats, int D, cudaStream_t st);
 cudaError_t diag_prepare(int max_smem);
 cudaError_t diag_stats_launch(const DiagLaunch& L, size_t smem, cudaStream_t st);
 cudaError_t diag_finish_launch(const DiagFinish& L, cudaStream_t st);
+// k_obs.cu
+cudaError_t obs_forward_launch(const ObsLaunch& L, cudaStream_t st);
 // k_gemm.cu
 cudaError_t image_build_launch(const float* src, int R_src, int K_src, int transpose, int R, int K,
                                unsigned char* hi, unsigned char* lo, cudaStream_t st);

@@ -1,5 +1,6 @@
 from .hmc import HMC, NUTS, HMCAdaptState, HMCState, MCMCKernel, init_to_uniform, init_to_value
 from .mcmc import MCMC
+from .util import Predictive, log_likelihood
 
 __all__ = ["HMC", "NUTS", "MCMC", "MCMCKernel", "HMCState", "HMCAdaptState", "init_to_uniform",
-           "init_to_value"]
+           "init_to_value", "Predictive", "log_likelihood"]

@@ -143,6 +143,27 @@ def install_full(partitionable=True):
     jnp.number = np.number
     jnp.inexact = np.inexact
     lax = mods["jax.lax"]
+
+    # lax.map / vmap over the leading axis as a Python loop + stack: by definition the batched
+    # result equals the per-element calls, which is all the fixtures need (Predictive /
+    # log_likelihood batch over posterior draws through numpyro.util.soft_vmap)
+    def _loop_map(fn, xs):
+        leaves, treedef = refshim.tree_flatten(xs)
+        n = np.shape(leaves[0])[0]
+        outs = [fn(refshim.tree_unflatten(treedef, [np.asarray(leaf)[i] for leaf in leaves])) for i in range(n)]
+        o_leaves = [refshim.tree_flatten(o)[0] for o in outs]
+        o_def = refshim.tree_flatten(outs[0])[1]
+        return refshim.tree_unflatten(o_def, [_wrap(np.stack([np.asarray(ol[j]) for ol in o_leaves]))
+                                              for j in range(len(o_leaves[0]))])
+
+    lax.map = _loop_map
+
+    def _vmap(fn, in_axes=0, out_axes=0, **kw):
+        if in_axes != 0 or out_axes != 0:
+            raise NotImplementedError("refshim_full: vmap is emulated for in_axes=0, out_axes=0 only")
+        return lambda *xs: _loop_map(lambda t: fn(*t), tuple(xs))
+
+    jax.vmap = _vmap
     lax.broadcast_shapes = np.broadcast_shapes
     lax.lgamma = _lift(sps.gammaln)
     lax.digamma = _lift(sps.digamma)
