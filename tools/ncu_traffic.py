@@ -86,25 +86,30 @@ def parse():
     col = {h: i for i, h in enumerate(head)}
     out = [f"# ncu --set full --clock-control none (tools/ncu_traffic.py), chains={work['chains']}"]
     per = []
+    unit_scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    # the launches of the capture and of the workload list are aligned from the END (the capture
+    # may start with the short init launch, which the list folds into the warm-up entry)
+    off = len(work["launches"]) - len(data)
     for li, r in enumerate(data):
-        w = work["launches"][li] if li < len(work["launches"]) else None
+        wi = li + off
+        w = work["launches"][wi] if 0 <= wi < len(work["launches"]) else None
         out.append(f"launch {li}: {r[col['Kernel Name']][:40]} {w}")
         vals = {}
         for m in METRICS:
             if m in col:
                 vals[m] = r[col[m]]
-                out.append(f"  {m} = {r[col[m]]}")
+                out.append(f"  {m} = {r[col[m]]} {rows[1][col[m]]}")
         if w and "dram__bytes_read.sum" in vals:
-            rd = float(vals["dram__bytes_read.sum"].replace(",", "")) + float(vals["dram__bytes_write.sum"].replace(",", ""))
-            unit = rows[1][col["dram__bytes_read.sum"]]
-            scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1)
-            per.append((li, rd * scale / max(1, w["grad_evals"]), float(vals.get("lts__t_sector_hit_rate.pct", "nan"))))
+            byt = sum(float(vals[m].replace(",", "")) * unit_scale.get(rows[1][col[m]], 1)
+                      for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
+            per.append((li, byt / max(1, w["grad_evals"]), float(vals.get("lts__t_sector_hit_rate.pct", "nan")),
+                        w["what"]))
             out.append(f"  => DRAM bytes per pass over X: {per[-1][1]:.0f}")
     commit = subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
     with open(os.path.join(ROOT, "profiles", f"r02_glm{name}_ncu_summary.txt"), "w") as f:
         f.write("\n".join(out) + "\n")
     if per and work["chains"] == 1:
-        li, b, hit = per[-1]  # a sampling launch
+        li, b, hit, _ = per[-1]  # a sampling launch
         tj = {"glm_kernel_bytes_per_grad_eval": b, "algorithmic_bytes_per_grad_eval": 128403652,
               "lts_sector_hit_rate_pct": hit, "commit": commit, "captured": "round 2",
               "recipe": "python tools/ncu_traffic.py capture && python tools/ncu_traffic.py parse "
