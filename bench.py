@@ -736,6 +736,29 @@ def run_chain_workload(args):
         roofline = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                     "traffic": None, "peak_source": src, "kernel": "batch_matvec_kernel (whole step timed)",
                     "bytes_per_grad_eval": per}
+    elif args.workload == "sv":
+        # six D-vectors of chain state per leapfrog if the vectors live in HBM
+        peak, src = peaks()
+        per = 6 * D_flat * 4
+        ach = per * local_g / (local_ms * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                    "traffic": None, "peak_source": src, "kernel": "chain_kernel<2> (CTA per chain)",
+                    "bytes_per_grad_eval": per,
+                    "note": "state-traffic figure of SURVEY 8d (72 KB per chain and leapfrog); the kernel is "
+                            "latency-bound on block-wide reductions and dependent loads (DESIGN 4.2)"}
+    elif args.workload == "eight_schools":
+        # no meaningful HBM roofline (state in registers, ~200 flops per gradient): issue-slot
+        # utilisation from the committed ncu capture + the collection write bandwidth of this run
+        roofline = {"bound": "issue_slots", "achieved": None, "peak": 100.0, "unit": "% of issue slots",
+                    "frac": None, "traffic": None, "kernel": "chain_kernel<0> (thread per chain)",
+                    "collection_write_gbs": (T_ * chains * D_flat * 4 * args.steps) / (local_ms * 1e-3) / 1e9}
+        pj = os.path.join(ROOT, "profiles", "eight_schools_ncu.json")
+        if os.path.exists(pj):
+            with open(pj) as f:
+                nj = json.load(f)
+            roofline.update({"achieved": nj.get("issue_active_pct"), "frac": (nj.get("issue_active_pct") or 0) / 100.0,
+                             "active_threads_per_inst": nj.get("active_threads_per_inst"),
+                             "source": {k: nj.get(k) for k in ("commit", "recipe", "launch")}})
     elif args.workload == "logistic_many":
         # two contractions of 2*N*D*C flops each, three TF32 passes; dense TF32 peak 1130 TFLOP/s
         # (blackwell guide; MEASURED_PEAKS.json holds bf16 only)
