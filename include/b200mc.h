@@ -236,6 +236,24 @@ int b200mc_diag_ess_rhat(const float* x_dev, int n_total, int first, int n, int 
 int b200mc_potential_and_grad_passes(b200mc_handle* h, const float* z_dev, int passes,
                                      float* U_dev, float* grad_dev, void* stream);
 
+/* Allocation-free variant of the horseshoe potential + gradient (the kernel behind
+ * b200mc_potential_and_grad for the HORSESHOE family below the lock-step threshold).  NO
+ * COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  It needs no handle and allocates nothing (no cudaMalloc / cudaFree / allocating
+ * library call): the kernel's scratch -- one residual per (point, data row), n * N floats --
+ * lives in a file-scope device array of B200MC_NOALLOC_MAX_FLOATS floats (4 MiB) that every GPU
+ * that loads the library holds until exit; n * N beyond that is refused with an error.
+ * Inputs and outputs are the caller's device buffers: X[N][ncols] f32 row-major, Y[N] f32,
+ * likelihood 0 Bernoulli(logits) / 1 Normal, z[n][D] with D = 2 * ncols + 1 (+ 1 if Normal) in
+ * flat sorted-site order, U[n], grad[n][D].  Asynchronous on `stream`.  All calls share the one
+ * scratch array (it keeps the last call's contents; nothing in it has to start at zero): calls
+ * that overlap on the GPU -- different streams, different host threads -- RACE; serialise them. */
+#define B200MC_NOALLOC_MAX_FLOATS (1u << 20)
+int b200mc_horseshoe_potential_noalloc(const float* X_dev, const float* Y_dev, int N, int ncols,
+                                       int likelihood, const float* z_dev, int n, float* U_dev,
+                                       float* grad_dev, void* stream);
+
 /* jax.random on Threefry-2x32 (tier-1 parity hooks). */
 int b200mc_threefry2x32(const uint32_t* key_dev /*[n][2]*/, const uint32_t* ctr_dev /*[n][2]*/,
                         uint32_t* out_dev /*[n][2]*/, int n, void* stream);

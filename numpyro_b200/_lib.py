@@ -92,6 +92,7 @@ SYMBOLS = {
     "b200mc_membench": (_i, [_u64, _i, _i, _i, _i, C.POINTER(_f), _vp]),
     "b200mc_potential_and_grad": (_i, [_vp, _vp, _i, _vp, _vp, _vp]),
     "b200mc_potential_and_grad_passes": (_i, [_vp, _vp, _i, _vp, _vp, _vp]),
+    "b200mc_horseshoe_potential_noalloc": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp, _vp]),
     "b200mc_threefry2x32": (_i, [_vp, _vp, _vp, _i, _vp]),
     "b200mc_random_split": (_i, [_vp, _i, _i, _vp, _i, _vp]),
     "b200mc_random_bits": (_i, [_vp, _i, _vp, _i, _vp]),

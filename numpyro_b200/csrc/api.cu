@@ -1537,3 +1537,65 @@ extern "C" int b200mc_obs_forward(const float* X_dev, int N, int K, const float*
   g_launches++;
   return 0;
 }
+
+// ---------------------------------------------------------------- allocation-free entry point
+// b200mc_horseshoe_potential_noalloc: the horseshoe potential + gradient kernel
+// (chain_potential_kernel, models.cuh) with its per-point residual scratch -- [n][N] floats, which
+// the handle-based path takes from the caching allocator at b200mc_create -- in a file-scope
+// device array instead, for callers that must not allocate (CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc).  Every GPU that loads the library holds the 4 MiB
+// until exit.  No counterpart in the reference.
+// Calls no cudaMalloc / cudaFree / allocating library routine.  The array is shared by every
+// call and keeps the last call's contents; nothing in it has to start at zero (the kernel writes
+// every residual before it reads it), but two calls that overlap on the GPU (different streams)
+// race on it.
+namespace {
+constexpr size_t kNoAllocScratchFloats = B200MC_NOALLOC_MAX_FLOATS;
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocScratchFloats];
+constexpr int kNoAllocMaxDevices = 64;
+float* g_noalloc_ptr[kNoAllocMaxDevices] = {};  // device address of the array, per device
+std::mutex g_noalloc_mu;
+}  // namespace
+
+extern "C" int b200mc_horseshoe_potential_noalloc(const float* X_dev, const float* Y_dev, int N,
+                                                  int ncols, int likelihood, const float* z_dev, int n,
+                                                  float* U_dev, float* grad_dev, void* stream) {
+  if (!X_dev || !Y_dev || !z_dev || !U_dev || !grad_dev) return fail("null argument");
+  if (N < 1 || ncols < 1 || n < 1) return fail("horseshoe_potential_noalloc: N, ncols and n must be >= 1");
+  if (likelihood != 0 && likelihood != 1) return fail("horseshoe_potential_noalloc: likelihood must be 0 or 1");
+  if ((size_t)n * (size_t)N > kNoAllocScratchFloats)
+    return fail("horseshoe_potential_noalloc: n * N = %zu residuals exceed the static scratch of %zu floats "
+                "(B200MC_NOALLOC_MAX_FLOATS); use the handle-based b200mc_potential_and_grad",
+                (size_t)n * (size_t)N, kNoAllocScratchFloats);
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return fail("horseshoe_potential_noalloc: device index %d", dev);
+  float* scratch = nullptr;
+  {
+    // In host code the array's name is only a stand-in: the device address comes from
+    // cudaGetSymbolAddress, once per device, with that device current.
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+      float* p = nullptr;
+      CK(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+      g_noalloc_ptr[dev] = p;
+    }
+    scratch = g_noalloc_ptr[dev];
+  }
+  ModelData M;
+  memset(&M, 0, sizeof(M));
+  M.family = B200MC_HORSESHOE;
+  M.N = N;
+  M.ncols = ncols;
+  M.likelihood = likelihood;
+  M.D = 2 * ncols + 1 + (likelihood == 1 ? 1 : 0);
+  M.a = X_dev;
+  M.b = Y_dev;
+  M.scratch = scratch;
+  cudaStream_t st = (cudaStream_t)stream;
+  // same chain grouping as a handle of this shape (b200mc_create): thread / warp / CTA per point
+  const int mode = (M.D <= 32) ? 0 : (M.D <= 512 ? 1 : 2);
+  CK(kl::chain_potential_launch(mode, M, z_dev, U_dev, grad_dev, n, st));
+  g_launches++;
+  return 0;
+}
