@@ -737,14 +737,26 @@ static int launch_chain(b200mc_handle* h, const CollectSpec& col, const uint32_t
     }
     L.end_thresh = thresh;
   }
+  L.hot_mask = 0u;
   if (h->mode == 0) {
     const int threads = 64;  // small blocks spread the chains over all SMs
-    CK(kl::chain_launch(0, L, (h->C + threads - 1) / threads, threads, st));
+    CK(kl::chain_launch(0, L, (h->C + threads - 1) / threads, threads, 0, st));
   } else if (h->mode == 1) {
     const int wpb = 4;
-    CK(kl::chain_launch(1, L, (h->C + wpb - 1) / wpb, wpb * 32, st));
+    CK(kl::chain_launch(1, L, (h->C + wpb - 1) / wpb, wpb * 32, 0, st));
   } else {
-    CK(kl::chain_launch(2, L, h->C, kChainCtaThreads, st));
+    // hot slots in shared memory when four resident CTAs per SM still fit (B200MC_CHAIN_HOT=0: off)
+    static int hot_on = -1;
+    if (hot_on < 0) {
+      const char* e = getenv("B200MC_CHAIN_HOT");
+      hot_on = e ? atoi(e) : 1;
+    }
+    size_t smem = 0;
+    if (hot_on && !h->P.dense_mass && 4 * (chain_hot_bytes(h->D, kChainHotMask) + 1024) <= (size_t)h->max_smem) {
+      L.hot_mask = kChainHotMask;
+      smem = chain_hot_bytes(h->D, kChainHotMask);
+    }
+    CK(kl::chain_launch(2, L, h->C, kChainCtaThreads, smem, st));
   }
   g_launches++;
   return 0;

@@ -21,7 +21,20 @@ struct ChainLaunch {
   int c_pad;                // thread-per-chain: chains padded to a multiple of 32
   int end_thresh;           // thread-per-chain: lanes that must wait at a subtree end before
                             // the tail runs (1 = never wait), see chain_kernel<0>
+  unsigned hot_mask;        // CTA-per-chain: slots kept in (dynamic) shared memory, see kChainHotMask
 };
+
+// CTA per chain: the leaf under construction (position, momentum, gradient) and the subtree's
+// momentum sum are read and written several times per leapfrog; in the global work array every
+// one of those is an L2 / HBM round trip (39 slots x 12 KB per stochastic-volatility chain, 1,024
+// chains: 480 MB, past the L2).  They live in shared memory instead when four copies of D floats
+// fit four resident CTAs per SM.
+constexpr unsigned kChainHotMask = (1u << LZ) | (1u << LR) | (1u << LG) | (1u << S_RSUM);
+__host__ __device__ inline size_t chain_hot_bytes(int D, unsigned mask) {
+  int n = 0;
+  for (unsigned m = mask; m; m &= m - 1) ++n;
+  return (size_t)n * D * sizeof(float);
+}
 
 // MODE 0: thread per chain (work is [slot][D][c_pad]); 1: warp per chain; 2: CTA per
 // chain (work is [chain][slot][D]).
@@ -37,6 +50,7 @@ template <int MODE>
 __global__ void __launch_bounds__(MODE == 2 ? kChainCtaThreads : 128, MODE == 2 ? B200MC_CTA_MINB : 1)
 chain_kernel(const __grid_constant__ ChainLaunch L) {
   __shared__ float red_scratch[64];
+  extern __shared__ float hot_slots[];
   const int D = L.P.D;
   const int nslots = num_slots(L.P.max_depth, L.P.dense_mass);
   int chain;
@@ -102,6 +116,10 @@ chain_kernel(const __grid_constant__ ChainLaunch L) {
   auto run = [&](auto g) {
     Sampler<decltype(g)> S;
     S.setup(&L.P, g, base, sstride, es, chain, L.C, &L.col);
+    if (MODE == 2 && L.hot_mask) {
+      S.hot = hot_slots;
+      S.hot_mask = L.hot_mask;
+    }
     S.load(L.cs, L.cv);
     StepResult r;
     if (L.init_keys)

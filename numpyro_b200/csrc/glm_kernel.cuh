@@ -162,6 +162,15 @@ __device__ __forceinline__ uint2 ld_relaxed_sys_v2(const uint2* p) {
   asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
   return v;
 }
+// Clock read that the hardware cannot issue before `dep` is available: bar.sync is deferred-
+// blocking, so a bare clock read placed after it may issue before the barrier completes.
+__device__ __forceinline__ long long clk_after(int dep) {
+  long long t;
+  asm volatile("{\n\t.reg .b32 z;\n\tand.b32 z, %1, 0;\n\tmov.u64 %0, %%clock64;\n\t}"
+               : "=l"(t) : "r"(dep) : "memory");
+  return t;
+}
+__device__ __forceinline__ long long clk_ordered() { return clk_after(0); }
 __device__ __forceinline__ void consumer_bar() {  // named barrier 1: consumer warps only
   asm volatile("bar.sync 1, %0;" ::"n"(kGlmConsumerThreads) : "memory");
 }
@@ -229,16 +238,18 @@ __global__ void glm_retile_kernel(const float* __restrict__ X, const uint8_t* __
 // zero-padded to 4G floats (shared).  acc[k] accumulates, per lane, (sigmoid(l) - y) * x[k]
 // over this lane's rows.  GT = G for the register-resident variant (G <= 16); GT = 0 selects
 // the wide variant (G <= 32), which re-reads the row for the gradient.
-template <int GT>
+template <int GT, typename Release>
 __device__ __forceinline__ void glm_tile(const float4* __restrict__ xt,
                                          const uint8_t* __restrict__ ys, int rows,
                                          const float4* __restrict__ th4, int G,
-                                         float (&acc)[GT ? 4 * GT : 128], float& ll) {
+                                         float (&acc)[GT ? 4 * GT : 128], float& ll,
+                                         Release release) {
   constexpr int GM = GT ? GT : 32;
   const int lane = threadIdx.x & 31;
   const float4* xr = xt + lane;
   float4 x[GT ? GT : 1];
   float2 l01 = make_float2(0.f, 0.f), l23 = make_float2(0.f, 0.f);
+  const float yv = (lane < rows) ? (float)ys[lane] : 0.f;
 #pragma unroll
   for (int g = 0; g < GM; ++g) {
     if (GT || g < G) {
@@ -250,9 +261,12 @@ __device__ __forceinline__ void glm_tile(const float4* __restrict__ xt,
     }
   }
   const float l = (l01.x + l01.y) + (l23.x + l23.y);
+  // Register-resident variant: the row now lives in x[] (l depends on every load, so they have
+  // all returned), the stage can go back to the producer before the sigmoid and the gradient
+  // FMAs -- its time out of flight is what bounds the ring's bytes in flight (Little's law)
+  if (GT) release(l + yv);
   float gres = 0.f;
   if (lane < rows) {
-    const float yv = (float)ys[lane];
     const float e = expf(-fabsf(l));
     const float inv = rcp_1to2(1.0f + e);
     const float sig = (l >= 0.f) ? inv : e * inv;
@@ -272,6 +286,7 @@ __device__ __forceinline__ void glm_tile(const float4* __restrict__ xt,
       acc[4 * g + 2] = a23.x; acc[4 * g + 3] = a23.y;
     }
   }
+  if (!GT) release(0.f);
 }
 
 // Recursive-halving transpose-reduce: on return a[0] of lane L holds the sum over all
@@ -370,10 +385,14 @@ __device__ __forceinline__ void glm_consume_pass(const GlmLaunch& L, unsigned ch
       tile = tile0 + (rev ? (nt - 1 - j) : j);
     }
     const int rows = (tile == L.nt_total - 1) ? (L.N - 32 * tile) : 32;
-    glm_tile<GT>(reinterpret_cast<const float4*>(sp), sp + G * 512, rows, th4, G, acc, ll);
-    __syncwarp();
+    glm_tile<GT>(reinterpret_cast<const float4*>(sp), sp + G * 512, rows, th4, G, acc, ll,
+                 [&](float dep) {
+                   // `dep` carries the data dependence on this lane's loads of the tile
+                   asm volatile("" ::"f"(dep) : "memory");
+                   __syncwarp();
+                   if (stage >= 0 && lane == 0) mbar_arrive(&empty[stage]);
+                 });
     if (stage >= 0) {
-      if (lane == 0) mbar_arrive(&empty[stage]);
       p_next += kGlmConsumerWarps;
       if (++si == m) {
         si = 0;
@@ -446,6 +465,8 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
       while (j >= nt) { j -= nt; ++pass_l; }
       uint32_t n_issued = 0;
       unsigned char* sp = smem + (long)s * tb;
+      // (polling, not a blocking mbarrier.try_wait: sleeping lanes woke late enough to cost 5 %
+      // of the pass, profiles/r02_glm_stream_experiments.md)
       while (!flags[0]) {
         if (mbar_test_wait(&empty[s], (n_issued & 1u) ^ 1u)) {
           const int jj = (L.reverse_odd && (pass_l & 1)) ? (nt - 1 - j) : j;
@@ -646,7 +667,7 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
   uint32_t ph = 0;
   int pass = 0;
   handoff_bar();  // theta of pass 0
-  long long t_mark = clock64();
+  long long t_mark = clk_ordered();
   unsigned long long c_stream = 0, c_wait = 0, c_reduce = 0, c_sampler = 0;
   while (flags[2]) {
     // ---- stream this CTA's tiles
@@ -678,14 +699,14 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
       flags[1] = pass + 1;
       __threadfence();
       red_release_add(L.arrive, 1u);
-      const long long t1 = clock64();
+      const long long t1 = clk_ordered();
       c_stream += (unsigned long long)(t1 - t_mark);
       const bool ok = spin_until_ge(L.arrive, (unsigned)(pass + 1) * (unsigned)nCTA);
       if (!ok) {
         atomicExch(L.error, 1);
         flags[3] = 0;
       }
-      t_mark = clock64();
+      t_mark = clk_ordered();
       c_wait += (unsigned long long)(t_mark - t1);
     }
     consumer_bar();
@@ -718,13 +739,13 @@ __global__ void __launch_bounds__(kGlmThreads, 1) glm_kernel(const __grid_consta
     }
     long long t2 = 0;
     if (tid == 0) {
-      t2 = clock64();
+      t2 = clk_ordered();
       c_reduce += (unsigned long long)(t2 - t_mark);
     }
     handoff_bar();  // red2 -> control warp
     handoff_bar();  // control warp -> next theta
     if (tid == 0) {
-      t_mark = clock64();
+      t_mark = clk_after(flags[2]);  // a value the control warp wrote before the barrier
       c_sampler += (unsigned long long)(t_mark - t2);
     }
     ++pass;

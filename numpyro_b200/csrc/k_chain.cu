@@ -5,10 +5,16 @@
 namespace b200mc {
 namespace kl {
 
-cudaError_t chain_launch(int mode, const ChainLaunch& L, int grid, int block, cudaStream_t st) {
+cudaError_t chain_launch(int mode, const ChainLaunch& L, int grid, int block, size_t smem, cudaStream_t st) {
   if (mode == 0) chain_kernel<0><<<grid, block, 0, st>>>(L);
   else if (mode == 1) chain_kernel<1><<<grid, block, 0, st>>>(L);
-  else chain_kernel<2><<<grid, block, 0, st>>>(L);
+  else {
+    if (smem > 48 * 1024) {
+      cudaError_t e = cudaFuncSetAttribute(chain_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+    }
+    chain_kernel<2><<<grid, block, smem, st>>>(L);
+  }
   return cudaGetLastError();
 }
 cudaError_t chain_potential_launch(int mode, const ModelData& M, const float* z, float* U, float* grad,

@@ -160,7 +160,17 @@ struct Sampler {
   Key ad_kss;             // adapt stages: key of the window-end step-size search
   bool ad_middle, ad_reinit;
 
-  __device__ __forceinline__ float* v(int slot) const { return w + (long)slot * slot_stride; }
+  // CTA-per-chain kernels may keep a few hot slots (the leaf under construction) in shared
+  // memory instead of the chain's global work array: hot_mask has their bits, `hot` their copies
+  float* hot;
+  unsigned hot_mask;
+  __device__ __forceinline__ float* v(int slot) const {
+    if constexpr (G::kBlockWide) {
+      if (slot < 32 && ((hot_mask >> slot) & 1u))
+        return hot + (long)__popc(hot_mask & ((1u << slot) - 1u)) * D;
+    }
+    return w + (long)slot * slot_stride;
+  }
   __device__ __forceinline__ float* ckpt_r(int i) const { return v(CKPT0 + ck_stride * i); }
   __device__ __forceinline__ float* ckpt_rs(int i) const { return v(CKPT0 + ck_stride * i + 1); }
   __device__ __forceinline__ float* ckpt_v(int i) const { return v(CKPT0 + 3 * i + 2); }  // dense only
@@ -200,6 +210,7 @@ struct Sampler {
     deferred = 0;
     end_yield = false; y_sub_turning = false;
     mv_yield = false; leaf_cached = false; mv_resume = 0;
+    hot = nullptr; hot_mask = 0u;
   }
 
   __device__ void load(const ChainScalars* cs, const ChainVectors& cv) {

@@ -49,6 +49,9 @@ class Config:
     def split(self, key, n=2):
         return rnd.split(key, n, partitionable=self.partitionable)
 
+    def random_bits(self, key, shape=()):
+        return rnd.random_bits(key, shape, partitionable=self.partitionable)
+
     def uniform(self, key, shape=(), lo=0.0, hi=1.0):
         return rnd.uniform(key, shape, lo, hi, partitionable=self.partitionable).astype(self.dtype)
 
