@@ -35,7 +35,11 @@ extern "C" {
 
 typedef struct b200mc_handle b200mc_handle;
 
-enum { B200MC_LOGISTIC = 0, B200MC_EIGHT_SCHOOLS = 1, B200MC_HORSESHOE = 2, B200MC_SV = 3 };
+enum { B200MC_LOGISTIC = 0, B200MC_EIGHT_SCHOOLS = 1, B200MC_HORSESHOE = 2, B200MC_SV = 3,
+       /* LOGISTIC with a subsampled plate, for HMCECS (hmc_gibbs.py:502-665): see subsample_size */
+       B200MC_LOGISTIC_ECS = 4,
+       /* EIGHT_SCHOOLS data; the centred model under LocScaleReparam(centered), reparam.py:64-145 */
+       B200MC_EIGHT_SCHOOLS_LOCSCALE = 5 };
 enum { B200MC_NUTS = 0, B200MC_HMC = 1 };
 
 /* Arguments of NUTS.__init__/HMC.__init__ (hmc.py:625-642, 913-930) + MCMC's
@@ -93,6 +97,17 @@ typedef struct {
   const int* block_perm_host;
   const int* block_sizes_host;
   const int* block_dense_host;
+  /* LOGISTIC_ECS (examples/covtype.py:66-71 with subsample_size, under HMCECS): the potential is
+   * evaluated on each chain's current subsample of `subsample_size` of the N rows.
+   * ecs_degree 0: no proxy, the subsample log-likelihood scaled by N/m (plate scale);
+   * 1 / 2: difference estimator with a first / second order Taylor control variate around
+   * ecs_ref_dev[D] (hmc_gibbs.py:584-588, contrib/ecs_proxies.py:23-52,94-278); the sums over
+   * ALL rows at the reference point are computed once by b200mc_create. */
+  int subsample_size;
+  int ecs_degree;
+  const float* ecs_ref_dev;
+  /* EIGHT_SCHOOLS_LOCSCALE: 0 <= centered <= 1 (1 = the centred model, 0 = fully decentred) */
+  float centered;
 } b200mc_config;
 
 /* Scalar leaves of HMCState (hmc.py:31-48) and HMCAdaptState (hmc_util.py:18-30). */
@@ -149,7 +164,7 @@ typedef struct {
 const char* b200mc_last_error(void);
 /* ABI version of the loaded library; a binding compares it with the B200MC_ABI_VERSION it was
  * written against before calling anything else (numpyro_b200/_lib.py does). */
-#define B200MC_ABI_VERSION 2
+#define B200MC_ABI_VERSION 3
 int b200mc_version(void);
 
 /* HMC.__init__ + the data binding of MCMC.run.  Raises (returns non-zero) for an
@@ -206,6 +221,26 @@ int b200mc_membench(uint64_t bytes, int tile_bytes, int n_stages, int passes, in
  * n points z[n][D]: tier-2 parity hook. */
 int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, int n, float* U_dev,
                               float* grad_dev, void* stream);
+
+/* ---- HMCECS (numpyro/infer/hmc_gibbs.py:502-665) on a LOGISTIC_ECS handle; all on `stream`.
+ * b200mc_ecs_init_subsample: every chain's initial subsample = the plate's value in the
+ *   prototype trace `trace(substitute(seed(model, key_u), init_to_sample))` (hmc_gibbs.py:547-552):
+ *   key_u_dev[C][2]; the seed handler's splits for the sites before the plate, then the
+ *   Fisher-Yates of primitives.py:443-462 (one jax.random.randint per index).
+ * b200mc_ecs_get_subsample / _set_subsample: idx[C][subsample_size] int32, device pointers.
+ * b200mc_ecs_update: one Gibbs step per chain (hmc_gibbs.py:619-652): rng_key = split(key)[0];
+ *   _update_block(rng_key, num_blocks, ...) (contrib/ecs_proxies.py:58-73) proposes one block of
+ *   new indices; pe_new at the chain's current z; accept_prob = min(exp(pe - pe_new), 1);
+ *   bernoulli(rng_key, accept_prob); on acceptance the chain's subsample, potential energy and
+ *   z_grad are replaced.  keys_dev[C][2] is overwritten with rng_key; accept_prob_dev[C]. */
+int b200mc_ecs_init_subsample(b200mc_handle* h, const uint32_t* key_u_dev, void* stream);
+int b200mc_ecs_get_subsample(b200mc_handle* h, int32_t* idx_dev, void* stream);
+int b200mc_ecs_set_subsample(b200mc_handle* h, const int32_t* idx_dev, void* stream);
+int b200mc_ecs_update(b200mc_handle* h, uint32_t* keys_dev, int num_blocks, float* accept_prob_dev,
+                      void* stream);
+/* tier-1 hook: jax.random.randint(key, (n,), minval, maxval) int32 (n = 0: shape ()) */
+int b200mc_random_randint(const uint32_t* key_dev, int n, int minval, int maxval,
+                            int partitionable, int32_t* out_dev, void* stream);
 
 /* log_likelihood / Predictive (numpyro/infer/util.py:803-1148) for the registered families'
  * observation site over S posterior draws: m[s][i] = X[i] . B[s] (X_dev [N][K] row-major and

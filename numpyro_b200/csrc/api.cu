@@ -72,6 +72,10 @@ struct b200mc_handle {
   unsigned* xarrive[kGlmMaxRanks] = {};
   bool comm_ready = false;
   bool initialized = false;
+  // HMCECS (LOGISTIC_ECS): subsamples, proposals, proxy sums, scratch
+  int *ecs_idx = nullptr, *ecs_prop = nullptr, *ecs_hash = nullptr;
+  float *ecs_sums = nullptr, *ecs_ref = nullptr, *ecs_gtmp = nullptr;
+  int ecs_hcap = 0;
   // many-chain lock-step engine (mode 3): operand images and GEMM plumbing
   struct Batch {
     unsigned char *x_hi = nullptr, *x_lo = nullptr;    // X   [RA1][K1]
@@ -134,9 +138,14 @@ static int family_sites(const b200mc_config& c, SamplerParams& P, int& D) {
   // sites in TRACE order with their offsets in the flat (sorted-name) vector
   switch (c.family) {
     case B200MC_LOGISTIC:  // coefs
+    case B200MC_LOGISTIC_ECS:
       D = c.ncols;
       P.nsites = 1; P.site_off[0] = 0; P.site_size[0] = D;
       return 0;
+    case B200MC_EIGHT_SCHOOLS_LOCSCALE:  // trace: mu, tau, theta(_decentered) == sorted
+      if (!(c.centered >= 0.f && c.centered <= 1.f))
+        return fail("`centered` argument does not satisfy `0 <= centered <= 1`.");
+      [[fallthrough]];
     case B200MC_EIGHT_SCHOOLS:  // trace: mu, tau, theta_base == sorted
       D = 2 + c.N;
       P.nsites = 3;
@@ -166,7 +175,7 @@ static int family_sites(const b200mc_config& c, SamplerParams& P, int& D) {
     }
     default:
       return fail("model family %d is not a registered potential family (logistic=0, "
-                  "eight_schools=1, horseshoe=2, stochastic_volatility=3); no fallback", c.family);
+                  "eight_schools=1, horseshoe=2, stochastic_volatility=3, logistic_ecs=4, eight_schools_locscale=5); no fallback", c.family);
   }
 }
 
@@ -320,6 +329,8 @@ extern "C" void b200mc_destroy(b200mc_handle* h) {
   dfree(h->work); dfree(h->partials); dfree(h->mc_partials); dfree(h->counters); dfree(h->prof); dfree(h->glm_xt); dfree(h->mc_xt);
   dfree(h->cv.dense); dfree(h->dense_replicas); dfree(h->M.scratch);
   dfree(h->blk_tables);
+  dfree(h->ecs_idx); dfree(h->ecs_prop); dfree(h->ecs_hash); dfree(h->ecs_sums); dfree(h->ecs_ref);
+  dfree(h->ecs_gtmp);
   for (int r = 0; r < h->nranks; ++r) {
     if (r == h->rank) continue;
     if (h->xchg[r]) cudaIpcCloseMemHandle(h->xchg[r]);
@@ -405,6 +416,9 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   h->M.ncols = c.ncols;
   h->M.likelihood = c.likelihood;
   h->M.scratch = nullptr;
+  h->M.y8 = nullptr; h->M.ecs_idx = nullptr; h->M.ecs_ref = nullptr; h->M.ecs_sums = nullptr;
+  h->M.ecs_m = 0; h->M.ecs_degree = 0; h->M.scratch_stride = 0;
+  h->M.centered = c.centered;
 
   const size_t vec_bytes = (size_t)C * D * sizeof(float);
   auto alloc = [&](void** p, size_t bytes) {
@@ -610,6 +624,49 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
     // thread per chain (tiny D, diagonal mass), warp per chain, CTA per chain; or the
     // lock-step tensor-core engine (batch_kernel.cuh)
     h->mode = batch ? 3 : ((D <= 32 && !c.dense_mass) ? 0 : (D <= 512 ? 1 : 2));
+    if (c.family == B200MC_LOGISTIC_ECS) {
+      const int m = c.subsample_size, deg = c.ecs_degree;
+      if (!c.data0_dev || !c.data1_dev) { b200mc_destroy(h); return fail("logistic_ecs: data missing"); }
+      if (m < 1 || m >= c.N) { b200mc_destroy(h); return fail("logistic_ecs: need 0 < subsample_size < N"); }
+      if (deg < 0 || deg > 2 || (deg > 0 && !c.ecs_ref_dev)) {
+        b200mc_destroy(h);
+        return fail("logistic_ecs: ecs_degree must be 0, 1 or 2 (with ecs_ref_dev for 1, 2)");
+      }
+      if (deg == 2 && D > 62) { b200mc_destroy(h); return fail("logistic_ecs: second-order proxy needs D <= 62"); }
+      h->mode = 2;  // a CTA per chain: the subsample's rows are spread over its threads
+      h->M.y8 = (const uint8_t*)c.data1_dev;
+      h->M.ecs_m = m;
+      h->M.ecs_degree = deg;
+      h->M.scratch_stride = 2L * m + (long)kEcsSlices * D;
+      ACK(alloc((void**)&h->M.scratch, sizeof(float) * (size_t)C * h->M.scratch_stride));
+      ACK(alloc((void**)&h->ecs_idx, sizeof(int) * (size_t)C * m));
+      ACK(alloc((void**)&h->ecs_prop, sizeof(int) * (size_t)C * m));
+      ACK(alloc((void**)&h->ecs_gtmp, sizeof(float) * (size_t)C * D));
+      h->ecs_hcap = 16;
+      while (h->ecs_hcap < 4 * m) h->ecs_hcap *= 2;
+      ACK(alloc((void**)&h->ecs_hash, sizeof(int) * 2 * (size_t)C * h->ecs_hcap));
+      ACK(alloc((void**)&h->ecs_sums, sizeof(float) * (size_t)(1 + D + D * D)));
+      h->M.ecs_idx = h->ecs_idx;
+      h->M.ecs_sums = h->ecs_sums;
+      if (deg > 0) {
+        ACK(alloc((void**)&h->ecs_ref, sizeof(float) * D));
+        ACK(cudaMemcpy(h->ecs_ref, c.ecs_ref_dev, sizeof(float) * D, cudaMemcpyDeviceToDevice));
+        h->M.ecs_ref = h->ecs_ref;
+        const int nparts = 4 * h->num_sms;
+        float* parts = nullptr;
+        ACK(alloc((void**)&parts, sizeof(float) * (size_t)nparts * (1 + D + D * D)));
+        cudaError_t e = kl::ecs_taylor_sums_launch(h->M.a, h->M.y8, c.N, D, h->ecs_ref, deg, parts, nparts,
+                                                   h->ecs_sums, 0);
+        g_launches += 2;
+        if (e == cudaSuccess) e = cudaDeviceSynchronize();
+        dfree(parts);
+        ACK(e);
+      }
+      // until b200mc_ecs_init_subsample / _set_subsample: rows 0 .. m-1
+      std::vector<int> id0((size_t)C * m);
+      for (size_t i = 0; i < id0.size(); ++i) id0[i] = (int)(i % (size_t)m);
+      ACK(cudaMemcpy(h->ecs_idx, id0.data(), sizeof(int) * id0.size(), cudaMemcpyHostToDevice));
+    }
     if (const char* e = getenv("B200MC_CHAIN_MODE")) {  // tuning aid: force the chain grouping
       const int m = atoi(e);
       if (!batch && ((m == 0 && D <= 32 && !c.dense_mass) || (m == 1 && D <= 512) || m == 2)) h->mode = m;
@@ -1116,6 +1173,63 @@ extern "C" int b200mc_potential_and_grad_passes(b200mc_handle* h, const float* z
     return fail("multi-pass evaluation exists for the one-chain streaming (tall-data logistic) kernel only");
   const CollectSpec col = make_collect(0, 0, 1, nullptr);
   return launch_glm(h, col, nullptr, 0, 0, z_dev, U_dev, grad_dev, (cudaStream_t)stream, passes);
+}
+
+// ---------------------------------------------------------------- HMCECS (hmc_gibbs.py:502-665)
+static int ecs_check(b200mc_handle* h) {
+  if (!h) return fail("null handle");
+  if (h->cfg.family != B200MC_LOGISTIC_ECS) return fail("not a LOGISTIC_ECS handle");
+  return 0;
+}
+static void fill_ecs_launch(b200mc_handle* h, EcsLaunch& L) {
+  L.M = h->M; L.cs = h->cs; L.cv = h->cv; L.C = h->C; L.partitionable = h->P.partitionable;
+  L.idx = h->ecs_idx; L.idx_prop = h->ecs_prop; L.grad_tmp = h->ecs_gtmp;
+  L.keys = nullptr; L.accept_prob = nullptr; L.num_blocks = 1; L.key_u = nullptr;
+  L.sites_before_plate = 1;  // `coefs` precedes plate `N` in examples/covtype.py:66-71
+  L.hkeys = h->ecs_hash; L.hvals = h->ecs_hash + (size_t)h->C * h->ecs_hcap; L.hcap = h->ecs_hcap;
+}
+extern "C" int b200mc_ecs_init_subsample(b200mc_handle* h, const uint32_t* key_u_dev, void* stream) {
+  if (ecs_check(h)) return 1;
+  if (!key_u_dev) return fail("null argument");
+  EcsLaunch L;
+  fill_ecs_launch(h, L);
+  L.key_u = key_u_dev;
+  CK(kl::ecs_subsample_init_launch(L, (cudaStream_t)stream));
+  g_launches++;
+  return 0;
+}
+extern "C" int b200mc_ecs_get_subsample(b200mc_handle* h, int32_t* idx_dev, void* stream) {
+  if (ecs_check(h)) return 1;
+  CK(cudaMemcpyAsync(idx_dev, h->ecs_idx, sizeof(int) * (size_t)h->C * h->M.ecs_m,
+                     cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return 0;
+}
+extern "C" int b200mc_ecs_set_subsample(b200mc_handle* h, const int32_t* idx_dev, void* stream) {
+  if (ecs_check(h)) return 1;
+  CK(cudaMemcpyAsync(h->ecs_idx, idx_dev, sizeof(int) * (size_t)h->C * h->M.ecs_m,
+                     cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return 0;
+}
+extern "C" int b200mc_ecs_update(b200mc_handle* h, uint32_t* keys_dev, int num_blocks,
+                                 float* accept_prob_dev, void* stream) {
+  if (ecs_check(h)) return 1;
+  if (!h->initialized) return fail("b200mc_ecs_update called before b200mc_init / b200mc_set_*");
+  if (!keys_dev || !accept_prob_dev || num_blocks < 1) return fail("bad argument");
+  EcsLaunch L;
+  fill_ecs_launch(h, L);
+  L.keys = keys_dev;
+  L.accept_prob = accept_prob_dev;
+  L.num_blocks = num_blocks;
+  CK(kl::ecs_gibbs_launch(L, (cudaStream_t)stream));
+  g_launches++;
+  return 0;
+}
+extern "C" int b200mc_random_randint(const uint32_t* key_dev, int n, int minval, int maxval,
+                                     int partitionable, int32_t* out_dev, void* stream) {
+  if (!key_dev || !out_dev || n < 0) return fail("bad argument");
+  CK(kl::ecs_randint_launch(key_dev, n, minval, maxval, partitionable, out_dev, (cudaStream_t)stream));
+  g_launches++;
+  return 0;
 }
 
 // ---------------------------------------------------------------- roofline microbenchmark

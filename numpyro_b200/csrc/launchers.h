@@ -7,6 +7,7 @@
 #include "batch_kernel.cuh"
 #include "chain_kernel.cuh"
 #include "diag_kernel.cuh"
+#include "ecs_kernel.cuh"
 #include "gemm3x_kernel.cuh"
 #include "glm_kernel.cuh"
 #include "glm_mc_kernel.cuh"
@@ -44,6 +45,14 @@ cudaError_t diag_stats_launch(const DiagLaunch& L, size_t smem, cudaStream_t st)
 cudaError_t diag_finish_launch(const DiagFinish& L, cudaStream_t st);
 // k_obs.cu
 cudaError_t obs_forward_launch(const ObsLaunch& L, cudaStream_t st);
+// k_ecs.cu
+cudaError_t ecs_randint_launch(const uint32_t* key, int n, int minval, int maxval, int part, int* out,
+                               cudaStream_t st);
+cudaError_t ecs_subsample_init_launch(const EcsLaunch& L, cudaStream_t st);
+cudaError_t ecs_taylor_sums_launch(const float* X, const uint8_t* y, int N, int D, const float* ref,
+                                   int degree, float* partials, int nparts, float* out,
+                                   cudaStream_t st);
+cudaError_t ecs_gibbs_launch(const EcsLaunch& L, cudaStream_t st);
 // k_gemm.cu
 cudaError_t image_build_launch(const float* src, int R_src, int K_src, int transpose, int R, int K,
                                unsigned char* hi, unsigned char* lo, cudaStream_t st);

@@ -14,7 +14,9 @@
 
 namespace b200mc {
 
-enum Family { FAM_LOGISTIC = 0, FAM_EIGHT_SCHOOLS = 1, FAM_HORSESHOE = 2, FAM_SV = 3 };
+enum Family { FAM_LOGISTIC = 0, FAM_EIGHT_SCHOOLS = 1, FAM_HORSESHOE = 2, FAM_SV = 3,
+              FAM_LOGISTIC_ECS = 4, FAM_EIGHT_SCHOOLS_LOCSCALE = 5 };
+constexpr int kEcsSlices = 4;  // row slices of the subsample in the gradient sweep
 
 struct ModelData {
   int family;
@@ -24,7 +26,15 @@ struct ModelData {
   const float* b;  // eight schools: sigma[J];                 horseshoe: Y[N] (float)
   int ncols;       // horseshoe: number of covariates
   int likelihood;  // horseshoe: 0 Bernoulli(logits), 1 Normal(mean, prec_obs^-1/2)
-  float* scratch;  // horseshoe: [C][N] residuals dU/dmean
+  float* scratch;  // horseshoe: [C][N] residuals dU/dmean; logistic ECS: [C][scratch_stride]
+  // logistic with a subsampled plate (HMCECS): a = X[N][ncols], y8 = labels[N]
+  const uint8_t* y8;
+  const int* ecs_idx;     // [C][ecs_m] current subsample of every chain
+  const float* ecs_ref;   // [D] reference point of the Taylor proxy (degree > 0)
+  const float* ecs_sums;  // [1 + D + D*D] log-lik sum, its gradient and Hessian at ecs_ref, all rows
+  int ecs_m, ecs_degree;
+  long scratch_stride;    // 2 * ecs_m + kEcsSlices * D floats per chain
+  float centered;         // eight schools under LocScaleReparam(centered)
 };
 
 #define B200MC_LOG_SQRT_2PI 0.9189385332046727f
@@ -64,6 +74,51 @@ __device__ float eight_schools_potential(const ModelData& M, const G& g, const f
     grad[gs] = (2.0f * qq / (1.0f + qq)) - 1.0f + tau * s2;
   }
   g.sync();  // gradient elements are read back by their owner lanes
+  return -(lp0 + lp);
+}
+
+// Eight schools under LocScaleReparam(centered) (numpyro/infer/reparam.py:64-145) around the
+// centred model theta ~ Normal(mu, tau): z = [mu, log tau, t[J]], t = theta (centered = 1) or
+// theta_decentered ~ Normal(c mu, tau^c) (Normal(0, 1) for c = 0, :129-134) with
+// theta = mu + tau^(1-c) (t - c mu) (:141-142).
+template <class G>
+__device__ float eight_schools_locscale_potential(const ModelData& M, const G& g, const float* z,
+                                                  int zs, float* grad, int gs) {
+  const int J = M.N;
+  const float c = M.centered;
+  g.sync();
+  const float mu = z[0], tu = z[zs];
+  const float tau = expf(tu);
+  const float q = tau / 5.0f;
+  const float qq = q * q;
+  float lp0 = -0.5f * (mu / 5.0f) * (mu / 5.0f) - logf(B200MC_SQRT_2PI * 5.0f);
+  lp0 += (0.6931471805599453f - 1.1447298858494002f - 1.6094379124341003f - log1pf(qq)) + tu;
+  const float loc = (c == 0.f) ? 0.f : mu * c;
+  const float s = (c == 0.f) ? 1.f : powf(tau, c);
+  const float w = powf(tau, 1.0f - c);
+  const float log_s = logf(s);
+  float lp = 0.f, smu = 0.f, stu = 0.f;
+  for (int j = g.lane(); j < J; j += g.size()) {
+    const float t = z[(2 + j) * zs];
+    const float sig = M.b[j];
+    const float a = (t - loc) / s;
+    const float delta = t - c * mu;
+    const float theta = mu + w * delta;
+    const float resid = (M.a[j] - theta) / sig;
+    lp += ((-0.5f * a * a - log_s) - B200MC_LOG_SQRT_2PI) +
+          (-0.5f * resid * resid - logf(B200MC_SQRT_2PI * sig));
+    const float e = resid / sig;  // d lp / d theta_j
+    smu += a * c / s + e * (1.0f - w * c);
+    stu += (c * a * a - c) + (1.0f - c) * w * (e * delta);
+    grad[(2 + j) * gs] = a / s - e * w;
+  }
+  g.sum2(smu, stu);
+  lp = g.sum(lp);
+  if (g.lane() == 0) {
+    grad[0] = mu / 25.0f - smu;
+    grad[gs] = ((2.0f * qq / (1.0f + qq)) - 1.0f) - stu;
+  }
+  g.sync();
   return -(lp0 + lp);
 }
 
@@ -291,11 +346,121 @@ __device__ float horseshoe_potential(const ModelData& M, const G& g, const float
   return -lp;
 }
 
+// Logistic regression with a subsampled plate under HMCECS (examples/covtype.py:66-71 with
+// subsample_size; numpyro/infer/hmc_gibbs.py:502-665).  idx[m] is the chain's subsample.
+//   degree 0: U = -logN(theta) + (n/m) sum_i bce_i               (plate scale, no proxy)
+//   degree 1/2: estimate_likelihood + perturbed_method (contrib/ecs_proxies.py:23-52) with the
+//   Taylor proxy (:232-274): U = -logN(theta) - [proxy_sum(theta) + n mean(diff) - n^2/(2m) var(diff)],
+//   diff_i = loglik_i(theta) - proxy_i(theta); for Bernoulli(logits = x_i.theta) the per-row proxy is
+//   loglik_i* + (y_i - s_i*) d_i - 1/2 s_i*(1 - s_i*) d_i^2 with d_i = x_i.(theta - theta*), and
+//   proxy_sum = A + b.dt + 1/2 dt^T H dt with the all-row sums A, b, H of b200mc_create.
+template <class G>
+__device__ float logistic_ecs_potential(const ModelData& M, const G& g, const float* z, int zs,
+                                        float* grad, int gs, int chain, const int* idx) {
+  const int D = M.D, m = M.ecs_m, deg = M.ecs_degree, lane = g.lane(), size = g.size();
+  const float nf = (float)M.N, mf = (float)m, scale = nf / mf;
+  float* coef = M.scratch + (long)chain * M.scratch_stride;
+  float* dif = coef + m;
+  float* part = dif + m;
+  const float* ref = M.ecs_ref;
+  g.sync();
+  float prior = 0.f, s1 = 0.f;
+  for (int d = lane; d < D; d += size) {
+    const float t = z[d * zs];
+    prior += 0.5f * t * t + B200MC_LOG_SQRT_2PI;
+  }
+  for (int i = lane; i < m; i += size) {
+    const int row = idx[i];
+    const float* x = M.a + (long)row * M.ncols;
+    float l = 0.f, ls = 0.f, dl = 0.f;
+    for (int d = 0; d < D; ++d) {
+      const float xv = x[d], zv = z[d * zs];
+      l = fmaf(xv, zv, l);
+      if (deg) {
+        const float rv = ref[d];
+        ls = fmaf(xv, rv, ls);
+        dl = fmaf(xv, zv - rv, dl);
+      }
+    }
+    const float yv = (float)M.y8[row];
+    const float e = expf(-fabsf(l));
+    const float bce = (fmaxf(l, 0.f) + log1pf(e)) - l * yv;  // distributions/util.py:295-298
+    const float inv = 1.0f / (1.0f + e);
+    const float sig = (l >= 0.f) ? inv : e * inv;
+    if (!deg) {
+      s1 += bce;
+      coef[i] = scale * (yv - sig);
+    } else {
+      const float es = expf(-fabsf(ls));
+      const float bces = (fmaxf(ls, 0.f) + log1pf(es)) - ls * yv;
+      const float invs = 1.0f / (1.0f + es);
+      const float sigs = (ls >= 0.f) ? invs : es * invs;
+      float proxy = -bces + (yv - sigs) * dl;
+      float dproxy = yv - sigs;
+      if (deg == 2) {
+        const float w = sigs * (1.0f - sigs);
+        proxy -= 0.5f * w * dl * dl;
+        dproxy -= w * dl;
+      }
+      const float diff = -bce - proxy;
+      dif[i] = diff;
+      coef[i] = (yv - sig) - dproxy;  // d diff_i / d logit_i
+      s1 += diff;
+    }
+  }
+  g.sum2(prior, s1);
+  float U;
+  if (!deg) {
+    U = prior + scale * s1;
+  } else {
+    const float mean = s1 / mf;
+    float s2 = 0.f, ps = 0.f;
+    for (int i = lane; i < m; i += size) {  // this lane's own entries
+      const float dv = dif[i] - mean;
+      s2 += dv * dv;
+      coef[i] *= scale - (scale * scale) * dv;
+    }
+    const float* bsum = M.ecs_sums + 1;
+    const float* H = bsum + D;
+    for (int d = lane; d < D; d += size) {
+      const float dz = z[d * zs] - ref[d];
+      float hd = 0.f;
+      if (deg == 2)
+        for (int k = 0; k < D; ++k) hd = fmaf(H[(long)d * D + k], z[k * zs] - ref[k], hd);
+      grad[d * gs] = bsum[d] + hd;  // gradient of proxy_sum, folded in below
+      ps += bsum[d] * dz + 0.5f * hd * dz;
+    }
+    g.sum2(s2, ps);
+    const float var = s2 / mf;  // jnp.var: population variance
+    const float loglik = (M.ecs_sums[0] + ps) + nf * mean - 0.5f * (nf * nf / mf) * var;
+    U = prior - loglik;
+  }
+  g.sync();  // coef[] complete
+  for (int t = lane; t < kEcsSlices * D; t += size) {
+    const int sl = t / D, d = t - sl * D;
+    float a = 0.f;
+    for (int i = sl; i < m; i += kEcsSlices) a = fmaf(coef[i], M.a[(long)idx[i] * M.ncols + d], a);
+    part[t] = a;
+  }
+  g.sync();
+  for (int d = lane; d < D; d += size) {
+    float a = 0.f;
+    for (int sl = 0; sl < kEcsSlices; ++sl) a += part[sl * D + d];  // fixed order
+    const float gp = deg ? grad[d * gs] : 0.f;
+    grad[d * gs] = z[d * zs] - gp - a;
+  }
+  g.sync();
+  return U;
+}
+
 template <class G>
 __device__ __forceinline__ float model_potential(const ModelData& M, const G& g, const float* z,
                                                  int zs, float* grad, int gs, int chain) {
   if (M.family == FAM_EIGHT_SCHOOLS) return eight_schools_potential(M, g, z, zs, grad, gs);
   if (M.family == FAM_HORSESHOE) return horseshoe_potential(M, g, z, zs, grad, gs, chain);
+  if (M.family == FAM_EIGHT_SCHOOLS_LOCSCALE) return eight_schools_locscale_potential(M, g, z, zs, grad, gs);
+  if (M.family == FAM_LOGISTIC_ECS)
+    return logistic_ecs_potential(M, g, z, zs, grad, gs, chain, M.ecs_idx + (long)chain * M.ecs_m);
   return sv_potential(M, g, z, zs, grad, gs);
 }
 

@@ -146,6 +146,7 @@ class HMC(MCMCKernel):
         self._last_state = None
         self._row_shard = None  # (rank, nranks, allgather) -- see shard_rows
         self._bound_sig = None  # identity of the model args the device handle was built from
+        self._ecs = None  # set by HMCECS: {"degree", "ref", "after_create"} (hmc_gibbs.py)
 
     # ------------------------------------------------------------------ properties
     @property
@@ -208,7 +209,7 @@ class HMC(MCMCKernel):
         # everything that only exists after init() -- device handle and buffers, the model bound
         # to its data (holds closures), transports -- is dropped; init() rebuilds it
         for k in ("_sample_fn", "_init_fn", "_handle", "_data", "_last_state", "_postprocess_fn",
-                  "_row_shard", "_bound", "_potential_fn_gen", "_bound_sig"):
+                  "_row_shard", "_bound", "_potential_fn_gen", "_bound_sig", "_ecs"):
             state[k] = None
         state["_model"] = self._model.__name__  # registry entries hold closures: pickle by name
         return state
@@ -216,7 +217,7 @@ class HMC(MCMCKernel):
     def __setstate__(self, state):
         self.__dict__.update(state)
         if isinstance(self._model, str):
-            self._model = models.REGISTRY[self._model]
+            self._model = models.lookup(self._model)
 
     def _part(self):
         return int(b2random.DEFAULT_PARTITIONABLE if self.partitionable is None
@@ -266,6 +267,10 @@ class HMC(MCMCKernel):
         return blocks, key_order, user
 
     def _create(self, bound, num_chains, num_warmup):
+        if bound.family == models.LOGISTIC_ECS and self._ecs is None:  # primitives.py:444-449
+            raise ValueError("Missing random key to generate subsample indices."
+                             " Algorithms like HMC/NUTS do not support subsampling."
+                             " You might want to use SVI or HMCECS instead.")
         _lib.require_device()
         self._destroy()
         lib = _lib.lib()
@@ -315,6 +320,9 @@ class HMC(MCMCKernel):
         depth = self._max_tree_depth
         depth = depth if isinstance(depth, tuple) else (depth, depth)
         kind, arg = self._strategy()
+        ecs_ref = None
+        if bound.family == models.LOGISTIC_ECS and self._ecs["degree"]:
+            ecs_ref = _lib.DeviceArray.from_numpy(bound.ravel(self._ecs["ref"]).reshape(-1), np.float32)
         cfg = _lib.Config(
             struct_size=C.sizeof(_lib.Config), family=bound.family, num_chains=num_chains, N=bound.N, ncols=bound.ncols,
             data0_dev=d0.ptr, data1_dev=d1.ptr if d1 is not None else None,
@@ -338,7 +346,11 @@ class HMC(MCMCKernel):
             num_blocks=len(blocks),
             block_perm_host=tables[0].ctypes.data if tables else None,
             block_sizes_host=tables[1].ctypes.data if tables else None,
-            block_dense_host=tables[2].ctypes.data if tables else None)
+            block_dense_host=tables[2].ctypes.data if tables else None,
+            subsample_size=int(getattr(bound, "subsample_size", 0)),
+            ecs_degree=int(self._ecs["degree"]) if self._ecs else 0,
+            ecs_ref_dev=ecs_ref.ptr if ecs_ref is not None else None,
+            centered=float(getattr(bound, "centered", 0.0)))
         h = C.c_void_p()
         if self._row_shard and bound.family != models.LOGISTIC:
             raise NotImplementedError("row sharding exists for the tall-data logistic family only")
@@ -351,7 +363,7 @@ class HMC(MCMCKernel):
             if len(table) != self._row_shard[1] or any(len(t) != 128 for t in table):
                 raise _lib.B200Error("row sharding: allgather must return one 128-byte entry per rank")
             _lib.check(lib.b200mc_comm_import(h, C.create_string_buffer(b"".join(table), 128 * len(table))))
-        self._data = (d0, d1, imm)
+        self._data = (d0, d1, imm, ecs_ref)
         self._bound = bound
         self._num_chains = num_chains
         self._num_warmup = num_warmup
@@ -509,6 +521,8 @@ class HMC(MCMCKernel):
             z = z.reshape(keys.shape[0], bound.dim) if self._vectorized else z.reshape(1, bound.dim)
             z0 = _lib.DeviceArray.from_numpy(z, np.float32)
         kd = _lib.DeviceArray.from_numpy(keys)
+        if self._ecs is not None and self._ecs.get("after_create") is not None:
+            self._ecs["after_create"](self)  # HMCECS: the initial subsample, before the init search
         _lib.check(_lib.lib().b200mc_init(self._handle, kd.ptr, z0.ptr if z0 is not None else None,
                                           None))
         sc, vec = self._snapshot()

@@ -13,7 +13,7 @@ from collections import OrderedDict
 
 import numpy as np
 
-LOGISTIC, EIGHT_SCHOOLS, HORSESHOE, SV = 0, 1, 2, 3
+LOGISTIC, EIGHT_SCHOOLS, HORSESHOE, SV, LOGISTIC_ECS, EIGHT_SCHOOLS_LOCSCALE = 0, 1, 2, 3, 4, 5
 
 
 class BoundModel:
@@ -83,12 +83,18 @@ class RegisteredModel:
 
 
 def _bind_logistic(data, labels, subsample_size=None):
-    if subsample_size is not None:
-        raise NotImplementedError("subsample_size (HMCECS) is not part of the registered hot path")
     X = np.ascontiguousarray(data, np.float32)
     y = np.ascontiguousarray(labels).astype(np.uint8, copy=False)
     if X.ndim != 2 or y.shape != (X.shape[0],):
         raise ValueError("logistic_regression expects data [N, D] and labels [N]")
+    if subsample_size is not None and subsample_size != X.shape[0]:
+        # plate("N", N, subsample_size=m) (examples/covtype.py:69): the potential is evaluated on a
+        # subsample of the rows that HMCECS owns (hmc_gibbs.py:502-665)
+        bound = BoundModel(LOGISTIC_ECS, "logistic", X.shape[0], X.shape[1], X, y,
+                           [("coefs", (X.shape[1],))], lambda z: dict(z))
+        bound.subsample_size = int(subsample_size)
+        bound.plate_name = "N"
+        return bound
     return BoundModel(LOGISTIC, "logistic", X.shape[0], X.shape[1], X, y,
                       [("coefs", (X.shape[1],))], lambda z: dict(z))
 
@@ -109,6 +115,38 @@ def _bind_eight_schools(J, sigma, y=None):
     return BoundModel(EIGHT_SCHOOLS, "eight_schools", J, 0, y, sigma,
                       [("mu", ()), ("tau", ()), ("theta_base", (J,))], constrain,
                       positive=("tau",))
+
+
+def _bind_eight_schools_locscale(centered):
+    """The centred model ``theta ~ Normal(mu, tau)`` (README.md:60-68) under
+    ``LocScaleReparam(centered)`` (``numpyro/infer/reparam.py:64-145``); ``centered`` = 1 is the
+    centred model itself (``:119-120``)."""
+    centered = float(centered)
+    if not 0.0 <= centered <= 1.0:  # reparam.py:95-99
+        raise ValueError("`centered` argument does not satisfy `0 <= centered <= 1`.")
+    site = "theta" if centered == 1.0 else "theta_decentered"
+
+    def bind(J, sigma, y=None):
+        if y is None:
+            raise NotImplementedError("eight_schools without observations (prior sampling) is not registered")
+        sigma_ = np.ascontiguousarray(sigma, np.float32)
+        y_ = np.ascontiguousarray(y, np.float32)
+        assert sigma_.shape == (J,) and y_.shape == (J,)
+
+        def constrain(z):
+            mu, tau = z["mu"], np.exp(z["tau"])
+            out = {"mu": mu, "tau": tau, site: z[site]}
+            if centered != 1.0:  # reparam.py:141-145: the reparametrised site becomes deterministic
+                delta = z[site] - np.float32(centered) * mu[..., None]
+                out["theta"] = mu[..., None] + np.power(tau[..., None], np.float32(1.0 - centered)) * delta
+            return out
+
+        bound = BoundModel(EIGHT_SCHOOLS_LOCSCALE, "eight_schools_locscale", J, 0, y_, sigma_,
+                           [("mu", ()), ("tau", ()), (site, (J,))], constrain, positive=("tau",))
+        bound.centered = centered
+        return bound
+
+    return bind
 
 
 def _bind_sv(returns):
@@ -155,6 +193,9 @@ logistic_regression = RegisteredModel(
 eight_schools_noncentered = RegisteredModel(
     "eight_schools_noncentered", _bind_eight_schools,
     "Non-centred eight schools with TransformReparam (README.md:101-110)")
+eight_schools = RegisteredModel(
+    "eight_schools", _bind_eight_schools_locscale(1.0),
+    "Centred eight schools: theta ~ Normal(mu, tau) (README.md:60-68)")
 stochastic_volatility = RegisteredModel(
     "stochastic_volatility", _bind_sv,
     "Random-walk stochastic volatility (examples/stochastic_volatility.py:57-65)")
@@ -166,9 +207,39 @@ horseshoe_normal = RegisteredModel(
     "horseshoe_normal", _bind_horseshoe(1),
     "Horseshoe regression, Normal likelihood (examples/horseshoe_regression.py:37-58)")
 
-REGISTRY = {m.__name__: m for m in (logistic_regression, eight_schools_noncentered,
+REGISTRY = {m.__name__: m for m in (logistic_regression, eight_schools_noncentered, eight_schools,
                                     stochastic_volatility, horseshoe_bernoulli,
                                     horseshoe_normal)}
+
+
+def reparam(model, config):
+    """``numpyro.handlers.reparam(model, config=...)`` for the registered families: the centred
+    ``eight_schools`` with ``{"theta": LocScaleReparam(centered)}`` (``reparam.py:64-145``) or
+    ``{"theta": TransformReparam()}`` is NOT a rewrite of a traced program here -- it selects the
+    closed-form potential of the reparametrised model."""
+    from .infer.reparam import LocScaleReparam
+
+    model = resolve(model)
+    if model is not eight_schools or set(config) != {"theta"} or not isinstance(config["theta"], LocScaleReparam):
+        raise NotImplementedError(
+            "reparam is registered for models.eight_schools with config={'theta': LocScaleReparam(c)}")
+    c = config["theta"].centered
+    name = f"eight_schools[theta=LocScaleReparam({c!r})]"
+    if name not in REGISTRY:
+        REGISTRY[name] = RegisteredModel(name, _bind_eight_schools_locscale(c),
+                                         "eight schools under LocScaleReparam (reparam.py:64-145)")
+    return REGISTRY[name]
+
+
+def lookup(name):
+    """Registered model by name (how kernels pickle their model); reparametrised entries are
+    re-created on demand in a fresh process."""
+    if name not in REGISTRY and name.startswith("eight_schools[theta=LocScaleReparam("):
+        from .infer.reparam import LocScaleReparam
+
+        c = float(name[len("eight_schools[theta=LocScaleReparam("):-2])
+        reparam(eight_schools, {"theta": LocScaleReparam(c)})
+    return REGISTRY[name]
 
 
 def resolve(model):

@@ -105,6 +105,16 @@ def _sigmoid(l, e):
     return np.where(l >= 0, 1 / (1 + e), e / (1 + e))
 
 
+def perturbed_loglik(loglik_rows, proxy_rows, proxy_sum, n, m, f=np.float32):
+    """``perturbed_method.estimator`` (``contrib/ecs_proxies.py:23-52``) for one subsample site:
+    ``proxy_sum + n mean(diff) - 0.5 n^2/m var(diff)``.  Returns (estimate, diff, mean)."""
+    n, m = f(n), f(m)
+    diff = (loglik_rows - proxy_rows).astype(f)
+    mean = diff.mean(dtype=f)
+    var = ((diff - mean) ** 2).mean(dtype=f)  # jnp.var: population variance
+    return f(proxy_sum + n * mean - f(0.5) * (n * n / m) * var), diff, mean
+
+
 class LogisticECS(Family):
     """``coefs ~ Normal(0, 1)[D]``; plate ``N`` of size n subsampled to m rows;
     ``obs ~ Bernoulli(logits = X[idx] @ coefs)``.
@@ -170,10 +180,7 @@ class LogisticECS(Family):
             Hd = self.ref_hess @ dz
             proxy_sum = proxy_sum + f(0.5) * (Hd @ dz)
             gsum = gsum + Hd
-        diff = (-bce) - proxy
-        mean = diff.mean(dtype=self.dtype)
-        var = ((diff - mean) ** 2).mean(dtype=self.dtype)  # jnp.var: population variance
-        loglik = proxy_sum + n * mean - f(0.5) * (n * n / m) * var  # ecs_proxies.py:44-46
+        loglik, diff, mean = perturbed_loglik(-bce, proxy, proxy_sum, self.n, self.m, f)
         U = prior - loglik
         cdiff = (ys - sig) - dproxy
         coef = cdiff * (n / m - (n * n / (m * m)) * (diff - mean))

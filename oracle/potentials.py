@@ -164,6 +164,70 @@ class EightSchools(Family):
 # --------------------------------------------------------------------------
 # Horseshoe regression: examples/horseshoe_regression.py:37-78
 # --------------------------------------------------------------------------
+class EightSchoolsLocScale(Family):
+    """Eight schools with ``reparam(config={"theta": LocScaleReparam(centered)})``
+    (``numpyro/infer/reparam.py:64-145``) around the centred model ``theta ~ Normal(mu, tau)``.
+
+    ``centered`` = 1: the centred model itself, z = [mu, log tau, theta[J]].  Otherwise the latent
+    is ``theta_decentered ~ Normal(centered * mu, tau ** centered)`` (``Normal(0, 1)`` for 0,
+    ``reparam.py:129-134``) and ``theta = mu + tau ** (1 - centered) * (theta_decentered -
+    centered * mu)`` is deterministic (``:141-142``); z = [mu, log tau, theta_decentered[J]].
+    """
+
+    name = "eight_schools_locscale"
+
+    def __init__(self, sigma, y, centered=0.0, dtype=np.float32):
+        super().__init__(dtype)
+        self.sigma = np.asarray(sigma, self.dtype)
+        self.y = np.asarray(y, self.dtype)
+        self.J = self.y.shape[0]
+        self.centered = float(centered)
+        if not 0.0 <= self.centered <= 1.0:
+            raise ValueError("`centered` argument does not satisfy `0 <= centered <= 1`.")
+        self.site = "theta" if self.centered == 1.0 else "theta_decentered"
+        self.trace_sites = (("mu", 1), ("tau", 1), (self.site, self.J))
+
+    def potential_and_grad(self, z):
+        f = self.dtype.type
+        z = np.asarray(z, self.dtype)
+        c = f(self.centered)
+        mu, tu, t = z[0], z[1], z[2:]
+        tau = np.exp(tu)
+        lp = -f(0.5) * (mu / f(5)) ** 2 - np.log(f(math.sqrt(2 * math.pi)) * f(5))
+        q = tau / f(5)
+        lp = lp + (f(math.log(2.0)) - f(math.log(math.pi)) - np.log(f(5)) - np.log1p(q * q)) + tu
+        if self.centered == 0.0:
+            loc, s = f(0), f(1)
+        else:
+            loc, s = mu * c, np.power(tau, c)
+        a = (t - loc) / s
+        lp = lp + (-f(0.5) * a * a - np.log(s) - f(LOG_SQRT_2PI)).sum(dtype=self.dtype)
+        w = np.power(tau, f(1) - c)
+        delta = t - c * mu
+        theta = mu + w * delta
+        resid = (self.y - theta) / self.sigma
+        lp = lp + (-f(0.5) * resid * resid - np.log(f(math.sqrt(2 * math.pi)) * self.sigma)).sum(
+            dtype=self.dtype)
+        e = resid / self.sigma  # d lp / d theta_j
+        g = np.empty_like(z)
+        dmu = -mu / f(25) + (a * c / s).sum(dtype=self.dtype) + (e * (f(1) - w * c)).sum(dtype=self.dtype)
+        dtu = -(f(2) * q * q / (f(1) + q * q)) + f(1)
+        dtu = dtu + (c * a * a - c).sum(dtype=self.dtype) + ((f(1) - c) * w * (e * delta)).sum(dtype=self.dtype)
+        g[0] = -dmu
+        g[1] = -dtu
+        g[2:] = -(-a / s + e * w)
+        return self.dtype.type(-lp), g
+
+    def constrain(self, z):
+        z = np.asarray(z)
+        c = self.centered
+        mu, tau, t = z[..., 0], np.exp(z[..., 1]), z[..., 2:]
+        out = {"mu": mu, "tau": tau, self.site: t}
+        if c != 1.0:
+            out["theta"] = mu[..., None] + tau[..., None] ** (1 - c) * (t - c * mu[..., None])
+        return out
+
+
 class Horseshoe(Family):
     """z = [lambdas_u[D], (prec_obs_u,) tau_u, unscaled_betas[D]] (sorted names).
 

@@ -188,3 +188,22 @@ def test_kernel_pickles_after_binding_a_model(nb):
         assert k2._step_size == 0.5
         m2 = pickle.loads(pickle.dumps(MCMC(k, num_warmup=3, num_samples=4)))
         assert m2.num_samples == 4 and m2.sampler._model is model
+
+
+def test_nuts_alone_refuses_a_subsampled_plate():
+    """primitives.py:444-449: without HMCECS nothing owns the subsample indices."""
+    import numpy as np
+    import pytest
+    from numpyro_b200 import models
+    from numpyro_b200.infer import HMCECS, HMCGibbs, NUTS
+
+    X, y = np.zeros((300, 3), np.float32), np.zeros(300, np.uint8)
+    with pytest.raises(ValueError, match="do not support subsampling"):
+        NUTS(models.logistic_regression).init(np.array([0, 0], np.uint32), 5, None, (X, y),
+                                              {"subsample_size": 50})
+    with pytest.raises(ValueError, match="inner_kernel must be a HMC or NUTS sampler"):
+        HMCGibbs(object(), lambda **k: {}, [])  # hmc_gibbs.py:89-90
+    with pytest.raises(ValueError, match="gibbs_fn must be a callable"):
+        HMCGibbs(NUTS(models.logistic_regression), None, [])
+    with pytest.raises(AssertionError, match="Cannot detect any subsample statements"):
+        HMCECS(NUTS(models.logistic_regression)).init(np.array([0, 0], np.uint32), 5, None, (X, y), {})
