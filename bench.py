@@ -811,10 +811,114 @@ def run_chain_workload(args):
     return 0
 
 
+def run_ecs_workload(args):
+    """HMCECS on the covtype shape (the default algorithm of examples/covtype.py:154-165,223):
+    NUTS on a 1000-row subsample with the second-order Taylor proxy, 100 blocks.  One GPU; a step
+    is `--transitions` iterations of { Gibbs step; NUTS transition } in one launch."""
+    rank, world, local = dist_env()
+    if rank != 0:
+        return 0
+    sys.path.insert(0, ROOT)
+    import ctypes as C
+
+    import __graft_entry__ as g
+
+    g.build()
+    from numpyro_b200 import _lib, models
+    from numpyro_b200.diagnostics import bulk_effective_sample_size, split_gelman_rubin
+    from numpyro_b200.infer import HMCECS, NUTS
+    from numpyro_b200.random import PRNGKey, split
+
+    lib = _lib.lib()
+    _lib.require_device()
+    X, y = make_covtype_shape()
+    m, nb = 1000, 100
+    # reference parameters: the posterior mode by Newton steps on a 50,000-row slice, float64
+    # (the example gets them from SVI, covtype.py:137-152)
+    Xs, ys, ref = X[:50000].astype(np.float64), y[:50000].astype(np.float64), np.zeros(N_COLS)
+    scale = N_ROWS / Xs.shape[0]
+    for _ in range(12):
+        sg = 1.0 / (1.0 + np.exp(-Xs @ ref))
+        gr = ref + scale * (Xs.T @ (sg - ys))
+        H = np.eye(N_COLS) + scale * ((Xs.T * (sg * (1 - sg))) @ Xs)
+        ref = ref - np.linalg.solve(H, gr)
+    chains = args.chains or 1
+    kern = HMCECS(NUTS(models.logistic_regression), num_blocks=nb,
+                  proxy=HMCECS.taylor_proxy({"coefs": ref.astype(np.float32)}))
+    keys = split(PRNGKey(1), chains) if chains > 1 else PRNGKey(1)
+    margs, mkw = (X, y), {"subsample_size": m}
+    t0 = time.perf_counter()
+    state = kern.init(keys, args.adapt, None, margs, mkw)
+    _, state = kern.run_loop(state, args.adapt, 0, 1, 0, [], margs, mkw)
+    adapt_s = time.perf_counter() - t0
+    ev0, ev1 = lib.b200mc_event_create(), lib.b200mc_event_create()
+    clocks = ClockSampler(local)
+    tot_ms, tot_g, draws, accs, launches0 = 0.0, 0, [], [], None
+    T_ = args.transitions
+    for it in range(args.warmup + args.steps):
+        if it == args.warmup:
+            launches0 = lib.b200mc_kernel_launches()
+        _lib.check(lib.b200mc_event_record(ev0, None))
+        raw, state = kern.run_loop(state, T_, 0, 1, T_, ["z", "accept_prob", "hmc_state.num_steps"],
+                                   margs, mkw)
+        _lib.check(lib.b200mc_event_record(ev1, None))
+        ms = C.c_float()
+        _lib.check(lib.b200mc_event_elapsed_ms(ev0, ev1, C.byref(ms)))
+        if it >= args.warmup:
+            tot_ms += float(ms.value)
+            tot_g += int(raw["hmc_state.num_steps"].sum())
+            draws.append(raw["z"])
+            accs.append(raw["accept_prob"])
+    clk = clocks.stop()
+    launches = lib.b200mc_kernel_launches() - launches0
+    x = np.concatenate(draws, axis=0).transpose(1, 0, 2)
+    bulk = float(np.min(bulk_effective_sample_size(x)))
+    line = {
+        "metric": "grad_evals_per_sec", "value": tot_g / (tot_ms * 1e-3), "unit": "grad-evals/s",
+        "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": "covtype-shape logistic HMCECS(NUTS), subsample 1000 of 581012 rows, "
+                               "100 blocks, second-order Taylor proxy (examples/covtype.py:154-165)",
+                   "chains": chains, "transitions_per_step": T_, "adapt_transitions_untimed": args.adapt,
+                   "note": "a gradient evaluation here touches 1000 rows, not 581012"},
+        "transitions_per_sec": args.steps * T_ * chains / (tot_ms * 1e-3),
+        "mean_subsample_accept_prob": float(np.mean(np.concatenate(accs))),
+        "ess": {"metric": "min_bulk_ess_per_sec", "value": bulk / (tot_ms * 1e-3), "unit": "ESS/s",
+                "min_bulk_ess": bulk, "draws_per_chain": int(x.shape[1]), "chains": chains,
+                "max_split_r_hat": float(np.max(split_gelman_rubin(x.astype(np.float64))))},
+        "gpu_launches": int(launches), "clocks": clk, "adapt_seconds": adapt_s,
+        "posterior_mean_minus_mode_max_sd": float(np.max(
+            np.abs(x.reshape(-1, N_COLS).mean(0) - ref) / x.reshape(-1, N_COLS).std(0))),
+    }
+    if not args.no_cpu:  # the oracle's HMCECS on one core, same data / proxy / blocks
+        from oracle import ecs as oecs
+        from oracle.threefry import PRNGKey as OKey
+
+        fam = oecs.LogisticECS(X, y, m, 2, ref=ref.astype(np.float32))
+        ok = oecs.HMCECSKernel(fam, num_blocks=nb)
+        st = ok.init(OKey(1), 50)
+        t0, n_tr, g0 = time.perf_counter(), 0, None
+        while time.perf_counter() - t0 < args.cpu_budget:
+            if n_tr == 50:
+                g0, t1 = ok.inner.num_grad_evals, time.perf_counter()
+            st = ok.sample(st)
+            n_tr += 1
+        if g0 is not None and n_tr > 60:
+            dt = time.perf_counter() - t1
+            line["cpu_baseline"] = {"value": (ok.inner.num_grad_evals - g0) / dt, "unit": "grad-evals/s",
+                                    "cores": 1, "kind": "port",
+                                    "sample": f"{n_tr - 50} HMCECS transitions after 50 adaptive ones "
+                                              "(oracle/ecs.py, NumPy)",
+                                    "transitions_per_sec": (n_tr - 50) / dt}
+    print(json.dumps(line))
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workload", default="logistic",
-                    choices=["logistic", "eight_schools", "sv", "horseshoe", "logistic_many"])
+                    choices=["logistic", "eight_schools", "sv", "horseshoe", "logistic_many", "ecs"])
     ap.add_argument("--chains", type=int, default=0)
     ap.add_argument("--sharding", default="rows", choices=["chains", "rows"],
                     help="N>1 headline: one row-sharded chain (strong, configs[2]'s partitioning; "
@@ -841,6 +945,8 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "ecs":
+        return run_ecs_workload(args)
     if args.workload != "logistic":
         return run_chain_workload(args)
     return run_own(args)

@@ -238,6 +238,13 @@ int b200mc_ecs_get_subsample(b200mc_handle* h, int32_t* idx_dev, void* stream);
 int b200mc_ecs_set_subsample(b200mc_handle* h, const int32_t* idx_dev, void* stream);
 int b200mc_ecs_update(b200mc_handle* h, uint32_t* keys_dev, int num_blocks, float* accept_prob_dev,
                       void* stream);
+/* The whole HMCECS loop on the device: num_iters times { the Gibbs step of b200mc_ecs_update; one
+ * transition of the inner kernel }, in ONE launch, collecting like b200mc_sample.
+ * accept_prob_dev[C]: the last step's accept_prob; accept_all_dev[num_iters][C] (or NULL): every
+ * step's (HMCECSState.accept_prob of each iteration, hmc_gibbs.py:665). */
+int b200mc_ecs_sample(b200mc_handle* h, uint32_t* keys_dev, int num_blocks, int num_iters,
+                      int collect_start, int thinning, const b200mc_collect* out,
+                      float* accept_prob_dev, float* accept_all_dev, void* stream);
 /* tier-1 hook: jax.random.randint(key, (n,), minval, maxval) int32 (n = 0: shape ()) */
 int b200mc_random_randint(const uint32_t* key_dev, int n, int minval, int maxval,
                             int partitionable, int32_t* out_dev, void* stream);

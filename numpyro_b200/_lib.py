@@ -101,6 +101,7 @@ SYMBOLS = {
     "b200mc_ecs_get_subsample": (_i, [_vp, _vp, _vp]),
     "b200mc_ecs_set_subsample": (_i, [_vp, _vp, _vp]),
     "b200mc_ecs_update": (_i, [_vp, _vp, _i, _vp, _vp]),
+    "b200mc_ecs_sample": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "b200mc_random_split": (_i, [_vp, _i, _i, _vp, _i, _vp]),
     "b200mc_random_bits": (_i, [_vp, _i, _vp, _i, _vp]),
     "b200mc_random_uniform": (_i, [_vp, _i, _f, _f, _vp, _i, _vp]),

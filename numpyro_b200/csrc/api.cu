@@ -780,8 +780,10 @@ static CollectSpec make_collect(int num_iters, int collect_start, int thinning,
 }
 
 static int launch_chain(b200mc_handle* h, const CollectSpec& col, const uint32_t* keys,
-                        int user_init, cudaStream_t st) {
+                        int user_init, cudaStream_t st, const EcsStep* ecs = nullptr) {
   ChainLaunch L;
+  if (ecs) L.ecs = *ecs;
+  else memset(&L.ecs, 0, sizeof(L.ecs));
   L.P = h->P; L.M = h->M; L.col = col; L.cs = h->cs; L.cv = h->cv; L.work = h->work;
   L.init_keys = keys; L.user_init = user_init; L.C = h->C; L.c_pad = h->c_pad;
   {
@@ -1223,6 +1225,21 @@ extern "C" int b200mc_ecs_update(b200mc_handle* h, uint32_t* keys_dev, int num_b
   CK(kl::ecs_gibbs_launch(L, (cudaStream_t)stream));
   g_launches++;
   return 0;
+}
+extern "C" int b200mc_ecs_sample(b200mc_handle* h, uint32_t* keys_dev, int num_blocks, int num_iters,
+                                 int collect_start, int thinning, const b200mc_collect* out,
+                                 float* accept_prob_dev, float* accept_all_dev, void* stream) {
+  if (ecs_check(h)) return 1;
+  if (!h->initialized) return fail("b200mc_ecs_sample called before b200mc_init / b200mc_set_*");
+  if (!keys_dev || !accept_prob_dev || num_blocks < 1) return fail("bad argument");
+  if (num_iters <= 0) return 0;
+  if (thinning < 1) return fail("thinning must be a positive integer");
+  EcsStep E;
+  E.enabled = 1; E.idx = h->ecs_idx; E.prop = h->ecs_prop; E.gtmp = h->ecs_gtmp; E.keys = keys_dev;
+  E.accept_prob = accept_prob_dev; E.accept_all = accept_all_dev; E.num_blocks = num_blocks;
+  E.partitionable = h->P.partitionable;
+  const CollectSpec col = make_collect(num_iters, collect_start, thinning, out);
+  return launch_chain(h, col, nullptr, 0, (cudaStream_t)stream, &E);
 }
 extern "C" int b200mc_random_randint(const uint32_t* key_dev, int n, int minval, int maxval,
                                      int partitionable, int32_t* out_dev, void* stream) {

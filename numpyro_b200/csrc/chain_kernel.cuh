@@ -3,6 +3,7 @@
 // runs ALL of its transitions inside a single launch; chains advance independently
 // (no lock-step across chains, unlike the reference's vmap, hmc.py:797).
 #pragma once
+#include "ecs_kernel.cuh"
 #include "models.cuh"
 #include "sampler.cuh"
 
@@ -22,6 +23,7 @@ struct ChainLaunch {
   int end_thresh;           // thread-per-chain: lanes that must wait at a subtree end before
                             // the tail runs (1 = never wait), see chain_kernel<0>
   unsigned hot_mask;        // CTA-per-chain: slots kept in (dynamic) shared memory, see kChainHotMask
+  EcsStep ecs;              // HMCECS: the Gibbs step before every transition (enabled = 0: none)
 };
 
 // CTA per chain: the leaf under construction (position, momentum, gradient) and the subtree's
@@ -121,14 +123,33 @@ chain_kernel(const __grid_constant__ ChainLaunch L) {
       S.hot_mask = L.hot_mask;
     }
     S.load(L.cs, L.cv);
+    S.transition_hook = L.ecs.enabled != 0;
     StepResult r;
     if (L.init_keys)
       r = S.begin_init(Key{L.init_keys[2 * chain], L.init_keys[2 * chain + 1]}, L.user_init != 0);
     else
       r = S.begin_sampling();
-    while (r == NEED_GRAD) {
-      const float U = model_potential(L.M, g, S.v(LZ), es, S.v(LG), es, chain);
-      r = S.advance(U);
+    for (;;) {
+      if (r == NEED_GRAD) {
+        const float U = model_potential(L.M, g, S.v(LZ), es, S.v(LG), es, chain);
+        r = S.advance(U);
+      } else if (r == AT_TRANSITION_END) {
+        // HMCECS (hmc_gibbs.py:619-652): block update of the subsample at the current point
+        float pe_new;
+        const bool acc = ecs_propose_test(L.M, L.ecs, g, S.v(Z_PROP), es, S.s.potential_energy, chain,
+                                          S.local_iter, L.C, pe_new);
+        if (acc) {
+          S.s.potential_energy = pe_new;
+          float* gp = S.v(G_PROP);
+          const float* gt = L.ecs.gtmp + (long)chain * D;
+          for (int d = g.lane(); d < D; d += g.size()) gp[d * es] = gt[d];
+        }
+        S.s.grad_evals += 1;
+        g.sync();
+        r = S.resume_transition();
+      } else {
+        break;
+      }
     }
     S.store(L.cs, L.cv);
   };

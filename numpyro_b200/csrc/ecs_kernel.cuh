@@ -33,6 +33,66 @@ __host__ __device__ __forceinline__ int randint_at(Key key, uint32_t n, uint32_t
   return minval + (int)off;
 }
 
+// The Gibbs step of HMCECS.sample (hmc_gibbs.py:619-652) for one chain, executed by the chain's
+// group g (every lane computes the same keys and the same decision):
+//   rng_key = split(key)[0]; _update_block(rng_key, ...) -> proposal; pe_new = U(z; proposal);
+//   accept_prob = min(exp(pe - pe_new), 1) (NaN kept); accepted = uniform(rng_key) < accept_prob.
+// On acceptance the chain's subsample is replaced; the caller replaces potential energy and
+// gradient (left in gtmp[chain]).  keys[chain] <- rng_key, accept_prob[chain] <- accept_prob.
+struct EcsStep {
+  int enabled;
+  int* idx;            // [C][m] current subsamples (== ModelData::ecs_idx)
+  int* prop;           // [C][m] proposals
+  float* gtmp;         // [C][D] gradient at the proposal
+  uint32_t* keys;      // [C][2] wrapper keys, in / out
+  float* accept_prob;  // [C] accept_prob of the last step
+  float* accept_all;   // [num_iters][C] accept_prob of every step of a device-resident run, or null
+  int num_blocks, partitionable;
+};
+
+template <class G>
+__device__ bool ecs_propose_test(const ModelData& M, const EcsStep& E, const G& g, const float* z,
+                                 int zs, float pe, int chain, int local_iter, int C, float& pe_new) {
+  const bool part = E.partitionable != 0;
+  const int m = M.ecs_m, size = M.N, D = M.D;
+  int* idx = E.idx + (long)chain * m;
+  int* prop = E.prop + (long)chain * m;
+  // hmc_gibbs.py:619: rng_key, rng_gibbs = split(state.rng_key); rng_gibbs is not used
+  Key rng_key, unused;
+  split2(Key{E.keys[2 * chain], E.keys[2 * chain + 1]}, part, rng_key, unused);
+  // _update_block (contrib/ecs_proxies.py:58-73)
+  Key k_next, subkey, block_key;
+  split3(rng_key, part, k_next, subkey, block_key);
+  const int block_size = (m - 1) / E.num_blocks + 1;
+  const int pad = block_size - (m - 1) % block_size - 1;
+  const int chosen = randint_at(block_key, 1u, 0u, 0, E.num_blocks, part);
+  int start = chosen * block_size;
+  if (start > m + pad - block_size) start = m + pad - block_size;  // dynamic_update_slice clamps
+  if (start < 0) start = 0;
+  for (int i = g.lane(); i < m; i += g.size()) {
+    int v = idx[i];
+    if (i >= start && i < start + block_size)
+      v = randint_at(subkey, (uint32_t)block_size, (uint32_t)(i - start), 0, size, part);
+    prop[i] = v;
+  }
+  g.sync();
+  pe_new = logistic_ecs_potential(M, g, z, zs, E.gtmp + (long)chain * D, 1, chain, prop);
+  const float ex = expf(pe - pe_new);
+  const float ap = (ex != ex) ? ex : fminf(ex, 1.0f);  // jnp.clip(exp(pe - pe_new), None, 1): NaN stays NaN
+  const float u = uniform01(rng_key, part);            // random.bernoulli(rng_key, accept_prob)
+  const bool acc = u < ap;
+  if (g.lane() == 0) {
+    E.accept_prob[chain] = ap;
+    if (E.accept_all) E.accept_all[(long)local_iter * C + chain] = ap;
+    E.keys[2 * chain] = rng_key.k0;
+    E.keys[2 * chain + 1] = rng_key.k1;
+  }
+  if (acc)
+    for (int i = g.lane(); i < m; i += g.size()) idx[i] = prop[i];
+  g.sync();
+  return acc;
+}
+
 struct EcsLaunch {
   ModelData M;
   ChainScalars* cs;
@@ -183,52 +243,24 @@ __global__ void ecs_taylor_reduce_kernel(const float* partials, int nparts, int 
 // one CTA per chain
 __global__ void __launch_bounds__(256) ecs_gibbs_kernel(const EcsLaunch L) {
   __shared__ float red_scratch[64];
-  __shared__ int s_accept;
   const int chain = blockIdx.x;
   if (chain >= L.C) return;
-  const bool part = L.partitionable != 0;
-  const int m = L.M.ecs_m, size = L.M.N, D = L.M.D;
+  const int D = L.M.D;
   BlockGroup g{red_scratch};
-  int* idx = L.idx + (long)chain * m;
-  int* prop = L.idx_prop + (long)chain * m;
-  // hmc_gibbs.py:619: rng_key, rng_gibbs = split(state.rng_key); rng_gibbs is not used
-  Key rng_key, unused;
-  split2(Key{L.keys[2 * chain], L.keys[2 * chain + 1]}, part, rng_key, unused);
-  // _update_block (contrib/ecs_proxies.py:58-73)
-  Key k_next, subkey, block_key;
-  split3(rng_key, part, k_next, subkey, block_key);
-  const int block_size = (m - 1) / L.num_blocks + 1;
-  const int pad = block_size - (m - 1) % block_size - 1;
-  const int chosen = randint_at(block_key, 1u, 0u, 0, L.num_blocks, part);
-  int start = chosen * block_size;
-  if (start > m + pad - block_size) start = m + pad - block_size;  // dynamic_update_slice clamps
-  if (start < 0) start = 0;
-  for (int i = threadIdx.x; i < m; i += blockDim.x) {
-    int v = idx[i];
-    if (i >= start && i < start + block_size)
-      v = randint_at(subkey, (uint32_t)block_size, (uint32_t)(i - start), 0, size, part);
-    prop[i] = v;
-  }
-  __syncthreads();
-  float* gt = L.grad_tmp + (long)chain * D;
-  const float pe_new = logistic_ecs_potential(L.M, g, L.cv.z + (long)chain * D, 1, gt, 1, chain, prop);
+  EcsStep E;
+  E.enabled = 1; E.idx = L.idx; E.prop = L.idx_prop; E.gtmp = L.grad_tmp; E.keys = L.keys;
+  E.accept_prob = L.accept_prob; E.accept_all = nullptr; E.num_blocks = L.num_blocks;
+  E.partitionable = L.partitionable;
+  const float pe = L.cs[chain].potential_energy;
+  float pe_new;
+  const bool acc = ecs_propose_test(L.M, E, g, L.cv.z + (long)chain * D, 1, pe, chain, 0, L.C, pe_new);
   if (threadIdx.x == 0) {
-    const float pe = L.cs[chain].potential_energy;
-    const float ex = expf(pe - pe_new);
-    const float ap = (ex != ex) ? ex : fminf(ex, 1.0f);  // jnp.clip(exp(pe - pe_new), None, 1): NaN stays NaN
-    const float u = uniform01(rng_key, part);         // random.bernoulli(rng_key, accept_prob)
-    const int acc = (u < ap) ? 1 : 0;
-    s_accept = acc;
     if (acc) L.cs[chain].potential_energy = pe_new;
     L.cs[chain].grad_evals += 1;
-    L.accept_prob[chain] = ap;
-    L.keys[2 * chain] = rng_key.k0;
-    L.keys[2 * chain + 1] = rng_key.k1;
   }
-  __syncthreads();
-  if (s_accept) {
-    for (int i = threadIdx.x; i < m; i += blockDim.x) idx[i] = prop[i];
+  if (acc) {
     float* zg = L.cv.z_grad + (long)chain * D;
+    const float* gt = L.grad_tmp + (long)chain * D;
     for (int d = threadIdx.x; d < D; d += blockDim.x) zg[d] = gt[d];
   }
 }

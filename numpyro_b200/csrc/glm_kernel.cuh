@@ -253,8 +253,13 @@ __device__ __forceinline__ void glm_tile(const float4* __restrict__ xt,
 #pragma unroll
   for (int g = 0; g < GM; ++g) {
     if (GT || g < G) {
+#if B200MC_GLM_DBG  // timing experiments only (profiles/r02_glm_stream_experiments.md): wrong numerics
+      const float4 v = xr[((B200MC_GLM_DBG & 2) ? 0 : g) * 32];
+      const float4 t = (B200MC_GLM_DBG & 1) ? make_float4(0.01f, 0.02f, 0.03f, 0.04f) : th4[g];
+#else
       const float4 v = xr[g * 32];
       const float4 t = th4[g];
+#endif
       if (GT) x[g] = v;
       l01 = __ffma2_rn(make_float2(v.x, v.y), make_float2(t.x, t.y), l01);
       l23 = __ffma2_rn(make_float2(v.z, v.w), make_float2(t.z, t.w), l23);

@@ -65,7 +65,12 @@ enum StepResult { NEED_GRAD = 0, FINISHED = 1, NEED_MATVEC = 2, NEED_FACTOR = 3,
                   // long tail (combine, U-turn of the whole tree, next doubling's or next
                   // transition's Threefry draws, adaptation) runs in finish_subtree_yielded(),
                   // which the caller invokes when enough lanes of the warp wait for it
-                  AT_SUBTREE_END = 5 };
+                  AT_SUBTREE_END = 5,
+                  // only with transition_hook (HMCECS): a transition is complete (or sampling is
+                  // about to begin) and another follows; the caller may change the potential --
+                  // s.potential_energy and the gradient at v(G_PROP) -- and then calls
+                  // resume_transition()
+                  AT_TRANSITION_END = 6 };
 
 struct MatvecRequest {
   int mat;         // which of the chain's four D x D matrices
@@ -164,6 +169,7 @@ struct Sampler {
   // memory instead of the chain's global work array: hot_mask has their bits, `hot` their copies
   float* hot;
   unsigned hot_mask;
+  bool transition_hook;  // see AT_TRANSITION_END
   __device__ __forceinline__ float* v(int slot) const {
     if constexpr (G::kBlockWide) {
       if (slot < 32 && ((hot_mask >> slot) & 1u))
@@ -211,6 +217,7 @@ struct Sampler {
     end_yield = false; y_sub_turning = false;
     mv_yield = false; leaf_cached = false; mv_resume = 0;
     hot = nullptr; hot_mask = 0u;
+    transition_hook = false;
   }
 
   __device__ void load(const ChainScalars* cs, const ChainVectors& cv) {
@@ -841,8 +848,11 @@ struct Sampler {
       phase = PH_IDLE;
       return FINISHED;
     }
+    if (transition_hook) return AT_TRANSITION_END;
     return start_transition();
   }
+
+  __device__ StepResult resume_transition() { return start_transition(); }
 
   // ------------------------------------------------------------------ transition start
   // sample_kernel head (hmc.py:472-490) + build_tree head (hmc_util.py:1129-1153)
@@ -1232,7 +1242,7 @@ struct Sampler {
         combine_bookkeeping(sub_turning, tree_turning);
         s.potential_energy = prop_pe;
         s.energy = prop_energy;
-        if (s.i >= P->num_warmup && iters_left > 1) {
+        if (s.i >= P->num_warmup && iters_left > 1 && !transition_hook) {
           // sampling phase: nothing adapts between transitions, so the first point of the
           // next transition is known now (prefetched momentum draw and direction);
           // finish_transition / start_transition run in run_deferred() and recompute it
@@ -1515,12 +1525,14 @@ struct Sampler {
       phase = PH_IDLE;
       return FINISHED;
     }
+    if (transition_hook) return AT_TRANSITION_END;
     return start_transition();
   }
 
   // ------------------------------------------------------------------ driver interface
   __device__ StepResult begin_sampling() {
     if (iters_left <= 0 || s.status != 0) return FINISHED;
+    if (transition_hook) return AT_TRANSITION_END;
     return start_transition();
   }
 

@@ -572,6 +572,18 @@ class HMC(MCMCKernel):
         (``numpyro/util.py:277-407``).  Returns ``(dict of [n_keep, C, ...] arrays, last state)``."""
         self._check_args(model_args, model_kwargs or {})
         self._push_state(state)
+        bufs, col = self._collect_buffers(n_keep, fields)
+        _lib.check(_lib.lib().b200mc_sample(self._handle, int(num_iters), int(collect_start),
+                                            int(thinning), C.byref(col), None))
+        new_state = self._to_state(*self._snapshot())
+        out = {f: b.numpy() for f, b in bufs.items()}
+        if "diverging" in out:
+            out["diverging"] = out["diverging"].astype(bool)
+        return out, new_state
+
+    def _collect_buffers(self, n_keep, fields):
+        """Device buffers ``[n_keep, C, ...]`` for the collected ``fields`` and the C struct that
+        points at them."""
         Cn, D = self._num_chains, self._bound.dim
         bufs, col = {}, _lib.Collect(n_keep=n_keep)
         spec = {"z": ("z_dev", (n_keep, Cn, D), np.float32),
@@ -587,13 +599,7 @@ class HMC(MCMCKernel):
                 attr, shape, dt = spec[f]
                 bufs[f] = _lib.DeviceArray(shape, dt).zero_()
                 setattr(col, attr, bufs[f].ptr)
-        _lib.check(_lib.lib().b200mc_sample(self._handle, int(num_iters), int(collect_start),
-                                            int(thinning), C.byref(col), None))
-        new_state = self._to_state(*self._snapshot())
-        out = {f: b.numpy() for f, b in bufs.items()}
-        if "diverging" in out:
-            out["diverging"] = out["diverging"].astype(bool)
-        return out, new_state
+        return bufs, col
 
     def grad_evals(self):
         """Cumulative potential+gradient evaluations per chain (init search included)."""

@@ -192,3 +192,57 @@ class HMCECS(HMCGibbs):
         z = {name: self._get_subsample(), **hmc_state.z}
         self._last = HMCECSState(z, hmc_state, rng_key, (), ap)
         return self._last
+
+    # ------------------------------------------------------------------ fused loop (fori_collect)
+    @property
+    def _bound(self):
+        return self.inner_kernel._bound
+
+    def run_loop(self, state, num_iters, collect_start, thinning, n_keep, fields,
+                 model_args=(), model_kwargs=None):
+        """``num_iters`` iterations of { Gibbs step; inner transition } in ONE launch
+        (``b200mc_ecs_sample``), collecting like ``fori_collect`` (``numpyro/util.py:277-407``).
+        ``fields``: ``"z"`` (the HMC sites, flat), ``"accept_prob"`` (of the subsample update) and
+        ``"hmc_state.<field>"``.  Returns ``(dict of [n_keep, C, ...] arrays, last state)``."""
+        inner, lib = self.inner_kernel, _lib.lib()
+        if inner._handle is None:
+            raise RuntimeError("call `init` before `run_loop`")
+        name = self._gibbs_sites[0]
+        if state is not self._last:
+            inner._push_state(state.hmc_state)
+            self._set_subsample(state.z[name])
+        Cn = inner._num_chains
+        want_acc = "accept_prob" in fields
+        inner_fields = []
+        for f in fields:
+            if f == "z":
+                inner_fields.append("z")
+            elif f.startswith("hmc_state."):
+                inner_fields.append(f[len("hmc_state."):])
+            elif f != "accept_prob":
+                raise ValueError(f"HMCECS cannot collect field {f!r}")
+        bufs, col = inner._collect_buffers(n_keep, inner_fields)
+        keys = _lib.DeviceArray.from_numpy(np.ascontiguousarray(state.rng_key, np.uint32).reshape(Cn, 2))
+        acc = _lib.DeviceArray((Cn,), np.float32).zero_()
+        acc_all = _lib.DeviceArray((int(num_iters), Cn), np.float32).zero_() if want_acc else None
+        _lib.check(lib.b200mc_ecs_sample(inner._handle, keys.ptr, self._num_blocks, int(num_iters),
+                                         int(collect_start), int(thinning), C.byref(col), acc.ptr,
+                                         acc_all.ptr if acc_all is not None else None, None))
+        hmc_state = inner._to_state(*inner._snapshot())
+        rng_key, ap = keys.numpy(), acc.numpy()
+        if not inner._vectorized:
+            rng_key, ap = rng_key[0], ap[0]
+        z = {name: self._get_subsample(), **hmc_state.z}
+        self._last = HMCECSState(z, hmc_state, rng_key, (), ap)
+        out = {}
+        for f in fields:
+            if f == "z":
+                out[f] = bufs["z"].numpy()
+            elif f.startswith("hmc_state."):
+                v = bufs[f[len("hmc_state."):]].numpy()
+                out[f] = v.astype(bool) if f.endswith("diverging") else v
+        if want_acc:  # fori_collect keeps the LAST iteration of every thinning block
+            a = acc_all.numpy()
+            rows = collect_start + thinning - 1 + thinning * np.arange(n_keep)
+            out["accept_prob"] = a[rows[rows < num_iters]]
+        return out, self._last

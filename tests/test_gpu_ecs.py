@@ -141,6 +141,36 @@ def test_tier3_runs_decision_for_decision(degree, part):
     assert same_idx == T and same_steps == T, (same_idx, same_steps)
 
 
+def test_device_resident_loop_equals_step_by_step():
+    """``run_loop`` (one launch: Gibbs step + transition per iteration, adaptation included) gives
+    the draws, accept probabilities, tree sizes and final state of ``sample()`` called in a loop."""
+    from numpyro_b200.random import PRNGKey
+
+    X, y, th = _problem(n=6000, D=7, seed=5)
+    m, T, W = 250, 45, 25
+    out = []
+    for fused in (False, True):
+        gk, _ = _kernels(X, y, m, 2, th.astype(np.float32), 5, True, max_tree_depth=6)
+        st = gk.init(PRNGKey(11), W, None, (X, y), {"subsample_size": m})
+        if fused:
+            raw, st = gk.run_loop(st, T, 0, 1, T, ["z", "accept_prob", "hmc_state.num_steps"], (X, y),
+                                  {"subsample_size": m})
+            out.append((raw["z"][:, 0], raw["accept_prob"][:, 0], raw["hmc_state.num_steps"][:, 0], st))
+        else:
+            zs, ap, ns = [], [], []
+            for _ in range(T):
+                st = gk.sample(st, (X, y), {"subsample_size": m})
+                zs.append(st.hmc_state.z["coefs"]); ap.append(st.accept_prob); ns.append(st.hmc_state.num_steps)
+            out.append((np.stack(zs), np.asarray(ap), np.asarray(ns), st))
+    (z0, a0, n0, s0), (z1, a1, n1, s1) = out
+    np.testing.assert_array_equal(n0, n1)
+    np.testing.assert_array_equal(z0, z1)
+    np.testing.assert_array_equal(a0, a1)
+    np.testing.assert_array_equal(s0.z["N"], s1.z["N"])
+    np.testing.assert_array_equal(s0.rng_key, s1.rng_key)
+    assert s0.hmc_state.adapt_state.step_size == s1.hmc_state.adapt_state.step_size
+
+
 def test_tier4_posterior_matches_full_data_nuts():
     from numpyro_b200 import models
     from numpyro_b200.diagnostics import split_gelman_rubin

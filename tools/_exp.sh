@@ -1,6 +1,6 @@
 set -x
-timeout 1200 python -m pytest tests/test_gpu_ecs.py -m gpu -x -q 2>&1 | tail -40 > gpurun_out/exp3_ecs_tests.log
-timeout 600 python bench.py --workload eight_schools --chains 4 --adapt 1000 --transitions 1000 --steps 3 --warmup 1 > gpurun_out/r02_bench_eight_schools_4.json 2> gpurun_out/r02_bench_eight_schools_4.err
-timeout 900 python bench.py --workload sv > gpurun_out/r02_bench_sv.json 2> gpurun_out/r02_bench_sv.err
-timeout 900 python tools/ncu_chain.py capture eight_schools > gpurun_out/ncu_chain_es.log 2>&1
-ls -la gpurun_out | tail -20
+timeout 900 python -m pytest tests/test_gpu_ecs.py tests/test_reflocscale.py tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -15 > gpurun_out/exp4_tests.log
+timeout 600 python bench.py --workload ecs --steps 5 --warmup 2 --transitions 200 --adapt 500 > gpurun_out/r02_bench_ecs.json 2> gpurun_out/r02_bench_ecs.err
+B="--no-out-of-l2 --no-multi-chain --no-many-chain --no-cpu --steps 4 --warmup 3"
+for v in 1 2 3; do B200MC_LIB=$PWD/numpyro_b200/libdbg$v.so timeout 300 python bench.py $B > gpurun_out/exp4_dbg$v.json 2> gpurun_out/exp4_dbg$v.err; done
+ls -la gpurun_out | tail -8
