@@ -833,15 +833,15 @@ def run_ecs_workload(args):
     _lib.require_device()
     X, y = make_covtype_shape()
     m, nb = 1000, 100
-    # reference parameters: the posterior mode by Newton steps on a 50,000-row slice, float64
-    # (the example gets them from SVI, covtype.py:137-152)
-    Xs, ys, ref = X[:50000].astype(np.float64), y[:50000].astype(np.float64), np.zeros(N_COLS)
-    scale = N_ROWS / Xs.shape[0]
-    for _ in range(12):
-        sg = 1.0 / (1.0 + np.exp(-Xs @ ref))
-        gr = ref + scale * (Xs.T @ (sg - ys))
-        H = np.eye(N_COLS) + scale * ((Xs.T * (sg * (1 - sg))) @ Xs)
+    # reference parameters: the posterior mode by Newton steps on the full data, float64 (the
+    # example gets them from SVI, covtype.py:137-152)
+    X64, y64, ref = X.astype(np.float64), y.astype(np.float64), np.zeros(N_COLS)
+    for _ in range(8):
+        sg = 1.0 / (1.0 + np.exp(-X64 @ ref))
+        gr = ref + X64.T @ (sg - y64)
+        H = np.eye(N_COLS) + (X64.T * (sg * (1 - sg))) @ X64
         ref = ref - np.linalg.solve(H, gr)
+    del X64
     chains = args.chains or 1
     kern = HMCECS(NUTS(models.logistic_regression), num_blocks=nb,
                   proxy=HMCECS.taylor_proxy({"coefs": ref.astype(np.float32)}))

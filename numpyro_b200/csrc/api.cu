@@ -815,6 +815,16 @@ static int launch_chain(b200mc_handle* h, const CollectSpec& col, const uint32_t
       L.hot_mask = kChainHotMask;
       smem = chain_hot_bytes(h->D, kChainHotMask);
     }
+    if (L.ecs.enabled) {
+      const size_t rows = sizeof(float) * (size_t)h->M.ecs_m * h->M.ncols;
+      static int rows_on = -1;  // B200MC_ECS_ROWS_SMEM=0: gather the rows from X every time (A/B aid)
+      if (rows_on < 0) {
+        const char* e = getenv("B200MC_ECS_ROWS_SMEM");
+        rows_on = e ? atoi(e) : 1;
+      }
+      L.ecs.rows_in_smem = (rows_on && smem + rows + 2048 <= (size_t)h->max_smem) ? 1 : 0;
+      if (L.ecs.rows_in_smem) smem += rows;
+    }
     CK(kl::chain_launch(2, L, h->C, kChainCtaThreads, smem, st));
   }
   g_launches++;
@@ -1237,7 +1247,7 @@ extern "C" int b200mc_ecs_sample(b200mc_handle* h, uint32_t* keys_dev, int num_b
   EcsStep E;
   E.enabled = 1; E.idx = h->ecs_idx; E.prop = h->ecs_prop; E.gtmp = h->ecs_gtmp; E.keys = keys_dev;
   E.accept_prob = accept_prob_dev; E.accept_all = accept_all_dev; E.num_blocks = num_blocks;
-  E.partitionable = h->P.partitionable;
+  E.partitionable = h->P.partitionable; E.rows_in_smem = 0;
   const CollectSpec col = make_collect(num_iters, collect_start, thinning, out);
   return launch_chain(h, col, nullptr, 0, (cudaStream_t)stream, &E);
 }

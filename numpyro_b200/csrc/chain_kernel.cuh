@@ -116,6 +116,18 @@ chain_kernel(const __grid_constant__ ChainLaunch L) {
   if (chain >= L.C) return;
 
   auto run = [&](auto g) {
+    const ModelData& M = L.M;
+    float* ecs_rows = nullptr;
+    if (MODE == 2 && L.ecs.enabled && L.ecs.rows_in_smem) {
+      // HMCECS: the subsample is fixed during a transition and changes by one block between
+      // transitions -- its rows (m x ncols floats) stay in shared memory behind the hot slots
+      float* rows = hot_slots + chain_hot_bytes(D, L.hot_mask) / sizeof(float);
+      const int* idx = M.ecs_idx + (long)chain * M.ecs_m;
+      for (int t = g.lane(); t < M.ecs_m * M.ncols; t += g.size())
+        rows[t] = M.a[(long)idx[t / M.ncols] * M.ncols + t % M.ncols];
+      ecs_rows = rows;
+      g.sync();
+    }
     Sampler<decltype(g)> S;
     S.setup(&L.P, g, base, sstride, es, chain, L.C, &L.col);
     if (MODE == 2 && L.hot_mask) {
@@ -131,13 +143,13 @@ chain_kernel(const __grid_constant__ ChainLaunch L) {
       r = S.begin_sampling();
     for (;;) {
       if (r == NEED_GRAD) {
-        const float U = model_potential(L.M, g, S.v(LZ), es, S.v(LG), es, chain);
+        const float U = model_potential(M, g, S.v(LZ), es, S.v(LG), es, chain, ecs_rows);
         r = S.advance(U);
       } else if (r == AT_TRANSITION_END) {
         // HMCECS (hmc_gibbs.py:619-652): block update of the subsample at the current point
         float pe_new;
-        const bool acc = ecs_propose_test(L.M, L.ecs, g, S.v(Z_PROP), es, S.s.potential_energy, chain,
-                                          S.local_iter, L.C, pe_new);
+        const bool acc = ecs_propose_test(M, L.ecs, g, S.v(Z_PROP), es, S.s.potential_energy, chain,
+                                          S.local_iter, L.C, pe_new, ecs_rows);
         if (acc) {
           S.s.potential_energy = pe_new;
           float* gp = S.v(G_PROP);

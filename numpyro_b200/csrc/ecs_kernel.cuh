@@ -48,11 +48,13 @@ struct EcsStep {
   float* accept_prob;  // [C] accept_prob of the last step
   float* accept_all;   // [num_iters][C] accept_prob of every step of a device-resident run, or null
   int num_blocks, partitionable;
+  int rows_in_smem;    // device-resident loop: stage the subsample's rows behind the hot slots
 };
 
 template <class G>
 __device__ bool ecs_propose_test(const ModelData& M, const EcsStep& E, const G& g, const float* z,
-                                 int zs, float pe, int chain, int local_iter, int C, float& pe_new) {
+                                 int zs, float pe, int chain, int local_iter, int C, float& pe_new,
+                                 float* rows = nullptr) {
   const bool part = E.partitionable != 0;
   const int m = M.ecs_m, size = M.N, D = M.D;
   int* idx = E.idx + (long)chain * m;
@@ -76,7 +78,8 @@ __device__ bool ecs_propose_test(const ModelData& M, const EcsStep& E, const G& 
     prop[i] = v;
   }
   g.sync();
-  pe_new = logistic_ecs_potential(M, g, z, zs, E.gtmp + (long)chain * D, 1, chain, prop);
+  pe_new = logistic_ecs_potential(M, g, z, zs, E.gtmp + (long)chain * D, 1, chain, prop, rows, start,
+                                  start + block_size);
   const float ex = expf(pe - pe_new);
   const float ap = (ex != ex) ? ex : fminf(ex, 1.0f);  // jnp.clip(exp(pe - pe_new), None, 1): NaN stays NaN
   const float u = uniform01(rng_key, part);            // random.bernoulli(rng_key, accept_prob)
@@ -87,8 +90,16 @@ __device__ bool ecs_propose_test(const ModelData& M, const EcsStep& E, const G& 
     E.keys[2 * chain] = rng_key.k0;
     E.keys[2 * chain + 1] = rng_key.k1;
   }
-  if (acc)
+  if (acc) {
     for (int i = g.lane(); i < m; i += g.size()) idx[i] = prop[i];
+    if (rows) {  // refresh the staged copy of the replaced block
+      const int i1 = (start + block_size < m) ? start + block_size : m;
+      for (int t = g.lane(); t < (i1 - start) * M.ncols; t += g.size()) {
+        const int i = start + t / M.ncols, d = t % M.ncols;
+        rows[(long)i * M.ncols + d] = M.a[(long)prop[i] * M.ncols + d];
+      }
+    }
+  }
   g.sync();
   return acc;
 }
@@ -250,7 +261,7 @@ __global__ void __launch_bounds__(256) ecs_gibbs_kernel(const EcsLaunch L) {
   EcsStep E;
   E.enabled = 1; E.idx = L.idx; E.prop = L.idx_prop; E.gtmp = L.grad_tmp; E.keys = L.keys;
   E.accept_prob = L.accept_prob; E.accept_all = nullptr; E.num_blocks = L.num_blocks;
-  E.partitionable = L.partitionable;
+  E.partitionable = L.partitionable; E.rows_in_smem = 0;
   const float pe = L.cs[chain].potential_energy;
   float pe_new;
   const bool acc = ecs_propose_test(L.M, E, g, L.cv.z + (long)chain * D, 1, pe, chain, 0, L.C, pe_new);

@@ -390,13 +390,13 @@ __device__ __forceinline__ void glm_consume_pass(const GlmLaunch& L, unsigned ch
       tile = tile0 + (rev ? (nt - 1 - j) : j);
     }
     const int rows = (tile == L.nt_total - 1) ? (L.N - 32 * tile) : 32;
-    glm_tile<GT>(reinterpret_cast<const float4*>(sp), sp + G * 512, rows, th4, G, acc, ll,
-                 [&](float dep) {
-                   // `dep` carries the data dependence on this lane's loads of the tile
-                   asm volatile("" ::"f"(dep) : "memory");
-                   __syncwarp();
-                   if (stage >= 0 && lane == 0) mbar_arrive(&empty[stage]);
-                 });
+    auto release = [&](float dep) {
+      // `dep` carries the data dependence on this lane's loads of the tile
+      asm volatile("" ::"f"(dep) : "memory");
+      __syncwarp();
+      if (stage >= 0 && lane == 0) mbar_arrive(&empty[stage]);
+    };
+    glm_tile<GT>(reinterpret_cast<const float4*>(sp), sp + G * 512, rows, th4, G, acc, ll, release);
     if (stage >= 0) {
       p_next += kGlmConsumerWarps;
       if (++si == m) {

@@ -356,7 +356,16 @@ __device__ float horseshoe_potential(const ModelData& M, const G& g, const float
 //   proxy_sum = A + b.dt + 1/2 dt^T H dt with the all-row sums A, b, H of b200mc_create.
 template <class G>
 __device__ float logistic_ecs_potential(const ModelData& M, const G& g, const float* z, int zs,
-                                        float* grad, int gs, int chain, const int* idx) {
+                                        float* grad, int gs, int chain, const int* idx,
+                                        const float* rows = nullptr, int fresh0 = 0,
+                                        int fresh1 = 0) {
+  // rows: the subsample's rows staged in shared memory ([m][ncols], row i = X[idx[i]]; the
+  // device-resident HMCECS loop) or null (gathered from X through idx); rows [fresh0, fresh1) of
+  // the subsample differ from the staged copy (a proposal) and are gathered
+  auto rowp = [&](int i) -> const float* {
+    return (rows && !(i >= fresh0 && i < fresh1)) ? rows + (long)i * M.ncols
+                                                  : M.a + (long)idx[i] * M.ncols;
+  };
   const int D = M.D, m = M.ecs_m, deg = M.ecs_degree, lane = g.lane(), size = g.size();
   const float nf = (float)M.N, mf = (float)m, scale = nf / mf;
   float* coef = M.scratch + (long)chain * M.scratch_stride;
@@ -371,7 +380,7 @@ __device__ float logistic_ecs_potential(const ModelData& M, const G& g, const fl
   }
   for (int i = lane; i < m; i += size) {
     const int row = idx[i];
-    const float* x = M.a + (long)row * M.ncols;
+    const float* x = rowp(i);
     float l = 0.f, ls = 0.f, dl = 0.f;
     for (int d = 0; d < D; ++d) {
       const float xv = x[d], zv = z[d * zs];
@@ -439,7 +448,7 @@ __device__ float logistic_ecs_potential(const ModelData& M, const G& g, const fl
   for (int t = lane; t < kEcsSlices * D; t += size) {
     const int sl = t / D, d = t - sl * D;
     float a = 0.f;
-    for (int i = sl; i < m; i += kEcsSlices) a = fmaf(coef[i], M.a[(long)idx[i] * M.ncols + d], a);
+    for (int i = sl; i < m; i += kEcsSlices) a = fmaf(coef[i], rowp(i)[d], a);
     part[t] = a;
   }
   g.sync();
@@ -455,12 +464,14 @@ __device__ float logistic_ecs_potential(const ModelData& M, const G& g, const fl
 
 template <class G>
 __device__ __forceinline__ float model_potential(const ModelData& M, const G& g, const float* z,
-                                                 int zs, float* grad, int gs, int chain) {
+                                                 int zs, float* grad, int gs, int chain,
+                                                 const float* ecs_rows = nullptr) {
   if (M.family == FAM_EIGHT_SCHOOLS) return eight_schools_potential(M, g, z, zs, grad, gs);
   if (M.family == FAM_HORSESHOE) return horseshoe_potential(M, g, z, zs, grad, gs, chain);
   if (M.family == FAM_EIGHT_SCHOOLS_LOCSCALE) return eight_schools_locscale_potential(M, g, z, zs, grad, gs);
   if (M.family == FAM_LOGISTIC_ECS)
-    return logistic_ecs_potential(M, g, z, zs, grad, gs, chain, M.ecs_idx + (long)chain * M.ecs_m);
+    return logistic_ecs_potential(M, g, z, zs, grad, gs, chain, M.ecs_idx + (long)chain * M.ecs_m,
+                                  ecs_rows);
   return sv_potential(M, g, z, zs, grad, gs);
 }
 
