@@ -43,13 +43,15 @@ def workload(name):
 
     model, margs, mkw, kkw, chains, desc = bench.make_workload(name, 0)
     k = NUTS(model, **kkw)
-    m = MCMC(k, num_warmup=100, num_samples=30, num_chains=chains, chain_method="vectorized")
+    # ncu replays every launch ~40 times: the CTA-per-chain SV launches are seconds long
+    nw, ns_ = (20, 10) if name == "sv" else (100, 30)
+    m = MCMC(k, num_warmup=nw, num_samples=ns_, num_chains=chains, chain_method="vectorized")
     m.warmup(split(PRNGKey(0), chains), *margs, **mkw)
     g0 = int(np.asarray(k.grad_evals()).sum())
     m.run(m.post_warmup_state.rng_key, *margs, extra_fields=("num_steps",), **mkw)
     ns = int(m.get_extra_fields()["num_steps"].sum())
-    json.dump({"name": name, "chains": chains, "launches": [{"what": "init + 100 warm-up transitions", "grad_evals": g0},
-                                                            {"what": "30 sampling transitions", "grad_evals": ns}]},
+    json.dump({"name": name, "chains": chains, "launches": [{"what": f"init + {nw} warm-up transitions", "grad_evals": g0},
+                                                            {"what": f"{ns_} sampling transitions", "grad_evals": ns}]},
               open(paths(name)[2], "w"))
     print(g0, ns)
 
@@ -86,7 +88,8 @@ def parse(name):
             if k in col:
                 vals[k] = r[col[k]]
                 out.append(f"  {k} = {r[col[k]]} {rows[1][col[k]]}")
-        if w:
+        ok = "nan" not in str(vals.get("sm__issue_active.avg.pct_of_peak_sustained_elapsed", "nan")).lower()
+        if w and ok:  # a launch whose counters ncu failed to collect (nan) is listed, not used
             last = (vals, w)
     commit = subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
     open(os.path.join(ROOT, "profiles", f"r02_{name}_ncu_summary.txt"), "w").write("\n".join(out) + "\n")
@@ -97,6 +100,10 @@ def parse(name):
               "issue_active_pct": f("sm__issue_active.avg.pct_of_peak_sustained_elapsed"),
               "active_threads_per_inst": f("smsp__thread_inst_executed_per_inst_executed.ratio"),
               "warps_active_pct": f("sm__warps_active.avg.pct_of_peak_sustained_active"),
+              "dram_bytes_per_grad_eval": ((f("dram__bytes_read.sum") or 0) + (f("dram__bytes_write.sum") or 0)) * 1e9
+              / max(1, w["grad_evals"]) if rows[1][col["dram__bytes_read.sum"]] == "Gbyte" else None,
+              "fma_pipe_pct": f("sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active"),
+              "xu_pipe_pct": f("sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active"),
               "commit": commit, "recipe": f"python tools/ncu_chain.py capture {name} && python tools/ncu_chain.py parse {name}"}
         json.dump(js, open(os.path.join(ROOT, "profiles", f"{name}_ncu.json"), "w"), indent=1)
         print(json.dumps(js))
