@@ -39,7 +39,15 @@ enum { B200MC_LOGISTIC = 0, B200MC_EIGHT_SCHOOLS = 1, B200MC_HORSESHOE = 2, B200
        /* LOGISTIC with a subsampled plate, for HMCECS (hmc_gibbs.py:502-665): see subsample_size */
        B200MC_LOGISTIC_ECS = 4,
        /* EIGHT_SCHOOLS data; the centred model under LocScaleReparam(centered), reparam.py:64-145 */
-       B200MC_EIGHT_SCHOOLS_LOCSCALE = 5 };
+       B200MC_EIGHT_SCHOOLS_LOCSCALE = 5,
+       /* test/infer/test_mcmc.py:239-244: p ~ Beta(alpha, beta)[N], obs ~ Bernoulli(p);
+        * data0 = column counts of ones s[N] float32, data1 = [N][4] float32: number of
+        * observations, alpha, beta, lgamma(alpha) + lgamma(beta) - lgamma(alpha + beta) */
+       B200MC_BETA_BERNOULLI = 6,
+       /* test/infer/test_mcmc.py:283-288: p ~ Dirichlet(c[N]), obs ~ Categorical(p); flat
+        * dimension N - 1 (StickBreakingTransform); data0 = class counts[N] float32, data1 =
+        * c[N] followed by sum lgamma(c) - lgamma(sum c), float32 */
+       B200MC_DIRICHLET_CATEGORICAL = 7 };
 enum { B200MC_NUTS = 0, B200MC_HMC = 1 };
 
 /* Arguments of NUTS.__init__/HMC.__init__ (hmc.py:625-642, 913-930) + MCMC's

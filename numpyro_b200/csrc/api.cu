@@ -153,6 +153,15 @@ static int family_sites(const b200mc_config& c, SamplerParams& P, int& D) {
       P.site_off[1] = 1; P.site_size[1] = 1;
       P.site_off[2] = 2; P.site_size[2] = c.N;
       return 0;
+    case B200MC_BETA_BERNOULLI:  // p_latent
+      D = c.N;
+      P.nsites = 1; P.site_off[0] = 0; P.site_size[0] = D;
+      return 0;
+    case B200MC_DIRICHLET_CATEGORICAL:  // p_latent on the simplex: N - 1 unconstrained coordinates
+      if (c.N < 2) return fail("dirichlet_categorical: need at least two classes");
+      D = c.N - 1;
+      P.nsites = 1; P.site_off[0] = 0; P.site_size[0] = D;
+      return 0;
     case B200MC_SV:  // trace: sigma, s, nu; sorted: nu, s, sigma
       D = 2 + c.N;
       P.nsites = 3;
@@ -175,7 +184,7 @@ static int family_sites(const b200mc_config& c, SamplerParams& P, int& D) {
     }
     default:
       return fail("model family %d is not a registered potential family (logistic=0, "
-                  "eight_schools=1, horseshoe=2, stochastic_volatility=3, logistic_ecs=4, eight_schools_locscale=5); no fallback", c.family);
+                  "eight_schools=1, horseshoe=2, stochastic_volatility=3, logistic_ecs=4, eight_schools_locscale=5, beta_bernoulli=6, dirichlet_categorical=7); no fallback", c.family);
   }
 }
 

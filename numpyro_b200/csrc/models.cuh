@@ -15,7 +15,8 @@
 namespace b200mc {
 
 enum Family { FAM_LOGISTIC = 0, FAM_EIGHT_SCHOOLS = 1, FAM_HORSESHOE = 2, FAM_SV = 3,
-              FAM_LOGISTIC_ECS = 4, FAM_EIGHT_SCHOOLS_LOCSCALE = 5 };
+              FAM_LOGISTIC_ECS = 4, FAM_EIGHT_SCHOOLS_LOCSCALE = 5,
+              FAM_BETA_BERNOULLI = 6, FAM_DIRICHLET_CATEGORICAL = 7 };
 constexpr int kEcsSlices = 4;  // row slices of the subsample in the gradient sweep
 
 struct ModelData {
@@ -120,6 +121,77 @@ __device__ float eight_schools_locscale_potential(const ModelData& M, const G& g
   }
   g.sync();
   return -(lp0 + lp);
+}
+
+// Beta-Bernoulli of the reference's own test-suite (test/infer/test_mcmc.py:239-244):
+// p ~ Beta(alpha, beta)[K], obs[n][K] ~ Bernoulli(p); z = logit(p).  M.a = column counts of ones
+// s[K]; M.b = [K][4]: n, alpha, beta, lgamma(alpha) + lgamma(beta) - lgamma(alpha + beta).
+// SigmoidTransform with clipped expit and log|J| = -softplus(z) - softplus(-z)
+// (transforms.py:59-61,960-961); Beta via the Dirichlet log-density (continuous.py:193-194,
+// 292-299); Bernoulli(probs) with clamped probabilities (discrete.py:90-93).
+template <class G>
+__device__ float beta_bernoulli_potential(const ModelData& M, const G& g, const float* z, int zs,
+                                          float* grad, int gs) {
+  const int K = M.N;
+  float lp = 0.f;
+  for (int k = g.lane(); k < K; k += g.size()) {
+    const float zk = z[k * zs];
+    float p = 1.0f / (1.0f + expf(-zk));
+    p = fminf(fmaxf(p, 1.17549435e-38f), 1.0f - 1.1920929e-07f);
+    const float q = 1.0f - p;
+    const float s = M.a[k], n = M.b[4 * k], a = M.b[4 * k + 1], b = M.b[4 * k + 2], norm = M.b[4 * k + 3];
+    const float sp_pos = fmaxf(zk, 0.f) + log1pf(expf(-fabsf(zk)));   // softplus(z)
+    const float sp_neg = fmaxf(-zk, 0.f) + log1pf(expf(-fabsf(zk)));  // softplus(-z)
+    const float lgp = logf(p);
+    lp += ((lgp * (a - 1.0f) + logf(q) * (b - 1.0f)) - norm) + (-sp_pos - sp_neg) +
+          (s * lgp + (n - s) * log1pf(-p));
+    grad[k * gs] = -((a - 1.0f) * q - (b - 1.0f) * p + (1.0f - 2.0f * p) + s * q - (n - s) * p);
+  }
+  g.sync();
+  return -g.sum(lp);
+}
+
+// Dirichlet-Categorical of the reference's test-suite (test/infer/test_mcmc.py:283-288):
+// p ~ Dirichlet(c[K]), obs[n] ~ Categorical(p); z[K-1] through StickBreakingTransform
+// (transforms.py:1090-1122).  M.a = class counts[K]; M.b = c[K] followed by the Dirichlet
+// normaliser sum lgamma(c) - lgamma(sum c).  K is small: lane 0 walks the stick.
+template <class G>
+__device__ float dirichlet_categorical_potential(const ModelData& M, const G& g, const float* z,
+                                                 int zs, float* grad, int gs) {
+  const int K = M.N;
+  g.sync();
+  float lp = 0.f;
+  if (g.lane() == 0) {
+    // forward: sticks s_i = clipped expit(z_i - log(K-1-i)), p_i = s_i prod_{j<i}(1 - s_j)
+    float rem = 1.0f, tail = 0.f;
+    for (int k = 0; k < K; ++k) {
+      float s = 1.0f, ls_minus_x = 0.f;
+      if (k < K - 1) {
+        const float x = z[k * zs] - logf((float)(K - 1 - k));
+        s = 1.0f / (1.0f + expf(-x));
+        s = fminf(fmaxf(s, 1.17549435e-38f), 1.0f - 1.1920929e-07f);
+        ls_minus_x = -(fmaxf(-x, 0.f) + log1pf(expf(-fabsf(x)))) - x;  // log_sigmoid(x) - x
+      }
+      const float logp = logf(s * rem);
+      lp += logp * (M.b[k] - 1.0f) + M.a[k] * fmaxf(logp, -3.40282347e+38f);
+      if (k < K - 1) lp += logp + ls_minus_x;
+      rem *= 1.0f - s;
+    }
+    lp -= M.b[K];
+    // backward: d lp / d x_i = w_i (1 - s_i) - s_i (sum_{k>i} w_k + 1), w_k = c_k - 1 + count_k + [k < K-1]
+    for (int k = K - 1; k >= 0; --k) {
+      const float w = M.b[k] - 1.0f + M.a[k] + ((k < K - 1) ? 1.0f : 0.f);
+      if (k < K - 1) {
+        const float x = z[k * zs] - logf((float)(K - 1 - k));
+        float s = 1.0f / (1.0f + expf(-x));
+        s = fminf(fmaxf(s, 1.17549435e-38f), 1.0f - 1.1920929e-07f);
+        grad[k * gs] = -(w * (1.0f - s) - s * tail - s);
+      }
+      tail += w;
+    }
+  }
+  g.sync();
+  return -g.sum(lp);
 }
 
 // digamma(x), x > 0, in double (recurrence up to x >= 6, then the asymptotic series).
@@ -468,6 +540,8 @@ __device__ __forceinline__ float model_potential(const ModelData& M, const G& g,
                                                  const float* ecs_rows = nullptr) {
   if (M.family == FAM_EIGHT_SCHOOLS) return eight_schools_potential(M, g, z, zs, grad, gs);
   if (M.family == FAM_HORSESHOE) return horseshoe_potential(M, g, z, zs, grad, gs, chain);
+  if (M.family == FAM_DIRICHLET_CATEGORICAL) return dirichlet_categorical_potential(M, g, z, zs, grad, gs);
+  if (M.family == FAM_BETA_BERNOULLI) return beta_bernoulli_potential(M, g, z, zs, grad, gs);
   if (M.family == FAM_EIGHT_SCHOOLS_LOCSCALE) return eight_schools_locscale_potential(M, g, z, zs, grad, gs);
   if (M.family == FAM_LOGISTIC_ECS)
     return logistic_ecs_potential(M, g, z, zs, grad, gs, chain, M.ecs_idx + (long)chain * M.ecs_m,

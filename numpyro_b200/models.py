@@ -13,7 +13,8 @@ from collections import OrderedDict
 
 import numpy as np
 
-LOGISTIC, EIGHT_SCHOOLS, HORSESHOE, SV, LOGISTIC_ECS, EIGHT_SCHOOLS_LOCSCALE = 0, 1, 2, 3, 4, 5
+LOGISTIC, EIGHT_SCHOOLS, HORSESHOE, SV, LOGISTIC_ECS, EIGHT_SCHOOLS_LOCSCALE, BETA_BERNOULLI = 0, 1, 2, 3, 4, 5, 6
+DIRICHLET_CATEGORICAL = 7
 
 
 class BoundModel:
@@ -58,7 +59,12 @@ class BoundModel:
         out = {}
         for k, (o, size, shp) in self.flat_sites.items():
             v = np.asarray(values[k], np.float32)
-            out[k] = np.log(v) if k in self.positive else v
+            if k in self.positive:
+                out[k] = np.log(v)
+            elif k in getattr(self, "unit_interval", ()):  # SigmoidTransform inverse: logit
+                out[k] = np.log(v) - np.log1p(-v)
+            else:
+                out[k] = v
         return out
 
     def postprocess(self, zdict):
@@ -149,6 +155,69 @@ def _bind_eight_schools_locscale(centered):
     return bind
 
 
+def _bind_beta_bernoulli(data, alpha=1.1, beta=1.1):
+    """``test/infer/test_mcmc.py:239-244``: ``p_latent ~ Beta(alpha, beta)``, one per column of
+    ``data``; ``obs ~ Bernoulli(p_latent)``.  The potential sees the column counts of ones."""
+    import math
+
+    data = np.asarray(data)
+    if data.ndim != 2:
+        raise ValueError("beta_bernoulli expects data [n, K] of 0/1")
+    n, K = data.shape
+    a = np.broadcast_to(np.asarray(alpha, np.float32), (K,))
+    b = np.broadcast_to(np.asarray(beta, np.float32), (K,))
+    norm = [math.lgamma(float(x)) + math.lgamma(float(y)) - math.lgamma(float(x) + float(y)) for x, y in zip(a, b)]
+    table = np.stack([np.full(K, n, np.float32), a, b, np.asarray(norm, np.float32)], axis=1)
+    fi = np.finfo(np.float32)
+
+    def constrain(z):  # SigmoidTransform with the clipped expit (transforms.py:59-61)
+        zz = np.asarray(z["p_latent"], np.float32)
+        return {"p_latent": np.clip(1 / (1 + np.exp(-zz)), fi.tiny, np.float32(1) - fi.eps).astype(np.float32)}
+
+    bound = BoundModel(BETA_BERNOULLI, "beta_bernoulli", K, 0, data.sum(0).astype(np.float32),
+                       np.ascontiguousarray(table, np.float32), [("p_latent", (K,))], constrain)
+    bound.unit_interval = ("p_latent",)
+    return bound
+
+
+def _stick_breaking(z):
+    """``StickBreakingTransform.__call__`` (``transforms.py:1094-1108``), float32."""
+    z = np.asarray(z, np.float32)
+    K1 = z.shape[-1]
+    fi = np.finfo(np.float32)
+    x = z - np.log(np.arange(K1, 0, -1, dtype=np.float32))
+    s = np.clip(1 / (1 + np.exp(-x)), fi.tiny, np.float32(1) - fi.eps).astype(np.float32)
+    rem = np.cumprod(1 - s, axis=-1)
+    ones = np.ones(z.shape[:-1] + (1,), np.float32)
+    return (np.concatenate([s, ones], -1) * np.concatenate([ones, rem], -1)).astype(np.float32)
+
+
+def _bind_dirichlet_categorical(data, concentration=(1.0, 1.0, 1.0)):
+    """``test/infer/test_mcmc.py:283-288``: ``p_latent ~ Dirichlet(concentration)``;
+    ``obs ~ Categorical(p_latent)``.  The potential sees the class counts."""
+    import math
+
+    c = np.asarray(concentration, np.float32)
+    K = c.shape[0]
+    data = np.asarray(data)
+    if data.ndim != 1 or data.min() < 0 or data.max() >= K:
+        raise ValueError("dirichlet_categorical expects class labels [n] in 0..K-1")
+    counts = np.bincount(data.astype(np.int64), minlength=K).astype(np.float32)
+    norm = sum(math.lgamma(float(v)) for v in c) - math.lgamma(float(c.sum()))
+    table = np.concatenate([c, [np.float32(norm)]]).astype(np.float32)
+    bound = BoundModel(DIRICHLET_CATEGORICAL, "dirichlet_categorical", K, 0, counts, table,
+                       [("p_latent", (K - 1,))], lambda z: {"p_latent": _stick_breaking(z["p_latent"])})
+
+    def unconstrain(values):  # StickBreakingTransform._inverse (transforms.py:1110-1115)
+        y = np.asarray(values["p_latent"], np.float32)
+        crop = y[..., :-1]
+        rem = np.clip(1 - np.cumsum(crop, -1), np.finfo(np.float32).tiny, None)
+        return {"p_latent": np.log(crop / rem) + np.log(np.arange(K - 1, 0, -1, dtype=np.float32))}
+
+    bound.unconstrain = unconstrain
+    return bound
+
+
 def _bind_sv(returns):
     r = np.ascontiguousarray(returns, np.float32)
     T = r.shape[0]
@@ -196,6 +265,12 @@ eight_schools_noncentered = RegisteredModel(
 eight_schools = RegisteredModel(
     "eight_schools", _bind_eight_schools_locscale(1.0),
     "Centred eight schools: theta ~ Normal(mu, tau) (README.md:60-68)")
+beta_bernoulli = RegisteredModel(
+    "beta_bernoulli", _bind_beta_bernoulli,
+    "p_latent ~ Beta(1.1, 1.1)[K]; obs ~ Bernoulli(p_latent)  (test/infer/test_mcmc.py:239-244)")
+dirichlet_categorical = RegisteredModel(
+    "dirichlet_categorical", _bind_dirichlet_categorical,
+    "p_latent ~ Dirichlet(1, 1, 1); obs ~ Categorical(p_latent)  (test/infer/test_mcmc.py:283-288)")
 stochastic_volatility = RegisteredModel(
     "stochastic_volatility", _bind_sv,
     "Random-walk stochastic volatility (examples/stochastic_volatility.py:57-65)")
@@ -208,6 +283,7 @@ horseshoe_normal = RegisteredModel(
     "Horseshoe regression, Normal likelihood (examples/horseshoe_regression.py:37-58)")
 
 REGISTRY = {m.__name__: m for m in (logistic_regression, eight_schools_noncentered, eight_schools,
+                                    beta_bernoulli, dirichlet_categorical,
                                     stochastic_volatility, horseshoe_bernoulli,
                                     horseshoe_normal)}
 

@@ -228,6 +228,95 @@ class EightSchoolsLocScale(Family):
         return out
 
 
+class BetaBernoulli(Family):
+    """``p_latent ~ Beta(alpha, beta)[K]``; ``obs[n, K] ~ Bernoulli(p_latent)``
+    (``test/infer/test_mcmc.py:239-244``).  z = logit(p) (``SigmoidTransform``, clipped expit
+    ``transforms.py:59-61``, log|J| = -softplus(z) - softplus(-z) ``:960-961``); Beta through the
+    Dirichlet log-density (``continuous.py:193-194,292-299``); Bernoulli(probs) with clamped
+    probabilities (``discrete.py:90-93``, ``util.py:492-494``).  The likelihood enters through
+    the column counts of ones."""
+
+    name = "beta_bernoulli"
+
+    def __init__(self, data, alpha=1.1, beta=1.1, dtype=np.float32):
+        super().__init__(dtype)
+        data = np.asarray(data)
+        self.K = data.shape[1]
+        self.n = self.dtype.type(data.shape[0])
+        self.s = data.sum(0).astype(self.dtype)
+        self.a = np.broadcast_to(np.asarray(alpha, self.dtype), (self.K,)).copy()
+        self.b = np.broadcast_to(np.asarray(beta, self.dtype), (self.K,)).copy()
+        self.norm = np.array([math.lgamma(a) + math.lgamma(b) - math.lgamma(a + b)
+                              for a, b in zip(self.a.astype(float), self.b.astype(float))], self.dtype)
+        self.trace_sites = (("p_latent", self.K),)
+
+    def _p(self, z):
+        fi = np.finfo(self.dtype)
+        return np.clip(1 / (1 + np.exp(-z)), fi.tiny, self.dtype.type(1) - fi.eps).astype(self.dtype)
+
+    def potential_and_grad(self, z):
+        f = self.dtype.type
+        z = np.asarray(z, self.dtype)
+        p = self._p(z)
+        q = f(1) - p
+        lp = (np.log(p) * (self.a - f(1)) + np.log(q) * (self.b - f(1))) - self.norm
+        lp = lp + (-np.logaddexp(z, f(0)) - np.logaddexp(-z, f(0)))
+        lp = lp + self.s * np.log(p) + (self.n - self.s) * np.log1p(-p)
+        dl = (self.a - f(1)) * q - (self.b - f(1)) * p + (f(1) - f(2) * p) + self.s * q - (self.n - self.s) * p
+        return f(-lp.sum(dtype=self.dtype)), (-dl).astype(self.dtype)
+
+    def constrain(self, z):
+        return {"p_latent": self._p(np.asarray(z, self.dtype))}
+
+
+class DirichletCategorical(Family):
+    """``p_latent ~ Dirichlet(concentration[K])``; ``obs[n] ~ Categorical(p_latent)``
+    (``test/infer/test_mcmc.py:283-288``).  z[K-1] through ``StickBreakingTransform``
+    (``transforms.py:1090-1122``: x = z - log(K-1-i), sticks = clipped expit, log|J| = sum(log
+    y[:-1] + log_sigmoid(x) - x)); Dirichlet ``continuous.py:292-299``; Categorical(probs) =
+    clipped ``log(probs)`` at the observed class (``discrete.py:66-68,323-329``): class counts."""
+
+    name = "dirichlet_categorical"
+
+    def __init__(self, data, concentration=(1.0, 1.0, 1.0), dtype=np.float32):
+        super().__init__(dtype)
+        self.c = np.asarray(concentration, self.dtype)
+        self.K = self.c.shape[0]
+        self.counts = np.bincount(np.asarray(data).astype(np.int64), minlength=self.K).astype(self.dtype)
+        cf = self.c.astype(float)
+        self.norm = self.dtype.type(sum(math.lgamma(v) for v in cf) - math.lgamma(cf.sum()))
+        self.offset = np.log(np.arange(self.K - 1, 0, -1).astype(self.dtype)).astype(self.dtype)
+        self.trace_sites = (("p_latent", self.K - 1),)
+
+    def _probs(self, z):
+        f, fi = self.dtype.type, np.finfo(self.dtype)
+        x = (np.asarray(z, self.dtype) - self.offset).astype(self.dtype)
+        s = np.clip(1 / (1 + np.exp(-x)), fi.tiny, f(1) - fi.eps).astype(self.dtype)
+        rem = np.concatenate([[f(1)], np.cumprod(f(1) - s)]).astype(self.dtype)
+        return x, s, (np.concatenate([s, [f(1)]]) * rem).astype(self.dtype)
+
+    def potential_and_grad(self, z):
+        f = self.dtype.type
+        x, s, p = self._probs(z)
+        logp = np.log(p)
+        lp = (logp * (self.c - f(1))).sum(dtype=self.dtype) - self.norm
+        log_sig = -np.logaddexp(-x, f(0))
+        lp = lp + (logp[:-1] + (log_sig - x)).sum(dtype=self.dtype)
+        lp = lp + (self.counts * np.maximum(logp, np.finfo(self.dtype).min)).sum(dtype=self.dtype)
+        w = self.c - f(1) + self.counts
+        w[:-1] += f(1)
+        tail = np.cumsum(w[::-1])[::-1]  # tail[k] = sum_{j >= k} w_j
+        dl = w[:-1] * (f(1) - s) - s * tail[1:] - s
+        return f(-lp), (-dl).astype(self.dtype)
+
+    def constrain(self, z):
+        z = np.asarray(z, self.dtype)
+        if z.ndim == 1:
+            return {"p_latent": self._probs(z)[2]}
+        return {"p_latent": np.stack([self._probs(r)[2] for r in z.reshape(-1, self.K - 1)]).reshape(
+            z.shape[:-1] + (self.K,))}
+
+
 class Horseshoe(Family):
     """z = [lambdas_u[D], (prec_obs_u,) tau_u, unscaled_betas[D]] (sorted names).
 
