@@ -398,8 +398,8 @@ def run_own(args):
     l2_peak = None
     if rank == 0:
         gbs = C.c_float()
-        stages = lay["stages"] - lay["stages"] % 10 or 10
-        _lib.check(lib.b200mc_membench(max(streamed, 8 << 20), lay["tile_bytes"], min(stages, 30), 40, 1,
+        stages = lay["stages"]  # the kernel's own ring depth (a multiple of its consumer-warp count)
+        _lib.check(lib.b200mc_membench(max(streamed, 8 << 20), lay["tile_bytes"], stages, 40, 1,
                                        C.byref(gbs), None))
         l2_peak = float(gbs.value)
     traffic, traffic_src = None, None

@@ -1,5 +1,3 @@
 set -x
-timeout 900 python tools/ncu_traffic.py capture > gpurun_out/ncu_traffic.log 2>&1
-ncu -i gpurun_out/glm_r02.ncu-rep --page source --print-source cuda,sass --csv 2>/dev/null | gzip > gpurun_out/glm_r02_source.csv.gz
-rm -f gpurun_out/*.ncu-rep
-ls -la gpurun_out | tail -4
+B="--no-out-of-l2 --no-multi-chain --no-many-chain --no-cpu --steps 6 --warmup 3"
+for v in w12p1 w14p1 w12p0; do B200MC_LIB=$PWD/numpyro_b200/lib$v.so timeout 300 python bench.py $B > gpurun_out/exp11_$v.json 2> gpurun_out/exp11_$v.err; done
