@@ -806,9 +806,33 @@ static int launch_chain(b200mc_handle* h, const CollectSpec& col, const uint32_t
     L.end_thresh = thresh;
   }
   L.hot_mask = 0u;
+  L.cpw = 32;
   if (h->mode == 0) {
     const int threads = 64;  // small blocks spread the chains over all SMs
-    CK(kl::chain_launch(0, L, (h->C + threads - 1) / threads, threads, 0, st));
+    // chains per warp (B200MC_CHAINS_PER_WARP overrides)
+    static int cpw_env = -1;
+    if (cpw_env < 0) {
+      const char* e = getenv("B200MC_CHAINS_PER_WARP");
+      cpw_env = e ? atoi(e) : 0;
+    }
+    // Measured on eight schools (profiles/r02_chains_per_warp.txt): a launch takes
+    // max(latency of one warp, warps x issue cost of a warp); both grow with the chains per warp
+    // (divergence), so few chains want a warp each and many chains want full warps.  Relative
+    // figures of that sweep (ms, 148 SMs):
+    static const float kLat[6] = {24.5f, 28.8f, 28.5f, 28.3f, 30.0f, 32.2f};      // cpw 1, 2, .., 32
+    static const float kIssue[6] = {0.020f, 0.025f, 0.031f, 0.040f, 0.053f, 0.070f};
+    int cpw = 32;
+    float best = 1e30f;
+    for (int i = 0; i < 6; ++i) {
+      const int c = 1 << i;
+      const float warps = (float)((h->C + c - 1) / c) * (148.0f / (float)h->num_sms);
+      const float t = fmaxf(kLat[i], warps * kIssue[i]);
+      if (t < best) { best = t; cpw = c; }
+    }
+    if (cpw_env >= 1 && cpw_env <= 32) cpw = cpw_env;
+    L.cpw = cpw;
+    const int warps = (h->C + cpw - 1) / cpw;
+    CK(kl::chain_launch(0, L, (warps * 32 + threads - 1) / threads, threads, 0, st));
   } else if (h->mode == 1) {
     const int wpb = 4;
     CK(kl::chain_launch(1, L, (h->C + wpb - 1) / wpb, wpb * 32, 0, st));

@@ -24,6 +24,7 @@ struct ChainLaunch {
                             // the tail runs (1 = never wait), see chain_kernel<0>
   unsigned hot_mask;        // CTA-per-chain: slots kept in (dynamic) shared memory, see kChainHotMask
   EcsStep ecs;              // HMCECS: the Gibbs step before every transition (enabled = 0: none)
+  int cpw;                  // thread-per-chain: chains (live lanes) per warp, 1..32
 };
 
 // CTA per chain: the leaf under construction (position, momentum, gradient) and the subtree's
@@ -60,7 +61,11 @@ chain_kernel(const __grid_constant__ ChainLaunch L) {
   long sstride;
   int es;
   if (MODE == 0) {
-    chain = blockIdx.x * blockDim.x + threadIdx.x;
+    // cpw chains per warp (lanes 0 .. cpw-1): a GPU that 16,384 chains fill to 3.5 warps per SM at
+    // 32 chains per warp is latency-bound with one warp per scheduler (ncu: issue slots 10 %);
+    // fewer chains per warp means more warps to hide latency behind and fewer lanes to diverge
+    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, ln = threadIdx.x & 31;
+    chain = (ln < L.cpw) ? gw * L.cpw + ln : L.C;
     base = L.work + chain;
     sstride = (long)D * L.c_pad;
     es = L.c_pad;
