@@ -676,7 +676,7 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
       for (size_t i = 0; i < id0.size(); ++i) id0[i] = (int)(i % (size_t)m);
       ACK(cudaMemcpy(h->ecs_idx, id0.data(), sizeof(int) * id0.size(), cudaMemcpyHostToDevice));
     }
-    if (const char* e = getenv("B200MC_CHAIN_MODE")) {  // tuning aid: force the chain grouping
+    if (const char* e = (c.family == B200MC_LOGISTIC_ECS) ? nullptr : getenv("B200MC_CHAIN_MODE")) {  // tuning aid: force the chain grouping
       const int m = atoi(e);
       if (!batch && ((m == 0 && D <= 32 && !c.dense_mass) || (m == 1 && D <= 512) || m == 2)) h->mode = m;
     }

@@ -140,7 +140,7 @@ chain_kernel(const __grid_constant__ ChainLaunch L) {
       S.hot_mask = L.hot_mask;
     }
     S.load(L.cs, L.cv);
-    S.transition_hook = L.ecs.enabled != 0;
+    S.transition_hook = MODE == 2 && L.ecs.enabled != 0;
     StepResult r;
     if (L.init_keys)
       r = S.begin_init(Key{L.init_keys[2 * chain], L.init_keys[2 * chain + 1]}, L.user_init != 0);
@@ -150,7 +150,7 @@ chain_kernel(const __grid_constant__ ChainLaunch L) {
       if (r == NEED_GRAD) {
         const float U = model_potential(M, g, S.v(LZ), es, S.v(LG), es, chain, ecs_rows);
         r = S.advance(U);
-      } else if (r == AT_TRANSITION_END) {
+      } else if (MODE == 2 && r == AT_TRANSITION_END) {
         // HMCECS (hmc_gibbs.py:619-652): block update of the subsample at the current point
         float pe_new;
         const bool acc = ecs_propose_test(M, L.ecs, g, S.v(Z_PROP), es, S.s.potential_energy, chain,

@@ -543,9 +543,11 @@ __device__ __forceinline__ float model_potential(const ModelData& M, const G& g,
   if (M.family == FAM_DIRICHLET_CATEGORICAL) return dirichlet_categorical_potential(M, g, z, zs, grad, gs);
   if (M.family == FAM_BETA_BERNOULLI) return beta_bernoulli_potential(M, g, z, zs, grad, gs);
   if (M.family == FAM_EIGHT_SCHOOLS_LOCSCALE) return eight_schools_locscale_potential(M, g, z, zs, grad, gs);
-  if (M.family == FAM_LOGISTIC_ECS)
-    return logistic_ecs_potential(M, g, z, zs, grad, gs, chain, M.ecs_idx + (long)chain * M.ecs_m,
-                                  ecs_rows);
+  if constexpr (G::kBlockWide) {  // HMCECS handles run CTA per chain only (api.cu)
+    if (M.family == FAM_LOGISTIC_ECS)
+      return logistic_ecs_potential(M, g, z, zs, grad, gs, chain, M.ecs_idx + (long)chain * M.ecs_m,
+                                    ecs_rows);
+  }
   return sv_potential(M, g, z, zs, grad, gs);
 }
 
