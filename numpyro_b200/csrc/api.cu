@@ -807,6 +807,24 @@ static int launch_chain(b200mc_handle* h, const CollectSpec& col, const uint32_t
   }
   L.hot_mask = 0u;
   L.cpw = 32;
+  if (L.ecs.enabled && !keys) {
+    // HMCECS loop: step machine in one warp, state and subsample rows in shared memory, when
+    // they fit (B200MC_ECS_FAST=0: the CTA-per-chain kernel below)
+    static int fast_on = -1;
+    if (fast_on < 0) {
+      const char* e = getenv("B200MC_ECS_FAST");
+      fast_on = e ? atoi(e) : 1;
+    }
+    const size_t smem = ecs_chain_smem(h->D, h->P.max_depth, h->P.dense_mass, h->M.ecs_m, h->M.ncols);
+    if (fast_on && h->D <= kEcsCtaCols && h->M.ecs_m <= kEcsCtaRows * 256 && !h->P.dense_mass &&
+        smem + kl::ecs_chain_static_smem() <= (size_t)h->max_smem) {
+      L.hot_mask = 0u;
+      L.ecs.rows_in_smem = 1;
+      CK(kl::ecs_chain_launch(L, h->C, smem, st));
+      g_launches++;
+      return 0;
+    }
+  }
   if (h->mode == 0) {
     const int threads = 64;  // small blocks spread the chains over all SMs
     // chains per warp (B200MC_CHAINS_PER_WARP overrides)

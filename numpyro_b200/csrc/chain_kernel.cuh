@@ -175,6 +175,75 @@ chain_kernel(const __grid_constant__ ChainLaunch L) {
   else run(BlockGroup{red_scratch});
 }
 
+// HMCECS, device-resident loop, one CTA per chain (b200mc_ecs_sample): the step machine runs in
+// WARP 0 with the whole tree state of the chain in shared memory (Sampler<WarpGroup>: vectors of
+// D <= 128 in registers, warp shuffles -- the control warp of glm_kernel, 4.1), the potential on the
+// subsample (rows staged in shared memory) and the Gibbs step run on all 256 threads.  The CTA-wide
+// step machine of chain_kernel<2> costs ~30 us per leapfrog in block-wide reductions and global
+// tree slots, which is what bounded a single HMCECS chain.
+__host__ __device__ inline size_t ecs_chain_smem(int D, int max_depth, int dense, int m, int ncols) {
+  return sizeof(float) * (((size_t)num_slots(max_depth, dense) * D + 3) / 4 * 4 + (size_t)m * ncols);
+}
+#ifdef B200MC_TU_CHAIN
+__global__ void __launch_bounds__(256, 1) ecs_chain_kernel(const __grid_constant__ ChainLaunch L) {
+  extern __shared__ float esm[];
+  __shared__ float red_scratch[64];
+  __shared__ int s_r, s_iter;
+  __shared__ float s_pe;
+  __shared__ float ecs_part[8 * kEcsCtaCols];
+  const int D = L.P.D, chain = blockIdx.x, warp = threadIdx.x >> 5;
+  if (chain >= L.C) return;
+  const ModelData& M = L.M;
+  float* work = esm;
+  float* rows = esm + ((size_t)num_slots(L.P.max_depth, L.P.dense_mass) * D + 3) / 4 * 4;
+  const int* idx = M.ecs_idx + (long)chain * M.ecs_m;
+  BlockGroup g{red_scratch};
+  for (int t = threadIdx.x; t < M.ecs_m * M.ncols; t += blockDim.x)
+    rows[t] = M.a[(long)idx[t / M.ncols] * M.ncols + t % M.ncols];
+  Sampler<WarpGroup> S;  // warp 0 only
+  StepResult r = FINISHED;
+  if (warp == 0) {
+    S.setup(&L.P, WarpGroup{}, work, D, 1, chain, L.C, &L.col);
+    S.load(L.cs, L.cv);
+    S.transition_hook = true;
+    r = S.begin_sampling();
+  }
+  for (;;) {
+    if (threadIdx.x == 0) {
+      s_r = (int)r;
+      s_pe = S.s.potential_energy;
+      s_iter = S.local_iter;
+    }
+    __syncthreads();  // also: warp 0's writes to the work array are visible to the CTA
+    const int rr = s_r;
+    if (rr == (int)NEED_GRAD) {
+      const float U = logistic_ecs_potential_cta(M, g, work + (long)LZ * D, work + (long)LG * D, chain, idx,
+                                                 rows, 0, 0, ecs_part);
+      if (warp == 0) r = S.advance(U);
+    } else if (rr == (int)AT_TRANSITION_END) {
+      // hmc_gibbs.py:619-652: block update of the subsample at the current point
+      float pe_new;
+      const bool acc = ecs_propose_test(M, L.ecs, g, work + (long)Z_PROP * D, 1, s_pe, chain, s_iter, L.C,
+                                        pe_new, rows, ecs_part);
+      if (acc) {
+        const float* gt = L.ecs.gtmp + (long)chain * D;
+        for (int d = threadIdx.x; d < D; d += blockDim.x) work[(long)G_PROP * D + d] = gt[d];
+      }
+      __syncthreads();
+      if (warp == 0) {
+        if (acc) S.s.potential_energy = pe_new;
+        S.s.grad_evals += 1;
+        r = S.resume_transition();
+      }
+    } else {
+      break;
+    }
+    __syncthreads();  // everyone has read s_r / s_pe before thread 0 rewrites them
+  }
+  if (warp == 0) S.store(L.cs, L.cv);
+}
+#endif  // B200MC_TU_CHAIN
+
 // Tier-2 test hook: U and gradient at caller-supplied points z[C][D].
 template <int MODE>
 __global__ void chain_potential_kernel(ModelData M, const float* z, float* U, float* grad,

@@ -54,7 +54,7 @@ struct EcsStep {
 template <class G>
 __device__ bool ecs_propose_test(const ModelData& M, const EcsStep& E, const G& g, const float* z,
                                  int zs, float pe, int chain, int local_iter, int C, float& pe_new,
-                                 float* rows = nullptr) {
+                                 float* rows = nullptr, float* cta_part = nullptr) {
   const bool part = E.partitionable != 0;
   const int m = M.ecs_m, size = M.N, D = M.D;
   int* idx = E.idx + (long)chain * m;
@@ -78,8 +78,17 @@ __device__ bool ecs_propose_test(const ModelData& M, const EcsStep& E, const G& 
     prop[i] = v;
   }
   g.sync();
-  pe_new = logistic_ecs_potential(M, g, z, zs, E.gtmp + (long)chain * D, 1, chain, prop, rows, start,
-                                  start + block_size);
+  if constexpr (G::kBlockWide) {
+    if (cta_part)  // ecs_chain_kernel: the one-CTA form with the rows in shared memory
+      pe_new = logistic_ecs_potential_cta(M, g, z, E.gtmp + (long)chain * D, chain, prop, rows, start,
+                                          start + block_size, cta_part);
+    else
+      pe_new = logistic_ecs_potential(M, g, z, zs, E.gtmp + (long)chain * D, 1, chain, prop, rows, start,
+                                      start + block_size);
+  } else {
+    pe_new = logistic_ecs_potential(M, g, z, zs, E.gtmp + (long)chain * D, 1, chain, prop, rows, start,
+                                    start + block_size);
+  }
   const float ex = expf(pe - pe_new);
   const float ap = (ex != ex) ? ex : fminf(ex, 1.0f);  // jnp.clip(exp(pe - pe_new), None, 1): NaN stays NaN
   const float u = uniform01(rng_key, part);            // random.bernoulli(rng_key, accept_prob)

@@ -25,5 +25,17 @@ cudaError_t chain_potential_launch(int mode, const ModelData& M, const float* z,
   return cudaGetLastError();
 }
 
+size_t ecs_chain_static_smem() {
+  cudaFuncAttributes a;
+  return cudaFuncGetAttributes(&a, ecs_chain_kernel) == cudaSuccess ? a.sharedSizeBytes : (size_t)1 << 20;
+}
+
+cudaError_t ecs_chain_launch(const ChainLaunch& L, int grid, size_t smem, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(ecs_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  ecs_chain_kernel<<<grid, 256, smem, st>>>(L);
+  return cudaGetLastError();
+}
+
 }  // namespace kl
 }  // namespace b200mc

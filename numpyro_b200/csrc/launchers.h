@@ -31,6 +31,8 @@ cudaError_t glm_mc_prepare(int max_smem, int smem, int* occupancy);
 cudaError_t glm_mc_launch(const GlmMcLaunch& L, int ctas, size_t smem, cudaStream_t st);  // cooperative
 // k_chain.cu
 cudaError_t chain_launch(int mode, const ChainLaunch& L, int grid, int block, size_t smem, cudaStream_t st);
+cudaError_t ecs_chain_launch(const ChainLaunch& L, int grid, size_t smem, cudaStream_t st);
+size_t ecs_chain_static_smem();
 cudaError_t chain_potential_launch(int mode, const ModelData& M, const float* z, float* U, float* grad,
                                    int n, cudaStream_t st);
 // k_batch.cu

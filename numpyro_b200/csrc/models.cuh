@@ -454,6 +454,9 @@ __device__ float logistic_ecs_potential(const ModelData& M, const G& g, const fl
     const int row = idx[i];
     const float* x = rowp(i);
     float l = 0.f, ls = 0.f, dl = 0.f;
+    // (the loops of this function are load-latency bound on one CTA: unrolled so that several
+    // loads are in flight per thread; the order of every sum is unchanged)
+#pragma unroll 11
     for (int d = 0; d < D; ++d) {
       const float xv = x[d], zv = z[d * zs];
       l = fmaf(xv, zv, l);
@@ -506,8 +509,10 @@ __device__ float logistic_ecs_potential(const ModelData& M, const G& g, const fl
     for (int d = lane; d < D; d += size) {
       const float dz = z[d * zs] - ref[d];
       float hd = 0.f;
-      if (deg == 2)
+      if (deg == 2) {
+#pragma unroll 11
         for (int k = 0; k < D; ++k) hd = fmaf(H[(long)d * D + k], z[k * zs] - ref[k], hd);
+      }
       grad[d * gs] = bsum[d] + hd;  // gradient of proxy_sum, folded in below
       ps += bsum[d] * dz + 0.5f * hd * dz;
     }
@@ -520,6 +525,7 @@ __device__ float logistic_ecs_potential(const ModelData& M, const G& g, const fl
   for (int t = lane; t < kEcsSlices * D; t += size) {
     const int sl = t / D, d = t - sl * D;
     float a = 0.f;
+#pragma unroll 8
     for (int i = sl; i < m; i += kEcsSlices) a = fmaf(coef[i], rowp(i)[d], a);
     part[t] = a;
   }
@@ -531,6 +537,179 @@ __device__ float logistic_ecs_potential(const ModelData& M, const G& g, const fl
     grad[d * gs] = z[d * zs] - gp - a;
   }
   g.sync();
+  return U;
+}
+
+// The same potential for ONE 256-thread CTA with the subsample's rows staged in shared memory
+// (ecs_chain_kernel; D <= 64, m <= 2048), written for latency: with 215 KB of rows staged the SM has
+// ~24 KB of L1 left, so every global access of the generic form above is an L2 round trip and the
+// per-row coefficients it parks in global memory are re-read 55 times.  Here a thread keeps its
+// rows' labels, differences and coefficients in registers, accumulates its rows' contribution to ALL
+// columns in registers (a second pass over its rows in shared memory) and the CTA combines them with
+// two 31-shuffle transpose-reduces per warp and one fixed-order sum over the warps; H (theta - theta*)
+// is a warp-per-row sweep with coalesced loads.  part: 8 x 64 floats of shared memory.
+constexpr int kEcsCtaRows = 8;   // rows per thread (m <= 8 * 256)
+constexpr int kEcsCtaCols = 64;  // columns (D <= 64)
+
+__device__ __forceinline__ float ecs_transpose_reduce32(float (&a)[32]) {
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+    const bool upper = (lane & s) != 0;
+#pragma unroll
+    for (int i = 0; i < s; ++i) {
+      const float send = upper ? a[i] : a[i + s];
+      const float keep = upper ? a[i + s] : a[i];
+      a[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+    }
+  }
+  return a[0];
+}
+
+__device__ inline float logistic_ecs_potential_cta(const ModelData& M, const BlockGroup& g, const float* z,
+                                            float* grad, int chain, const int* idx, const float* rows,
+                                            int fresh0, int fresh1, float* part) {
+  const int D = M.D, m = M.ecs_m, deg = M.ecs_degree, tid = threadIdx.x, nthr = blockDim.x;
+  const int warp = tid >> 5, lane = tid & 31, nwarp = nthr >> 5;
+  const float nf = (float)M.N, mf = (float)m, scale = nf / mf;
+  const float* ref = M.ecs_ref;
+  auto rowp = [&](int i) -> const float* {
+    return (i >= fresh0 && i < fresh1) ? M.a + (long)idx[i] * M.ncols : rows + (long)i * M.ncols;
+  };
+  __syncthreads();
+  // labels of this thread's rows: independent loads, all in flight together
+  float yv[kEcsCtaRows];
+  {
+    int rw[kEcsCtaRows];
+#pragma unroll
+    for (int k = 0; k < kEcsCtaRows; ++k) {
+      const int i = tid + k * nthr;
+      rw[k] = (i < m) ? idx[i] : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < kEcsCtaRows; ++k) yv[k] = (tid + k * nthr < m) ? (float)M.y8[rw[k]] : 0.f;
+  }
+  float prior = 0.f, s1 = 0.f;
+  for (int d = tid; d < D; d += nthr) {
+    const float t = z[d];
+    prior += 0.5f * t * t + B200MC_LOG_SQRT_2PI;
+  }
+  float dif[kEcsCtaRows], cf[kEcsCtaRows];
+#pragma unroll
+  for (int k = 0; k < kEcsCtaRows; ++k) {
+    const int i = tid + k * nthr;
+    dif[k] = 0.f;
+    cf[k] = 0.f;
+    if (i < m) {
+      const float* x = rowp(i);
+      float l = 0.f, ls = 0.f, dl = 0.f;
+#pragma unroll 11
+      for (int d = 0; d < D; ++d) {
+        const float xv = x[d], zv = z[d];
+        l = fmaf(xv, zv, l);
+        if (deg) {
+          const float rv = ref[d];
+          ls = fmaf(xv, rv, ls);
+          dl = fmaf(xv, zv - rv, dl);
+        }
+      }
+      const float e = expf(-fabsf(l));
+      const float bce = (fmaxf(l, 0.f) + log1pf(e)) - l * yv[k];  // distributions/util.py:295-298
+      const float inv = 1.0f / (1.0f + e);
+      const float sig = (l >= 0.f) ? inv : e * inv;
+      if (!deg) {
+        s1 += bce;
+        cf[k] = scale * (yv[k] - sig);
+      } else {
+        const float es = expf(-fabsf(ls));
+        const float bces = (fmaxf(ls, 0.f) + log1pf(es)) - ls * yv[k];
+        const float invs = 1.0f / (1.0f + es);
+        const float sigs = (ls >= 0.f) ? invs : es * invs;
+        float proxy = -bces + (yv[k] - sigs) * dl;
+        float dproxy = yv[k] - sigs;
+        if (deg == 2) {
+          const float w = sigs * (1.0f - sigs);
+          proxy -= 0.5f * w * dl * dl;
+          dproxy -= w * dl;
+        }
+        dif[k] = -bce - proxy;
+        cf[k] = (yv[k] - sig) - dproxy;  // d diff_i / d logit_i
+        s1 += dif[k];
+      }
+    }
+  }
+  g.sum2(prior, s1);
+  float U;
+  if (!deg) {
+    U = prior + scale * s1;
+  } else {
+    const float mean = s1 / mf;
+    float s2 = 0.f, ps = 0.f;
+#pragma unroll
+    for (int k = 0; k < kEcsCtaRows; ++k) {
+      if (tid + k * nthr < m) {
+        const float dv = dif[k] - mean;
+        s2 += dv * dv;
+        cf[k] *= scale - (scale * scale) * dv;
+      }
+    }
+    // proxy_sum = A + b.dt + 1/2 dt^T H dt; its gradient b + H dt goes to grad[] (folded in below).
+    // H dt: warp w takes rows w, w + nwarp, ... of H, lanes over the columns (coalesced)
+    const float* bsum = M.ecs_sums + 1;
+    const float* H = bsum + D;
+    const float dz0 = (lane < D) ? z[lane] - ref[lane] : 0.f;
+    const float dz1 = (lane + 32 < D) ? z[lane + 32] - ref[lane + 32] : 0.f;
+    for (int d = warp; d < D; d += nwarp) {
+      float hd = 0.f;
+      if (deg == 2) {
+        const float h0 = (lane < D) ? H[(long)d * D + lane] : 0.f;
+        const float h1 = (lane + 32 < D) ? H[(long)d * D + lane + 32] : 0.f;
+        hd = fmaf(h0, dz0, h1 * dz1);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) hd += __shfl_xor_sync(0xffffffffu, hd, o);
+      }
+      if (lane == 0) {
+        const float dzd = z[d] - ref[d];
+        grad[d] = bsum[d] + hd;
+        ps += bsum[d] * dzd + 0.5f * hd * dzd;
+      }
+    }
+    g.sum2(s2, ps);
+    const float var = s2 / mf;  // jnp.var: population variance
+    const float loglik = (M.ecs_sums[0] + ps) + nf * mean - 0.5f * (nf * nf / mf) * var;
+    U = prior - loglik;
+  }
+  // gradient: sum_i cf_i x_i, this thread's rows into registers, then across the CTA
+  float acc[kEcsCtaCols];
+#pragma unroll
+  for (int d = 0; d < kEcsCtaCols; ++d) acc[d] = 0.f;
+#pragma unroll
+  for (int k = 0; k < kEcsCtaRows; ++k) {
+    const int i = tid + k * nthr;
+    if (i < m) {
+      const float* x = rowp(i);
+      const float c = cf[k];
+#pragma unroll
+      for (int d = 0; d < kEcsCtaCols; ++d)
+        if (d < D) acc[d] = fmaf(c, x[d], acc[d]);
+    }
+  }
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    float a[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) a[i] = acc[32 * half + i];
+    const float v = ecs_transpose_reduce32(a);
+    part[warp * kEcsCtaCols + 32 * half + lane] = v;
+  }
+  __syncthreads();
+  for (int d = tid; d < D; d += nthr) {
+    float a = 0.f;
+    for (int w = 0; w < nwarp; ++w) a += part[w * kEcsCtaCols + d];  // fixed order
+    const float gp = deg ? grad[d] : 0.f;
+    grad[d] = z[d] - gp - a;
+  }
+  __syncthreads();
   return U;
 }
 

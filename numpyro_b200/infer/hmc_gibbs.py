@@ -105,6 +105,9 @@ class HMCECS(HMCGibbs):
         self._num_blocks = int(num_blocks)
         self._proxy = proxy
         self._last = None
+        # sample(): one iteration of the device-resident loop (b200mc_ecs_sample); False: the
+        # stand-alone Gibbs kernel followed by one inner transition (b200mc_ecs_update + b200mc_sample)
+        self._fused_step = True
 
     @staticmethod
     def taylor_proxy(reference_params, degree=2):
@@ -183,8 +186,12 @@ class HMCECS(HMCGibbs):
         Cn = inner._num_chains
         keys = _lib.DeviceArray.from_numpy(np.ascontiguousarray(state.rng_key, np.uint32).reshape(Cn, 2))
         acc = _lib.DeviceArray((Cn,), np.float32)
-        _lib.check(lib.b200mc_ecs_update(inner._handle, keys.ptr, self._num_blocks, acc.ptr, None))
-        _lib.check(lib.b200mc_sample(inner._handle, 1, 1, 1, None, None))
+        if self._fused_step:
+            _lib.check(lib.b200mc_ecs_sample(inner._handle, keys.ptr, self._num_blocks, 1, 1, 1, None,
+                                             acc.ptr, None, None))
+        else:
+            _lib.check(lib.b200mc_ecs_update(inner._handle, keys.ptr, self._num_blocks, acc.ptr, None))
+            _lib.check(lib.b200mc_sample(inner._handle, 1, 1, 1, None, None))
         hmc_state = inner._to_state(*inner._snapshot())
         rng_key, ap = keys.numpy(), acc.numpy()
         if not inner._vectorized:

@@ -115,8 +115,9 @@ def test_tier2_subsampled_potential(degree, shape):
         np.testing.assert_allclose(g[0], go, rtol=2e-4, atol=(2e-5 if degree == 0 else 5e-4) * scale)
 
 
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("degree,part", [(0, True), (2, True), (2, False)])
-def test_tier3_runs_decision_for_decision(degree, part):
+def test_tier3_runs_decision_for_decision(degree, part, fused):
     """Fixed step size, no adaptation: 20 HMCECS transitions from the same key -- subsample
     proposals, Metropolis decisions, wrapper keys and tree sizes equal the oracle's."""
     from oracle.threefry import PRNGKey
@@ -125,6 +126,7 @@ def test_tier3_runs_decision_for_decision(degree, part):
     m = 200
     kw = dict(step_size=0.02, adapt_step_size=False, adapt_mass_matrix=False, max_tree_depth=5)
     gk, ok = _kernels(X, y, m, degree, th.astype(np.float32), 4, part, **kw)
+    gk._fused_step = fused  # the one-warp step machine of the resident loop / the stand-alone kernels
     gs = gk.init(PRNGKey(7), 0, None, (X, y), {"subsample_size": m})
     os_ = ok.init(PRNGKey(7), 0)
     same_idx = same_steps = 0
