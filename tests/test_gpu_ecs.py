@@ -143,6 +143,27 @@ def test_tier3_runs_decision_for_decision(degree, part, fused):
     assert same_idx == T and same_steps == T, (same_idx, same_steps)
 
 
+@pytest.mark.parametrize("m,nb", [(37, 5), (64, 64), (10, 1), (250, 7), (33, 40)])
+def test_block_update_shapes_match_oracle(m, nb):
+    """Ragged blocks (padding, clamped slice start, more blocks than indices): the subsample after
+    every one of 6 transitions equals the oracle's (whose `update_block` equals the reference's
+    `_update_block` on these shapes, tests/test_refecs.py)."""
+    from oracle.threefry import PRNGKey
+
+    X, y, th = _problem(n=3000, D=4, seed=8)
+    kw = dict(step_size=0.05, adapt_step_size=False, adapt_mass_matrix=False, max_tree_depth=4)
+    gk, ok = _kernels(X, y, m, 2, th.astype(np.float32), nb, True, **kw)
+    gs = gk.init(PRNGKey(3), 0, None, (X, y), {"subsample_size": m})
+    os_ = ok.init(PRNGKey(3), 0)
+    np.testing.assert_array_equal(gs.z["N"], os_.z["N"])
+    for _ in range(6):
+        gs = gk.sample(gs, (X, y), {"subsample_size": m})
+        os_ = ok.sample(os_)
+        np.testing.assert_array_equal(gs.rng_key, os_.rng_key)
+        np.testing.assert_array_equal(gs.z["N"], os_.z["N"])
+        assert int(gs.hmc_state.num_steps) == int(os_.hmc_state.num_steps)
+
+
 def test_device_resident_loop_equals_step_by_step():
     """``run_loop`` (one launch: Gibbs step + transition per iteration, adaptation included) gives
     the draws, accept probabilities, tree sizes and final state of ``sample()`` called in a loop."""
