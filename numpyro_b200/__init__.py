@@ -5,6 +5,6 @@ kernel, the potentials of the registered model families (``models``) and the Thr
 generator (``random``) run in hand-written CUDA (``csrc/``) behind the C ABI declared in
 ``include/b200mc.h``.  There is no CPU path.
 """
-from . import diagnostics, distributed, infer, models, random  # noqa: F401
+from . import diagnostics, distributed, handlers, infer, models, random  # noqa: F401
 
 __version__ = "0.1.0"

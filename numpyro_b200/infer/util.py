@@ -41,6 +41,22 @@ def _site_plan(model, draws, args, kwargs):
                     + np.asarray(draws["tau"], np.float32).reshape(S, 1) * np.asarray(draws["theta_base"], np.float32))
         return dict(site="obs", X=None, B=theta, scale=sigma, scale_kind=2, df=None,
                     y=None if y is None else f32(y), likelihood=_NORMAL, N=sigma.shape[0], det={"theta": theta})
+    if name == "eight_schools" or name.startswith("eight_schools[theta=LocScaleReparam("):
+        # the centred model, possibly under LocScaleReparam(c) (reparam.py:64-145): theta is the
+        # latent itself (c = 1) or theta = mu + tau^(1-c) (theta_decentered - c mu)
+        sigma = f32(args[1])
+        y = kwargs.get("y", args[2] if len(args) > 2 else None)
+        if "theta" in draws:
+            theta = f32(draws["theta"]).reshape(S, sigma.shape[0])
+        else:
+            c = np.float32(name[len("eight_schools[theta=LocScaleReparam("):-2])
+            mu = np.asarray(draws["mu"], np.float32).reshape(S, 1)
+            tau = np.asarray(draws["tau"], np.float32).reshape(S, 1)
+            theta = f32(mu + np.power(tau, np.float32(1) - c)
+                        * (np.asarray(draws["theta_decentered"], np.float32) - c * mu))
+        return dict(site="obs", X=None, B=theta, scale=sigma, scale_kind=2, df=None,
+                    y=None if y is None else f32(y), likelihood=_NORMAL, N=sigma.shape[0],
+                    det={} if name == "eight_schools" else {"theta": theta})
     if name == "stochastic_volatility":
         r = f32(args[0])
         s = f32(draws["s"]).reshape(S, r.shape[0])

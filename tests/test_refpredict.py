@@ -106,3 +106,23 @@ def test_cuda_predictive_matches_reference(nb, key, part):
     for k in pred:
         if k != site:
             np.testing.assert_allclose(pred[k], G[f"{key}/predictive/{tag}/{k}"], rtol=1e-6)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("c", [1.0, 0.3, 0.0])
+def test_cuda_log_likelihood_locscale_eight_schools(nb, c):
+    """The centred eight schools / LocScaleReparam(c) give the reference's log-likelihood of the
+    non-centred fixture at the same theta (the observation site is the same Normal(theta, sigma))."""
+    from numpyro_b200.infer.reparam import LocScaleReparam
+
+    d = _draws("es")
+    mu, tau = np.asarray(d["mu"], np.float32), np.asarray(d["tau"], np.float32)
+    theta = mu[:, None] + tau[:, None] * np.asarray(d["theta_base"], np.float32)
+    if c == 1.0:
+        model, draws = nb.models.eight_schools, {"mu": mu, "tau": tau, "theta": theta}
+    else:
+        model = nb.handlers.reparam(nb.models.eight_schools, config={"theta": LocScaleReparam(c)})
+        dec = (theta - mu[:, None]) / np.power(tau[:, None], np.float32(1 - c)) + np.float32(c) * mu[:, None]
+        draws = {"mu": mu, "tau": tau, "theta_decentered": dec.astype(np.float32)}
+    ll = nb.infer.log_likelihood(model, draws, 8, rc.S8, y=rc.Y8)
+    np.testing.assert_allclose(ll["obs"], G["es/loglik/obs"], rtol=2e-5, atol=2e-5)
