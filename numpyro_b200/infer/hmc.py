@@ -505,16 +505,20 @@ class HMC(MCMCKernel):
         self._bound_sig = _args_signature(model_args, model_kwargs)
         kind, arg = self._strategy()
         if init_params is None and kind == "value":
-            # initialization.py `init_to_value`: CONSTRAINED values per site.  The reference
-            # falls back to init_to_uniform for sites that are not listed; the device init
-            # search draws either every site or none, so a partial dict is refused.
+            # initialization.py `init_to_value`: CONSTRAINED values per site.  The device init
+            # search draws either every site or none; a partial dict is completed on the host
+            # (device RNG, device potential) and handed over as the initial point.
             missing = [k for k, _ in bound.trace_sites if k not in arg]
             if missing:
-                raise NotImplementedError(f"init_to_value must cover every latent site; missing {missing}")
-            init_params = bound.unconstrain(arg)
-            if self._vectorized:
-                init_params = {k: np.broadcast_to(v, (keys.shape[0],) + np.shape(v)).copy()
-                               for k, v in init_params.items()}
+                # the sites that are not listed fall back to init_to_uniform (initialization.py)
+                k_init = b2random.split(keys, 2, self._part())[:, 1]  # hmc.py:745
+                z = self._partial_init_values(bound, k_init, arg)
+                init_params = bound.unravel(z if self._vectorized else z[0])
+            else:
+                init_params = bound.unconstrain(arg)
+                if self._vectorized:
+                    init_params = {k: np.broadcast_to(v, (keys.shape[0],) + np.shape(v)).copy()
+                                   for k, v in init_params.items()}
         z0 = None
         if init_params is not None:
             z = bound.ravel(init_params)
@@ -531,6 +535,54 @@ class HMC(MCMCKernel):
         self._sample_fn = self._sample_one
         self._init_fn = True
         return self._to_state(sc, vec)
+
+    def _partial_init_values(self, bound, init_keys, values, radius=2.0):
+        """``find_valid_initial_params`` (``infer/util.py:386-424``, the branch that traces the seeded
+        model) under ``init_to_value(values=...)`` with only SOME sites given: per attempt
+        ``key, subkey = split(key)``; the seed handler then splits ``subkey`` once per latent site
+        in trace order; a listed site takes its (constrained) value, any other one
+        ``Uniform(-radius, radius)`` in unconstrained space pushed through the site's transform
+        (``initialization.py`` ``init_to_uniform``); the constrained values go back through the
+        inverse transforms; the point must have a finite potential and gradient (100 attempts).
+        ``init_keys``: ``uint32[C, 2]`` (``rng_key_init_model`` of every chain).  Returns z[C, D]."""
+        part = self._part()
+        unit = getattr(bound, "unit_interval", ())
+        for k, _ in bound.trace_sites:
+            if k not in values and k not in bound.positive and k not in unit and \
+                    bound.family == models.DIRICHLET_CATEGORICAL:
+                raise NotImplementedError("init_to_value with a missing simplex site is not available")
+        out = np.zeros((init_keys.shape[0], bound.dim), np.float32)
+        fi = np.finfo(np.float32)
+        for c in range(init_keys.shape[0]):
+            key = np.asarray(init_keys[c], np.uint32)
+            for _ in range(100):
+                key, subkey = b2random.split(key, 2, part)
+                k, zc = subkey, {}
+                for name, shape in bound.trace_sites:
+                    k, ks = b2random.split(k, 2, part)
+                    if name in values:
+                        v = np.asarray(values[name], np.float32)
+                        if name in bound.positive:
+                            v = np.log(v)
+                        elif name in unit:
+                            v = np.log(v) - np.log1p(-v)
+                    else:
+                        v = b2random.uniform(ks, shape, -radius, radius, part)
+                        with np.errstate(all="ignore"):
+                            if name in bound.positive:  # ExpTransform and back
+                                v = np.log(np.exp(v))
+                            elif name in unit:          # SigmoidTransform (clipped expit) and back
+                                p = np.clip(1 / (1 + np.exp(-v)), fi.tiny, np.float32(1) - fi.eps).astype(np.float32)
+                                v = np.log(p) - np.log1p(-p)
+                    zc[name] = np.broadcast_to(np.asarray(v, np.float32), shape)
+                z = bound.ravel(zc).astype(np.float32).reshape(1, bound.dim)
+                U, g = self.potential_and_grad(z)
+                if np.isfinite(U).all() and np.isfinite(g).all():
+                    out[c] = z[0]
+                    break
+            else:
+                raise RuntimeError("Cannot find valid initial parameters. Please check your model again.")
+        return out
 
     def _check_args(self, model_args, model_kwargs):
         """The reference rebuilds the potential from the args on every call

@@ -388,9 +388,76 @@ def test_cuda_init_to_value_equals_init_params(nb):
         out.append((m.get_extra_fields()["num_steps"], m.get_samples()["mu"]))
     assert np.array_equal(out[0][0], out[1][0])
     np.testing.assert_allclose(out[0][1], out[1][1], rtol=1e-5, atol=1e-6)
-    with pytest.raises(NotImplementedError):
-        k = infer.NUTS(models.eight_schools_noncentered, init_strategy=infer.hmc.init_to_value(values={"mu": 0.0}))
-        infer.MCMC(k, num_warmup=0, num_samples=2).run(PRNGKey(3), *args, **kwargs)
+
+
+REFINIT_CASES = {"mu": {"mu": 1.5}, "tau": {"tau": 2.0},
+                 "mu_theta": {"mu": -0.5, "theta_base": np.linspace(-1, 1, 8)}}  # make_refinit.py
+
+
+def _partial_init_restated(cfg, key, values):
+    """infer/util.py:396-424 under a partial ``init_to_value``, on the oracle's Threefry."""
+    _, subkey = cfg.split(key)
+    k, z = subkey, {}
+    for name, shape in (("mu", ()), ("tau", ()), ("theta_base", (8,))):  # trace order
+        k, ks = cfg.split(k)
+        if name in values:
+            v = np.asarray(values[name], np.float32)
+            v = np.log(v) if name == "tau" else v
+        else:
+            v = cfg.uniform(ks, shape, -2.0, 2.0)
+            v = np.log(np.exp(v)) if name == "tau" else v
+        z[name] = np.broadcast_to(v, shape).astype(np.float32)
+    return np.concatenate([np.ravel(z[k]) for k in sorted(z)])
+
+
+def test_partial_init_to_value_restatement_matches_reference():
+    """``refinit.npz`` = the reference's ``initialize_model`` with ``init_to_value`` given SOME sites."""
+    from oracle.hmc_util import Config
+    from oracle.threefry import PRNGKey
+
+    fx = np.load(os.path.join(os.path.dirname(__file__), "golden", "refinit.npz"))
+    for name, vals in REFINIT_CASES.items():
+        for part in (True, False):
+            for seed in (0, 1, 2):
+                z = _partial_init_restated(Config(np.float32, part), PRNGKey(seed), vals)
+                assert np.array_equal(z, fx[f"{name}/{'part' if part else 'legacy'}_{seed}"])
+
+
+@pytest.mark.gpu
+def test_cuda_partial_init_to_value_matches_reference(nb):
+    """A partial ``init_to_value``: the sites that are not listed are drawn as ``init_to_uniform``
+    does, on the reference's key tree -- bit for bit the reference's ``initialize_model``; and
+    ``init`` feeds it ``split(chain_key)[1]`` (hmc.py:745)."""
+    from numpyro_b200 import infer, models
+    from oracle.hmc_util import Config
+    from oracle.threefry import PRNGKey
+
+    fx = np.load(os.path.join(os.path.dirname(__file__), "golden", "refinit.npz"))
+    args, kwargs = (8, rc.S8), {"y": rc.Y8}
+    bound = models.eight_schools_noncentered.bind(*args, **kwargs)
+    for name, vals in REFINIT_CASES.items():
+        k = infer.NUTS(models.eight_schools_noncentered, init_strategy=infer.hmc.init_to_value(values=vals))
+        for part in (True, False):
+            k.partitionable = part
+            k._create(bound, 3, 10)
+            keys = np.stack([PRNGKey(s) for s in (0, 1, 2)]).astype(np.uint32)
+            z = k._partial_init_values(bound, keys, vals)
+            for seed in (0, 1, 2):
+                assert np.array_equal(z[seed], fx[f"{name}/{'part' if part else 'legacy'}_{seed}"])
+            cfg = Config(np.float32, part)
+            chain_key = np.asarray(PRNGKey(40), np.uint32)
+            st = k.init(chain_key, 10, model_args=args, model_kwargs=kwargs)
+            want = _partial_init_restated(cfg, cfg.split(chain_key)[1], vals)
+            assert np.array_equal(bound.ravel(st.z), want)
+            ck = np.stack([PRNGKey(41), PRNGKey(42)]).astype(np.uint32)  # vectorized chains
+            st = k.init(ck, 10, model_args=args, model_kwargs=kwargs)
+            for c in range(2):
+                assert np.array_equal(bound.ravel(st.z)[c], _partial_init_restated(cfg, cfg.split(ck[c])[1], vals))
+    m = infer.MCMC(infer.NUTS(models.eight_schools_noncentered,
+                              init_strategy=infer.hmc.init_to_value(values={"mu": 0.0})),
+                   num_warmup=50, num_samples=20)
+    m.run(np.asarray(PRNGKey(3), np.uint32), *args, **kwargs)
+    assert np.isfinite(m.get_samples()["tau"]).all()
 
 
 @pytest.mark.gpu
