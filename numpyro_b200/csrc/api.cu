@@ -496,7 +496,7 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   if (c.family == B200MC_HORSESHOE && c.dense_mass) batch_min = 16;
   if (const char* e = getenv("B200MC_BATCH_MIN_CHAINS")) batch_min = atoi(e);
   const bool batch = (c.family == B200MC_HORSESHOE || c.family == B200MC_LOGISTIC) &&
-                     C >= batch_min && C <= kBatchCols && !(c.nranks > 1) && P.num_blocks <= 1;
+                     C >= batch_min && !(c.nranks > 1) && P.num_blocks <= 1;  // (> kBatchCols: column groups)
   if (c.family == B200MC_LOGISTIC && !batch) {
     if (D > kGlmMaxD) { b200mc_destroy(h); return fail("logistic: D=%d > %d not supported", D, kGlmMaxD); }
     if (!c.data1_dev) { b200mc_destroy(h); return fail("logistic: labels missing"); }
@@ -984,7 +984,8 @@ static int launch_batch_gemms(b200mc_handle* h, cudaStream_t st) {
 static void fill_batch_launch(b200mc_handle* h, BatchLaunch& L) {
   auto& b = h->bt;
   memset(&L, 0, sizeof(L));
-  L.P = h->P; L.M = h->M; L.cs = h->cs; L.cv = h->cv; L.work = h->work; L.C = h->C;
+  L.P = h->P; L.M = h->M; L.cs = h->cs; L.cv = h->cv; L.work = h->work;
+  L.C = h->C < kBatchCols ? h->C : kBatchCols; L.c0 = 0; L.C_total = h->C;
   L.snap = b.snap; L.snap_stride = b.snap_stride; L.status = b.status; L.active = b.active;
   L.reqs = b.reqs;
   L.b_hi = b.b_hi; L.b_lo = b.b_lo; L.K1 = b.K1;
@@ -996,18 +997,34 @@ static void fill_batch_launch(b200mc_handle* h, BatchLaunch& L) {
 // contractions and advances every chain by one gradient.  The host only looks at the device
 // every kBatchStepsPerSync steps (how many chains still wait for a gradient), so this call
 // returns after the work is DONE, unlike the single-launch paths.
+static int launch_batch_group(b200mc_handle* h, const CollectSpec& col, const uint32_t* keys,
+                              int user_init, int c0, int Cg, cudaStream_t st);
+
+// More than kBatchCols chains: one column group of the operand images after the other, each
+// run to the end of the call's quota (chains are independent; a group's chains keep their
+// global indices in every per-chain array and in the collected draws).
 static int launch_batch(b200mc_handle* h, const CollectSpec& col, const uint32_t* keys,
                         int user_init, cudaStream_t st) {
+  for (int c0 = 0; c0 < h->C; c0 += kBatchCols) {
+    const int Cg = (h->C - c0 < kBatchCols) ? h->C - c0 : kBatchCols;
+    if (launch_batch_group(h, col, keys, user_init, c0, Cg, st)) return 1;
+  }
+  return 0;
+}
+
+static int launch_batch_group(b200mc_handle* h, const CollectSpec& col, const uint32_t* keys,
+                              int user_init, int c0, int Cg, cudaStream_t st) {
   BatchLaunch L;
   fill_batch_launch(h, L);
   L.col = col; L.init_keys = keys; L.user_init = user_init;
+  L.c0 = c0; L.C = Cg;
   auto& b = h->bt;
   unsigned* const slot_begin = b.active + kBatchStepsPerSync;     // count after the first launch
   unsigned* const slot_scrap = b.active + kBatchStepsPerSync + 1;  // launches nobody reads
   const bool dense = h->P.dense_mass != 0;
-  std::vector<int> status_h(h->C);
-  std::vector<MatvecRequest> reqs_h(h->C);
-  const dim3 mv_grid((h->D + kMatvecRows - 1) / kMatvecRows, h->C);
+  std::vector<int> status_h(Cg);
+  std::vector<MatvecRequest> reqs_h(Cg);
+  const dim3 mv_grid((h->D + kMatvecRows - 1) / kMatvecRows, Cg);
   const size_t mv_smem = sizeof(float) * 2 * (size_t)h->D;
   // a chain needs at most three sweeps between two gradients (leaf, then the two of a
   // transition start); chains that still wait afterwards simply continue in the next step
@@ -1016,7 +1033,7 @@ static int launch_batch(b200mc_handle* h, const CollectSpec& col, const uint32_t
       CK(kl::batch_matvec_launch(L, mv_grid, mv_smem, st));
       L.kind = BATCH_RESUME;
       L.active = (k == 2) ? count_slot : slot_scrap;
-      CK(kl::batch_step_launch(L, h->C, st));
+      CK(kl::batch_step_launch(L, Cg, st));
       g_launches += 2;
     }
     return 0;
@@ -1024,7 +1041,7 @@ static int launch_batch(b200mc_handle* h, const CollectSpec& col, const uint32_t
   CK(cudaMemsetAsync(b.active, 0, sizeof(unsigned) * (kBatchStepsPerSync + 2), st));
   L.kind = BATCH_BEGIN;
   L.active = dense ? slot_scrap : slot_begin;
-  CK(kl::batch_step_launch(L, h->C, st));
+  CK(kl::batch_step_launch(L, Cg, st));
   g_launches++;
   L.init_keys = nullptr;
   if (dense && sweeps_and_resumes(slot_begin)) return 1;
@@ -1038,7 +1055,7 @@ static int launch_batch(b200mc_handle* h, const CollectSpec& col, const uint32_t
       if (launch_batch_gemms(h, st)) return 1;
       L.kind = BATCH_GRAD;
       L.active = dense ? slot_scrap : b.active + i;
-      CK(kl::batch_step_launch(L, h->C, st));
+      CK(kl::batch_step_launch(L, Cg, st));
       g_launches++;
       if (dense && sweeps_and_resumes(b.active + i)) return 1;
     }
@@ -1046,19 +1063,19 @@ static int launch_batch(b200mc_handle* h, const CollectSpec& col, const uint32_t
     CK(cudaMemcpyAsync(&active, b.active + kBatchStepsPerSync - 1, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
     if (dense && h->P.adapt_mass_matrix) {
       // chains parked at a window end: covariance, Cholesky, triangular inverse, then resume
-      CK(cudaMemcpyAsync(status_h.data(), b.status, sizeof(int) * h->C, cudaMemcpyDeviceToHost, st));
-      CK(cudaMemcpyAsync(reqs_h.data(), b.reqs, sizeof(MatvecRequest) * h->C, cudaMemcpyDeviceToHost, st));
+      CK(cudaMemcpyAsync(status_h.data(), b.status + c0, sizeof(int) * Cg, cudaMemcpyDeviceToHost, st));
+      CK(cudaMemcpyAsync(reqs_h.data(), b.reqs + c0, sizeof(MatvecRequest) * Cg, cudaMemcpyDeviceToHost, st));
       CK(cudaStreamSynchronize(st));
       bool any = false;
-      for (int c = 0; c < h->C; ++c) {
+      for (int c = 0; c < Cg; ++c) {
         if (status_h[c] != 3) continue;
-        if (factor_chain_dense(h->cv.dense + (long)c * 4 * h->D * h->D, h->D, reqs_h[c].src1,
+        if (factor_chain_dense(h->cv.dense + (long)(c0 + c) * 4 * h->D * h->D, h->D, reqs_h[c].src1,
                                h->P.regularize_mass_matrix, st))
           return 1;
         status_h[c] = 2;  // its request has mat = -1: the next resume launch just continues
         any = true;
       }
-      if (any) CK(cudaMemcpyAsync(b.status, status_h.data(), sizeof(int) * h->C, cudaMemcpyHostToDevice, st));
+      if (any) CK(cudaMemcpyAsync(b.status + c0, status_h.data(), sizeof(int) * Cg, cudaMemcpyHostToDevice, st));
     }
     CK(cudaStreamSynchronize(st));
   }

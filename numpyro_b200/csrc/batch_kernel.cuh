@@ -33,7 +33,9 @@ struct BatchLaunch {
   ChainScalars* cs;
   ChainVectors cv;
   float* work;  // [C][num_slots][D]
-  int C;
+  int C;                // chains of THIS column group (<= kBatchCols): the launch's grid
+  int c0, C_total;      // first chain of the group / all chains of the handle: chain c0 + i is
+                        // column i of the operand images
   const uint32_t* init_keys;
   int user_init;
   int kind;             // BATCH_BEGIN / BATCH_GRAD / BATCH_RESUME
@@ -179,8 +181,9 @@ __device__ __forceinline__ float batch_finish(const BatchLaunch& L, const G& g, 
 // finish the potential at the published point, advance, publish the next point.
 __global__ void __launch_bounds__(kBatchThreads, 2) batch_step_kernel(const __grid_constant__ BatchLaunch L) {
   __shared__ float red_scratch[64];
-  const int c = blockIdx.x;
-  if (c >= L.C) return;
+  const int cl = blockIdx.x;  // column of the operand images
+  if (cl >= L.C) return;
+  const int c = L.c0 + cl;    // chain
   const BlockGroup g{red_scratch};
   const int D = L.P.D;
   using S_t = Sampler<BlockGroup>;
@@ -189,7 +192,7 @@ __global__ void __launch_bounds__(kBatchThreads, 2) batch_step_kernel(const __gr
   S_t S;
   StepResult r;
   if (L.kind == BATCH_BEGIN) {
-    S.setup(&L.P, g, base, D, 1, c, L.C, &L.col);
+    S.setup(&L.P, g, base, D, 1, c, L.C_total, &L.col);
     S.mv_yield = L.P.dense_mass != 0;
     S.load(L.cs, L.cv);
     if (L.init_keys)
@@ -206,7 +209,7 @@ __global__ void __launch_bounds__(kBatchThreads, 2) batch_step_kernel(const __gr
     S.P = &L.P; S.g = g; S.w = base; S.col = &L.col;
     if (S.dense) S.dn = L.cv.dense + (long)c * 4 * D * D;
     if (L.kind == BATCH_GRAD) {
-      const float U = batch_finish(L, g, S.v(LZ), S.v(LG), c);
+      const float U = batch_finish(L, g, S.v(LZ), S.v(LG), cl);
       r = S.advance(U);
     } else {
       r = S.resume();
@@ -214,7 +217,7 @@ __global__ void __launch_bounds__(kBatchThreads, 2) batch_step_kernel(const __gr
   }
   if (r == NEED_GRAD) {
     g.sync();
-    batch_prepare(L, g, S.v(LZ), c);
+    batch_prepare(L, g, S.v(LZ), cl);
     if (threadIdx.x == 0) L.status[c] = 0;
   } else if (r == NEED_MATVEC || r == NEED_FACTOR) {
     if (threadIdx.x == 0) {
@@ -237,7 +240,7 @@ __global__ void __launch_bounds__(kBatchThreads, 2) batch_step_kernel(const __gr
 // of a request come from ONE pass over the matrix.  Fixed summation order => deterministic.
 __global__ void __launch_bounds__(kMatvecThreads, 4) batch_matvec_kernel(const __grid_constant__ BatchLaunch L) {
   extern __shared__ float mv_src[];  // [2][D]
-  const int c = blockIdx.y;
+  const int c = L.c0 + blockIdx.y;
   if (L.status[c] != 2) return;
   const MatvecRequest rq = L.reqs[c];
   if (rq.mat < 0) return;  // nothing to sweep (a chain resuming after its factorisation)

@@ -175,6 +175,37 @@ def test_tier3_batched_logistic_matches_oracle_and_streaming_kernel(nb):
         assert_allclose(out["batch"][0]["potential_energy"][c], r["potential_energy"], rtol=1e-4)
 
 
+def test_more_chains_than_operand_columns_run_as_column_groups(nb):
+    """300 chains = a group of 256 operand columns + a group of 44: every chain keeps its global
+    index (keys, state, collected draws) and matches the oracle's chain on its own key."""
+    X, y = make_logistic(2000, 5, seed=6)
+    fam = opot.Logistic(X, y)
+    kw = dict(step_size=0.02, adapt_step_size=False, adapt_mass_matrix=False)
+    chains, n = 300, 8
+    key = T.PRNGKey(11)
+    mc = nb.infer.MCMC(nb.infer.NUTS(nb.models.logistic_regression, **kw), num_warmup=0,
+                       num_samples=n, num_chains=chains, chain_method="vectorized")
+    mc.run(key, X, y, extra_fields=("num_steps", "potential_energy"))
+    ex = mc.get_extra_fields(group_by_chain=True)
+    z = mc.get_samples(group_by_chain=True)["coefs"]
+    assert z.shape == (chains, n, 5) and np.isfinite(z).all()
+    keys = T.split(key, chains, True)
+    for c in (0, 255, 256, 299):
+        ok = ohmc.HMCKernel(fam, cfg=Config(np.float32, True), **kw)
+        r, _ = ohmc.run_chain(ok, keys[c], 0, n)
+        assert np.array_equal(ex["num_steps"][c], r["num_steps"]), c
+        assert_allclose(ex["potential_energy"][c], r["potential_energy"], rtol=1e-4)
+        assert_allclose(z[c], r["z"], rtol=2e-3, atol=2e-4)
+    # adaptation on, all chains: the second group adapts like the first
+    mc = nb.infer.MCMC(nb.infer.NUTS(nb.models.logistic_regression), num_warmup=100, num_samples=50,
+                       num_chains=chains, chain_method="vectorized")
+    mc.run(T.PRNGKey(12), X, y)
+    s = np.asarray(mc.get_samples(group_by_chain=True)["coefs"], np.float64)
+    assert nb.diagnostics.split_gelman_rubin(s).max() < 1.02
+    m = s.mean(1)
+    assert np.abs(m[256:].mean(0) - m[:256].mean(0)).max() < 0.02
+
+
 def test_batched_logistic_posterior(nb):
     X, y = make_logistic(4000, 6, seed=9)
     mc = nb.infer.MCMC(nb.infer.NUTS(nb.models.logistic_regression), num_warmup=200, num_samples=100,
