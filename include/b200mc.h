@@ -116,6 +116,13 @@ typedef struct {
   const float* ecs_ref_dev;
   /* EIGHT_SCHOOLS_LOCSCALE: 0 <= centered <= 1 (1 = the centred model, 0 = fully decentred) */
   float centered;
+  /* Conditioned latent sites (HMCGibbs: the wrapped model `condition`s + `substitute`s the Gibbs
+   * sites, hmc_gibbs.py:30-34,139-152): cond_count coordinates of the family's flat vector,
+   * cond_index_host[cond_count] ascending, whole sites only, are taken out of the sampler's
+   * vector (D shrinks by cond_count) and held at the values of b200mc_set_conditioned.  Families
+   * that run through the chain-batched kernels only (not LOGISTIC / the lock-step engine). */
+  int cond_count;
+  const int* cond_index_host;
 } b200mc_config;
 
 /* Scalar leaves of HMCState (hmc.py:31-48) and HMCAdaptState (hmc_util.py:18-30). */
@@ -172,7 +179,7 @@ typedef struct {
 const char* b200mc_last_error(void);
 /* ABI version of the loaded library; a binding compares it with the B200MC_ABI_VERSION it was
  * written against before calling anything else (numpyro_b200/_lib.py does). */
-#define B200MC_ABI_VERSION 3
+#define B200MC_ABI_VERSION 4
 int b200mc_version(void);
 
 /* HMC.__init__ + the data binding of MCMC.run.  Raises (returns non-zero) for an
@@ -246,6 +253,15 @@ int b200mc_ecs_get_subsample(b200mc_handle* h, int32_t* idx_dev, void* stream);
 int b200mc_ecs_set_subsample(b200mc_handle* h, const int32_t* idx_dev, void* stream);
 int b200mc_ecs_update(b200mc_handle* h, uint32_t* keys_dev, int num_blocks, float* accept_prob_dev,
                       void* stream);
+/* Values of the conditioned coordinates of every chain (b200mc_config.cond_count):
+ * values_dev[num_chains][cond_count] in UNCONSTRAINED space, in cond_index order, and
+ * offset_dev[num_chains] (or null: zeros) added to the potential -- the Jacobian terms of the
+ * conditioned sites, which the reference's conditioned density does not carry.  The chains'
+ * cached potential_energy / z_grad are NOT refreshed: the caller re-evaluates them
+ * (b200mc_potential_and_grad, point i uses chain i's values) as hmc_gibbs.py:170-185 does. */
+int b200mc_set_conditioned(b200mc_handle* h, const float* values_dev, const float* offset_dev,
+                           void* stream);
+
 /* The whole HMCECS loop on the device: num_iters times { the Gibbs step of b200mc_ecs_update; one
  * transition of the inner kernel }, in ONE launch, collecting like b200mc_sample.
  * accept_prob_dev[C]: the last step's accept_prob; accept_all_dev[num_iters][C] (or NULL): every

@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("B200MC_LIB") or os.path.join(_HERE, "libb200mc.so")
 
 
-ABI_VERSION = 3  # include/b200mc.h B200MC_ABI_VERSION
+ABI_VERSION = 4  # include/b200mc.h B200MC_ABI_VERSION
 
 
 class B200Error(RuntimeError):
@@ -35,7 +35,7 @@ class Config(C.Structure):
         ("num_blocks", C.c_int), ("block_perm_host", C.c_void_p),
         ("block_sizes_host", C.c_void_p), ("block_dense_host", C.c_void_p),
         ("subsample_size", C.c_int), ("ecs_degree", C.c_int), ("ecs_ref_dev", C.c_void_p),
-        ("centered", C.c_float),
+        ("centered", C.c_float), ("cond_count", C.c_int), ("cond_index_host", C.c_void_p),
     ]
 
 
@@ -102,6 +102,7 @@ SYMBOLS = {
     "b200mc_ecs_set_subsample": (_i, [_vp, _vp, _vp]),
     "b200mc_ecs_update": (_i, [_vp, _vp, _i, _vp, _vp]),
     "b200mc_ecs_sample": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "b200mc_set_conditioned": (_i, [_vp, _vp, _vp, _vp]),
     "b200mc_random_split": (_i, [_vp, _i, _i, _vp, _i, _vp]),
     "b200mc_random_bits": (_i, [_vp, _i, _vp, _i, _vp]),
     "b200mc_random_uniform": (_i, [_vp, _i, _f, _f, _vp, _i, _vp]),

@@ -50,6 +50,12 @@ struct b200mc_handle {
   ChainVectors cv{};
   float* work = nullptr;
   int mode = 0, c_pad = 0;
+  // conditioned sites (b200mc_config.cond_count)
+  int cond_count = 0, cond_dfull = 0;
+  int* cond_map = nullptr;     // [D] free -> full
+  int* cond_index = nullptr;   // [cond_count] conditioned -> full
+  float* cond_full = nullptr;  // [C][2 * cond_dfull]
+  float* cond_offset = nullptr;
   // glm
   int glm_ctas = 0, glm_nt_total = 0, glm_stages = 0, glm_pinned = 0, glm_smem = 0;
   unsigned char* glm_xt = nullptr;  // re-tiled X + labels
@@ -346,6 +352,7 @@ extern "C" void b200mc_destroy(b200mc_handle* h) {
     if (h->xarrive[r]) cudaIpcCloseMemHandle(h->xarrive[r]);
   }
   cudaFree(h->xchg_local); cudaFree(h->xarrive_local);
+  dfree(h->cond_map); dfree(h->cond_index); dfree(h->cond_full); dfree(h->cond_offset);
   dfree(h->bt.x_hi); dfree(h->bt.x_lo); dfree(h->bt.xt_hi); dfree(h->bt.xt_lo);
   dfree(h->bt.b_hi); dfree(h->bt.b_lo); dfree(h->bt.r_hi); dfree(h->bt.r_lo);
   dfree(h->bt.ll_part); dfree(h->bt.gpart); dfree(h->bt.col_scale);
@@ -378,6 +385,42 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   SamplerParams& P = h->P;
   memset(&P, 0, sizeof(P));
   if (family_sites(c, P, h->D)) { delete h; return 1; }
+  std::vector<int> cond_map_h;
+  if (c.cond_count > 0) {
+    // Conditioned sites: whole sites leave the sampler's vector; the site table (trace order,
+    // offsets in the flat vector) and D describe the free coordinates from here on.
+    if (c.family == B200MC_LOGISTIC || c.family == B200MC_LOGISTIC_ECS || c.num_blocks > 1 || c.nranks > 1) {
+      delete h;
+      return fail("conditioned sites: not available for this family / configuration");
+    }
+    if (!c.cond_index_host || c.cond_count >= h->D) { delete h; return fail("conditioned sites: bad index list"); }
+    const int Dfull = h->D;
+    std::vector<int> is_cond(Dfull, 0), to_free(Dfull, -1);
+    for (int k = 0; k < c.cond_count; ++k) {
+      const int i = c.cond_index_host[k];
+      if (i < 0 || i >= Dfull || (k > 0 && i <= c.cond_index_host[k - 1])) {
+        delete h;
+        return fail("conditioned sites: indices must be ascending and inside the vector");
+      }
+      is_cond[i] = 1;
+    }
+    for (int i = 0; i < Dfull; ++i)
+      if (!is_cond[i]) { to_free[i] = (int)cond_map_h.size(); cond_map_h.push_back(i); }
+    int ns = 0;
+    for (int k = 0; k < P.nsites; ++k) {
+      int n_in = 0;
+      for (int j = 0; j < P.site_size[k]; ++j) n_in += is_cond[P.site_off[k] + j];
+      if (n_in == P.site_size[k]) continue;  // conditioned: observed for the init search's key tree
+      if (n_in != 0) { delete h; return fail("conditioned sites: a site is conditioned as a whole or not at all"); }
+      P.site_off[ns] = to_free[P.site_off[k]];
+      P.site_size[ns] = P.site_size[k];
+      ++ns;
+    }
+    P.nsites = ns;
+    h->cond_count = c.cond_count;
+    h->cond_dfull = Dfull;
+    h->D = (int)cond_map_h.size();
+  }
   cudaGetDevice(&h->device);
   cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, h->device);
   cudaDeviceGetAttribute(&h->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device);
@@ -428,6 +471,8 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   h->M.y8 = nullptr; h->M.ecs_idx = nullptr; h->M.ecs_ref = nullptr; h->M.ecs_sums = nullptr;
   h->M.ecs_m = 0; h->M.ecs_degree = 0; h->M.scratch_stride = 0;
   h->M.centered = c.centered;
+  h->M.cond_map = nullptr; h->M.cond_full = nullptr; h->M.cond_offset = nullptr;
+  h->M.cond_dfull = 0; h->M.cond_nfree = 0;
 
   const size_t vec_bytes = (size_t)C * D * sizeof(float);
   auto alloc = [&](void** p, size_t bytes) {
@@ -457,6 +502,17 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   ACK(alloc((void**)&h->cv.welford_mean, vec_bytes));
   ACK(alloc((void**)&h->cv.welford_m2, vec_bytes));
   if (c.dense_mass) ACK(alloc((void**)&h->cv.dense, sizeof(float) * 4 * (size_t)C * D * D));
+  if (h->cond_count > 0) {
+    ACK(alloc((void**)&h->cond_map, sizeof(int) * D));
+    ACK(alloc((void**)&h->cond_index, sizeof(int) * h->cond_count));
+    ACK(alloc((void**)&h->cond_full, sizeof(float) * 2 * (size_t)C * h->cond_dfull));
+    ACK(alloc((void**)&h->cond_offset, sizeof(float) * C));
+    ACK(cudaMemcpy(h->cond_map, cond_map_h.data(), sizeof(int) * D, cudaMemcpyHostToDevice));
+    ACK(cudaMemcpy(h->cond_index, c.cond_index_host, sizeof(int) * h->cond_count, cudaMemcpyHostToDevice));
+    h->M.cond_map = h->cond_map; h->M.cond_full = h->cond_full; h->M.cond_offset = h->cond_offset;
+    h->M.cond_dfull = h->cond_dfull; h->M.cond_nfree = D;
+    h->cfg.cond_index_host = nullptr;  // the caller's array is not referenced after create
+  }
 
   P.num_blocks = 1;
   if (c.num_blocks > 1) {  // structured mass matrix: validate and upload the block tables
@@ -496,7 +552,7 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
   if (c.family == B200MC_HORSESHOE && c.dense_mass) batch_min = 16;
   if (const char* e = getenv("B200MC_BATCH_MIN_CHAINS")) batch_min = atoi(e);
   const bool batch = (c.family == B200MC_HORSESHOE || c.family == B200MC_LOGISTIC) &&
-                     C >= batch_min && !(c.nranks > 1) && P.num_blocks <= 1;  // (> kBatchCols: column groups)
+                     h->cond_count == 0 && C >= batch_min && !(c.nranks > 1) && P.num_blocks <= 1;  // (> kBatchCols: column groups)
   if (c.family == B200MC_LOGISTIC && !batch) {
     if (D > kGlmMaxD) { b200mc_destroy(h); return fail("logistic: D=%d > %d not supported", D, kGlmMaxD); }
     if (!c.data1_dev) { b200mc_destroy(h); return fail("logistic: labels missing"); }
@@ -1195,6 +1251,31 @@ extern "C" int b200mc_sample(b200mc_handle* h, int num_iters, int collect_start,
   return launch_chain(h, col, nullptr, 0, st);
 }
 
+__global__ void cond_scatter_kernel(float* full, const int* index, const float* values, int C,
+                                    int count, int dfull) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= C * count) return;
+  const int c = i / count, k = i - c * count;
+  full[(long)c * 2 * dfull + index[k]] = values[i];
+}
+
+extern "C" int b200mc_set_conditioned(b200mc_handle* h, const float* values_dev, const float* offset_dev,
+                                      void* stream) {
+  if (!h || !values_dev) return fail("null argument");
+  if (h->cond_count <= 0) return fail("the handle has no conditioned sites (b200mc_config.cond_count)");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int n = h->C * h->cond_count;
+  cond_scatter_kernel<<<(n + 255) / 256, 256, 0, st>>>(h->cond_full, h->cond_index, values_dev, h->C,
+                                                      h->cond_count, h->cond_dfull);
+  g_launches++;
+  CK(cudaGetLastError());
+  if (offset_dev)
+    CK(cudaMemcpyAsync(h->cond_offset, offset_dev, sizeof(float) * h->C, cudaMemcpyDeviceToDevice, st));
+  else
+    CK(cudaMemsetAsync(h->cond_offset, 0, sizeof(float) * h->C, st));
+  return 0;
+}
+
 extern "C" int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, int n, float* U_dev,
                                          float* grad_dev, void* stream) {
   if (!h || !z_dev || !U_dev || !grad_dev) return fail("null argument");
@@ -1235,6 +1316,8 @@ extern "C" int b200mc_potential_and_grad(b200mc_handle* h, const float* z_dev, i
         return 1;
     return 0;
   }
+  if (h->cond_count > 0 && n > h->C)
+    return fail("conditioned sites: point i is evaluated with chain i's values, so n <= num_chains");
   // per-chain scratch (horseshoe residuals) is sized for num_chains: evaluate in batches
   for (int i0 = 0; i0 < n; i0 += h->C) {
     const int m = (n - i0 < h->C) ? n - i0 : h->C;

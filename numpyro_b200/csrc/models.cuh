@@ -36,6 +36,14 @@ struct ModelData {
   int ecs_m, ecs_degree;
   long scratch_stride;    // 2 * ecs_m + kEcsSlices * D floats per chain
   float centered;         // eight schools under LocScaleReparam(centered)
+  // Conditioned sites (HMCGibbs, hmc_gibbs.py:30-34 `condition` + `substitute`): the sampler's
+  // vector holds the FREE coordinates only; the family's potential is evaluated on the full vector
+  // with the conditioned coordinates held at the values of b200mc_set_conditioned.
+  const int* cond_map;       // [cond_nfree] free coordinate -> index in the full vector (null: none)
+  float* cond_full;          // [C][2 * cond_dfull]: full position, then full gradient
+  const float* cond_offset;  // [C] added to U: the conditioned sites' Jacobian terms the
+                             // reference's conditioned density does not have
+  int cond_dfull, cond_nfree;
 };
 
 #define B200MC_LOG_SQRT_2PI 0.9189385332046727f
@@ -714,9 +722,9 @@ __device__ inline float logistic_ecs_potential_cta(const ModelData& M, const Blo
 }
 
 template <class G>
-__device__ __forceinline__ float model_potential(const ModelData& M, const G& g, const float* z,
-                                                 int zs, float* grad, int gs, int chain,
-                                                 const float* ecs_rows = nullptr) {
+__device__ __forceinline__ float family_potential(const ModelData& M, const G& g, const float* z,
+                                                  int zs, float* grad, int gs, int chain,
+                                                  const float* ecs_rows = nullptr) {
   if (M.family == FAM_EIGHT_SCHOOLS) return eight_schools_potential(M, g, z, zs, grad, gs);
   if (M.family == FAM_HORSESHOE) return horseshoe_potential(M, g, z, zs, grad, gs, chain);
   if (M.family == FAM_DIRICHLET_CATEGORICAL) return dirichlet_categorical_potential(M, g, z, zs, grad, gs);
@@ -728,6 +736,24 @@ __device__ __forceinline__ float model_potential(const ModelData& M, const G& g,
                                     ecs_rows);
   }
   return sv_potential(M, g, z, zs, grad, gs);
+}
+
+template <class G>
+__device__ __forceinline__ float model_potential(const ModelData& M, const G& g, const float* z,
+                                                 int zs, float* grad, int gs, int chain,
+                                                 const float* ecs_rows = nullptr) {
+  if (M.cond_map == nullptr) return family_potential(M, g, z, zs, grad, gs, chain, ecs_rows);
+  // conditioned sites: scatter the free coordinates into the chain's full vector, evaluate the
+  // family there, gather the free coordinates of the gradient
+  float* zf = M.cond_full + (long)chain * 2 * M.cond_dfull;
+  float* gf = zf + M.cond_dfull;
+  for (int d = g.lane(); d < M.cond_nfree; d += g.size()) zf[M.cond_map[d]] = z[(long)d * zs];
+  g.sync();
+  const float U = family_potential(M, g, zf, 1, gf, 1, chain, ecs_rows);
+  g.sync();
+  for (int d = g.lane(); d < M.cond_nfree; d += g.size()) grad[(long)d * gs] = gf[M.cond_map[d]];
+  g.sync();
+  return U + M.cond_offset[chain];
 }
 
 }  // namespace b200mc

@@ -323,7 +323,10 @@ class HMC(MCMCKernel):
         ecs_ref = None
         if bound.family == models.LOGISTIC_ECS and self._ecs["degree"]:
             ecs_ref = _lib.DeviceArray.from_numpy(bound.ravel(self._ecs["ref"]).reshape(-1), np.float32)
+        cond = getattr(bound, "cond_index", None)
         cfg = _lib.Config(
+            cond_count=0 if cond is None else int(cond.size),
+            cond_index_host=None if cond is None else cond.ctypes.data,
             struct_size=C.sizeof(_lib.Config), family=bound.family, num_chains=num_chains, N=bound.N, ncols=bound.ncols,
             data0_dev=d0.ptr, data1_dev=d1.ptr if d1 is not None else None,
             algo=0 if self._algo == "NUTS" else 1, step_size=float(self._step_size),

@@ -9,9 +9,11 @@ potential on the current subsample (with or without the Taylor control variate o
 on the device (``csrc/ecs_kernel.cuh``, ``csrc/models.cuh``); this module holds the reference's
 key handling and state threading.
 
-``HMCGibbs`` with a user ``gibbs_fn`` needs a potential that is a function of arbitrary
-conditioned sites; the registered closed-form potentials have none, so ``HMCGibbs.init``
-raises -- the class carries the shared surface (constructor checks, state, diagnostics string).
+``HMCGibbs`` with a user ``gibbs_fn``: the Gibbs sites are conditioned sites of the registered
+family (``models.BoundModel.condition``; on the device the family's potential is evaluated on the
+full vector with those coordinates held, ``csrc/models.cuh`` ``model_potential``), the HMC/NUTS
+transition over the remaining sites is the CUDA one, and ``gibbs_fn`` is the caller's Python
+function on host arrays -- one host round trip per transition, as a Python ``gibbs_fn`` implies.
 """
 import copy
 import ctypes as C
@@ -36,6 +38,22 @@ def taylor_proxy(reference_params, degree=2):
     return TaylorProxy(dict(reference_params), 2 if degree == 2 else 1)
 
 
+def _identity(x):
+    return x
+
+
+class _ConditionedModel:
+    """``_wrap_model`` (``hmc_gibbs.py:30-34``) for a registered family: binding gives the view
+    with the Gibbs sites conditioned."""
+
+    def __init__(self, model, sites):
+        self._model, self._sites = model, list(sites)
+        self.__name__ = getattr(model, "__name__", "model")
+
+    def bind(self, *args, **kwargs):
+        return self._model.bind(*args, **kwargs).condition(self._sites)
+
+
 class HMCGibbs(MCMCKernel):
     """``hmc_gibbs.py:38-190``."""
 
@@ -49,6 +67,10 @@ class HMCGibbs(MCMCKernel):
         assert inner_kernel.model is not None, (
             "HMCGibbs does not support models specified via a potential function.")
         self.inner_kernel = copy.copy(inner_kernel)
+        # hmc_gibbs.py:99-100: the inner kernel sees the model with the Gibbs sites conditioned
+        self._model0 = inner_kernel._model
+        if gibbs_fn is not _identity:
+            self.inner_kernel._model = _ConditionedModel(inner_kernel._model, gibbs_sites)
         self._gibbs_sites = gibbs_sites
         self._gibbs_fn = gibbs_fn
         self._prototype_trace = None
@@ -68,31 +90,126 @@ class HMCGibbs(MCMCKernel):
             state.num_steps, state.adapt_state.step_size, state.mean_accept_prob)
 
     def postprocess_fn(self, args, kwargs):
+        """``hmc_gibbs.py:109-119``: the HMC sites through the inner kernel's ``postprocess_fn``
+        with the Gibbs sites substituted; the Gibbs sites as they are (constrained)."""
+        full = self._model0.bind(*args, **(kwargs or {}))
+        view = full.condition(self._gibbs_sites)
+
         def fn(z):
             hmc_sites = {k: v for k, v in z.items() if k not in self._gibbs_sites}
             gibbs_sites = {k: v for k, v in z.items() if k in self._gibbs_sites}
-            hmc_sites = self.inner_kernel.postprocess_fn(args, kwargs)(hmc_sites)
+            flat, _ = view.cond_unconstrained(gibbs_sites)
+            off, un = 0, {}
+            for k, (_, n, shp) in view.cond_sites.items():
+                un[k] = flat[..., off:off + n].reshape(flat.shape[:-1] + shp)
+                off += n
+            out = full.postprocess({**hmc_sites, **un})
+            hmc_sites = {k: v for k, v in out.items() if k not in self._gibbs_sites}
             return {**gibbs_sites, **hmc_sites}
 
         return fn
 
+    # ------------------------------------------------------------------ conditioned values
+    def _push_gibbs(self, gibbs_sites):
+        """Constrained Gibbs-site values (``[...]`` or ``[C, ...]`` per site) -> the device."""
+        inner = self.inner_kernel
+        view, Cn = inner._bound, inner._num_chains
+        flat, off = view.cond_unconstrained(gibbs_sites)
+        flat = np.ascontiguousarray(np.broadcast_to(flat.reshape(-1, flat.shape[-1]), (Cn, flat.shape[-1])),
+                                    np.float32)
+        off = np.ascontiguousarray(np.broadcast_to(np.reshape(off, (-1,)), (Cn,)), np.float32)
+        fd, od = _lib.DeviceArray.from_numpy(flat), _lib.DeviceArray.from_numpy(off)
+        _lib.check(_lib.lib().b200mc_set_conditioned(inner._handle, fd.ptr, od.ptr, None))
+        _lib.check(_lib.lib().b200mc_stream_synchronize(None))
+
+    def _prior_sample(self, full, name, key, part):
+        """``init_to_sample`` (``initialization.py:88-93``): ONE prior draw of the site, its median
+        over that one draw.  Registered priors: ``Normal(loc, scale)`` (``continuous.py``
+        ``Normal.sample``: ``loc + scale * normal(key, (1,) + shape)``)."""
+        prior = getattr(full, "prior", {}).get(name)
+        if prior is None or prior[0] != "normal":
+            raise NotImplementedError(
+                f"HMCGibbs: no registered prior sampler for the Gibbs site {name!r}; pass its initial "
+                "value in `init_params`")
+        _, loc, scale = prior
+        shape = dict(full.trace_sites)[name]
+        eps = b2random.normal(key, (1,) + tuple(shape), part)
+        return (np.float32(loc) + np.float32(scale) * eps)[0].astype(np.float32)
+
     def init(self, rng_key, num_warmup, init_params, model_args, model_kwargs):
-        raise NotImplementedError(
-            "HMCGibbs with a user gibbs_fn needs a potential conditioned on arbitrary sites; the "
-            "registered closed-form potentials have none (use HMCECS for subsampled plates)")
+        """``hmc_gibbs.py:121-152``."""
+        inner = self.inner_kernel
+        part = inner._part()
+        model_kwargs = {} if model_kwargs is None else dict(model_kwargs)
+        rng_key = np.asarray(rng_key, np.uint32)
+        vectorized = not b2random.is_prng_key(rng_key)
+        keys = rng_key.reshape(-1, 2)
+        full = self._model0.bind(*model_args, **model_kwargs)
+        init_params = None if init_params is None else dict(init_params)
+        first = self._prototype_trace is None
+        proto = [dict() for _ in keys]
+        out_keys, keys_z = [], []
+        for c, key in enumerate(keys):
+            if first:
+                key, key_u = b2random.split(key, 2, part)
+                k = key_u  # seed(model, key_u): one split per latent site, trace order
+                for name, _ in full.trace_sites:
+                    k, ks = b2random.split(k, 2, part)
+                    if name in self._gibbs_sites and not (init_params and name in init_params):
+                        proto[c][name] = self._prior_sample(full, name, ks, part)
+            key, key_z = b2random.split(key, 2, part)
+            out_keys.append(key)
+            keys_z.append(key_z)
+        if first:
+            self._prototype_trace = proto
+        gibbs_sites = {}
+        for name, _ in full.trace_sites:
+            if name not in self._gibbs_sites:
+                continue
+            if init_params and name in init_params:
+                gibbs_sites[name] = np.asarray(init_params.pop(name), np.float32)
+            else:
+                v = np.stack([self._prototype_trace[min(c, len(self._prototype_trace) - 1)][name]
+                              for c in range(len(keys))])
+                gibbs_sites[name] = v if vectorized else v[0]
+        inner._ecs = {"degree": 0, "ref": None,
+                      "after_create": lambda kern: self._push_gibbs(gibbs_sites)}
+        key_z = np.stack(keys_z) if vectorized else keys_z[0]
+        hmc_state = inner.init(key_z, num_warmup, init_params or None, model_args=model_args,
+                               model_kwargs=model_kwargs)
+        self._sample_fn = True
+        rk = np.stack(out_keys) if vectorized else out_keys[0]
+        return HMCGibbsState({**gibbs_sites, **hmc_state.z}, hmc_state, rk)
 
     def sample(self, state, model_args, model_kwargs):
-        raise NotImplementedError("see HMCGibbs.init")
+        """``hmc_gibbs.py:154-190``: new Gibbs-site values from ``gibbs_fn``, the HMC state's
+        ``potential_energy`` / ``z_grad`` re-evaluated under them, one HMC/NUTS transition."""
+        inner = self.inner_kernel
+        part = inner._part()
+        ks = b2random.split(state.rng_key, 2, part)
+        rng_key, rng_gibbs = ks[..., 0, :], ks[..., 1, :]
+        z_gibbs = {k: v for k, v in state.z.items() if k not in state.hmc_state.z}
+        z_hmc = {k: v for k, v in state.z.items() if k in state.hmc_state.z}
+        post = self.postprocess_fn(model_args, model_kwargs)({**z_gibbs, **z_hmc})
+        z_hmc_c = {k: v for k, v in post.items() if k not in z_gibbs}
+        z_gibbs = self._gibbs_fn(rng_key=rng_gibbs, gibbs_sites=z_gibbs, hmc_sites=z_hmc_c)
+        z_gibbs = {k: np.asarray(v, np.float32) for k, v in z_gibbs.items()}
+        self._push_gibbs(z_gibbs)
+        view = inner._bound
+        flat = view.ravel(state.hmc_state.z).reshape(inner._num_chains, view.dim)
+        pe, grad = inner.potential_and_grad(flat)
+        if not inner._vectorized:
+            pe, grad = pe[0], grad[0]
+        hmc_state = state.hmc_state._replace(z_grad=view.unravel(grad),
+                                             potential_energy=np.asarray(pe, np.float32))
+        hmc_state = inner.sample(hmc_state, model_args, model_kwargs)
+        return HMCGibbsState({**z_gibbs, **hmc_state.z}, hmc_state, rng_key)
 
     def __getstate__(self):
         state = self.__dict__.copy()
         state["_prototype_trace"] = None
         state["_sample_fn"] = None
         return state
-
-
-def _identity(x):
-    return x
 
 
 class HMCECS(HMCGibbs):

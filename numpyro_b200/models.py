@@ -72,6 +72,60 @@ class BoundModel:
         (``infer/util.py:176-230,583-609``)."""
         return self._constrain(zdict)
 
+    def condition(self, names):
+        """The model with the latent sites ``names`` conditioned on values that are supplied at
+        run time (``hmc_gibbs.py:30-34``: ``condition`` + ``substitute`` of the Gibbs sites): a view
+        whose site layout, dimension and trace order cover the remaining sites only; ``full`` is
+        the unconditioned model and ``cond_index`` the conditioned coordinates of ITS flat vector
+        (``b200mc_config.cond_index_host``)."""
+        import copy
+
+        names = list(names)
+        unknown = [k for k in names if k not in self.flat_sites]
+        if unknown:
+            raise ValueError(f"cannot condition on {unknown}: not latent sites of {self.name}")
+        if self.family in (LOGISTIC, LOGISTIC_ECS):
+            raise NotImplementedError("conditioned sites are not available for the streaming logistic kernels")
+        b = copy.copy(self)
+        b.full = self
+        b.cond_sites = OrderedDict((k, v) for k, v in self.flat_sites.items() if k in names)
+        b.cond_index = np.ascontiguousarray(np.concatenate(
+            [np.arange(o, o + n) for o, n, _ in b.cond_sites.values()]), np.int32)
+        b.trace_sites = tuple((k, shp) for k, shp in self.trace_sites if k not in names)
+        if not b.trace_sites:
+            raise ValueError("every latent site is conditioned: nothing left for HMC")
+        b.positive = tuple(k for k in self.positive if k not in names)
+        if hasattr(self, "unit_interval"):
+            b.unit_interval = tuple(k for k in self.unit_interval if k not in names)
+        off, b.flat_sites = 0, OrderedDict()
+        for k, shape in sorted(b.trace_sites):
+            size = int(np.prod(shape)) if len(shape) else 1
+            b.flat_sites[k] = (off, size, tuple(shape))
+            off += size
+        b.dim = off
+        return b
+
+    def cond_unconstrained(self, values):
+        """Constrained values of the conditioned sites -> (flat unconstrained ``[..., cond_count]``,
+        potential offset ``[...]``).  The offset is the conditioned sites' log|Jacobian|: the
+        device potential of the full model carries ``-log|J|`` for every site, the reference's
+        conditioned density does not for a site that is given in constrained space."""
+        u = self.full.unconstrain({**{k: np.zeros(shp, np.float32) + 0.5 for k, (_, _, shp) in
+                                      self.full.flat_sites.items()}, **values})
+        parts, off = [], 0.0
+        for k, (_, n, shp) in self.cond_sites.items():
+            v = np.asarray(u[k], np.float32)
+            batch = v.shape[:v.ndim - len(shp)]
+            parts.append(v.reshape(batch + (n,)))
+            if k in self.full.positive:        # ExpTransform: log|J| = z
+                off = off + parts[-1].sum(-1)
+            elif k in getattr(self.full, "unit_interval", ()):  # SigmoidTransform: log|J| = -softplus(-z) - softplus(z)
+                off = off - (np.logaddexp(0, -parts[-1]) + np.logaddexp(0, parts[-1])).sum(-1)
+            elif self.full.family == DIRICHLET_CATEGORICAL:
+                raise NotImplementedError("a simplex site cannot be conditioned")
+        flat = np.concatenate(parts, axis=-1)
+        return flat, np.zeros(flat.shape[:-1], np.float32) + np.asarray(off, np.float32)
+
 
 class RegisteredModel:
     def __init__(self, name, binder, doc):
@@ -118,9 +172,12 @@ def _bind_eight_schools(J, sigma, y=None):
         out["theta"] = mu[..., None] + tau[..., None] * z["theta_base"]
         return out
 
-    return BoundModel(EIGHT_SCHOOLS, "eight_schools", J, 0, y, sigma,
-                      [("mu", ()), ("tau", ()), ("theta_base", (J,))], constrain,
-                      positive=("tau",))
+    bound = BoundModel(EIGHT_SCHOOLS, "eight_schools", J, 0, y, sigma,
+                       [("mu", ()), ("tau", ()), ("theta_base", (J,))], constrain,
+                       positive=("tau",))
+    # priors with a registered sampler (HMCGibbs' prototype trace draws its Gibbs sites from them)
+    bound.prior = {"mu": ("normal", 0.0, 5.0), "theta_base": ("normal", 0.0, 1.0)}
+    return bound
 
 
 def _bind_eight_schools_locscale(centered):
