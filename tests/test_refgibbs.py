@@ -140,6 +140,39 @@ def test_cuda_hmcgibbs_matches_reference(fx, part):
 
 
 @pytest.mark.gpu
+def test_cuda_hmcgibbs_vectorized_chains_are_independent():
+    """Vectorized chains (``uint32[C, 2]`` keys): chain c is the single-chain run on key c."""
+    import __graft_entry__ as g
+    from numpyro_b200 import random as b2random
+
+    nb = g.build()
+    args, kwargs = (8, rc.S8), {"y": rc.Y8}
+    one = gc.make_gibbs_fn(lambda key: b2random.normal(key, (), True))
+
+    def batched(rng_key, gibbs_sites, hmc_sites):
+        if np.ndim(rng_key) == 1:
+            return one(rng_key, gibbs_sites, hmc_sites)
+        rows = [one(rng_key[c], None, {k: v[c] for k, v in hmc_sites.items()})["mu"] for c in range(len(rng_key))]
+        return {"mu": np.asarray(rows, np.float32)}
+
+    keys = np.stack([PRNGKey(s) for s in (3, 4, 5)]).astype(np.uint32)
+    kv = nb.infer.HMCGibbs(nb.infer.NUTS(nb.models.eight_schools_noncentered, **gc.KERNEL_KW), batched, ["mu"])
+    sv = kv.init(keys, 8, None, args, kwargs)
+    singles = []
+    for c in range(3):
+        k1 = nb.infer.HMCGibbs(nb.infer.NUTS(nb.models.eight_schools_noncentered, **gc.KERNEL_KW), batched, ["mu"])
+        singles.append((k1, k1.init(keys[c], 8, None, args, kwargs)))
+    for step in range(12):
+        for c, (k1, s1) in enumerate(singles):
+            assert np.array_equal(np.asarray(sv.z["mu"])[c], np.asarray(s1.z["mu"])), (step, c)
+            assert np.array_equal(np.asarray(sv.hmc_state.z["theta_base"])[c], s1.hmc_state.z["theta_base"]), (step, c)
+            assert np.array_equal(np.asarray(sv.rng_key)[c], s1.rng_key)
+            assert int(np.asarray(sv.hmc_state.num_steps)[c]) == int(s1.hmc_state.num_steps)
+        sv = kv.sample(sv, args, kwargs)
+        singles = [(k1, k1.sample(s1, args, kwargs)) for k1, s1 in singles]
+
+
+@pytest.mark.gpu
 def test_cuda_hmcgibbs_posterior():
     """tier 4: HMC-within-Gibbs samples the same posterior as NUTS on the full model
     (``test_hmc_gibbs.py`` style: moments, here against the plain CUDA NUTS run)."""
