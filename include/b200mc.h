@@ -47,7 +47,12 @@ enum { B200MC_LOGISTIC = 0, B200MC_EIGHT_SCHOOLS = 1, B200MC_HORSESHOE = 2, B200
        /* test/infer/test_mcmc.py:283-288: p ~ Dirichlet(c[N]), obs ~ Categorical(p); flat
         * dimension N - 1 (StickBreakingTransform); data0 = class counts[N] float32, data1 =
         * c[N] followed by sum lgamma(c) - lgamma(sum c), float32 */
-       B200MC_DIRICHLET_CATEGORICAL = 7 };
+       B200MC_DIRICHLET_CATEGORICAL = 7,
+       /* GLMs on a dense design matrix: coefs ~ Normal(0, 1)[ncols]; likelihood 0: obs ~
+        * Poisson(exp(X coefs)); likelihood 1: prec_obs ~ Gamma(3, 1), obs ~ Normal(X coefs,
+        * prec_obs^-1/2).  data0 = X[N][ncols] float32 row-major, data1 = y[N] float32 followed
+        * by one float32: sum_i lgamma(y_i + 1) (Poisson; anything for Normal) */
+       B200MC_GLM = 8 };
 enum { B200MC_NUTS = 0, B200MC_HMC = 1 };
 
 /* Arguments of NUTS.__init__/HMC.__init__ (hmc.py:625-642, 913-930) + MCMC's

@@ -188,9 +188,18 @@ static int family_sites(const b200mc_config& c, SamplerParams& P, int& D) {
       if (nrm) { P.site_off[3] = Dh; P.site_size[3] = 1; }
       return 0;
     }
+    case B200MC_GLM: {  // trace: coefs(, prec_obs) == sorted
+      const int nrm = c.likelihood == 1 ? 1 : 0;
+      if (c.ncols < 1) return fail("glm: ncols must be >= 1");
+      D = c.ncols + nrm;
+      P.nsites = 1 + nrm;
+      P.site_off[0] = 0; P.site_size[0] = c.ncols;
+      if (nrm) { P.site_off[1] = c.ncols; P.site_size[1] = 1; }
+      return 0;
+    }
     default:
       return fail("model family %d is not a registered potential family (logistic=0, "
-                  "eight_schools=1, horseshoe=2, stochastic_volatility=3, logistic_ecs=4, eight_schools_locscale=5, beta_bernoulli=6, dirichlet_categorical=7); no fallback", c.family);
+                  "eight_schools=1, horseshoe=2, stochastic_volatility=3, logistic_ecs=4, eight_schools_locscale=5, beta_bernoulli=6, dirichlet_categorical=7, glm=8); no fallback", c.family);
   }
 }
 
@@ -686,9 +695,17 @@ extern "C" int b200mc_create(const b200mc_config* cfg, b200mc_handle** out) {
       if (!c.data1_dev) { b200mc_destroy(h); return fail("horseshoe: Y missing"); }
       if (!batch) ACK(alloc((void**)&h->M.scratch, sizeof(float) * (size_t)C * c.N));
     }
+    if (c.family == B200MC_GLM) {
+      if (!c.data1_dev) { b200mc_destroy(h); return fail("glm: y missing"); }
+      ACK(alloc((void**)&h->M.scratch, sizeof(float) * (size_t)C * c.N));
+    }
     // thread per chain (tiny D, diagonal mass), warp per chain, CTA per chain; or the
     // lock-step tensor-core engine (batch_kernel.cuh)
     h->mode = batch ? 3 : ((D <= 32 && !c.dense_mass) ? 0 : (D <= 512 ? 1 : 2));
+    // a GLM's potential is N x ncols work: a warp per chain from a few thousand products on,
+    // a CTA per chain beyond that, whatever D is
+    if (c.family == B200MC_GLM && (long)c.N * c.ncols >= 2048)
+      h->mode = ((long)c.N * c.ncols >= 65536 || D > 512) ? 2 : 1;
     if (c.family == B200MC_LOGISTIC_ECS) {
       const int m = c.subsample_size, deg = c.ecs_degree;
       if (!c.data0_dev || !c.data1_dev) { b200mc_destroy(h); return fail("logistic_ecs: data missing"); }

@@ -16,7 +16,7 @@ namespace b200mc {
 
 enum Family { FAM_LOGISTIC = 0, FAM_EIGHT_SCHOOLS = 1, FAM_HORSESHOE = 2, FAM_SV = 3,
               FAM_LOGISTIC_ECS = 4, FAM_EIGHT_SCHOOLS_LOCSCALE = 5,
-              FAM_BETA_BERNOULLI = 6, FAM_DIRICHLET_CATEGORICAL = 7 };
+              FAM_BETA_BERNOULLI = 6, FAM_DIRICHLET_CATEGORICAL = 7, FAM_GLM = 8 };
 constexpr int kEcsSlices = 4;  // row slices of the subsample in the gradient sweep
 
 struct ModelData {
@@ -721,6 +721,87 @@ __device__ inline float logistic_ecs_potential_cta(const ModelData& M, const Blo
   return U;
 }
 
+// Generalised linear models on a dense design matrix: coefs ~ Normal(0, 1)[ncols],
+//   likelihood 0: obs ~ Poisson(rate = exp(X coefs))      (discrete.py:743: log(rate) y - lgamma(y + 1) - rate)
+//   likelihood 1: prec_obs ~ Gamma(3, 1), obs ~ Normal(X coefs, prec_obs^-1/2)   (the horseshoe example's
+//                 observation model, horseshoe_regression.py:60-66, without the shrinkage prior)
+// z = [coefs (, log prec_obs)].  a = X[N][ncols] row-major, b = y[N] followed by ONE float: the sum
+// over rows of lgamma(y + 1) (Poisson; constant in z, computed once by the binding).  Rows are
+// swept like the horseshoe's: residuals dU/dmean_i parked in the chain's scratch row, then the
+// transposed sweep.
+template <class G>
+__device__ float glm_potential(const ModelData& M, const G& g, const float* z, int zs, float* grad,
+                               int gs, int chain) {
+  const int Dc = M.ncols, N = M.N;
+  const bool normal = M.likelihood == 1;
+  g.sync();
+  float pu = 0.f, prec = 1.f;
+  if (normal) {
+    pu = z[(long)Dc * zs];
+    prec = expf(pu);
+  }
+  float lp = 0.f;
+  for (int d = g.lane(); d < Dc; d += g.size()) {
+    const float t = z[(long)d * zs];
+    lp += -0.5f * t * t - B200MC_LOG_SQRT_2PI;
+  }
+  float* res = M.scratch + (long)chain * N;
+  float lt = 0.f;  // Poisson: sum of rate - mean y; Normal: sum of squared residuals
+  auto row_term = [&](int i, float m) {
+    const float yv = M.b[i];
+    if (normal) {
+      const float r = yv - m;
+      lt += r * r;
+      res[i] = -(prec * r);
+    } else {
+      const float e = expf(m);
+      lt += e - m * yv;
+      res[i] = e - yv;
+    }
+  };
+  if constexpr (G::kBlockWide) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int i = wid; i < N; i += nw) {  // warp per row: coalesced lines of X
+      const float* x = M.a + (long)i * Dc;
+      float m = 0.f;
+      for (int d = lane; d < Dc; d += 32) m = fmaf(__ldg(x + d), z[(long)d * zs], m);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) m += __shfl_xor_sync(0xffffffffu, m, o);
+      if (lane == 0) row_term(i, m);
+    }
+  } else {
+    for (int i = g.lane(); i < N; i += g.size()) {
+      const float* x = M.a + (long)i * Dc;
+      float m = 0.f;
+      for (int d = 0; d < Dc; ++d) m = fmaf(x[d], z[(long)d * zs], m);
+      row_term(i, m);
+    }
+  }
+  g.sync();
+  for (int d = g.lane(); d < Dc; d += g.size()) {  // dU/dcoefs_d = coefs_d + sum_i X[i][d] res_i
+    const float* col = M.a + d;
+    float a0 = 0.f, a1 = 0.f;
+    int i = 0;
+    for (; i + 1 < N; i += 2) {
+      a0 = fmaf(__ldg(col + (long)i * Dc), res[i], a0);
+      a1 = fmaf(__ldg(col + (long)(i + 1) * Dc), res[i + 1], a1);
+    }
+    if (i < N) a0 = fmaf(__ldg(col + (long)i * Dc), res[i], a0);
+    grad[(long)d * gs] = z[(long)d * zs] + (a0 + a1);
+  }
+  g.sum2(lp, lt);
+  const float fN = (float)N;
+  if (normal) {
+    lp += (2.0f * pu - prec - 0.6931471805599453f) + pu;  // Gamma(3, 1) + log|J|
+    lp += -0.5f * prec * lt - fN * B200MC_LOG_SQRT_2PI + 0.5f * fN * pu;
+    if (g.lane() == 0) grad[(long)Dc * gs] = -(3.0f - prec) + 0.5f * prec * lt - 0.5f * fN;
+  } else {
+    lp -= lt + M.b[N];
+  }
+  g.sync();
+  return -lp;
+}
+
 template <class G>
 __device__ __forceinline__ float family_potential(const ModelData& M, const G& g, const float* z,
                                                   int zs, float* grad, int gs, int chain,
@@ -728,6 +809,7 @@ __device__ __forceinline__ float family_potential(const ModelData& M, const G& g
   if (M.family == FAM_EIGHT_SCHOOLS) return eight_schools_potential(M, g, z, zs, grad, gs);
   if (M.family == FAM_HORSESHOE) return horseshoe_potential(M, g, z, zs, grad, gs, chain);
   if (M.family == FAM_DIRICHLET_CATEGORICAL) return dirichlet_categorical_potential(M, g, z, zs, grad, gs);
+  if (M.family == FAM_GLM) return glm_potential(M, g, z, zs, grad, gs, chain);
   if (M.family == FAM_BETA_BERNOULLI) return beta_bernoulli_potential(M, g, z, zs, grad, gs);
   if (M.family == FAM_EIGHT_SCHOOLS_LOCSCALE) return eight_schools_locscale_potential(M, g, z, zs, grad, gs);
   if constexpr (G::kBlockWide) {  // HMCECS handles run CTA per chain only (api.cu)

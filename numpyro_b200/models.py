@@ -15,6 +15,7 @@ import numpy as np
 
 LOGISTIC, EIGHT_SCHOOLS, HORSESHOE, SV, LOGISTIC_ECS, EIGHT_SCHOOLS_LOCSCALE, BETA_BERNOULLI = 0, 1, 2, 3, 4, 5, 6
 DIRICHLET_CATEGORICAL = 7
+GLM = 8
 
 
 class BoundModel:
@@ -275,6 +276,38 @@ def _bind_dirichlet_categorical(data, concentration=(1.0, 1.0, 1.0)):
     return bound
 
 
+def _bind_glm(likelihood):
+    """GLMs on a dense design matrix: ``coefs ~ Normal(0, 1)[D]`` and
+    ``obs ~ Poisson(exp(data @ coefs))`` (likelihood 0) or ``prec_obs ~ Gamma(3, 1)``,
+    ``obs ~ Normal(data @ coefs, prec_obs ** -0.5)`` (likelihood 1)."""
+    def bind(data, obs):
+        import math
+
+        X = np.ascontiguousarray(data, np.float32)
+        y = np.ascontiguousarray(obs, np.float32)
+        if X.ndim != 2 or y.shape != (X.shape[0],):
+            raise ValueError("expects data [N, D] and observations [N]")
+        N, D = X.shape
+        const = 0.0
+        if likelihood == 0:
+            if (y < 0).any() or (y != np.round(y)).any():
+                raise ValueError("poisson_regression expects non-negative integer counts")
+            const = sum(math.lgamma(float(v) + 1.0) for v in y)  # discrete.py:743, constant in z
+        table = np.concatenate([y, [np.float32(const)]]).astype(np.float32)
+        sites = [("coefs", (D,))] + ([("prec_obs", ())] if likelihood else [])
+
+        def constrain(z):
+            out = {"coefs": z["coefs"]}
+            if likelihood:
+                out["prec_obs"] = np.exp(z["prec_obs"])
+            return out
+
+        return BoundModel(GLM, "poisson_regression" if likelihood == 0 else "linear_regression", N, D, X,
+                          table, sites, constrain, likelihood=likelihood,
+                          positive=("prec_obs",) if likelihood else ())
+    return bind
+
+
 def _bind_sv(returns):
     r = np.ascontiguousarray(returns, np.float32)
     T = r.shape[0]
@@ -339,8 +372,16 @@ horseshoe_normal = RegisteredModel(
     "horseshoe_normal", _bind_horseshoe(1),
     "Horseshoe regression, Normal likelihood (examples/horseshoe_regression.py:37-58)")
 
+poisson_regression = RegisteredModel(
+    "poisson_regression", _bind_glm(0),
+    "coefs ~ Normal(0, 1)[D]; obs ~ Poisson(exp(data @ coefs))")
+linear_regression = RegisteredModel(
+    "linear_regression", _bind_glm(1),
+    "coefs ~ Normal(0, 1)[D]; prec_obs ~ Gamma(3, 1); obs ~ Normal(data @ coefs, prec_obs ** -0.5)")
+
 REGISTRY = {m.__name__: m for m in (logistic_regression, eight_schools_noncentered, eight_schools,
-                                    beta_bernoulli, dirichlet_categorical,
+                                    beta_bernoulli, dirichlet_categorical, poisson_regression,
+                                    linear_regression,
                                     stochastic_volatility, horseshoe_bernoulli,
                                     horseshoe_normal)}
 

@@ -228,6 +228,71 @@ class EightSchoolsLocScale(Family):
         return out
 
 
+# --------------------------------------------------------------------------
+# GLMs on a dense design matrix
+# --------------------------------------------------------------------------
+class PoissonGLM(Family):
+    """coefs ~ Normal(0, 1)[D]; obs ~ Poisson(rate = exp(X @ coefs)).
+
+    ``Poisson.log_prob`` (``discrete.py:743``): ``log(rate) * y - gammaln(y + 1) - rate``."""
+
+    name = "poisson_regression"
+
+    def __init__(self, X, y, dtype=np.float32):
+        super().__init__(dtype)
+        self.X = np.ascontiguousarray(X, dtype=self.dtype)
+        self.y = np.ascontiguousarray(y).astype(self.dtype)
+        self.trace_sites = (("coefs", self.X.shape[1]),)
+        self._lg = _lgamma(self.y.astype(np.float64) + 1.0)
+
+    def potential_and_grad(self, z):
+        f = self.dtype.type
+        z = np.asarray(z, self.dtype)
+        prior = (f(0.5) * z * z + f(LOG_SQRT_2PI)).sum(dtype=self.dtype)
+        rate = np.exp(self.X @ z)
+        lp = (np.log(rate) * self.y - self._lg.astype(self.dtype) - rate).sum(dtype=self.dtype)
+        grad = z + self.X.T @ (rate - self.y)
+        return f(prior - lp), grad.astype(self.dtype)
+
+    def constrain(self, z):
+        return {"coefs": np.asarray(z)}
+
+
+class NormalGLM(Family):
+    """coefs ~ Normal(0, 1)[D]; prec_obs ~ Gamma(3, 1) through ExpTransform;
+    obs ~ Normal(X @ coefs, prec_obs ** -0.5) (the observation model of
+    ``examples/horseshoe_regression.py:60-66``).  z = [coefs, log prec_obs]."""
+
+    name = "linear_regression"
+
+    def __init__(self, X, y, dtype=np.float32):
+        super().__init__(dtype)
+        self.X = np.ascontiguousarray(X, dtype=self.dtype)
+        self.y = np.ascontiguousarray(y).astype(self.dtype)
+        self.trace_sites = (("coefs", self.X.shape[1]), ("prec_obs", 1))
+
+    def potential_and_grad(self, z):
+        f = self.dtype.type
+        z = np.asarray(z, self.dtype)
+        D, N = self.X.shape[1], self.X.shape[0]
+        b, pu = z[:D], z[D]
+        prec = np.exp(pu)
+        lp = (-f(0.5) * b * b - f(LOG_SQRT_2PI)).sum(dtype=self.dtype)
+        # Gamma(3, 1).log_prob(prec) = 2 log prec - prec - lgamma(3); + log|J| = pu
+        lp = lp + (f(2) * pu - prec - f(math.log(2.0))) + pu
+        r = self.y - self.X @ b
+        ss = (r * r).sum(dtype=self.dtype)
+        lp = lp + (-f(0.5) * prec * ss - f(N) * f(LOG_SQRT_2PI) + f(0.5) * f(N) * pu)
+        g = np.empty_like(z)
+        g[:D] = b + self.X.T @ (-(prec * r))
+        g[D] = -(f(3) - prec) + f(0.5) * prec * ss - f(0.5) * f(N)
+        return f(-lp), g.astype(self.dtype)
+
+    def constrain(self, z):
+        z = np.asarray(z)
+        return {"coefs": z[..., :-1], "prec_obs": np.exp(z[..., -1])}
+
+
 class BetaBernoulli(Family):
     """``p_latent ~ Beta(alpha, beta)[K]``; ``obs[n, K] ~ Bernoulli(p_latent)``
     (``test/infer/test_mcmc.py:239-244``).  z = logit(p) (``SigmoidTransform``, clipped expit
