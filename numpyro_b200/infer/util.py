@@ -34,6 +34,12 @@ def _site_plan(model, draws, args, kwargs):
         scale = f32(1.0 / np.sqrt(np.asarray(draws["prec_obs"], np.float32))).reshape(S) if normal else None
         return dict(site="Y", X=X, B=betas, scale=scale, scale_kind=1 if normal else 0, df=None, y=y,
                     likelihood=_NORMAL if normal else _BERNOULLI, N=X.shape[0], det={"betas": betas})
+    if name == "linear_regression":  # the Normal GLM: the horseshoe example's observation model on coefs
+        X = f32(args[0])
+        y = None if len(args) < 2 or args[1] is None else f32(args[1])
+        scale = f32(1.0 / np.sqrt(np.asarray(draws["prec_obs"], np.float32))).reshape(S)
+        return dict(site="obs", X=X, B=f32(draws["coefs"]).reshape(S, X.shape[1]), scale=scale, scale_kind=1,
+                    df=None, y=y, likelihood=_NORMAL, N=X.shape[0], det={})
     if name == "eight_schools_noncentered":
         sigma = f32(args[1])
         y = kwargs.get("y", args[2] if len(args) > 2 else None)

@@ -72,6 +72,12 @@ def main():
             c = constrain_fn(model, args, {}, sites, return_deterministic=True)
             for k, v in c.items():
                 out[f"{name}/constrained/{k}"] = np.asarray(v, np.float32)
+            if name == "normal":  # log_likelihood (infer/util.py:1094-1148) over the four points as draws
+                from numpyro.infer.util import log_likelihood
+
+                samples = {"coefs": W(pts[:, :6]), "prec_obs": W(np.exp(pts[:, 6]).astype(np.float32))}
+                ll = log_likelihood(model, samples, *args)
+                out["normal/loglik"] = np.asarray(ll["obs"], np.float32)
             for part in (True, False):
                 refshim.PARTITIONABLE = part
                 for seed in (0, 1, 2):

@@ -100,3 +100,36 @@ def test_cuda_glm_potential_init_and_posterior(fx, name):
     r, _ = ohmc.run_chain(ohmc.HMCKernel(fam, cfg=Config(np.float32, True), **kw), key, 0, 8)
     assert np.array_equal(mc.get_extra_fields()["num_steps"], r["num_steps"])
     np.testing.assert_allclose(mc.get_extra_fields()["potential_energy"], r["potential_energy"], rtol=2e-4)
+
+
+def _normal_loglik(fx):
+    z = fx["normal/z"]
+    prec = np.exp(z[:, 6:7]).astype(np.float32)
+    m = z[:, :6] @ fx["X"].T
+    sig = (np.float32(1) / np.sqrt(prec)).astype(np.float32)
+    return -0.5 * ((fx["y"][None] - m) / sig) ** 2 - np.log(sig) - 0.5 * np.log(2 * np.pi)
+
+
+def test_log_likelihood_formula_matches_reference(fx):
+    np.testing.assert_allclose(_normal_loglik(fx), fx["normal/loglik"], rtol=2e-5, atol=2e-5)
+
+
+@pytest.mark.gpu
+def test_cuda_log_likelihood_and_predictive_linear_regression(fx):
+    """``log_likelihood`` (``infer/util.py:1094-1148``) of the Normal GLM over draws, against the
+    reference's own; ``Predictive`` samples the observation site around ``data @ coefs``."""
+    import __graft_entry__ as g
+
+    nb = g.build()
+    z = fx["normal/z"]
+    samples = {"coefs": z[:, :6], "prec_obs": np.exp(z[:, 6]).astype(np.float32)}
+    ll = nb.infer.log_likelihood(nb.models.linear_regression, samples, fx["X"], fx["y"])["obs"]
+    np.testing.assert_allclose(ll, fx["normal/loglik"], rtol=2e-5, atol=2e-5)
+    big = {"coefs": np.repeat(z[:1, :6], 2000, 0), "prec_obs": np.full(2000, 6.25, np.float32)}
+    pred = nb.infer.Predictive(nb.models.linear_regression, posterior_samples=big)(
+        np.asarray(PRNGKey(4), np.uint32), fx["X"], None)["obs"]
+    assert pred.shape == (2000, 400)
+    np.testing.assert_allclose(pred.mean(0), fx["X"] @ z[0, :6], atol=0.06)
+    np.testing.assert_allclose(pred.std(0), 0.4, rtol=0.1)
+    with pytest.raises(NotImplementedError):
+        nb.infer.log_likelihood(nb.models.poisson_regression, {"coefs": z[:, :6]}, fx["X"], fx["counts"])
