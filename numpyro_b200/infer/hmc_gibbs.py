@@ -209,7 +209,15 @@ class HMCGibbs(MCMCKernel):
         state = self.__dict__.copy()
         state["_prototype_trace"] = None
         state["_sample_fn"] = None
+        state["_model0"] = self._model0.__name__  # registry entries hold closures: pickle by name
         return state
+
+    def __setstate__(self, state):
+        self.__dict__.update(state)
+        if isinstance(self._model0, str):
+            self._model0 = models.lookup(self._model0)
+        if self._gibbs_fn is not _identity:  # the inner kernel came back with the plain model
+            self.inner_kernel._model = _ConditionedModel(self._model0, self._gibbs_sites)
 
 
 class HMCECS(HMCGibbs):

@@ -190,6 +190,51 @@ def test_kernel_pickles_after_binding_a_model(nb):
         assert m2.num_samples == 4 and m2.sampler._model is model
 
 
+def _pickle_gibbs_fn(rng_key, gibbs_sites, hmc_sites):
+    return {"mu": np.float32(0)}
+
+
+def test_hmcgibbs_and_hmcecs_pickle(nb):
+    # hmc_gibbs.py:187-190: the wrappers pickle too; the inner kernel comes back seeing the model
+    # with the Gibbs sites conditioned
+    import pickle
+
+    from numpyro_b200 import models
+    from numpyro_b200.infer import HMCECS, HMCGibbs, NUTS
+
+    k = HMCGibbs(NUTS(models.eight_schools_noncentered, max_tree_depth=6), _pickle_gibbs_fn, ["mu"])
+    k._prototype_trace = [{"mu": np.float32(1)}]
+    k2 = pickle.loads(pickle.dumps(k))
+    assert k2._prototype_trace is None and k2._model0 is models.eight_schools_noncentered
+    view = k2.inner_kernel._model.bind(8, np.ones(8, np.float32), y=np.zeros(8, np.float32))
+    assert view.dim == 9 and list(view.cond_index) == [0] and "mu" not in view.flat_sites
+    e2 = pickle.loads(pickle.dumps(HMCECS(NUTS(models.logistic_regression), num_blocks=5)))
+    assert e2.inner_kernel._model is models.logistic_regression and e2._num_blocks == 5
+
+
+def test_conditioned_view_of_a_bound_model():
+    """``BoundModel.condition`` (the registered-family form of ``hmc_gibbs.py:30-34``)."""
+    import pytest
+
+    from numpyro_b200 import models
+
+    full = models.eight_schools_noncentered.bind(8, np.ones(8, np.float32), y=np.zeros(8, np.float32))
+    v = full.condition(["tau"])
+    assert v.dim == 9 and list(v.cond_index) == [1] and v.positive == ()
+    assert [k for k, _ in v.trace_sites] == ["mu", "theta_base"]
+    flat, off = v.cond_unconstrained({"tau": np.float32(2.0)})
+    np.testing.assert_allclose(flat, [np.log(2.0)], rtol=1e-6)
+    np.testing.assert_allclose(off, np.log(2.0), rtol=1e-6)  # log|J| of ExpTransform at the value
+    v2 = full.condition(["mu", "theta_base"])
+    assert v2.dim == 1 and list(v2.cond_index) == [0] + list(range(2, 10)) and v2.positive == ("tau",)
+    with pytest.raises(ValueError):
+        full.condition(["nope"])
+    with pytest.raises(ValueError):
+        full.condition(["mu", "tau", "theta_base"])
+    with pytest.raises(NotImplementedError):
+        models.logistic_regression.bind(np.zeros((4, 3), np.float32), np.zeros(4)).condition(["coefs"])
+
+
 def test_nuts_alone_refuses_a_subsampled_plate():
     """primitives.py:444-449: without HMCECS nothing owns the subsample indices."""
     import numpy as np
