@@ -94,6 +94,32 @@ def main():
                 for k, v in rows.items():
                     out[f"{tag}/{k}"] = np.asarray(v)
                 print(tag, "tree sizes", rows["num_steps"], "mu[-1]", rows["mu"][-1])
+        # HMC as the inner kernel
+        from numpyro.infer import HMC
+
+        refshim.PARTITIONABLE = True
+        cur["fam"] = Conditioned(fam_full, ["mu"], positive=("tau",))
+        kernel = hg.HMCGibbs(HMC(model, **gc.HMC_KW), gibbs_fn=gibbs_fn, gibbs_sites=["mu"])
+        state = kernel.init(W(PRNGKey(gc.HMC_SEED)), gc.HMC_WARMUP, None, args, kwargs)
+        rows = {k: [] for k in ("mu", "z", "pe", "num_steps", "rng_key", "step_size", "accept_prob")}
+
+        def rec2(st):
+            h = st.hmc_state
+            rows["mu"].append(np.asarray(st.z["mu"], np.float32))
+            rows["z"].append(np.concatenate([np.ravel(np.asarray(h.z[k], np.float32)) for k in sorted(h.z)]))
+            rows["pe"].append(np.float32(np.asarray(h.potential_energy)))
+            rows["num_steps"].append(int(np.asarray(h.num_steps)))
+            rows["rng_key"].append(np.asarray(st.rng_key, np.uint32))
+            rows["step_size"].append(np.float32(np.asarray(h.adapt_state.step_size)))
+            rows["accept_prob"].append(np.float32(np.asarray(h.accept_prob)))
+
+        rec2(state)
+        for _ in range(gc.HMC_STEPS):
+            state = kernel.sample(state, args, kwargs)
+            rec2(state)
+        for k, v in rows.items():
+            out[f"hmc/{k}"] = np.asarray(v)
+        print("hmc inner: accept", rows["accept_prob"], "mu[-1]", rows["mu"][-1])
         # the conditioned potential itself, reference model code only
         refshim.PARTITIONABLE = True
         wrapped = hg.partial(real_wrap, model) if hasattr(hg, "partial") else None

@@ -10,6 +10,9 @@ import refpin_cases as rc
 NUM_WARMUP, NUM_STEPS = 12, 22
 SEEDS = (0, 1)
 KERNEL_KW = dict(max_tree_depth=6)
+# the same wrapper around HMC (test_hmc_gibbs.py parametrises its models over [HMC, NUTS])
+HMC_KW = dict(trajectory_length=0.4, step_size=0.02)
+HMC_SEED, HMC_WARMUP, HMC_STEPS = 3, 6, 14
 
 
 def make_gibbs_fn(normal, wrap=lambda v: v):

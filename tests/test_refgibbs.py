@@ -71,6 +71,25 @@ def test_oracle_hmcgibbs_matches_reference_state_by_state(fx, part, seed):
                           fx[f"{tag}/step_size"])
 
 
+def test_oracle_hmcgibbs_around_hmc_matches_reference(fx):
+    """The wrapper around ``HMC`` (fixed trajectory length, step size adapted over 6 transitions)."""
+    cfg = Config(np.float32, True)
+    k = ogibbs.HMCGibbs(
+        opot.EightSchools(rc.S8, rc.Y8), gc.make_gibbs_fn(lambda key: cfg.normal(key, ())), ["mu"],
+        prior_sample=lambda name, key, c: gc.prior_sample_mu(c.normal(key, (1,))),
+        positive=("tau",), cfg=cfg, algo="HMC", **gc.HMC_KW)
+    st = k.init(PRNGKey(gc.HMC_SEED), gc.HMC_WARMUP)
+    states = [st]
+    for _ in range(gc.HMC_STEPS):
+        st = k.sample(st)
+        states.append(st)
+    assert np.array_equal([s.hmc_state.num_steps for s in states], fx["hmc/num_steps"])
+    assert np.array_equal(np.stack([s.hmc_state.z for s in states]), fx["hmc/z"])
+    assert np.array_equal(np.array([s.z["mu"] for s in states], np.float32), fx["hmc/mu"])
+    assert np.array_equal(np.array([s.hmc_state.accept_prob for s in states], np.float32), fx["hmc/accept_prob"])
+    assert np.array_equal(np.stack([np.asarray(s.rng_key, np.uint32) for s in states]), fx["hmc/rng_key"])
+
+
 # ---------------------------------------------------------------------------------------- CUDA
 def _cuda_kernel(nb, part):
     from numpyro_b200 import random as b2random
@@ -137,6 +156,28 @@ def test_cuda_hmcgibbs_matches_reference(fx, part):
                 np.testing.assert_allclose(np.float32(st.z["mu"]), fx[f"{tag}/mu"][i], rtol=2e-3, atol=2e-3)
                 np.testing.assert_allclose(st.hmc_state.potential_energy, fx[f"{tag}/pe"][i], rtol=1e-3)
         assert n_same >= 5, (tag, n_same)
+
+
+@pytest.mark.gpu
+def test_cuda_hmcgibbs_around_hmc_matches_reference(fx):
+    import __graft_entry__ as g
+    from numpyro_b200 import random as b2random
+
+    nb = g.build()
+    args, kwargs = (8, rc.S8), {"y": rc.Y8}
+    inner = nb.infer.HMC(nb.models.eight_schools_noncentered, **gc.HMC_KW)
+    k = nb.infer.HMCGibbs(inner, gc.make_gibbs_fn(lambda key: b2random.normal(key, (), True)), ["mu"])
+    st = k.init(np.asarray(PRNGKey(gc.HMC_SEED), np.uint32), gc.HMC_WARMUP, None, args, kwargs)
+    view = k.inner_kernel._bound
+    assert np.array_equal(view.ravel(st.hmc_state.z), fx["hmc/z"][0])
+    assert np.array_equal(np.float32(st.z["mu"]), fx["hmc/mu"][0])
+    for i in range(1, gc.HMC_STEPS + 1):
+        st = k.sample(st, args, kwargs)
+        assert np.array_equal(np.asarray(st.rng_key, np.uint32), fx["hmc/rng_key"][i])
+        assert int(st.hmc_state.num_steps) == int(fx["hmc/num_steps"][i])
+        tol = 2e-3 if i <= 5 else 3e-2  # no tree decisions to flip: the runs drift by round-off only
+        np.testing.assert_allclose(view.ravel(st.hmc_state.z), fx["hmc/z"][i], rtol=tol, atol=tol)
+        np.testing.assert_allclose(st.hmc_state.accept_prob, fx["hmc/accept_prob"][i], atol=max(tol, 5e-3))
 
 
 @pytest.mark.gpu
